@@ -1,0 +1,137 @@
+/*
+ * lammcu.h -- C-ABI of the B200 (sm_100a) quantized mul_mat device library
+ * (liblammcu.so).  Plain pointers and sizes only; no C++ or torch types.
+ *
+ * This is the boundary the reference's host code binds to.  It replaces the
+ * CPU kernels behind src/loongarch_matmul.cpp:64-143 (lamm_mul_mat) and the
+ * activation quantize of llama.cpp-b2430/ggml.c:10865-10887:
+ *
+ *   reference (CPU)                                  here (CUDA)
+ *   ------------------------------------------------ ---------------------------
+ *   from_float_to_vec_dot / quantize_row_q8_{0,1,K}   lammcu_quantize_act_dev
+ *     ggml-quants.c:1207,1431,4031
+ *   LAMMImpl<T>::matmul  src/lamm_impl.hpp:20-29      lammcu_mul_mat_q_dev
+ *     + lamm_kernel_*.hpp                              lammcu_mul_mat_dev (fused)
+ *   ggml type_traits rows  ggml.c:458-775             lammcu_{blck,type,row}_size,
+ *   ggml_type_trait<T>  src/lamm_ggml_type_trait.h     lammcu_vec_dot_type
+ *   lamm_mul_mat on host tensors                      lammcu_weight_register +
+ *     src/loongarch_matmul.cpp:64-143                  lammcu_mul_mat_host
+ *
+ * Data layouts are ggml's, unchanged (llama.cpp-b2430/ggml-common.h:144-225,
+ * 316-321): W is M rows of K/QK packed blocks, row stride in bytes; X is N rows
+ * of K f32; Xq is N rows of vec-dot blocks packed at lammcu_row_size(); C is N
+ * rows of M f32, C[j*ldc + i] (src/lamm_kernel_q4_1.hpp:24).
+ *
+ * All functions return LAMMCU_OK (0) or a negative lammcu_status; the message
+ * of the last failure on the calling thread is lammcu_last_error().  There is
+ * no CPU fallback: without a CUDA device every compute entry point fails with
+ * LAMMCU_ERR_NO_DEVICE.
+ *
+ * `stream` arguments are a cudaStream_t passed as void* (NULL = the library's
+ * own stream for the current device).  *_dev entry points are asynchronous on
+ * that stream; *_host entry points return after the result is in host memory.
+ */
+#ifndef LAMMCU_H
+#define LAMMCU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  LAMMCU_OK = 0,
+  LAMMCU_ERR_NO_DEVICE = -1,   /* no CUDA device / driver                      */
+  LAMMCU_ERR_CUDA = -2,        /* a CUDA runtime call failed                   */
+  LAMMCU_ERR_TYPE = -3,        /* ggml type not on the path                    */
+  LAMMCU_ERR_SHAPE = -4,       /* K not a multiple of the block size, M/N<=0.. */
+  LAMMCU_ERR_ALIGN = -5,       /* pointer / stride alignment not supported     */
+  LAMMCU_ERR_ARG = -6,         /* NULL pointer, bad handle                     */
+  LAMMCU_ERR_NOMEM = -7
+} lammcu_status;
+
+/* ggml type ids accepted (llama.cpp-b2430/ggml.h:341-369) */
+enum {
+  LAMMCU_TYPE_F32 = 0, LAMMCU_TYPE_Q4_0 = 2, LAMMCU_TYPE_Q4_1 = 3,
+  LAMMCU_TYPE_Q5_0 = 6, LAMMCU_TYPE_Q5_1 = 7, LAMMCU_TYPE_Q8_0 = 8,
+  LAMMCU_TYPE_Q8_1 = 9, LAMMCU_TYPE_Q2_K = 10, LAMMCU_TYPE_Q8_K = 15
+};
+
+/* ---- library / device ------------------------------------------------- */
+const char *lammcu_version(void);
+const char *lammcu_last_error(void);
+int lammcu_device_count(void);              /* >=0, or negative status         */
+int lammcu_init(int device);                /* select device, create stream    */
+int lammcu_shutdown(void);                  /* free weights, workspaces        */
+int lammcu_sm_count(void);
+/* number of kernels this library has launched since load (bench's
+ * gpu_launches); lammcu_launch_count_reset() zeroes it                      */
+uint64_t lammcu_launch_count(void);
+void lammcu_launch_count_reset(void);
+
+/* ---- type table (pure host functions, no device needed) ---------------- */
+int    lammcu_type_supported(int w_type);   /* 1 if lamm_can_mul_mat's table has it */
+int    lammcu_blck_size(int type);
+size_t lammcu_type_size(int type);
+int    lammcu_vec_dot_type(int w_type);
+size_t lammcu_row_size(int type, int64_t k);
+
+/* ---- device-resident operands ------------------------------------------ */
+/* X f32 [n_rows, k] (row stride ldx elements) -> Xq packed at row_size.
+ * Bit-exact with quantize_row_q8_{0,1,K}_reference; Q8_K bsums of an all-zero
+ * super-block are written as 0 (the reference leaves them untouched).        */
+int lammcu_quantize_act_dev(int vec_dot_type, const float *x_dev, int64_t ldx,
+                            void *xq_dev, int64_t n_rows, int64_t k, void *stream);
+
+/* C = W . Xq^T on already quantized activations (what COMPUTE sees).
+ * For LAMMCU_TYPE_F32 weights xq_dev is the f32 X itself.                    */
+int lammcu_mul_mat_q_dev(int w_type, const void *w_dev, int64_t w_stride_bytes,
+                         const void *xq_dev, int64_t xq_stride_bytes,
+                         float *c_dev, int64_t ldc, int64_t M, int64_t N,
+                         int64_t K, void *stream);
+
+/* The whole path on device operands: activation quantize + mul_mat.
+ * xq_ws_dev: caller workspace of >= N*lammcu_row_size(vec_dot,K) bytes, or
+ * NULL to use the library's own (grown on demand, per device).               */
+int lammcu_mul_mat_dev(int w_type, const void *w_dev, int64_t w_stride_bytes,
+                       const float *x_dev, int64_t ldx, float *c_dev,
+                       int64_t ldc, int64_t M, int64_t N, int64_t K,
+                       void *xq_ws_dev, void *stream);
+
+/* Path selection (diagnostics / benchmarking): N <= threshold runs the
+ * memory-bound GEMV kernels, larger N the tensor-core GEMM.  Default 8.      */
+int lammcu_set_gemv_max_n(int n);
+int lammcu_get_gemv_max_n(void);
+
+/* ---- host operands (what lamm_mul_mat passes) --------------------------- */
+typedef struct lammcu_weight *lammcu_weight_t;
+
+/* Upload W once (weights are immutable); rows [row_begin,row_end) only, so a
+ * rank can hold its shard.  Keyed by (host pointer, shard) in a registry so a
+ * second registration of the same tensor returns the same handle.            */
+int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K,
+                           int64_t w_stride_bytes, int64_t row_begin,
+                           int64_t row_end, lammcu_weight_t *out);
+int lammcu_weight_lookup(const void *w_host, lammcu_weight_t *out); /* LAMMCU_ERR_ARG if absent */
+int lammcu_weight_release(lammcu_weight_t w);
+const void *lammcu_weight_dev_ptr(lammcu_weight_t w);
+int64_t lammcu_weight_rows(lammcu_weight_t w);
+
+/* X (host f32, N rows, ldx elements) -> H2D -> quantize -> mul_mat -> D2H into
+ * C (host f32, ldc elements; only the handle's rows [row_begin,row_end) of
+ * every output row are written).  xq_out_host (optional) receives the GPU's
+ * quantized activations, for the bit-exact check.  Synchronous.              */
+int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N,
+                        int64_t ldx, float *c_host, int64_t ldc,
+                        void *xq_out_host);
+/* same, activations already quantized on the host (src1->type == vec_dot_type) */
+int lammcu_mul_mat_q_host(lammcu_weight_t w, const void *xq_host,
+                          int64_t xq_stride_bytes, int64_t N, float *c_host,
+                          int64_t ldc);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LAMMCU_H */

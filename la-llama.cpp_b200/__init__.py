@@ -1,0 +1,224 @@
+"""la-llama.cpp_b200 -- B200 (sm_100a) quantized mul_mat behind the LAMM operator boundary.
+
+Python view of the C-ABI in include/lammcu.h and of the drop-in operator in
+include/lamm_b200.h (`lamm_can_mul_mat` / `lamm_mul_mat` / `lamm_get_opt_level`,
+reference: src/loongarch_matmul.h:18-24).  This module is plumbing only: it loads
+liblammcu.so with ctypes and passes raw pointers; all arithmetic runs in the CUDA
+library.  There is no CPU fallback -- if the library is missing or no B200 is
+visible, compute calls raise `LammError`.
+
+The directory name is not a valid Python identifier; import it through the
+repo-root shim `lamm_b200.py` (``import lamm_b200``).
+"""
+import ctypes as C
+import os
+
+from . import build as _build
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liblammcu.so")
+
+# ggml type ids (llama.cpp-b2430/ggml.h:341-369)
+F32, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0, Q8_1, Q2_K, Q8_K = 0, 2, 3, 6, 7, 8, 9, 10, 15
+TYPE_NAMES = {F32: "f32", Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1",
+              Q8_0: "q8_0", Q8_1: "q8_1", Q2_K: "q2_k", Q8_K: "q8_k"}
+NAME_TO_TYPE = {v: k for k, v in TYPE_NAMES.items()}
+W_TYPES = (F32, Q2_K, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0)      # src/loongarch_matmul.cpp:37-42
+TASK_INIT, TASK_COMPUTE, TASK_FINALIZE = 0, 1, 2
+
+# every symbol include/lammcu.h and include/lamm_b200.h declare
+EXPORTS = [
+    "lammcu_version", "lammcu_last_error", "lammcu_device_count", "lammcu_init", "lammcu_shutdown",
+    "lammcu_sm_count", "lammcu_launch_count", "lammcu_launch_count_reset", "lammcu_type_supported",
+    "lammcu_blck_size", "lammcu_type_size", "lammcu_vec_dot_type", "lammcu_row_size",
+    "lammcu_quantize_act_dev", "lammcu_mul_mat_q_dev", "lammcu_mul_mat_dev", "lammcu_set_gemv_max_n",
+    "lammcu_get_gemv_max_n", "lammcu_weight_register", "lammcu_weight_lookup", "lammcu_weight_release",
+    "lammcu_weight_dev_ptr", "lammcu_weight_rows", "lammcu_mul_mat_host", "lammcu_mul_mat_q_host",
+    "lamm_can_mul_mat", "lamm_mul_mat", "lamm_get_opt_level", "lamm_set_writeback_wdata",
+]
+
+
+class LammError(RuntimeError):
+    pass
+
+
+# ---- ggml structs (include/lamm_b200.h; llama.cpp-b2430/ggml.h:552-590, 668-677) ----
+class GgmlComputeParams(C.Structure):
+    _fields_ = [("type", C.c_int), ("ith", C.c_int), ("nth", C.c_int),
+                ("wsize", C.c_size_t), ("wdata", C.c_void_p)]
+
+
+class GgmlTensor(C.Structure):
+    pass
+
+
+GgmlTensor._fields_ = [
+    ("type", C.c_int), ("backend", C.c_int), ("buffer", C.c_void_p),
+    ("ne", C.c_int64 * 4), ("nb", C.c_size_t * 4), ("op", C.c_int),
+    ("op_params", C.c_int32 * 16), ("flags", C.c_int32),
+    ("grad", C.POINTER(GgmlTensor)), ("src", C.POINTER(GgmlTensor) * 10),
+    ("perf_runs", C.c_int), ("perf_cycles", C.c_int64), ("perf_time_us", C.c_int64),
+    ("view_src", C.POINTER(GgmlTensor)), ("view_offs", C.c_size_t),
+    ("data", C.c_void_p), ("name", C.c_char * 64), ("extra", C.c_void_p), ("padding", C.c_char * 8),
+]
+
+_lib = None
+
+
+def lib():
+    """Load liblammcu.so (building it if the sources are newer).  Raises LammError."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        try:
+            _build.build()
+        except Exception as e:  # no nvcc, compile error
+            raise LammError(f"liblammcu.so is missing and could not be built: {e}") from e
+    try:
+        L = C.CDLL(LIB_PATH)
+    except OSError as e:
+        raise LammError(f"cannot load {LIB_PATH}: {e}") from e
+    i64, vp, fp, sz = C.c_int64, C.c_void_p, C.c_void_p, C.c_size_t
+    L.lammcu_version.restype = C.c_char_p
+    L.lammcu_last_error.restype = C.c_char_p
+    L.lammcu_init.argtypes = [C.c_int]
+    L.lammcu_launch_count.restype = C.c_uint64
+    L.lammcu_launch_count_reset.restype = None
+    L.lammcu_type_size.restype = sz
+    L.lammcu_type_size.argtypes = [C.c_int]
+    L.lammcu_blck_size.argtypes = [C.c_int]
+    L.lammcu_vec_dot_type.argtypes = [C.c_int]
+    L.lammcu_type_supported.argtypes = [C.c_int]
+    L.lammcu_row_size.restype = sz
+    L.lammcu_row_size.argtypes = [C.c_int, i64]
+    L.lammcu_quantize_act_dev.argtypes = [C.c_int, fp, i64, vp, i64, i64, vp]
+    L.lammcu_mul_mat_q_dev.argtypes = [C.c_int, vp, i64, vp, i64, fp, i64, i64, i64, i64, vp]
+    L.lammcu_mul_mat_dev.argtypes = [C.c_int, vp, i64, fp, i64, fp, i64, i64, i64, i64, vp, vp]
+    L.lammcu_set_gemv_max_n.argtypes = [C.c_int]
+    L.lammcu_weight_register.argtypes = [vp, C.c_int, i64, i64, i64, i64, i64, C.POINTER(vp)]
+    L.lammcu_weight_lookup.argtypes = [vp, C.POINTER(vp)]
+    L.lammcu_weight_release.argtypes = [vp]
+    L.lammcu_weight_dev_ptr.restype = vp
+    L.lammcu_weight_dev_ptr.argtypes = [vp]
+    L.lammcu_weight_rows.restype = i64
+    L.lammcu_weight_rows.argtypes = [vp]
+    L.lammcu_mul_mat_host.argtypes = [vp, fp, i64, i64, fp, i64, vp]
+    L.lammcu_mul_mat_q_host.argtypes = [vp, vp, i64, i64, fp, i64]
+    L.lamm_can_mul_mat.restype = C.c_bool
+    L.lamm_can_mul_mat.argtypes = [C.POINTER(GgmlComputeParams), C.POINTER(GgmlTensor)]
+    L.lamm_mul_mat.restype = None
+    L.lamm_mul_mat.argtypes = [C.POINTER(GgmlComputeParams), C.POINTER(GgmlTensor)]
+    L.lamm_set_writeback_wdata.restype = None
+    L.lamm_set_writeback_wdata.argtypes = [C.c_int]
+    _lib = L
+    return L
+
+
+def check(rc, what=""):
+    if rc != 0:
+        raise LammError(f"{what or 'lammcu'} failed ({rc}): {lib().lammcu_last_error().decode()}")
+
+
+def type_size(t):
+    return lib().lammcu_type_size(t)
+
+
+def blck_size(t):
+    return lib().lammcu_blck_size(t)
+
+
+def vec_dot_type(t):
+    return lib().lammcu_vec_dot_type(t)
+
+
+def row_size(t, k):
+    return lib().lammcu_row_size(t, k)
+
+
+def init(device=-1):
+    check(lib().lammcu_init(device), "lammcu_init")
+
+
+# ---- device-tensor helpers (torch = device memory + streams only) -----------------
+def _stream_ptr():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def quantize_act(x, vt):
+    """x: cuda f32 [N, K] (row stride in elements = x.stride(0)) -> cuda uint8 [N, row_size]."""
+    import torch
+    assert x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+    n, k = x.shape
+    out = torch.empty((n, row_size(vt, k)), dtype=torch.uint8, device=x.device)
+    check(lib().lammcu_quantize_act_dev(vt, x.data_ptr(), x.stride(0), out.data_ptr(), n, k, _stream_ptr()),
+          "quantize_act")
+    return out
+
+
+def mul_mat_q(w_type, w, xq, k, out=None):
+    """w: cuda uint8 [M, row bytes] (F32: float32 [M, K]); xq: cuda uint8 [N, row_size(vec_dot)]
+    (F32: float32 [N, K]).  Returns C: cuda f32 [N, M]."""
+    import torch
+    m, n = w.shape[0], xq.shape[0]
+    if out is None:
+        out = torch.empty((n, m), dtype=torch.float32, device=w.device)
+    check(lib().lammcu_mul_mat_q_dev(w_type, w.data_ptr(), w.stride(0) * w.element_size(), xq.data_ptr(),
+                                     xq.stride(0) * xq.element_size(), out.data_ptr(), out.stride(0),
+                                     m, n, k, _stream_ptr()), "mul_mat_q")
+    return out
+
+
+def mul_mat(w_type, w, x, out=None, ws=None):
+    """The whole path on device tensors: fused activation quantize + mul_mat.
+    w: cuda uint8 [M, row bytes] in ggml block layout; x: cuda f32 [N, K]; returns f32 [N, M]."""
+    import torch
+    assert x.is_cuda and x.dtype == torch.float32 and x.stride(1) == 1
+    m, (n, k) = w.shape[0], x.shape
+    if out is None:
+        out = torch.empty((n, m), dtype=torch.float32, device=x.device)
+    check(lib().lammcu_mul_mat_dev(w_type, w.data_ptr(), w.stride(0) * w.element_size(), x.data_ptr(),
+                                   x.stride(0), out.data_ptr(), out.stride(0), m, n, k,
+                                   ws.data_ptr() if ws is not None else None, _stream_ptr()), "mul_mat")
+    return out
+
+
+# ---- the drop-in operator on host (numpy) tensors, as ggml would call it -------------
+def make_tensor_2d(ttype, ne0, ne1, data_ptr, nb1=None):
+    t = GgmlTensor()
+    t.type = ttype
+    t.ne[0], t.ne[1], t.ne[2], t.ne[3] = ne0, ne1, 1, 1
+    ts, bs = type_size(ttype), blck_size(ttype)
+    t.nb[0] = ts
+    t.nb[1] = nb1 if nb1 is not None else ts * (ne0 // bs)
+    t.nb[2] = t.nb[1] * ne1
+    t.nb[3] = t.nb[2]
+    t.data = data_ptr
+    return t
+
+
+def lamm_mul_mat_host(w_type, w_np, x_np, nth=1, wdata=None, task=TASK_COMPUTE):
+    """Build ggml_tensor / ggml_compute_params by hand and drive lamm_can_mul_mat +
+    lamm_mul_mat exactly as ggml.c:10858-10863 does, once per thread.
+    w_np: uint8 [M, row bytes] (or float32 [M, K] for F32); x_np: float32 [N, K].
+    Returns (can, C[N, M] float32)."""
+    import numpy as np
+    L = lib()
+    m = w_np.shape[0]
+    n, k = x_np.shape
+    c = np.zeros((n, m), np.float32)
+    src0 = make_tensor_2d(w_type, k, m, w_np.ctypes.data, w_np.strides[0])
+    src1 = make_tensor_2d(F32, k, n, x_np.ctypes.data, x_np.strides[0])
+    dst = make_tensor_2d(F32, m, n, c.ctypes.data)
+    dst.src[0] = C.pointer(src0)
+    dst.src[1] = C.pointer(src1)
+    can = True
+    for ith in range(nth):
+        p = GgmlComputeParams(task, ith, nth, wdata.nbytes if wdata is not None else 0,
+                              wdata.ctypes.data if wdata is not None else None)
+        if not L.lamm_can_mul_mat(C.byref(p), C.byref(dst)):
+            can = False
+            break
+        L.lamm_mul_mat(C.byref(p), C.byref(dst))
+    return can, c

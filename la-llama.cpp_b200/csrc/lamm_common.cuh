@@ -1,0 +1,129 @@
+// lamm_common.cuh -- shared device/host definitions for the sm_100a LAMM path.
+//
+// Block layouts are ggml's, byte for byte (llama.cpp-b2430/ggml-common.h:144-225,
+// 316-321); the type table mirrors src/lamm_ggml_type_trait.h:8-56 and the
+// (src0, vec_dot) pairs of src/loongarch_matmul.cpp:37-42.
+#pragma once
+
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/lammcu.h"
+
+namespace lamm {
+
+// ---------------------------------------------------------------- type table
+struct TypeInfo {
+  int blck;       // elements per block
+  int size;       // bytes per block
+  int vec_dot;    // activation type it is multiplied with
+};
+
+__host__ __device__ constexpr TypeInfo type_info(int t) {
+  switch (t) {
+  case LAMMCU_TYPE_F32:  return {1, 4, LAMMCU_TYPE_F32};
+  case LAMMCU_TYPE_Q4_0: return {32, 18, LAMMCU_TYPE_Q8_0};
+  case LAMMCU_TYPE_Q4_1: return {32, 20, LAMMCU_TYPE_Q8_1};
+  case LAMMCU_TYPE_Q5_0: return {32, 22, LAMMCU_TYPE_Q8_0};
+  case LAMMCU_TYPE_Q5_1: return {32, 24, LAMMCU_TYPE_Q8_1};
+  case LAMMCU_TYPE_Q8_0: return {32, 34, LAMMCU_TYPE_Q8_0};
+  case LAMMCU_TYPE_Q8_1: return {32, 36, LAMMCU_TYPE_Q8_1};
+  case LAMMCU_TYPE_Q2_K: return {256, 84, LAMMCU_TYPE_Q8_K};
+  case LAMMCU_TYPE_Q8_K: return {256, 292, LAMMCU_TYPE_Q8_K};
+  default:               return {0, 0, -1};
+  }
+}
+
+// byte offsets inside the activation blocks
+constexpr int Q8_0_QS = 2;     // {f16 d; i8 qs[32]}
+constexpr int Q8_1_QS = 4;     // {f16 d, s; i8 qs[32]}
+constexpr int Q8_K_QS = 4;     // {f32 d; i8 qs[256]; i16 bsums[16]}
+constexpr int Q8_K_BSUMS = 260;
+
+// ---------------------------------------------------------------- launch book-keeping
+extern unsigned long long g_launch_count;   // lammcu_launch_count()
+
+// ---------------------------------------------------------------- small device helpers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+__device__ __forceinline__ float half_bits_to_float(uint32_t h16) {
+  return __half2float(__ushort_as_half((unsigned short)h16));
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ---------------------------------------------------------------- mbarrier / bulk copy (TMA 1-D)
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "LAMM_WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra LAMM_DONE_%=;\n\t"
+      "bra LAMM_WAIT_%=;\n\t"
+      "LAMM_DONE_%=:\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// global -> shared bulk copy (SASS: UBLKCP).  dst, src 16 B aligned; bytes % 16 == 0.
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gmem_src, uint32_t bytes,
+                                         uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_u32(smem_dst)),
+      "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+// same with an L2 evict-first policy: weights are streamed once
+__device__ __forceinline__ void bulk_g2s_stream(void *smem_dst, const void *gmem_src,
+                                                uint32_t bytes, uint64_t *bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+      "[%0], [%1], %2, [%3], %4;" ::"r"(smem_u32(smem_dst)),
+      "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+
+// ---------------------------------------------------------------- host-side launchers (defined in the .cu files)
+int launch_quantize_act(int vec_dot_type, const float *x, int64_t ldx, void *xq, int64_t n_rows,
+                        int64_t k, cudaStream_t st);
+int launch_gemv(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride,
+                float *c, int64_t ldc, int64_t M, int64_t N, int64_t K, cudaStream_t st);
+int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride,
+                float *c, int64_t ldc, int64_t M, int64_t N, int64_t K, cudaStream_t st);
+void set_error(const char *fmt, ...);
+int sm_count_cached();
+// scratch for the dynamic tile scheduler: returns a zeroed pair of counters
+unsigned int *next_sched_slot();
+
+}  // namespace lamm

@@ -1,0 +1,126 @@
+// lamm_host.cpp -- the drop-in operator: lamm_can_mul_mat / lamm_mul_mat /
+// lamm_get_opt_level with the reference's signatures and gate semantics
+// (src/loongarch_matmul.h:18-24, src/loongarch_matmul.cpp:10-145), implemented on
+// the C-ABI of include/lammcu.h.  Host C++ only; all device work is behind lammcu_*.
+//
+// Differences from the reference that stay ABI-compatible:
+//   * the work is done once, by thread ith == 0; other threads return at once and
+//     see dst after ggml's post-COMPUTE barrier (ggml.c:18443-18450);
+//   * the activation quantize is part of the operator (fused on the GPU from the
+//     f32 src1->data) instead of ggml's INIT phase; params->wdata is only read when
+//     the caller asks for it (lamm_set_writeback_wdata) or src1 is pre-quantized;
+//   * all M rows are computed (the reference drops M % nth rows);
+//   * the gate also refuses what the CUDA path cannot take, so ggml falls back.
+#include "../../include/lamm_b200.h"
+#include "../../include/lammcu.h"
+
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+
+#ifndef LAMM_OPT_LEVEL
+#define LAMM_OPT_LEVEL 3        // src/lamm_common.h:96-100
+#endif
+
+namespace {
+
+std::atomic<int> g_writeback{0};
+
+int opt_level() {
+  static const int lvl = [] {
+    const char *e = std::getenv("LAMM_OPT_LEVEL");
+    return e ? std::atoi(e) : LAMM_OPT_LEVEL;
+  }();
+  return lvl;
+}
+
+bool device_ok() {
+  static const bool ok = (lammcu_init(-1) == LAMMCU_OK);
+  return ok;
+}
+
+// ggml_is_contiguous (ggml.c:2616-2624)
+bool is_contiguous(const ggml_tensor *t) {
+  const size_t ts = lammcu_type_size(t->type);
+  const int bs = lammcu_blck_size(t->type);
+  if (!ts || !bs) return false;
+  return t->nb[0] == ts && t->nb[1] == (t->nb[0] * t->ne[0]) / bs &&
+         t->nb[2] == t->nb[1] * t->ne[1] && t->nb[3] == t->nb[2] * t->ne[2];
+}
+
+[[noreturn]] void die(const char *what) {
+  std::fprintf(stderr, "lamm_mul_mat: %s: %s\n", what, lammcu_last_error());
+  std::abort();
+}
+
+}  // namespace
+
+extern "C" {
+
+int lamm_get_opt_level(void) { return opt_level(); }
+
+void lamm_set_writeback_wdata(int enable) { g_writeback.store(enable); }
+
+bool lamm_can_mul_mat(const struct ggml_compute_params *params, const struct ggml_tensor *dst) {
+  if (opt_level() == 0) return false;                                   // :12
+  if (params->type != GGML_TASK_TYPE_COMPUTE) return false;             // :15
+  const ggml_tensor *src0 = dst->src[0], *src1 = dst->src[1];
+  if (!src0 || !src1) return false;
+  if (!lammcu_type_supported(src0->type)) return false;                 // :37-59 (never asserts)
+  const int vec_dot = lammcu_vec_dot_type(src0->type);
+  if ((int)src1->type == vec_dot && !is_contiguous(src1)) return false; // :26
+  if (src1->nb[0] != lammcu_type_size(src1->type)) return false;        // :29
+  if (dst->type != GGML_TYPE_F32) return false;                         // :34
+  // src1 must be F32 (quantized here) or already in the vec-dot type
+  if (src1->type != GGML_TYPE_F32 && (int)src1->type != vec_dot) return false;
+  // --- what the CUDA path additionally needs ---
+  const int64_t K = src0->ne[0];
+  const int kmul = (src0->type == GGML_TYPE_F32) ? 8 : lammcu_blck_size(src0->type);
+  if (K <= 0 || K % kmul) return false;                                 // lamm_impl.hpp:123-126 aborts instead
+  if (src0->nb[0] != lammcu_type_size(src0->type)) return false;        // rows are block-contiguous
+  if (src0->nb[1] < lammcu_row_size(src0->type, K)) return false;
+  if (src0->ne[2] <= 0 || src0->ne[3] <= 0 || src1->ne[2] % src0->ne[2] || src1->ne[3] % src0->ne[3])
+    return false;
+  if (dst->nb[0] != sizeof(float)) return false;
+  return device_ok();                                                   // no GPU: stock ggml path
+}
+
+void lamm_mul_mat(const struct ggml_compute_params *params, struct ggml_tensor *dst) {
+  if (params->ith != 0) return;            // one launch per node; rows are not thread-split
+  const ggml_tensor *src0 = dst->src[0], *src1 = dst->src[1];
+  // GGML_TENSOR_BINARY_OP_LOCALS (ggml.h:306-312), the names the reference uses
+  const int64_t ne00 = src0->ne[0], ne01 = src0->ne[1], ne02 = src0->ne[2], ne03 = src0->ne[3];
+  const size_t nb01 = src0->nb[1], nb02 = src0->nb[2], nb03 = src0->nb[3];
+  const int64_t ne11 = src1->ne[1], ne12 = src1->ne[2], ne13 = src1->ne[3];
+  const size_t nb11 = src1->nb[1], nb12 = src1->nb[2], nb13 = src1->nb[3];
+  const size_t nb1 = dst->nb[1], nb2 = dst->nb[2], nb3 = dst->nb[3];
+
+  const int64_t r2 = ne12 / ne02, r3 = ne13 / ne03;                     // :75-76 broadcast factors
+  const int vec_dot = lammcu_vec_dot_type(src0->type);
+  const size_t row_size = lammcu_row_size(vec_dot, ne00);               // :80
+  const bool src1_quantized = ((int)src1->type == vec_dot) && src0->type != GGML_TYPE_F32;
+  const int64_t ldc = (int64_t)(nb1 / sizeof(float));                   // :99
+
+  for (int64_t i13 = 0; i13 < ne13; i13++) {                            // :130-142
+    for (int64_t i12 = 0; i12 < ne12; i12++) {
+      const char *a = (const char *)src0->data + (i12 / r2) * nb02 + (i13 / r3) * nb03;
+      float *c = (float *)((char *)dst->data + i12 * nb2 + i13 * nb3);
+      lammcu_weight_t w;
+      if (lammcu_weight_register(a, src0->type, ne01, ne00, (int64_t)nb01, 0, ne01, &w) != LAMMCU_OK)
+        die("weight upload");
+      const char *b = (const char *)src1->data + i12 * nb12 + i13 * nb13;
+      if (src1_quantized) {
+        if (lammcu_mul_mat_q_host(w, b, (int64_t)nb11, ne11, c, ldc) != LAMMCU_OK) die("mul_mat_q");
+      } else {
+        void *xq_out = nullptr;
+        if (g_writeback.load() && params->wdata && src0->type != GGML_TYPE_F32)
+          xq_out = (char *)params->wdata + (i12 * ne11 + i13 * ne12 * ne11) * row_size;   // :137-138
+        if (lammcu_mul_mat_host(w, (const float *)b, ne11, (int64_t)(nb11 / sizeof(float)), c, ldc,
+                                xq_out) != LAMMCU_OK)
+          die("mul_mat");
+      }
+    }
+  }
+}
+
+}  // extern "C"

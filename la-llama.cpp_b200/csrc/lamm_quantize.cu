@@ -1,0 +1,200 @@
+// lamm_quantize.cu -- activation re-quantization f32 -> Q8_0 / Q8_1 / Q8_K.
+//
+// Bit-exact with the scalar reference quantizers the reference platform runs
+// in ggml's INIT phase (llama.cpp-b2430/ggml.c:10865-10887):
+//   quantize_row_q8_0_reference  ggml-quants.c:1182-1205
+//   quantize_row_q8_1_reference  ggml-quants.c:1396-1429
+//   quantize_row_q8_K_reference  ggml-quants.c:3981-4018 (+ nearest_int :1767)
+// Every f32 operation below is an explicitly rounded intrinsic (__fdiv_rn,
+// __fmul_rn, __fadd_rn) so nvcc can neither contract a*b+c into an FMA nor
+// substitute an approximate division; max/abs are exact and order-free.
+//
+// HBM-bound: 4 B read + ~1.06 B written per element.  One lane owns 4 (Q8_0/1)
+// or 8 (Q8_K) consecutive elements, read as float4; 8 / 32 lanes form one block.
+#include "lamm_common.cuh"
+
+namespace lamm {
+
+// ---- the per-block arithmetic, shared with the fused GEMV prologue ---------
+
+// 8 lanes x 4 elements = one 32-block.  Returns the 4 quants packed little-
+// endian; d (f32, before fp16 rounding) and the integer sum of the block's
+// quants are broadcast to the 8 lanes.
+__device__ __forceinline__ uint32_t quant32_lane4(float4 v, float &d_out, int &sum_out) {
+  float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+  const float d = __fdiv_rn(amax, 127.0f);
+  const float id = (d != 0.0f) ? __fdiv_rn(1.0f, d) : 0.0f;
+  // roundf: half away from zero, as C's roundf
+  const int q0 = (int)roundf(__fmul_rn(v.x, id));
+  const int q1 = (int)roundf(__fmul_rn(v.y, id));
+  const int q2 = (int)roundf(__fmul_rn(v.z, id));
+  const int q3 = (int)roundf(__fmul_rn(v.w, id));
+  int s = q0 + q1 + q2 + q3;
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  d_out = d;
+  sum_out = s;
+  return (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) |
+         ((uint32_t)(q3 & 0xff) << 24);
+}
+
+__device__ __forceinline__ int nearest_int_rne(float v) {
+  const float t = __fadd_rn(v, 12582912.0f);           // 1.5 * 2^23
+  return (__float_as_int(t) & 0x007fffff) - 0x00400000;
+}
+
+template <bool VEC>
+__device__ __forceinline__ float4 load4(const float *p) {
+  if (VEC) return *reinterpret_cast<const float4 *>(p);
+  return make_float4(p[0], p[1], p[2], p[3]);
+}
+
+// ---- Q8_0 / Q8_1 ------------------------------------------------------------
+// grid-stride over groups of 4 blocks (one warp = 4 blocks of one row).
+template <int VT, bool VEC>
+__global__ void __launch_bounds__(256) quantize_q8_01_kernel(const float *__restrict__ x,
+                                                            int64_t ldx, uint8_t *__restrict__ xq,
+                                                            int64_t n_rows, int64_t kb_per_row) {
+  constexpr int BS = (VT == LAMMCU_TYPE_Q8_0) ? 34 : 36;
+  constexpr int QS = (VT == LAMMCU_TYPE_Q8_0) ? Q8_0_QS : Q8_1_QS;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane >> 3, l8 = lane & 7;
+  const int64_t groups_per_row = (kb_per_row + 3) >> 2;
+  const int64_t n_groups = n_rows * groups_per_row;
+  const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t g = warp0; g < n_groups; g += n_warps) {
+    const int64_t row = g / groups_per_row;
+    const int64_t kb = (g - row * groups_per_row) * 4 + sub;
+    const bool live = kb < kb_per_row;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (live) v = load4<VEC>(x + row * ldx + kb * 32 + l8 * 4);
+    float d;
+    int sum;
+    const uint32_t q = quant32_lane4(v, d, sum);
+    if (!live) continue;
+    uint8_t *blk = xq + (row * kb_per_row + kb) * BS;
+    if (VT == LAMMCU_TYPE_Q8_1) {
+      *reinterpret_cast<uint32_t *>(blk + QS + l8 * 4) = q;            // 36-B blocks: 4-B aligned
+      if (l8 == 0) {
+        const float s = __fmul_rn((float)sum, d);
+        __half2 ds = __halves2half2(__float2half_rn(d), __float2half_rn(s));
+        *reinterpret_cast<__half2 *>(blk) = ds;
+      }
+    } else {
+      uint16_t *p = reinterpret_cast<uint16_t *>(blk + QS + l8 * 4);   // 34-B blocks: 2-B aligned
+      p[0] = (uint16_t)(q & 0xffff);
+      p[1] = (uint16_t)(q >> 16);
+      if (l8 == 0) *reinterpret_cast<__half *>(blk) = __float2half_rn(d);
+    }
+  }
+}
+
+// ---- Q8_K -------------------------------------------------------------------
+// one warp = one 256-super-block; lane owns elements [8*lane, 8*lane+8).
+template <bool VEC>
+__global__ void __launch_bounds__(256) quantize_q8_K_kernel(const float *__restrict__ x,
+                                                           int64_t ldx, uint8_t *__restrict__ xq,
+                                                           int64_t n_rows, int64_t kb_per_row) {
+  const int lane = threadIdx.x & 31;
+  const int64_t n_blocks = n_rows * kb_per_row;
+  const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t b = warp0; b < n_blocks; b += n_warps) {
+    const int64_t row = b / kb_per_row, kb = b - row * kb_per_row;
+    const float *xp = x + row * ldx + kb * 256 + lane * 8;
+    const float4 a = load4<VEC>(xp), c = load4<VEC>(xp + 4);
+    const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+    // first index attaining the largest |x| (strict '>' scan in the reference)
+    float amax = 0.0f;
+    int idx = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const float ax = fabsf(v[j]);
+      if (ax > amax) { amax = ax; idx = j; }
+    }
+    idx += lane * 8;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float oa = __shfl_xor_sync(0xffffffffu, amax, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+      if (oa > amax || (oa == amax && oi < idx)) { amax = oa; idx = oi; }
+    }
+    float mx = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 8; j++) mx = ((idx & 7) == j) ? v[j] : mx;
+    mx = __shfl_sync(0xffffffffu, mx, idx >> 3);
+
+    uint8_t *blk = xq + b * 292;
+    uint32_t q_lo = 0, q_hi = 0;
+    int sum = 0;
+    float d = 0.0f;
+    if (amax != 0.0f) {
+      const float iscale = __fdiv_rn(-127.0f, mx);
+      int q[8];
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        q[j] = min(127, nearest_int_rne(__fmul_rn(iscale, v[j])));
+        sum += q[j];
+      }
+      q_lo = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) |
+             ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
+      q_hi = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) |
+             ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)(q[7] & 0xff) << 24);
+      d = __fdiv_rn(1.0f, iscale);
+    }
+    sum += __shfl_xor_sync(0xffffffffu, sum, 1);       // 16-element group = 2 lanes
+    uint32_t *qs = reinterpret_cast<uint32_t *>(blk + Q8_K_QS + lane * 8);   // 292 % 4 == 0
+    qs[0] = q_lo;
+    qs[1] = q_hi;
+    // all-zero block: the reference leaves bsums untouched; we write zeros.
+    if ((lane & 1) == 0)
+      *reinterpret_cast<int16_t *>(blk + Q8_K_BSUMS + lane) = (int16_t)sum;  // bsums[lane/2]
+    if (lane == 0) *reinterpret_cast<float *>(blk) = d;
+  }
+}
+
+int launch_quantize_act(int vt, const float *x, int64_t ldx, void *xq, int64_t n_rows, int64_t k,
+                        cudaStream_t st) {
+  const TypeInfo ti = type_info(vt);
+  if (vt != LAMMCU_TYPE_Q8_0 && vt != LAMMCU_TYPE_Q8_1 && vt != LAMMCU_TYPE_Q8_K) {
+    set_error("quantize_act: type %d is not an activation type", vt);
+    return LAMMCU_ERR_TYPE;
+  }
+  if (n_rows <= 0 || k <= 0 || k % ti.blck) {
+    set_error("quantize_act: bad shape rows=%lld k=%lld", (long long)n_rows, (long long)k);
+    return LAMMCU_ERR_SHAPE;
+  }
+  if (((uintptr_t)x & 3) || ((uintptr_t)xq & 3)) {
+    set_error("quantize_act: x and xq must be 4-byte aligned");
+    return LAMMCU_ERR_ALIGN;
+  }
+  const bool vec = (((uintptr_t)x & 15) == 0) && (ldx % 4 == 0);
+  const int64_t kb = k / ti.blck;
+  const int64_t warps = (vt == LAMMCU_TYPE_Q8_K) ? n_rows * kb : n_rows * ((kb + 3) / 4);
+  int64_t blocks = (warps + 7) / 8;
+  const int64_t cap = (int64_t)sm_count_cached() * 8;
+  if (blocks > cap) blocks = cap;
+  uint8_t *out = (uint8_t *)xq;
+  if (vt == LAMMCU_TYPE_Q8_0) {
+    if (vec) quantize_q8_01_kernel<LAMMCU_TYPE_Q8_0, true><<<blocks, 256, 0, st>>>(x, ldx, out, n_rows, kb);
+    else quantize_q8_01_kernel<LAMMCU_TYPE_Q8_0, false><<<blocks, 256, 0, st>>>(x, ldx, out, n_rows, kb);
+  } else if (vt == LAMMCU_TYPE_Q8_1) {
+    if (vec) quantize_q8_01_kernel<LAMMCU_TYPE_Q8_1, true><<<blocks, 256, 0, st>>>(x, ldx, out, n_rows, kb);
+    else quantize_q8_01_kernel<LAMMCU_TYPE_Q8_1, false><<<blocks, 256, 0, st>>>(x, ldx, out, n_rows, kb);
+  } else {
+    if (vec) quantize_q8_K_kernel<true><<<blocks, 256, 0, st>>>(x, ldx, out, n_rows, kb);
+    else quantize_q8_K_kernel<false><<<blocks, 256, 0, st>>>(x, ldx, out, n_rows, kb);
+  }
+  g_launch_count++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("quantize_act launch: %s", cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
+}  // namespace lamm

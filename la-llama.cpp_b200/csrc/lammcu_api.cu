@@ -1,0 +1,384 @@
+// lammcu_api.cu -- the C-ABI of include/lammcu.h: device/stream ownership,
+// the weight registry (upload once per src0->data), workspaces, and dispatch
+// between the decode GEMV and the prefill GEMM.  No torch, no C++ types in the
+// exported signatures.  There is no CPU fallback: without a device every
+// compute entry point returns LAMMCU_ERR_NO_DEVICE.
+#include "lamm_common.cuh"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <vector>
+
+namespace lamm {
+
+unsigned long long g_launch_count = 0;
+
+static thread_local char t_err[512] = "";
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(t_err, sizeof(t_err), fmt, ap);
+  va_end(ap);
+}
+
+#define CU_TRY(expr)                                                                 \
+  do {                                                                               \
+    cudaError_t e_ = (expr);                                                         \
+    if (e_ != cudaSuccess) {                                                         \
+      set_error("%s failed: %s", #expr, cudaGetErrorString(e_));                     \
+      return LAMMCU_ERR_CUDA;                                                        \
+    }                                                                                \
+  } while (0)
+
+struct DeviceState {
+  bool inited = false;
+  int device = -1;
+  int sms = 0;
+  cudaStream_t stream = nullptr;
+  unsigned int *sched = nullptr;   // ring of self-resetting scheduler counter pairs
+  unsigned int sched_next = 0;
+  void *ws = nullptr;  size_t ws_bytes = 0;      // quantized-activation workspace
+  void *xin = nullptr; size_t xin_bytes = 0;     // host path: X on device
+  void *cout = nullptr; size_t cout_bytes = 0;   // host path: C on device
+  void *hx = nullptr;  size_t hx_bytes = 0;      // pinned staging
+  void *hc = nullptr;  size_t hc_bytes = 0;
+};
+static DeviceState g_dev;
+static std::mutex g_mu;
+static int g_gemv_max_n = 8;
+constexpr unsigned int kSchedSlots = 4096;
+
+int sm_count_cached() { return g_dev.sms > 0 ? g_dev.sms : 148; }
+
+unsigned int *next_sched_slot() {
+  if (!g_dev.sched) {
+    set_error("lammcu not initialised (call lammcu_init)");
+    return nullptr;
+  }
+  unsigned int i = g_dev.sched_next++ % kSchedSlots;
+  return g_dev.sched + 2 * i;
+}
+
+static int ensure_init() {
+  if (g_dev.inited) return LAMMCU_OK;
+  return lammcu_init(-1);
+}
+
+static int grow(void **p, size_t *have, size_t need, bool pinned) {
+  if (*have >= need) return LAMMCU_OK;
+  if (*p) {
+    if (pinned) cudaFreeHost(*p); else cudaFree(*p);
+    *p = nullptr; *have = 0;
+  }
+  size_t n = need + need / 4 + 4096;
+  cudaError_t e = pinned ? cudaMallocHost(p, n) : cudaMalloc(p, n);
+  if (e != cudaSuccess) {
+    set_error("allocation of %zu bytes failed: %s", n, cudaGetErrorString(e));
+    return LAMMCU_ERR_NOMEM;
+  }
+  *have = n;
+  return LAMMCU_OK;
+}
+
+}  // namespace lamm
+
+using namespace lamm;
+
+struct lammcu_weight {
+  const void *host;     // registry key
+  int type;
+  int64_t M, K, row_begin, row_end;
+  int64_t stride;       // bytes between device rows (packed)
+  void *dev;
+  size_t bytes;
+  int refs;
+};
+static std::map<const void *, lammcu_weight *> g_weights;
+
+extern "C" {
+
+const char *lammcu_version(void) { return "lammcu 0.1 (sm_100a)"; }
+const char *lammcu_last_error(void) { return t_err; }
+
+int lammcu_device_count(void) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    set_error("cudaGetDeviceCount: %s", cudaGetErrorString(e));
+    return LAMMCU_ERR_NO_DEVICE;
+  }
+  return n;
+}
+
+int lammcu_init(int device) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  int n = lammcu_device_count();
+  if (n <= 0) {
+    if (n == 0) set_error("no CUDA device");
+    return LAMMCU_ERR_NO_DEVICE;
+  }
+  if (device < 0) {
+    if (g_dev.inited) return LAMMCU_OK;
+    CU_TRY(cudaGetDevice(&device));
+  }
+  if (device >= n) {
+    set_error("device %d out of range (%d devices)", device, n);
+    return LAMMCU_ERR_ARG;
+  }
+  if (g_dev.inited && g_dev.device == device) return LAMMCU_OK;
+  if (g_dev.inited) {
+    set_error("lammcu already bound to device %d; call lammcu_shutdown first", g_dev.device);
+    return LAMMCU_ERR_ARG;
+  }
+  CU_TRY(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CU_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    set_error("device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    return LAMMCU_ERR_NO_DEVICE;
+  }
+  g_dev.device = device;
+  g_dev.sms = prop.multiProcessorCount;
+  CU_TRY(cudaStreamCreateWithFlags(&g_dev.stream, cudaStreamNonBlocking));
+  CU_TRY(cudaMalloc(&g_dev.sched, kSchedSlots * 2 * sizeof(unsigned int)));
+  CU_TRY(cudaMemset(g_dev.sched, 0, kSchedSlots * 2 * sizeof(unsigned int)));
+  CU_TRY(cudaDeviceSynchronize());
+  g_dev.inited = true;
+  return LAMMCU_OK;
+}
+
+int lammcu_shutdown(void) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_dev.inited) return LAMMCU_OK;
+  cudaSetDevice(g_dev.device);
+  cudaDeviceSynchronize();
+  for (auto &kv : g_weights) {
+    cudaFree(kv.second->dev);
+    delete kv.second;
+  }
+  g_weights.clear();
+  if (g_dev.ws) cudaFree(g_dev.ws);
+  if (g_dev.xin) cudaFree(g_dev.xin);
+  if (g_dev.cout) cudaFree(g_dev.cout);
+  if (g_dev.hx) cudaFreeHost(g_dev.hx);
+  if (g_dev.hc) cudaFreeHost(g_dev.hc);
+  if (g_dev.sched) cudaFree(g_dev.sched);
+  if (g_dev.stream) cudaStreamDestroy(g_dev.stream);
+  g_dev = DeviceState();
+  return LAMMCU_OK;
+}
+
+int lammcu_sm_count(void) { return g_dev.inited ? g_dev.sms : 0; }
+uint64_t lammcu_launch_count(void) { return g_launch_count; }
+void lammcu_launch_count_reset(void) { g_launch_count = 0; }
+
+// ---- type table -------------------------------------------------------------
+int lammcu_type_supported(int t) {
+  return t == LAMMCU_TYPE_F32 || t == LAMMCU_TYPE_Q2_K || t == LAMMCU_TYPE_Q4_0 ||
+         t == LAMMCU_TYPE_Q4_1 || t == LAMMCU_TYPE_Q5_0 || t == LAMMCU_TYPE_Q5_1 ||
+         t == LAMMCU_TYPE_Q8_0;
+}
+int lammcu_blck_size(int t) { return type_info(t).blck; }
+size_t lammcu_type_size(int t) { return (size_t)type_info(t).size; }
+int lammcu_vec_dot_type(int t) { return type_info(t).vec_dot; }
+size_t lammcu_row_size(int t, int64_t k) {
+  const TypeInfo ti = type_info(t);
+  return ti.blck ? (size_t)(k / ti.blck) * ti.size : 0;
+}
+
+int lammcu_set_gemv_max_n(int n) {
+  if (n < 0) return LAMMCU_ERR_ARG;
+  g_gemv_max_n = n;
+  return LAMMCU_OK;
+}
+int lammcu_get_gemv_max_n(void) { return g_gemv_max_n; }
+
+// ---- device operands ----------------------------------------------------------
+static cudaStream_t pick_stream(void *s) { return s ? (cudaStream_t)s : g_dev.stream; }
+
+int lammcu_quantize_act_dev(int vt, const float *x, int64_t ldx, void *xq, int64_t n_rows,
+                            int64_t k, void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!x || !xq) { set_error("quantize_act: NULL operand"); return LAMMCU_ERR_ARG; }
+  return launch_quantize_act(vt, x, ldx, xq, n_rows, k, pick_stream(stream));
+}
+
+int lammcu_mul_mat_q_dev(int w_type, const void *w, int64_t w_stride, const void *xq,
+                         int64_t xq_stride, float *c, int64_t ldc, int64_t M, int64_t N,
+                         int64_t K, void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!w || !xq || !c) { set_error("mul_mat_q: NULL operand"); return LAMMCU_ERR_ARG; }
+  if (!lammcu_type_supported(w_type)) { set_error("mul_mat_q: type %d not supported", w_type); return LAMMCU_ERR_TYPE; }
+  cudaStream_t st = pick_stream(stream);
+  if (N <= g_gemv_max_n) return launch_gemv(w_type, w, w_stride, xq, xq_stride, c, ldc, M, N, K, st);
+  return launch_gemm(w_type, w, w_stride, xq, xq_stride, c, ldc, M, N, K, st);
+}
+
+int lammcu_mul_mat_dev(int w_type, const void *w, int64_t w_stride, const float *x, int64_t ldx,
+                       float *c, int64_t ldc, int64_t M, int64_t N, int64_t K, void *xq_ws,
+                       void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!w || !x || !c) { set_error("mul_mat: NULL operand"); return LAMMCU_ERR_ARG; }
+  if (!lammcu_type_supported(w_type)) { set_error("mul_mat: type %d not supported", w_type); return LAMMCU_ERR_TYPE; }
+  if (w_type == LAMMCU_TYPE_F32)   // F32 x F32: X is used as it is (src/loongarch_matmul.cpp:89-94)
+    return lammcu_mul_mat_q_dev(w_type, w, w_stride, x, ldx * 4, c, ldc, M, N, K, stream);
+  const int vt = type_info(w_type).vec_dot;
+  if (K <= 0 || K % type_info(w_type).blck || N <= 0) {
+    set_error("mul_mat: bad shape N=%lld K=%lld", (long long)N, (long long)K);
+    return LAMMCU_ERR_SHAPE;
+  }
+  const size_t rs = lammcu_row_size(vt, K);
+  if (!xq_ws) {
+    rc = grow(&g_dev.ws, &g_dev.ws_bytes, rs * (size_t)N, false);
+    if (rc) return rc;
+    xq_ws = g_dev.ws;
+  }
+  rc = launch_quantize_act(vt, x, ldx, xq_ws, N, K, pick_stream(stream));
+  if (rc) return rc;
+  return lammcu_mul_mat_q_dev(w_type, w, w_stride, xq_ws, (int64_t)rs, c, ldc, M, N, K, stream);
+}
+
+// ---- host operands --------------------------------------------------------------
+int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K,
+                           int64_t w_stride, int64_t row_begin, int64_t row_end,
+                           lammcu_weight_t *out) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!w_host || !out) { set_error("weight_register: NULL argument"); return LAMMCU_ERR_ARG; }
+  if (!lammcu_type_supported(w_type)) { set_error("weight_register: type %d not supported", w_type); return LAMMCU_ERR_TYPE; }
+  const TypeInfo ti = type_info(w_type);
+  if (M <= 0 || K <= 0 || K % ti.blck || row_begin < 0 || row_end > M || row_begin >= row_end) {
+    set_error("weight_register: bad shape M=%lld K=%lld rows [%lld,%lld)", (long long)M, (long long)K,
+              (long long)row_begin, (long long)row_end);
+    return LAMMCU_ERR_SHAPE;
+  }
+  const size_t rs = lammcu_row_size(w_type, K);
+  if ((size_t)w_stride < rs) { set_error("weight_register: row stride smaller than a row"); return LAMMCU_ERR_SHAPE; }
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto it = g_weights.find(w_host);
+  if (it != g_weights.end()) {
+    lammcu_weight *h = it->second;
+    if (h->type == w_type && h->M == M && h->K == K && h->row_begin == row_begin && h->row_end == row_end) {
+      h->refs++;
+      *out = h;
+      return LAMMCU_OK;
+    }
+    // same address, different tensor: the old one is stale
+    cudaFree(h->dev);
+    delete h;
+    g_weights.erase(it);
+  }
+  lammcu_weight *h = new lammcu_weight();
+  h->host = w_host; h->type = w_type; h->M = M; h->K = K;
+  h->row_begin = row_begin; h->row_end = row_end;
+  h->stride = (int64_t)rs; h->refs = 1;
+  const int64_t rows = row_end - row_begin;
+  h->bytes = rs * (size_t)rows;
+  // +256: the GEMV's bulk copies round every row span out to 16-byte boundaries
+  cudaError_t e = cudaMalloc(&h->dev, h->bytes + 256);
+  if (e != cudaSuccess) {
+    set_error("weight_register: cudaMalloc(%zu): %s", h->bytes + 256, cudaGetErrorString(e));
+    delete h;
+    return LAMMCU_ERR_NOMEM;
+  }
+  e = cudaMemcpy2D(h->dev, rs, (const char *)w_host + row_begin * w_stride, (size_t)w_stride, rs,
+                   (size_t)rows, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemset((char *)h->dev + h->bytes, 0, 256);
+  if (e != cudaSuccess) {
+    set_error("weight_register: upload: %s", cudaGetErrorString(e));
+    cudaFree(h->dev);
+    delete h;
+    return LAMMCU_ERR_CUDA;
+  }
+  g_weights[w_host] = h;
+  *out = h;
+  return LAMMCU_OK;
+}
+
+int lammcu_weight_lookup(const void *w_host, lammcu_weight_t *out) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto it = g_weights.find(w_host);
+  if (it == g_weights.end()) { set_error("weight_lookup: not registered"); return LAMMCU_ERR_ARG; }
+  *out = it->second;
+  return LAMMCU_OK;
+}
+
+int lammcu_weight_release(lammcu_weight_t w) {
+  if (!w) return LAMMCU_ERR_ARG;
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto it = g_weights.find(w->host);
+  if (it == g_weights.end() || it->second != w) { set_error("weight_release: bad handle"); return LAMMCU_ERR_ARG; }
+  if (--w->refs > 0) return LAMMCU_OK;
+  cudaStreamSynchronize(g_dev.stream);
+  cudaFree(w->dev);
+  g_weights.erase(it);
+  delete w;
+  return LAMMCU_OK;
+}
+
+const void *lammcu_weight_dev_ptr(lammcu_weight_t w) { return w ? w->dev : nullptr; }
+int64_t lammcu_weight_rows(lammcu_weight_t w) { return w ? w->row_end - w->row_begin : 0; }
+
+// D2H of the shard's column range of every output row
+static int copy_c_back(lammcu_weight_t w, int64_t N, float *c_host, int64_t ldc) {
+  const int64_t rows = w->row_end - w->row_begin;
+  int rc = grow(&g_dev.hc, &g_dev.hc_bytes, (size_t)N * rows * 4, true);
+  if (rc) return rc;
+  CU_TRY(cudaMemcpyAsync(g_dev.hc, g_dev.cout, (size_t)N * rows * 4, cudaMemcpyDeviceToHost, g_dev.stream));
+  CU_TRY(cudaStreamSynchronize(g_dev.stream));
+  for (int64_t j = 0; j < N; j++)
+    memcpy(c_host + j * ldc + w->row_begin, (const float *)g_dev.hc + j * rows, (size_t)rows * 4);
+  return LAMMCU_OK;
+}
+
+int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N, int64_t ldx,
+                        float *c_host, int64_t ldc, void *xq_out_host) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!w || !x_host || !c_host || N <= 0) { set_error("mul_mat_host: bad argument"); return LAMMCU_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(g_mu);
+  const int64_t K = w->K, rows = w->row_end - w->row_begin;
+  const size_t xbytes = (size_t)N * K * 4;
+  if ((rc = grow(&g_dev.hx, &g_dev.hx_bytes, xbytes, true))) return rc;
+  if ((rc = grow(&g_dev.xin, &g_dev.xin_bytes, xbytes, false))) return rc;
+  if ((rc = grow(&g_dev.cout, &g_dev.cout_bytes, (size_t)N * rows * 4, false))) return rc;
+  for (int64_t j = 0; j < N; j++) memcpy((float *)g_dev.hx + j * K, x_host + j * ldx, (size_t)K * 4);
+  CU_TRY(cudaMemcpyAsync(g_dev.xin, g_dev.hx, xbytes, cudaMemcpyHostToDevice, g_dev.stream));
+  rc = lammcu_mul_mat_dev(w->type, w->dev, w->stride, (const float *)g_dev.xin, K, (float *)g_dev.cout,
+                          rows, rows, N, K, nullptr, g_dev.stream);
+  if (rc) return rc;
+  if (xq_out_host && w->type != LAMMCU_TYPE_F32) {
+    const size_t qb = lammcu_row_size(type_info(w->type).vec_dot, K) * (size_t)N;
+    CU_TRY(cudaMemcpyAsync(xq_out_host, g_dev.ws, qb, cudaMemcpyDeviceToHost, g_dev.stream));
+  }
+  return copy_c_back(w, N, c_host, ldc);
+}
+
+int lammcu_mul_mat_q_host(lammcu_weight_t w, const void *xq_host, int64_t xq_stride, int64_t N,
+                          float *c_host, int64_t ldc) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!w || !xq_host || !c_host || N <= 0) { set_error("mul_mat_q_host: bad argument"); return LAMMCU_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(g_mu);
+  const int64_t K = w->K, rows = w->row_end - w->row_begin;
+  const int vt = type_info(w->type).vec_dot;
+  const size_t rs = (vt == LAMMCU_TYPE_F32) ? (size_t)K * 4 : lammcu_row_size(vt, K);
+  if ((size_t)xq_stride < rs) { set_error("mul_mat_q_host: activation stride smaller than a row"); return LAMMCU_ERR_SHAPE; }
+  if ((rc = grow(&g_dev.ws, &g_dev.ws_bytes, rs * (size_t)N, false))) return rc;
+  if ((rc = grow(&g_dev.cout, &g_dev.cout_bytes, (size_t)N * rows * 4, false))) return rc;
+  CU_TRY(cudaMemcpy2DAsync(g_dev.ws, rs, xq_host, (size_t)xq_stride, rs, (size_t)N, cudaMemcpyHostToDevice,
+                           g_dev.stream));
+  rc = lammcu_mul_mat_q_dev(w->type, w->dev, w->stride, g_dev.ws, (int64_t)rs, (float *)g_dev.cout, rows,
+                            rows, N, K, g_dev.stream);
+  if (rc) return rc;
+  return copy_c_back(w, N, c_host, ldc);
+}
+
+}  // extern "C"

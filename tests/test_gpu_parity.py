@@ -1,0 +1,183 @@
+"""Parity of the CUDA path against the oracle and the golden fixtures.  All calls go through
+the C-ABI (ctypes -> liblammcu.so); torch only owns the device buffers."""
+import glob
+import os
+
+import numpy as np
+import pytest
+from conftest import GOLDEN, golden, make_x, tol_c
+from oracle_lib import F32, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES, row_size
+
+pytestmark = pytest.mark.gpu
+QTYPES = [t for t in W_TYPES if t != F32]
+
+
+def dev(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def zero_dead_bsums(xq, n):
+    """Q8_K: bsums of all-zero super-blocks are unwritten in the reference, 0 on the GPU."""
+    blk = xq.reshape(n, -1, 292).copy()
+    dead = (blk[:, :, :4] == 0).all(axis=2)
+    blk[dead, 260:] = 0
+    return blk.reshape(n, -1)
+
+
+def weights(oracle, t, m, k, seed):
+    rng = np.random.default_rng(seed)
+    if t == F32:
+        return rng.standard_normal((m, k)).astype(np.float32)
+    return oracle.quantize_weights(t, rng.standard_normal((m, k)).astype(np.float32), seed=seed)
+
+
+# ---------------------------------------------------------------- activation quantize
+@pytest.mark.parametrize("vt,key", [(Q8_0, "q8_0"), (Q8_1, "q8_1"), (Q8_K, "q8_k")])
+def test_quantize_golden_bit_exact(gpu, vt, key):
+    g = golden("quantize_act_n12_k2048.npz")
+    got = gpu.quantize_act(dev(g["x"]), vt).cpu().numpy()
+    want = g[key]
+    if vt == Q8_K:
+        want = zero_dead_bsums(np.where(want == 0xAB, want, want), 12)
+        # pre-fill bytes only survive in dead bsums, which zero_dead_bsums cleared
+    assert np.array_equal(got, want), f"{(got != want).sum()} bytes differ"
+
+
+@pytest.mark.parametrize("vt", [Q8_0, Q8_1, Q8_K])
+@pytest.mark.parametrize("n,k", [(1, 256), (1, 4096), (3, 11008), (8, 4096), (17, 5120), (512, 4096)])
+def test_quantize_vs_oracle_bit_exact(gpu, oracle, vt, n, k):
+    rng = np.random.default_rng(n * 131 + k)
+    x = make_x(rng, n, k)
+    for scale in (1.0, 3e-5, 700.0):
+        xs = x * np.float32(scale)
+        got = gpu.quantize_act(dev(xs), vt).cpu().numpy()
+        want = oracle.quantize_act(vt, xs, prefill=0)
+        assert np.array_equal(got, want), f"{TYPE_NAMES[vt]} n={n} k={k} scale={scale}: {(got != want).sum()} bytes differ"
+
+
+def test_quantize_strided_and_unaligned_rows(gpu, oracle):
+    import torch
+    rng = np.random.default_rng(3)
+    big = rng.standard_normal((5, 1024 + 3)).astype(np.float32)
+    xd = dev(big)[:, 3:]                      # row stride 1027 floats, base 12 B off alignment
+    for vt in (Q8_0, Q8_1, Q8_K):
+        got = gpu.quantize_act(xd, vt).cpu().numpy()
+        assert np.array_equal(got, oracle.quantize_act(vt, big[:, 3:], prefill=0))
+
+
+# ---------------------------------------------------------------- mul_mat, golden
+@pytest.mark.parametrize("name", sorted(os.path.basename(p) for p in glob.glob(os.path.join(GOLDEN, "mulmat_*.npz"))))
+def test_mul_mat_golden(gpu, name):
+    g = golden(name)
+    t, x = int(g["w_type"]), g["x"]
+    n, k = x.shape
+    if t == F32:
+        w = dev(g["wq"].view(np.float32).reshape(-1, k))
+        c = gpu.mul_mat(t, w, dev(x)).cpu().numpy()
+        assert np.abs(c - g["c_graph"]).max() <= tol_c(g["c_graph"], k)
+        return
+    xq = gpu.quantize_act(dev(x), VEC_DOT[t]).cpu().numpy()
+    want_xq = zero_dead_bsums(g["xq"], n) if VEC_DOT[t] == Q8_K else g["xq"]
+    assert np.array_equal(xq, want_xq)
+    c = gpu.mul_mat(t, dev(g["wq"]), dev(x)).cpu().numpy()
+    assert np.abs(c - g["c_vecdot"]).max() <= tol_c(g["c_vecdot"], k)
+    if TYPE_NAMES[t] != "q8_0":
+        assert np.abs(c - g["c_lamm"]).max() <= tol_c(g["c_lamm"], k)
+
+
+# ---------------------------------------------------------------- mul_mat vs oracle
+SHAPES = [  # (M, N, K): odd M/N exercise tile edges like the reference's 33x18 case
+    (33, 1, 4096), (33, 18, 4096), (1, 1, 256), (7, 3, 256), (130, 2, 512), (257, 5, 1024),
+    (64, 8, 11008), (31, 7, 5120), (19, 4, 17920), (100, 17, 2048),
+]
+
+
+@pytest.mark.parametrize("t", W_TYPES)
+@pytest.mark.parametrize("m,n,k", SHAPES)
+def test_mul_mat_vs_oracle(gpu, oracle, t, m, n, k):
+    w = weights(oracle, t, m, k, seed=m * 7 + k)
+    x = make_x(np.random.default_rng(n + k), n, k)
+    want = oracle.mul_mat(t, w if t != F32 else w.view(np.uint8).reshape(m, -1), x)
+    got = gpu.mul_mat(t, dev(w), dev(x)).cpu().numpy()
+    err = np.abs(got - want).max()
+    assert err <= tol_c(want, k), f"{TYPE_NAMES[t]} {m}x{n}x{k}: err {err} tol {tol_c(want, k)}"
+
+
+@pytest.mark.parametrize("t", W_TYPES)
+def test_llama7b_shapes_full_size(gpu, oracle, t):
+    """BASELINE.json config[1]: K=4096, M in {4096, 11008}, N=1.  Oracle on a row sample
+    (the full oracle would take minutes), plus linearity in X as a size-independent property."""
+    import torch
+    for (m, k) in [(4096, 4096), (11008, 4096), (4096, 11008)]:
+        w = weights(oracle, t, m, k, seed=m + k)
+        rng = np.random.default_rng(17)
+        x = rng.standard_normal((1, k)).astype(np.float32)
+        got = gpu.mul_mat(t, dev(w), dev(x)).cpu().numpy()
+        rows = np.r_[0:8, m // 2 - 3:m // 2 + 5, m - 8:m, rng.integers(0, m, 40)]
+        wv = w if t != F32 else w.view(np.uint8).reshape(m, -1)
+        want = oracle.mul_mat(t, wv[rows], x)
+        assert np.abs(got[:, rows] - want).max() <= tol_c(want, k), f"{TYPE_NAMES[t]} {m}x{k}"
+        # power-of-two scaling of X is exact through the quantizer: C(2x) == 2 C(x) bit for bit
+        got2 = gpu.mul_mat(t, dev(w), dev(2 * x)).cpu().numpy()
+        if t not in (3, 7):          # Q4_1/Q5_1 carry the fp16-rounded s: exact too unless s overflows
+            assert np.array_equal(got2, 2 * got)
+        else:
+            assert np.abs(got2 - 2 * got).max() <= tol_c(want, k)
+
+
+def test_strided_weights_and_output(gpu, oracle):
+    """Row stride larger than the row (nb01 > row_size) and ldc > M."""
+    import torch
+    t, m, n, k = 3, 50, 3, 1024
+    w = weights(oracle, t, m, k, seed=1)
+    pad = np.zeros((m, w.shape[1] + 12), np.uint8)
+    pad[:, : w.shape[1]] = w
+    x = make_x(np.random.default_rng(2), n, k)
+    want = oracle.mul_mat(t, w, x)
+    wd = dev(pad)[:, : w.shape[1]]
+    out = torch.zeros((n, m + 5), dtype=torch.float32, device="cuda")
+    gpu.mul_mat(t, wd, dev(x), out=out[:, :m])
+    got = out.cpu().numpy()
+    assert np.abs(got[:, :m] - want).max() <= tol_c(want, k)
+    assert (got[:, m:] == 0).all()
+
+
+def test_zero_activations_give_zero(gpu, oracle):
+    for t in QTYPES:
+        w = weights(oracle, t, 40, 512, seed=9)
+        c = gpu.mul_mat(t, dev(w), dev(np.zeros((2, 512), np.float32))).cpu().numpy()
+        assert (c == 0).all(), TYPE_NAMES[t]
+
+
+def test_bad_arguments_fail_loudly(gpu):
+    import torch
+    w = torch.zeros((4, 20 * 8), dtype=torch.uint8, device="cuda")
+    x = torch.zeros((1, 250), dtype=torch.float32, device="cuda")
+    with pytest.raises(gpu.LammError):
+        gpu.mul_mat(3, w, x)                       # K % 32 != 0
+    with pytest.raises(gpu.LammError):
+        gpu.mul_mat(12, w, torch.zeros((1, 256), dtype=torch.float32, device="cuda"))   # Q4_K
+
+
+# ---------------------------------------------------------------- the drop-in operator
+@pytest.mark.parametrize("t", W_TYPES)
+def test_lamm_mul_mat_operator(gpu, oracle, t):
+    """lamm_can_mul_mat + lamm_mul_mat driven with hand-built ggml structs, as ggml.c:10858-10863
+    does, at the reference's test shape (M=33, N=18, K=4096), 4 'threads'."""
+    m, n, k = 33, 18, 4096
+    w = weights(oracle, t, m, k, seed=33)
+    x = make_x(np.random.default_rng(18), n, k)
+    wv = w if t != F32 else w.view(np.uint8).reshape(m, -1)
+    want, want_xq = oracle.mul_mat(t, wv, x, want_xq=True) if t != F32 else (oracle.mul_mat(t, wv, x), None)
+    wdata = np.zeros((n, row_size(VEC_DOT[t], k)), np.uint8) if t != F32 else None
+    gpu.lib().lamm_set_writeback_wdata(1)
+    can, got = gpu.lamm_mul_mat_host(t, wv, x, nth=4, wdata=wdata)
+    gpu.lib().lamm_set_writeback_wdata(0)
+    assert can
+    assert np.abs(got - want).max() <= tol_c(want, k)
+    if t != F32:
+        assert np.array_equal(wdata, want_xq), "GPU Xq != what ggml INIT would have written to wdata"
+    # second call hits the weight registry (no re-upload) and gives the same bits
+    can, again = gpu.lamm_mul_mat_host(t, wv, x, nth=1)
+    assert can and np.array_equal(again, got)

@@ -1,0 +1,52 @@
+"""Pin the oracle against the real reference compiled into oracle/_ref/libref.so.
+Runs only where that library exists (this container; it also travels to the GPU box)."""
+import numpy as np
+import pytest
+from conftest import make_x, tol_c
+from oracle_lib import F32, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES
+
+
+@pytest.mark.parametrize("vt", [Q8_0, Q8_1, Q8_K])
+def test_act_quantizers_bit_exact(oracle, ref, vt):
+    rng = np.random.default_rng(7)
+    x = make_x(rng, 9, 4096)
+    for scale in (1.0, 1e-4, 250.0):
+        a = oracle.quantize_act(vt, x * np.float32(scale), prefill=0x5C)
+        b = ref.quantize_act(vt, x * np.float32(scale), prefill=0x5C)
+        assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("t", [t for t in W_TYPES if t not in (F32, Q2_K)])
+def test_weight_quantizers_bit_exact(oracle, ref, t):
+    rng = np.random.default_rng(11)
+    w = rng.standard_normal((5, 1024)).astype(np.float32)
+    assert np.array_equal(oracle.quantize_weights(t, w), ref.quantize_weights(t, w))
+
+
+@pytest.mark.parametrize("t", [t for t in W_TYPES if t != F32])
+def test_mul_mat_vs_lamm_and_vecdot(oracle, ref, t):
+    rng = np.random.default_rng(1234)
+    m, n, k = 37, 6, 4096
+    w = rng.standard_normal((m, k)).astype(np.float32)
+    x = make_x(rng, n, k)
+    wq = ref.quantize_weights(t, w)
+    xq = ref.quantize_act(VEC_DOT[t], x)
+    c = oracle.mul_mat_q(t, wq, xq, k)
+    tol = tol_c(c, k)
+    assert np.abs(ref.vec_dot(t, wq, xq, k) - c).max() <= tol
+    if TYPE_NAMES[t] != "q8_0":            # lamm's AVX2 Q8_0 kernel is wrong
+        assert np.abs(ref.lamm_mul_mat(t, wq, x, xq) - c).max() <= tol
+    else:
+        assert np.abs(ref.lamm_mul_mat(t, wq, x, xq) - c).max() > 100 * tol
+
+
+def test_q2k_random_blocks(oracle, ref):
+    rng = np.random.default_rng(5)
+    m, n, k = 8, 3, 2048
+    wq = oracle.quantize_weights(Q2_K, np.zeros((m, k), np.float32), seed=99)
+    x = rng.standard_normal((n, k)).astype(np.float32)
+    xq = ref.quantize_act(Q8_K, x)
+    c = oracle.mul_mat_q(Q2_K, wq, xq, k)
+    assert np.isfinite(c).all()
+    assert np.abs(ref.lamm_mul_mat(Q2_K, wq, x, xq) - c).max() <= tol_c(c, k)
+    assert np.array_equal(oracle.dequantize(Q2_K, wq, k), ref.dequantize(Q2_K, wq, k))
