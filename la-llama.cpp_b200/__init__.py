@@ -141,9 +141,16 @@ def init(device=-1):
 
 
 # ---- device-tensor helpers (torch = device memory + streams only) -----------------
+CUDA_STREAM_LEGACY = 1      # cudaStreamLegacy: the NULL stream, spelled so it is not "library's own"
+
+
 def _stream_ptr():
+    """torch's current stream as the void* the C-ABI wants.  torch's default stream has handle 0,
+    which lammcu.h reads as 'use the library's own stream'; pass cudaStreamLegacy instead so the
+    kernels stay ordered with torch's copies on that stream."""
     import torch
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    h = torch.cuda.current_stream().cuda_stream
+    return C.c_void_p(h if h else CUDA_STREAM_LEGACY)
 
 
 def quantize_act(x, vt):
