@@ -1,0 +1,485 @@
+#!/usr/bin/env python
+"""bench.py -- the LAMM hot path on B200: LLaMA-7B Q4_1 decode tokens/s through the
+quantized mul_mat chain, with the GEMV's HBM roofline and the reference's
+own CPU path timed beside it.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--fmt q4_1]
+
+One "step" = one decoded token = the weight matmuls of one LLaMA-7B forward pass at
+N=1: 32 layers x {wq, wk, wv, wo (4096x4096), gate, up (11008x4096), down (4096x11008)}
++ the output head (32000x4096), each one `activation quantize -> quantized GEMV`, run
+back to back on one stream (captured once into a CUDA graph).  Attention / norm / rope /
+sampling are not on the path and are not run (stated in `config`).  All 225 weight
+matrices are distinct device buffers (4.13 GB for Q4_1 >> 126 MB L2), so every step
+streams its weights from HBM.
+
+value : tokens/s with inputs resident in HBM (CUDA events on the launching stream).
+e2e   : tokens/s through the drop-in operator `lamm_mul_mat` (ggml_tensor structs over
+        HOST buffers; per matmul H2D of X, kernels, D2H of C inside the timed region).
+roofline : the GEMV kernel alone (pre-quantized activations), algorithmic bytes / time.
+cpu_baseline / --impl reference : the UNMODIFIED reference (oracle/_ref/libref.so,
+        lamm AVX2 backend) through ggml_graph_compute on the host cores.
+
+With --gpus N > 1 (torchrun) every weight is row-sharded M/N per rank and the output
+slices are all-gathered over NVLink after every matmul (strong scaling).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# ---- the workload (SURVEY 8d "tok/s definition") ---------------------------------------
+H, F, V, LAYERS = 4096, 11008, 32000, 32
+LAYER_SHAPES = [("wq", H, H), ("wk", H, H), ("wv", H, H), ("wo", H, H),
+                ("gate", F, H), ("up", F, H), ("down", H, F)]          # (name, M, K)
+HEAD_SHAPE = ("head", V, H)
+TYPE_IDS = {"f32": 0, "q4_0": 2, "q4_1": 3, "q5_0": 6, "q5_1": 7, "q8_0": 8, "q2_k": 10}
+BLCK = {0: 1, 2: 32, 3: 32, 6: 32, 7: 32, 8: 32, 10: 256}
+TSIZE = {0: 4, 2: 18, 3: 20, 6: 22, 7: 24, 8: 34, 10: 84}
+VEC_DOT = {0: 0, 2: 8, 3: 9, 6: 8, 7: 9, 8: 8, 10: 15}
+ACT_SIZE = {0: (1, 4), 8: (32, 34), 9: (32, 36), 15: (256, 292)}
+
+
+def chain_ops():
+    ops = []
+    for _ in range(LAYERS):
+        ops.extend(LAYER_SHAPES)
+    ops.append(HEAD_SHAPE)
+    return ops
+
+
+def w_row_bytes(t, k):
+    return (k // BLCK[t]) * TSIZE[t]
+
+
+def gemv_bytes(t, m, k, n=1):
+    """Algorithmic bytes of one mul_mat: W blocks + f32 X + f32 C."""
+    return m * w_row_bytes(t, k) + n * k * 4 + n * m * 4
+
+
+def gemv_kernel_bytes(t, m, k, n=1):
+    """Algorithmic bytes of the GEMV kernel alone: W blocks + quantized X + f32 C."""
+    blck, size = ACT_SIZE[VEC_DOT[t]]
+    return m * w_row_bytes(t, k) + n * (k // blck) * size + n * m * 4
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ---- clocks during the timed region ---------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---- synthetic quantized tensors, generated on the device -----------------------------
+def synth_weight(torch, t, m, k, gen, device):
+    """Random ggml blocks: uniform random quant bytes, fp16 scales/mins in U(0.001, 0.03)
+    (never NaN/Inf) -- SURVEY 8d 'alternative fast path'.  Returns uint8 [m, row_bytes]."""
+    if t == 0:
+        return (torch.randn((m, k), generator=gen, device=device, dtype=torch.float32) * 0.02).view(torch.uint8)
+    kb, bs = k // BLCK[t], TSIZE[t]
+    raw = torch.randint(0, 256, (m, kb, bs), generator=gen, device=device, dtype=torch.uint8)
+    halves = raw.view(torch.int16)                       # [m, kb, bs/2]
+
+    def scale():
+        v = torch.rand((m, kb), generator=gen, device=device) * 0.029 + 0.001
+        return v.to(torch.float16).view(torch.int16)
+    if t in (2, 6, 8):       # {d, ...}
+        halves[:, :, 0] = scale()
+    elif t in (3, 7):        # {d, m, ...}
+        halves[:, :, 0] = scale()
+        halves[:, :, 1] = scale()
+    elif t == 10:            # q2_K {scales[16], qs[64], d, dmin}
+        halves[:, :, 40] = scale()
+        halves[:, :, 41] = scale()
+    return raw.view(m, kb * bs)
+
+
+def host_threads():
+    try:
+        import psutil
+        n = psutil.cpu_count(logical=False) or os.cpu_count() or 1
+    except Exception:
+        n = os.cpu_count() or 1
+    try:
+        n = min(n, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        pass
+    p = 1
+    while p * 2 <= min(n, 64):   # power of two: must divide M (reference drops M % nth rows)
+        p *= 2
+    return p
+
+
+# ---- the reference's own CPU path ------------------------------------------------------
+def cpu_reference_run(t, iters, warmup, nth=None):
+    """Times the unmodified reference (oracle/_ref/libref.so; falls back to the oracle port)
+    on the host cores.  Per step: ONE timed ggml_graph_compute of each distinct matmul shape of
+    the token chain (plus the reference benchmark's untimed cache-thrash graph in between),
+    extrapolated by the shapes' multiplicities: t_token = 32*(4 a + 2 b + c) + head."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle_lib import Oracle, Ref
+    nth = nth or host_threads()
+    rng = np.random.default_rng(5)
+    shapes = [("attn", H, H, 4 * LAYERS), ("gate_up", F, H, 2 * LAYERS), ("down", H, F, LAYERS), ("head", V, H, 1)]
+    per = {}
+    kind = "reference" if Ref.available() else "port"
+    if kind == "reference":
+        r = Ref()
+        for name, m, k, _ in shapes:
+            x = rng.standard_normal((1, k)).astype(np.float32)
+            w = rng.integers(0, 256, (m, w_row_bytes(t, k)), dtype=np.uint8)
+            fix_scales_host(w, t, k)
+            per[name] = np.array(r.bench(t, m, 1, k, nth, warmup + iters, wq=w, x=x))[warmup:] * 1e-6
+    else:
+        o = Oracle()
+        for name, m, k, _ in shapes:
+            x = rng.standard_normal((1, k)).astype(np.float32)
+            w = rng.integers(0, 256, (m, w_row_bytes(t, k)), dtype=np.uint8)
+            fix_scales_host(w, t, k)
+            ts = []
+            for _ in range(warmup + iters):
+                t0 = time.perf_counter()
+                o.mul_mat_mt(t, w, x, nth)
+                ts.append(time.perf_counter() - t0)
+            per[name] = np.array(ts[warmup:])
+    tok = sum(per[name] * mult for name, _, _, mult in shapes)        # seconds per token, per step
+    return {"sec_per_token": tok, "kind": kind, "cores": nth,
+            "sample": "per step one timed ggml_graph_compute (INIT quantize + lamm_mul_mat, N=1) of each "
+                      "distinct chain shape (4096x4096, 11008x4096, 4096x11008, 32000x4096), extrapolated "
+                      "x(128, 64, 32, 1); cache-thrash graph between timings as in la-benchmark-matmult",
+            "per_shape_us": {n_: float(np.mean(v) * 1e6) for n_, v in per.items()}}
+
+
+def fix_scales_host(w, t, k):
+    """Give random host blocks sane fp16 scales (same recipe as synth_weight)."""
+    if t == 0:
+        w.view(np.float32)[:] = 0.02
+        return
+    kb, bs = k // BLCK[t], TSIZE[t]
+    h = w.reshape(w.shape[0], kb, bs).view(np.uint16)
+    rng = np.random.default_rng(1)
+    sc = lambda: (rng.random((w.shape[0], kb), np.float32) * 0.029 + 0.001).astype(np.float16).view(np.uint16)
+    if t in (2, 6, 8):
+        h[:, :, 0] = sc()
+    elif t in (3, 7):
+        h[:, :, 0] = sc(); h[:, :, 1] = sc()
+    elif t == 10:
+        h[:, :, 40] = sc(); h[:, :, 41] = sc()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    t = TYPE_IDS[args.fmt]
+    r = cpu_reference_run(t, args.steps, args.warmup)
+    sec = float(np.mean(r["sec_per_token"]))
+    val = 1.0 / sec
+    line = {
+        "impl": "reference", "metric": "llama7b_%s_decode_matmul_chain_tokens_per_s" % args.fmt,
+        "value": val, "unit": "tok/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "i8 x u4 -> i32, f32 scale-accumulate (AVX2 maddubs)", "data": "synthetic",
+        "config": workload_config(args.fmt, 1),
+        "cpu_baseline": {"value": val, "unit": "tok/s", "cores": r["cores"], "kind": r["kind"],
+                         "sample": r["sample"], "per_shape_us": r["per_shape_us"]},
+        "e2e": {"value": val, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(fmt, world):
+    return {"workload": "LLaMA-7B %s decode (N=1) weight-matmul chain: 32 x {4x 4096x4096, 2x 11008x4096, "
+                        "1x 4096x11008} + head 32000x4096; activation quantize + quantized GEMV per matmul; "
+                        "attention/norm/rope/sampling excluded (not on the path)" % fmt.upper(),
+            "format": fmt, "n_tokens_per_step": 1, "matmuls_per_step": len(chain_ops()),
+            "l2_defeat": "225 distinct weight buffers per step (4.13 GB for Q4_1) >> 126 MB L2",
+            "parallelism": "row-sharded M/%d per rank + all-gather of C" % world if world > 1 else "single GPU"}
+
+
+# ---- the CUDA path ---------------------------------------------------------------------
+def run_cuda(args):
+    import torch
+    import lamm_b200 as L
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus %d needs torchrun (one rank per GPU)" % args.gpus)
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    L.init(local)
+    lib = L.lib()
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    t = TYPE_IDS[args.fmt]
+    vt = VEC_DOT[t]
+    ops = chain_ops()
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234)
+
+    def shard(m):                      # contiguous rows [lo, hi) of this rank
+        per = (m + world - 1) // world
+        lo = min(m, rank * per)
+        return lo, min(m, lo + per)
+
+    # weights: the rank's row shard of every matrix, distinct buffers
+    weights = []
+    for name, m, k in ops:
+        lo, hi = shard(m)
+        weights.append(synth_weight(torch, t, hi - lo, k, gen, dev))
+    xin = {H: torch.randn((1, H), generator=gen, device=dev), F: torch.randn((1, F), generator=gen, device=dev)}
+    outs = {m: torch.zeros((1, m), device=dev) for m in (H, F, V)}
+    act_blck, act_size = ACT_SIZE[vt]
+    xq_ws = torch.zeros(((F // act_blck) * act_size + 64,), dtype=torch.uint8, device=dev)
+    xq_pre = {k: (L.quantize_act(xin[k], vt) if t != 0 else xin[k]) for k in (H, F)}
+    gather_buf = {m: torch.zeros((world, (m + world - 1) // world), device=dev) for m in (H, F, V)} if world > 1 else None
+
+    def one_token(prequantized=False):
+        for (name, m, k), w in zip(ops, weights):
+            rows = w.shape[0]
+            if world == 1:
+                c = outs[m]
+            else:
+                c = gather_buf[m][rank:rank + 1, :rows]
+            wv = w if t != 0 else w.view(torch.float32)
+            if prequantized:
+                L.mul_mat_q(t, wv, xq_pre[k], k, out=c)
+            else:
+                L.mul_mat(t, wv, xin[k], out=c, ws=xq_ws)
+            if world > 1:
+                dist.all_gather_into_tensor(gather_buf[m].view(-1), gather_buf[m][rank])   # in place
+
+    def capture(fn):
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(2):
+                fn()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        lib.lammcu_launch_count_reset()
+        with torch.cuda.graph(g):
+            fn()
+        return g, int(lib.lammcu_launch_count())
+
+    def timed(g, steps, warmup):
+        for _ in range(warmup):
+            g.replay()
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if dist:
+            tt = torch.tensor([ms], device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dist.barrier()
+            ms = float(tt.item())
+        return ms
+
+    g_full, launches_per_token = capture(lambda: one_token(False))
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms = timed(g_full, args.steps, max(args.warmup, 3))
+    clocks = sampler.stop() if rank == 0 else None
+    tok_s = args.steps / (ms * 1e-3)
+
+    # roofline leg: the GEMV kernel alone on pre-quantized activations (same chain, same buffers)
+    g_q, launches_q = capture(lambda: one_token(True))
+    ms_q = timed(g_q, args.steps, 3)
+    peak, peak_src = peaks()
+    kern_bytes = sum(gemv_kernel_bytes(t, shard(m)[1] - shard(m)[0], k) for _, m, k in ops)
+    achieved = kern_bytes * args.steps / (ms_q * 1e-3) / 1e9
+    path_bytes = sum(gemv_bytes(t, m, k) for _, m, k in ops)
+
+    # e2e leg: the drop-in operator on HOST buffers (rank 0 / N=1 only does the H2D/D2H variant;
+    # with N>1 every rank runs it on its shard)
+    e2e = e2e_run(torch, L, t, ops, weights, shard, max(3, args.steps // 10), dist, dev, rank, world)
+
+    if rank != 0:
+        if dist:
+            dist.destroy_process_group()
+        return 0
+
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        try:
+            r = cpu_reference_run(t, 8, 2)
+            cpu = {"value": 1.0 / float(np.mean(r["sec_per_token"])), "unit": "tok/s", "cores": r["cores"],
+                   "kind": r["kind"], "sample": r["sample"], "per_shape_us": r["per_shape_us"]}
+        except Exception as e:      # the checker library is absent: say so, do not fake a number
+            cpu = {"value": None, "unit": "tok/s", "cores": 0, "kind": "unavailable", "sample": str(e)}
+
+    line = {
+        "metric": "llama7b_%s_decode_matmul_chain_tokens_per_s" % args.fmt,
+        "value": tok_s, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u4/u5/i8 weights x i8 activations -> i32 (dp4a), f32 scale-accumulate",
+        "data": "synthetic", "config": workload_config(args.fmt, world),
+        "path_gbs": path_bytes * args.steps / (ms * 1e-3) / 1e9,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "kernel": "gemv_stream_kernel<%s,1>" % args.fmt,
+                     "peak_source": peak_src,
+                     "how": "same chain on pre-quantized activations (GEMV launches only), CUDA events; "
+                            "bytes = W blocks + Xq + C per launch, %d launches/step, avg %.2f us/launch"
+                            % (launches_q, ms_q * 1e3 / args.steps / max(launches_q, 1))},
+        "cpu_baseline": cpu,
+        "e2e": e2e,
+        "gpu_launches": launches_per_token * args.steps,
+        "clocks": clocks,
+    }
+    print(json.dumps(line))
+    if dist:
+        dist.destroy_process_group()
+    return 0
+
+
+def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
+    """tokens/s through lamm_can_mul_mat + lamm_mul_mat with ggml_tensor structs over HOST memory:
+    the call ggml.c:10858-10863 makes.  Weights are registered (uploaded) on first use, outside the
+    timed region, exactly once -- they are immutable model state; X goes H2D and C comes D2H inside
+    every call."""
+    lib = L.lib()
+    # host copies of a bounded set of distinct weights: one layer + head, cycled (host RAM, not HBM,
+    # is what limits holding 4 GB twice); the device-side registry still holds them as distinct buffers
+    host_w = {}
+    n_layer = len(LAYER_SHAPES)
+    idx_for = list(range(n_layer)) * LAYERS + [len(ops) - 1]
+    for i in set(idx_for):
+        host_w[i] = weights[i].cpu().numpy()
+    xh = {k: np.random.default_rng(3).standard_normal((1, k)).astype(np.float32) for k in (H, F)}
+    ch = {m: np.zeros((1, m), np.float32) for m in (H, F, V)}
+    calls = []
+    keep = []
+    for (name, m, k), wi in zip(ops, idx_for):
+        w = host_w[wi]
+        rows = w.shape[0]
+        src0 = L.make_tensor_2d(t, k, rows, w.ctypes.data, w.strides[0])
+        src1 = L.make_tensor_2d(L.F32, k, 1, xh[k].ctypes.data, xh[k].strides[0])
+        dst = L.make_tensor_2d(L.F32, rows, 1, ch[m].ctypes.data)
+        dst.src[0] = C.pointer(src0)
+        dst.src[1] = C.pointer(src1)
+        p = L.GgmlComputeParams(L.TASK_COMPUTE, 0, 1, 0, None)
+        keep.append((src0, src1, dst, p))
+        calls.append((C.byref(p), C.byref(dst)))
+    can, mm = lib.lamm_can_mul_mat, lib.lamm_mul_mat
+
+    def token():
+        for p, d in calls:
+            if not can(p, d):
+                raise RuntimeError("lamm_can_mul_mat refused the bench shape")
+            mm(p, d)
+    token()          # uploads the weights
+    token()
+    torch.cuda.synchronize()
+    if dist:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        token()
+    torch.cuda.synchronize()
+    sec = time.perf_counter() - t0
+    if dist:
+        tt = torch.tensor([sec], device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        sec = float(tt.item())
+    h2d = sum(k * 4 for _, m, k in ops)
+    d2h = sum((shard(m)[1] - shard(m)[0]) * 4 for _, m, k in ops)
+    return {"value": steps / sec, "unit": "tok/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "steps": steps, "ms_per_step": sec / steps * 1e3,
+            "api": "lamm_can_mul_mat + lamm_mul_mat(ggml_compute_params*, ggml_tensor*) on host tensors, "
+                   "one synchronous call per matmul (225 per token); host wall clock",
+            "note": "weights uploaded once at first use (registry keyed by src0->data); with N>1 the "
+                    "per-rank C slices are not gathered in this leg"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--fmt", default="q4_1", choices=sorted(TYPE_IDS))
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_cuda(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
