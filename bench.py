@@ -467,6 +467,78 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
                     "per-rank C slices are not gathered in this leg"}
 
 
+# ---- per-format / per-shape sweep (not the driver's line; writes a table for profiles/) ----
+def run_suite(args):
+    """GEMV sweep: every format x LLaMA shape at N=args.n, a ring of distinct weight buffers
+    >= 512 MB replayed from one CUDA graph (L2-defeating).  Prints one JSON line
+    per case: us/launch, GB/s (algorithmic bytes of the whole op incl. the activation quantize when
+    --fused), fraction of the measured HBM peak."""
+    import torch
+    import lamm_b200 as L
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    L.init(0)
+    peak, _ = peaks()
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(7)
+    fmts = args.fmts.split(",") if args.fmts else ["q4_0", "q4_1", "q5_0", "q5_1", "q8_0", "q2_k", "f32"]
+    shapes = [(4096, 4096), (11008, 4096), (4096, 11008), (32000, 4096), (5120, 5120), (13824, 5120),
+              (6656, 6656), (17920, 6656), (6656, 17920)]
+    if args.shapes:
+        shapes = [tuple(int(v) for v in s_.split("x")) for s_ in args.shapes.split(",")]
+    n = args.n
+    out = []
+    for fmt in fmts:
+        t = TYPE_IDS[fmt]
+        vt = VEC_DOT[t]
+        for (m, k) in shapes:
+            if k % BLCK[t]:
+                continue
+            wb = m * w_row_bytes(t, k)
+            ring = max(2, min(96, (args.ring_mb * (1 << 20) + wb - 1) // wb))
+            ws = [synth_weight(torch, t, m, k, gen, dev) for _ in range(ring)]
+            x = torch.randn((n, k), generator=gen, device=dev)
+            xq = L.quantize_act(x, vt) if t != 0 else x
+            c = torch.zeros((n, m), device=dev)
+            blck, size = ACT_SIZE[vt]
+            xq_ws = torch.zeros((n * (k // blck) * size + 64,), dtype=torch.uint8, device=dev)
+
+            def body():
+                for w in ws:
+                    wv = w if t != 0 else w.view(torch.float32)
+                    if args.fused:
+                        L.mul_mat(t, wv, x, out=c, ws=xq_ws)
+                    else:
+                        L.mul_mat_q(t, wv, xq, k, out=c)
+            s = torch.cuda.Stream()
+            with torch.cuda.stream(s):
+                body()
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                body()
+            for _ in range(3):
+                g.replay()
+            torch.cuda.synchronize()
+            reps = max(3, int(2000 / ring))
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                g.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            us = e0.elapsed_time(e1) * 1e3 / (reps * ring)
+            by = gemv_bytes(t, m, k, n) if args.fused else gemv_kernel_bytes(t, m, k, n)
+            rec = {"fmt": fmt, "M": m, "K": k, "N": n, "fused_quantize": bool(args.fused), "ring": ring,
+                   "us": round(us, 3), "GBps": round(by / us / 1e3, 1), "frac_hbm": round(by / us / 1e3 / peak, 4),
+                   "gops": round(2.0 * m * n * k / us / 1e3, 1)}
+            print(json.dumps(rec), flush=True)
+            out.append(rec)
+            del ws, g
+            torch.cuda.empty_cache()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -475,7 +547,15 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--fmt", default="q4_1", choices=sorted(TYPE_IDS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--suite", default=None, choices=[None, "gemv"], help="per-format sweep instead of the bench line")
+    ap.add_argument("--fmts", default=None)
+    ap.add_argument("--shapes", default=None, help="MxK,MxK,...")
+    ap.add_argument("--n", type=int, default=1)
+    ap.add_argument("--ring-mb", type=int, default=512)
+    ap.add_argument("--fused", action="store_true", help="suite: include the activation quantize launch")
     args = ap.parse_args()
+    if args.suite:
+        return run_suite(args)
     if args.impl == "reference":
         return run_reference(args)
     return run_cuda(args)

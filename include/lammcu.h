@@ -104,6 +104,10 @@ int lammcu_mul_mat_dev(int w_type, const void *w_dev, int64_t w_stride_bytes,
  * memory-bound GEMV kernels, larger N the tensor-core GEMM.  Default 8.      */
 int lammcu_set_gemv_max_n(int n);
 int lammcu_get_gemv_max_n(void);
+/* N == 1: 1 (default) = the single-launch decode kernel (fused activation
+ * quantize, programmatic dependent launch); 0 = quantize kernel + generic GEMV */
+int lammcu_set_decode_kernel(int enable);
+int lammcu_get_decode_kernel(void);
 
 /* ---- host operands (what lamm_mul_mat passes) --------------------------- */
 typedef struct lammcu_weight *lammcu_weight_t;

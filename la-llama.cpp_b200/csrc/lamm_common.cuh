@@ -121,6 +121,10 @@ int launch_gemv(int w_type, const void *w, int64_t w_stride, const void *xq, int
                 float *c, int64_t ldc, int64_t M, int64_t N, int64_t K, cudaStream_t st);
 int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride,
                 float *c, int64_t ldc, int64_t M, int64_t N, int64_t K, cudaStream_t st);
+// single-launch decode (N == 1): fused activation quantize (x != NULL) or pre-quantized row (xq)
+bool decode_supported(int w_type, const void *w, int64_t w_stride, const void *x_or_xq, int64_t M, int64_t K);
+int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
+                  float *c, int64_t M, int64_t K, cudaStream_t st);
 void set_error(const char *fmt, ...);
 int sm_count_cached();
 // scratch for the dynamic tile scheduler: returns a zeroed pair of counters

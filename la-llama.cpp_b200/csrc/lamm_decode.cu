@@ -1,0 +1,542 @@
+// lamm_decode.cu -- the decode path proper (N == 1): one launch per mul_mat.
+//
+// Replaces, for one activation row, ggml's INIT-phase quantize (llama.cpp-b2430/ggml.c:
+// 10865-10887 -> quantize_row_q8_{0,1,K}) AND LAMMImpl<T>::matmul + lamm_kernel_*.hpp
+// (src/lamm_impl.hpp:20-147) with a single HBM-bound kernel:
+//
+//   * every warp streams its own rows: lane 0 issues cp.async.bulk (TMA 1-D, SASS UBLKCP)
+//     copies of (row, K-segment) spans HBM -> a private ring of shared-memory slots, each
+//     guarded by an mbarrier; no producer warp, no cross-warp hand-off;
+//   * the activation row is quantized once per CTA (bit-exact q8_0 / q8_1 / q8_K, shared
+//     arithmetic with lamm_quantize.cu), laid out conflict-free in shared memory, and each
+//     lane then keeps the quants of ITS blocks in registers for the whole kernel, so the
+//     inner loop reads only weights from shared memory;
+//   * a lane owns 4 consecutive 32-blocks (72/80/88/96/136 contiguous bytes, read with
+//     LDS.64/LDS.128, fields picked with compile-time offsets) or half a Q2_K super-block;
+//     nibbles / 5th bits / K-quant sub-scales are unpacked in registers, the block dot is
+//     dp4a (dp2a for the Q2_K min term), the row finishes with a warp-shuffle reduction;
+//   * rows are dealt round-robin to SMs so every SM streams the same number of bytes (+-1
+//     row), and programmatic dependent launch lets the NEXT mul_mat of a chain start
+//     streaming its (immutable) weights while this one drains -- activations are only read
+//     after griddepcontrol.wait.
+#include "lamm_quant_dev.cuh"
+
+namespace lamm {
+
+constexpr int kDecWarps = 8;
+constexpr int kDecThreads = kDecWarps * 32;
+constexpr int kDecMaxSlots = 4;
+constexpr int kDecCtrl = 1024;       // mbarriers [8][4] + partial sums
+
+struct DecodeParams {
+  const uint8_t *w;   int64_t w_stride;   // bytes
+  const float *x;                         // f32 activation row      (XF32)
+  const uint8_t *xq;                      // quantized activation row (!XF32), ggml layout
+  uint8_t *xq_out;                        // optional: CTA 0 stores the quantized row here
+  float *c;
+  int M, kb;            // rows; blocks per row (Q2_K: super-blocks)
+  int units;            // lane units per row (4 blocks, or half a super-block)
+  int KS, seg_units;    // K segments per row, units per segment (<= 32)
+  int RG;               // row groups per CTA (= active warps / KS)
+  int slots, slot_bytes;
+  int x_bytes;          // shared-memory bytes of the staged activations
+};
+
+// ---- integer dots -------------------------------------------------------------------
+__device__ __forceinline__ int dp4a_u8s8(uint32_t a, uint32_t b, int c) {
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ int dp4a_s8s8(uint32_t a, uint32_t b, int c) {
+  int d;
+  asm("dp4a.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+// a: 2 x s16, b: 4 x u8 (lo: bytes 0,1; hi: bytes 2,3)
+__device__ __forceinline__ int dp2a_lo_s16u8(uint32_t a, uint32_t b, int c) {
+  int d;
+  asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ int dp2a_hi_s16u8(uint32_t a, uint32_t b, int c) {
+  int d;
+  asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+
+// ---- per-format constants -------------------------------------------------------------
+template <int WT> struct DecFmt {
+  static constexpr int BS = type_info(WT).size;          // bytes per 32-block
+  static constexpr int NW = BS;                          // words per lane chunk (4 blocks)
+  static constexpr int VT = type_info(WT).vec_dot;
+  static constexpr bool kHasMin = (WT == LAMMCU_TYPE_Q4_1 || WT == LAMMCU_TYPE_Q5_1);
+};
+
+// NW consecutive words from a shared address aligned to 16 (NW % 4 == 0) or 8 bytes
+template <int NW>
+__device__ __forceinline__ void lds_chunk(uint32_t (&w)[NW], uint32_t addr) {
+  if constexpr (NW % 4 == 0) {
+#pragma unroll
+    for (int i = 0; i < NW / 4; i++)
+      asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(w[4 * i]), "=r"(w[4 * i + 1]), "=r"(w[4 * i + 2]), "=r"(w[4 * i + 3])
+                   : "r"(addr + 16u * i));
+  } else {
+#pragma unroll
+    for (int i = 0; i < NW / 2; i++)
+      asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(w[2 * i]), "=r"(w[2 * i + 1]) : "r"(addr + 8u * i));
+  }
+}
+// the 32-bit word at compile-time byte offset OFF (OFF % 2 == 0) of the chunk
+template <int OFF, int NW>
+__device__ __forceinline__ uint32_t word_at(const uint32_t (&w)[NW]) {
+  if constexpr (OFF % 4 == 0) return w[OFF / 4];
+  else return __byte_perm(w[OFF / 4], w[OFF / 4 + 1], 0x5432);
+}
+template <int OFF, int NW>
+__device__ __forceinline__ float half_at(const uint32_t (&w)[NW]) {
+  if constexpr (OFF % 4 == 0) return half_bits_to_float(w[OFF / 4] & 0xffffu);
+  else return half_bits_to_float(w[OFF / 4] >> 16);
+}
+// 4 bits -> bit 4 of 4 consecutive bytes (Q5 "5th bit": element j <- bit j)
+__device__ __forceinline__ uint32_t spread_bit4(uint32_t nib) {
+  return (nib * 0x02040810u) & 0x10101010u;
+}
+
+// One 32-block of the lane's chunk against the lane's register-resident activations.
+// xq[0..3]: elements 0..15, xq[4..7]: elements 16..31; xd = f32(d_x);
+// xs = f32(s_x) for q8_1, or bit-cast integer sum of the quants for q8_0.
+template <int WT, int J, int NW>
+__device__ __forceinline__ float block_dot(const uint32_t (&w)[NW], const uint32_t (&xall)[32], float xd,
+                                           float xs, float acc) {
+  constexpr int O = J * DecFmt<WT>::BS;
+  const uint32_t xq[8] = {xall[8 * J],     xall[8 * J + 1], xall[8 * J + 2], xall[8 * J + 3],
+                          xall[8 * J + 4], xall[8 * J + 5], xall[8 * J + 6], xall[8 * J + 7]};
+  if constexpr (WT == LAMMCU_TYPE_Q4_0 || WT == LAMMCU_TYPE_Q4_1) {
+    constexpr int QS = O + (WT == LAMMCU_TYPE_Q4_0 ? 2 : 4);
+    int slo = 0, shi = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const uint32_t q = (i == 0)   ? word_at<QS, NW>(w)
+                         : (i == 1) ? word_at<QS + 4, NW>(w)
+                         : (i == 2) ? word_at<QS + 8, NW>(w)
+                                    : word_at<QS + 12, NW>(w);
+      slo = dp4a_u8s8(q & 0x0F0F0F0Fu, xq[i], slo);
+      shi = dp4a_u8s8(q & 0xF0F0F0F0u, xq[4 + i], shi);      // 16 x the high-nibble dot, exactly
+    }
+    int sumi = slo + (shi >> 4);
+    if constexpr (WT == LAMMCU_TYPE_Q4_0) {
+      sumi -= 8 * __float_as_int(xs);                          // sum((q-8) x) = sum(q x) - 8 sum(x)
+      return fmaf(half_at<O, NW>(w) * xd, (float)sumi, acc);
+    } else {
+      acc = fmaf(half_at<O, NW>(w) * xd, (float)sumi, acc);
+      return fmaf(half_at<O + 2, NW>(w), xs, acc);             // + m_w * s_x
+    }
+  } else if constexpr (WT == LAMMCU_TYPE_Q5_0 || WT == LAMMCU_TYPE_Q5_1) {
+    constexpr int QH = O + (WT == LAMMCU_TYPE_Q5_0 ? 2 : 4);
+    constexpr int QS = QH + 4;
+    const uint32_t qh = word_at<QH, NW>(w);
+    int sumi = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const uint32_t q = (i == 0)   ? word_at<QS, NW>(w)
+                         : (i == 1) ? word_at<QS + 4, NW>(w)
+                         : (i == 2) ? word_at<QS + 8, NW>(w)
+                                    : word_at<QS + 12, NW>(w);
+      const uint32_t lo = (q & 0x0F0F0F0Fu) | spread_bit4((qh >> (4 * i)) & 0xFu);
+      const uint32_t hi = ((q >> 4) & 0x0F0F0F0Fu) | spread_bit4((qh >> (16 + 4 * i)) & 0xFu);
+      sumi = dp4a_u8s8(lo, xq[i], sumi);
+      sumi = dp4a_u8s8(hi, xq[4 + i], sumi);
+    }
+    if constexpr (WT == LAMMCU_TYPE_Q5_0) {
+      sumi -= 16 * __float_as_int(xs);
+      return fmaf(half_at<O, NW>(w) * xd, (float)sumi, acc);
+    } else {
+      acc = fmaf(half_at<O, NW>(w) * xd, (float)sumi, acc);
+      return fmaf(half_at<O + 2, NW>(w), xs, acc);
+    }
+  } else {   // Q8_0
+    constexpr int QS = O + 2;
+    int sumi = 0;
+    sumi = dp4a_s8s8(word_at<QS, NW>(w), xq[0], sumi);
+    sumi = dp4a_s8s8(word_at<QS + 4, NW>(w), xq[1], sumi);
+    sumi = dp4a_s8s8(word_at<QS + 8, NW>(w), xq[2], sumi);
+    sumi = dp4a_s8s8(word_at<QS + 12, NW>(w), xq[3], sumi);
+    sumi = dp4a_s8s8(word_at<QS + 16, NW>(w), xq[4], sumi);
+    sumi = dp4a_s8s8(word_at<QS + 20, NW>(w), xq[5], sumi);
+    sumi = dp4a_s8s8(word_at<QS + 24, NW>(w), xq[6], sumi);
+    sumi = dp4a_s8s8(word_at<QS + 28, NW>(w), xq[7], sumi);
+    return fmaf(half_at<O, NW>(w) * xd, (float)sumi, acc);
+  }
+}
+
+// ---- activation staging: f32 (or ggml-quantized) row -> shared memory --------------------
+// 32-element formats, U = units per row (kb / 4):
+//   xqs : uint4 [8][U]   slot j of unit u = quant words (j&1)*4.. of block 4u + j/2
+//   xds : float2 [kb]    (d, s) or (d, bit-cast int sum)
+// Q2_K / Q8_K, U = 2 * super-blocks (unit = 128 elements):
+//   xqs : uint4 [8][U]   slot j of unit u = quant words 4j..4j+3 of the unit (32 words)
+//   xbs : uint4 [U]      8 x int16 bsums of the unit
+//   xd  : float [kb]
+template <int VT, bool XF32>
+__device__ __forceinline__ void stage_x_row(const DecodeParams &p, uint8_t *xs) {
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int U = p.units;
+  uint32_t *xqs = reinterpret_cast<uint32_t *>(xs);
+  const bool store = (p.xq_out != nullptr) && blockIdx.x == 0 && XF32;
+  if constexpr (VT == LAMMCU_TYPE_Q8_K) {
+    uint32_t *xbs = xqs + (size_t)32 * U;
+    float *xd = reinterpret_cast<float *>(xbs + (size_t)4 * U);
+    for (int sb = tid >> 5; sb < p.kb; sb += kDecWarps) {
+      uint32_t q_lo, q_hi;
+      float d;
+      int pair_sum;
+      if constexpr (XF32) {
+        const float4 *xp = reinterpret_cast<const float4 *>(p.x + (size_t)sb * 256 + lane * 8);
+        const float4 a = xp[0], b = xp[1];
+        const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        quant256_lane8(v, lane, q_lo, q_hi, d, pair_sum);
+        if (store) {
+          uint8_t *blk = p.xq_out + (size_t)sb * 292;
+          uint32_t *qs = reinterpret_cast<uint32_t *>(blk + Q8_K_QS + lane * 8);
+          qs[0] = q_lo;
+          qs[1] = q_hi;
+          if ((lane & 1) == 0) *reinterpret_cast<int16_t *>(blk + Q8_K_BSUMS + lane) = (int16_t)pair_sum;
+          if (lane == 0) *reinterpret_cast<float *>(blk) = d;
+        }
+      } else {
+        const uint8_t *blk = p.xq + (size_t)sb * 292;
+        const uint32_t *qs = reinterpret_cast<const uint32_t *>(blk + Q8_K_QS + lane * 8);
+        q_lo = qs[0];
+        q_hi = qs[1];
+        pair_sum = *reinterpret_cast<const int16_t *>(blk + Q8_K_BSUMS + (lane & ~1));
+        d = *reinterpret_cast<const float *>(blk);
+      }
+      const int unit = 2 * sb + (lane >> 4), wi = (2 * lane) & 31;
+      uint32_t *dst = xqs + ((size_t)(wi >> 2) * U + unit) * 4 + (wi & 3);
+      dst[0] = q_lo;
+      dst[1] = q_hi;
+      if ((lane & 1) == 0) {
+        const int g = lane >> 1;
+        reinterpret_cast<int16_t *>(xbs)[(size_t)(2 * sb + (g >> 3)) * 8 + (g & 7)] = (int16_t)pair_sum;
+      }
+      if (lane == 0) xd[sb] = d;
+    }
+  } else {
+    constexpr int XB = (VT == LAMMCU_TYPE_Q8_0) ? 34 : 36;
+    float2 *xds = reinterpret_cast<float2 *>(xqs + (size_t)32 * U);
+    const int l8 = tid & 7;
+    for (int b0 = 0; b0 < p.kb; b0 += kDecThreads / 8) {
+      const int b = b0 + (tid >> 3);
+      const bool live = b < p.kb;
+      uint32_t q = 0;
+      float df = 0.f, sf = 0.f;
+      if constexpr (XF32) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (live) v = *reinterpret_cast<const float4 *>(p.x + (size_t)b * 32 + l8 * 4);
+        float d;
+        int sum;
+        q = quant32_lane4(v, d, sum);
+        const __half hd = __float2half_rn(d);
+        df = __half2float(hd);
+        __half hs = __float2half_rn(0.f);
+        if constexpr (VT == LAMMCU_TYPE_Q8_1) {
+          hs = __float2half_rn(__fmul_rn((float)sum, d));
+          sf = __half2float(hs);
+        } else {
+          sf = __int_as_float(sum);
+        }
+        if (store && live) {
+          uint8_t *blk = p.xq_out + (size_t)b * XB;
+          if constexpr (VT == LAMMCU_TYPE_Q8_1) {
+            *reinterpret_cast<uint32_t *>(blk + 4 + l8 * 4) = q;
+            if (l8 == 0) *reinterpret_cast<__half2 *>(blk) = __halves2half2(hd, hs);
+          } else {
+            uint16_t *o = reinterpret_cast<uint16_t *>(blk + 2 + l8 * 4);
+            o[0] = (uint16_t)(q & 0xffff);
+            o[1] = (uint16_t)(q >> 16);
+            if (l8 == 0) *reinterpret_cast<__half *>(blk) = hd;
+          }
+        }
+      } else {
+        int sum = 0;
+        if (live) {
+          const uint8_t *blk = p.xq + (size_t)b * XB;
+          if constexpr (VT == LAMMCU_TYPE_Q8_1) {
+            q = *reinterpret_cast<const uint32_t *>(blk + 4 + 4 * l8);
+            const uint32_t ds = *reinterpret_cast<const uint32_t *>(blk);
+            df = half_bits_to_float(ds & 0xffffu);
+            sf = half_bits_to_float(ds >> 16);
+          } else {
+            const uint16_t *h = reinterpret_cast<const uint16_t *>(blk + 2 + 4 * l8);
+            q = (uint32_t)h[0] | ((uint32_t)h[1] << 16);
+            df = half_bits_to_float(*reinterpret_cast<const uint16_t *>(blk));
+          }
+        }
+        if constexpr (VT == LAMMCU_TYPE_Q8_0) {
+          sum = dp4a_s8s8(q, 0x01010101u, 0);
+          sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+          sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+          sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+          sf = __int_as_float(sum);
+        }
+      }
+      if (live) {
+        const int u = b >> 2, j = (b & 3) * 2 + (l8 >> 2);
+        xqs[((size_t)j * U + u) * 4 + (l8 & 3)] = q;
+        if (l8 == 0) xds[b] = make_float2(df, sf);
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// ---- the kernel ----------------------------------------------------------------------
+template <int WT, bool XF32>
+__global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodeParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  constexpr bool kQ2K = (WT == LAMMCU_TYPE_Q2_K);
+  constexpr int VT = type_info(WT).vec_dot;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem) + warp * kDecMaxSlots;
+  float *part = reinterpret_cast<float *>(smem + 512);          // [RG][2][KS]
+  uint8_t *xs = smem + kDecCtrl;
+  uint8_t *ring = xs + p.x_bytes + (size_t)warp * p.slots * p.slot_bytes;
+
+  const bool active = warp < p.RG * p.KS;
+  const int rg = warp / p.KS, seg = warp - rg * p.KS;
+  const int u0 = seg * p.seg_units;                              // first unit of the segment
+  const int seg_n = max(0, min(p.seg_units, p.units - u0));      // live lanes
+  const int unit_bytes = kQ2K ? 42 : 4 * type_info(WT).size;
+  // Q2_K: a unit is half a super-block, segments start on super-block boundaries
+  const uint32_t seg_off = kQ2K ? (uint32_t)(u0 >> 1) * 84u : (uint32_t)u0 * unit_bytes;
+  const uint32_t seg_bytes = kQ2K ? (uint32_t)((seg_n + 1) >> 1) * 84u : (uint32_t)seg_n * unit_bytes;
+  const int row0 = blockIdx.x + gridDim.x * rg, row_step = gridDim.x * p.RG;
+
+  auto issue = [&](int i, uint64_t pol) {                        // lane 0: stream row i of this warp
+    const int r = row0 + i * row_step;
+    const uintptr_t a = (uintptr_t)(p.w + (int64_t)r * p.w_stride + seg_off);
+    const uintptr_t a0 = a & ~(uintptr_t)15;
+    const uint32_t bytes = (uint32_t)(((a + seg_bytes + 15) & ~(uintptr_t)15) - a0);
+    const int s = i % p.slots;
+    mbar_arrive_expect_tx(&full[s], bytes);
+    bulk_g2s_stream(ring + (size_t)s * p.slot_bytes, reinterpret_cast<const void *>(a0), bytes, &full[s], pol);
+  };
+
+  uint64_t pol = 0;
+  if (active && lane == 0) {
+    for (int s = 0; s < p.slots; s++) mbar_init(&full[s], 1);
+    fence_barrier_init();
+    pol = policy_evict_first();
+    // weights are immutable: start streaming before the previous kernel has finished
+    for (int i = 0; i < p.slots; i++)
+      if (row0 + i * row_step < p.M) issue(i, pol);
+  }
+  pdl_launch_dependents();
+  pdl_wait();                                                    // activations are valid from here on
+  stage_x_row<VT, XF32>(p, xs);
+  __syncthreads();
+  if (!active) return;
+
+  // ---- the lane's activations, register-resident for the whole kernel ----
+  const int U = p.units, ug = u0 + lane;
+  const bool lane_live = lane < seg_n;
+  const uint4 *xqs = reinterpret_cast<const uint4 *>(xs);
+  uint32_t xq[32];
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    const uint4 v = lane_live ? xqs[(size_t)j * U + ug] : make_uint4(0u, 0u, 0u, 0u);
+    xq[4 * j] = v.x; xq[4 * j + 1] = v.y; xq[4 * j + 2] = v.z; xq[4 * j + 3] = v.w;
+  }
+  float xd[4] = {0.f, 0.f, 0.f, 0.f}, xsum[4] = {0.f, 0.f, 0.f, 0.f};
+  uint32_t xb[4] = {0u, 0u, 0u, 0u};
+  if constexpr (kQ2K) {
+    const uint4 *xbs = xqs + (size_t)8 * U;
+    const float *xdp = reinterpret_cast<const float *>(xbs + U);
+    const uint4 b = lane_live ? xbs[ug] : make_uint4(0u, 0u, 0u, 0u);
+    xb[0] = b.x; xb[1] = b.y; xb[2] = b.z; xb[3] = b.w;
+    xd[0] = lane_live ? xdp[ug >> 1] : 0.f;
+  } else {
+    const float2 *xds = reinterpret_cast<const float2 *>(xqs + (size_t)8 * U);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const float2 v = lane_live ? xds[4 * ug + j] : make_float2(0.f, 0.f);
+      xd[j] = v.x;
+      xsum[j] = v.y;
+    }
+  }
+
+  const int lane_c = lane_live ? lane : 0;     // dead lanes re-read unit 0 (their activations are 0)
+  for (int i = 0;; i++) {
+    const int r = row0 + i * row_step;
+    if (r >= p.M) break;
+    const int s = i % p.slots;
+    mbar_wait(&full[s], (uint32_t)(i / p.slots) & 1u);
+    const uintptr_t a = (uintptr_t)(p.w + (int64_t)r * p.w_stride + seg_off);
+    const uint32_t base = smem_u32(ring + (size_t)s * p.slot_bytes) + (uint32_t)(a & 15);
+    float acc = 0.f;
+    if constexpr (kQ2K) {
+      const uint32_t blk = base + (uint32_t)(lane_c >> 1) * 84u;
+      const uint32_t h = lane_c & 1;
+      uint32_t q[8], scw[2], dm;
+#pragma unroll
+      for (int k = 0; k < 8; k++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(q[k]) : "r"(blk + 16u + 32u * h + 4u * k));
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(scw[0]) : "r"(blk + 8u * h));
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(scw[1]) : "r"(blk + 8u * h + 4u));
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(dm) : "r"(blk + 80u));
+      const uint32_t sc0 = scw[0] & 0x0F0F0F0Fu, sc1 = scw[1] & 0x0F0F0F0Fu;
+      const uint32_t mn0 = (scw[0] >> 4) & 0x0F0F0F0Fu, mn1 = (scw[1] >> 4) & 0x0F0F0F0Fu;
+      int summs = dp2a_lo_s16u8(xb[0], mn0, 0);
+      summs = dp2a_hi_s16u8(xb[1], mn0, summs);
+      summs = dp2a_lo_s16u8(xb[2], mn1, summs);
+      summs = dp2a_hi_s16u8(xb[3], mn1, summs);
+      int isum = 0;
+#pragma unroll
+      for (int j = 0; j < 4; j++) {          // bit plane j: elements 32j.. of the unit
+        const uint32_t mask = 0x03030303u << (2 * j);
+#pragma unroll
+        for (int e = 0; e < 2; e++) {        // sub-block 2j + e
+          int t = 0;
+#pragma unroll
+          for (int k = 0; k < 4; k++) t = dp4a_u8s8(q[4 * e + k] & mask, xq[8 * j + 4 * e + k], t);
+          const int g = 2 * j + e;
+          const uint32_t scale = ((g < 4 ? sc0 : sc1) >> (8 * (g & 3))) & 0xFFu;
+          isum += (int)scale * (t >> (2 * j));             // t is exactly 4^j x the plane dot
+        }
+      }
+      const float wd = half_bits_to_float(dm & 0xffffu), wdmin = half_bits_to_float(dm >> 16);
+      acc = fmaf(xd[0] * wd, (float)isum, acc);
+      acc = fmaf(-(xd[0] * wdmin), (float)summs, acc);
+    } else {
+      constexpr int NW = DecFmt<WT>::NW;
+      uint32_t w[NW];
+      lds_chunk<NW>(w, base + (uint32_t)lane_c * (4u * NW));
+      acc = block_dot<WT, 0, NW>(w, xq, xd[0], xsum[0], acc);
+      acc = block_dot<WT, 1, NW>(w, xq, xd[1], xsum[1], acc);
+      acc = block_dot<WT, 2, NW>(w, xq, xd[2], xsum[2], acc);
+      acc = block_dot<WT, 3, NW>(w, xq, xd[3], xsum[3], acc);
+    }
+    __syncwarp();
+    if (lane == 0 && row0 + (i + p.slots) * row_step < p.M) {
+      fence_proxy_async();                                   // our reads of the slot precede the refill
+      issue(i + p.slots, pol);
+    }
+    acc = warp_sum(acc);
+    if (p.KS == 1) {
+      if (lane == 0) p.c[r] = acc;
+    } else {
+      float *pb = part + (size_t)(rg * 2 + (i & 1)) * p.KS;
+      if (lane == 0) pb[seg] = acc;
+      asm volatile("bar.sync %0, %1;" ::"r"(1 + rg), "r"(p.KS * 32) : "memory");
+      if (seg == 0 && lane == 0) {
+        float t = 0.f;
+        for (int k = 0; k < p.KS; k++) t += pb[k];
+        p.c[r] = t;
+      }
+    }
+  }
+}
+
+// ---- host side --------------------------------------------------------------------------
+constexpr int kDecSmemMax = 227 * 1024;
+
+template <int WT, bool XF32>
+static int launch_decode_t(const DecodeParams &p, int grid, int smem, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(decode_kernel<WT, XF32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kDecSmemMax);
+    if (e != cudaSuccess) {
+      set_error("decode: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      return LAMMCU_ERR_CUDA;
+    }
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kDecThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, decode_kernel<WT, XF32>, p);
+  g_launch_count++;
+  if (e != cudaSuccess) {
+    set_error("decode launch (type %d, smem %d): %s", WT, smem, cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
+template <bool XF32>
+static int launch_decode_x(int w_type, const DecodeParams &p, int grid, int smem, cudaStream_t st) {
+  switch (w_type) {
+  case LAMMCU_TYPE_Q4_0: return launch_decode_t<LAMMCU_TYPE_Q4_0, XF32>(p, grid, smem, st);
+  case LAMMCU_TYPE_Q4_1: return launch_decode_t<LAMMCU_TYPE_Q4_1, XF32>(p, grid, smem, st);
+  case LAMMCU_TYPE_Q5_0: return launch_decode_t<LAMMCU_TYPE_Q5_0, XF32>(p, grid, smem, st);
+  case LAMMCU_TYPE_Q5_1: return launch_decode_t<LAMMCU_TYPE_Q5_1, XF32>(p, grid, smem, st);
+  case LAMMCU_TYPE_Q8_0: return launch_decode_t<LAMMCU_TYPE_Q8_0, XF32>(p, grid, smem, st);
+  default:               return launch_decode_t<LAMMCU_TYPE_Q2_K, XF32>(p, grid, smem, st);
+  }
+}
+
+// Whether the single-launch decode kernel can take this operand set (else the caller uses
+// the generic GEMV of lamm_gemv.cu, which handles any 2/4-byte alignment and any K).
+bool decode_supported(int w_type, const void *w, int64_t w_stride, const void *x_or_xq, int64_t M, int64_t K) {
+  if (w_type == LAMMCU_TYPE_F32 || !lammcu_type_supported(w_type)) return false;
+  if (M <= 0 || M > 0x3fffffff || K <= 0 || K > (1 << 22)) return false;
+  if (w_type == LAMMCU_TYPE_Q2_K) {
+    if (K % 256) return false;
+    return (((uintptr_t)w | (uintptr_t)w_stride) & 3) == 0 && ((uintptr_t)x_or_xq & 15) == 0;
+  }
+  if (K % 256) return false;                       // 8 blocks: every lane chunk and segment is 16-B aligned
+  return (((uintptr_t)w | (uintptr_t)w_stride) & 15) == 0 && ((uintptr_t)x_or_xq & 15) == 0;
+}
+
+int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
+                  float *c, int64_t M, int64_t K, cudaStream_t st) {
+  const TypeInfo ti = type_info(w_type);
+  const bool q2k = (w_type == LAMMCU_TYPE_Q2_K);
+  DecodeParams p = {};
+  p.w = (const uint8_t *)w;  p.w_stride = w_stride;
+  p.x = x;  p.xq = (const uint8_t *)xq;  p.xq_out = (uint8_t *)xq_out;
+  p.c = c;  p.M = (int)M;
+  p.kb = (int)(K / ti.blck);
+  p.units = q2k ? 2 * p.kb : p.kb / 4;
+  p.KS = (p.units + 31) / 32;
+  if (p.KS > kDecWarps) {
+    set_error("decode: K=%lld needs more than %d K-segments", (long long)K, kDecWarps);
+    return LAMMCU_ERR_SHAPE;
+  }
+  const int gran = q2k ? 8 : 2;                    // keeps every segment start 16-byte aligned
+  p.seg_units = (((p.units + p.KS - 1) / p.KS) + gran - 1) / gran * gran;
+  if (p.seg_units > 32) p.seg_units = 32;
+  p.KS = (p.units + p.seg_units - 1) / p.seg_units;
+  p.RG = kDecWarps / p.KS;
+  const int seg_bytes = q2k ? (p.seg_units / 2) * 84 : p.seg_units * 4 * ti.size;
+  p.slot_bytes = ((seg_bytes + 15) & ~15) + 16;
+  p.x_bytes = q2k ? (p.units * (128 + 16) + p.kb * 4) : (p.units * 128 + p.kb * 8);
+  p.x_bytes = (p.x_bytes + 127) & ~127;
+  // ring depth: 4 slots when two CTAs still fit per SM (PDL overlap), else what fits
+  p.slots = kDecMaxSlots;
+  while (p.slots > 2 && kDecCtrl + p.x_bytes + kDecWarps * p.slots * p.slot_bytes > kDecSmemMax / 2 - 1024) p.slots--;
+  const int smem = kDecCtrl + p.x_bytes + kDecWarps * p.slots * p.slot_bytes;
+  if (smem > kDecSmemMax) {
+    set_error("decode: K=%lld too large for shared memory", (long long)K);
+    return LAMMCU_ERR_SHAPE;
+  }
+  int grid = sm_count_cached();
+  const int64_t need = (M + p.RG - 1) / p.RG;
+  if (grid > need) grid = (int)need;
+  return x ? launch_decode_x<true>(w_type, p, grid, smem, st) : launch_decode_x<false>(w_type, p, grid, smem, st);
+}
+
+}  // namespace lamm

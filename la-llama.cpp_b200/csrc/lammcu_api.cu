@@ -49,6 +49,7 @@ struct DeviceState {
 static DeviceState g_dev;
 static std::mutex g_mu;
 static int g_gemv_max_n = 8;
+static int g_decode_kernel = 1;     // N == 1: the single-launch kernel of lamm_decode.cu
 constexpr unsigned int kSchedSlots = 4096;
 
 int sm_count_cached() { return g_dev.sms > 0 ? g_dev.sms : 148; }
@@ -196,6 +197,11 @@ int lammcu_set_gemv_max_n(int n) {
   return LAMMCU_OK;
 }
 int lammcu_get_gemv_max_n(void) { return g_gemv_max_n; }
+int lammcu_set_decode_kernel(int enable) {
+  g_decode_kernel = enable ? 1 : 0;
+  return LAMMCU_OK;
+}
+int lammcu_get_decode_kernel(void) { return g_decode_kernel; }
 
 // ---- device operands ----------------------------------------------------------
 static cudaStream_t pick_stream(void *s) { return s ? (cudaStream_t)s : g_dev.stream; }
@@ -216,6 +222,8 @@ int lammcu_mul_mat_q_dev(int w_type, const void *w, int64_t w_stride, const void
   if (!w || !xq || !c) { set_error("mul_mat_q: NULL operand"); return LAMMCU_ERR_ARG; }
   if (!lammcu_type_supported(w_type)) { set_error("mul_mat_q: type %d not supported", w_type); return LAMMCU_ERR_TYPE; }
   cudaStream_t st = pick_stream(stream);
+  if (N == 1 && g_decode_kernel && decode_supported(w_type, w, w_stride, xq, M, K))
+    return launch_decode(w_type, w, w_stride, nullptr, xq, nullptr, c, M, K, st);
   if (N <= g_gemv_max_n) return launch_gemv(w_type, w, w_stride, xq, xq_stride, c, ldc, M, N, K, st);
   return launch_gemm(w_type, w, w_stride, xq, xq_stride, c, ldc, M, N, K, st);
 }
@@ -235,6 +243,10 @@ int lammcu_mul_mat_dev(int w_type, const void *w, int64_t w_stride, const float 
     return LAMMCU_ERR_SHAPE;
   }
   const size_t rs = lammcu_row_size(vt, K);
+  // decode: one launch, the quantized row only leaves the SM when the caller asks for it
+  if (N == 1 && g_decode_kernel && decode_supported(w_type, w, w_stride, x, M, K) &&
+      (!xq_ws || ((uintptr_t)xq_ws & 3) == 0))
+    return launch_decode(w_type, w, w_stride, x, nullptr, xq_ws, c, M, K, pick_stream(stream));
   if (!xq_ws) {
     rc = grow(&g_dev.ws, &g_dev.ws_bytes, rs * (size_t)N, false);
     if (rc) return rc;
@@ -351,8 +363,14 @@ int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N, int64
   if ((rc = grow(&g_dev.cout, &g_dev.cout_bytes, (size_t)N * rows * 4, false))) return rc;
   for (int64_t j = 0; j < N; j++) memcpy((float *)g_dev.hx + j * K, x_host + j * ldx, (size_t)K * 4);
   CU_TRY(cudaMemcpyAsync(g_dev.xin, g_dev.hx, xbytes, cudaMemcpyHostToDevice, g_dev.stream));
+  void *ws = nullptr;
+  if (xq_out_host && w->type != LAMMCU_TYPE_F32) {
+    const size_t qb = lammcu_row_size(type_info(w->type).vec_dot, K) * (size_t)N;
+    if ((rc = grow(&g_dev.ws, &g_dev.ws_bytes, qb, false))) return rc;
+    ws = g_dev.ws;
+  }
   rc = lammcu_mul_mat_dev(w->type, w->dev, w->stride, (const float *)g_dev.xin, K, (float *)g_dev.cout,
-                          rows, rows, N, K, nullptr, g_dev.stream);
+                          rows, rows, N, K, ws, g_dev.stream);
   if (rc) return rc;
   if (xq_out_host && w->type != LAMMCU_TYPE_F32) {
     const size_t qb = lammcu_row_size(type_info(w->type).vec_dot, K) * (size_t)N;

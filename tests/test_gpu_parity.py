@@ -181,3 +181,60 @@ def test_lamm_mul_mat_operator(gpu, oracle, t):
     # second call hits the weight registry (no re-upload) and gives the same bits
     can, again = gpu.lamm_mul_mat_host(t, wv, x, nth=1)
     assert can and np.array_equal(again, got)
+
+
+# ---------------------------------------------------------------- single-launch decode kernel (N == 1)
+DECODE_SHAPES = [(33, 4096), (1, 256), (7, 512), (300, 11008), (64, 5120), (50, 17920), (9, 6656),
+                 (1185, 4096), (2500, 1024), (129, 13824)]
+
+
+@pytest.mark.parametrize("t", QTYPES)
+@pytest.mark.parametrize("m,k", DECODE_SHAPES)
+def test_decode_kernel_fused_quantize(gpu, oracle, t, m, k):
+    """N == 1 through lammcu_mul_mat_dev: ONE launch (fused bit-exact activation quantize), Xq written
+    to the caller's workspace must equal quantize_row_q8_*_reference, C within tolerance; the same
+    operands through the two-launch generic path must agree."""
+    import torch
+    w = weights(oracle, t, m, k, seed=m + 3 * k)
+    rng = np.random.default_rng(m * k)
+    for variant in range(2):
+        x = rng.standard_normal((1, k)).astype(np.float32)
+        if variant == 1:                       # quantizer edge cases: zero blocks, ties, tiny values
+            x[0, : k // 4] = 0.0
+            x[0, k // 4: k // 4 + 64] = 2.5
+            x[0, k // 2: k // 2 + 40] *= 1e-6
+        want, want_xq = oracle.mul_mat(t, w, x, want_xq=True)
+        ws = torch.full((row_size(VEC_DOT[t], k),), 0, dtype=torch.uint8, device="cuda")
+        gpu.lib().lammcu_launch_count_reset()
+        got = gpu.mul_mat(t, dev(w), dev(x), ws=ws).cpu().numpy()
+        assert gpu.lib().lammcu_launch_count() == 1, "decode must be a single launch"
+        assert np.abs(got - want).max() <= tol_c(want, k), f"{TYPE_NAMES[t]} {m}x{k}"
+        want_xq = zero_dead_bsums(want_xq, 1) if VEC_DOT[t] == Q8_K else want_xq
+        assert np.array_equal(ws.cpu().numpy().reshape(1, -1), want_xq), "fused quantize is not bit-exact"
+        # pre-quantized activations through the same kernel
+        got_q = gpu.mul_mat_q(t, dev(w), dev(want_xq), k).cpu().numpy()
+        assert np.array_equal(got_q, got), "fused and pre-quantized decode differ"
+        # generic two-launch path
+        gpu.lib().lammcu_set_decode_kernel(0)
+        try:
+            ref2 = gpu.mul_mat(t, dev(w), dev(x)).cpu().numpy()
+        finally:
+            gpu.lib().lammcu_set_decode_kernel(1)
+        assert np.abs(ref2 - want).max() <= tol_c(want, k)
+
+
+def test_decode_kernel_chain_pdl(gpu, oracle):
+    """Back-to-back dependent decode launches (programmatic dependent launch): y = W2 (W1 x).
+    The second kernel prefetches W2 early but must read W1's output only after it is complete."""
+    import torch
+    t, k = 3, 4096
+    w1 = weights(oracle, t, 4096, k, seed=11)
+    w2 = weights(oracle, t, 512, k, seed=12)
+    x = np.random.default_rng(5).standard_normal((1, k)).astype(np.float32) * 0.05
+    y1 = oracle.mul_mat(t, w1, x)
+    y2 = oracle.mul_mat(t, w2, y1)
+    w1d, w2d, xd = dev(w1), dev(w2), dev(x)
+    for _ in range(20):
+        a = gpu.mul_mat(t, w1d, xd)
+        b = gpu.mul_mat(t, w2d, a)
+        assert np.abs(b.cpu().numpy() - y2).max() <= 2 * tol_c(y2, k)
