@@ -21,6 +21,8 @@
 //     after griddepcontrol.wait.
 #include "lamm_quant_dev.cuh"
 
+#include <cstdlib>
+
 namespace lamm {
 
 constexpr int kDecWarps = 8;
@@ -297,45 +299,128 @@ __device__ __forceinline__ void pdl_launch_dependents() {
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 // ---- the kernel ----------------------------------------------------------------------
+// One weight row-segment (the lane's unit of it) against the lane's activations.
+template <int WT>
+struct LaneX {                       // register-resident activations of one lane
+  uint32_t q[32];
+  float d[4], s[4];                  // Q2_K: d[0] = x.d
+  uint32_t bs[4];                    // Q2_K: 8 x int16 bsums
+};
+
+template <int WT, int NW>
+__device__ __forceinline__ void load_unit(uint32_t (&w)[NW], uint32_t slot_addr, int lane_c) {
+  if constexpr (WT == LAMMCU_TYPE_Q2_K) {
+    // half h of super-block lane_c/2: scales[8h..8h+8), qs[32h..32h+32), (d, dmin)
+    const uint32_t blk = slot_addr + (uint32_t)(lane_c >> 1) * 84u, h = lane_c & 1;
+#pragma unroll
+    for (int k = 0; k < 8; k++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[k]) : "r"(blk + 16u + 32u * h + 4u * k));
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[8]) : "r"(blk + 8u * h));
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[9]) : "r"(blk + 8u * h + 4u));
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[10]) : "r"(blk + 80u));
+  } else {
+    lds_chunk<NW>(w, slot_addr + (uint32_t)lane_c * (4u * NW));
+  }
+}
+
+template <int WT, int NW>
+__device__ __forceinline__ float dot_unit(const uint32_t (&w)[NW], const LaneX<WT> &x) {
+  float acc = 0.f;
+  if constexpr (WT == LAMMCU_TYPE_Q2_K) {
+    const uint32_t sc0 = w[8] & 0x0F0F0F0Fu, sc1 = w[9] & 0x0F0F0F0Fu;
+    const uint32_t mn0 = (w[8] >> 4) & 0x0F0F0F0Fu, mn1 = (w[9] >> 4) & 0x0F0F0F0Fu;
+    int summs = dp2a_lo_s16u8(x.bs[0], mn0, 0);
+    summs = dp2a_hi_s16u8(x.bs[1], mn0, summs);
+    summs = dp2a_lo_s16u8(x.bs[2], mn1, summs);
+    summs = dp2a_hi_s16u8(x.bs[3], mn1, summs);
+    int isum = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {          // bit plane j: elements 32j.. of the unit
+      const uint32_t mask = 0x03030303u << (2 * j);
+#pragma unroll
+      for (int e = 0; e < 2; e++) {        // sub-block 2j + e
+        int t = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) t = dp4a_u8s8(w[4 * e + k] & mask, x.q[8 * j + 4 * e + k], t);
+        const int g = 2 * j + e;
+        const uint32_t scale = ((g < 4 ? sc0 : sc1) >> (8 * (g & 3))) & 0xFFu;
+        isum += (int)scale * (t >> (2 * j));             // t is exactly 4^j x the plane dot
+      }
+    }
+    const float wd = half_bits_to_float(w[10] & 0xffffu), wdmin = half_bits_to_float(w[10] >> 16);
+    acc = fmaf(x.d[0] * wd, (float)isum, acc);
+    acc = fmaf(-(x.d[0] * wdmin), (float)summs, acc);
+  } else {
+    acc = block_dot<WT, 0, NW>(w, x.q, x.d[0], x.s[0], acc);
+    acc = block_dot<WT, 1, NW>(w, x.q, x.d[1], x.s[1], acc);
+    acc = block_dot<WT, 2, NW>(w, x.q, x.d[2], x.s[2], acc);
+    acc = block_dot<WT, 3, NW>(w, x.q, x.d[3], x.s[3], acc);
+  }
+  return acc;
+}
+
+// Sum each of a[0..3] over the 32 lanes with 6 shuffles; lane l (l < 4) returns the total of a[l].
+__device__ __forceinline__ float warp_sum4(float a0, float a1, float a2, float a3, int lane) {
+  const bool hi16 = lane & 16, hi8 = lane & 8;
+  // lanes with bit 4 clear keep (a0, a1), the others (a2, a3)
+  const float s0 = hi16 ? a0 : a2, s1 = hi16 ? a1 : a3;
+  float k0 = (hi16 ? a2 : a0) + __shfl_xor_sync(0xffffffffu, s0, 16);
+  float k1 = (hi16 ? a3 : a1) + __shfl_xor_sync(0xffffffffu, s1, 16);
+  // bit 3 clear keeps k0, set keeps k1
+  const float s = hi8 ? k0 : k1;
+  float v = (hi8 ? k1 : k0) + __shfl_xor_sync(0xffffffffu, s, 8);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  // lanes 0..7 hold a0 total, 8..15 a1, 16..23 a2, 24..31 a3
+  return __shfl_sync(0xffffffffu, v, (lane & 3) * 8);
+}
+
 template <int WT, bool XF32>
 __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodeParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr bool kQ2K = (WT == LAMMCU_TYPE_Q2_K);
   constexpr int VT = type_info(WT).vec_dot;
+  constexpr int NW = kQ2K ? 11 : DecFmt<WT>::NW;
+  constexpr int S = kDecMaxSlots;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint64_t *full = reinterpret_cast<uint64_t *>(smem) + warp * kDecMaxSlots;
-  float *part = reinterpret_cast<float *>(smem + 512);          // [RG][2][KS]
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem) + warp * S;
+  float *part = reinterpret_cast<float *>(smem + 512);          // [RG][2][KS][4]
   uint8_t *xs = smem + kDecCtrl;
-  uint8_t *ring = xs + p.x_bytes + (size_t)warp * p.slots * p.slot_bytes;
+  uint8_t *ring = xs + p.x_bytes + (size_t)warp * S * p.slot_bytes;
 
   const bool active = warp < p.RG * p.KS;
   const int rg = warp / p.KS, seg = warp - rg * p.KS;
   const int u0 = seg * p.seg_units;                              // first unit of the segment
   const int seg_n = max(0, min(p.seg_units, p.units - u0));      // live lanes
-  const int unit_bytes = kQ2K ? 42 : 4 * type_info(WT).size;
+  constexpr int unit_bytes = kQ2K ? 42 : 4 * type_info(WT).size;
   // Q2_K: a unit is half a super-block, segments start on super-block boundaries
   const uint32_t seg_off = kQ2K ? (uint32_t)(u0 >> 1) * 84u : (uint32_t)u0 * unit_bytes;
   const uint32_t seg_bytes = kQ2K ? (uint32_t)((seg_n + 1) >> 1) * 84u : (uint32_t)seg_n * unit_bytes;
   const int row0 = blockIdx.x + gridDim.x * rg, row_step = gridDim.x * p.RG;
+  const int n_rows = (row0 < p.M) ? (p.M - 1 - row0) / row_step + 1 : 0;      // rows of this warp
+  const uint8_t *wseg = p.w + seg_off;
+  const uint32_t ring_addr = smem_u32(ring);
+  const uint32_t full_addr = smem_u32(full);
 
-  auto issue = [&](int i, uint64_t pol) {                        // lane 0: stream row i of this warp
-    const int r = row0 + i * row_step;
-    const uintptr_t a = (uintptr_t)(p.w + (int64_t)r * p.w_stride + seg_off);
+  auto issue = [&](int i, int s, uint64_t pol) {                 // lane 0: stream this warp's i-th row
+    const uintptr_t a = (uintptr_t)(wseg + (int64_t)(row0 + i * row_step) * p.w_stride);
     const uintptr_t a0 = a & ~(uintptr_t)15;
     const uint32_t bytes = (uint32_t)(((a + seg_bytes + 15) & ~(uintptr_t)15) - a0);
-    const int s = i % p.slots;
-    mbar_arrive_expect_tx(&full[s], bytes);
-    bulk_g2s_stream(ring + (size_t)s * p.slot_bytes, reinterpret_cast<const void *>(a0), bytes, &full[s], pol);
+    uint64_t *bar = full + s;
+    mbar_arrive_expect_tx(bar, bytes);
+    bulk_g2s_stream(ring + (size_t)s * p.slot_bytes, reinterpret_cast<const void *>(a0), bytes, bar, pol);
   };
 
   uint64_t pol = 0;
   if (active && lane == 0) {
-    for (int s = 0; s < p.slots; s++) mbar_init(&full[s], 1);
+#pragma unroll
+    for (int s = 0; s < S; s++) mbar_init(&full[s], 1);
     fence_barrier_init();
     pol = policy_evict_first();
     // weights are immutable: start streaming before the previous kernel has finished
-    for (int i = 0; i < p.slots; i++)
-      if (row0 + i * row_step < p.M) issue(i, pol);
+#pragma unroll
+    for (int s = 0; s < S; s++)
+      if (s < n_rows) issue(s, s, pol);
   }
   pdl_launch_dependents();
   pdl_wait();                                                    // activations are valid from here on
@@ -347,99 +432,72 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
   const int U = p.units, ug = u0 + lane;
   const bool lane_live = lane < seg_n;
   const uint4 *xqs = reinterpret_cast<const uint4 *>(xs);
-  uint32_t xq[32];
+  LaneX<WT> X;
 #pragma unroll
   for (int j = 0; j < 8; j++) {
     const uint4 v = lane_live ? xqs[(size_t)j * U + ug] : make_uint4(0u, 0u, 0u, 0u);
-    xq[4 * j] = v.x; xq[4 * j + 1] = v.y; xq[4 * j + 2] = v.z; xq[4 * j + 3] = v.w;
+    X.q[4 * j] = v.x; X.q[4 * j + 1] = v.y; X.q[4 * j + 2] = v.z; X.q[4 * j + 3] = v.w;
   }
-  float xd[4] = {0.f, 0.f, 0.f, 0.f}, xsum[4] = {0.f, 0.f, 0.f, 0.f};
-  uint32_t xb[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+  for (int j = 0; j < 4; j++) { X.d[j] = 0.f; X.s[j] = 0.f; X.bs[j] = 0u; }
   if constexpr (kQ2K) {
     const uint4 *xbs = xqs + (size_t)8 * U;
     const float *xdp = reinterpret_cast<const float *>(xbs + U);
-    const uint4 b = lane_live ? xbs[ug] : make_uint4(0u, 0u, 0u, 0u);
-    xb[0] = b.x; xb[1] = b.y; xb[2] = b.z; xb[3] = b.w;
-    xd[0] = lane_live ? xdp[ug >> 1] : 0.f;
+    if (lane_live) {
+      const uint4 b = xbs[ug];
+      X.bs[0] = b.x; X.bs[1] = b.y; X.bs[2] = b.z; X.bs[3] = b.w;
+      X.d[0] = xdp[ug >> 1];
+    }
   } else {
     const float2 *xds = reinterpret_cast<const float2 *>(xqs + (size_t)8 * U);
+    if (lane_live) {
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
-      const float2 v = lane_live ? xds[4 * ug + j] : make_float2(0.f, 0.f);
-      xd[j] = v.x;
-      xsum[j] = v.y;
+      for (int j = 0; j < 4; j++) {
+        const float2 v = xds[4 * ug + j];
+        X.d[j] = v.x;
+        X.s[j] = v.y;
+      }
     }
   }
 
   const int lane_c = lane_live ? lane : 0;     // dead lanes re-read unit 0 (their activations are 0)
-  for (int i = 0;; i++) {
-    const int r = row0 + i * row_step;
-    if (r >= p.M) break;
-    const int s = i % p.slots;
-    mbar_wait(&full[s], (uint32_t)(i / p.slots) & 1u);
-    const uintptr_t a = (uintptr_t)(p.w + (int64_t)r * p.w_stride + seg_off);
-    const uint32_t base = smem_u32(ring + (size_t)s * p.slot_bytes) + (uint32_t)(a & 15);
-    float acc = 0.f;
-    if constexpr (kQ2K) {
-      const uint32_t blk = base + (uint32_t)(lane_c >> 1) * 84u;
-      const uint32_t h = lane_c & 1;
-      uint32_t q[8], scw[2], dm;
+  // every row of this warp has the same (address & 15): w_stride % 16 == 0 or Q2_K 4-byte rows
+  for (int i0 = 0, ph = 0; i0 < n_rows; i0 += S, ph ^= 1) {
+    const int nb = min(S, n_rows - i0);          // rows in this batch (warp-uniform)
+    float acc[S];
 #pragma unroll
-      for (int k = 0; k < 8; k++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(q[k]) : "r"(blk + 16u + 32u * h + 4u * k));
-      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(scw[0]) : "r"(blk + 8u * h));
-      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(scw[1]) : "r"(blk + 8u * h + 4u));
-      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(dm) : "r"(blk + 80u));
-      const uint32_t sc0 = scw[0] & 0x0F0F0F0Fu, sc1 = scw[1] & 0x0F0F0F0Fu;
-      const uint32_t mn0 = (scw[0] >> 4) & 0x0F0F0F0Fu, mn1 = (scw[1] >> 4) & 0x0F0F0F0Fu;
-      int summs = dp2a_lo_s16u8(xb[0], mn0, 0);
-      summs = dp2a_hi_s16u8(xb[1], mn0, summs);
-      summs = dp2a_lo_s16u8(xb[2], mn1, summs);
-      summs = dp2a_hi_s16u8(xb[3], mn1, summs);
-      int isum = 0;
+    for (int s = 0; s < S; s++) acc[s] = 0.f;
+    uint32_t w[2][NW];
+    const uint32_t a15 = (uint32_t)((uintptr_t)(wseg + (int64_t)row0 * p.w_stride) & 15);
+    mbar_wait(full, (uint32_t)ph);
+    load_unit<WT, NW>(w[0], ring_addr + a15, lane_c);
 #pragma unroll
-      for (int j = 0; j < 4; j++) {          // bit plane j: elements 32j.. of the unit
-        const uint32_t mask = 0x03030303u << (2 * j);
-#pragma unroll
-        for (int e = 0; e < 2; e++) {        // sub-block 2j + e
-          int t = 0;
-#pragma unroll
-          for (int k = 0; k < 4; k++) t = dp4a_u8s8(q[4 * e + k] & mask, xq[8 * j + 4 * e + k], t);
-          const int g = 2 * j + e;
-          const uint32_t scale = ((g < 4 ? sc0 : sc1) >> (8 * (g & 3))) & 0xFFu;
-          isum += (int)scale * (t >> (2 * j));             // t is exactly 4^j x the plane dot
-        }
+    for (int s = 0; s < S; s++) {
+      if (s + 1 < S && s + 1 < nb) {             // next row's weights are in flight while this one is multiplied
+        mbar_wait(full + s + 1, (uint32_t)ph);
+        load_unit<WT, NW>(w[(s + 1) & 1], ring_addr + (uint32_t)(s + 1) * p.slot_bytes + a15, lane_c);
       }
-      const float wd = half_bits_to_float(dm & 0xffffu), wdmin = half_bits_to_float(dm >> 16);
-      acc = fmaf(xd[0] * wd, (float)isum, acc);
-      acc = fmaf(-(xd[0] * wdmin), (float)summs, acc);
-    } else {
-      constexpr int NW = DecFmt<WT>::NW;
-      uint32_t w[NW];
-      lds_chunk<NW>(w, base + (uint32_t)lane_c * (4u * NW));
-      acc = block_dot<WT, 0, NW>(w, xq, xd[0], xsum[0], acc);
-      acc = block_dot<WT, 1, NW>(w, xq, xd[1], xsum[1], acc);
-      acc = block_dot<WT, 2, NW>(w, xq, xd[2], xsum[2], acc);
-      acc = block_dot<WT, 3, NW>(w, xq, xd[3], xsum[3], acc);
+      if (s < nb) {
+        acc[s] = dot_unit<WT, NW>(w[s & 1], X);
+        __syncwarp();                            // all lanes have consumed slot s
+        if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
+      }
     }
-    __syncwarp();
-    if (lane == 0 && row0 + (i + p.slots) * row_step < p.M) {
-      fence_proxy_async();                                   // our reads of the slot precede the refill
-      issue(i + p.slots, pol);
-    }
-    acc = warp_sum(acc);
+    const float tot = warp_sum4(acc[0], acc[1], acc[2], acc[3], lane);
     if (p.KS == 1) {
-      if (lane == 0) p.c[r] = acc;
+      if (lane < nb) p.c[row0 + (i0 + lane) * row_step] = tot;
     } else {
-      float *pb = part + (size_t)(rg * 2 + (i & 1)) * p.KS;
-      if (lane == 0) pb[seg] = acc;
+      float *pb = part + (size_t)((rg * 2 + ph) * p.KS) * 4;
+      if (lane < 4) pb[seg * 4 + lane] = tot;
       asm volatile("bar.sync %0, %1;" ::"r"(1 + rg), "r"(p.KS * 32) : "memory");
-      if (seg == 0 && lane == 0) {
+      if (seg == 0 && lane < nb) {
         float t = 0.f;
-        for (int k = 0; k < p.KS; k++) t += pb[k];
-        p.c[r] = t;
+        for (int k = 0; k < p.KS; k++) t += pb[k * 4 + lane];
+        p.c[row0 + (i0 + lane) * row_step] = t;
       }
     }
   }
+  (void)full_addr;
 }
 
 // ---- host side --------------------------------------------------------------------------
@@ -525,15 +583,17 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   p.slot_bytes = ((seg_bytes + 15) & ~15) + 16;
   p.x_bytes = q2k ? (p.units * (128 + 16) + p.kb * 4) : (p.units * 128 + p.kb * 8);
   p.x_bytes = (p.x_bytes + 127) & ~127;
-  // ring depth: 4 slots when two CTAs still fit per SM (PDL overlap), else what fits
   p.slots = kDecMaxSlots;
-  while (p.slots > 2 && kDecCtrl + p.x_bytes + kDecWarps * p.slots * p.slot_bytes > kDecSmemMax / 2 - 1024) p.slots--;
   const int smem = kDecCtrl + p.x_bytes + kDecWarps * p.slots * p.slot_bytes;
   if (smem > kDecSmemMax) {
     set_error("decode: K=%lld too large for shared memory", (long long)K);
     return LAMMCU_ERR_SHAPE;
   }
-  int grid = sm_count_cached();
+  static const int per_sm = [] {
+    const char *e = getenv("LAMM_DECODE_CTAS_PER_SM");       // tuning knob: 1 (default) or 2
+    return (e && atoi(e) == 2) ? 2 : 1;
+  }();
+  int grid = sm_count_cached() * per_sm;
   const int64_t need = (M + p.RG - 1) / p.RG;
   if (grid > need) grid = (int)need;
   return x ? launch_decode_x<true>(w_type, p, grid, smem, st) : launch_decode_x<false>(w_type, p, grid, smem, st);
