@@ -108,6 +108,10 @@ int lammcu_get_gemv_max_n(void);
  * quantize, programmatic dependent launch); 0 = quantize kernel + generic GEMV */
 int lammcu_set_decode_kernel(int enable);
 int lammcu_get_decode_kernel(void);
+/* Diagnostics: every following decode launch writes 8 x u64 %globaltimer stamps per
+ * CTA (start, weights issued, dependency wait done, activations staged, done) into
+ * consecutive slots of dev_buf (n_u64 entries); NULL switches tracing off.          */
+int lammcu_set_trace(void *dev_buf, int64_t n_u64);
 
 /* ---- host operands (what lamm_mul_mat passes) --------------------------- */
 typedef struct lammcu_weight *lammcu_weight_t;

@@ -129,5 +129,7 @@ void set_error(const char *fmt, ...);
 int sm_count_cached();
 // scratch for the dynamic tile scheduler: returns a zeroed pair of counters
 unsigned int *next_sched_slot();
+// diagnostics: 8 x u64 per CTA of the next decode launch, or NULL (lammcu_set_trace)
+unsigned long long *next_trace_slot(int grid);
 
 }  // namespace lamm

@@ -25,10 +25,11 @@
 
 namespace lamm {
 
-constexpr int kDecWarps = 8;
-constexpr int kDecThreads = kDecWarps * 32;
+constexpr int kDecWarps = 8;            // default consumer warps per CTA
+constexpr int kDecMaxWarps = 10;        // K-segment counts that do not divide 8 use 9 or 10
+constexpr int kDecMaxThreads = kDecMaxWarps * 32;
 constexpr int kDecMaxSlots = 4;
-constexpr int kDecCtrl = 1024;       // mbarriers [8][4] + partial sums
+constexpr int kDecCtrl = 1024;       // mbarriers [10][4] + partial sums
 
 struct DecodeParams {
   const uint8_t *w;   int64_t w_stride;   // bytes
@@ -42,6 +43,7 @@ struct DecodeParams {
   int RG;               // row groups per CTA (= active warps / KS)
   int slots, slot_bytes;
   int x_bytes;          // shared-memory bytes of the staged activations
+  unsigned long long *trace;   // optional: 8 globaltimer stamps per CTA (lammcu_set_trace)
 };
 
 // ---- integer dots -------------------------------------------------------------------
@@ -110,11 +112,21 @@ __device__ __forceinline__ uint32_t spread_bit4(uint32_t nib) {
 // xq[0..3]: elements 0..15, xq[4..7]: elements 16..31; xd = f32(d_x);
 // xs = f32(s_x) for q8_1, or bit-cast integer sum of the quants for q8_0.
 template <int WT, int J, int NW>
+__device__ __forceinline__ float block_dot8(const uint32_t (&w)[NW], const uint32_t (&xq)[8], float xd,
+                                            float xs, float acc);
+
+template <int WT, int J, int NW>
 __device__ __forceinline__ float block_dot(const uint32_t (&w)[NW], const uint32_t (&xall)[32], float xd,
                                            float xs, float acc) {
-  constexpr int O = J * DecFmt<WT>::BS;
   const uint32_t xq[8] = {xall[8 * J],     xall[8 * J + 1], xall[8 * J + 2], xall[8 * J + 3],
                           xall[8 * J + 4], xall[8 * J + 5], xall[8 * J + 6], xall[8 * J + 7]};
+  return block_dot8<WT, J, NW>(w, xq, xd, xs, acc);
+}
+
+template <int WT, int J, int NW>
+__device__ __forceinline__ float block_dot8(const uint32_t (&w)[NW], const uint32_t (&xq)[8], float xd,
+                                            float xs, float acc) {
+  constexpr int O = J * DecFmt<WT>::BS;
   if constexpr (WT == LAMMCU_TYPE_Q4_0 || WT == LAMMCU_TYPE_Q4_1) {
     constexpr int QS = O + (WT == LAMMCU_TYPE_Q4_0 ? 2 : 4);
     int slo = 0, shi = 0;
@@ -190,7 +202,7 @@ __device__ __forceinline__ void stage_x_row(const DecodeParams &p, uint8_t *xs) 
   if constexpr (VT == LAMMCU_TYPE_Q8_K) {
     uint32_t *xbs = xqs + (size_t)32 * U;
     float *xd = reinterpret_cast<float *>(xbs + (size_t)4 * U);
-    for (int sb = tid >> 5; sb < p.kb; sb += kDecWarps) {
+    for (int sb = tid >> 5; sb < p.kb; sb += (int)(blockDim.x >> 5)) {
       uint32_t q_lo, q_hi;
       float d;
       int pair_sum;
@@ -228,8 +240,66 @@ __device__ __forceinline__ void stage_x_row(const DecodeParams &p, uint8_t *xs) 
   } else {
     constexpr int XB = (VT == LAMMCU_TYPE_Q8_0) ? 34 : 36;
     float2 *xds = reinterpret_cast<float2 *>(xqs + (size_t)32 * U);
+    if constexpr (XF32) {
+      // 4 lanes x 8 floats per block, 64 blocks per pass, two passes' loads in flight
+      const int l4 = tid & 3;
+      const int per_pass = (int)(blockDim.x >> 2);
+      for (int b0 = 0; b0 < p.kb; b0 += 2 * per_pass) {
+        float4 va[2], vb[2];
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const int b = b0 + h * per_pass + (tid >> 2);
+          va[h] = vb[h] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (b < p.kb) {
+            const float4 *xp = reinterpret_cast<const float4 *>(p.x + (size_t)b * 32 + l4 * 8);
+            va[h] = xp[0];
+            vb[h] = xp[1];
+          }
+        }
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const int b = b0 + h * per_pass + (tid >> 2);
+          if (b0 + h * per_pass + ((tid & ~31) >> 2) >= p.kb) break;     // warp-uniform: nothing left
+          uint32_t q_lo, q_hi;
+          float d;
+          int sum;
+          quant32_lane8(va[h], vb[h], q_lo, q_hi, d, sum);
+          if (b < p.kb) {
+            const __half hd = __float2half_rn(d);
+            __half hs = hd;
+            float sf;
+            if constexpr (VT == LAMMCU_TYPE_Q8_1) {
+              hs = __float2half_rn(__fmul_rn((float)sum, d));
+              sf = __half2float(hs);
+            } else {
+              sf = __int_as_float(sum);
+            }
+            const int u = b >> 2, j = (b & 3) * 2 + (l4 >> 1);
+            *reinterpret_cast<uint2 *>(xqs + ((size_t)j * U + u) * 4 + (l4 & 1) * 2) = make_uint2(q_lo, q_hi);
+            if (l4 == 0) xds[b] = make_float2(__half2float(hd), sf);
+            if (store) {
+              uint8_t *blk = p.xq_out + (size_t)b * XB;
+              if constexpr (VT == LAMMCU_TYPE_Q8_1) {
+                uint32_t *o = reinterpret_cast<uint32_t *>(blk + 4 + l4 * 8);
+                o[0] = q_lo;
+                o[1] = q_hi;
+                if (l4 == 0) *reinterpret_cast<__half2 *>(blk) = __halves2half2(hd, hs);
+              } else {
+                uint16_t *o = reinterpret_cast<uint16_t *>(blk + 2 + l4 * 8);
+                o[0] = (uint16_t)(q_lo & 0xffff);
+                o[1] = (uint16_t)(q_lo >> 16);
+                o[2] = (uint16_t)(q_hi & 0xffff);
+                o[3] = (uint16_t)(q_hi >> 16);
+                if (l4 == 0) *reinterpret_cast<__half *>(blk) = hd;
+              }
+            }
+          }
+        }
+      }
+      return;
+    }
     const int l8 = tid & 7;
-    for (int b0 = 0; b0 < p.kb; b0 += kDecThreads / 8) {
+    for (int b0 = 0; b0 < p.kb; b0 += (int)(blockDim.x >> 3)) {
       const int b = b0 + (tid >> 3);
       const bool live = b < p.kb;
       uint32_t q = 0;
@@ -297,6 +367,15 @@ __device__ __forceinline__ void pdl_launch_dependents() {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// event 0: %globaltimer (ns); events 1..7: SM cycle counter (cheap; deltas within a CTA only)
+__device__ __forceinline__ void trace_stamp(unsigned long long *trace, int e) {
+  if (trace && threadIdx.x == 0) {
+    unsigned long long t;
+    if (e == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    else asm volatile("mov.u64 %0, %%clock64;" : "=l"(t));
+    trace[(size_t)blockIdx.x * 8 + e] = t;
+  }
+}
 
 // ---- the kernel ----------------------------------------------------------------------
 // One weight row-segment (the lane's unit of it) against the lane's activations.
@@ -375,8 +454,8 @@ __device__ __forceinline__ float warp_sum4(float a0, float a1, float a2, float a
   return __shfl_sync(0xffffffffu, v, (lane & 3) * 8);
 }
 
-template <int WT, bool XF32>
-__global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodeParams p) {
+template <int WT, bool XF32, int MAXT>
+__global__ void __launch_bounds__(MAXT, 2) decode_kernel(const DecodeParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr bool kQ2K = (WT == LAMMCU_TYPE_Q2_K);
   constexpr int VT = type_info(WT).vec_dot;
@@ -411,6 +490,8 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
     bulk_g2s_stream(ring + (size_t)s * p.slot_bytes, reinterpret_cast<const void *>(a0), bytes, bar, pol);
   };
 
+  trace_stamp(p.trace, 0);
+  trace_stamp(p.trace, 1);
   uint64_t pol = 0;
   if (active && lane == 0) {
 #pragma unroll
@@ -424,8 +505,10 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
   }
   pdl_launch_dependents();
   pdl_wait();                                                    // activations are valid from here on
+  trace_stamp(p.trace, 2);
   stage_x_row<VT, XF32>(p, xs);
   __syncthreads();
+  trace_stamp(p.trace, 3);
   if (!active) return;
 
   // ---- the lane's activations, register-resident for the whole kernel ----
@@ -460,6 +543,7 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
     }
   }
 
+  trace_stamp(p.trace, 5);
   const int lane_c = lane_live ? lane : 0;     // dead lanes re-read unit 0 (their activations are 0)
   // every row of this warp has the same (address & 15): w_stride % 16 == 0 or Q2_K 4-byte rows
   for (int i0 = 0, ph = 0; i0 < n_rows; i0 += S, ph ^= 1) {
@@ -467,20 +551,26 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
     float acc[S];
 #pragma unroll
     for (int s = 0; s < S; s++) acc[s] = 0.f;
-    uint32_t w[2][NW];
     const uint32_t a15 = (uint32_t)((uintptr_t)(wseg + (int64_t)row0 * p.w_stride) & 15);
-    mbar_wait(full, (uint32_t)ph);
-    load_unit<WT, NW>(w[0], ring_addr + a15, lane_c);
 #pragma unroll
-    for (int s = 0; s < S; s++) {
-      if (s + 1 < S && s + 1 < nb) {             // next row's weights are in flight while this one is multiplied
-        mbar_wait(full + s + 1, (uint32_t)ph);
-        load_unit<WT, NW>(w[(s + 1) & 1], ring_addr + (uint32_t)(s + 1) * p.slot_bytes + a15, lane_c);
-      }
-      if (s < nb) {
-        acc[s] = dot_unit<WT, NW>(w[s & 1], X);
-        __syncwarp();                            // all lanes have consumed slot s
-        if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
+    for (int pr = 0; pr < S; pr += 2) {          // two rows at a time: 2x the independent dp4a chains
+      if (pr < nb) {
+        const bool two = pr + 1 < nb;
+        uint32_t w0[NW], w1[NW];
+        mbar_wait(full + pr, (uint32_t)ph);
+        if (two) mbar_wait(full + pr + 1, (uint32_t)ph);
+        load_unit<WT, NW>(w0, ring_addr + (uint32_t)pr * p.slot_bytes + a15, lane_c);
+        load_unit<WT, NW>(w1, ring_addr + (uint32_t)(two ? pr + 1 : pr) * p.slot_bytes + a15, lane_c);
+        const float d0 = dot_unit<WT, NW>(w0, X);
+        const float d1 = dot_unit<WT, NW>(w1, X);
+        acc[pr] = d0;
+        acc[pr + 1] = two ? d1 : 0.f;
+        __syncwarp();                            // all lanes have consumed both slots
+        if (i0 == 0) trace_stamp(p.trace, 6 + pr / 2);
+        if (lane == 0) {
+          if (i0 + S + pr < n_rows) issue(i0 + S + pr, pr, pol);
+          if (i0 + S + pr + 1 < n_rows) issue(i0 + S + pr + 1, pr + 1, pol);
+        }
       }
     }
     const float tot = warp_sum4(acc[0], acc[1], acc[2], acc[3], lane);
@@ -498,16 +588,202 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
     }
   }
   (void)full_addr;
+  trace_stamp(p.trace, 4);
+}
+
+// ---- the 16-warp variant ---------------------------------------------------------------
+// Same streaming structure, tuned for the latency of SHORT kernels (a 4096x4096 Q4_1 matrix is
+// 71 KB per SM: the whole mul_mat is one DRAM round trip plus a serial phase after the
+// activations arrive).  16 warps at <= 64 registers so that two CTAs -- this mul_mat and the
+// next one of the chain, already prefetching -- are resident per SM, 4 warps per scheduler
+// during the serial phase.  The lane keeps only the activation SCALES in registers and re-reads
+// the activation quants from shared memory (conflict-free uint4 slots) for every row.
+constexpr int kD16Warps = 16;
+constexpr int kD16Slots = 2;
+
+// lanes 0..15 return the total of a0, lanes 16..31 of a1 ... then lane l < 2 gets a_l
+__device__ __forceinline__ float warp_sum2(float a0, float a1, int lane) {
+  const bool hi16 = lane & 16;
+  float v = (hi16 ? a1 : a0) + __shfl_xor_sync(0xffffffffu, hi16 ? a0 : a1, 16);
+  v += __shfl_xor_sync(0xffffffffu, v, 8);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  return __shfl_sync(0xffffffffu, v, (lane & 1) * 16);
+}
+
+__device__ __forceinline__ void lds128(uint32_t (&v)[4], uint32_t addr) {
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(addr));
+}
+
+// xaddr: shared address of uint4 slot 0 of the lane's unit; jstride: bytes between slots j
+template <int WT, int NW>
+__device__ __forceinline__ float dot_unit_sx(const uint32_t (&w)[NW], uint32_t xaddr, uint32_t jstride,
+                                             const float (&xd)[4], const float (&xs)[4], const uint32_t (&xbs)[4]) {
+  float acc = 0.f;
+  if constexpr (WT == LAMMCU_TYPE_Q2_K) {
+    const uint32_t sc0 = w[8] & 0x0F0F0F0Fu, sc1 = w[9] & 0x0F0F0F0Fu;
+    const uint32_t mn0 = (w[8] >> 4) & 0x0F0F0F0Fu, mn1 = (w[9] >> 4) & 0x0F0F0F0Fu;
+    int summs = dp2a_lo_s16u8(xbs[0], mn0, 0);
+    summs = dp2a_hi_s16u8(xbs[1], mn0, summs);
+    summs = dp2a_lo_s16u8(xbs[2], mn1, summs);
+    summs = dp2a_hi_s16u8(xbs[3], mn1, summs);
+    int isum = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const uint32_t mask = 0x03030303u << (2 * j);
+#pragma unroll
+      for (int e = 0; e < 2; e++) {
+        uint32_t x[4];
+        lds128(x, xaddr + (uint32_t)(2 * j + e) * jstride);
+        int t = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) t = dp4a_u8s8(w[4 * e + k] & mask, x[k], t);
+        const int g = 2 * j + e;
+        const uint32_t scale = ((g < 4 ? sc0 : sc1) >> (8 * (g & 3))) & 0xFFu;
+        isum += (int)scale * (t >> (2 * j));
+      }
+    }
+    const float wd = half_bits_to_float(w[10] & 0xffffu), wdmin = half_bits_to_float(w[10] >> 16);
+    acc = fmaf(xd[0] * wd, (float)isum, acc);
+    acc = fmaf(-(xd[0] * wdmin), (float)summs, acc);
+  } else {
+    uint32_t a[4], b[4];
+#define LAMM_D16_BLOCK(J)                                                                   \
+    lds128(a, xaddr + (uint32_t)(2 * J) * jstride);                                         \
+    lds128(b, xaddr + (uint32_t)(2 * J + 1) * jstride);                                     \
+    {                                                                                       \
+      const uint32_t xq[8] = {a[0], a[1], a[2], a[3], b[0], b[1], b[2], b[3]};              \
+      acc = block_dot8<WT, J, NW>(w, xq, xd[J], xs[J], acc);                                \
+    }
+    LAMM_D16_BLOCK(0)
+    LAMM_D16_BLOCK(1)
+    LAMM_D16_BLOCK(2)
+    LAMM_D16_BLOCK(3)
+#undef LAMM_D16_BLOCK
+  }
+  return acc;
+}
+
+template <int WT, bool XF32>
+__global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const DecodeParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  constexpr bool kQ2K = (WT == LAMMCU_TYPE_Q2_K);
+  constexpr int VT = type_info(WT).vec_dot;
+  constexpr int NW = kQ2K ? 11 : DecFmt<WT>::NW;
+  constexpr int S = kD16Slots;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem) + warp * S;
+  float *part = reinterpret_cast<float *>(smem + 512);          // [RG][2][KS][2]
+  uint8_t *xs = smem + kDecCtrl;
+  uint8_t *ring = xs + p.x_bytes + (size_t)warp * S * p.slot_bytes;
+
+  const bool active = warp < p.RG * p.KS;
+  const int rg = warp / p.KS, seg = warp - rg * p.KS;
+  const int u0 = seg * p.seg_units;
+  const int seg_n = max(0, min(p.seg_units, p.units - u0));
+  constexpr int unit_bytes = kQ2K ? 42 : 4 * type_info(WT).size;
+  const uint32_t seg_off = kQ2K ? (uint32_t)(u0 >> 1) * 84u : (uint32_t)u0 * unit_bytes;
+  const uint32_t seg_bytes = kQ2K ? (uint32_t)((seg_n + 1) >> 1) * 84u : (uint32_t)seg_n * unit_bytes;
+  const int row0 = blockIdx.x + gridDim.x * rg, row_step = gridDim.x * p.RG;
+  const int n_rows = (row0 < p.M) ? (p.M - 1 - row0) / row_step + 1 : 0;
+  const uint8_t *wseg = p.w + seg_off;
+  const uint32_t ring_addr = smem_u32(ring);
+
+  auto issue = [&](int i, int s, uint64_t pol) {
+    const uintptr_t a = (uintptr_t)(wseg + (int64_t)(row0 + i * row_step) * p.w_stride);
+    const uintptr_t a0 = a & ~(uintptr_t)15;
+    const uint32_t bytes = (uint32_t)(((a + seg_bytes + 15) & ~(uintptr_t)15) - a0);
+    uint64_t *bar = full + s;
+    mbar_arrive_expect_tx(bar, bytes);
+    bulk_g2s_stream(ring + (size_t)s * p.slot_bytes, reinterpret_cast<const void *>(a0), bytes, bar, pol);
+  };
+
+  trace_stamp(p.trace, 0);
+  trace_stamp(p.trace, 1);
+  uint64_t pol = 0;
+  if (active && lane == 0) {
+#pragma unroll
+    for (int s = 0; s < S; s++) mbar_init(&full[s], 1);
+    fence_barrier_init();
+    pol = policy_evict_first();
+#pragma unroll
+    for (int s = 0; s < S; s++)
+      if (s < n_rows) issue(s, s, pol);
+  }
+  pdl_launch_dependents();
+  pdl_wait();
+  trace_stamp(p.trace, 2);
+  stage_x_row<VT, XF32>(p, xs);
+  __syncthreads();
+  trace_stamp(p.trace, 3);
+  if (!active) return;
+
+  const int U = p.units, ug = u0 + lane;
+  const bool lane_live = lane < seg_n;
+  const int lane_c = lane_live ? lane : 0;
+  const uint4 *xqs = reinterpret_cast<const uint4 *>(xs);
+  // dead lanes read unit u0's quants against zero scales (Q2_K: zero d and bsums)
+  const uint32_t xaddr = smem_u32(xqs + (lane_live ? ug : u0));
+  const uint32_t jstride = (uint32_t)U * 16u;
+  float xd[4] = {0.f, 0.f, 0.f, 0.f}, xsc[4] = {0.f, 0.f, 0.f, 0.f};
+  uint32_t xbs[4] = {0u, 0u, 0u, 0u};
+  if (lane_live) {
+    if constexpr (kQ2K) {
+      const uint4 *xb = xqs + (size_t)8 * U;
+      const float *xdp = reinterpret_cast<const float *>(xb + U);
+      const uint4 b = xb[ug];
+      xbs[0] = b.x; xbs[1] = b.y; xbs[2] = b.z; xbs[3] = b.w;
+      xd[0] = xdp[ug >> 1];
+    } else {
+      const float4 *xds = reinterpret_cast<const float4 *>(xqs + (size_t)8 * U);   // float2 [kb]
+      const float4 v0 = xds[2 * ug], v1 = xds[2 * ug + 1];
+      xd[0] = v0.x; xsc[0] = v0.y; xd[1] = v0.z; xsc[1] = v0.w;
+      xd[2] = v1.x; xsc[2] = v1.y; xd[3] = v1.z; xsc[3] = v1.w;
+    }
+  }
+  const uint32_t a15 = (uint32_t)((uintptr_t)(wseg + (int64_t)row0 * p.w_stride) & 15);
+  for (int i0 = 0, ph = 0; i0 < n_rows; i0 += S, ph ^= 1) {
+    const int nb = min(S, n_rows - i0);
+    float acc[S] = {0.f, 0.f};
+#pragma unroll
+    for (int s = 0; s < S; s++) {
+      if (s < nb) {
+        uint32_t w[NW];
+        mbar_wait(full + s, (uint32_t)ph);
+        if (i0 == 0 && s == 0) trace_stamp(p.trace, 5);
+        load_unit<WT, NW>(w, ring_addr + (uint32_t)s * p.slot_bytes + a15, lane_c);
+        acc[s] = dot_unit_sx<WT, NW>(w, xaddr, jstride, xd, xsc, xbs);
+        __syncwarp();
+        if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
+        if (i0 == 0) trace_stamp(p.trace, 6 + s);
+      }
+    }
+    const float tot = warp_sum2(acc[0], acc[1], lane);
+    if (p.KS == 1) {
+      if (lane < nb) p.c[row0 + (i0 + lane) * row_step] = tot;
+    } else {
+      float *pb = part + (size_t)((rg * 2 + ph) * p.KS) * 2;
+      if (lane < 2) pb[seg * 2 + lane] = tot;
+      asm volatile("bar.sync %0, %1;" ::"r"(1 + rg), "r"(p.KS * 32) : "memory");
+      if (seg == 0 && lane < nb) {
+        float t = 0.f;
+        for (int k = 0; k < p.KS; k++) t += pb[k * 2 + lane];
+        p.c[row0 + (i0 + lane) * row_step] = t;
+      }
+    }
+  }
+  trace_stamp(p.trace, 4);
 }
 
 // ---- host side --------------------------------------------------------------------------
 constexpr int kDecSmemMax = 227 * 1024;
 
-template <int WT, bool XF32>
-static int launch_decode_t(const DecodeParams &p, int grid, int smem, cudaStream_t st) {
+template <int WT, bool XF32, int MAXT>
+static int launch_decode_tt(const DecodeParams &p, int grid, int threads, int smem, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(decode_kernel<WT, XF32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(decode_kernel<WT, XF32, MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          kDecSmemMax);
     if (e != cudaSuccess) {
       set_error("decode: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -517,7 +793,7 @@ static int launch_decode_t(const DecodeParams &p, int grid, int smem, cudaStream
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kDecThreads);
+  cfg.blockDim = dim3(threads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -525,7 +801,7 @@ static int launch_decode_t(const DecodeParams &p, int grid, int smem, cudaStream
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, decode_kernel<WT, XF32>, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, decode_kernel<WT, XF32, MAXT>, p);
   g_launch_count++;
   if (e != cudaSuccess) {
     set_error("decode launch (type %d, smem %d): %s", WT, smem, cudaGetErrorString(e));
@@ -534,15 +810,65 @@ static int launch_decode_t(const DecodeParams &p, int grid, int smem, cudaStream
   return LAMMCU_OK;
 }
 
+template <int WT, bool XF32>
+static int launch_decode_t(const DecodeParams &p, int grid, int threads, int smem, cudaStream_t st) {
+  // 8 warps: 128 registers per thread; 9-10 warps (K-segment counts 3, 5): 102
+  if (threads <= kDecWarps * 32) return launch_decode_tt<WT, XF32, kDecWarps * 32>(p, grid, threads, smem, st);
+  return launch_decode_tt<WT, XF32, kDecMaxThreads>(p, grid, threads, smem, st);
+}
+
+template <int WT, bool XF32>
+static int launch_decode16_t(const DecodeParams &p, int grid, int threads, int smem, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(decode16_kernel<WT, XF32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kDecSmemMax);
+    if (e != cudaSuccess) {
+      set_error("decode16: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      return LAMMCU_ERR_CUDA;
+    }
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(threads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, decode16_kernel<WT, XF32>, p);
+  g_launch_count++;
+  if (e != cudaSuccess) {
+    set_error("decode16 launch (type %d, smem %d): %s", WT, smem, cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
 template <bool XF32>
-static int launch_decode_x(int w_type, const DecodeParams &p, int grid, int smem, cudaStream_t st) {
+static int launch_decode16_x(int w_type, const DecodeParams &p, int grid, int threads, int smem, cudaStream_t st) {
   switch (w_type) {
-  case LAMMCU_TYPE_Q4_0: return launch_decode_t<LAMMCU_TYPE_Q4_0, XF32>(p, grid, smem, st);
-  case LAMMCU_TYPE_Q4_1: return launch_decode_t<LAMMCU_TYPE_Q4_1, XF32>(p, grid, smem, st);
-  case LAMMCU_TYPE_Q5_0: return launch_decode_t<LAMMCU_TYPE_Q5_0, XF32>(p, grid, smem, st);
-  case LAMMCU_TYPE_Q5_1: return launch_decode_t<LAMMCU_TYPE_Q5_1, XF32>(p, grid, smem, st);
-  case LAMMCU_TYPE_Q8_0: return launch_decode_t<LAMMCU_TYPE_Q8_0, XF32>(p, grid, smem, st);
-  default:               return launch_decode_t<LAMMCU_TYPE_Q2_K, XF32>(p, grid, smem, st);
+  case LAMMCU_TYPE_Q4_0: return launch_decode16_t<LAMMCU_TYPE_Q4_0, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q4_1: return launch_decode16_t<LAMMCU_TYPE_Q4_1, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q5_0: return launch_decode16_t<LAMMCU_TYPE_Q5_0, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q5_1: return launch_decode16_t<LAMMCU_TYPE_Q5_1, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q8_0: return launch_decode16_t<LAMMCU_TYPE_Q8_0, XF32>(p, grid, threads, smem, st);
+  default:               return launch_decode16_t<LAMMCU_TYPE_Q2_K, XF32>(p, grid, threads, smem, st);
+  }
+}
+
+template <bool XF32>
+static int launch_decode_x(int w_type, const DecodeParams &p, int grid, int threads, int smem, cudaStream_t st) {
+  switch (w_type) {
+  case LAMMCU_TYPE_Q4_0: return launch_decode_t<LAMMCU_TYPE_Q4_0, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q4_1: return launch_decode_t<LAMMCU_TYPE_Q4_1, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q5_0: return launch_decode_t<LAMMCU_TYPE_Q5_0, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q5_1: return launch_decode_t<LAMMCU_TYPE_Q5_1, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q8_0: return launch_decode_t<LAMMCU_TYPE_Q8_0, XF32>(p, grid, threads, smem, st);
+  default:               return launch_decode_t<LAMMCU_TYPE_Q2_K, XF32>(p, grid, threads, smem, st);
   }
 }
 
@@ -570,21 +896,32 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   p.kb = (int)(K / ti.blck);
   p.units = q2k ? 2 * p.kb : p.kb / 4;
   p.KS = (p.units + 31) / 32;
-  if (p.KS > kDecWarps) {
-    set_error("decode: K=%lld needs more than %d K-segments", (long long)K, kDecWarps);
+  if (p.KS > kDecMaxWarps) {
+    set_error("decode: K=%lld needs more than %d K-segments", (long long)K, kDecMaxWarps);
     return LAMMCU_ERR_SHAPE;
   }
   const int gran = q2k ? 8 : 2;                    // keeps every segment start 16-byte aligned
   p.seg_units = (((p.units + p.KS - 1) / p.KS) + gran - 1) / gran * gran;
   if (p.seg_units > 32) p.seg_units = 32;
   p.KS = (p.units + p.seg_units - 1) / p.seg_units;
-  p.RG = kDecWarps / p.KS;
+  static const int variant = [] {
+    const char *e = getenv("LAMM_DECODE_VARIANT");          // tuning knob: 8 or 16 (default) warps
+    return (e && atoi(e) == 8) ? 8 : 16;
+  }();
+  int warps;
+  if (variant == 16) {
+    warps = (kD16Warps / p.KS) * p.KS;
+  } else {
+    warps = kDecWarps;                             // the most warps <= 10 that K-segments tile exactly
+    if (kDecWarps % p.KS) warps = (kDecMaxWarps / p.KS) * p.KS;
+  }
+  p.RG = warps / p.KS;
   const int seg_bytes = q2k ? (p.seg_units / 2) * 84 : p.seg_units * 4 * ti.size;
   p.slot_bytes = ((seg_bytes + 15) & ~15) + 16;
   p.x_bytes = q2k ? (p.units * (128 + 16) + p.kb * 4) : (p.units * 128 + p.kb * 8);
   p.x_bytes = (p.x_bytes + 127) & ~127;
-  p.slots = kDecMaxSlots;
-  const int smem = kDecCtrl + p.x_bytes + kDecWarps * p.slots * p.slot_bytes;
+  p.slots = (variant == 16) ? kD16Slots : kDecMaxSlots;
+  const int smem = kDecCtrl + p.x_bytes + warps * p.slots * p.slot_bytes;
   if (smem > kDecSmemMax) {
     set_error("decode: K=%lld too large for shared memory", (long long)K);
     return LAMMCU_ERR_SHAPE;
@@ -596,7 +933,12 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   int grid = sm_count_cached() * per_sm;
   const int64_t need = (M + p.RG - 1) / p.RG;
   if (grid > need) grid = (int)need;
-  return x ? launch_decode_x<true>(w_type, p, grid, smem, st) : launch_decode_x<false>(w_type, p, grid, smem, st);
+  p.trace = next_trace_slot(grid);
+  if (variant == 16)
+    return x ? launch_decode16_x<true>(w_type, p, grid, warps * 32, smem, st)
+             : launch_decode16_x<false>(w_type, p, grid, warps * 32, smem, st);
+  return x ? launch_decode_x<true>(w_type, p, grid, warps * 32, smem, st)
+           : launch_decode_x<false>(w_type, p, grid, warps * 32, smem, st);
 }
 
 }  // namespace lamm

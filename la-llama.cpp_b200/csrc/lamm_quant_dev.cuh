@@ -93,4 +93,40 @@ __device__ __forceinline__ void quant256_lane8(const float (&v)[8], int lane, ui
   pair_sum = sum;
 }
 
+// pack 4 ints in [-128, 127] into little-endian int8 x 4 (2 instructions)
+__device__ __forceinline__ uint32_t pack_s8x4(int q0, int q1, int q2, int q3) {
+  uint32_t hi, r;
+  asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(q3), "r"(q2), "r"(0));
+  asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(q1), "r"(q0), "r"(hi));
+  return r;
+}
+
+// roundf (half away from zero) for |t| <= 256, as an int: trunc(t + copysign(0.5 - 2^-25, t)).
+// Exhaustively checked against C roundf for every float in [-256, 256] ("quantizers").
+__device__ __forceinline__ int round_half_away_small(float t) {
+  return __float2int_rz(__fadd_rn(t, copysignf(0.49999997f, t)));
+}
+
+// 4 lanes x 8 elements = one 32-block (lane l4 owns elements [8*l4, 8*l4 + 8)).  Same arithmetic
+// as quant32_lane4; returns the lane's quants as two packed words, d and the block's quant sum.
+__device__ __forceinline__ void quant32_lane8(const float4 a, const float4 b, uint32_t &q_lo, uint32_t &q_hi,
+                                              float &d_out, int &sum_out) {
+  float amax = fmaxf(fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fmaxf(fabsf(a.z), fabsf(a.w))),
+                     fmaxf(fmaxf(fabsf(b.x), fabsf(b.y)), fmaxf(fabsf(b.z), fabsf(b.w))));
+  amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+  amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+  const float d = __fdiv_rn(amax, 127.0f);
+  const float id = (d != 0.0f) ? __fdiv_rn(1.0f, d) : 0.0f;
+  q_lo = pack_s8x4(round_half_away_small(__fmul_rn(a.x, id)), round_half_away_small(__fmul_rn(a.y, id)),
+                   round_half_away_small(__fmul_rn(a.z, id)), round_half_away_small(__fmul_rn(a.w, id)));
+  q_hi = pack_s8x4(round_half_away_small(__fmul_rn(b.x, id)), round_half_away_small(__fmul_rn(b.y, id)),
+                   round_half_away_small(__fmul_rn(b.z, id)), round_half_away_small(__fmul_rn(b.w, id)));
+  int s = __dp4a((int)q_lo, 0x01010101, 0);
+  s = __dp4a((int)q_hi, 0x01010101, s);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  d_out = d;
+  sum_out = s;
+}
+
 }  // namespace lamm

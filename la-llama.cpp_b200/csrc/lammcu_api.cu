@@ -54,6 +54,15 @@ constexpr unsigned int kSchedSlots = 4096;
 
 int sm_count_cached() { return g_dev.sms > 0 ? g_dev.sms : 148; }
 
+static unsigned long long *g_trace = nullptr;
+static long long g_trace_cap = 0, g_trace_used = 0;
+unsigned long long *next_trace_slot(int grid) {
+  if (!g_trace || g_trace_used + (long long)grid * 8 > g_trace_cap) return nullptr;
+  unsigned long long *p = g_trace + g_trace_used;
+  g_trace_used += (long long)grid * 8;
+  return p;
+}
+
 unsigned int *next_sched_slot() {
   if (!g_dev.sched) {
     set_error("lammcu not initialised (call lammcu_init)");
@@ -202,6 +211,12 @@ int lammcu_set_decode_kernel(int enable) {
   return LAMMCU_OK;
 }
 int lammcu_get_decode_kernel(void) { return g_decode_kernel; }
+int lammcu_set_trace(void *dev_buf, int64_t n_u64) {
+  g_trace = (unsigned long long *)dev_buf;
+  g_trace_cap = dev_buf ? n_u64 : 0;
+  g_trace_used = 0;
+  return LAMMCU_OK;
+}
 
 // ---- device operands ----------------------------------------------------------
 static cudaStream_t pick_stream(void *s) { return s ? (cudaStream_t)s : g_dev.stream; }
