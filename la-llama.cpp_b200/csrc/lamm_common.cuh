@@ -125,6 +125,9 @@ int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int
 bool decode_supported(int w_type, const void *w, int64_t w_stride, const void *x_or_xq, int64_t M, int64_t K);
 int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
                   float *c, int64_t M, int64_t K, cudaStream_t st);
+int launch_gemm_prep(int vt, int perm, const void *xq, int64_t xq_stride, void *x16, float *dxT, float *sxT,
+                     int64_t N, int64_t Npad, int64_t K, cudaStream_t st);
+void *gemm_workspace(size_t bytes);      // library-owned scratch for the prefill GEMM (grown on demand)
 void set_error(const char *fmt, ...);
 int sm_count_cached();
 // scratch for the dynamic tile scheduler: returns a zeroed pair of counters

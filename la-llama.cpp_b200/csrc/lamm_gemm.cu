@@ -1,12 +1,556 @@
-// lamm_gemm.cu -- prefill path (N > gemv_max_n).  PLACEHOLDER for this commit:
-// routes to the column-grouped GEMV (correct, re-reads W once per 8 columns).
-// The tcgen05 int8 kernel replaces this file's body.
+// lamm_gemm.cu -- prefill path (N > gemv_max_n): the one dense contraction of the hot path,
+// on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM).
+//
+// Replaces LAMMImpl<T>::matmul_simd_block + lamm_simd_block_kernel<4,4>
+// (src/lamm_impl.hpp:90-147, src/lamm_kernel_*.hpp) for many activation rows.
+//
+// C[n, m] = sum_kb d_w[m,kb] * d_x[n,kb] * sumi[m,n,kb]  (+ m_w[m,kb] * s_x[n,kb])
+// The scale changes every 32-element block on BOTH operands, so the integer block sum has to
+// leave the tensor core once per block.  Design:
+//   * kind::f16 MMA on exact small integers: the unpacked weight quants and the int8
+//     activation quants are exactly representable in fp16, the block sums are exact in the
+//     f32 accumulator (|sumi| < 2^24) -- bit-identical to the reference's int32 sumi -- and
+//     arrive in registers as floats: the drain is one packed FMUL2 + one packed FFMA2 per TWO
+//     accumulator elements instead of I2F + FMUL + FFMA per element for an s32 accumulator.
+//   * one CTA = 128 weight rows x 128 activation rows, 16 warps:
+//       warp 0      TMA producer: raw packed weight blocks (2-D box over bytes), the fp16
+//                   activation tile (SWIZZLE_128B), the per-block activation scales
+//       warp 1      MMA issuer (one thread): per 32-block 2 x tcgen05.mma M128 N128 K16 into a
+//                   ring of 3 TMEM stages, tcgen05.commit -> mbarrier
+//       warp 2      TMEM allocation
+//       warps 4-7   weight unpack (thread = row): nibbles / 5th bits -> fp16 with the
+//                   0x6400-magic trick, written in the UMMA K-major SWIZZLE_128B layout
+//       warps 8-15  drain (thread = TMEM lane = weight row, 64 columns each): tcgen05.ld,
+//                   acc += (d_w * d_x[n]) * S  with f32x2 math, accumulators in registers
+//   * the epilogue stores C[n*ldc + m] straight from registers (consecutive lanes =
+//     consecutive m: coalesced).
 #include "lamm_common.cuh"
+
+#include <cuda.h>
 
 namespace lamm {
 
-int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride,
-                float *c, int64_t ldc, int64_t M, int64_t N, int64_t K, cudaStream_t st) {
+constexpr int GM = 128, GN = 128, GK = 64;     // CTA tile; K elements per pipeline stage
+constexpr int kGStages = 4;                    // A16 / B16 ring
+constexpr int kSStages = 3;                    // TMEM accumulator ring (128 columns each)
+constexpr int kRawStages = 2;                  // raw packed-weight ring (256 K elements each)
+constexpr int kScaleRing = 16;                 // K-blocks of d_w / d_x kept in shared memory
+constexpr int kGemmThreads = 512;
+
+struct GemmParams {
+  const float *dxT, *sxT;     // [Kb][Npad]
+  float *c;
+  int64_t ldc;
+  int M, N, Npad, K;
+};
+
+// ---- tcgen05 / TMA PTX ------------------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t *smem_dst, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, one thread issues for the CTA
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// the mbarrier gets one arrival when all previously issued MMAs of this thread have completed
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+// 32 lanes x 32 consecutive columns (thread i <- lane base + i)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *map, int x, int y, uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y)
+      : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap *map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+
+// K-major SWIZZLE_128B operand tile: 8-row groups 1024 B apart, rows 128 B
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);        // start address
+  d |= (uint64_t)1 << 16;                              // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;                    // stride byte offset
+  d |= (uint64_t)1 << 46;                              // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;                              // SWIZZLE_128B
+  return d;
+}
+// kind::f16, A/B = F16 K-major, D = F32, M = 128, N = 128
+constexpr uint32_t kIdescF16 = (1u << 4) | ((uint32_t)(GN >> 3) << 17) | ((uint32_t)(GM >> 4) << 24);
+
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  uint64_t ra, rb, rc, rd;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+  float2 d;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+  return d;
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+  uint64_t ra, rb, rd;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+  float2 d;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+  return d;
+}
+
+// two fp16 holding the small integers in the low bits of each half of p: (1024 + v) - bias
+__device__ __forceinline__ uint32_t magic_pair(uint32_t p, uint32_t bias_h2) {
+  const uint32_t m = p | 0x64006400u;
+  const __half2 r = __hsub2(*reinterpret_cast<const __half2 *>(&m), *reinterpret_cast<const __half2 *>(&bias_h2));
+  return *reinterpret_cast<const uint32_t *>(&r);
+}
+
+// ---- weight unpack: one 32-block of the thread's row -> 4 x 16 B chunks of fp16 ------------
+template <int OFF, int NWR>
+__device__ __forceinline__ uint32_t raw_word(const uint32_t (&w)[NWR]) {
+  if constexpr (OFF % 4 == 0) return w[OFF / 4];
+  else return __byte_perm(w[OFF / 4], w[OFF / 4 + 1], 0x5432);
+}
+template <int OFF, int NWR>
+__device__ __forceinline__ float raw_half(const uint32_t (&w)[NWR]) {
+  if constexpr (OFF % 4 == 0) return half_bits_to_float(w[OFF / 4] & 0xffffu);
+  else return half_bits_to_float(w[OFF / 4] >> 16);
+}
+
+// JB: block index inside the thread's 8-block raw chunk.  out[w] = chunk w (8 fp16) in the
+// element order documented in lamm_gemm_prep.cu; d / m = f32 of the block's scale / min.
+template <int WT, int JB, int NWR>
+__device__ __forceinline__ void unpack_block(const uint32_t (&raw)[NWR], uint4 (&out)[4], float &d, float &m) {
+  constexpr int BS = type_info(WT).size;
+  constexpr int O = JB * BS;
+  d = raw_half<O, NWR>(raw);
+  m = 0.f;
+  if constexpr (WT == LAMMCU_TYPE_Q4_0 || WT == LAMMCU_TYPE_Q4_1) {
+    constexpr int QS = O + (WT == LAMMCU_TYPE_Q4_0 ? 2 : 4);
+    constexpr uint32_t bias = (WT == LAMMCU_TYPE_Q4_0) ? 0x64086408u : 0x64006400u;     // (q - 8) or q
+    if constexpr (WT == LAMMCU_TYPE_Q4_1) m = raw_half<O + 2, NWR>(raw);
+    const uint32_t q[4] = {raw_word<QS, NWR>(raw), raw_word<QS + 4, NWR>(raw), raw_word<QS + 8, NWR>(raw),
+                           raw_word<QS + 12, NWR>(raw)};
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+      out[w].x = magic_pair(q[w] & 0x000F000Fu, bias);
+      out[w].y = magic_pair((q[w] >> 4) & 0x000F000Fu, bias);
+      out[w].z = magic_pair((q[w] >> 8) & 0x000F000Fu, bias);
+      out[w].w = magic_pair((q[w] >> 12) & 0x000F000Fu, bias);
+    }
+  } else if constexpr (WT == LAMMCU_TYPE_Q5_0 || WT == LAMMCU_TYPE_Q5_1) {
+    constexpr int QH = O + (WT == LAMMCU_TYPE_Q5_0 ? 2 : 4);
+    constexpr int QS = QH + 4;
+    constexpr uint32_t bias = (WT == LAMMCU_TYPE_Q5_0) ? 0x64106410u : 0x64006400u;     // (q - 16) or q
+    if constexpr (WT == LAMMCU_TYPE_Q5_1) m = raw_half<O + 2, NWR>(raw);
+    const uint32_t qh = raw_word<QH, NWR>(raw);
+    const uint32_t q[4] = {raw_word<QS, NWR>(raw), raw_word<QS + 4, NWR>(raw), raw_word<QS + 8, NWR>(raw),
+                           raw_word<QS + 12, NWR>(raw)};
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+      const uint32_t h = qh >> (4 * w), g = qh >> (16 + 4 * w);
+      out[w].x = magic_pair((q[w] & 0x000F000Fu) | ((h & 1u) << 4) | ((h & 4u) << 18), bias);
+      out[w].y = magic_pair(((q[w] >> 4) & 0x000F000Fu) | ((g & 1u) << 4) | ((g & 4u) << 18), bias);
+      out[w].z = magic_pair(((q[w] >> 8) & 0x000F000Fu) | ((h & 2u) << 3) | ((h & 8u) << 17), bias);
+      out[w].w = magic_pair(((q[w] >> 12) & 0x000F000Fu) | ((g & 2u) << 3) | ((g & 8u) << 17), bias);
+    }
+  } else {   // Q8_0: natural order, (b ^ 0x80) | 0x6400 = 1024 + 128 + b
+    constexpr int QS = O + 2;
+    const uint32_t q[8] = {raw_word<QS, NWR>(raw),      raw_word<QS + 4, NWR>(raw),  raw_word<QS + 8, NWR>(raw),
+                           raw_word<QS + 12, NWR>(raw), raw_word<QS + 16, NWR>(raw), raw_word<QS + 20, NWR>(raw),
+                           raw_word<QS + 24, NWR>(raw), raw_word<QS + 28, NWR>(raw)};
+    constexpr uint32_t bias = 0x64806480u;
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+      const uint32_t a = q[2 * w] ^ 0x80808080u, b = q[2 * w + 1] ^ 0x80808080u;
+      const uint32_t a0 = __byte_perm(a, 0x64646464u, 0x5140), a1 = __byte_perm(a, 0x64646464u, 0x7362);
+      const uint32_t b0 = __byte_perm(b, 0x64646464u, 0x5140), b1 = __byte_perm(b, 0x64646464u, 0x7362);
+      const __half2 bh = *reinterpret_cast<const __half2 *>(&bias);
+      __half2 r0 = __hsub2(*reinterpret_cast<const __half2 *>(&a0), bh), r1 = __hsub2(*reinterpret_cast<const __half2 *>(&a1), bh);
+      __half2 r2 = __hsub2(*reinterpret_cast<const __half2 *>(&b0), bh), r3 = __hsub2(*reinterpret_cast<const __half2 *>(&b1), bh);
+      out[w].x = *reinterpret_cast<uint32_t *>(&r0);
+      out[w].y = *reinterpret_cast<uint32_t *>(&r1);
+      out[w].z = *reinterpret_cast<uint32_t *>(&r2);
+      out[w].w = *reinterpret_cast<uint32_t *>(&r3);
+    }
+  }
+}
+
+// One pipeline stage (64 K = blocks 2Q, 2Q+1 of the raw chunk) of the thread's row r.
+template <int WT, int Q, int NWR>
+__device__ __forceinline__ void unpack_stage(const uint32_t (&raw)[NWR], uint8_t *a_stage, int r, float *dws,
+                                             float *mws, int kbi0) {
+  const uint32_t row_base = smem_u32(a_stage) + (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u;
+#pragma unroll
+  for (int j = 0; j < 2; j++) {
+    uint4 out[4];
+    float d, m;
+    if (j == 0) unpack_block<WT, 2 * Q, NWR>(raw, out, d, m);
+    else unpack_block<WT, 2 * Q + 1, NWR>(raw, out, d, m);
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+      const uint32_t c = (uint32_t)(4 * j + w) ^ (uint32_t)(r & 7);
+      asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(row_base + c * 16u), "r"(out[w].x), "r"(out[w].y),
+                   "r"(out[w].z), "r"(out[w].w)
+                   : "memory");
+    }
+    const int slot = ((kbi0 + j) % kScaleRing) * GM + r;
+    dws[slot] = d;
+    if constexpr (WT == LAMMCU_TYPE_Q4_1 || WT == LAMMCU_TYPE_Q5_1) mws[slot] = m;
+  }
+}
+
+// ---- the kernel ----------------------------------------------------------------------------
+// shared memory map (offsets from the 1024-aligned base)
+template <int WT> struct GemmSmem {
+  static constexpr int BS = type_info(WT).size;
+  static constexpr int kRawRowBytes = 8 * BS;                       // 8 blocks = 256 K elements
+  static constexpr int kRawBytes = GM * kRawRowBytes;
+  static constexpr int kAOff = 0;
+  static constexpr int kBOff = kAOff + kGStages * GM * GK * 2;
+  static constexpr int kRawOff = kBOff + kGStages * GN * GK * 2;
+  static constexpr int kDxOff = kRawOff + kRawStages * ((kRawBytes + 127) / 128 * 128);
+  static constexpr bool kMin = (WT == LAMMCU_TYPE_Q4_1 || WT == LAMMCU_TYPE_Q5_1);   // s_x / m_w rings only then
+  static constexpr int kSxOff = kDxOff + kScaleRing * GN * 4;
+  static constexpr int kDwOff = kSxOff + (kMin ? kScaleRing * GN * 4 : 0);
+  static constexpr int kMwOff = kDwOff + kScaleRing * GM * 4;
+  static constexpr int kBarOff = kMwOff + (kMin ? kScaleRing * GM * 4 : 0);
+  static constexpr int kTotal = kBarOff + 256;
+};
+
+template <int WT>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x, const GemmParams p) {
+  using L = GemmSmem<WT>;
+  constexpr bool kMin = (WT == LAMMCU_TYPE_Q4_1 || WT == LAMMCU_TYPE_Q5_1);
+  constexpr int NWR = 2 * L::BS;                                    // raw words per row chunk
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + L::kBarOff);
+  uint64_t *full_b = bars, *full_a = bars + 4, *empty = bars + 8, *raw_full = bars + 12, *raw_empty = bars + 14,
+           *s_full = bars + 16, *s_empty = bars + 19;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 24);
+  float *dxs = reinterpret_cast<float *>(smem + L::kDxOff), *sxs = reinterpret_cast<float *>(smem + L::kSxOff);
+  float *dws = reinterpret_cast<float *>(smem + L::kDwOff), *mws = reinterpret_cast<float *>(smem + L::kMwOff);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles = (p.N + GN - 1) / GN;
+  const int m0 = (blockIdx.x / n_tiles) * GM, n0 = (blockIdx.x % n_tiles) * GN;
+  const int n_stages = p.K / GK, n_kb = p.K / 32;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kGStages; i++) {
+      mbar_init(&full_b[i], 1);
+      mbar_init(&full_a[i], 4);          // one arrival per unpack warp
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < kRawStages; i++) {
+      mbar_init(&raw_full[i], 1);
+      mbar_init(&raw_empty[i], 4);
+    }
+    for (int i = 0; i < kSStages; i++) {
+      mbar_init(&s_full[i], 1);
+      mbar_init(&s_empty[i], 8);         // one arrival per drain warp
+    }
+    fence_barrier_init();
+    prefetch_tmap(&tm_w);
+    prefetch_tmap(&tm_x);
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      for (int st = 0; st < n_stages; st++) {
+        if ((st & 3) == 0) {
+          const int ms = st >> 2, r = ms % kRawStages;
+          mbar_wait(&raw_empty[r], ((uint32_t)(ms / kRawStages) & 1u) ^ 1u);
+          mbar_arrive_expect_tx(&raw_full[r], (uint32_t)L::kRawBytes);
+          tma_load_2d(smem + L::kRawOff + r * ((L::kRawBytes + 127) / 128 * 128), &tm_w, ms * (L::kRawRowBytes / 2), m0,
+                      &raw_full[r]);
+        }
+        const int s = st % kGStages;
+        mbar_wait(&empty[s], ((uint32_t)(st / kGStages) & 1u) ^ 1u);
+        mbar_arrive_expect_tx(&full_b[s], (uint32_t)(GN * GK * 2 + 2 * GN * 4 * (kMin ? 2 : 1)));
+        tma_load_2d(smem + L::kBOff + s * (GN * GK * 2), &tm_x, st * GK, n0, &full_b[s]);
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+          const int kbi = 2 * st + j, slot = (kbi % kScaleRing) * GN;
+          bulk_g2s(dxs + slot, p.dxT + (int64_t)kbi * p.Npad + n0, GN * 4, &full_b[s]);
+          if (kMin) bulk_g2s(sxs + slot, p.sxT + (int64_t)kbi * p.Npad + n0, GN * 4, &full_b[s]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      for (int st = 0; st < n_stages; st++) {
+        const int s = st % kGStages;
+        const uint32_t ph = (uint32_t)(st / kGStages) & 1u;
+        mbar_wait(&full_a[s], ph);
+        mbar_wait(&full_b[s], ph);
+        tc_fence_after();
+        const uint64_t adesc = make_sw128_desc(smem_u32(smem + L::kAOff + s * (GM * GK * 2)));
+        const uint64_t bdesc = make_sw128_desc(smem_u32(smem + L::kBOff + s * (GN * GK * 2)));
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+          const int kbi = 2 * st + j, sr = kbi % kSStages;
+          mbar_wait(&s_empty[sr], ((uint32_t)(kbi / kSStages) & 1u) ^ 1u);
+          tc_fence_after();
+          // the K offset inside the 128-byte swizzle atom advances the start address (16-byte units)
+          umma_f16(tmem_base + sr * GN, adesc + (uint64_t)(j * 4), bdesc + (uint64_t)(j * 4), kIdescF16, 0u);
+          umma_f16(tmem_base + sr * GN, adesc + (uint64_t)(j * 4 + 2), bdesc + (uint64_t)(j * 4 + 2), kIdescF16, 1u);
+          umma_commit(&s_full[sr]);
+        }
+        umma_commit(&empty[s]);
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ===================== weight unpack (thread = row) =====================
+    const int r = threadIdx.x - 128;
+    for (int ms = 0; ms < n_stages / 4; ms++) {
+      const int rs = ms % kRawStages;
+      mbar_wait(&raw_full[rs], (uint32_t)(ms / kRawStages) & 1u);
+      uint32_t raw[NWR];
+      const uint32_t src = smem_u32(smem + L::kRawOff + rs * ((L::kRawBytes + 127) / 128 * 128)) + (uint32_t)r * L::kRawRowBytes;
+#pragma unroll
+      for (int i = 0; i < NWR / 4; i++)
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(raw[4 * i]), "=r"(raw[4 * i + 1]), "=r"(raw[4 * i + 2]), "=r"(raw[4 * i + 3])
+                     : "r"(src + 16u * i));
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&raw_empty[rs]);
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const int st = ms * 4 + q, s = st % kGStages;
+        mbar_wait(&empty[s], ((uint32_t)(st / kGStages) & 1u) ^ 1u);
+        uint8_t *a_stage = smem + L::kAOff + s * (GM * GK * 2);
+        if (q == 0) unpack_stage<WT, 0, NWR>(raw, a_stage, r, dws, mws, 2 * st);
+        else if (q == 1) unpack_stage<WT, 1, NWR>(raw, a_stage, r, dws, mws, 2 * st);
+        else if (q == 2) unpack_stage<WT, 2, NWR>(raw, a_stage, r, dws, mws, 2 * st);
+        else unpack_stage<WT, 3, NWR>(raw, a_stage, r, dws, mws, 2 * st);
+        fence_proxy_async();             // generic-proxy stores -> visible to the tensor core
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full_a[s]);
+      }
+    }
+  } else if (warp >= 8) {
+    // ===================== drain (thread = weight row, 64 activation rows) =====================
+    const int q4 = warp & 3, h = (warp - 8) >> 2;
+    const int row = q4 * 32 + lane;
+    float2 acc[32];
+#pragma unroll
+    for (int i = 0; i < 32; i++) acc[i] = make_float2(0.f, 0.f);
+    for (int kbi = 0; kbi < n_kb; kbi++) {
+      const int sr = kbi % kSStages;
+      mbar_wait(&s_full[sr], (uint32_t)(kbi / kSStages) & 1u);
+      tc_fence_after();
+      const int slot = (kbi % kScaleRing);
+      const float dw = dws[slot * GM + row];
+      const float2 dw2 = make_float2(dw, dw);
+      float2 mw2 = make_float2(0.f, 0.f);
+      if constexpr (kMin) {
+        const float mw = mws[slot * GM + row];
+        mw2 = make_float2(mw, mw);
+      }
+      const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(sr * GN + h * 64);
+#pragma unroll
+      for (int hh = 0; hh < 2; hh++) {           // 2 x 32 columns: keeps the register count under 128
+        uint32_t sv[32];
+        tmem_ld32(taddr + 32 * hh, sv);
+        tmem_ld_wait();
+        if (hh == 1) {                           // this warp's part of the TMEM stage is in registers
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&s_empty[sr]);
+        }
+        const float4 *dx4 = reinterpret_cast<const float4 *>(dxs + slot * GN + h * 64 + hh * 32);
+        const float4 *sx4 = reinterpret_cast<const float4 *>(sxs + slot * GN + h * 64 + hh * 32);
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+          const float4 dx = dx4[c];
+          float2 &a0 = acc[16 * hh + 2 * c], &a1 = acc[16 * hh + 2 * c + 1];
+          a0 = ffma2(fmul2(dw2, make_float2(dx.x, dx.y)),
+                     make_float2(__uint_as_float(sv[4 * c]), __uint_as_float(sv[4 * c + 1])), a0);
+          a1 = ffma2(fmul2(dw2, make_float2(dx.z, dx.w)),
+                     make_float2(__uint_as_float(sv[4 * c + 2]), __uint_as_float(sv[4 * c + 3])), a1);
+          if constexpr (kMin) {
+            const float4 sx = sx4[c];
+            a0 = ffma2(mw2, make_float2(sx.x, sx.y), a0);
+            a1 = ffma2(mw2, make_float2(sx.z, sx.w), a1);
+          }
+        }
+      }
+    }
+    // epilogue: C[n * ldc + m]; lanes = consecutive m
+    const int m = m0 + row;
+    if (m < p.M) {
+#pragma unroll
+      for (int c = 0; c < 32; c++) {
+        const int n = n0 + h * 64 + 2 * c;
+        if (n < p.N) p.c[(int64_t)n * p.ldc + m] = acc[c].x;
+        if (n + 1 < p.N) p.c[(int64_t)(n + 1) * p.ldc + m] = acc[c].y;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+// ---- host side ------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled encode_fn() {
+  static PFN_encodeTiled fn = [] {
+    void *f = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qr) != cudaSuccess ||
+        qr != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    return (PFN_encodeTiled)f;
+  }();
+  return fn;
+}
+
+static int make_map_2d(CUtensorMap *map, CUtensorMapDataType dt, int elem_bytes, const void *base, uint64_t dim0,
+                       uint64_t dim1, uint64_t stride1_bytes, uint32_t box0, uint32_t box1, CUtensorMapSwizzle sw) {
+  PFN_encodeTiled fn = encode_fn();
+  if (!fn) {
+    set_error("gemm: cuTensorMapEncodeTiled is not available");
+    return LAMMCU_ERR_CUDA;
+  }
+  cuuint64_t dims[2] = {dim0, dim1};
+  cuuint64_t strides[1] = {stride1_bytes};
+  cuuint32_t box[2] = {box0, box1};
+  cuuint32_t estr[2] = {1, 1};
+  (void)elem_bytes;
+  CUresult r = fn(map, dt, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("gemm: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
+template <int WT>
+static int launch_gemm_tc(const CUtensorMap &tm_w, const CUtensorMap &tm_x, const GemmParams &p, cudaStream_t st) {
+  using L = GemmSmem<WT>;
+  constexpr int smem = L::kTotal + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<WT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) {
+      set_error("gemm: cudaFuncSetAttribute(%d): %s", smem, cudaGetErrorString(e));
+      return LAMMCU_ERR_CUDA;
+    }
+    attr_set = true;
+  }
+  const int tiles = ((p.M + GM - 1) / GM) * ((p.N + GN - 1) / GN);
+  gemm_tc_kernel<WT><<<tiles, kGemmThreads, smem, st>>>(tm_w, tm_x, p);
+  g_launch_count++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("gemm launch (type %d): %s", WT, cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
+bool gemm_tc_supported(int w_type, const void *w, int64_t w_stride, int64_t M, int64_t N, int64_t K) {
+  if (w_type != LAMMCU_TYPE_Q4_0 && w_type != LAMMCU_TYPE_Q4_1 && w_type != LAMMCU_TYPE_Q5_0 &&
+      w_type != LAMMCU_TYPE_Q5_1 && w_type != LAMMCU_TYPE_Q8_0)
+    return false;
+  if (K <= 0 || K % 256 || M <= 0 || N <= 0 || M > 0x3fffffff || N > 0x3fffffff) return false;
+  return (((uintptr_t)w | (uintptr_t)w_stride) & 15) == 0;
+}
+
+size_t gemm_ws_bytes(int64_t N, int64_t K) {
+  const int64_t npad = (N + GN - 1) / GN * GN, kb = K / 32;
+  return (size_t)(npad * K * 2 + 2 * kb * npad * 4 + 1024);
+}
+
+// xq: quantized activations (ggml blocks, row stride xq_stride); ws: gemm_ws_bytes() of scratch
+int launch_gemm_tc_any(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
+                       int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st) {
+  const TypeInfo ti = type_info(w_type);
+  const int64_t npad = (N + GN - 1) / GN * GN, kb = K / 32;
+  uint8_t *base = (uint8_t *)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
+  void *x16 = base;
+  float *dxT = (float *)(base + npad * K * 2);
+  float *sxT = dxT + kb * npad;
+  const int perm = (w_type == LAMMCU_TYPE_Q8_0) ? 0 : 1;
+  int rc = launch_gemm_prep(ti.vec_dot, perm, xq, xq_stride, x16, dxT, sxT, N, npad, K, st);
+  if (rc) return rc;
+  CUtensorMap tm_w, tm_x;
+  // raw weights as uint16 [M][row_bytes / 2], box = 8 blocks x 128 rows
+  rc = make_map_2d(&tm_w, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, w, (uint64_t)(kb * ti.size / 2), (uint64_t)M,
+                   (uint64_t)w_stride, (uint32_t)(4 * ti.size), GM, CU_TENSOR_MAP_SWIZZLE_NONE);
+  if (rc) return rc;
+  rc = make_map_2d(&tm_x, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, x16, (uint64_t)K, (uint64_t)npad, (uint64_t)K * 2, GK, GN,
+                   CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  GemmParams p;
+  p.dxT = dxT;  p.sxT = sxT;  p.c = c;  p.ldc = ldc;
+  p.M = (int)M;  p.N = (int)N;  p.Npad = (int)npad;  p.K = (int)K;
+  switch (w_type) {
+  case LAMMCU_TYPE_Q4_0: return launch_gemm_tc<LAMMCU_TYPE_Q4_0>(tm_w, tm_x, p, st);
+  case LAMMCU_TYPE_Q4_1: return launch_gemm_tc<LAMMCU_TYPE_Q4_1>(tm_w, tm_x, p, st);
+  case LAMMCU_TYPE_Q5_0: return launch_gemm_tc<LAMMCU_TYPE_Q5_0>(tm_w, tm_x, p, st);
+  case LAMMCU_TYPE_Q5_1: return launch_gemm_tc<LAMMCU_TYPE_Q5_1>(tm_w, tm_x, p, st);
+  default:               return launch_gemm_tc<LAMMCU_TYPE_Q8_0>(tm_w, tm_x, p, st);
+  }
+}
+
+// Prefill entry: tensor-core GEMM where it applies, else the column-grouped GEMV (correct for
+// every type / alignment; re-reads W once per 8 columns).
+int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
+                int64_t ldc, int64_t M, int64_t N, int64_t K, cudaStream_t st) {
+  if (gemm_tc_supported(w_type, w, w_stride, M, N, K)) {
+    void *ws = gemm_workspace(gemm_ws_bytes(N, K));
+    if (!ws) return LAMMCU_ERR_NOMEM;
+    return launch_gemm_tc_any(w_type, w, w_stride, xq, xq_stride, c, ldc, M, N, K, ws, st);
+  }
   return launch_gemv(w_type, w, w_stride, xq, xq_stride, c, ldc, M, N, K, st);
 }
 

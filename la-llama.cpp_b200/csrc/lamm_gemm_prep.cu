@@ -1,0 +1,107 @@
+// lamm_gemm_prep.cu -- operand preparation for the prefill GEMM (lamm_gemm.cu).
+//
+// The tensor-core GEMM multiplies EXACT small integers held in fp16: the int8 activation
+// quants q_x in [-127, 127] and the unpacked weight quants are exactly representable, their
+// products and the per-block sums (< 2^24) are exact in the tensor core's f32 accumulator,
+// so every 32-element block sum equals the reference's integer sumi bit for bit
+// (src/lamm_kernel_q4_1.hpp:12-24: sumi, then d_w * d_x * sumi + m_w * s_x).
+//
+// This kernel turns the quantized activation rows Xq (ggml block_q8_0 / block_q8_1, the
+// bit-exact output of lamm_quantize.cu) into the GEMM's B operand:
+//   X16 : fp16 [Npad][K]   the quants as fp16, K contiguous.  Inside every 32-block the
+//                          elements are stored in the order the weight unpacker produces
+//                          them cheaply (perm 1, "nibble order", for Q4/Q5: 16-byte chunk w
+//                          = elements 4w, 4w+2, 16+4w, 16+4w+2, 4w+1, 4w+3, 16+4w+1,
+//                          16+4w+3; perm 0 = natural order for Q8_0).  A dot product does
+//                          not care about the order as long as both operands agree.
+//   dxT : f32 [Kb][Npad]   f32(d_x) of block kb of row n (transposed: one K-block's scales of
+//                          all rows are contiguous, broadcast-read by the drain warps)
+//   sxT : f32 [Kb][Npad]   f32(s_x) (q8_1 only)
+// Rows n >= N are written as zeros.
+#include "lamm_common.cuh"
+
+namespace lamm {
+
+template <int VT, int PERM>
+__global__ void __launch_bounds__(256) gemm_prep_kernel(const uint8_t *__restrict__ xq, int64_t xq_stride,
+                                                       __half *__restrict__ x16, float *__restrict__ dxT,
+                                                       float *__restrict__ sxT, int N, int Npad, int kb) {
+  constexpr int XB = (VT == LAMMCU_TYPE_Q8_0) ? 34 : 36;
+  const int64_t total = (int64_t)Npad * kb;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int n = (int)(i / kb), b = (int)(i - (int64_t)n * kb);
+    uint32_t x[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    float d = 0.f, s = 0.f;
+    if (n < N) {
+      const uint8_t *blk = xq + (int64_t)n * xq_stride + (int64_t)b * XB;
+      if constexpr (VT == LAMMCU_TYPE_Q8_1) {
+        const uint32_t ds = *reinterpret_cast<const uint32_t *>(blk);
+        d = half_bits_to_float(ds & 0xffffu);
+        s = half_bits_to_float(ds >> 16);
+#pragma unroll
+        for (int j = 0; j < 8; j++) x[j] = *reinterpret_cast<const uint32_t *>(blk + 4 + 4 * j);
+      } else {
+        d = half_bits_to_float(*reinterpret_cast<const uint16_t *>(blk));
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          const uint16_t *h = reinterpret_cast<const uint16_t *>(blk + 2 + 4 * j);
+          x[j] = (uint32_t)h[0] | ((uint32_t)h[1] << 16);
+        }
+      }
+    }
+    auto el = [&](int e) -> __half {                 // element e of the block as fp16
+      const int v = (int)(signed char)((x[e >> 2] >> (8 * (e & 3))) & 0xffu);
+      return __int2half_rn(v);
+    };
+    uint4 *dst = reinterpret_cast<uint4 *>(x16 + ((int64_t)n * kb + b) * 32);
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+      __half h[8];
+      if constexpr (PERM == 1) {
+        h[0] = el(4 * w);      h[1] = el(4 * w + 2);      h[2] = el(16 + 4 * w);     h[3] = el(16 + 4 * w + 2);
+        h[4] = el(4 * w + 1);  h[5] = el(4 * w + 3);      h[6] = el(16 + 4 * w + 1); h[7] = el(16 + 4 * w + 3);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; j++) h[j] = el(8 * w + j);
+      }
+      uint4 v;
+      v.x = (uint32_t)__half_as_ushort(h[0]) | ((uint32_t)__half_as_ushort(h[1]) << 16);
+      v.y = (uint32_t)__half_as_ushort(h[2]) | ((uint32_t)__half_as_ushort(h[3]) << 16);
+      v.z = (uint32_t)__half_as_ushort(h[4]) | ((uint32_t)__half_as_ushort(h[5]) << 16);
+      v.w = (uint32_t)__half_as_ushort(h[6]) | ((uint32_t)__half_as_ushort(h[7]) << 16);
+      dst[w] = v;
+    }
+    dxT[(int64_t)b * Npad + n] = d;
+    if (VT == LAMMCU_TYPE_Q8_1) sxT[(int64_t)b * Npad + n] = s;
+  }
+}
+
+int launch_gemm_prep(int vt, int perm, const void *xq, int64_t xq_stride, void *x16, float *dxT, float *sxT,
+                     int64_t N, int64_t Npad, int64_t K, cudaStream_t st) {
+  const int kb = (int)(K / 32);
+  const int64_t total = Npad * kb;
+  int blocks = (int)((total + 255) / 256);
+  const int cap = sm_count_cached() * 8;
+  if (blocks > cap) blocks = cap;
+  const uint8_t *p = (const uint8_t *)xq;
+  __half *o = (__half *)x16;
+  if (vt == LAMMCU_TYPE_Q8_1) {
+    if (perm) gemm_prep_kernel<LAMMCU_TYPE_Q8_1, 1><<<blocks, 256, 0, st>>>(p, xq_stride, o, dxT, sxT, (int)N, (int)Npad, kb);
+    else gemm_prep_kernel<LAMMCU_TYPE_Q8_1, 0><<<blocks, 256, 0, st>>>(p, xq_stride, o, dxT, sxT, (int)N, (int)Npad, kb);
+  } else if (vt == LAMMCU_TYPE_Q8_0) {
+    if (perm) gemm_prep_kernel<LAMMCU_TYPE_Q8_0, 1><<<blocks, 256, 0, st>>>(p, xq_stride, o, dxT, sxT, (int)N, (int)Npad, kb);
+    else gemm_prep_kernel<LAMMCU_TYPE_Q8_0, 0><<<blocks, 256, 0, st>>>(p, xq_stride, o, dxT, sxT, (int)N, (int)Npad, kb);
+  } else {
+    set_error("gemm_prep: activation type %d not supported", vt);
+    return LAMMCU_ERR_TYPE;
+  }
+  g_launch_count++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("gemm_prep launch: %s", cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
+}  // namespace lamm

@@ -45,6 +45,7 @@ struct DeviceState {
   void *cout = nullptr; size_t cout_bytes = 0;   // host path: C on device
   void *hx = nullptr;  size_t hx_bytes = 0;      // pinned staging
   void *hc = nullptr;  size_t hc_bytes = 0;
+  void *gws = nullptr; size_t gws_bytes = 0;     // prefill GEMM operand scratch
 };
 static DeviceState g_dev;
 static std::mutex g_mu;
@@ -91,6 +92,11 @@ static int grow(void **p, size_t *have, size_t need, bool pinned) {
   }
   *have = n;
   return LAMMCU_OK;
+}
+
+void *gemm_workspace(size_t bytes) {
+  if (grow(&g_dev.gws, &g_dev.gws_bytes, bytes, false) != LAMMCU_OK) return nullptr;
+  return g_dev.gws;
 }
 
 }  // namespace lamm
@@ -176,6 +182,7 @@ int lammcu_shutdown(void) {
   if (g_dev.cout) cudaFree(g_dev.cout);
   if (g_dev.hx) cudaFreeHost(g_dev.hx);
   if (g_dev.hc) cudaFreeHost(g_dev.hc);
+  if (g_dev.gws) cudaFree(g_dev.gws);
   if (g_dev.sched) cudaFree(g_dev.sched);
   if (g_dev.stream) cudaStreamDestroy(g_dev.stream);
   g_dev = DeviceState();
