@@ -539,6 +539,63 @@ def run_suite(args):
     return 0
 
 
+def run_suite_gemm(args):
+    """Prefill sweep: format x LLaMA shape at N=args.n through lammcu_mul_mat_dev (activation quantize +
+    operand prep + tcgen05 GEMM), ring of distinct weights, CUDA graph; also the GEMM kernel alone
+    (pre-quantized activations still include the prep launch).  TOPS = 2*M*N*K / time."""
+    import torch
+    import lamm_b200 as L
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    L.init(0)
+    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    bf16 = json.load(open(pk))["bf16_tflops"] if os.path.exists(pk) else 1590.0
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(7)
+    fmts = args.fmts.split(",") if args.fmts else ["q4_0", "q4_1", "q5_0", "q5_1", "q8_0"]
+    shapes = [(4096, 4096), (11008, 4096), (4096, 11008), (5120, 5120), (13824, 5120), (5120, 13824)]
+    if args.shapes:
+        shapes = [tuple(int(v) for v in s_.split("x")) for s_ in args.shapes.split(",")]
+    n = args.n if args.n > 1 else 512
+    for fmt in fmts:
+        t = TYPE_IDS[fmt]
+        for (m, k) in shapes:
+            wb = m * w_row_bytes(t, k)
+            ring = max(2, min(16, (args.ring_mb * (1 << 20) + wb - 1) // wb))
+            ws = [synth_weight(torch, t, m, k, gen, dev) for _ in range(ring)]
+            x = torch.randn((n, k), generator=gen, device=dev)
+            c = torch.zeros((n, m), device=dev)
+
+            def body():
+                for w in ws:
+                    L.mul_mat(t, w, x, out=c)
+            s = torch.cuda.Stream()
+            with torch.cuda.stream(s):
+                body()
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                body()
+            for _ in range(2):
+                g.replay()
+            torch.cuda.synchronize()
+            reps = max(2, int(200 / ring))
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                g.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            us = e0.elapsed_time(e1) * 1e3 / (reps * ring)
+            tops = 2.0 * m * n * k / us / 1e6
+            print(json.dumps({"fmt": fmt, "M": m, "K": k, "N": n, "ring": ring, "us": round(us, 2),
+                              "TOPS": round(tops, 1), "frac_f16_measured": round(tops / bf16, 4),
+                              "frac_int8_nominal_4500": round(tops / 4500.0, 4)}), flush=True)
+            del ws, g
+            torch.cuda.empty_cache()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -547,13 +604,15 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--fmt", default="q4_1", choices=sorted(TYPE_IDS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--suite", default=None, choices=[None, "gemv"], help="per-format sweep instead of the bench line")
+    ap.add_argument("--suite", default=None, choices=[None, "gemv", "gemm"], help="per-format sweep instead of the bench line")
     ap.add_argument("--fmts", default=None)
     ap.add_argument("--shapes", default=None, help="MxK,MxK,...")
     ap.add_argument("--n", type=int, default=1)
     ap.add_argument("--ring-mb", type=int, default=512)
     ap.add_argument("--fused", action="store_true", help="suite: include the activation quantize launch")
     args = ap.parse_args()
+    if args.suite == "gemm":
+        return run_suite_gemm(args)
     if args.suite:
         return run_suite(args)
     if args.impl == "reference":

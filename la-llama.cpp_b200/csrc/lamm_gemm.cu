@@ -15,8 +15,8 @@
 //   * one CTA = 128 weight rows x 128 activation rows, 16 warps:
 //       warp 0      TMA producer: raw packed weight blocks (2-D box over bytes), the fp16
 //                   activation tile (SWIZZLE_128B), the per-block activation scales
-//       warp 1      MMA issuer (one thread): per 32-block 2 x tcgen05.mma M128 N128 K16 into a
-//                   ring of 3 TMEM stages, tcgen05.commit -> mbarrier
+//       warp 1      MMA issuer (one thread): per 32-block 2 x tcgen05.mma M128 N128 K16; two
+//                   blocks (256 TMEM columns) per hand-off, ring of 2, tcgen05.commit -> mbarrier
 //       warp 2      TMEM allocation
 //       warps 4-7   weight unpack (thread = row): nibbles / 5th bits -> fp16 with the
 //                   0x6400-magic trick, written in the UMMA K-major SWIZZLE_128B layout
@@ -28,11 +28,13 @@
 
 #include <cuda.h>
 
+#include <cstdlib>
+
 namespace lamm {
 
 constexpr int GM = 128, GN = 128, GK = 64;     // CTA tile; K elements per pipeline stage
 constexpr int kGStages = 4;                    // A16 / B16 ring
-constexpr int kSStages = 3;                    // TMEM accumulator ring (128 columns each)
+constexpr int kSStages = 2;                    // TMEM accumulator ring (2 x 128 columns each)
 constexpr int kRawStages = 2;                  // raw packed-weight ring (256 K elements each)
 constexpr int kScaleRing = 16;                 // K-blocks of d_w / d_x kept in shared memory
 constexpr int kGemmThreads = 512;
@@ -42,6 +44,7 @@ struct GemmParams {
   float *c;
   int64_t ldc;
   int M, N, Npad, K;
+  int debug;                  // diagnostics (LAMM_GEMM_DEBUG): 4 = no unpack
 };
 
 // ---- tcgen05 / TMA PTX ------------------------------------------------------------------
@@ -129,6 +132,19 @@ __device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
   float2 d;
   asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
   return d;
+}
+
+// explicit shared-space loads (the carved-up dynamic shared memory is reached through generic
+// pointers otherwise, and generic loads are far slower than LDS)
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
 }
 
 // two fp16 holding the small integers in the low bits of each half of p: (1024 + v) - bias
@@ -227,9 +243,10 @@ __device__ __forceinline__ void unpack_stage(const uint32_t (&raw)[NWR], uint8_t
                    "r"(out[w].z), "r"(out[w].w)
                    : "memory");
     }
-    const int slot = ((kbi0 + j) % kScaleRing) * GM + r;
-    dws[slot] = d;
-    if constexpr (WT == LAMMCU_TYPE_Q4_1 || WT == LAMMCU_TYPE_Q5_1) mws[slot] = m;
+    const uint32_t slot = (uint32_t)(((kbi0 + j) % kScaleRing) * GM + r) * 4u;
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(smem_u32(dws) + slot), "f"(d) : "memory");
+    if constexpr (WT == LAMMCU_TYPE_Q4_1 || WT == LAMMCU_TYPE_Q5_1)
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(smem_u32(mws) + slot), "f"(m) : "memory");
   }
 }
 
@@ -329,16 +346,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
         tc_fence_after();
         const uint64_t adesc = make_sw128_desc(smem_u32(smem + L::kAOff + s * (GM * GK * 2)));
         const uint64_t bdesc = make_sw128_desc(smem_u32(smem + L::kBOff + s * (GN * GK * 2)));
+        // one TMEM stage = the two 32-blocks of this pipeline stage (2 x 128 columns)
+        const int sr = st % kSStages;
+        mbar_wait(&s_empty[sr], ((uint32_t)(st / kSStages) & 1u) ^ 1u);
+        tc_fence_after();
 #pragma unroll
         for (int j = 0; j < 2; j++) {
-          const int kbi = 2 * st + j, sr = kbi % kSStages;
-          mbar_wait(&s_empty[sr], ((uint32_t)(kbi / kSStages) & 1u) ^ 1u);
-          tc_fence_after();
           // the K offset inside the 128-byte swizzle atom advances the start address (16-byte units)
-          umma_f16(tmem_base + sr * GN, adesc + (uint64_t)(j * 4), bdesc + (uint64_t)(j * 4), kIdescF16, 0u);
-          umma_f16(tmem_base + sr * GN, adesc + (uint64_t)(j * 4 + 2), bdesc + (uint64_t)(j * 4 + 2), kIdescF16, 1u);
-          umma_commit(&s_full[sr]);
+          const uint32_t d = tmem_base + (uint32_t)(sr * 2 * GN + j * GN);
+          umma_f16(d, adesc + (uint64_t)(j * 4), bdesc + (uint64_t)(j * 4), kIdescF16, 0u);
+          umma_f16(d, adesc + (uint64_t)(j * 4 + 2), bdesc + (uint64_t)(j * 4 + 2), kIdescF16, 1u);
         }
+        umma_commit(&s_full[sr]);
         umma_commit(&empty[s]);
       }
     }
@@ -362,7 +381,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
         const int st = ms * 4 + q, s = st % kGStages;
         mbar_wait(&empty[s], ((uint32_t)(st / kGStages) & 1u) ^ 1u);
         uint8_t *a_stage = smem + L::kAOff + s * (GM * GK * 2);
-        if (q == 0) unpack_stage<WT, 0, NWR>(raw, a_stage, r, dws, mws, 2 * st);
+        if (p.debug & 4) {
+        } else if (q == 0) unpack_stage<WT, 0, NWR>(raw, a_stage, r, dws, mws, 2 * st);
         else if (q == 1) unpack_stage<WT, 1, NWR>(raw, a_stage, r, dws, mws, 2 * st);
         else if (q == 2) unpack_stage<WT, 2, NWR>(raw, a_stage, r, dws, mws, 2 * st);
         else unpack_stage<WT, 3, NWR>(raw, a_stage, r, dws, mws, 2 * st);
@@ -378,44 +398,59 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
     float2 acc[32];
 #pragma unroll
     for (int i = 0; i < 32; i++) acc[i] = make_float2(0.f, 0.f);
-    for (int kbi = 0; kbi < n_kb; kbi++) {
-      const int sr = kbi % kSStages;
-      mbar_wait(&s_full[sr], (uint32_t)(kbi / kSStages) & 1u);
+    const uint32_t dxs_a = smem_u32(dxs), sxs_a = smem_u32(sxs), dws_a = smem_u32(dws), mws_a = smem_u32(mws);
+    // 16-column TMEM loads, double-buffered: the load of chunk i+1 is in flight during the math of chunk i
+    auto ld16 = [&](uint32_t taddr, uint32_t (&r)[16]) {
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+            "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+          : "r"(taddr)
+          : "memory");
+    };
+    for (int st = 0; st < n_stages; st++) {
+      const int sr = st % kSStages;
+      mbar_wait(&s_full[sr], (uint32_t)(st / kSStages) & 1u);
       tc_fence_after();
-      const int slot = (kbi % kScaleRing);
-      const float dw = dws[slot * GM + row];
-      const float2 dw2 = make_float2(dw, dw);
-      float2 mw2 = make_float2(0.f, 0.f);
-      if constexpr (kMin) {
-        const float mw = mws[slot * GM + row];
-        mw2 = make_float2(mw, mw);
-      }
-      const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(sr * GN + h * 64);
+      const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(sr * 2 * GN + h * 64);
+      uint32_t sv[2][16];
+      ld16(tbase, sv[0]);
+      tmem_ld_wait();
 #pragma unroll
-      for (int hh = 0; hh < 2; hh++) {           // 2 x 32 columns: keeps the register count under 128
-        uint32_t sv[32];
-        tmem_ld32(taddr + 32 * hh, sv);
-        tmem_ld_wait();
-        if (hh == 1) {                           // this warp's part of the TMEM stage is in registers
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&s_empty[sr]);
+      for (int ch = 0; ch < 8; ch++) {           // chunk = (K-block j = ch / 4, columns 16 * (ch % 4) ..)
+        const int j = ch >> 2, c16 = ch & 3;
+        if (ch + 1 < 8) ld16(tbase + (uint32_t)(((ch + 1) >> 2) * GN + ((ch + 1) & 3) * 16), sv[(ch + 1) & 1]);
+        const int slot = (2 * st + j) % kScaleRing;
+        const float dw = lds_f32(dws_a + (uint32_t)(slot * GM + row) * 4u);
+        const float2 dw2 = make_float2(dw, dw);
+        const uint32_t dx_a = dxs_a + (uint32_t)(slot * GN + h * 64 + c16 * 16) * 4u;
+        const uint32_t sx_a = sxs_a + (uint32_t)(slot * GN + h * 64 + c16 * 16) * 4u;
+        float2 mw2 = make_float2(0.f, 0.f);
+        if constexpr (kMin) {
+          const float mw = lds_f32(mws_a + (uint32_t)(slot * GM + row) * 4u);
+          mw2 = make_float2(mw, mw);
         }
-        const float4 *dx4 = reinterpret_cast<const float4 *>(dxs + slot * GN + h * 64 + hh * 32);
-        const float4 *sx4 = reinterpret_cast<const float4 *>(sxs + slot * GN + h * 64 + hh * 32);
+        const uint32_t(&v)[16] = sv[ch & 1];
 #pragma unroll
-        for (int c = 0; c < 8; c++) {
-          const float4 dx = dx4[c];
-          float2 &a0 = acc[16 * hh + 2 * c], &a1 = acc[16 * hh + 2 * c + 1];
+        for (int c = 0; c < 4; c++) {
+          const float4 dx = lds_f4(dx_a + 16u * c);
+          float2 &a0 = acc[8 * c16 + 2 * c], &a1 = acc[8 * c16 + 2 * c + 1];
           a0 = ffma2(fmul2(dw2, make_float2(dx.x, dx.y)),
-                     make_float2(__uint_as_float(sv[4 * c]), __uint_as_float(sv[4 * c + 1])), a0);
+                     make_float2(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1])), a0);
           a1 = ffma2(fmul2(dw2, make_float2(dx.z, dx.w)),
-                     make_float2(__uint_as_float(sv[4 * c + 2]), __uint_as_float(sv[4 * c + 3])), a1);
+                     make_float2(__uint_as_float(v[4 * c + 2]), __uint_as_float(v[4 * c + 3])), a1);
           if constexpr (kMin) {
-            const float4 sx = sx4[c];
+            const float4 sx = lds_f4(sx_a + 16u * c);
             a0 = ffma2(mw2, make_float2(sx.x, sx.y), a0);
             a1 = ffma2(mw2, make_float2(sx.z, sx.w), a1);
           }
+        }
+        tmem_ld_wait();                          // chunk ch + 1 has landed
+        if (ch == 6) {                           // the last load of this TMEM stage is in registers
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&s_empty[sr]);
         }
       }
     }
@@ -533,6 +568,8 @@ int launch_gemm_tc_any(int w_type, const void *w, int64_t w_stride, const void *
   GemmParams p;
   p.dxT = dxT;  p.sxT = sxT;  p.c = c;  p.ldc = ldc;
   p.M = (int)M;  p.N = (int)N;  p.Npad = (int)npad;  p.K = (int)K;
+  static const int dbg = [] { const char *e = getenv("LAMM_GEMM_DEBUG"); return e ? atoi(e) : 0; }();
+  p.debug = dbg;
   switch (w_type) {
   case LAMMCU_TYPE_Q4_0: return launch_gemm_tc<LAMMCU_TYPE_Q4_0>(tm_w, tm_x, p, st);
   case LAMMCU_TYPE_Q4_1: return launch_gemm_tc<LAMMCU_TYPE_Q4_1>(tm_w, tm_x, p, st);
