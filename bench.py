@@ -49,6 +49,11 @@ VEC_DOT = {0: 0, 2: 8, 3: 9, 6: 8, 7: 9, 8: 8, 10: 15}
 ACT_SIZE = {0: (1, 4), 8: (32, 34), 9: (32, 36), 15: (256, 292)}
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, averaged over the chain's
+# launches, from the committed `ncu --set full` capture (profiles/); None until measured for a format
+TRAFFIC_PER_LAUNCH = {}
+
+
 def chain_ops():
     ops = []
     for _ in range(LAYERS):
@@ -248,13 +253,18 @@ def run_reference(args):
     return 0
 
 
-def workload_config(fmt, world):
-    return {"workload": "LLaMA-7B %s decode (N=1) weight-matmul chain: 32 x {4x 4096x4096, 2x 11008x4096, "
+def workload_config(fmt, world, collective="fused"):
+    cfg = {"workload": "LLaMA-7B %s decode (N=1) weight-matmul chain: 32 x {4x 4096x4096, 2x 11008x4096, "
                         "1x 4096x11008} + head 32000x4096; activation quantize + quantized GEMV per matmul; "
                         "attention/norm/rope/sampling excluded (not on the path)" % fmt.upper(),
             "format": fmt, "n_tokens_per_step": 1, "matmuls_per_step": len(chain_ops()),
             "l2_defeat": "225 distinct weight buffers per step (4.13 GB for Q4_1) >> 126 MB L2",
-            "parallelism": "row-sharded M/%d per rank + all-gather of C" % world if world > 1 else "single GPU"}
+            "parallelism": "single GPU"}
+    if world > 1:
+        cfg["parallelism"] = ("row-sharded M/%d per rank; C replicated on every rank by %s" % (
+            world, "the decode kernel's NVLink peer-store epilogue + system-scope flags (no collective call)"
+            if collective == "fused" else "ncclAllGather after every matmul"))
+    return cfg
 
 
 # ---- the CUDA path ---------------------------------------------------------------------
@@ -299,10 +309,22 @@ def run_cuda(args):
     xq_ws = torch.zeros(((F // act_blck) * act_size + 64,), dtype=torch.uint8, device=dev)
     xq_pre = {k: (L.quantize_act(xin[k], vt) if t != 0 else xin[k]) for k in (H, F)}
     gather_buf = {m: torch.zeros((world, (m + world - 1) // world), device=dev) for m in (H, F, V)} if world > 1 else None
+    fused = world > 1 and args.collective == "fused" and t != 0
+    comm = cbufs = None
+    if fused:
+        # peer-store epilogue (SURVEY 8e "preferred"): every rank's decode kernel writes its rows of C
+        # straight into the full C vector of every rank over NVLink and raises a system-scope flag;
+        # the next launch waits on the flags.  No collective call on the data path.
+        from lamm_b200 import sharding
+        comm = sharding.Comm(L, dist)
+        cbufs = {m: sharding.SharedBuffer(L, dist, 4 * m) for m in (H, F, V)}
 
-    def one_token(prequantized=False):
+    def one_token(prequantized=False, gather=True):
         for (name, m, k), w in zip(ops, weights):
             rows = w.shape[0]
+            if fused and gather and not prequantized:
+                comm.mul_mat(t, w, xin[k].data_ptr(), cbufs[m], m, k)
+                continue
             if world == 1:
                 c = outs[m]
             else:
@@ -312,7 +334,7 @@ def run_cuda(args):
                 L.mul_mat_q(t, wv, xq_pre[k], k, out=c)
             else:
                 L.mul_mat(t, wv, xin[k], out=c, ws=xq_ws)
-            if world > 1:
+            if world > 1 and gather:
                 dist.all_gather_into_tensor(gather_buf[m].view(-1), gather_buf[m][rank])   # in place
 
     def capture(fn):
@@ -359,7 +381,7 @@ def run_cuda(args):
     tok_s = args.steps / (ms * 1e-3)
 
     # roofline leg: the GEMV kernel alone on pre-quantized activations (same chain, same buffers)
-    g_q, launches_q = capture(lambda: one_token(True))
+    g_q, launches_q = capture(lambda: one_token(True, gather=False))
     ms_q = timed(g_q, args.steps, 3)
     peak, peak_src = peaks()
     kern_bytes = sum(gemv_kernel_bytes(t, shard(m)[1] - shard(m)[0], k) for _, m, k in ops)
@@ -389,10 +411,11 @@ def run_cuda(args):
         "value": tok_s, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "u4/u5/i8 weights x i8 activations -> i32 (dp4a), f32 scale-accumulate",
-        "data": "synthetic", "config": workload_config(args.fmt, world),
+        "data": "synthetic", "config": workload_config(args.fmt, world, "fused" if fused else "nccl"),
         "path_gbs": path_bytes * args.steps / (ms * 1e-3) / 1e9,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "gemv_stream_kernel<%s,1>" % args.fmt,
+                     "traffic": TRAFFIC_PER_LAUNCH.get(args.fmt) if world == 1 else None,
+                     "kernel": "lamm::decode16_kernel<%s>" % args.fmt,
                      "peak_source": peak_src,
                      "how": "same chain on pre-quantized activations (GEMV launches only), CUDA events; "
                             "bytes = W blocks + Xq + C per launch, %d launches/step, avg %.2f us/launch"
@@ -604,6 +627,8 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--fmt", default="q4_1", choices=sorted(TYPE_IDS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
+                    help="N>1: how C slices reach every rank (peer-store epilogue, or ncclAllGather per matmul)")
     ap.add_argument("--suite", default=None, choices=[None, "gemv", "gemm"], help="per-format sweep instead of the bench line")
     ap.add_argument("--fmts", default=None)
     ap.add_argument("--shapes", default=None, help="MxK,MxK,...")

@@ -41,6 +41,8 @@
 extern "C" {
 #endif
 
+#define LAMMCU_MAX_RANKS 8
+
 typedef enum {
   LAMMCU_OK = 0,
   LAMMCU_ERR_NO_DEVICE = -1,   /* no CUDA device / driver                      */
@@ -112,6 +114,38 @@ int lammcu_get_decode_kernel(void);
  * CTA (start, weights issued, dependency wait done, activations staged, done) into
  * consecutive slots of dev_buf (n_u64 entries); NULL switches tracing off.          */
 int lammcu_set_trace(void *dev_buf, int64_t n_u64);
+
+/* ---- row-sharded multi-GPU decode (one process per GPU) ------------------------
+ * Weight rows (M) are split contiguously across ranks the way the reference splits
+ * them across threads (src/lamm_impl.hpp:107-112) and upstream CUDA across devices
+ * (llama.cpp-b2430/ggml-cuda.cu:8480-8492).  Every rank computes its row slice and
+ * the kernel's epilogue stores it straight into the full C vector of EVERY rank
+ * through peer-mapped memory (NVLink): there is no separate all-gather.  Completion
+ * is published with one release-store flag per (rank, peer); the next sharded launch
+ * waits on the flags before it reads its activations.
+ *
+ * lammcu_ipc_alloc / _open give peer-mappable device buffers (cudaIpc*): the owner
+ * allocates (zero-filled) and ships the 64-byte handle to the other ranks by any host
+ * channel (torch.distributed in the Python layer), who open it.                      */
+typedef struct lammcu_comm *lammcu_comm_t;
+int lammcu_ipc_alloc(size_t bytes, void **dev_ptr, void *handle64);
+int lammcu_ipc_open(const void *handle64, void **dev_ptr);
+int lammcu_ipc_close(void *dev_ptr);
+int lammcu_ipc_free(void *dev_ptr);
+/* cudaMemcpyAsync(cudaMemcpyDefault) on the given stream: moves data between caller
+ * tensors and peer-mappable buffers without another CUDA binding                     */
+int lammcu_memcpy_async(void *dst, const void *src, size_t bytes, void *stream);
+/* flag_ptrs[g]: rank g's flag array (>= LAMMCU_MAX_RANKS u32, zero-filled, from
+ * lammcu_ipc_alloc on rank g), as mapped in THIS process                              */
+int lammcu_comm_create(int rank, int world, void *const *flag_ptrs, lammcu_comm_t *out);
+int lammcu_comm_destroy(lammcu_comm_t comm);
+/* N == 1.  w_shard: this rank's rows [row_begin, row_begin + rows) of W; x: the f32
+ * activation row (local); c_all[g]: the full C vector (M floats) on rank g.  All ranks
+ * must issue the same sequence of sharded calls.                                      */
+int lammcu_mul_mat_sharded_dev(lammcu_comm_t comm, int w_type, const void *w_shard,
+                               int64_t w_stride_bytes, const float *x_dev,
+                               float *const *c_all, int64_t row_begin, int64_t rows,
+                               int64_t K, void *stream);
 
 /* ---- host operands (what lamm_mul_mat passes) --------------------------- */
 typedef struct lammcu_weight *lammcu_weight_t;

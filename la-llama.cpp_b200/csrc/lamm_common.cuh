@@ -123,8 +123,15 @@ int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int
                 float *c, int64_t ldc, int64_t M, int64_t N, int64_t K, cudaStream_t st);
 // single-launch decode (N == 1): fused activation quantize (x != NULL) or pre-quantized row (xq)
 bool decode_supported(int w_type, const void *w, int64_t w_stride, const void *x_or_xq, int64_t M, int64_t K);
+// row-sharded launch: where the results go and how completion is published (lamm_decode.cu)
+struct ShardInfo {
+  float *c_peer[LAMMCU_MAX_RANKS];
+  unsigned int *flag_peer[LAMMCU_MAX_RANKS];
+  unsigned int *my_flags, *done_ctr, *epoch_ctr;
+  int n_peer, my_rank, row_begin;
+};
 int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
-                  float *c, int64_t M, int64_t K, cudaStream_t st);
+                  float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh = nullptr);
 int launch_gemm_prep(int vt, int perm, const void *xq, int64_t xq_stride, void *x16, float *dxT, float *sxT,
                      int64_t N, int64_t Npad, int64_t K, cudaStream_t st);
 void *gemm_workspace(size_t bytes);      // library-owned scratch for the prefill GEMM (grown on demand)

@@ -44,6 +44,13 @@ struct DecodeParams {
   int slots, slot_bytes;
   int x_bytes;          // shared-memory bytes of the staged activations
   unsigned long long *trace;   // optional: 8 globaltimer stamps per CTA (lammcu_set_trace)
+  // row-sharded multi-GPU (n_peer > 0): the epilogue stores every result into the full C vector
+  // of EVERY rank over NVLink; a flag per (rank, peer) replaces the all-gather collective
+  float *c_peer[LAMMCU_MAX_RANKS];         // full C on each rank (peer-mapped)
+  unsigned int *flag_peer[LAMMCU_MAX_RANKS];   // flag array of each rank; this rank writes slot [my_rank]
+  unsigned int *my_flags;                  // this rank's flag array (slot g written by rank g)
+  unsigned int *done_ctr, *epoch_ctr;      // local: CTAs finished / sharded launches completed
+  int n_peer, my_rank, row_begin;
 };
 
 // ---- integer dots -------------------------------------------------------------------
@@ -665,6 +672,22 @@ __device__ __forceinline__ float dot_unit_sx(const uint32_t (&w)[NW], uint32_t x
   return acc;
 }
 
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int *p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned int *p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void store_c(const DecodeParams &p, int row, float v) {
+  if (p.n_peer == 0) {
+    p.c[row] = v;
+  } else {
+    for (int g = 0; g < p.n_peer; g++) p.c_peer[g][p.row_begin + row] = v;
+  }
+}
+
 template <int WT, bool XF32>
 __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const DecodeParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -713,11 +736,21 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
   }
   pdl_launch_dependents();
   pdl_wait();
+  if (p.n_peer > 0) {
+    // every rank must have finished (and published) all earlier sharded launches: their stores
+    // into this rank's buffers are this launch's activations
+    if (threadIdx.x == 0) {
+      const unsigned int want = *reinterpret_cast<volatile unsigned int *>(p.epoch_ctr);
+      for (int g = 0; g < p.n_peer; g++)
+        while ((int)(ld_acquire_sys(p.my_flags + g) - want) < 0) __nanosleep(20);
+    }
+    __syncthreads();
+  }
   trace_stamp(p.trace, 2);
   stage_x_row<VT, XF32>(p, xs);
   __syncthreads();
   trace_stamp(p.trace, 3);
-  if (!active) return;
+  if (active) {
 
   const int U = p.units, ug = u0 + lane;
   const bool lane_live = lane < seg_n;
@@ -761,7 +794,7 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
     }
     const float tot = warp_sum2(acc[0], acc[1], lane);
     if (p.KS == 1) {
-      if (lane < nb) p.c[row0 + (i0 + lane) * row_step] = tot;
+      if (lane < nb) store_c(p, row0 + (i0 + lane) * row_step, tot);
     } else {
       float *pb = part + (size_t)((rg * 2 + ph) * p.KS) * 2;
       if (lane < 2) pb[seg * 2 + lane] = tot;
@@ -769,11 +802,28 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
       if (seg == 0 && lane < nb) {
         float t = 0.f;
         for (int k = 0; k < p.KS; k++) t += pb[k * 2 + lane];
-        p.c[row0 + (i0 + lane) * row_step] = t;
+        store_c(p, row0 + (i0 + lane) * row_step, t);
       }
     }
   }
+  }   // active
   trace_stamp(p.trace, 4);
+  if (p.n_peer > 0) {
+    // publish: when the last CTA of this rank is done, bump the launch epoch and raise this
+    // rank's flag on every peer (release at system scope orders the peer stores before it)
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned int done = atomicAdd(p.done_ctr, 1u);
+      if (done == gridDim.x - 1) {
+        *p.done_ctr = 0u;
+        const unsigned int e = *reinterpret_cast<volatile unsigned int *>(p.epoch_ctr) + 1u;
+        *reinterpret_cast<volatile unsigned int *>(p.epoch_ctr) = e;
+        __threadfence_system();
+        for (int g = 0; g < p.n_peer; g++) st_release_sys(p.flag_peer[g] + p.my_rank, e);
+      }
+    }
+  }
 }
 
 // ---- host side --------------------------------------------------------------------------
@@ -886,7 +936,7 @@ bool decode_supported(int w_type, const void *w, int64_t w_stride, const void *x
 }
 
 int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
-                  float *c, int64_t M, int64_t K, cudaStream_t st) {
+                  float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh) {
   const TypeInfo ti = type_info(w_type);
   const bool q2k = (w_type == LAMMCU_TYPE_Q2_K);
   DecodeParams p = {};
@@ -904,10 +954,19 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   p.seg_units = (((p.units + p.KS - 1) / p.KS) + gran - 1) / gran * gran;
   if (p.seg_units > 32) p.seg_units = 32;
   p.KS = (p.units + p.seg_units - 1) / p.seg_units;
-  static const int variant = [] {
+  static const int variant_env = [] {
     const char *e = getenv("LAMM_DECODE_VARIANT");          // tuning knob: 8 or 16 (default) warps
     return (e && atoi(e) == 8) ? 8 : 16;
   }();
+  const int variant = sh ? 16 : variant_env;                // the peer-store epilogue lives in the 16-warp kernel
+  if (sh) {
+    for (int g = 0; g < sh->n_peer; g++) {
+      p.c_peer[g] = sh->c_peer[g];
+      p.flag_peer[g] = sh->flag_peer[g];
+    }
+    p.my_flags = sh->my_flags;  p.done_ctr = sh->done_ctr;  p.epoch_ctr = sh->epoch_ctr;
+    p.n_peer = sh->n_peer;  p.my_rank = sh->my_rank;  p.row_begin = sh->row_begin;
+  }
   int warps;
   if (variant == 16) {
     warps = (kD16Warps / p.KS) * p.KS;

@@ -279,6 +279,118 @@ int lammcu_mul_mat_dev(int w_type, const void *w, int64_t w_stride, const float 
   return lammcu_mul_mat_q_dev(w_type, w, w_stride, xq_ws, (int64_t)rs, c, ldc, M, N, K, stream);
 }
 
+// ---- row-sharded multi-GPU decode ---------------------------------------------------
+struct lammcu_comm {
+  int rank, world;
+  unsigned int *flags[LAMMCU_MAX_RANKS];      // flag array of every rank (peer-mapped)
+  unsigned int *ctrs;                          // local: [0] CTAs done, [1] launch epoch
+};
+
+int lammcu_ipc_alloc(size_t bytes, void **dev_ptr, void *handle64) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!dev_ptr || !handle64 || !bytes) { set_error("ipc_alloc: bad argument"); return LAMMCU_ERR_ARG; }
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+  void *p = nullptr;
+  CU_TRY(cudaMalloc(&p, bytes));
+  CU_TRY(cudaMemset(p, 0, bytes));
+  CU_TRY(cudaDeviceSynchronize());
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    set_error("cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  memcpy(handle64, &h, 64);
+  *dev_ptr = p;
+  return LAMMCU_OK;
+}
+
+int lammcu_ipc_open(const void *handle64, void **dev_ptr) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!dev_ptr || !handle64) { set_error("ipc_open: bad argument"); return LAMMCU_ERR_ARG; }
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  CU_TRY(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return LAMMCU_OK;
+}
+
+int lammcu_ipc_close(void *dev_ptr) {
+  CU_TRY(cudaIpcCloseMemHandle(dev_ptr));
+  return LAMMCU_OK;
+}
+
+int lammcu_ipc_free(void *dev_ptr) {
+  CU_TRY(cudaFree(dev_ptr));
+  return LAMMCU_OK;
+}
+
+int lammcu_memcpy_async(void *dst, const void *src, size_t bytes, void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, pick_stream(stream)));
+  return LAMMCU_OK;
+}
+
+int lammcu_comm_create(int rank, int world, void *const *flag_ptrs, lammcu_comm_t *out) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!out || !flag_ptrs || world < 1 || world > LAMMCU_MAX_RANKS || rank < 0 || rank >= world) {
+    set_error("comm_create: bad argument (rank %d of %d)", rank, world);
+    return LAMMCU_ERR_ARG;
+  }
+  lammcu_comm *c = new lammcu_comm();
+  c->rank = rank;
+  c->world = world;
+  for (int g = 0; g < world; g++) c->flags[g] = (unsigned int *)flag_ptrs[g];
+  cudaError_t e = cudaMalloc(&c->ctrs, 256);
+  if (e == cudaSuccess) e = cudaMemset(c->ctrs, 0, 256);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    set_error("comm_create: %s", cudaGetErrorString(e));
+    delete c;
+    return LAMMCU_ERR_CUDA;
+  }
+  *out = c;
+  return LAMMCU_OK;
+}
+
+int lammcu_comm_destroy(lammcu_comm_t c) {
+  if (!c) return LAMMCU_ERR_ARG;
+  cudaFree(c->ctrs);
+  delete c;
+  return LAMMCU_OK;
+}
+
+int lammcu_mul_mat_sharded_dev(lammcu_comm_t comm, int w_type, const void *w_shard, int64_t w_stride,
+                               const float *x, float *const *c_all, int64_t row_begin, int64_t rows, int64_t K,
+                               void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!comm || !w_shard || !x || !c_all || rows <= 0 || row_begin < 0) {
+    set_error("mul_mat_sharded: bad argument");
+    return LAMMCU_ERR_ARG;
+  }
+  if (!decode_supported(w_type, w_shard, w_stride, x, rows, K)) {
+    set_error("mul_mat_sharded: needs a quantized type, K %% 256 == 0 and 16-byte aligned operands");
+    return LAMMCU_ERR_SHAPE;
+  }
+  ShardInfo sh;
+  for (int g = 0; g < comm->world; g++) {
+    sh.c_peer[g] = c_all[g];
+    sh.flag_peer[g] = comm->flags[g];
+  }
+  sh.my_flags = comm->flags[comm->rank];
+  sh.done_ctr = comm->ctrs;
+  sh.epoch_ctr = comm->ctrs + 1;
+  sh.n_peer = comm->world;
+  sh.my_rank = comm->rank;
+  sh.row_begin = (int)row_begin;
+  return launch_decode(w_type, w_shard, w_stride, x, nullptr, nullptr, nullptr, rows, K, pick_stream(stream), &sh);
+}
+
 // ---- host operands --------------------------------------------------------------
 int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K,
                            int64_t w_stride, int64_t row_begin, int64_t row_end,

@@ -1,0 +1,68 @@
+"""Row-sharded decode across the GPUs of one box, checked against the oracle.
+Run under torchrun (one rank per GPU):  torchrun --nproc-per-node 2 tests/multi_gpu_check.py"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    import lamm_b200 as L
+    from lamm_b200 import sharding
+    from oracle_lib import Oracle, Q4_1, Q8_0, Q2_K, Q5_0
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    L.init(local)
+    comm = sharding.Comm(L, dist)
+    o = Oracle()
+    ok = True
+    for t, m, k in [(Q4_1, 4096, 4096), (Q8_0, 1000, 2048), (Q5_0, 11008, 4096), (Q2_K, 515, 11008)]:
+        rng = np.random.default_rng(7)                      # same data on every rank
+        w = o.quantize_weights(t, rng.standard_normal((m, k)).astype(np.float32), seed=3)
+        x = rng.standard_normal((1, k)).astype(np.float32)
+        want = o.mul_mat(t, w, x)
+        lo, hi = sharding.row_shard(m, rank, world)
+        wd = torch.from_numpy(w[lo:hi].copy()).cuda()
+        xd = torch.from_numpy(x).cuda()
+        cbuf = sharding.SharedBuffer(L, dist, 4 * m)
+        for it in range(3):                                 # chained launches exercise the flag protocol
+            comm.mul_mat(t, wd, xd.data_ptr(), cbuf, m, k)
+        # a follow-up sharded launch that READS the gathered vector (every rank needs all of it)
+        w2 = o.quantize_weights(Q4_1, np.random.default_rng(9).standard_normal((256, (m // 256) * 256)).astype(np.float32))
+        k2 = (m // 256) * 256
+        lo2, hi2 = sharding.row_shard(256, rank, world)
+        c2 = sharding.SharedBuffer(L, dist, 4 * 256)
+        comm.mul_mat(Q4_1, torch.from_numpy(w2[lo2:hi2].copy()).cuda(), cbuf.local, c2, 256, k2)
+        torch.cuda.synchronize()
+        dist.barrier()
+        got = cbuf.to_tensor(torch, torch.float32, m).cpu().numpy()[None, :]
+        tol = 1e-5 * np.sqrt(k) * np.abs(want).max()
+        err = np.abs(got - want).max()
+        want2 = o.mul_mat(Q4_1, w2, got[:, :k2])
+        got2 = c2.to_tensor(torch, torch.float32, 256).cpu().numpy()[None, :]
+        err2 = np.abs(got2 - want2).max()
+        tol2 = 1e-5 * np.sqrt(k2) * np.abs(want2).max()
+        good = err <= tol and err2 <= tol2
+        ok &= bool(good)
+        print(f"rank {rank} type {t} {m}x{k}: err {err:.3g} (tol {tol:.3g}), chained err {err2:.3g} (tol {tol2:.3g}) "
+              f"{'ok' if good else 'FAIL'}", flush=True)
+        dist.barrier()
+    flag = torch.tensor([0 if ok else 1], device="cuda")
+    dist.all_reduce(flag)
+    dist.barrier()
+    dist.destroy_process_group()
+    if flag.item():
+        sys.exit(1)
+    if rank == 0:
+        print("multi_gpu_check: all ok")
+
+
+if __name__ == "__main__":
+    main()
