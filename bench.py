@@ -134,26 +134,52 @@ class ClockSampler:
 
 
 # ---- synthetic quantized tensors, generated on the device -----------------------------
+# variance of the zero-mean integer a weight element takes in the unit-gain recipe below
+_QVAR = {2: 18.6667, 3: 21.25, 6: 82.6667, 7: 85.25, 8: 5461.25, 10: 97.0}
+
+
 def synth_weight(torch, t, m, k, gen, device):
-    """Random ggml blocks: uniform random quant bytes, fp16 scales/mins in U(0.001, 0.03)
-    (never NaN/Inf) -- SURVEY 8d 'alternative fast path'.  Returns uint8 [m, row_bytes]."""
+    """Random ggml blocks (SURVEY 8d 'alternative fast path': uniform random quant bytes, finite fp16
+    scales), with the scales chosen so that the matrix has ZERO-MEAN elements of variance 1/K: a chain
+    of such matmuls (each one's output is the next one's activation row) keeps |x| ~ 1 for hundreds of
+    steps instead of overflowing.  Q4_1/Q5_1: m = -7.5 d / -15.5 d; Q4_0/Q5_0: nibbles in 1..15 so
+    that q-8 / q-16 is symmetric; Q2_K: scales byte = s | s<<4 (s in 1..15), dmin = 1.5 d.
+    Returns uint8 [m, row_bytes]."""
     if t == 0:
-        return (torch.randn((m, k), generator=gen, device=device, dtype=torch.float32) * 0.02).view(torch.uint8)
+        return (torch.randn((m, k), generator=gen, device=device, dtype=torch.float32) * (k ** -0.5)).view(torch.uint8)
     kb, bs = k // BLCK[t], TSIZE[t]
     raw = torch.randint(0, 256, (m, kb, bs), generator=gen, device=device, dtype=torch.uint8)
     halves = raw.view(torch.int16)                       # [m, kb, bs/2]
+    base = (k * _QVAR[t] * 1.0208) ** -0.5
+    d = (torch.rand((m, kb), generator=gen, device=device) * 0.5 + 0.75) * base
+    d16 = d.to(torch.float16)
 
-    def scale():
-        v = torch.rand((m, kb), generator=gen, device=device) * 0.029 + 0.001
-        return v.to(torch.float16).view(torch.int16)
-    if t in (2, 6, 8):       # {d, ...}
-        halves[:, :, 0] = scale()
-    elif t in (3, 7):        # {d, m, ...}
-        halves[:, :, 0] = scale()
-        halves[:, :, 1] = scale()
-    elif t == 10:            # q2_K {scales[16], qs[64], d, dmin}
-        halves[:, :, 40] = scale()
-        halves[:, :, 41] = scale()
+    def nib_1_15(lo, hi):                                # both nibbles of every qs byte uniform in 1..15
+        shape = (m, kb, hi - lo)
+        a = torch.randint(1, 16, shape, generator=gen, device=device, dtype=torch.uint8)
+        b = torch.randint(1, 16, shape, generator=gen, device=device, dtype=torch.uint8)
+        raw[:, :, lo:hi] = a | (b << 4)
+    if t == 2:                                           # q4_0 {d, qs[16]}
+        halves[:, :, 0] = d16.view(torch.int16)
+        nib_1_15(2, 18)
+    elif t == 3:                                         # q4_1 {d, m, qs[16]}
+        halves[:, :, 0] = d16.view(torch.int16)
+        halves[:, :, 1] = (d16.float() * -7.5).to(torch.float16).view(torch.int16)
+    elif t == 6:                                         # q5_0 {d, qh[4], qs[16]}
+        halves[:, :, 0] = d16.view(torch.int16)
+        nib_1_15(6, 22)
+    elif t == 7:                                         # q5_1 {d, m, qh[4], qs[16]}
+        halves[:, :, 0] = d16.view(torch.int16)
+        halves[:, :, 1] = (d16.float() * -15.5).to(torch.float16).view(torch.int16)
+    elif t == 8:                                         # q8_0 {d, qs[32]}
+        halves[:, :, 0] = d16.view(torch.int16)
+    elif t == 10:                                        # q2_K {scales[16], qs[64], d, dmin}
+        sc = raw[:, :, 0:16]
+        lo = sc & 0x0F
+        lo = torch.where(lo == 0, torch.ones_like(lo), lo)
+        sc.copy_(lo | (lo << 4))
+        halves[:, :, 40] = d16.view(torch.int16)
+        halves[:, :, 41] = (d16.float() * 1.5).to(torch.float16).view(torch.int16)
     return raw.view(m, kb * bs)
 
 
@@ -253,13 +279,15 @@ def run_reference(args):
     return 0
 
 
-def workload_config(fmt, world, collective="fused"):
+def workload_config(fmt, world, collective="fused", ll=False):
     cfg = {"workload": "LLaMA-7B %s decode (N=1) weight-matmul chain: 32 x {4x 4096x4096, 2x 11008x4096, "
                         "1x 4096x11008} + head 32000x4096; activation quantize + quantized GEMV per matmul; "
                         "attention/norm/rope/sampling excluded (not on the path)" % fmt.upper(),
             "format": fmt, "n_tokens_per_step": 1, "matmuls_per_step": len(chain_ops()),
             "l2_defeat": "225 distinct weight buffers per step (4.13 GB for Q4_1) >> 126 MB L2",
-            "parallelism": "single GPU"}
+            "parallelism": "single GPU",
+            "activation_vectors": "LL {f32 value, u32 tag} pairs, consumer polls tags (no kernel-boundary wait)" if ll
+                                  else "plain f32 (ggml layout)"}
     if world > 1:
         cfg["parallelism"] = ("row-sharded M/%d per rank; C replicated on every rank by %s" % (
             world, "the decode kernel's NVLink peer-store epilogue + system-scope flags (no collective call)"
@@ -303,39 +331,53 @@ def run_cuda(args):
     for name, m, k in ops:
         lo, hi = shard(m)
         weights.append(synth_weight(torch, t, hi - lo, k, gen, dev))
-    xin = {H: torch.randn((1, H), generator=gen, device=dev), F: torch.randn((1, F), generator=gen, device=dev)}
-    outs = {m: torch.zeros((1, m), device=dev) for m in (H, F, V)}
+    x0 = torch.randn((1, H), generator=gen, device=dev)          # the token's input row (layer 0)
     act_blck, act_size = ACT_SIZE[vt]
     xq_ws = torch.zeros(((F // act_blck) * act_size + 64,), dtype=torch.uint8, device=dev)
-    xq_pre = {k: (L.quantize_act(xin[k], vt) if t != 0 else xin[k]) for k in (H, F)}
-    gather_buf = {m: torch.zeros((world, (m + world - 1) // world), device=dev) for m in (H, F, V)} if world > 1 else None
-    fused = world > 1 and args.collective == "fused" and t != 0
-    comm = cbufs = None
+    fused = ((world > 1 and args.collective == "fused") or args.chain == "ll") and t != 0
+    for m in (H, F, V):
+        assert m % world == 0, "row shards must be equal for the in-place all-gather"
+
+    # activation / output vectors of the chain.  The chain is DATA DEPENDENT, as in the model:
+    #   q,k,v = W{q,k,v} x;  o = Wo v;  g = Wgate o;  u = Wup o;  x' = Wdown u;  logits = Whead x_last
+    # (attention / SiLU.mul / norm are not on the path, so v and u stand in for their results).
+    comm = None
     if fused:
-        # peer-store epilogue (SURVEY 8e "preferred"): every rank's decode kernel writes its rows of C
-        # straight into the full C vector of every rank over NVLink and raises a system-scope flag;
-        # the next launch waits on the flags.  No collective call on the data path.
+        # peer-store epilogue (SURVEY 8e "preferred"): every rank's decode kernel writes its rows of C as
+        # {value, tag} pairs straight into the full vector of every rank over NVLink; the consumer launch
+        # polls the tags.  No collective call, fence or flag on the data path.
         from lamm_b200 import sharding
         comm = sharding.Comm(L, dist)
-        cbufs = {m: sharding.SharedBuffer(L, dist, 4 * m) for m in (H, F, V)}
+        mk = comm.vector
+    else:
+        mk = lambda m: torch.zeros((1, m), device=dev)
+    buf = {"x0": mk(H), "x1": mk(H), "q": mk(H), "k": mk(H), "v": mk(H), "o": mk(H), "g": mk(F), "u": mk(F),
+           "logits": mk(V)}
+    plan = []                                   # (weight index, M, K, input key or None for x0 tensor, output key)
+    wi = 0
+    for layer in range(LAYERS):
+        xin_key = None if layer == 0 else "x%d" % (layer % 2)
+        xout_key = "x%d" % ((layer + 1) % 2)
+        for name, src, dst in (("wq", xin_key, "q"), ("wk", xin_key, "k"), ("wv", xin_key, "v"), ("wo", "v", "o"),
+                               ("gate", "o", "g"), ("up", "o", "u"), ("down", "u", xout_key)):
+            _, m, k = ops[wi]
+            plan.append((wi, m, k, src, dst))
+            wi += 1
+    plan.append((wi, V, H, "x%d" % (LAYERS % 2), "logits"))
 
-    def one_token(prequantized=False, gather=True):
-        for (name, m, k), w in zip(ops, weights):
+    def one_token():
+        for wi, m, k, src, dst in plan:
+            w = weights[wi]
             rows = w.shape[0]
-            if fused and gather and not prequantized:
-                comm.mul_mat(t, w, xin[k].data_ptr(), cbufs[m], m, k)
+            xin = x0 if src is None else buf[src]
+            if fused:
+                comm.mul_mat(t, w, xin, buf[dst], m, k)
                 continue
-            if world == 1:
-                c = outs[m]
-            else:
-                c = gather_buf[m][rank:rank + 1, :rows]
             wv = w if t != 0 else w.view(torch.float32)
-            if prequantized:
-                L.mul_mat_q(t, wv, xq_pre[k], k, out=c)
-            else:
-                L.mul_mat(t, wv, xin[k], out=c, ws=xq_ws)
-            if world > 1 and gather:
-                dist.all_gather_into_tensor(gather_buf[m].view(-1), gather_buf[m][rank])   # in place
+            lo = rank * rows
+            L.mul_mat(t, wv, xin, out=buf[dst][:, lo:lo + rows])
+            if world > 1:
+                dist.all_gather_into_tensor(buf[dst].view(-1), buf[dst][0, lo:lo + rows])   # in place
 
     def capture(fn):
         s = torch.cuda.Stream()
@@ -372,30 +414,37 @@ def run_cuda(args):
             ms = float(tt.item())
         return ms
 
-    g_full, launches_per_token = capture(lambda: one_token(False))
+    g_full, launches_per_token = capture(one_token)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     ms = timed(g_full, args.steps, max(args.warmup, 3))
     clocks = sampler.stop() if rank == 0 else None
     tok_s = args.steps / (ms * 1e-3)
+    # the chain's final output must be finite (unit-gain weights) and, with N>1, no poll may have timed out
+    logits = comm.unpack(torch, buf["logits"]) if fused else buf["logits"].view(-1)
+    torch.cuda.synchronize()
+    if not bool(torch.isfinite(logits).all().item()):
+        raise SystemExit("bench: non-finite logits at the end of the chain")
+    if fused and comm.timed_out():
+        raise SystemExit("bench: a peer poll timed out")
+    logit_rms = float(logits.float().pow(2).mean().sqrt().item())
 
-    # roofline leg: the GEMV kernel alone on pre-quantized activations (same chain, same buffers)
-    g_q, launches_q = capture(lambda: one_token(True, gather=False))
-    ms_q = timed(g_q, args.steps, 3)
+    # roofline of the dominant kernel (decode16_kernel, the ONLY kernel of the step at N=1): the
+    # algorithmic bytes of this rank's launches (W blocks + f32 X + f32 C) over the average
+    # launch duration measured above with CUDA events
     peak, peak_src = peaks()
-    kern_bytes = sum(gemv_kernel_bytes(t, shard(m)[1] - shard(m)[0], k) for _, m, k in ops)
-    achieved = kern_bytes * args.steps / (ms_q * 1e-3) / 1e9
+    kern_bytes = sum(gemv_bytes(t, shard(m)[1] - shard(m)[0], k) for _, m, k in ops)
+    achieved = kern_bytes * args.steps / (ms * 1e-3) / 1e9
     path_bytes = sum(gemv_bytes(t, m, k) for _, m, k in ops)
+    launches_q = launches_per_token
 
     # e2e leg: the drop-in operator on HOST buffers (rank 0 / N=1 only does the H2D/D2H variant;
     # with N>1 every rank runs it on its shard)
     e2e = e2e_run(torch, L, t, ops, weights, shard, max(3, args.steps // 10), dist, dev, rank, world)
 
     if rank != 0:
-        if dist:
-            dist.destroy_process_group()
-        return 0
+        return finish(dist)
 
     cpu = None
     if world == 1 and not args.no_cpu:
@@ -411,23 +460,34 @@ def run_cuda(args):
         "value": tok_s, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "u4/u5/i8 weights x i8 activations -> i32 (dp4a), f32 scale-accumulate",
-        "data": "synthetic", "config": workload_config(args.fmt, world, "fused" if fused else "nccl"),
+        "data": "synthetic", "config": workload_config(args.fmt, world, "fused" if fused else "nccl", fused),
         "path_gbs": path_bytes * args.steps / (ms * 1e-3) / 1e9,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": TRAFFIC_PER_LAUNCH.get(args.fmt) if world == 1 else None,
                      "kernel": "lamm::decode16_kernel<%s>" % args.fmt,
                      "peak_source": peak_src,
-                     "how": "same chain on pre-quantized activations (GEMV launches only), CUDA events; "
-                            "bytes = W blocks + Xq + C per launch, %d launches/step, avg %.2f us/launch"
-                            % (launches_q, ms_q * 1e3 / args.steps / max(launches_q, 1))},
+                     "how": "the timed chain itself (every launch of the step is this kernel, activation quantize "
+                            "fused), CUDA events; bytes = W blocks + f32 X + f32 C per launch; %d launches/step, "
+                            "avg %.2f us and %.2f MB per launch"
+                            % (launches_q, ms * 1e3 / args.steps / max(launches_q, 1),
+                               kern_bytes / max(launches_q, 1) / 1e6)},
         "cpu_baseline": cpu,
         "e2e": e2e,
-        "gpu_launches": launches_per_token * args.steps,
+        "gpu_launches": launches_per_token * args.steps, "logits_rms": logit_rms,
         "clocks": clocks,
     }
     print(json.dumps(line))
+    return finish(dist)
+
+
+def finish(dist):
+    """Leave without tearing NCCL down: captured graphs still reference the communicator and
+    destroy_process_group() can block on them; every rank has already passed the last barrier."""
+    sys.stdout.flush()
+    sys.stderr.flush()
     if dist:
-        dist.destroy_process_group()
+        dist.barrier()
+        os._exit(0)
     return 0
 
 
@@ -627,6 +687,9 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--fmt", default="q4_1", choices=sorted(TYPE_IDS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--chain", default="plain", choices=["plain", "ll"],
+                    help="N=1: activation vectors between matmuls as plain f32 (ggml layout, kernel boundary = "
+                         "dependency) or as LL {value, tag} vectors (dependency carried by the data)")
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
                     help="N>1: how C slices reach every rank (peer-store epilogue, or ncclAllGather per matmul)")
     ap.add_argument("--suite", default=None, choices=[None, "gemv", "gemm"], help="per-format sweep instead of the bench line")

@@ -119,10 +119,26 @@ int lammcu_set_trace(void *dev_buf, int64_t n_u64);
  * Weight rows (M) are split contiguously across ranks the way the reference splits
  * them across threads (src/lamm_impl.hpp:107-112) and upstream CUDA across devices
  * (llama.cpp-b2430/ggml-cuda.cu:8480-8492).  Every rank computes its row slice and
- * the kernel's epilogue stores it straight into the full C vector of EVERY rank
- * through peer-mapped memory (NVLink): there is no separate all-gather.  Completion
- * is published with one release-store flag per (rank, peer); the next sharded launch
- * waits on the flags before it reads its activations.
+ * the kernel's epilogue stores it straight into the full output vector of EVERY rank
+ * through peer-mapped memory (NVLink): there is no separate all-gather and no
+ * collective call.
+ *
+ * Output vectors of sharded launches are in "LL" format so that no fence, flag or
+ * kernel boundary is needed: M pairs {f32 value, u32 tag}, each pair written with ONE
+ * 64-bit store.  The tag is the launch's sequence number on the communicator, drawn on
+ * the device from an arrival-ticket counter (all ranks must issue the same sequence of
+ * sharded calls; every sharded launch uses the same grid size).  A consumer -- a later
+ * sharded launch with x_back >= 1, or lammcu_ll_unpack_dev -- polls each pair until its
+ * tag equals (own sequence number - x_back), so an element is usable the moment it
+ * lands and the consumer does not wait for the producer GRID to complete (it never
+ * executes griddepcontrol.wait): the dependency is carried by the data itself.
+ * x_back is how many sharded launches ago (on this communicator, in issue order) the
+ * vector was produced: 1 = by the previous sharded launch.  Producer and consumer must
+ * be issued in the same eager sequence or captured into the same CUDA graph.
+ * Buffer reuse: a vector may be overwritten by a sharded launch once an earlier-issued
+ * sharded launch has consumed output produced AFTER the vector's last reader (two
+ * vectors per role, ping-pong, always satisfy this in a layer chain).
+ * A poll gives up after ~2 s (lost peer) and sets the communicator's status word.
  *
  * lammcu_ipc_alloc / _open give peer-mappable device buffers (cudaIpc*): the owner
  * allocates (zero-filled) and ships the 64-byte handle to the other ranks by any host
@@ -135,17 +151,28 @@ int lammcu_ipc_free(void *dev_ptr);
 /* cudaMemcpyAsync(cudaMemcpyDefault) on the given stream: moves data between caller
  * tensors and peer-mappable buffers without another CUDA binding                     */
 int lammcu_memcpy_async(void *dst, const void *src, size_t bytes, void *stream);
-/* flag_ptrs[g]: rank g's flag array (>= LAMMCU_MAX_RANKS u32, zero-filled, from
- * lammcu_ipc_alloc on rank g), as mapped in THIS process                              */
-int lammcu_comm_create(int rank, int world, void *const *flag_ptrs, lammcu_comm_t *out);
+int lammcu_comm_create(int rank, int world, lammcu_comm_t *out);
 int lammcu_comm_destroy(lammcu_comm_t comm);
-/* N == 1.  w_shard: this rank's rows [row_begin, row_begin + rows) of W; x: the f32
- * activation row (local); c_all[g]: the full C vector (M floats) on rank g.  All ranks
- * must issue the same sequence of sharded calls.                                      */
+/* *timed_out = 1 if any poll on this communicator gave up (synchronous D2H read)    */
+int lammcu_comm_status(lammcu_comm_t comm, int *timed_out);
+/* bytes of an LL vector of M elements (8 per element); allocate with lammcu_ipc_alloc
+ * (zero-filled: tag 0 is never used)                                                  */
+size_t lammcu_ll_bytes(int64_t M);
+/* N == 1.  w_shard: this rank's rows [row_begin, row_begin + rows) of W.  x: the
+ * activation row on THIS rank -- K plain f32 (x_back = 0; the launch then waits for the
+ * previous kernel in the stream as usual) or an LL vector (x_back >= 1, see above).
+ * c_ll_all[g]: the output LL vector (M elements) on rank g as mapped in this process.
+ * world == 1 is allowed (a single GPU chaining its own launches through LL vectors).
+ * Asynchronous on `stream`.                                                           */
 int lammcu_mul_mat_sharded_dev(lammcu_comm_t comm, int w_type, const void *w_shard,
-                               int64_t w_stride_bytes, const float *x_dev,
-                               float *const *c_all, int64_t row_begin, int64_t rows,
+                               int64_t w_stride_bytes, const void *x, int x_back,
+                               void *const *c_ll_all, int64_t row_begin, int64_t rows,
                                int64_t K, void *stream);
+/* LL vector (local, produced `back` sharded launches ago, >= 1) -> plain f32 out[M],
+ * waiting for every element.  An ordinary kernel: it starts after all earlier work on
+ * the stream has completed.                                                           */
+int lammcu_ll_unpack_dev(lammcu_comm_t comm, const void *c_ll, int back, float *out,
+                         int64_t M, void *stream);
 
 /* ---- host operands (what lamm_mul_mat passes) --------------------------- */
 typedef struct lammcu_weight *lammcu_weight_t;

@@ -125,9 +125,10 @@ int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int
 bool decode_supported(int w_type, const void *w, int64_t w_stride, const void *x_or_xq, int64_t M, int64_t K);
 // row-sharded launch: where the results go and how completion is published (lamm_decode.cu)
 struct ShardInfo {
-  float *c_peer[LAMMCU_MAX_RANKS];
-  unsigned int *flag_peer[LAMMCU_MAX_RANKS];
-  unsigned int *my_flags, *done_ctr, *epoch_ctr;
+  unsigned long long *ll_peer[LAMMCU_MAX_RANKS];   // LL pairs of the output vector on every rank
+  const unsigned long long *x_ll;                  // activation row in LL format (or NULL: plain f32 x)
+  int x_back;                                      // ... produced this many sharded launches ago
+  unsigned int *arrive_ctr, *status;
   int n_peer, my_rank, row_begin;
 };
 int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,

@@ -44,12 +44,16 @@ struct DecodeParams {
   int slots, slot_bytes;
   int x_bytes;          // shared-memory bytes of the staged activations
   unsigned long long *trace;   // optional: 8 globaltimer stamps per CTA (lammcu_set_trace)
-  // row-sharded multi-GPU (n_peer > 0): the epilogue stores every result into the full C vector
-  // of EVERY rank over NVLink; a flag per (rank, peer) replaces the all-gather collective
-  float *c_peer[LAMMCU_MAX_RANKS];         // full C on each rank (peer-mapped)
-  unsigned int *flag_peer[LAMMCU_MAX_RANKS];   // flag array of each rank; this rank writes slot [my_rank]
-  unsigned int *my_flags;                  // this rank's flag array (slot g written by rank g)
-  unsigned int *done_ctr, *epoch_ctr;      // local: CTAs finished / sharded launches completed
+  // row-sharded multi-GPU (n_peer > 0): the epilogue stores every result as a {value, tag} pair
+  // (one 64-bit store, "LL" format) into the full C vector of EVERY rank over NVLink.  The tag is
+  // this launch's sequence number; a consumer polls the pairs of its activation row until every
+  // tag matches, so data and "ready" arrive in one NVLink transaction: no fence, no flag, no
+  // collective.  (See lammcu.h "row-sharded multi-GPU decode" for the buffer layout.)
+  unsigned long long *ll_peer[LAMMCU_MAX_RANKS];   // LL pairs of the full C on each rank (peer-mapped)
+  const unsigned long long *x_ll;          // XM == 2: activation row as LL pairs (a previous output)
+  unsigned int *arrive_ctr;                // local: CTA arrival tickets of all sharded launches
+  unsigned int *status;                    // local: [0] set to 1 if a poll timed out
+  int x_back;                              // XM == 2: x was produced x_back sharded launches ago (>= 1)
   int n_peer, my_rank, row_begin;
 };
 
@@ -200,8 +204,48 @@ __device__ __forceinline__ float block_dot8(const uint32_t (&w)[NW], const uint3
 //   xqs : uint4 [8][U]   slot j of unit u = quant words 4j..4j+3 of the unit (32 words)
 //   xbs : uint4 [U]      8 x int16 bsums of the unit
 //   xd  : float [kb]
-template <int VT, bool XF32>
-__device__ __forceinline__ void stage_x_row(const DecodeParams &p, uint8_t *xs) {
+// 8 consecutive activations starting at element e.  XM == 1: plain f32.  XM == 2: LL pairs written
+// by the peer-store epilogues of all ranks; spins until all 8 tags equal `tag` (bounded: ~2 s,
+// then status[0] = 1 and whatever is there is used, so a lost peer cannot hang the GPU).
+__device__ __forceinline__ void ld_ll2(const unsigned long long *p, unsigned long long &a, unsigned long long &b) {
+  asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+template <int XM>
+__device__ __forceinline__ void load_x8(const DecodeParams &p, size_t e, unsigned int tag, float4 &a, float4 &b) {
+  if constexpr (XM == 2) {
+    const unsigned long long *lp = p.x_ll + e;
+    unsigned long long v[8];
+    unsigned int spins = 0;
+    unsigned long long t0 = 0;
+    while (true) {
+#pragma unroll
+      for (int i = 0; i < 4; i++) ld_ll2(lp + 2 * i, v[2 * i], v[2 * i + 1]);
+      bool ok = true;
+#pragma unroll
+      for (int i = 0; i < 8; i++) ok &= ((unsigned int)(v[i] >> 32) == tag);
+      if (ok) break;
+      __nanosleep(100);          // a spinning warp would steal issue slots from the producer on this SM
+      if ((++spins & 1023u) == 0) {
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > 2000000000ull) { *p.status = 1u; break; }
+      }
+    }
+    a = make_float4(__uint_as_float((unsigned int)v[0]), __uint_as_float((unsigned int)v[1]),
+                    __uint_as_float((unsigned int)v[2]), __uint_as_float((unsigned int)v[3]));
+    b = make_float4(__uint_as_float((unsigned int)v[4]), __uint_as_float((unsigned int)v[5]),
+                    __uint_as_float((unsigned int)v[6]), __uint_as_float((unsigned int)v[7]));
+  } else {
+    const float4 *xp = reinterpret_cast<const float4 *>(p.x + e);
+    a = xp[0];
+    b = xp[1];
+  }
+}
+
+template <int VT, int XM>
+__device__ __forceinline__ void stage_x_row(const DecodeParams &p, uint8_t *xs, unsigned int tag = 0u) {
+  constexpr bool XF32 = (XM != 0);
   const int tid = threadIdx.x, lane = tid & 31;
   const int U = p.units;
   uint32_t *xqs = reinterpret_cast<uint32_t *>(xs);
@@ -214,8 +258,8 @@ __device__ __forceinline__ void stage_x_row(const DecodeParams &p, uint8_t *xs) 
       float d;
       int pair_sum;
       if constexpr (XF32) {
-        const float4 *xp = reinterpret_cast<const float4 *>(p.x + (size_t)sb * 256 + lane * 8);
-        const float4 a = xp[0], b = xp[1];
+        float4 a, b;
+        load_x8<XM>(p, (size_t)sb * 256 + lane * 8, tag, a, b);
         const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
         quant256_lane8(v, lane, q_lo, q_hi, d, pair_sum);
         if (store) {
@@ -257,11 +301,7 @@ __device__ __forceinline__ void stage_x_row(const DecodeParams &p, uint8_t *xs) 
         for (int h = 0; h < 2; h++) {
           const int b = b0 + h * per_pass + (tid >> 2);
           va[h] = vb[h] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (b < p.kb) {
-            const float4 *xp = reinterpret_cast<const float4 *>(p.x + (size_t)b * 32 + l4 * 8);
-            va[h] = xp[0];
-            vb[h] = xp[1];
-          }
+          if (b < p.kb) load_x8<XM>(p, (size_t)b * 32 + l4 * 8, tag, va[h], vb[h]);
         }
 #pragma unroll
         for (int h = 0; h < 2; h++) {
@@ -513,7 +553,7 @@ __global__ void __launch_bounds__(MAXT, 2) decode_kernel(const DecodeParams p) {
   pdl_launch_dependents();
   pdl_wait();                                                    // activations are valid from here on
   trace_stamp(p.trace, 2);
-  stage_x_row<VT, XF32>(p, xs);
+  stage_x_row<VT, XF32 ? 1 : 0>(p, xs);
   __syncthreads();
   trace_stamp(p.trace, 3);
   if (!active) return;
@@ -672,23 +712,17 @@ __device__ __forceinline__ float dot_unit_sx(const uint32_t (&w)[NW], uint32_t x
   return acc;
 }
 
-__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int *p) {
-  unsigned int v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys(unsigned int *p, unsigned int v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ void store_c(const DecodeParams &p, int row, float v) {
+__device__ __forceinline__ void store_c(const DecodeParams &p, int row, float v, unsigned int tag) {
   if (p.n_peer == 0) {
     p.c[row] = v;
   } else {
-    for (int g = 0; g < p.n_peer; g++) p.c_peer[g][p.row_begin + row] = v;
+    const unsigned long long pair = ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
+    for (int g = 0; g < p.n_peer; g++)
+      asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p.ll_peer[g] + p.row_begin + row), "l"(pair) : "memory");
   }
 }
 
-template <int WT, bool XF32>
+template <int WT, int XM>
 __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const DecodeParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr bool kQ2K = (WT == LAMMCU_TYPE_Q2_K);
@@ -734,20 +768,53 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
     for (int s = 0; s < S; s++)
       if (s < n_rows) issue(s, s, pol);
   }
-  pdl_launch_dependents();
-  pdl_wait();
+  unsigned int tag = 0u, x_tag = 0u;
   if (p.n_peer > 0) {
-    // every rank must have finished (and published) all earlier sharded launches: their stores
-    // into this rank's buffers are this launch's activations
-    if (threadIdx.x == 0) {
-      const unsigned int want = *reinterpret_cast<volatile unsigned int *>(p.epoch_ctr);
-      for (int g = 0; g < p.n_peer; g++)
-        while ((int)(ld_acquire_sys(p.my_flags + g) - want) < 0) __nanosleep(20);
-    }
+    // This launch's tag = its sequence number on the communicator, from an arrival ticket: every CTA of
+    // every sharded launch (all have gridDim.x == p.grid_fixed) adds 1 to a rank-local counter BEFORE it
+    // lets the next launch start, so when a CTA of this launch draws its ticket all CTAs of all earlier
+    // launches have drawn theirs: ticket / grid = number of earlier launches.  No dependence on the
+    // previous grid's COMPLETION, so a launch whose activations are an LL vector never executes
+    // griddepcontrol.wait: its inputs are validated element by element through their tags.
+    volatile unsigned int *tag_s = reinterpret_cast<volatile unsigned int *>(smem + kDecCtrl - 16);
+    if (threadIdx.x == 0) *tag_s = atomicAdd(p.arrive_ctr, 1u) / gridDim.x + 1u;
     __syncthreads();
+    tag = *tag_s;
+    x_tag = tag - (unsigned int)p.x_back;
+    pdl_launch_dependents();
+    if constexpr (XM != 2) pdl_wait();
+    if ((int)blockIdx.x >= p.M) return;              // padding CTA (the grid is fixed): owns no row
+    if constexpr (XM == 2) {
+      // Sleep until the activations are (nearly) there: lane g of warp 0 watches the LAST element of
+      // rank g's slice of x with a back-off while every other warp is parked at the barrier (no issue
+      // slots, no L2 traffic against the producer that shares this SM).  This is only a wake-up hint:
+      // stage_x_row still validates every element's tag.
+      if (warp == 0 && lane < p.n_peer) {
+        const int K = p.kb * type_info(WT).blck;
+        const int per = (K + p.n_peer - 1) / p.n_peer;
+        const unsigned long long *sp = p.x_ll + (min(K, (lane + 1) * per) - 1);
+        unsigned long long v, t0 = 0;
+        unsigned int spins = 0;
+        while (true) {
+          asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(sp) : "memory");
+          if ((unsigned int)(v >> 32) == x_tag) break;
+          __nanosleep(40);
+          if ((++spins & 1023u) == 0) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 2000000000ull) break;      // stage_x_row reports the timeout
+          }
+        }
+      }
+      __syncthreads();
+    }
+  } else {
+    pdl_launch_dependents();
+    pdl_wait();
   }
   trace_stamp(p.trace, 2);
-  stage_x_row<VT, XF32>(p, xs);
+  stage_x_row<VT, XM>(p, xs, x_tag);
   __syncthreads();
   trace_stamp(p.trace, 3);
   if (active) {
@@ -794,7 +861,7 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
     }
     const float tot = warp_sum2(acc[0], acc[1], lane);
     if (p.KS == 1) {
-      if (lane < nb) store_c(p, row0 + (i0 + lane) * row_step, tot);
+      if (lane < nb) store_c(p, row0 + (i0 + lane) * row_step, tot, tag);
     } else {
       float *pb = part + (size_t)((rg * 2 + ph) * p.KS) * 2;
       if (lane < 2) pb[seg * 2 + lane] = tot;
@@ -802,28 +869,12 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
       if (seg == 0 && lane < nb) {
         float t = 0.f;
         for (int k = 0; k < p.KS; k++) t += pb[k * 2 + lane];
-        store_c(p, row0 + (i0 + lane) * row_step, t);
+        store_c(p, row0 + (i0 + lane) * row_step, t, tag);
       }
     }
   }
   }   // active
   trace_stamp(p.trace, 4);
-  if (p.n_peer > 0) {
-    // publish: when the last CTA of this rank is done, bump the launch epoch and raise this
-    // rank's flag on every peer (release at system scope orders the peer stores before it)
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      const unsigned int done = atomicAdd(p.done_ctr, 1u);
-      if (done == gridDim.x - 1) {
-        *p.done_ctr = 0u;
-        const unsigned int e = *reinterpret_cast<volatile unsigned int *>(p.epoch_ctr) + 1u;
-        *reinterpret_cast<volatile unsigned int *>(p.epoch_ctr) = e;
-        __threadfence_system();
-        for (int g = 0; g < p.n_peer; g++) st_release_sys(p.flag_peer[g] + p.my_rank, e);
-      }
-    }
-  }
 }
 
 // ---- host side --------------------------------------------------------------------------
@@ -867,7 +918,7 @@ static int launch_decode_t(const DecodeParams &p, int grid, int threads, int sme
   return launch_decode_tt<WT, XF32, kDecMaxThreads>(p, grid, threads, smem, st);
 }
 
-template <int WT, bool XF32>
+template <int WT, int XF32>
 static int launch_decode16_t(const DecodeParams &p, int grid, int threads, int smem, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
@@ -898,7 +949,7 @@ static int launch_decode16_t(const DecodeParams &p, int grid, int threads, int s
   return LAMMCU_OK;
 }
 
-template <bool XF32>
+template <int XF32>
 static int launch_decode16_x(int w_type, const DecodeParams &p, int grid, int threads, int smem, cudaStream_t st) {
   switch (w_type) {
   case LAMMCU_TYPE_Q4_0: return launch_decode16_t<LAMMCU_TYPE_Q4_0, XF32>(p, grid, threads, smem, st);
@@ -959,13 +1010,12 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
     return (e && atoi(e) == 8) ? 8 : 16;
   }();
   const int variant = sh ? 16 : variant_env;                // the peer-store epilogue lives in the 16-warp kernel
+  int xm = x ? 1 : 0;
   if (sh) {
-    for (int g = 0; g < sh->n_peer; g++) {
-      p.c_peer[g] = sh->c_peer[g];
-      p.flag_peer[g] = sh->flag_peer[g];
-    }
-    p.my_flags = sh->my_flags;  p.done_ctr = sh->done_ctr;  p.epoch_ctr = sh->epoch_ctr;
+    for (int g = 0; g < sh->n_peer; g++) p.ll_peer[g] = sh->ll_peer[g];
+    p.arrive_ctr = sh->arrive_ctr;  p.status = sh->status;
     p.n_peer = sh->n_peer;  p.my_rank = sh->my_rank;  p.row_begin = sh->row_begin;
+    if (sh->x_ll) { p.x_ll = sh->x_ll;  p.x_back = sh->x_back;  xm = 2; }
   }
   int warps;
   if (variant == 16) {
@@ -992,10 +1042,13 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   int grid = sm_count_cached() * per_sm;
   const int64_t need = (M + p.RG - 1) / p.RG;
   if (grid > need) grid = (int)need;
+  if (sh) grid = sm_count_cached();                // fixed grid: the arrival-ticket tag divides by it
   p.trace = next_trace_slot(grid);
-  if (variant == 16)
-    return x ? launch_decode16_x<true>(w_type, p, grid, warps * 32, smem, st)
-             : launch_decode16_x<false>(w_type, p, grid, warps * 32, smem, st);
+  if (variant == 16) {
+    if (xm == 2) return launch_decode16_x<2>(w_type, p, grid, warps * 32, smem, st);
+    return xm ? launch_decode16_x<1>(w_type, p, grid, warps * 32, smem, st)
+              : launch_decode16_x<0>(w_type, p, grid, warps * 32, smem, st);
+  }
   return x ? launch_decode_x<true>(w_type, p, grid, warps * 32, smem, st)
            : launch_decode_x<false>(w_type, p, grid, warps * 32, smem, st);
 }

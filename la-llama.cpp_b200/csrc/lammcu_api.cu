@@ -4,6 +4,7 @@
 // exported signatures.  There is no CPU fallback: without a device every
 // compute entry point returns LAMMCU_ERR_NO_DEVICE.
 #include "lamm_common.cuh"
+#include <algorithm>
 
 #include <cstdarg>
 #include <cstdio>
@@ -282,8 +283,7 @@ int lammcu_mul_mat_dev(int w_type, const void *w, int64_t w_stride, const float 
 // ---- row-sharded multi-GPU decode ---------------------------------------------------
 struct lammcu_comm {
   int rank, world;
-  unsigned int *flags[LAMMCU_MAX_RANKS];      // flag array of every rank (peer-mapped)
-  unsigned int *ctrs;                          // local: [0] CTAs done, [1] launch epoch
+  unsigned int *ctrs;                          // local: [0] CTA arrival tickets, [2] status
 };
 
 int lammcu_ipc_alloc(size_t bytes, void **dev_ptr, void *handle64) {
@@ -334,17 +334,16 @@ int lammcu_memcpy_async(void *dst, const void *src, size_t bytes, void *stream) 
   return LAMMCU_OK;
 }
 
-int lammcu_comm_create(int rank, int world, void *const *flag_ptrs, lammcu_comm_t *out) {
+int lammcu_comm_create(int rank, int world, lammcu_comm_t *out) {
   int rc = ensure_init();
   if (rc) return rc;
-  if (!out || !flag_ptrs || world < 1 || world > LAMMCU_MAX_RANKS || rank < 0 || rank >= world) {
+  if (!out || world < 1 || world > LAMMCU_MAX_RANKS || rank < 0 || rank >= world) {
     set_error("comm_create: bad argument (rank %d of %d)", rank, world);
     return LAMMCU_ERR_ARG;
   }
   lammcu_comm *c = new lammcu_comm();
   c->rank = rank;
   c->world = world;
-  for (int g = 0; g < world; g++) c->flags[g] = (unsigned int *)flag_ptrs[g];
   cudaError_t e = cudaMalloc(&c->ctrs, 256);
   if (e == cudaSuccess) e = cudaMemset(c->ctrs, 0, 256);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -364,12 +363,22 @@ int lammcu_comm_destroy(lammcu_comm_t c) {
   return LAMMCU_OK;
 }
 
+int lammcu_comm_status(lammcu_comm_t c, int *timed_out) {
+  if (!c || !timed_out) return LAMMCU_ERR_ARG;
+  unsigned int v = 0;
+  CU_TRY(cudaMemcpy(&v, c->ctrs + 2, sizeof(v), cudaMemcpyDeviceToHost));
+  *timed_out = (int)v;
+  return LAMMCU_OK;
+}
+
+size_t lammcu_ll_bytes(int64_t M) { return (size_t)M * 8; }
+
 int lammcu_mul_mat_sharded_dev(lammcu_comm_t comm, int w_type, const void *w_shard, int64_t w_stride,
-                               const float *x, float *const *c_all, int64_t row_begin, int64_t rows, int64_t K,
-                               void *stream) {
+                               const void *x, int x_back, void *const *c_ll_all, int64_t row_begin,
+                               int64_t rows, int64_t K, void *stream) {
   int rc = ensure_init();
   if (rc) return rc;
-  if (!comm || !w_shard || !x || !c_all || rows <= 0 || row_begin < 0) {
+  if (!comm || !w_shard || !x || !c_ll_all || rows <= 0 || row_begin < 0 || x_back < 0) {
     set_error("mul_mat_sharded: bad argument");
     return LAMMCU_ERR_ARG;
   }
@@ -377,18 +386,58 @@ int lammcu_mul_mat_sharded_dev(lammcu_comm_t comm, int w_type, const void *w_sha
     set_error("mul_mat_sharded: needs a quantized type, K %% 256 == 0 and 16-byte aligned operands");
     return LAMMCU_ERR_SHAPE;
   }
-  ShardInfo sh;
+  ShardInfo sh = {};
   for (int g = 0; g < comm->world; g++) {
-    sh.c_peer[g] = c_all[g];
-    sh.flag_peer[g] = comm->flags[g];
+    if (!c_ll_all[g] || ((uintptr_t)c_ll_all[g] & 15)) { set_error("mul_mat_sharded: output %d NULL or misaligned", g); return LAMMCU_ERR_ALIGN; }
+    sh.ll_peer[g] = (unsigned long long *)c_ll_all[g];
   }
-  sh.my_flags = comm->flags[comm->rank];
-  sh.done_ctr = comm->ctrs;
-  sh.epoch_ctr = comm->ctrs + 1;
+  if (x_back > 0) {
+    sh.x_ll = (const unsigned long long *)x;
+    sh.x_back = x_back;
+  }
+  sh.arrive_ctr = comm->ctrs;
+  sh.status = comm->ctrs + 2;
   sh.n_peer = comm->world;
   sh.my_rank = comm->rank;
   sh.row_begin = (int)row_begin;
-  return launch_decode(w_type, w_shard, w_stride, x, nullptr, nullptr, nullptr, rows, K, pick_stream(stream), &sh);
+  return launch_decode(w_type, w_shard, w_stride, (const float *)x, nullptr, nullptr, nullptr, rows, K,
+                       pick_stream(stream), &sh);
+}
+
+// LL vector -> plain f32 (waits for every element's tag): the last consumer of a sharded chain
+__global__ void ll_unpack_kernel(const unsigned int *arrive_ctr, int grid_fixed, int back, const unsigned long long *ll,
+                                 float *out, int64_t M, unsigned int *status) {
+  // stream order: every earlier sharded launch has completed, so tickets / grid = launches so far
+  const unsigned int tag = *reinterpret_cast<const volatile unsigned int *>(arrive_ctr) / (unsigned int)grid_fixed -
+                           (unsigned int)back + 1u;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (int64_t)gridDim.x * blockDim.x) {
+    unsigned long long v;
+    unsigned int spins = 0;
+    unsigned long long t0 = 0;
+    while (true) {
+      asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(ll + i) : "memory");
+      if ((unsigned int)(v >> 32) == tag) break;
+      if ((++spins & 1023u) == 0) {
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > 2000000000ull) { *status = 1u; break; }
+      }
+    }
+    out[i] = __uint_as_float((unsigned int)v);
+  }
+}
+
+int lammcu_ll_unpack_dev(lammcu_comm_t comm, const void *c_ll, int back, float *out, int64_t M, void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!comm || !c_ll || !out || M <= 0 || back < 1) { set_error("ll_unpack: bad argument"); return LAMMCU_ERR_ARG; }
+  const int blocks = (int)std::min<int64_t>((M + 255) / 256, 148);
+  ll_unpack_kernel<<<blocks, 256, 0, pick_stream(stream)>>>(comm->ctrs, sm_count_cached(), back,
+                                                           (const unsigned long long *)c_ll, out, M, comm->ctrs + 2);
+  g_launch_count++;
+  CU_TRY(cudaGetLastError());
+  return LAMMCU_OK;
 }
 
 // ---- host operands --------------------------------------------------------------

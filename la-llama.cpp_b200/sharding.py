@@ -5,7 +5,8 @@ One process per GPU (torch.distributed is the plumbing: rank discovery and the e
 [g*ceil(M/G), (g+1)*ceil(M/G)) -- the reference's thread split (src/lamm_impl.hpp:107-112) and
 upstream's device split (llama.cpp-b2430/ggml-cuda.cu:8480-8492) -- activations are replicated, and
 the output slices reach every rank's full C vector through the decode kernel's peer-store epilogue
-(lammcu_mul_mat_sharded_dev): no collective call on the data path.
+(lammcu_mul_mat_sharded_dev; {value, tag} pairs in one 64-bit NVLink store, polled by the consumer):
+no collective call, fence or flag on the data path.
 """
 import ctypes as C
 
@@ -72,26 +73,77 @@ class SharedBuffer:
         L.lammcu_ipc_free(self.local)
 
 
+class LLVector(SharedBuffer):
+    """An M-element output vector of sharded launches in LL format (lammcu.h): M x {f32 value,
+    u32 tag}, one buffer per rank, each mapped into every process."""
+
+    def __init__(self, lamm, dist, m):
+        self.m = m
+        self.seq = None            # communicator sequence number of the launch that last wrote it
+        super().__init__(lamm, dist, lamm.lib().lammcu_ll_bytes(m))
+
+
+class _SoloDist:
+    """torch.distributed stand-in for world_size 1 (a single GPU chaining launches through LL vectors)."""
+
+    def get_rank(self):
+        return 0
+
+    def get_world_size(self):
+        return 1
+
+    def all_gather_object(self, out, obj):
+        out[0] = obj
+
+    def barrier(self):
+        pass
+
+
 class Comm:
-    """The flag arrays + the C-ABI communicator."""
+    """The C-ABI communicator plus the host-side bookkeeping of launch sequence numbers (the kernel
+    derives the same numbers on the device; the host only needs DISTANCES between launches)."""
 
-    def __init__(self, lamm, dist):
-        self.lamm, self.dist = lamm, dist
-        self.rank, self.world = dist.get_rank(), dist.get_world_size()
-        self.flags = SharedBuffer(lamm, dist, 256)
+    def __init__(self, lamm, dist=None):
+        self.lamm, self.dist = lamm, dist or _SoloDist()
+        self.rank, self.world = self.dist.get_rank(), self.dist.get_world_size()
         h = C.c_void_p()
-        lamm.check(lamm.lib().lammcu_comm_create(self.rank, self.world, self.flags.ptr_array(), C.byref(h)), "comm_create")
+        lamm.check(lamm.lib().lammcu_comm_create(self.rank, self.world, C.byref(h)), "comm_create")
         self.handle = h
+        self.seq = 0               # sharded launches issued (or captured) so far
 
-    def mul_mat(self, w_type, w_shard, x_ptr, c_buf, m, k):
-        """w_shard: cuda uint8 [rows, row_bytes] = this rank's rows of an M-row weight; x_ptr: device
-        pointer (int) of the f32 activation row; c_buf: SharedBuffer of >= 4*M bytes (the full C)."""
+    def vector(self, m):
+        return LLVector(self.lamm, self.dist, m)
+
+    def mul_mat(self, w_type, w_shard, x, out, m, k):
+        """w_shard: cuda uint8 [rows, row_bytes] = this rank's rows of an M-row weight; x: the
+        activation row, either a device pointer (int) / cuda f32 tensor of K plain floats or an
+        LLVector produced by an earlier call; out: LLVector of M elements (the full C on every rank)."""
         lo, hi = row_shard(m, self.rank, self.world)
-        assert w_shard.shape[0] == hi - lo
+        assert w_shard.shape[0] == hi - lo and out.m >= m
+        if isinstance(x, LLVector):
+            assert x.seq is not None, "LL activation vector was never produced"
+            xp, back = x.local, self.seq - x.seq
+            assert back >= 1
+        else:
+            xp, back = (x if isinstance(x, int) else x.data_ptr()), 0
         self.lamm.check(self.lamm.lib().lammcu_mul_mat_sharded_dev(
-            self.handle, w_type, w_shard.data_ptr(), w_shard.stride(0) * w_shard.element_size(), x_ptr,
-            c_buf.ptr_array(), lo, hi - lo, k, self.lamm._stream_ptr()), "mul_mat_sharded")
+            self.handle, w_type, w_shard.data_ptr(), w_shard.stride(0) * w_shard.element_size(), xp, back,
+            out.ptr_array(), lo, hi - lo, k, self.lamm._stream_ptr()), "mul_mat_sharded")
+        out.seq = self.seq
+        self.seq += 1
+
+    def unpack(self, torch, vec, m=None):
+        """LLVector -> plain f32 cuda tensor [m] (waits for every element on the device)."""
+        m = m or vec.m
+        out = torch.empty((m,), dtype=torch.float32, device="cuda")
+        self.lamm.check(self.lamm.lib().lammcu_ll_unpack_dev(self.handle, vec.local, self.seq - vec.seq, out.data_ptr(), m,
+                                                             self.lamm._stream_ptr()), "ll_unpack")
+        return out
+
+    def timed_out(self):
+        v = C.c_int(0)
+        self.lamm.check(self.lamm.lib().lammcu_comm_status(self.handle, C.byref(v)), "comm_status")
+        return bool(v.value)
 
     def close(self):
         self.lamm.lib().lammcu_comm_destroy(self.handle)
-        self.flags.close()

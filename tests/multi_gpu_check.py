@@ -31,22 +31,24 @@ def main():
         lo, hi = sharding.row_shard(m, rank, world)
         wd = torch.from_numpy(w[lo:hi].copy()).cuda()
         xd = torch.from_numpy(x).cuda()
-        cbuf = sharding.SharedBuffer(L, dist, 4 * m)
-        for it in range(3):                                 # chained launches exercise the flag protocol
-            comm.mul_mat(t, wd, xd.data_ptr(), cbuf, m, k)
+        cbuf = sharding.LLVector(L, dist, m)
+        for it in range(3):                                 # repeated launches exercise the tag protocol
+            comm.mul_mat(t, wd, xd, cbuf, m, k)
         # a follow-up sharded launch that READS the gathered vector (every rank needs all of it)
         w2 = o.quantize_weights(Q4_1, np.random.default_rng(9).standard_normal((256, (m // 256) * 256)).astype(np.float32))
         k2 = (m // 256) * 256
         lo2, hi2 = sharding.row_shard(256, rank, world)
-        c2 = sharding.SharedBuffer(L, dist, 4 * 256)
-        comm.mul_mat(Q4_1, torch.from_numpy(w2[lo2:hi2].copy()).cuda(), cbuf.local, c2, 256, k2)
+        c2 = sharding.LLVector(L, dist, 256)
+        comm.mul_mat(Q4_1, torch.from_numpy(w2[lo2:hi2].copy()).cuda(), cbuf, c2, 256, k2)
+        got_t = comm.unpack(torch, cbuf)
+        got2_t = comm.unpack(torch, c2)
         torch.cuda.synchronize()
         dist.barrier()
-        got = cbuf.to_tensor(torch, torch.float32, m).cpu().numpy()[None, :]
+        got = got_t.cpu().numpy()[None, :]
         tol = 1e-5 * np.sqrt(k) * np.abs(want).max()
         err = np.abs(got - want).max()
         want2 = o.mul_mat(Q4_1, w2, got[:, :k2])
-        got2 = c2.to_tensor(torch, torch.float32, 256).cpu().numpy()[None, :]
+        got2 = got2_t.cpu().numpy()[None, :]
         err2 = np.abs(got2 - want2).max()
         tol2 = 1e-5 * np.sqrt(k2) * np.abs(want2).max()
         good = err <= tol and err2 <= tol2
@@ -54,6 +56,7 @@ def main():
         print(f"rank {rank} type {t} {m}x{k}: err {err:.3g} (tol {tol:.3g}), chained err {err2:.3g} (tol {tol2:.3g}) "
               f"{'ok' if good else 'FAIL'}", flush=True)
         dist.barrier()
+    ok &= not comm.timed_out()
     flag = torch.tensor([0 if ok else 1], device="cuda")
     dist.all_reduce(flag)
     dist.barrier()

@@ -50,3 +50,33 @@ def test_q2k_random_blocks(oracle, ref):
     assert np.isfinite(c).all()
     assert np.abs(ref.lamm_mul_mat(Q2_K, wq, x, xq) - c).max() <= tol_c(c, k)
     assert np.array_equal(oracle.dequantize(Q2_K, wq, k), ref.dequantize(Q2_K, wq, k))
+
+
+def test_fp16_tables_all_65536_halves(oracle, ref):
+    """fp16 -> f32 of every half bit pattern: reference table (through dequantize_row_q8_0 with
+    qs = 1, ggml-impl.h:237-250) == oracle == IEEE (numpy).  NaNs compared by 'is NaN'."""
+    bits = np.arange(65536, dtype=np.uint16)
+    blocks = np.zeros((65536, 34), np.uint8)
+    blocks[:, 0:2] = bits.view(np.uint8).reshape(-1, 2)
+    blocks[:, 2] = 1                                           # qs[0] = 1 -> y[0] = d
+    k = 32 * 32
+    rows = blocks.reshape(65536 // 32, 32 * 34)
+    got_ref = ref.dequantize(Q8_0, rows, k).reshape(65536, 32)[:, 0]
+    got_orc = np.array([oracle.L.orc_fp16_to_fp32(int(b)) for b in bits], np.float32)
+    ieee = bits.view(np.float16).astype(np.float32)
+    nan = np.isnan(ieee)
+    assert np.array_equal(np.isnan(got_ref), nan) and np.array_equal(np.isnan(got_orc), nan)
+    assert np.array_equal(got_ref[~nan].view(np.uint32), ieee[~nan].view(np.uint32))
+    assert np.array_equal(got_orc[~nan].view(np.uint32), ieee[~nan].view(np.uint32))
+
+
+def test_fp32_to_fp16_rne(oracle):
+    """f32 -> fp16 narrowing (ggml-impl.h:119-120 / :202-226) is IEEE round-to-nearest-even,
+    subnormals and overflow included."""
+    rng = np.random.default_rng(3)
+    x = np.concatenate([rng.standard_normal(20000).astype(np.float32) * s for s in (1e-8, 1e-5, 1e-3, 1.0, 300.0, 7e4)])
+    x = np.concatenate([x, np.array([0.0, -0.0, 65504.0, 65519.9, 65520.0, 5.9604645e-8, 2.9802322e-8, 6.1035156e-5], np.float32)])
+    with np.errstate(over="ignore"):
+        want = x.astype(np.float16).view(np.uint16)
+    got = np.array([oracle.L.orc_fp32_to_fp16(float(v)) for v in x], np.uint16)
+    assert np.array_equal(got, want)
