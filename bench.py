@@ -365,7 +365,26 @@ def run_cuda(args):
             wi += 1
     plan.append((wi, V, H, "x%d" % (LAYERS % 2), "logits"))
 
+    # sibling matmuls that share an activation row (q/k/v, gate/up) go out as ONE launch
+    # (lammcu_mul_mat_batch_dev) unless --no-batch; same 225 matmuls, fewer dependency waits
+    groups = []
+    for item in plan:
+        if (groups and args.batch and not fused and world == 1 and t != 0 and groups[-1][0][3] == item[3]
+                and groups[-1][0][1:3] == item[1:3] and len(groups[-1]) < 4):
+            groups[-1].append(item)
+        else:
+            groups.append([item])
+
     def one_token():
+        if args.batch and not fused and world == 1 and t != 0:
+            for grp in groups:
+                xin = x0 if grp[0][3] is None else buf[grp[0][3]]
+                if len(grp) == 1:
+                    wi, m, k, src, dst = grp[0]
+                    L.mul_mat(t, weights[wi], xin, out=buf[dst])
+                else:
+                    L.mul_mat_batch(t, [weights[g[0]] for g in grp], xin, [buf[g[4]] for g in grp])
+            return
         for wi, m, k, src, dst in plan:
             w = weights[wi]
             rows = w.shape[0]
@@ -460,7 +479,9 @@ def run_cuda(args):
         "value": tok_s, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "u4/u5/i8 weights x i8 activations -> i32 (dp4a), f32 scale-accumulate",
-        "data": "synthetic", "config": workload_config(args.fmt, world, "fused" if fused else "nccl", fused),
+        "data": "synthetic", "config": dict(workload_config(args.fmt, world, "fused" if fused else "nccl", fused),
+                                             launches_per_step=launches_per_token,
+                                             sibling_batching=bool(args.batch and not fused and world == 1 and t != 0)),
         "path_gbs": path_bytes * args.steps / (ms * 1e-3) / 1e9,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": TRAFFIC_PER_LAUNCH.get(args.fmt) if world == 1 else None,
@@ -687,6 +708,8 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--fmt", default="q4_1", choices=sorted(TYPE_IDS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-batch", dest="batch", action="store_false",
+                    help="N=1: one launch per matmul (225/token) instead of one per sibling group (129/token)")
     ap.add_argument("--chain", default="plain", choices=["plain", "ll"],
                     help="N=1: activation vectors between matmuls as plain f32 (ggml layout, kernel boundary = "
                          "dependency) or as LL {value, tag} vectors (dependency carried by the data)")

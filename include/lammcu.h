@@ -102,6 +102,16 @@ int lammcu_mul_mat_dev(int w_type, const void *w_dev, int64_t w_stride_bytes,
                        int64_t ldc, int64_t M, int64_t N, int64_t K,
                        void *xq_ws_dev, void *stream);
 
+/* N == 1, sibling matmuls: `count` weight matrices of the same type, K and row stride
+ * that multiply the SAME activation row (wq/wk/wv, gate/up in llama.cpp's build_llama,
+ * llama.cpp:5726-5800) -- C_j = W_j . x for every j.  Up to 4 of them run as ONE launch of
+ * the decode kernel (one activation quantize, one dependency wait); anything the kernel
+ * cannot take falls back to one lammcu_mul_mat_dev call per matrix.  Results are identical
+ * to separate calls.                                                                     */
+int lammcu_mul_mat_batch_dev(int w_type, int count, const void *const *w_dev,
+                             int64_t w_stride_bytes, const int64_t *M, const float *x_dev,
+                             float *const *c_dev, int64_t K, void *xq_ws_dev, void *stream);
+
 /* Path selection (diagnostics / benchmarking): N <= threshold runs the
  * memory-bound GEMV kernels, larger N the tensor-core GEMM.  Default 8.      */
 int lammcu_set_gemv_max_n(int n);

@@ -33,7 +33,7 @@ EXPORTS = [
     "lammcu_blck_size", "lammcu_type_size", "lammcu_vec_dot_type", "lammcu_row_size",
     "lammcu_quantize_act_dev", "lammcu_mul_mat_q_dev", "lammcu_mul_mat_dev", "lammcu_set_gemv_max_n",
     "lammcu_get_gemv_max_n", "lammcu_set_decode_kernel", "lammcu_get_decode_kernel", "lammcu_set_trace", "lammcu_ipc_alloc", "lammcu_ipc_open", "lammcu_ipc_close", "lammcu_ipc_free", "lammcu_memcpy_async",
-    "lammcu_comm_create", "lammcu_comm_destroy", "lammcu_comm_status", "lammcu_ll_bytes", "lammcu_mul_mat_sharded_dev", "lammcu_ll_unpack_dev", "lammcu_weight_register", "lammcu_weight_lookup", "lammcu_weight_release",
+    "lammcu_mul_mat_batch_dev", "lammcu_comm_create", "lammcu_comm_destroy", "lammcu_comm_status", "lammcu_ll_bytes", "lammcu_mul_mat_sharded_dev", "lammcu_ll_unpack_dev", "lammcu_weight_register", "lammcu_weight_lookup", "lammcu_weight_release",
     "lammcu_weight_dev_ptr", "lammcu_weight_rows", "lammcu_mul_mat_host", "lammcu_mul_mat_q_host",
     "lamm_can_mul_mat", "lamm_mul_mat", "lamm_get_opt_level", "lamm_set_writeback_wdata",
 ]
@@ -104,6 +104,7 @@ def lib():
     L.lammcu_ipc_close.argtypes = [vp]
     L.lammcu_ipc_free.argtypes = [vp]
     L.lammcu_memcpy_async.argtypes = [vp, vp, sz, vp]
+    L.lammcu_mul_mat_batch_dev.argtypes = [C.c_int, C.c_int, C.POINTER(vp), i64, C.POINTER(i64), fp, C.POINTER(vp), i64, vp, vp]
     L.lammcu_comm_create.argtypes = [C.c_int, C.c_int, C.POINTER(vp)]
     L.lammcu_comm_destroy.argtypes = [vp]
     L.lammcu_comm_status.argtypes = [vp, C.POINTER(C.c_int)]
@@ -204,6 +205,21 @@ def mul_mat(w_type, w, x, out=None, ws=None):
                                    x.stride(0), out.data_ptr(), out.stride(0), m, n, k,
                                    ws.data_ptr() if ws is not None else None, _stream_ptr()), "mul_mat")
     return out
+
+
+def mul_mat_batch(w_type, ws, x, outs):
+    """Sibling matmuls sharing one activation row (N = 1): outs[j] = ws[j] . x, one launch when possible.
+    ws: cuda uint8 [M_j, row bytes] with equal row stride; x: cuda f32 [1, K]; outs: cuda f32 [1, M_j]."""
+    n = len(ws)
+    k = x.shape[-1]
+    stride = ws[0].stride(0) * ws[0].element_size()
+    assert all(w.stride(0) * w.element_size() == stride for w in ws)
+    wp = (C.c_void_p * n)(*[w.data_ptr() for w in ws])
+    cp = (C.c_void_p * n)(*[o.data_ptr() for o in outs])
+    ms = (C.c_int64 * n)(*[w.shape[0] for w in ws])
+    check(lib().lammcu_mul_mat_batch_dev(w_type, n, wp, stride, ms, x.data_ptr(), cp, k, None, _stream_ptr()),
+          "mul_mat_batch")
+    return outs
 
 
 # ---- the drop-in operator on host (numpy) tensors, as ggml would call it -------------

@@ -131,8 +131,16 @@ struct ShardInfo {
   unsigned int *arrive_ctr, *status;
   int n_peer, my_rank, row_begin;
 };
+// sibling batch: `count` (2..4) matrices of one type / K / row stride that share the activation row
+struct BatchInfo {
+  int count;
+  const void *w[4];
+  float *c[4];
+  int64_t M[4];
+};
 int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
-                  float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh = nullptr);
+                  float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh = nullptr,
+                  const BatchInfo *bt = nullptr);
 int launch_gemm_prep(int vt, int perm, const void *xq, int64_t xq_stride, void *x16, float *dxT, float *sxT,
                      int64_t N, int64_t Npad, int64_t K, cudaStream_t st);
 void *gemm_workspace(size_t bytes);      // library-owned scratch for the prefill GEMM (grown on demand)

@@ -44,6 +44,11 @@ struct DecodeParams {
   int slots, slot_bytes;
   int x_bytes;          // shared-memory bytes of the staged activations
   unsigned long long *trace;   // optional: 8 globaltimer stamps per CTA (lammcu_set_trace)
+  // sibling batch (16-warp kernel): up to 4 weight matrices of one type, K and row stride that share
+  // the activation row (q/k/v, gate/up) form one virtual matrix of M total rows.  Global rows
+  // [mc[j-1], mc[j]) belong to matrix j; wb[j] / cb[j] are VIRTUAL bases (pointer minus the rows
+  // before it), so a row's address is wb[j] + row * w_stride.  nbatch <= 1: w and c are used as is.
+  const uint8_t *wb[4];   float *cb[4];   int mc[3];   int nbatch;
   // row-sharded multi-GPU (n_peer > 0): the epilogue stores every result as a {value, tag} pair
   // (one 64-bit store, "LL" format) into the full C vector of EVERY rank over NVLink.  The tag is
   // this launch's sequence number; a consumer polls the pairs of its activation row until every
@@ -714,7 +719,14 @@ __device__ __forceinline__ float dot_unit_sx(const uint32_t (&w)[NW], uint32_t x
 
 __device__ __forceinline__ void store_c(const DecodeParams &p, int row, float v, unsigned int tag) {
   if (p.n_peer == 0) {
-    p.c[row] = v;
+    float *c = p.c;
+    if (p.nbatch > 1) {
+      c = p.cb[0];
+      if (row >= p.mc[0]) c = p.cb[1];
+      if (row >= p.mc[1]) c = p.cb[2];
+      if (row >= p.mc[2]) c = p.cb[3];
+    }
+    c[row] = v;
   } else {
     const unsigned long long pair = ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
     for (int g = 0; g < p.n_peer; g++)
@@ -748,7 +760,16 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
   const uint32_t ring_addr = smem_u32(ring);
 
   auto issue = [&](int i, int s, uint64_t pol) {
-    const uintptr_t a = (uintptr_t)(wseg + (int64_t)(row0 + i * row_step) * p.w_stride);
+    const int r = row0 + i * row_step;
+    const uint8_t *base = wseg;
+    if (p.nbatch > 1) {
+      base = p.wb[0];
+      if (r >= p.mc[0]) base = p.wb[1];
+      if (r >= p.mc[1]) base = p.wb[2];
+      if (r >= p.mc[2]) base = p.wb[3];
+      base += seg_off;
+    }
+    const uintptr_t a = (uintptr_t)(base + (int64_t)r * p.w_stride);
     const uintptr_t a0 = a & ~(uintptr_t)15;
     const uint32_t bytes = (uint32_t)(((a + seg_bytes + 15) & ~(uintptr_t)15) - a0);
     uint64_t *bar = full + s;
@@ -842,7 +863,8 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
       xd[2] = v1.x; xsc[2] = v1.y; xd[3] = v1.z; xsc[3] = v1.w;
     }
   }
-  const uint32_t a15 = (uint32_t)((uintptr_t)(wseg + (int64_t)row0 * p.w_stride) & 15);
+  // every row of this warp has the same (address & 15) -- also across the matrices of a batch (host check)
+  const uint32_t a15 = (uint32_t)((uintptr_t)((p.nbatch > 1 ? p.wb[0] + seg_off : wseg) + (int64_t)row0 * p.w_stride) & 15);
   for (int i0 = 0, ph = 0; i0 < n_rows; i0 += S, ph ^= 1) {
     const int nb = min(S, n_rows - i0);
     float acc[S] = {0.f, 0.f};
@@ -987,7 +1009,7 @@ bool decode_supported(int w_type, const void *w, int64_t w_stride, const void *x
 }
 
 int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
-                  float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh) {
+                  float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh, const BatchInfo *bt) {
   const TypeInfo ti = type_info(w_type);
   const bool q2k = (w_type == LAMMCU_TYPE_Q2_K);
   DecodeParams p = {};
@@ -1009,7 +1031,18 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
     const char *e = getenv("LAMM_DECODE_VARIANT");          // tuning knob: 8 or 16 (default) warps
     return (e && atoi(e) == 8) ? 8 : 16;
   }();
-  const int variant = sh ? 16 : variant_env;                // the peer-store epilogue lives in the 16-warp kernel
+  const int variant = (sh || bt) ? 16 : variant_env;        // peer stores and sibling batches live in the 16-warp kernel
+  if (bt) {
+    p.nbatch = bt->count;
+    int64_t first[4] = {0, 0, 0, 0};
+    for (int j = 1; j < bt->count; j++) first[j] = first[j - 1] + bt->M[j - 1];
+    for (int j = 0; j < 4; j++) {
+      const int jj = j < bt->count ? j : bt->count - 1;      // unused slots repeat the last matrix
+      p.wb[j] = (const uint8_t *)bt->w[jj] - first[jj] * w_stride;
+      p.cb[j] = bt->c[jj] - first[jj];
+      if (j > 0) p.mc[j - 1] = j < bt->count ? (int)first[j] : 0x7fffffff;
+    }
+  }
   int xm = x ? 1 : 0;
   if (sh) {
     for (int g = 0; g < sh->n_peer; g++) p.ll_peer[g] = sh->ll_peer[g];

@@ -440,6 +440,37 @@ int lammcu_ll_unpack_dev(lammcu_comm_t comm, const void *c_ll, int back, float *
   return LAMMCU_OK;
 }
 
+int lammcu_mul_mat_batch_dev(int w_type, int count, const void *const *w_dev, int64_t w_stride,
+                             const int64_t *M, const float *x_dev, float *const *c_dev, int64_t K,
+                             void *xq_ws_dev, void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (count < 1 || !w_dev || !M || !x_dev || !c_dev) { set_error("mul_mat_batch: bad argument"); return LAMMCU_ERR_ARG; }
+  for (int j = 0; j < count; j++)
+    if (!w_dev[j] || !c_dev[j] || M[j] <= 0) { set_error("mul_mat_batch: bad operand %d", j); return LAMMCU_ERR_ARG; }
+  // one launch when the decode kernel can take the whole set; else one call per matrix
+  bool fuse = count >= 2 && count <= 4 && g_decode_kernel;
+  int64_t total = 0;
+  for (int j = 0; fuse && j < count; j++) {
+    fuse = decode_supported(w_type, w_dev[j], w_stride, x_dev, M[j], K) &&
+           (((uintptr_t)total * (uintptr_t)w_stride) & 15) == 0 &&          // same (address & 15) for every row
+           (((uintptr_t)w_dev[j] & 15) == ((uintptr_t)w_dev[0] & 15));
+    total += M[j];
+  }
+  if (fuse && total <= 0x3fffffff) {
+    BatchInfo bt = {};
+    bt.count = count;
+    for (int j = 0; j < count; j++) { bt.w[j] = w_dev[j]; bt.c[j] = c_dev[j]; bt.M[j] = M[j]; }
+    return launch_decode(w_type, w_dev[0], w_stride, x_dev, nullptr, nullptr, c_dev[0], total, K, pick_stream(stream),
+                         nullptr, &bt);
+  }
+  for (int j = 0; j < count; j++) {
+    rc = lammcu_mul_mat_dev(w_type, w_dev[j], w_stride, x_dev, K, c_dev[j], M[j], M[j], 1, K, xq_ws_dev, stream);
+    if (rc) return rc;
+  }
+  return LAMMCU_OK;
+}
+
 // ---- host operands --------------------------------------------------------------
 int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K,
                            int64_t w_stride, int64_t row_begin, int64_t row_end,
@@ -522,11 +553,25 @@ const void *lammcu_weight_dev_ptr(lammcu_weight_t w) { return w ? w->dev : nullp
 int64_t lammcu_weight_rows(lammcu_weight_t w) { return w ? w->row_end - w->row_begin : 0; }
 
 // D2H of the shard's column range of every output row
+// Small results (decode / GEMV sizes) are written by the kernel straight into pinned host memory
+// (device-accessible under UVA): one DMA and its launch latency less per call.  Large (prefill)
+// results keep the coalesced D2H copy.
+static bool zero_copy_out(int64_t N) { return N <= (int64_t)lammcu_get_gemv_max_n(); }
+
+static int out_buffer(lammcu_weight_t w, int64_t N, float **c_dev) {
+  const size_t bytes = (size_t)N * (size_t)(w->row_end - w->row_begin) * 4;
+  int rc = grow(&g_dev.hc, &g_dev.hc_bytes, bytes, true);
+  if (rc) return rc;
+  if (zero_copy_out(N)) { *c_dev = (float *)g_dev.hc; return LAMMCU_OK; }
+  if ((rc = grow(&g_dev.cout, &g_dev.cout_bytes, bytes, false))) return rc;
+  *c_dev = (float *)g_dev.cout;
+  return LAMMCU_OK;
+}
+
 static int copy_c_back(lammcu_weight_t w, int64_t N, float *c_host, int64_t ldc) {
   const int64_t rows = w->row_end - w->row_begin;
-  int rc = grow(&g_dev.hc, &g_dev.hc_bytes, (size_t)N * rows * 4, true);
-  if (rc) return rc;
-  CU_TRY(cudaMemcpyAsync(g_dev.hc, g_dev.cout, (size_t)N * rows * 4, cudaMemcpyDeviceToHost, g_dev.stream));
+  if (!zero_copy_out(N))
+    CU_TRY(cudaMemcpyAsync(g_dev.hc, g_dev.cout, (size_t)N * rows * 4, cudaMemcpyDeviceToHost, g_dev.stream));
   CU_TRY(cudaStreamSynchronize(g_dev.stream));
   for (int64_t j = 0; j < N; j++)
     memcpy(c_host + j * ldc + w->row_begin, (const float *)g_dev.hc + j * rows, (size_t)rows * 4);
@@ -543,7 +588,8 @@ int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N, int64
   const size_t xbytes = (size_t)N * K * 4;
   if ((rc = grow(&g_dev.hx, &g_dev.hx_bytes, xbytes, true))) return rc;
   if ((rc = grow(&g_dev.xin, &g_dev.xin_bytes, xbytes, false))) return rc;
-  if ((rc = grow(&g_dev.cout, &g_dev.cout_bytes, (size_t)N * rows * 4, false))) return rc;
+  float *c_dev = nullptr;
+  if ((rc = out_buffer(w, N, &c_dev))) return rc;
   for (int64_t j = 0; j < N; j++) memcpy((float *)g_dev.hx + j * K, x_host + j * ldx, (size_t)K * 4);
   CU_TRY(cudaMemcpyAsync(g_dev.xin, g_dev.hx, xbytes, cudaMemcpyHostToDevice, g_dev.stream));
   void *ws = nullptr;
@@ -552,7 +598,7 @@ int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N, int64
     if ((rc = grow(&g_dev.ws, &g_dev.ws_bytes, qb, false))) return rc;
     ws = g_dev.ws;
   }
-  rc = lammcu_mul_mat_dev(w->type, w->dev, w->stride, (const float *)g_dev.xin, K, (float *)g_dev.cout,
+  rc = lammcu_mul_mat_dev(w->type, w->dev, w->stride, (const float *)g_dev.xin, K, c_dev,
                           rows, rows, N, K, ws, g_dev.stream);
   if (rc) return rc;
   if (xq_out_host && w->type != LAMMCU_TYPE_F32) {
@@ -573,10 +619,11 @@ int lammcu_mul_mat_q_host(lammcu_weight_t w, const void *xq_host, int64_t xq_str
   const size_t rs = (vt == LAMMCU_TYPE_F32) ? (size_t)K * 4 : lammcu_row_size(vt, K);
   if ((size_t)xq_stride < rs) { set_error("mul_mat_q_host: activation stride smaller than a row"); return LAMMCU_ERR_SHAPE; }
   if ((rc = grow(&g_dev.ws, &g_dev.ws_bytes, rs * (size_t)N, false))) return rc;
-  if ((rc = grow(&g_dev.cout, &g_dev.cout_bytes, (size_t)N * rows * 4, false))) return rc;
+  float *c_dev = nullptr;
+  if ((rc = out_buffer(w, N, &c_dev))) return rc;
   CU_TRY(cudaMemcpy2DAsync(g_dev.ws, rs, xq_host, (size_t)xq_stride, rs, (size_t)N, cudaMemcpyHostToDevice,
                            g_dev.stream));
-  rc = lammcu_mul_mat_q_dev(w->type, w->dev, w->stride, g_dev.ws, (int64_t)rs, (float *)g_dev.cout, rows,
+  rc = lammcu_mul_mat_q_dev(w->type, w->dev, w->stride, g_dev.ws, (int64_t)rs, c_dev, rows,
                             rows, N, K, g_dev.stream);
   if (rc) return rc;
   return copy_c_back(w, N, c_host, ldc);

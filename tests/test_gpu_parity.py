@@ -238,3 +238,34 @@ def test_decode_kernel_chain_pdl(gpu, oracle):
         a = gpu.mul_mat(t, w1d, xd)
         b = gpu.mul_mat(t, w2d, a)
         assert np.abs(b.cpu().numpy() - y2).max() <= 2 * tol_c(y2, k)
+
+
+@pytest.mark.parametrize("t", QTYPES)
+@pytest.mark.parametrize("k,ms", [(4096, (4096, 1024, 516)), (11008, (256, 1000)), (512, (33, 7, 64, 129))])
+def test_decode_batch_siblings(gpu, oracle, t, k, ms):
+    """lammcu_mul_mat_batch_dev: sibling matmuls (q/k/v, gate/up) that share one activation row in ONE
+    launch.  Must equal the separate launches bit for bit (same per-row arithmetic) and the oracle within
+    tolerance; shapes the fused launch cannot take (Q2_K rows whose prefix breaks 16-byte congruence)
+    fall back to separate launches and still agree."""
+    import torch
+    rng = np.random.default_rng(k + sum(ms))
+    x = make_x(rng, 1, k)
+    ws = [weights(oracle, t, m, k, seed=100 + j) for j, m in enumerate(ms)]
+    wd = [dev(w) for w in ws]
+    xd = dev(x)
+    outs = [torch.full((1, m), float("nan"), device="cuda") for m in ms]
+    lib = gpu.lib()
+    lib.lammcu_launch_count_reset()
+    gpu.mul_mat_batch(t, wd, xd, outs)
+    launches = int(lib.lammcu_launch_count())
+    torch.cuda.synchronize()
+    stride = ws[0].shape[1]
+    prefix_ok = all((sum(ms[:j]) * stride) % 16 == 0 for j in range(len(ms)))
+    if k % 256 == 0 and prefix_ok:
+        assert launches == 1, f"expected one fused launch, saw {launches}"
+    for w, wdev, o, m in zip(ws, wd, outs, ms):
+        got = o.cpu().numpy()
+        sep = gpu.mul_mat(t, wdev, xd).cpu().numpy()
+        want = oracle.mul_mat(t, w, x)
+        assert np.array_equal(got, sep), f"batch differs from separate launch (M={m})"
+        assert np.abs(got - want).max() <= tol_c(want, k)
