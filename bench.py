@@ -38,10 +38,23 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 # ---- the workload (SURVEY 8d "tok/s definition") ---------------------------------------
-H, F, V, LAYERS = 4096, 11008, 32000, 32
-LAYER_SHAPES = [("wq", H, H), ("wk", H, H), ("wv", H, H), ("wo", H, H),
-                ("gate", F, H), ("up", F, H), ("down", H, F)]          # (name, M, K)
-HEAD_SHAPE = ("head", V, H)
+MODELS = {"7b": (4096, 11008, 32000, 32), "13b": (5120, 13824, 32000, 40), "30b": (6656, 17920, 32000, 60)}
+MODEL = "7b"
+H, F, V, LAYERS = MODELS[MODEL]
+LAYER_SHAPES = HEAD_SHAPE = None
+
+
+def set_model(name):
+    """LLaMA-7B is the metric's model; 13B / 30B shapes (BASELINE.json configs 4-5) for the scaling runs."""
+    global MODEL, H, F, V, LAYERS, LAYER_SHAPES, HEAD_SHAPE
+    MODEL = name
+    H, F, V, LAYERS = MODELS[name]
+    LAYER_SHAPES = [("wq", H, H), ("wk", H, H), ("wv", H, H), ("wo", H, H),
+                    ("gate", F, H), ("up", F, H), ("down", H, F)]          # (name, M, K)
+    HEAD_SHAPE = ("head", V, H)
+
+
+set_model("7b")
 TYPE_IDS = {"f32": 0, "q4_0": 2, "q4_1": 3, "q5_0": 6, "q5_1": 7, "q8_0": 8, "q2_k": 10}
 BLCK = {0: 1, 2: 32, 3: 32, 6: 32, 7: 32, 8: 32, 10: 256}
 TSIZE = {0: 4, 2: 18, 3: 20, 6: 22, 7: 24, 8: 34, 10: 84}
@@ -234,8 +247,8 @@ def cpu_reference_run(t, iters, warmup, nth=None):
     tok = sum(per[name] * mult for name, _, _, mult in shapes)        # seconds per token, per step
     return {"sec_per_token": tok, "kind": kind, "cores": nth,
             "sample": "per step one timed ggml_graph_compute (INIT quantize + lamm_mul_mat, N=1) of each "
-                      "distinct chain shape (4096x4096, 11008x4096, 4096x11008, 32000x4096), extrapolated "
-                      "x(128, 64, 32, 1); cache-thrash graph between timings as in la-benchmark-matmult",
+                      "distinct chain shape (HxH, FxH, HxF, VxH of the model), extrapolated "
+                      "x(4L, 2L, L, 1); cache-thrash graph between timings as in la-benchmark-matmult",
             "per_shape_us": {n_: float(np.mean(v) * 1e6) for n_, v in per.items()}}
 
 
@@ -265,7 +278,7 @@ def run_reference(args):
     sec = float(np.mean(r["sec_per_token"]))
     val = 1.0 / sec
     line = {
-        "impl": "reference", "metric": "llama7b_%s_decode_matmul_chain_tokens_per_s" % args.fmt,
+        "impl": "reference", "metric": "llama%s_%s_decode_matmul_chain_tokens_per_s" % (MODEL, args.fmt),
         "value": val, "unit": "tok/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "i8 x u4 -> i32, f32 scale-accumulate (AVX2 maddubs)", "data": "synthetic",
@@ -280,18 +293,21 @@ def run_reference(args):
 
 
 def workload_config(fmt, world, collective="fused", ll=False):
-    cfg = {"workload": "LLaMA-7B %s decode (N=1) weight-matmul chain: 32 x {4x 4096x4096, 2x 11008x4096, "
-                        "1x 4096x11008} + head 32000x4096; activation quantize + quantized GEMV per matmul; "
-                        "attention/norm/rope/sampling excluded (not on the path)" % fmt.upper(),
-            "format": fmt, "n_tokens_per_step": 1, "matmuls_per_step": len(chain_ops()),
-            "l2_defeat": "225 distinct weight buffers per step (4.13 GB for Q4_1) >> 126 MB L2",
+    ops = chain_ops()
+    cfg = {"workload": "LLaMA-%s %s decode (N=1) weight-matmul chain: %d x {4x %dx%d, 2x %dx%d, 1x %dx%d} + head %dx%d; "
+                        "fused activation-quantize + quantized GEMV per matmul, data dependent (each output row is a "
+                        "later matmul's activation row); attention/norm/rope/sampling excluded (not on the path)"
+                        % (MODEL.upper(), fmt.upper(), LAYERS, H, H, F, H, H, F, V, H),
+            "format": fmt, "n_tokens_per_step": 1, "matmuls_per_step": len(ops),
+            "l2_defeat": "%d distinct weight buffers per step (%.2f GB) >> 126 MB L2" % (
+                len(ops), sum(m * w_row_bytes(TYPE_IDS[fmt], k) for _, m, k in ops) / 1e9),
             "parallelism": "single GPU",
             "activation_vectors": "LL {f32 value, u32 tag} pairs, consumer polls tags (no kernel-boundary wait)" if ll
                                   else "plain f32 (ggml layout)"}
     if world > 1:
         cfg["parallelism"] = ("row-sharded M/%d per rank; C replicated on every rank by %s" % (
-            world, "the decode kernel's NVLink peer-store epilogue + system-scope flags (no collective call)"
-            if collective == "fused" else "ncclAllGather after every matmul"))
+            world, "the decode kernel's NVLink peer-store epilogue ({value, tag} 64-bit stores, consumer polls; "
+                   "no collective call)" if collective == "fused" else "ncclAllGather after every matmul"))
     return cfg
 
 
@@ -475,7 +491,7 @@ def run_cuda(args):
             cpu = {"value": None, "unit": "tok/s", "cores": 0, "kind": "unavailable", "sample": str(e)}
 
     line = {
-        "metric": "llama7b_%s_decode_matmul_chain_tokens_per_s" % args.fmt,
+        "metric": "llama%s_%s_decode_matmul_chain_tokens_per_s" % (MODEL, args.fmt),
         "value": tok_s, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "u4/u5/i8 weights x i8 activations -> i32 (dp4a), f32 scale-accumulate",
@@ -552,11 +568,18 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
     torch.cuda.synchronize()
     if dist:
         dist.barrier()
+    prof = (C.c_double * 8)()
+    lib.lammcu_host_profile(prof, 1)
     t0 = time.perf_counter()
     for _ in range(steps):
         token()
     torch.cuda.synchronize()
     sec = time.perf_counter() - t0
+    lib.lammcu_host_profile(prof, 1)
+    calls = max(prof[5], 1.0)
+    phases = {k: round(prof[i] / calls, 2) for i, k in enumerate(
+        ("x_memcpy_us", "h2d_enqueue_us", "kernel_enqueue_us", "wait_us", "c_memcpy_us"))}
+    phases["total_per_call_us"] = round(sec * 1e6 / calls, 2)
     if dist:
         tt = torch.tensor([sec], device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -564,7 +587,7 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
     h2d = sum(k * 4 for _, m, k in ops)
     d2h = sum((shard(m)[1] - shard(m)[0]) * 4 for _, m, k in ops)
     return {"value": steps / sec, "unit": "tok/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-            "steps": steps, "ms_per_step": sec / steps * 1e3,
+            "steps": steps, "ms_per_step": sec / steps * 1e3, "per_call_phases": phases,
             "api": "lamm_can_mul_mat + lamm_mul_mat(ggml_compute_params*, ggml_tensor*) on host tensors, "
                    "one synchronous call per matmul (225 per token); host wall clock",
             "note": "weights uploaded once at first use (registry keyed by src0->data); with N>1 the "
@@ -707,6 +730,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--fmt", default="q4_1", choices=sorted(TYPE_IDS))
+    ap.add_argument("--model", default="7b", choices=sorted(MODELS), help="chain shapes (the metric is quoted on 7b)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-batch", dest="batch", action="store_false",
                     help="N=1: one launch per matmul (225/token) instead of one per sibling group (129/token)")
@@ -722,6 +746,7 @@ def main():
     ap.add_argument("--ring-mb", type=int, default=512)
     ap.add_argument("--fused", action="store_true", help="suite: include the activation quantize launch")
     args = ap.parse_args()
+    set_model(args.model)
     if args.suite == "gemm":
         return run_suite_gemm(args)
     if args.suite:

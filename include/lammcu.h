@@ -205,6 +205,10 @@ int64_t lammcu_weight_rows(lammcu_weight_t w);
 int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N,
                         int64_t ldx, float *c_host, int64_t ldc,
                         void *xq_out_host);
+/* Diagnostics: accumulated host-path phase times in microseconds since the last reset:
+ * [0] x memcpy to pinned, [1] H2D enqueue, [2] kernel enqueue, [3] wait for completion,
+ * [4] C memcpy from pinned, [5] number of calls.                                        */
+void lammcu_host_profile(double *out8, int reset);
 /* same, activations already quantized on the host (src1->type == vec_dot_type) */
 int lammcu_mul_mat_q_host(lammcu_weight_t w, const void *xq_host,
                           int64_t xq_stride_bytes, int64_t N, float *c_host,

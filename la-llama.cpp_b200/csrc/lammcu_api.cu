@@ -5,6 +5,7 @@
 // compute entry point returns LAMMCU_ERR_NO_DEVICE.
 #include "lamm_common.cuh"
 #include <algorithm>
+#include <chrono>
 
 #include <cstdarg>
 #include <cstdio>
@@ -556,6 +557,12 @@ int64_t lammcu_weight_rows(lammcu_weight_t w) { return w ? w->row_end - w->row_b
 // Small results (decode / GEMV sizes) are written by the kernel straight into pinned host memory
 // (device-accessible under UVA): one DMA and its launch latency less per call.  Large (prefill)
 // results keep the coalesced D2H copy.
+// host-path phase timers (diagnostics: lammcu_host_profile)
+static double g_hp[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+static inline double now_us() {
+  return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 static bool zero_copy_out(int64_t N) { return N <= (int64_t)lammcu_get_gemv_max_n(); }
 
 static int out_buffer(lammcu_weight_t w, int64_t N, float **c_dev) {
@@ -572,9 +579,12 @@ static int copy_c_back(lammcu_weight_t w, int64_t N, float *c_host, int64_t ldc)
   const int64_t rows = w->row_end - w->row_begin;
   if (!zero_copy_out(N))
     CU_TRY(cudaMemcpyAsync(g_dev.hc, g_dev.cout, (size_t)N * rows * 4, cudaMemcpyDeviceToHost, g_dev.stream));
+  const double t0 = now_us();
   CU_TRY(cudaStreamSynchronize(g_dev.stream));
+  const double t1 = now_us();
   for (int64_t j = 0; j < N; j++)
     memcpy(c_host + j * ldc + w->row_begin, (const float *)g_dev.hc + j * rows, (size_t)rows * 4);
+  g_hp[3] += t1 - t0;  g_hp[4] += now_us() - t1;  g_hp[5] += 1;
   return LAMMCU_OK;
 }
 
@@ -590,8 +600,12 @@ int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N, int64
   if ((rc = grow(&g_dev.xin, &g_dev.xin_bytes, xbytes, false))) return rc;
   float *c_dev = nullptr;
   if ((rc = out_buffer(w, N, &c_dev))) return rc;
+  const double t0 = now_us();
   for (int64_t j = 0; j < N; j++) memcpy((float *)g_dev.hx + j * K, x_host + j * ldx, (size_t)K * 4);
+  const double t1 = now_us();
   CU_TRY(cudaMemcpyAsync(g_dev.xin, g_dev.hx, xbytes, cudaMemcpyHostToDevice, g_dev.stream));
+  const double t2 = now_us();
+  g_hp[0] += t1 - t0;  g_hp[1] += t2 - t1;
   void *ws = nullptr;
   if (xq_out_host && w->type != LAMMCU_TYPE_F32) {
     const size_t qb = lammcu_row_size(type_info(w->type).vec_dot, K) * (size_t)N;
@@ -600,12 +614,18 @@ int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N, int64
   }
   rc = lammcu_mul_mat_dev(w->type, w->dev, w->stride, (const float *)g_dev.xin, K, c_dev,
                           rows, rows, N, K, ws, g_dev.stream);
+  g_hp[2] += now_us() - t2;
   if (rc) return rc;
   if (xq_out_host && w->type != LAMMCU_TYPE_F32) {
     const size_t qb = lammcu_row_size(type_info(w->type).vec_dot, K) * (size_t)N;
     CU_TRY(cudaMemcpyAsync(xq_out_host, g_dev.ws, qb, cudaMemcpyDeviceToHost, g_dev.stream));
   }
   return copy_c_back(w, N, c_host, ldc);
+}
+
+/* diagnostics: accumulated microseconds {x memcpy, H2D enqueue, kernel enqueue, sync wait, C memcpy, calls} */
+void lammcu_host_profile(double *out8, int reset) {
+  for (int i = 0; i < 8; i++) { if (out8) out8[i] = g_hp[i]; if (reset) g_hp[i] = 0; }
 }
 
 int lammcu_mul_mat_q_host(lammcu_weight_t w, const void *xq_host, int64_t xq_stride, int64_t N,
