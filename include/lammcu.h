@@ -116,6 +116,12 @@ int lammcu_mul_mat_batch_dev(int w_type, int count, const void *const *w_dev,
  * memory-bound GEMV kernels, larger N the tensor-core GEMM.  Default 8.      */
 int lammcu_set_gemv_max_n(int n);
 int lammcu_get_gemv_max_n(void);
+/* Prefill (N > gemv_max_n) tensor-core kernel: 0 (default) = scaled-operand mainloop (scales folded
+ * into bf16 hi/lo operand pairs, one accumulator over the whole K loop; error <= 2^-16 per product,
+ * inside the path's 1e-5*sqrt(K) tolerance); 1 = exact per-32-block integer sums (bit-identical to the
+ * reference's sumi), scaled on the CUDA cores, about half the throughput.                            */
+int lammcu_set_gemm_exact(int on);
+int lammcu_get_gemm_exact(void);
 /* N == 1: 1 (default) = the single-launch decode kernel (fused activation
  * quantize, programmatic dependent launch); 0 = quantize kernel + generic GEMV */
 int lammcu_set_decode_kernel(int enable);

@@ -143,6 +143,14 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
                   const BatchInfo *bt = nullptr);
 int launch_gemm_prep(int vt, int perm, const void *xq, int64_t xq_stride, void *x16, float *dxT, float *sxT,
                      int64_t N, int64_t Npad, int64_t K, cudaStream_t st);
+int launch_gemm_prep_so(int vt, int perm, const void *xq, int64_t xq_stride, void *xh, void *xl, void *sh, float *colscale,
+                        int64_t N, int64_t Npad, int64_t K, cudaStream_t st);
+constexpr int kSoShift = 6;      // scaled-operand GEMM: A carries 2^kSoShift, B carries 2^-kSoShift
+size_t gemm_so_ws_bytes(int64_t N, int64_t K);
+int launch_gemm_so(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
+                   int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st);
+void set_gemm_exact(int on);
+int get_gemm_exact();
 void *gemm_workspace(size_t bytes);      // library-owned scratch for the prefill GEMM (grown on demand)
 void set_error(const char *fmt, ...);
 int sm_count_cached();

@@ -20,6 +20,7 @@
 // Rows n >= N are written as zeros.
 #include "lamm_common.cuh"
 
+
 namespace lamm {
 
 template <int VT, int PERM>
@@ -99,6 +100,123 @@ int launch_gemm_prep(int vt, int perm, const void *xq, int64_t xq_stride, void *
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("gemm_prep launch: %s", cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
+// ---- scaled-operand variant (lamm_gemm_so.cu) ------------------------------------------------
+// The B operand carries the activation scale: v = f32(d_x) * q_x is exact in f32 (11 + 8 significant
+// bits).  Each activation row n is normalised by an exact power of two 2^-E_n (E_n from the row's
+// largest block scale, so that |v| 2^-E_n < 2^11: any activation range fits fp16) and split into two
+// fp16 terms, v 2^-E_n ~= hi + lo, |residue| <= 2^-22 |v| (or 2^-25 absolute for elements far below
+// the row maximum).  The epilogue multiplies column n by colscale[n] = 2^(E_n - kSoShift).
+//   XH, XL   : fp16 [Npad][K]      same element order as X16 above (perm 1 / perm 0)
+//   SH       : fp16 [Npad][Kbpad]  s_x 2^-E_n (q8_1 only; s_x is an fp16 field, so one term is exact)
+//                                  for the m_w * s_x extra stages; Kbpad = Kb rounded up to 64, zero filled
+//   colscale : f32 [Npad]
+// One warp per activation row.
+template <int VT, int PERM>
+__global__ void __launch_bounds__(256) gemm_prep_so_kernel(const uint8_t *__restrict__ xq, int64_t xq_stride,
+                                                          __half *__restrict__ xh, __half *__restrict__ xl,
+                                                          __half *__restrict__ sh, float *__restrict__ colscale,
+                                                          int N, int Npad, int kb, int kbpad) {
+  constexpr int XB = (VT == LAMMCU_TYPE_Q8_0) ? 34 : 36;
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; n < Npad; n += warps) {
+    const uint8_t *row = xq + (int64_t)n * xq_stride;
+    float dmax = 0.f;
+    if (n < N)
+      for (int b = lane; b < kb; b += 32)
+        dmax = fmaxf(dmax, fabsf(half_bits_to_float(*reinterpret_cast<const uint16_t *>(row + (int64_t)b * XB))));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+    int E = 0;
+    if (dmax > 0.f && dmax < 3.0e38f) E = ilogbf(dmax) - 3;         // |d q| < 2^(ilogb + 8)  ->  < 2^11 after 2^-E
+    const float down = ldexpf(1.0f, -E);                            // exact power of two
+    if (lane == 0) colscale[n] = ldexpf(1.0f, E - kSoShift);
+    for (int b = lane; b < kbpad; b += 32) {
+      if (b >= kb) {                                                // zero tail of the s_x tile row
+        if (VT == LAMMCU_TYPE_Q8_1) sh[(int64_t)n * kbpad + b] = __float2half_rn(0.f);
+        continue;
+      }
+      uint32_t x[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+      float d = 0.f, s = 0.f;
+      if (n < N) {
+        const uint8_t *blk = row + (int64_t)b * XB;
+        if constexpr (VT == LAMMCU_TYPE_Q8_1) {
+          const uint32_t ds = *reinterpret_cast<const uint32_t *>(blk);
+          d = half_bits_to_float(ds & 0xffffu);
+          s = half_bits_to_float(ds >> 16);
+#pragma unroll
+          for (int j = 0; j < 8; j++) x[j] = *reinterpret_cast<const uint32_t *>(blk + 4 + 4 * j);
+        } else {
+          d = half_bits_to_float(*reinterpret_cast<const uint16_t *>(blk));
+#pragma unroll
+          for (int j = 0; j < 8; j++) {
+            const uint16_t *h = reinterpret_cast<const uint16_t *>(blk + 2 + 4 * j);
+            x[j] = (uint32_t)h[0] | ((uint32_t)h[1] << 16);
+          }
+        }
+      }
+      const float ds_ = d * down;                       // exact
+      auto el = [&](int e) -> float {                   // d_x * q_x * 2^-E of element e, exact in f32
+        const int v = (int)(signed char)((x[e >> 2] >> (8 * (e & 3))) & 0xffu);
+        return __fmul_rn(ds_, (float)v);
+      };
+      uint4 *dh = reinterpret_cast<uint4 *>(xh + ((int64_t)n * kb + b) * 32);
+      uint4 *dl = reinterpret_cast<uint4 *>(xl + ((int64_t)n * kb + b) * 32);
+#pragma unroll
+      for (int w = 0; w < 4; w++) {
+        float f[8];
+        if constexpr (PERM == 1) {
+          f[0] = el(4 * w);      f[1] = el(4 * w + 2);      f[2] = el(16 + 4 * w);     f[3] = el(16 + 4 * w + 2);
+          f[4] = el(4 * w + 1);  f[5] = el(4 * w + 3);      f[6] = el(16 + 4 * w + 1); f[7] = el(16 + 4 * w + 3);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; j++) f[j] = el(8 * w + j);
+        }
+        uint32_t hw[4], lw[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          const __half h0 = __float2half_rn(f[2 * j]), h1 = __float2half_rn(f[2 * j + 1]);
+          const __half l0 = __float2half_rn(f[2 * j] - __half2float(h0));
+          const __half l1 = __float2half_rn(f[2 * j + 1] - __half2float(h1));
+          hw[j] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+          lw[j] = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
+        }
+        dh[w] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+        dl[w] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+      }
+      if (VT == LAMMCU_TYPE_Q8_1) sh[(int64_t)n * kbpad + b] = __float2half_rn(s * down);
+    }
+  }
+}
+
+int launch_gemm_prep_so(int vt, int perm, const void *xq, int64_t xq_stride, void *xh, void *xl, void *sh_,
+                        float *colscale, int64_t N, int64_t Npad, int64_t K, cudaStream_t st) {
+  const int kb = (int)(K / 32), kbpad = (kb + 63) / 64 * 64;
+  __half *sh = (__half *)sh_;
+  int blocks = (int)((Npad + 7) / 8);                 // 8 warps per CTA, one row per warp
+  const int cap = sm_count_cached() * 8;
+  if (blocks > cap) blocks = cap;
+  const uint8_t *p = (const uint8_t *)xq;
+  __half *h = (__half *)xh, *l = (__half *)xl;
+  if (vt == LAMMCU_TYPE_Q8_1) {
+    if (perm) gemm_prep_so_kernel<LAMMCU_TYPE_Q8_1, 1><<<blocks, 256, 0, st>>>(p, xq_stride, h, l, sh, colscale, (int)N, (int)Npad, kb, kbpad);
+    else gemm_prep_so_kernel<LAMMCU_TYPE_Q8_1, 0><<<blocks, 256, 0, st>>>(p, xq_stride, h, l, sh, colscale, (int)N, (int)Npad, kb, kbpad);
+  } else if (vt == LAMMCU_TYPE_Q8_0) {
+    if (perm) gemm_prep_so_kernel<LAMMCU_TYPE_Q8_0, 1><<<blocks, 256, 0, st>>>(p, xq_stride, h, l, sh, colscale, (int)N, (int)Npad, kb, kbpad);
+    else gemm_prep_so_kernel<LAMMCU_TYPE_Q8_0, 0><<<blocks, 256, 0, st>>>(p, xq_stride, h, l, sh, colscale, (int)N, (int)Npad, kb, kbpad);
+  } else {
+    set_error("gemm_prep_so: activation type %d not supported", vt);
+    return LAMMCU_ERR_TYPE;
+  }
+  g_launch_count++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("gemm_prep_so launch: %s", cudaGetErrorString(e));
     return LAMMCU_ERR_CUDA;
   }
   return LAMMCU_OK;

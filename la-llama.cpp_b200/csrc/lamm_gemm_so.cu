@@ -1,0 +1,406 @@
+// lamm_gemm_so.cu -- prefill GEMM, "scaled operand" variant: the per-block scales ride INSIDE the
+// tensor-core operands, so the accumulator never leaves TMEM during the K loop.
+//
+// Replaces LAMMImpl<T>::matmul_simd_block + lamm_simd_block_kernel<4,4> (src/lamm_impl.hpp:90-147,
+// src/lamm_kernel_*.hpp) for many activation rows, like lamm_gemm.cu, but trades the bit-exact
+// integer block sums of that kernel for a plain GEMM mainloop:
+//
+//   C[n, m] = sum_k (d_w[m,b(k)] * q_w[m,k]) * (d_x[n,b(k)] * q_x[n,k])   (+ sum_b m_w[m,b] * s_x[n,b])
+//
+//   A' = d_w * q_w * 2^6     : split EXACTLY into two fp16 terms hi + lo (hi = rn(d q), lo = fma(d, q, -hi))
+//   B' = d_x * q_x * 2^-E_n  : exact in f32 (11 + 8 bits), row-normalised by a power of two and split
+//                              into two fp16 terms by lamm_gemm_prep.cu (residue <= 2^-22)
+//   A'B' ~= Ah*Bh + Ah*Bl + Al*Bh   -- three kind::f16 MMAs per K step, f32 accumulate in TMEM; the
+//   dropped Al*Bl term is <= 2^-22 relative per product (mixed fp16 x bf16 operands are not accepted by
+//   the hardware, hence fp16 on both sides and the exact power-of-two scalings), against the
+//   path's tolerance of 1e-5 * sqrt(K) * max|C| (>= 1.6e-4): tests/test_gpu_gemm.py checks both modes.
+//   The m_w * s_x term of Q4_1 / Q5_1 (src/lamm_kernel_q4_1.hpp:24, s_x is the fp16 field of
+//   block_q8_1 and must be used as stored) is a rank-(K/32) update: the unpack threads collect the
+//   m_w of 64 consecutive blocks in an extra A tile (fp16, exact), lamm_gemm_prep.cu lays the s_x out
+//   the same way (fp16, exact), and the MMA issuer folds the pair in as one extra stage per 64 blocks.
+//
+// One CTA = 128 weight rows x 128 activation rows, 16 warps:
+//   warp 0      TMA producer: raw packed weight blocks (2-D box over bytes, 8 blocks per row), the two
+//               fp16 activation tiles (SWIZZLE_128B), the s_x tiles of the extra stages
+//   warp 1      MMA issuer (one thread): per 64-K stage 4 x 3 tcgen05.mma M128 N128 K16 into ONE
+//               128-column accumulator; tcgen05.commit frees the stage; a final commit ends the tile
+//   warp 2      TMEM allocation
+//   warps 4-11  weight unpack (thread = row x one 32-block of the stage): nibbles / 5th bits -> small
+//               ints (0x6400 magic) * d_w -> fp16 hi / lo in the UMMA K-major SWIZZLE_128B layout
+//   warps 12-15 epilogue: tcgen05.ld the accumulator (thread = TMEM lane = weight row), store C coalesced
+#include "lamm_tc.cuh"
+
+#include <cstdlib>
+
+namespace lamm {
+
+constexpr int kSoAStages = 2;                  // unpacked weight tiles (hi + lo)
+constexpr int kSoBStages = 3;                  // activation tiles (hi + lo)
+constexpr int kSoThreads = 512;
+constexpr int kTileBytes = GM * GK * 2;        // 16 KB: one 128 x 64 fp16 operand tile
+
+struct SoParams {
+  const float *colscale;      // [Npad]: 2^(E_n - kSoShift), undoes the operands' power-of-two scales
+  float *c;
+  int64_t ldc;
+  int M, N, Npad, K;
+};
+
+template <int WT> struct SoSmem {
+  static constexpr int BS = type_info(WT).size;
+  static constexpr int kRawRowBytes = 8 * BS;                       // 8 blocks = 256 K elements = 4 stages
+  static constexpr int kRawBytes = GM * kRawRowBytes;
+  static constexpr bool kMin = (WT == LAMMCU_TYPE_Q4_1 || WT == LAMMCU_TYPE_Q5_1);
+  static constexpr int kAhOff = 0;
+  static constexpr int kAlOff = kAhOff + kSoAStages * kTileBytes;
+  static constexpr int kBhOff = kAlOff + kSoAStages * kTileBytes;
+  static constexpr int kBlOff = kBhOff + kSoBStages * kTileBytes;
+  static constexpr int kEhOff = kBlOff + kSoBStages * kTileBytes;   // m_w of 64 blocks (kMin only)
+  static constexpr int kRawOff = kEhOff + (kMin ? kTileBytes : 0);
+  static constexpr int kBarOff = kRawOff + (kRawBytes + 127) / 128 * 128;
+  static constexpr int kTotal = kBarOff + 256;
+};
+
+// 8 fp16 small integers (one 16-byte chunk of unpack_block) * d -> 8 fp16 hi + 8 fp16 lo, EXACT:
+// hi = rn(q * d) in fp16, lo = fma(q, d, -hi) is the rounding residual (<= 8 significant bits, exactly
+// representable as long as it stays above the fp16 subnormal step 2^-24).  d2 = (d, d) carries the
+// fixed pre-scale 2^kSoShift, which lifts realistic weight scales (1e-5 .. 8) well clear of the
+// subnormal range; the epilogue takes it out again (colscale).
+__device__ __forceinline__ void scale_split8(const uint4 &q, __half2 d2, uint4 &hi, uint4 &lo) {
+  const uint32_t in[4] = {q.x, q.y, q.z, q.w};
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const __half2 qq = *reinterpret_cast<const __half2 *>(&in[i]);
+    const __half2 hh = __hmul2(qq, d2);
+    const __half2 ll = __hfma2(qq, d2, __hneg2(hh));
+    h[i] = *reinterpret_cast<const uint32_t *>(&hh);
+    l[i] = *reinterpret_cast<const uint32_t *>(&ll);
+  }
+  hi = make_uint4(h[0], h[1], h[2], h[3]);
+  lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+// Block JB of the raw chunk (j = JB & 1: first / second 32-block of its 64-K stage) of the thread's row r.
+template <int WT, int JB, int NWR>
+__device__ __forceinline__ void unpack_block_so(const uint32_t (&raw)[NWR], uint32_t ah_stage, uint32_t al_stage, int r) {
+  constexpr int j = JB & 1;
+  const uint32_t row_off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u;
+  uint4 out[4];
+  float d, m;
+  unpack_block<WT, JB, NWR>(raw, out, d, m);
+  const __half2 d2 = __float2half2_rn(d * (float)(1 << kSoShift));      // exact: d is an fp16 value
+#pragma unroll
+  for (int w = 0; w < 4; w++) {
+    uint4 hi, lo;
+    scale_split8(out[w], d2, hi, lo);
+    const uint32_t c = ((uint32_t)(4 * j + w) ^ (uint32_t)(r & 7)) * 16u;
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(ah_stage + row_off + c), "r"(hi.x), "r"(hi.y),
+                 "r"(hi.z), "r"(hi.w)
+                 : "memory");
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(al_stage + row_off + c), "r"(lo.x), "r"(lo.y),
+                 "r"(lo.z), "r"(lo.w)
+                 : "memory");
+  }
+}
+
+// the 8 m_w of the raw chunk (Q4_1 / Q5_1: fp16 at byte 2 of every block) times 2^kSoShift: one 16-byte
+// chunk of the extra A tile (m_w is an fp16 field, the power-of-two scale keeps it exact)
+template <int WT, int NWR>
+__device__ __forceinline__ uint4 chunk_mins(const uint32_t (&raw)[NWR]) {
+  constexpr int BS = type_info(WT).size;
+  constexpr float S = (float)(1 << kSoShift);
+  const __half2 a = __floats2half2_rn(raw_half<0 * BS + 2, NWR>(raw) * S, raw_half<1 * BS + 2, NWR>(raw) * S);
+  const __half2 b = __floats2half2_rn(raw_half<2 * BS + 2, NWR>(raw) * S, raw_half<3 * BS + 2, NWR>(raw) * S);
+  const __half2 c = __floats2half2_rn(raw_half<4 * BS + 2, NWR>(raw) * S, raw_half<5 * BS + 2, NWR>(raw) * S);
+  const __half2 d = __floats2half2_rn(raw_half<6 * BS + 2, NWR>(raw) * S, raw_half<7 * BS + 2, NWR>(raw) * S);
+  return make_uint4(*reinterpret_cast<const uint32_t *>(&a), *reinterpret_cast<const uint32_t *>(&b),
+                    *reinterpret_cast<const uint32_t *>(&c), *reinterpret_cast<const uint32_t *>(&d));
+}
+
+template <int WT>
+__global__ void __launch_bounds__(kSoThreads, 1)
+gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_xh,
+               const __grid_constant__ CUtensorMap tm_xl, const __grid_constant__ CUtensorMap tm_sh, const SoParams p) {
+  using L = SoSmem<WT>;
+  constexpr bool kMin = L::kMin;
+  constexpr int NWR = 2 * L::BS;                                    // raw words per row chunk
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + L::kBarOff);
+  uint64_t *full_a = bars, *empty_a = bars + 2, *full_b = bars + 4, *empty_b = bars + 7, *raw_full = bars + 10,
+           *raw_empty = bars + 11, *acc_full = bars + 12, *ext_full = bars + 13, *ext_empty = bars + 14;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles = (p.N + GN - 1) / GN;
+  const int m0 = (blockIdx.x / n_tiles) * GM, n0 = (blockIdx.x % n_tiles) * GN;
+  const int n_stages = p.K / GK, n_chunks = n_stages / 4;
+
+  // Q4_1 / Q5_1: an extra stage (m_w tile x s_x tile) is folded in before main stage 4c for every raw
+  // chunk c that completes a group of 64 blocks (c % 8 == 7) or is the last one.  The m_w tile is
+  // complete as soon as the unpack warps START chunk c, i.e. four stages before the group's end.
+  auto ext_before = [&](int st) -> bool {
+    if (!kMin || (st & 3)) return false;
+    const int c = st >> 2;
+    return (c & 7) == 7 || c == n_chunks - 1;
+  };
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kSoAStages; i++) {
+      mbar_init(&full_a[i], 8);                        // one arrival per unpack warp
+      mbar_init(&empty_a[i], 1);                       // MMA commit
+    }
+    for (int i = 0; i < kSoBStages; i++) {
+      mbar_init(&full_b[i], 1);
+      mbar_init(&empty_b[i], 1);
+    }
+    mbar_init(raw_full, 1);
+    mbar_init(raw_empty, 8);
+    mbar_init(acc_full, 1);
+    mbar_init(ext_full, 4);                            // the four unpack warps that own m_w (j == 0)
+    mbar_init(ext_empty, 1);
+    fence_barrier_init();
+    prefetch_tmap(&tm_w);
+    prefetch_tmap(&tm_xh);
+    prefetch_tmap(&tm_xl);
+    if (kMin) prefetch_tmap(&tm_sh);
+  }
+  if constexpr (kMin) {
+    // stale shared memory may hold NaN patterns: unwritten columns of the m_w tile meet zero s_x
+    const uint32_t e0 = smem_u32(smem + L::kEhOff) + threadIdx.x * 32u;
+#pragma unroll
+    for (int i = 0; i < 2; i++)
+      asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(e0 + 16u * i), "r"(0u) : "memory");
+    fence_proxy_async();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 128);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int bseq = 0;                                    // B-ring sequence number (main + extra stages)
+      for (int st = 0; st < n_stages; st++) {
+        if ((st & 3) == 0) {
+          const int ms = st >> 2;
+          mbar_wait(raw_empty, ((uint32_t)ms & 1u) ^ 1u);
+          mbar_arrive_expect_tx(raw_full, (uint32_t)L::kRawBytes);
+          tma_load_2d(smem + L::kRawOff, &tm_w, ms * (L::kRawRowBytes / 2), m0, raw_full);
+        }
+        if (ext_before(st)) {
+          const int s = bseq % kSoBStages, e = st >> 5;
+          mbar_wait(&empty_b[s], ((uint32_t)(bseq / kSoBStages) & 1u) ^ 1u);
+          mbar_arrive_expect_tx(&full_b[s], (uint32_t)kTileBytes);
+          tma_load_2d(smem + L::kBhOff + s * kTileBytes, &tm_sh, e * 64, n0, &full_b[s]);
+          bseq++;
+        }
+        const int s = bseq % kSoBStages;
+        mbar_wait(&empty_b[s], ((uint32_t)(bseq / kSoBStages) & 1u) ^ 1u);
+        mbar_arrive_expect_tx(&full_b[s], (uint32_t)(2 * kTileBytes));
+        tma_load_2d(smem + L::kBhOff + s * kTileBytes, &tm_xh, st * GK, n0, &full_b[s]);
+        tma_load_2d(smem + L::kBlOff + s * kTileBytes, &tm_xl, st * GK, n0, &full_b[s]);
+        bseq++;
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      int bseq = 0;
+      uint32_t acc_on = 0u;                            // 0 only for the very first MMA of the tile
+      for (int st = 0; st < n_stages; st++) {
+        if (ext_before(st)) {
+          const int sb = bseq % kSoBStages, e = st >> 5;
+          mbar_wait(ext_full, (uint32_t)e & 1u);
+          mbar_wait(&full_b[sb], (uint32_t)(bseq / kSoBStages) & 1u);
+          tc_fence_after();
+          const uint64_t ah = make_sw128_desc(smem_u32(smem + L::kEhOff));
+          const uint64_t bh = make_sw128_desc(smem_u32(smem + L::kBhOff + sb * kTileBytes));
+#pragma unroll
+          for (int kk = 0; kk < 4; kk++) {
+            umma_f16(tmem_base, ah + (uint64_t)(kk * 2), bh + (uint64_t)(kk * 2), kIdescF16, acc_on);
+            acc_on = 1u;
+          }
+          umma_commit(ext_empty);
+          umma_commit(&empty_b[sb]);
+          bseq++;
+        }
+        const int sa = st % kSoAStages, sb = bseq % kSoBStages;
+        mbar_wait(&full_a[sa], (uint32_t)(st / kSoAStages) & 1u);
+        mbar_wait(&full_b[sb], (uint32_t)(bseq / kSoBStages) & 1u);
+        tc_fence_after();
+        const uint64_t ah = make_sw128_desc(smem_u32(smem + L::kAhOff + sa * kTileBytes));
+        const uint64_t al = make_sw128_desc(smem_u32(smem + L::kAlOff + sa * kTileBytes));
+        const uint64_t bh = make_sw128_desc(smem_u32(smem + L::kBhOff + sb * kTileBytes));
+        const uint64_t bl = make_sw128_desc(smem_u32(smem + L::kBlOff + sb * kTileBytes));
+#pragma unroll
+        for (int kk = 0; kk < 4; kk++) {
+          // the K offset inside the 128-byte swizzle atom advances the start address (16-byte units)
+          const uint64_t o = (uint64_t)(kk * 2);
+          umma_f16(tmem_base, ah + o, bh + o, kIdescF16, acc_on);
+          acc_on = 1u;
+          umma_f16(tmem_base, ah + o, bl + o, kIdescF16, 1u);
+          umma_f16(tmem_base, al + o, bh + o, kIdescF16, 1u);
+        }
+        umma_commit(&empty_a[sa]);
+        umma_commit(&empty_b[sb]);
+        bseq++;
+      }
+      umma_commit(acc_full);
+    }
+  } else if (warp >= 4 && warp < 12) {
+    // ===================== weight unpack (thread = row x block j of the stage) =====================
+    const int r = (threadIdx.x - 128) & 127, j = (warp - 4) >> 2;
+    for (int ms = 0; ms < n_chunks; ms++) {
+      mbar_wait(raw_full, (uint32_t)ms & 1u);
+      uint32_t raw[NWR];
+      const uint32_t src = smem_u32(smem + L::kRawOff) + (uint32_t)r * L::kRawRowBytes;
+#pragma unroll
+      for (int i = 0; i < NWR / 4; i++)
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(raw[4 * i]), "=r"(raw[4 * i + 1]), "=r"(raw[4 * i + 2]), "=r"(raw[4 * i + 3])
+                     : "r"(src + 16u * i));
+      __syncwarp();
+      if (lane == 0) mbar_arrive(raw_empty);
+      if constexpr (kMin) {
+        if (j == 0) {
+          if ((ms & 7) == 0 && ms > 0) mbar_wait(ext_empty, (uint32_t)((ms >> 3) - 1) & 1u);
+          const uint4 mh = chunk_mins<WT, NWR>(raw);
+          const uint32_t off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u + (((uint32_t)(ms & 7) ^ (uint32_t)(r & 7)) * 16u);
+          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(smem + L::kEhOff) + off), "r"(mh.x),
+                       "r"(mh.y), "r"(mh.z), "r"(mh.w)
+                       : "memory");
+          if ((ms & 7) == 7 || ms == n_chunks - 1) {
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(ext_full);
+          }
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const int st = ms * 4 + q, s = st % kSoAStages;
+        mbar_wait(&empty_a[s], ((uint32_t)(st / kSoAStages) & 1u) ^ 1u);
+        const uint32_t ah = smem_u32(smem + L::kAhOff + s * kTileBytes), al = smem_u32(smem + L::kAlOff + s * kTileBytes);
+        if (j == 0) {
+          if (q == 0) unpack_block_so<WT, 0, NWR>(raw, ah, al, r);
+          else if (q == 1) unpack_block_so<WT, 2, NWR>(raw, ah, al, r);
+          else if (q == 2) unpack_block_so<WT, 4, NWR>(raw, ah, al, r);
+          else unpack_block_so<WT, 6, NWR>(raw, ah, al, r);
+        } else {
+          if (q == 0) unpack_block_so<WT, 1, NWR>(raw, ah, al, r);
+          else if (q == 1) unpack_block_so<WT, 3, NWR>(raw, ah, al, r);
+          else if (q == 2) unpack_block_so<WT, 5, NWR>(raw, ah, al, r);
+          else unpack_block_so<WT, 7, NWR>(raw, ah, al, r);
+        }
+        fence_proxy_async();             // generic-proxy stores -> visible to the tensor core
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full_a[s]);
+      }
+    }
+  } else if (warp >= 12) {
+    // ===================== epilogue (thread = TMEM lane = weight row) =====================
+    const int q4 = warp & 3, row = q4 * 32 + lane, m = m0 + row;
+    mbar_wait(acc_full, 0u);
+    tc_fence_after();
+    const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16);
+#pragma unroll 2
+    for (int c16 = 0; c16 < 8; c16++) {
+      uint32_t v[16];
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+            "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+          : "r"(tbase + (uint32_t)(c16 * 16))
+          : "memory");
+      tmem_ld_wait();
+      if (m < p.M) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+          const int n = n0 + c16 * 16 + i;
+          if (n < p.N) p.c[(int64_t)n * p.ldc + m] = __uint_as_float(v[i]) * __ldg(p.colscale + n);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, 128);
+}
+
+// ---- host side ------------------------------------------------------------------------------
+template <int WT>
+static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CUtensorMap &tm_xl,
+                     const CUtensorMap &tm_sh, const SoParams &p, cudaStream_t st) {
+  using L = SoSmem<WT>;
+  constexpr int smem = L::kTotal + 1024;
+  static_assert(smem <= 227 * 1024, "shared memory budget");
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_so_kernel<WT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) {
+      set_error("gemm_so: cudaFuncSetAttribute(%d): %s", smem, cudaGetErrorString(e));
+      return LAMMCU_ERR_CUDA;
+    }
+    attr_set = true;
+  }
+  const int tiles = ((p.M + GM - 1) / GM) * ((p.N + GN - 1) / GN);
+  gemm_so_kernel<WT><<<tiles, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);
+  g_launch_count++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("gemm_so launch (type %d): %s", WT, cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
+size_t gemm_so_ws_bytes(int64_t N, int64_t K) {
+  const int64_t npad = (N + GN - 1) / GN * GN, kbpad = (K / 32 + 63) / 64 * 64;
+  return (size_t)(2 * npad * K * 2 + npad * kbpad * 2 + npad * 4 + 1024);
+}
+
+// xq: quantized activations (ggml blocks, row stride xq_stride); ws: gemm_so_ws_bytes() of scratch
+int launch_gemm_so(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
+                   int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st) {
+  const TypeInfo ti = type_info(w_type);
+  const int64_t npad = (N + GN - 1) / GN * GN, kb = K / 32, kbpad = (kb + 63) / 64 * 64;
+  uint8_t *base = (uint8_t *)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
+  void *xh = base, *xl = base + npad * K * 2;
+  void *sh = base + 2 * npad * K * 2;
+  float *colscale = (float *)((uint8_t *)sh + npad * kbpad * 2);
+  const int perm = (w_type == LAMMCU_TYPE_Q8_0) ? 0 : 1;
+  int rc = launch_gemm_prep_so(ti.vec_dot, perm, xq, xq_stride, xh, xl, sh, colscale, N, npad, K, st);
+  if (rc) return rc;
+  CUtensorMap tm_w, tm_xh, tm_xl, tm_sh;
+  // raw weights as uint16 [M][row_bytes / 2], box = 8 blocks x 128 rows
+  rc = make_map_2d(&tm_w, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, w, (uint64_t)(kb * ti.size / 2), (uint64_t)M,
+                   (uint64_t)w_stride, (uint32_t)(4 * ti.size), GM, CU_TENSOR_MAP_SWIZZLE_NONE);
+  if (rc) return rc;
+  rc = make_map_2d(&tm_xh, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, xh, (uint64_t)K, (uint64_t)npad, (uint64_t)K * 2, GK, GN,
+                   CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  rc = make_map_2d(&tm_xl, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, xl, (uint64_t)K, (uint64_t)npad, (uint64_t)K * 2, GK, GN,
+                   CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  // s_x of the extra stages (Q4_1 / Q5_1; a harmless dummy otherwise)
+  rc = make_map_2d(&tm_sh, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, sh, (uint64_t)kbpad, (uint64_t)npad, (uint64_t)kbpad * 2,
+                   GK, GN, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  SoParams p;
+  p.colscale = colscale;  p.c = c;  p.ldc = ldc;
+  p.M = (int)M;  p.N = (int)N;  p.Npad = (int)npad;  p.K = (int)K;
+  switch (w_type) {
+  case LAMMCU_TYPE_Q4_0: return launch_so<LAMMCU_TYPE_Q4_0>(tm_w, tm_xh, tm_xl, tm_sh, p, st);
+  case LAMMCU_TYPE_Q4_1: return launch_so<LAMMCU_TYPE_Q4_1>(tm_w, tm_xh, tm_xl, tm_sh, p, st);
+  case LAMMCU_TYPE_Q5_0: return launch_so<LAMMCU_TYPE_Q5_0>(tm_w, tm_xh, tm_xl, tm_sh, p, st);
+  case LAMMCU_TYPE_Q5_1: return launch_so<LAMMCU_TYPE_Q5_1>(tm_w, tm_xh, tm_xl, tm_sh, p, st);
+  default:               return launch_so<LAMMCU_TYPE_Q8_0>(tm_w, tm_xh, tm_xl, tm_sh, p, st);
+  }
+}
+
+}  // namespace lamm

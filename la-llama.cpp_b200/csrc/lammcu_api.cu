@@ -441,6 +441,9 @@ int lammcu_ll_unpack_dev(lammcu_comm_t comm, const void *c_ll, int back, float *
   return LAMMCU_OK;
 }
 
+int lammcu_set_gemm_exact(int on) { set_gemm_exact(on); return LAMMCU_OK; }
+int lammcu_get_gemm_exact(void) { return get_gemm_exact(); }
+
 int lammcu_mul_mat_batch_dev(int w_type, int count, const void *const *w_dev, int64_t w_stride,
                              const int64_t *M, const float *x_dev, float *const *c_dev, int64_t K,
                              void *xq_ws_dev, void *stream) {
