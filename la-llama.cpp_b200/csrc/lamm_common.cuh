@@ -149,6 +149,13 @@ constexpr int kSoShift = 6;      // scaled-operand GEMM: A carries 2^kSoShift, B
 size_t gemm_so_ws_bytes(int64_t N, int64_t K);
 int launch_gemm_so(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
                    int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st);
+size_t gemm_direct_ws_bytes(int64_t M, int64_t N, int64_t K);
+int launch_gemm_direct(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
+                       int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st);
+int launch_dequant_hilo(int w_type, const void *w, int64_t w_stride, void *ah, void *al, int64_t M, int64_t Mpad,
+                        int64_t K, cudaStream_t st);
+int launch_prep_direct(int vt, const void *xq, int64_t xq_stride, void *xh, void *xl, float *colscale, int64_t N,
+                       int64_t Npad, int64_t K, cudaStream_t st);
 void set_gemm_exact(int on);
 int get_gemm_exact();
 void *gemm_workspace(size_t bytes);      // library-owned scratch for the prefill GEMM (grown on demand)

@@ -406,6 +406,15 @@ static int g_gemm_exact = [] { const char *e = getenv("LAMM_GEMM_EXACT"); return
 void set_gemm_exact(int on) { g_gemm_exact = on ? 1 : 0; }
 int get_gemm_exact() { return g_gemm_exact; }
 
+// Q2_K / F32 weights: dequantize-once + TMA-fed GEMM (lamm_gemm_so.cu, direct variant)
+static bool gemm_direct_supported(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride,
+                                  int64_t M, int64_t N, int64_t K) {
+  if (w_type != LAMMCU_TYPE_Q2_K && w_type != LAMMCU_TYPE_F32) return false;
+  if (K <= 0 || K % 256 || M <= 0 || N <= 0 || M > 0x3fffffff || N > 0x3fffffff) return false;
+  const uintptr_t al = (w_type == LAMMCU_TYPE_F32) ? 15 : 3;
+  return (((uintptr_t)w | (uintptr_t)w_stride | (uintptr_t)xq | (uintptr_t)xq_stride) & al) == 0;
+}
+
 int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
                 int64_t ldc, int64_t M, int64_t N, int64_t K, cudaStream_t st) {
   if (gemm_tc_supported(w_type, w, w_stride, M, N, K)) {
@@ -417,6 +426,11 @@ int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int
     void *ws = gemm_workspace(gemm_ws_bytes(N, K));
     if (!ws) return LAMMCU_ERR_NOMEM;
     return launch_gemm_tc_any(w_type, w, w_stride, xq, xq_stride, c, ldc, M, N, K, ws, st);
+  }
+  if (!g_gemm_exact && gemm_direct_supported(w_type, w, w_stride, xq, xq_stride, M, N, K)) {
+    void *ws = gemm_workspace(gemm_direct_ws_bytes(M, N, K));
+    if (!ws) return LAMMCU_ERR_NOMEM;
+    return launch_gemm_direct(w_type, w, w_stride, xq, xq_stride, c, ldc, M, N, K, ws, st);
   }
   return launch_gemv(w_type, w, w_stride, xq, xq_stride, c, ldc, M, N, K, st);
 }

@@ -222,4 +222,176 @@ int launch_gemm_prep_so(int vt, int perm, const void *xq, int64_t xq_stride, voi
   return LAMMCU_OK;
 }
 
+// ---- direct variant (gemm_direct_kernel): Q2_K / F32 weights ------------------------------------
+__device__ __forceinline__ void split_store32(const float (&v)[32], __half *hi, __half *lo) {
+  uint4 *dh = reinterpret_cast<uint4 *>(hi), *dl = reinterpret_cast<uint4 *>(lo);
+#pragma unroll
+  for (int w = 0; w < 4; w++) {
+    uint32_t hw[4], lw[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const float a = v[8 * w + 2 * j], b = v[8 * w + 2 * j + 1];
+      const __half h0 = __float2half_rn(a), h1 = __float2half_rn(b);
+      const __half l0 = __float2half_rn(a - __half2float(h0)), l1 = __float2half_rn(b - __half2float(h1));
+      hw[j] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+      lw[j] = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
+    }
+    dh[w] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+    dl[w] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+  }
+}
+
+// W (Q2_K super-blocks or f32 rows) -> AH, AL fp16 [Mpad][K], value * 2^kSoShift, natural K order.
+// Q2_K element (ggml-common.h:214-225, src/lamm_kernel_q2_k.hpp:49-71): for half n of the super-block and
+// shift s in {0,2,4,6}, elements 128n + 16s .. + 31 are (qs[32n + l] >> s) & 3 with scale bytes
+// scales[8n + s] (l < 16) and scales[8n + s + 1]; w = d * (sc & 15) * q - dmin * (sc >> 4).
+template <int WT>
+__global__ void __launch_bounds__(256) dequant_hilo_kernel(const uint8_t *__restrict__ w, int64_t w_stride,
+                                                          __half *__restrict__ ah, __half *__restrict__ al, int M,
+                                                          int Mpad, int K) {
+  const int kb32 = K / 32;
+  const int64_t total = (int64_t)Mpad * kb32;
+  constexpr float S = (float)(1 << kSoShift);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int m = (int)(i / kb32), b = (int)(i - (int64_t)m * kb32);
+    float v[32];
+#pragma unroll
+    for (int l = 0; l < 32; l++) v[l] = 0.f;
+    if (m < M) {
+      if constexpr (WT == LAMMCU_TYPE_Q2_K) {
+        const uint8_t *blk = w + (int64_t)m * w_stride + (int64_t)(b >> 3) * 84;
+        const int ib = b & 7, n = ib >> 2, shift = 2 * (ib & 3);
+        const uint32_t dd = *reinterpret_cast<const uint32_t *>(blk + 80);
+        const float d = half_bits_to_float(dd & 0xffffu) * S, dmin = half_bits_to_float(dd >> 16) * S;
+        const uint32_t sc2 = *reinterpret_cast<const uint16_t *>(blk + 2 * ib);
+        const float d0 = d * (float)(sc2 & 15u), m0 = dmin * (float)((sc2 >> 4) & 15u);
+        const float d1 = d * (float)((sc2 >> 8) & 15u), m1 = dmin * (float)(sc2 >> 12);
+        const uint32_t *qs = reinterpret_cast<const uint32_t *>(blk + 16 + 32 * n);
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          const uint32_t qw = qs[j] >> shift;
+#pragma unroll
+          for (int e = 0; e < 4; e++) {
+            const float qv = (float)((qw >> (8 * e)) & 3u);
+            v[4 * j + e] = (j < 4) ? fmaf(d0, qv, -m0) : fmaf(d1, qv, -m1);
+          }
+        }
+      } else {
+        const float4 *src = reinterpret_cast<const float4 *>(w + (int64_t)m * w_stride + (int64_t)b * 128);
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          const float4 f = src[j];
+          v[4 * j] = f.x * S;  v[4 * j + 1] = f.y * S;  v[4 * j + 2] = f.z * S;  v[4 * j + 3] = f.w * S;
+        }
+      }
+    }
+    split_store32(v, ah + ((int64_t)m * kb32 + b) * 32, al + ((int64_t)m * kb32 + b) * 32);
+  }
+}
+
+int launch_dequant_hilo(int w_type, const void *w, int64_t w_stride, void *ah, void *al, int64_t M, int64_t Mpad,
+                        int64_t K, cudaStream_t st) {
+  const int64_t total = Mpad * (K / 32);
+  int blocks = (int)((total + 255) / 256);
+  const int cap = sm_count_cached() * 16;
+  if (blocks > cap) blocks = cap;
+  if (w_type == LAMMCU_TYPE_Q2_K)
+    dequant_hilo_kernel<LAMMCU_TYPE_Q2_K><<<blocks, 256, 0, st>>>((const uint8_t *)w, w_stride, (__half *)ah, (__half *)al,
+                                                               (int)M, (int)Mpad, (int)K);
+  else if (w_type == LAMMCU_TYPE_F32)
+    dequant_hilo_kernel<LAMMCU_TYPE_F32><<<blocks, 256, 0, st>>>((const uint8_t *)w, w_stride, (__half *)ah, (__half *)al,
+                                                              (int)M, (int)Mpad, (int)K);
+  else {
+    set_error("dequant_hilo: weight type %d not supported", w_type);
+    return LAMMCU_ERR_TYPE;
+  }
+  g_launch_count++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("dequant_hilo launch: %s", cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
+// Activations for the direct variant: Q8_K blocks (x.d is f32, ggml-common.h:316-321) or plain f32 rows
+// -> XH, XL fp16 [Npad][K] (natural order), row-normalised by 2^-E_n, and colscale[n] = 2^(E_n - kSoShift).
+template <int VT>
+__global__ void __launch_bounds__(256) prep_direct_kernel(const uint8_t *__restrict__ xq, int64_t xq_stride,
+                                                         __half *__restrict__ xh, __half *__restrict__ xl,
+                                                         float *__restrict__ colscale, int N, int Npad, int K) {
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const int kb32 = K / 32;
+  for (int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; n < Npad; n += warps) {
+    const uint8_t *row = xq + (int64_t)n * xq_stride;
+    float vmax = 0.f;                                   // upper bound of |value| in the row
+    if (n < N) {
+      if constexpr (VT == LAMMCU_TYPE_Q8_K) {
+        for (int sb = lane; sb < K / 256; sb += 32)
+          vmax = fmaxf(vmax, fabsf(*reinterpret_cast<const float *>(row + (int64_t)sb * 292)) * 128.f);
+      } else {
+        const float *x = reinterpret_cast<const float *>(row);
+        for (int k = lane; k < K; k += 32) vmax = fmaxf(vmax, fabsf(x[k]));
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    int E = 0;
+    if (vmax > 0.f && vmax < 3.0e38f) E = ilogbf(vmax) - 10;       // |v| 2^-E < 2^11
+    const float down = ldexpf(1.0f, -E);
+    if (lane == 0) colscale[n] = ldexpf(1.0f, E - kSoShift);
+    for (int b = lane; b < kb32; b += 32) {
+      float v[32];
+#pragma unroll
+      for (int l = 0; l < 32; l++) v[l] = 0.f;
+      if (n < N) {
+        if constexpr (VT == LAMMCU_TYPE_Q8_K) {
+          const uint8_t *blk = row + (int64_t)(b >> 3) * 292;
+          const float d = *reinterpret_cast<const float *>(blk) * down;
+          const uint32_t *qs = reinterpret_cast<const uint32_t *>(blk + 4 + 32 * (b & 7));
+#pragma unroll
+          for (int j = 0; j < 8; j++) {
+            const uint32_t qw = qs[j];
+#pragma unroll
+            for (int e = 0; e < 4; e++) v[4 * j + e] = d * (float)(int)(signed char)((qw >> (8 * e)) & 0xffu);
+          }
+        } else {
+          const float4 *src = reinterpret_cast<const float4 *>(row + (int64_t)b * 128);
+#pragma unroll
+          for (int j = 0; j < 8; j++) {
+            const float4 f = src[j];
+            v[4 * j] = f.x * down;  v[4 * j + 1] = f.y * down;  v[4 * j + 2] = f.z * down;  v[4 * j + 3] = f.w * down;
+          }
+        }
+      }
+      split_store32(v, xh + ((int64_t)n * kb32 + b) * 32, xl + ((int64_t)n * kb32 + b) * 32);
+    }
+  }
+}
+
+int launch_prep_direct(int vt, const void *xq, int64_t xq_stride, void *xh, void *xl, float *colscale, int64_t N,
+                       int64_t Npad, int64_t K, cudaStream_t st) {
+  int blocks = (int)((Npad + 7) / 8);
+  const int cap = sm_count_cached() * 8;
+  if (blocks > cap) blocks = cap;
+  if (vt == LAMMCU_TYPE_Q8_K)
+    prep_direct_kernel<LAMMCU_TYPE_Q8_K><<<blocks, 256, 0, st>>>((const uint8_t *)xq, xq_stride, (__half *)xh, (__half *)xl,
+                                                              colscale, (int)N, (int)Npad, (int)K);
+  else if (vt == LAMMCU_TYPE_F32)
+    prep_direct_kernel<LAMMCU_TYPE_F32><<<blocks, 256, 0, st>>>((const uint8_t *)xq, xq_stride, (__half *)xh, (__half *)xl,
+                                                             colscale, (int)N, (int)Npad, (int)K);
+  else {
+    set_error("prep_direct: activation type %d not supported", vt);
+    return LAMMCU_ERR_TYPE;
+  }
+  g_launch_count++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("prep_direct launch: %s", cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
 }  // namespace lamm

@@ -332,6 +332,157 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
   if (warp == 2) tmem_dealloc(tmem_base, 128);
 }
 
+// ---- direct variant: both operands pre-split in global memory --------------------------------
+// Q2_K and F32 weights: lamm_gemm_prep.cu dequantizes W once per call into fp16 hi / lo [M][K]
+// (w * 2^kSoShift; Q2_K: w = d * sc * q - dmin * mn evaluated in f32, which is the reference's
+// d*isum - dmin*summs regrouped, src/lamm_kernel_q2_k.hpp:28-75), so the mainloop is a plain TMA-fed
+// GEMM: no unpack warps, no extra stages.  Same three MMAs per K step, same epilogue.
+constexpr int kDirStages = 3;
+
+__global__ void __launch_bounds__(192, 1)
+gemm_direct_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant__ CUtensorMap tm_al,
+                   const __grid_constant__ CUtensorMap tm_xh, const __grid_constant__ CUtensorMap tm_xl, const SoParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  constexpr int kStageBytes = 4 * kTileBytes;                     // Ah, Al, Bh, Bl
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kDirStages * kStageBytes);
+  uint64_t *full = bars, *empty = bars + kDirStages, *acc_full = bars + 2 * kDirStages;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 8);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles = (p.N + GN - 1) / GN;
+  const int m0 = (blockIdx.x / n_tiles) * GM, n0 = (blockIdx.x % n_tiles) * GN;
+  const int n_stages = p.K / GK;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kDirStages; i++) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    mbar_init(acc_full, 1);
+    fence_barrier_init();
+    prefetch_tmap(&tm_ah);
+    prefetch_tmap(&tm_al);
+    prefetch_tmap(&tm_xh);
+    prefetch_tmap(&tm_xl);
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 128);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int st = 0; st < n_stages; st++) {
+        const int s = st % kDirStages;
+        uint8_t *stage = smem + s * kStageBytes;
+        mbar_wait(&empty[s], ((uint32_t)(st / kDirStages) & 1u) ^ 1u);
+        mbar_arrive_expect_tx(&full[s], (uint32_t)kStageBytes);
+        tma_load_2d(stage, &tm_ah, st * GK, m0, &full[s]);
+        tma_load_2d(stage + kTileBytes, &tm_al, st * GK, m0, &full[s]);
+        tma_load_2d(stage + 2 * kTileBytes, &tm_xh, st * GK, n0, &full[s]);
+        tma_load_2d(stage + 3 * kTileBytes, &tm_xl, st * GK, n0, &full[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      for (int st = 0; st < n_stages; st++) {
+        const int s = st % kDirStages;
+        mbar_wait(&full[s], (uint32_t)(st / kDirStages) & 1u);
+        tc_fence_after();
+        const uint32_t base = smem_u32(smem + s * kStageBytes);
+        const uint64_t ah = make_sw128_desc(base), al = make_sw128_desc(base + kTileBytes);
+        const uint64_t bh = make_sw128_desc(base + 2 * kTileBytes), bl = make_sw128_desc(base + 3 * kTileBytes);
+#pragma unroll
+        for (int kk = 0; kk < 4; kk++) {
+          const uint64_t o = (uint64_t)(kk * 2);
+          umma_f16(tmem_base, ah + o, bh + o, kIdescF16, (st | kk) ? 1u : 0u);
+          umma_f16(tmem_base, ah + o, bl + o, kIdescF16, 1u);
+          umma_f16(tmem_base, al + o, bh + o, kIdescF16, 1u);
+        }
+        umma_commit(&empty[s]);
+      }
+      umma_commit(acc_full);
+    }
+  } else {
+    // epilogue warps 2..5: TMEM lane quarter = warp & 3
+    const int q4 = warp & 3, row = q4 * 32 + lane, m = m0 + row;
+    mbar_wait(acc_full, 0u);
+    tc_fence_after();
+    const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16);
+#pragma unroll 2
+    for (int c16 = 0; c16 < 8; c16++) {
+      uint32_t v[16];
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+            "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+          : "r"(tbase + (uint32_t)(c16 * 16))
+          : "memory");
+      tmem_ld_wait();
+      if (m < p.M) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+          const int n = n0 + c16 * 16 + i;
+          if (n < p.N) p.c[(int64_t)n * p.ldc + m] = __uint_as_float(v[i]) * __ldg(p.colscale + n);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 128);
+}
+
+size_t gemm_direct_ws_bytes(int64_t M, int64_t N, int64_t K) {
+  const int64_t npad = (N + GN - 1) / GN * GN, mpad = (M + GM - 1) / GM * GM;
+  return (size_t)(2 * mpad * K * 2 + 2 * npad * K * 2 + npad * 4 + 2048);
+}
+
+// W: Q2_K blocks or f32; X: Q8_K blocks (Q2_K) or f32 (F32 weights)
+int launch_gemm_direct(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
+                       int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st) {
+  const int64_t npad = (N + GN - 1) / GN * GN, mpad = (M + GM - 1) / GM * GM;
+  uint8_t *base = (uint8_t *)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
+  void *ah = base, *al = base + mpad * K * 2;
+  void *xh = base + 2 * mpad * K * 2, *xl = (uint8_t *)xh + npad * K * 2;
+  float *colscale = (float *)((uint8_t *)xl + npad * K * 2);
+  int rc = launch_dequant_hilo(w_type, w, w_stride, ah, al, M, mpad, K, st);
+  if (rc) return rc;
+  rc = launch_prep_direct(type_info(w_type).vec_dot, xq, xq_stride, xh, xl, colscale, N, npad, K, st);
+  if (rc) return rc;
+  CUtensorMap tm_ah, tm_al, tm_xh, tm_xl;
+  if ((rc = make_map_2d(&tm_ah, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, ah, (uint64_t)K, (uint64_t)mpad, (uint64_t)K * 2, GK, GM,
+                        CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = make_map_2d(&tm_al, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, al, (uint64_t)K, (uint64_t)mpad, (uint64_t)K * 2, GK, GM,
+                        CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = make_map_2d(&tm_xh, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, xh, (uint64_t)K, (uint64_t)npad, (uint64_t)K * 2, GK, GN,
+                        CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = make_map_2d(&tm_xl, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, xl, (uint64_t)K, (uint64_t)npad, (uint64_t)K * 2, GK, GN,
+                        CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  SoParams p;
+  p.colscale = colscale;  p.c = c;  p.ldc = ldc;
+  p.M = (int)M;  p.N = (int)N;  p.Npad = (int)npad;  p.K = (int)K;
+  constexpr int smem = kDirStages * 4 * kTileBytes + 256 + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) {
+      set_error("gemm_direct: cudaFuncSetAttribute(%d): %s", smem, cudaGetErrorString(e));
+      return LAMMCU_ERR_CUDA;
+    }
+    attr_set = true;
+  }
+  const int tiles = (int)((mpad / GM) * (npad / GN));
+  gemm_direct_kernel<<<tiles, 192, smem, st>>>(tm_ah, tm_al, tm_xh, tm_xl, p);
+  g_launch_count++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("gemm_direct launch: %s", cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
 // ---- host side ------------------------------------------------------------------------------
 template <int WT>
 static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CUtensorMap &tm_xl,

@@ -27,15 +27,21 @@ GEMM_SHAPES = [  # (M, N, K)
 ]
 
 
-@pytest.mark.parametrize("t", TC_TYPES)
+@pytest.mark.parametrize("t", TC_TYPES + [Q2_K, F32])
 @pytest.mark.parametrize("m,n,k", GEMM_SHAPES)
-def test_gemm_vs_oracle(gpu, oracle, t, m, n, k):
+def test_gemm_vs_oracle(gpu, oracle, t, m, n, k, gemm_mode):
     w = weights(oracle, t, m, k, seed=m + 5 * n + k)
     x = make_x(np.random.default_rng(n * 3 + k), n, k)
     want = oracle.mul_mat(t, w, x)
     gpu.lib().lammcu_launch_count_reset()
-    got = gpu.mul_mat(t, dev(w), dev(x)).cpu().numpy()
-    assert gpu.lib().lammcu_launch_count() == 3, "prefill = quantize + operand prep + tcgen05 GEMM"
+    wd = dev(w)
+    got = gpu.mul_mat(t, wd if t != F32 else wd.view(__import__("torch").float32), dev(x)).cpu().numpy()
+    launches = gpu.lib().lammcu_launch_count()
+    if t in TC_TYPES:
+        assert launches == 3, "prefill = quantize + operand prep + tcgen05 GEMM"
+    elif gemm_mode == "scaled" and k % 256 == 0:
+        # Q2_K / F32 weights: (quantize +) weight dequantize + operand prep + TMA-fed tcgen05 GEMM
+        assert launches == (4 if t == Q2_K else 3)
     err = np.abs(got - want).max()
     assert err <= tol_c(want, k), f"{TYPE_NAMES[t]} {m}x{n}x{k}: err {err} tol {tol_c(want, k)}"
 
