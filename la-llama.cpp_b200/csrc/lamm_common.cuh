@@ -148,7 +148,11 @@ int launch_gemm_prep_so(int vt, int perm, const void *xq, int64_t xq_stride, voi
 constexpr int kSoShift = 6;      // scaled-operand GEMM: A carries 2^kSoShift, B carries 2^-kSoShift
 size_t gemm_so_ws_bytes(int64_t N, int64_t K);
 int launch_gemm_so(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
-                   int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st);
+                   int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st, const float *x = nullptr,
+                   int64_t ldx = 0);
+int launch_quant_prep_so(int vt, int perm, const float *x, int64_t ldx, void *xq_out, int64_t xq_stride, void *xh,
+                         void *xl, void *sh, float *colscale, int64_t N, int64_t Npad, int64_t K, cudaStream_t st);
+bool gemm_tc_supported(int w_type, const void *w, int64_t w_stride, int64_t M, int64_t N, int64_t K);
 size_t gemm_direct_ws_bytes(int64_t M, int64_t N, int64_t K);
 int launch_gemm_direct(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
                        int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st);

@@ -19,6 +19,7 @@
 //   sxT : f32 [Kb][Npad]   f32(s_x) (q8_1 only)
 // Rows n >= N are written as zeros.
 #include "lamm_common.cuh"
+#include "lamm_quant_dev.cuh"
 
 
 namespace lamm {
@@ -217,6 +218,144 @@ int launch_gemm_prep_so(int vt, int perm, const void *xq, int64_t xq_stride, voi
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("gemm_prep_so launch: %s", cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
+// Fused activation quantize + operand prep: f32 X -> (bit-exact Q8_0 / Q8_1 quantization, in registers)
+// -> XH, XL, SH, colscale as gemm_prep_so_kernel writes them; the ggml-layout Xq is only written when
+// the caller wants it (xq_out != NULL).  Same arithmetic as quantize_row_q8_{0,1}_reference
+// (ggml-quants.c:1182-1205, 1396-1429): d = amax / 127, id = 1 / d, q = roundf(x * id), y.d = fp16(d),
+// y.s = fp16(sum * d).  One warp per row, one thread per 32-block.
+template <int VT, int PERM>
+__global__ void __launch_bounds__(256) quant_prep_so_kernel(const float *__restrict__ x, int64_t ldx,
+                                                           uint8_t *__restrict__ xq_out, int64_t xq_stride,
+                                                           __half *__restrict__ xh, __half *__restrict__ xl,
+                                                           __half *__restrict__ sh, float *__restrict__ colscale,
+                                                           int N, int Npad, int kb, int kbpad) {
+  constexpr int XB = (VT == LAMMCU_TYPE_Q8_0) ? 34 : 36;
+  __shared__ float red[8];
+  const int lane = threadIdx.x & 31, tid = threadIdx.x;
+  for (int n = blockIdx.x; n < Npad; n += gridDim.x) {          // one CTA per activation row
+    const float *row = x + (int64_t)n * ldx;
+    float dmax = 0.f;
+    if (n < N) {
+      for (int b = tid; b < kb; b += 256) {
+        const float4 *src = reinterpret_cast<const float4 *>(row + (int64_t)b * 32);
+        float amax = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          const float4 f = src[j];
+          amax = fmaxf(amax, fmaxf(fmaxf(fabsf(f.x), fabsf(f.y)), fmaxf(fabsf(f.z), fabsf(f.w))));
+        }
+        dmax = fmaxf(dmax, __half2float(__float2half_rn(__fdiv_rn(amax, 127.0f))));
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+    __syncthreads();                                              // red[] of the previous row is consumed
+    if (lane == 0) red[tid >> 5] = dmax;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 8; i++) dmax = fmaxf(dmax, red[i]);
+    int E = 0;
+    if (dmax > 0.f && dmax < 3.0e38f) E = ilogbf(dmax) - 3;
+    const float down = ldexpf(1.0f, -E);
+    if (tid == 0) colscale[n] = ldexpf(1.0f, E - kSoShift);
+    for (int b = tid; b < kbpad; b += 256) {
+      if (b >= kb) {
+        if (VT == LAMMCU_TYPE_Q8_1) sh[(int64_t)n * kbpad + b] = __float2half_rn(0.f);
+        continue;
+      }
+      int q[32];
+      float dsc = 0.f;
+      __half hd = __float2half_rn(0.f), hs = __float2half_rn(0.f);
+#pragma unroll
+      for (int e = 0; e < 32; e++) q[e] = 0;
+      if (n < N) {
+        const float4 *src = reinterpret_cast<const float4 *>(row + (int64_t)b * 32);
+        float v[32];
+        float amax = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          const float4 f = src[j];
+          v[4 * j] = f.x;  v[4 * j + 1] = f.y;  v[4 * j + 2] = f.z;  v[4 * j + 3] = f.w;
+          amax = fmaxf(amax, fmaxf(fmaxf(fabsf(f.x), fabsf(f.y)), fmaxf(fabsf(f.z), fabsf(f.w))));
+        }
+        const float d = __fdiv_rn(amax, 127.0f);
+        const float id = (d != 0.0f) ? __fdiv_rn(1.0f, d) : 0.0f;
+        int sum = 0;
+#pragma unroll
+        for (int e = 0; e < 32; e++) {
+          q[e] = round_half_away_small(__fmul_rn(v[e], id));
+          sum += q[e];
+        }
+        hd = __float2half_rn(d);
+        if (VT == LAMMCU_TYPE_Q8_1) hs = __float2half_rn(__fmul_rn((float)sum, d));
+        dsc = __half2float(hd) * down;
+        if (xq_out) {                                     // ggml block, for the bit-exact check
+          uint8_t *blk = xq_out + (int64_t)n * xq_stride + (int64_t)b * XB;
+          uint16_t *o16 = reinterpret_cast<uint16_t *>(blk);
+          o16[0] = __half_as_ushort(hd);
+          int off = 1;
+          if (VT == LAMMCU_TYPE_Q8_1) { o16[1] = __half_as_ushort(hs); off = 2; }
+#pragma unroll
+          for (int e = 0; e < 16; e++)
+            o16[off + e] = (uint16_t)((uint32_t)(q[2 * e] & 0xff) | ((uint32_t)(q[2 * e + 1] & 0xff) << 8));
+        }
+      }
+      auto el = [&](int e) -> float { return __fmul_rn(dsc, (float)q[e]); };
+      uint4 *dh = reinterpret_cast<uint4 *>(xh + ((int64_t)n * kb + b) * 32);
+      uint4 *dl = reinterpret_cast<uint4 *>(xl + ((int64_t)n * kb + b) * 32);
+#pragma unroll
+      for (int w = 0; w < 4; w++) {
+        float f[8];
+        if constexpr (PERM == 1) {
+          f[0] = el(4 * w);      f[1] = el(4 * w + 2);      f[2] = el(16 + 4 * w);     f[3] = el(16 + 4 * w + 2);
+          f[4] = el(4 * w + 1);  f[5] = el(4 * w + 3);      f[6] = el(16 + 4 * w + 1); f[7] = el(16 + 4 * w + 3);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; j++) f[j] = el(8 * w + j);
+        }
+        uint32_t hw[4], lw[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          const __half h0 = __float2half_rn(f[2 * j]), h1 = __float2half_rn(f[2 * j + 1]);
+          const __half l0 = __float2half_rn(f[2 * j] - __half2float(h0));
+          const __half l1 = __float2half_rn(f[2 * j + 1] - __half2float(h1));
+          hw[j] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+          lw[j] = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
+        }
+        dh[w] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+        dl[w] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+      }
+      if (VT == LAMMCU_TYPE_Q8_1) sh[(int64_t)n * kbpad + b] = __float2half_rn(__half2float(hs) * down);
+    }
+  }
+}
+
+int launch_quant_prep_so(int vt, int perm, const float *x, int64_t ldx, void *xq_out, int64_t xq_stride, void *xh,
+                         void *xl, void *sh_, float *colscale, int64_t N, int64_t Npad, int64_t K, cudaStream_t st) {
+  const int kb = (int)(K / 32), kbpad = (kb + 63) / 64 * 64;
+  __half *sh = (__half *)sh_;
+  int blocks = (int)Npad;
+  const int cap = sm_count_cached() * 16;
+  if (blocks > cap) blocks = cap;
+  __half *h = (__half *)xh, *l = (__half *)xl;
+  uint8_t *xo = (uint8_t *)xq_out;
+#define LAMM_QP(VT_, P_) quant_prep_so_kernel<VT_, P_><<<blocks, 256, 0, st>>>(x, ldx, xo, xq_stride, h, l, sh, colscale, (int)N, (int)Npad, kb, kbpad)
+  if (vt == LAMMCU_TYPE_Q8_1) { if (perm) LAMM_QP(LAMMCU_TYPE_Q8_1, 1); else LAMM_QP(LAMMCU_TYPE_Q8_1, 0); }
+  else if (vt == LAMMCU_TYPE_Q8_0) { if (perm) LAMM_QP(LAMMCU_TYPE_Q8_0, 1); else LAMM_QP(LAMMCU_TYPE_Q8_0, 0); }
+  else {
+    set_error("quant_prep_so: activation type %d not supported", vt);
+    return LAMMCU_ERR_TYPE;
+  }
+#undef LAMM_QP
+  g_launch_count++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("quant_prep_so launch: %s", cudaGetErrorString(e));
     return LAMMCU_ERR_CUDA;
   }
   return LAMMCU_OK;

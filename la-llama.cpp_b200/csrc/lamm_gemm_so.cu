@@ -516,8 +516,9 @@ size_t gemm_so_ws_bytes(int64_t N, int64_t K) {
 }
 
 // xq: quantized activations (ggml blocks, row stride xq_stride); ws: gemm_so_ws_bytes() of scratch
+// or x != NULL: f32 activations, quantized on the fly (the ggml-layout Xq is written to xq iff xq != NULL)
 int launch_gemm_so(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
-                   int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st) {
+                   int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st, const float *x, int64_t ldx) {
   const TypeInfo ti = type_info(w_type);
   const int64_t npad = (N + GN - 1) / GN * GN, kb = K / 32, kbpad = (kb + 63) / 64 * 64;
   uint8_t *base = (uint8_t *)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
@@ -525,7 +526,9 @@ int launch_gemm_so(int w_type, const void *w, int64_t w_stride, const void *xq, 
   void *sh = base + 2 * npad * K * 2;
   float *colscale = (float *)((uint8_t *)sh + npad * kbpad * 2);
   const int perm = (w_type == LAMMCU_TYPE_Q8_0) ? 0 : 1;
-  int rc = launch_gemm_prep_so(ti.vec_dot, perm, xq, xq_stride, xh, xl, sh, colscale, N, npad, K, st);
+  int rc = x ? launch_quant_prep_so(ti.vec_dot, perm, x, ldx, const_cast<void *>(xq), xq_stride, xh, xl, sh, colscale, N,
+                                    npad, K, st)
+             : launch_gemm_prep_so(ti.vec_dot, perm, xq, xq_stride, xh, xl, sh, colscale, N, npad, K, st);
   if (rc) return rc;
   CUtensorMap tm_w, tm_xh, tm_xl, tm_sh;
   // raw weights as uint16 [M][row_bytes / 2], box = 8 blocks x 128 rows
