@@ -48,6 +48,9 @@ struct DeviceState {
   void *hx = nullptr;  size_t hx_bytes = 0;      // pinned staging
   void *hc = nullptr;  size_t hc_bytes = 0;
   void *gws = nullptr; size_t gws_bytes = 0;     // prefill GEMM operand scratch
+  void *hll = nullptr; size_t hll_bytes = 0;     // host path: {value, tag} result pairs, pinned (polled by the CPU)
+  unsigned int *hctr = nullptr;                  // host path: arrival-ticket counter + status word
+  unsigned int hseq = 0;                         // host path: polled launches so far (= the last tag)
 };
 static DeviceState g_dev;
 static std::mutex g_mu;
@@ -185,6 +188,8 @@ int lammcu_shutdown(void) {
   if (g_dev.hx) cudaFreeHost(g_dev.hx);
   if (g_dev.hc) cudaFreeHost(g_dev.hc);
   if (g_dev.gws) cudaFree(g_dev.gws);
+  if (g_dev.hll) cudaFreeHost(g_dev.hll);
+  if (g_dev.hctr) cudaFree(g_dev.hctr);
   if (g_dev.sched) cudaFree(g_dev.sched);
   if (g_dev.stream) cudaStreamDestroy(g_dev.stream);
   g_dev = DeviceState();
@@ -599,6 +604,105 @@ static int copy_c_back(lammcu_weight_t w, int64_t N, float *c_host, int64_t ldc)
   return LAMMCU_OK;
 }
 
+// ---- the polled host path (decode-sized calls) ------------------------------------------------
+// A blocking H2D copy + launch + D2H copy + stream synchronize costs ~30 us per call, 6x the kernel.
+// For N = 1 the decode kernel instead stores its results as {f32 value, u32 tag} pairs (the multi-GPU
+// "LL" format, here with the HOST as the only peer) into pinned memory and the calling thread polls
+// the tags while it copies the values out: no D2H copy, no synchronize, completion is carried by the
+// data.  Mode 2 additionally lets the kernel read X straight from the pinned staging buffer
+// (no H2D copy operation in front of the launch).
+//   0: copy engine + cudaStreamSynchronize   1: H2D copy + polled result   2: X from pinned memory + polled result
+static int g_host_mode = [] {
+  const char *e = getenv("LAMM_HOST_MODE");
+  return e ? atoi(e) : 2;
+}();
+
+static int host_poll_setup(int64_t rows) {
+  if (!g_dev.hctr) {
+    CU_TRY(cudaMalloc(&g_dev.hctr, 256));
+    CU_TRY(cudaMemset(g_dev.hctr, 0, 256));
+    CU_TRY(cudaDeviceSynchronize());
+    g_dev.hseq = 0;
+  }
+  const size_t need = (size_t)rows * 8;
+  if (g_dev.hll_bytes < need) {
+    CU_TRY(cudaStreamSynchronize(g_dev.stream));
+    int rc = grow(&g_dev.hll, &g_dev.hll_bytes, need, true);
+    if (rc) return rc;
+    memset(g_dev.hll, 0, g_dev.hll_bytes);         // tag 0 is never issued
+  }
+  return LAMMCU_OK;
+}
+
+// after a failed or timed-out polled launch: re-derive the sequence number from the device counter
+static void host_poll_resync() {
+  cudaStreamSynchronize(g_dev.stream);
+  unsigned int ctr = 0;
+  if (cudaMemcpy(&ctr, g_dev.hctr, sizeof(ctr), cudaMemcpyDeviceToHost) == cudaSuccess)
+    g_dev.hseq = ctr / (unsigned int)sm_count_cached();
+  cudaGetLastError();
+}
+
+static int mul_mat_host_polled(lammcu_weight_t w, const float *x_host, float *c_host) {
+  const int64_t K = w->K, rows = w->row_end - w->row_begin;
+  int rc = host_poll_setup(rows);
+  if (rc) return rc;
+  const double t0 = now_us();
+  memcpy(g_dev.hx, x_host, (size_t)K * 4);
+  const double t1 = now_us();
+  const float *x_dev = (const float *)g_dev.hx;
+  if (g_host_mode == 1) {
+    CU_TRY(cudaMemcpyAsync(g_dev.xin, g_dev.hx, (size_t)K * 4, cudaMemcpyHostToDevice, g_dev.stream));
+    x_dev = (const float *)g_dev.xin;
+  }
+  const double t2 = now_us();
+  ShardInfo sh = {};
+  sh.ll_peer[0] = (unsigned long long *)g_dev.hll;
+  sh.arrive_ctr = g_dev.hctr;
+  sh.status = g_dev.hctr + 2;
+  sh.n_peer = 1;
+  rc = launch_decode(w->type, w->dev, w->stride, x_dev, nullptr, nullptr, nullptr, rows, K, g_dev.stream, &sh);
+  const double t3 = now_us();
+  if (rc) { host_poll_resync(); return rc; }
+  const unsigned int tag = ++g_dev.hseq;
+  const volatile unsigned long long *ll = (const volatile unsigned long long *)g_dev.hll;
+  float *out = c_host + w->row_begin;
+  uint32_t spins = 0;
+  double t_first = 0;
+  for (int64_t i = 0; i < rows; i++) {
+    unsigned long long v;
+    while ((unsigned int)((v = ll[i]) >> 32) != tag) {
+      __builtin_ia32_pause();
+      if ((++spins & 0xfffu) == 0) {
+        const double now = now_us();
+        if (t_first == 0) t_first = now;
+        else if (now - t_first > 2e6 || cudaStreamQuery(g_dev.stream) != cudaErrorNotReady) {
+          // finished (or failed) without delivering row i, or 2 s without progress
+          cudaError_t e = cudaStreamSynchronize(g_dev.stream);
+          if ((unsigned int)(ll[i] >> 32) == tag) continue;          // it did arrive
+          set_error("mul_mat_host: result row %lld never arrived (%s)", (long long)i, cudaGetErrorString(e));
+          host_poll_resync();
+          return LAMMCU_ERR_CUDA;
+        }
+      }
+    }
+    const uint32_t bits = (uint32_t)v;
+    memcpy(out + i, &bits, 4);
+  }
+  const double t4 = now_us();
+  g_hp[0] += t1 - t0;  g_hp[1] += t2 - t1;  g_hp[2] += t3 - t2;  g_hp[3] += t4 - t3;  g_hp[5] += 1;
+  return LAMMCU_OK;
+}
+
+int lammcu_set_host_mode(int mode) {
+  if (mode < 0 || mode > 2) { set_error("set_host_mode: 0, 1 or 2"); return LAMMCU_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (g_dev.inited) cudaStreamSynchronize(g_dev.stream);
+  g_host_mode = mode;
+  return LAMMCU_OK;
+}
+int lammcu_get_host_mode(void) { return g_host_mode; }
+
 int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N, int64_t ldx,
                         float *c_host, int64_t ldc, void *xq_out_host) {
   int rc = ensure_init();
@@ -609,6 +713,9 @@ int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N, int64
   const size_t xbytes = (size_t)N * K * 4;
   if ((rc = grow(&g_dev.hx, &g_dev.hx_bytes, xbytes, true))) return rc;
   if ((rc = grow(&g_dev.xin, &g_dev.xin_bytes, xbytes, false))) return rc;
+  if (N == 1 && g_host_mode > 0 && !xq_out_host && g_decode_kernel &&
+      decode_supported(w->type, w->dev, w->stride, g_dev.hx, rows, K))
+    return mul_mat_host_polled(w, x_host, c_host);
   float *c_dev = nullptr;
   if ((rc = out_buffer(w, N, &c_dev))) return rc;
   const double t0 = now_us();

@@ -26,31 +26,38 @@ KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
 
 
 def launch_list(path, out):
-    rows = []
     with open(path) as f:
         text = f.read()
     start = text.index('"ID"')
+    per = {}                                       # launch id -> [name, grid, block, ns, dram read B, dram write B]
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     for r in csv.DictReader(io.StringIO(text[start:])):
+        e = per.setdefault(r["ID"], [r["Kernel Name"], r["Grid Size"], r["Block Size"], 0.0, 0.0, 0.0])
+        v = float(r["Metric Value"].replace(",", ""))
+        u = r["Metric Unit"]
         if r["Metric Name"] == "gpu__time_duration.sum":
-            v = float(r["Metric Value"].replace(",", ""))
-            if r["Metric Unit"].startswith("us"):
-                v *= 1e3
-            elif r["Metric Unit"].startswith("ms"):
-                v *= 1e6
-            rows.append((r["Kernel Name"], r["Grid Size"], r["Block Size"], v))
-    agg = defaultdict(lambda: [0, 0.0, 1e30, 0.0])
-    for name, grid, block, ns in rows:
+            e[3] = v * (1e3 if u.startswith("us") else 1e6 if u.startswith("ms") else 1.0)
+        elif r["Metric Name"] == "dram__bytes_read.sum":
+            e[4] = v * scale.get(u, 1.0)
+        elif r["Metric Name"] == "dram__bytes_write.sum":
+            e[5] = v * scale.get(u, 1.0)
+    agg = defaultdict(lambda: [0, 0.0, 1e30, 0.0, 0.0, 0.0])
+    for name, grid, block, ns, rd, wr in per.values():
         a = agg[(name, grid, block)]
-        a[0] += 1; a[1] += ns; a[2] = min(a[2], ns); a[3] = max(a[3], ns)
+        a[0] += 1; a[1] += ns; a[2] = min(a[2], ns); a[3] = max(a[3], ns); a[4] += rd; a[5] += wr
     tot = sum(a[1] for a in agg.values())
     with open(out, "w") as f:
-        f.write("# ncu launch list (--metrics gpu__time_duration.sum --clock-control none): per-launch times are\n"
-                "# cold-cache and serialised; the kernel's SHARE of the step is what must agree with bench.py\n")
-        f.write("kernel,grid,block,launches,total_us,avg_us,min_us,max_us,share\n")
+        f.write("# ncu launch list (--metrics gpu__time_duration.sum,dram__bytes_{read,write}.sum --clock-control none):\n"
+                "# per-launch times are cold-cache and serialised; the kernel's SHARE of the step is what must agree\n")
+        f.write("kernel,grid,block,launches,total_us,avg_us,min_us,max_us,share,avg_dram_read_MB,avg_dram_write_MB\n")
         for (name, grid, block), a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-            f.write('"%s","%s","%s",%d,%.1f,%.3f,%.3f,%.3f,%.4f\n' % (name, grid, block, a[0], a[1] / 1e3, a[1] / a[0] / 1e3,
-                                                                  a[2] / 1e3, a[3] / 1e3, a[1] / tot))
-    return len(rows)
+            f.write('"%s","%s","%s",%d,%.1f,%.3f,%.3f,%.3f,%.4f,%.3f,%.3f\n' % (
+                name, grid, block, a[0], a[1] / 1e3, a[1] / a[0] / 1e3, a[2] / 1e3, a[3] / 1e3, a[1] / tot,
+                a[4] / a[0] / 1e6, a[5] / a[0] / 1e6))
+        n = sum(a[0] for a in agg.values())
+        f.write("# all kernels: %d launches, avg dram read %.3f MB + write %.3f MB per launch\n" % (
+            n, sum(a[4] for a in agg.values()) / n / 1e6, sum(a[5] for a in agg.values()) / n / 1e6))
+    return len(per)
 
 
 def rep_summary(rep, out):
@@ -78,7 +85,8 @@ def main():
         if f.endswith(".ncu-rep"):
             k = rep_summary(os.path.join(src, f), os.path.join(here, "%s_ncu_%s.csv" % (tag, f[:-8])))
             print(f, k, "launches")
-    for f in ("bench.json", "sweep_decode_fused.jsonl", "sweep_gemm_n512.jsonl", "sweep_gemm_13b_n2048.jsonl", "pytest_gpu.log"):
+    for f in ("bench.json", "bench_nobatch.json", "bench_reference.json", "sweep_decode_fused.jsonl", "sweep_gemm_n512.jsonl",
+              "sweep_gemm_13b_n2048.jsonl", "sweep_gemm_30b_q5_0_n512.jsonl", "pytest_gpu.log"):
         p = os.path.join(src, f)
         if os.path.exists(p):
             with open(p) as a, open(os.path.join(here, "%s_%s" % (tag, f)), "w") as b:
