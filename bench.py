@@ -476,6 +476,8 @@ def run_cuda(args):
 
     # e2e leg: the drop-in operator on HOST buffers (rank 0 / N=1 only does the H2D/D2H variant;
     # with N>1 every rank runs it on its shard)
+    if args.host_mode is not None:
+        L.lib().lammcu_set_host_mode(args.host_mode)
     e2e = e2e_run(torch, L, t, ops, weights, shard, max(3, args.steps // 10), dist, dev, rank, world)
 
     if rank != 0:
@@ -588,6 +590,7 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
     d2h = sum((shard(m)[1] - shard(m)[0]) * 4 for _, m, k in ops)
     return {"value": steps / sec, "unit": "tok/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "steps": steps, "ms_per_step": sec / steps * 1e3, "per_call_phases": phases,
+            "host_mode": int(lib.lammcu_get_host_mode()),
             "api": "lamm_can_mul_mat + lamm_mul_mat(ggml_compute_params*, ggml_tensor*) on host tensors, "
                    "one synchronous call per matmul (225 per token); host wall clock",
             "note": "weights uploaded once at first use (registry keyed by src0->data); with N>1 the "
@@ -732,6 +735,8 @@ def main():
     ap.add_argument("--fmt", default="q4_1", choices=sorted(TYPE_IDS))
     ap.add_argument("--model", default="7b", choices=sorted(MODELS), help="chain shapes (the metric is quoted on 7b)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--host-mode", type=int, default=None, choices=[0, 1, 2],
+                    help="e2e leg: completion mode of the host path (lammcu_set_host_mode; default: the library's)")
     ap.add_argument("--no-batch", dest="batch", action="store_false",
                     help="N=1: one launch per matmul (225/token) instead of one per sibling group (129/token)")
     ap.add_argument("--chain", default="plain", choices=["plain", "ll"],

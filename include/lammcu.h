@@ -215,11 +215,12 @@ int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N,
  * [0] x memcpy to pinned, [1] H2D enqueue, [2] kernel enqueue, [3] wait for completion,
  * [4] C memcpy from pinned, [5] number of calls.                                        */
 void lammcu_host_profile(double *out8, int reset);
-/* How lammcu_mul_mat_host completes a decode-sized (N == 1) call:
- *   0  H2D copy, kernel, (zero-copy) result, cudaStreamSynchronize;
- *   1  H2D copy, kernel stores {f32 value, u32 tag} pairs into pinned host memory and the calling
- *      thread polls the tags while copying the values out (no synchronize, no D2H copy);
- *   2  (default) as 1, and the kernel reads X straight from the pinned staging buffer.
+/* How lammcu_mul_mat_host runs a decode-sized (N == 1) call:
+ *   0  (default) copy-engine H2D of X, kernel (zero-copy f32 result in pinned memory), cudaStreamSynchronize;
+ *   1  a staging kernel pulls X from the pinned buffer and the decode kernel follows it
+ *      as a programmatic dependent launch; cudaStreamSynchronize;
+ *   2  as 1, and the kernel stores {f32 value, u32 tag} pairs into pinned host memory which the
+ *      calling thread polls while copying the values out (no synchronize).
  * Results are identical in every mode.  Environment override at load time: LAMM_HOST_MODE.      */
 int lammcu_set_host_mode(int mode);
 int lammcu_get_host_mode(void);

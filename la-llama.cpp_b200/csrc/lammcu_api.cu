@@ -604,18 +604,32 @@ static int copy_c_back(lammcu_weight_t w, int64_t N, float *c_host, int64_t ldc)
   return LAMMCU_OK;
 }
 
-// ---- the polled host path (decode-sized calls) ------------------------------------------------
-// A blocking H2D copy + launch + D2H copy + stream synchronize costs ~30 us per call, 6x the kernel.
-// For N = 1 the decode kernel instead stores its results as {f32 value, u32 tag} pairs (the multi-GPU
-// "LL" format, here with the HOST as the only peer) into pinned memory and the calling thread polls
-// the tags while it copies the values out: no D2H copy, no synchronize, completion is carried by the
-// data.  Mode 2 additionally lets the kernel read X straight from the pinned staging buffer
-// (no H2D copy operation in front of the launch).
-//   0: copy engine + cudaStreamSynchronize   1: H2D copy + polled result   2: X from pinned memory + polled result
+// ---- the low-latency host path (decode-sized calls) ---------------------------------------------
+// A blocking H2D copy + launch + stream synchronize costs ~30 us per call, 6x the kernel: the copy
+// engine -> compute hand-over alone is ~8 us.  For N = 1:
+//   mode 0  copy engine H2D, kernel (zero-copy f32 result in pinned memory), cudaStreamSynchronize;
+//   mode 1  a small staging KERNEL pulls X from the pinned buffer over PCIe into HBM and the decode
+//           kernel follows it as a programmatic dependent launch (its weight prefetch overlaps the
+//           PCIe read); completion by cudaStreamSynchronize;
+//   mode 2  as 1, but the decode kernel stores {f32 value, u32 tag} pairs (the multi-GPU "LL" format
+//           with the HOST as the only peer) into pinned memory and the calling thread polls the tags
+//           while it copies the values out: completion is carried by the data.
 static int g_host_mode = [] {
   const char *e = getenv("LAMM_HOST_MODE");
-  return e ? atoi(e) : 2;
+  const int m = e ? atoi(e) : 0;
+  return (m < 0 || m > 2) ? 0 : m;
 }();
+
+__global__ void __launch_bounds__(256) stage_x_kernel(const float4 *__restrict__ src, float4 *__restrict__ dst, int n4) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i < n4) {
+    float4 v;
+    asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(src + i) : "memory");
+    dst[i] = v;
+  }
+}
 
 static int host_poll_setup(int64_t rows) {
   if (!g_dev.hctr) {
@@ -643,26 +657,40 @@ static void host_poll_resync() {
   cudaGetLastError();
 }
 
-static int mul_mat_host_polled(lammcu_weight_t w, const float *x_host, float *c_host) {
+// N == 1, operands the decode kernel takes; g_dev.hx / xin are large enough (caller)
+static int mul_mat_host_fast(lammcu_weight_t w, const float *x_host, float *c_host) {
   const int64_t K = w->K, rows = w->row_end - w->row_begin;
-  int rc = host_poll_setup(rows);
+  const bool polled = g_host_mode == 2;
+  int rc;
+  float *c_dev = nullptr;
+  if (polled) rc = host_poll_setup(rows);
+  else rc = out_buffer(w, 1, &c_dev);
   if (rc) return rc;
   const double t0 = now_us();
   memcpy(g_dev.hx, x_host, (size_t)K * 4);
   const double t1 = now_us();
-  const float *x_dev = (const float *)g_dev.hx;
-  if (g_host_mode == 1) {
-    CU_TRY(cudaMemcpyAsync(g_dev.xin, g_dev.hx, (size_t)K * 4, cudaMemcpyHostToDevice, g_dev.stream));
-    x_dev = (const float *)g_dev.xin;
-  }
+  const int n4 = (int)(K / 4);
+  stage_x_kernel<<<(n4 + 255) / 256, 256, 0, g_dev.stream>>>((const float4 *)g_dev.hx, (float4 *)g_dev.xin, n4);
+  g_launch_count++;
   const double t2 = now_us();
-  ShardInfo sh = {};
-  sh.ll_peer[0] = (unsigned long long *)g_dev.hll;
-  sh.arrive_ctr = g_dev.hctr;
-  sh.status = g_dev.hctr + 2;
-  sh.n_peer = 1;
-  rc = launch_decode(w->type, w->dev, w->stride, x_dev, nullptr, nullptr, nullptr, rows, K, g_dev.stream, &sh);
+  if (polled) {
+    ShardInfo sh = {};
+    sh.ll_peer[0] = (unsigned long long *)g_dev.hll;
+    sh.arrive_ctr = g_dev.hctr;
+    sh.status = g_dev.hctr + 2;
+    sh.n_peer = 1;
+    rc = launch_decode(w->type, w->dev, w->stride, (const float *)g_dev.xin, nullptr, nullptr, nullptr, rows, K,
+                       g_dev.stream, &sh);
+  } else {
+    rc = launch_decode(w->type, w->dev, w->stride, (const float *)g_dev.xin, nullptr, nullptr, c_dev, rows, K,
+                       g_dev.stream);
+  }
   const double t3 = now_us();
+  g_hp[0] += t1 - t0;  g_hp[1] += t2 - t1;  g_hp[2] += t3 - t2;
+  if (!polled) {
+    if (rc) return rc;
+    return copy_c_back(w, 1, c_host, rows);
+  }
   if (rc) { host_poll_resync(); return rc; }
   const unsigned int tag = ++g_dev.hseq;
   const volatile unsigned long long *ll = (const volatile unsigned long long *)g_dev.hll;
@@ -689,8 +717,7 @@ static int mul_mat_host_polled(lammcu_weight_t w, const float *x_host, float *c_
     const uint32_t bits = (uint32_t)v;
     memcpy(out + i, &bits, 4);
   }
-  const double t4 = now_us();
-  g_hp[0] += t1 - t0;  g_hp[1] += t2 - t1;  g_hp[2] += t3 - t2;  g_hp[3] += t4 - t3;  g_hp[5] += 1;
+  g_hp[3] += now_us() - t3;  g_hp[5] += 1;
   return LAMMCU_OK;
 }
 
@@ -714,8 +741,8 @@ int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N, int64
   if ((rc = grow(&g_dev.hx, &g_dev.hx_bytes, xbytes, true))) return rc;
   if ((rc = grow(&g_dev.xin, &g_dev.xin_bytes, xbytes, false))) return rc;
   if (N == 1 && g_host_mode > 0 && !xq_out_host && g_decode_kernel &&
-      decode_supported(w->type, w->dev, w->stride, g_dev.hx, rows, K))
-    return mul_mat_host_polled(w, x_host, c_host);
+      decode_supported(w->type, w->dev, w->stride, g_dev.xin, rows, K))
+    return mul_mat_host_fast(w, x_host, c_host);
   float *c_dev = nullptr;
   if ((rc = out_buffer(w, N, &c_dev))) return rc;
   const double t0 = now_us();

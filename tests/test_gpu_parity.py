@@ -183,6 +183,33 @@ def test_lamm_mul_mat_operator(gpu, oracle, t):
     assert can and np.array_equal(again, got)
 
 
+@pytest.mark.parametrize("t", QTYPES)
+def test_operator_decode_host_modes(gpu, oracle, t):
+    """N == 1 through the operator in every completion mode of the host path (stream synchronize,
+    polled {value, tag} pairs, polled + X read from pinned memory): identical bits, fresh X each
+    call (a stale staging buffer or tag would show), shapes of different row counts interleaved."""
+    lib = gpu.lib()
+    shapes = [(33, 4096), (1000, 1024), (4096, 4096), (515, 11008), (1, 256)]
+    ws = [weights(oracle, t, m, k, seed=7 * m + k) for m, k in shapes]
+    rng = np.random.default_rng(t)
+    default_mode = lib.lammcu_get_host_mode()
+    try:
+        for rep in range(3):
+            for (m, k), w in zip(shapes, ws):
+                x = rng.standard_normal((1, k)).astype(np.float32)
+                want = oracle.mul_mat(t, w, x)
+                got = {}
+                for mode in (0, 1, 2):
+                    assert lib.lammcu_set_host_mode(mode) == 0
+                    can, got[mode] = gpu.lamm_mul_mat_host(t, w, x, nth=1)
+                    assert can
+                assert np.abs(got[0] - want).max() <= tol_c(want, k), f"{TYPE_NAMES[t]} {m}x{k}"
+                assert np.array_equal(got[1], got[0]) and np.array_equal(got[2], got[0]), f"{TYPE_NAMES[t]} {m}x{k}"
+    finally:
+        lib.lammcu_set_host_mode(default_mode)
+    assert lib.lammcu_set_host_mode(3) != 0
+
+
 # ---------------------------------------------------------------- single-launch decode kernel (N == 1)
 DECODE_SHAPES = [(33, 4096), (1, 256), (7, 512), (300, 11008), (64, 5120), (50, 17920), (9, 6656),
                  (1185, 4096), (2500, 1024), (129, 13824)]
