@@ -385,13 +385,23 @@ def run_cuda(args):
     # (lammcu_mul_mat_batch_dev) unless --no-batch; same 225 matmuls, fewer dependency waits
     groups = []
     for item in plan:
-        if (groups and args.batch and not fused and world == 1 and t != 0 and groups[-1][0][3] == item[3]
+        if (groups and args.batch and (fused or world == 1) and t != 0 and groups[-1][0][3] == item[3]
                 and groups[-1][0][1:3] == item[1:3] and len(groups[-1]) < 4):
             groups[-1].append(item)
         else:
             groups.append([item])
 
     def one_token():
+        if args.batch and fused:
+            for grp in groups:
+                xin = x0 if grp[0][3] is None else buf[grp[0][3]]
+                if len(grp) == 1:
+                    wi, m, k, src, dst = grp[0]
+                    comm.mul_mat(t, weights[wi], xin, buf[dst], m, k)
+                else:
+                    comm.mul_mat_batch(t, [weights[g[0]] for g in grp], xin, [buf[g[4]] for g in grp],
+                                       [g[1] for g in grp], grp[0][2])
+            return
         if args.batch and not fused and world == 1 and t != 0:
             for grp in groups:
                 xin = x0 if grp[0][3] is None else buf[grp[0][3]]
@@ -499,7 +509,7 @@ def run_cuda(args):
         "dtype": "u4/u5/i8 weights x i8 activations -> i32 (dp4a), f32 scale-accumulate",
         "data": "synthetic", "config": dict(workload_config(args.fmt, world, "fused" if fused else "nccl", fused),
                                              launches_per_step=launches_per_token,
-                                             sibling_batching=bool(args.batch and not fused and world == 1 and t != 0)),
+                                             sibling_batching=bool(args.batch and (fused or world == 1) and t != 0)),
         "path_gbs": path_bytes * args.steps / (ms * 1e-3) / 1e9,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": TRAFFIC_PER_LAUNCH.get(args.fmt) if world == 1 else None,

@@ -184,6 +184,15 @@ int lammcu_mul_mat_sharded_dev(lammcu_comm_t comm, int w_type, const void *w_sha
                                int64_t w_stride_bytes, const void *x, int x_back,
                                void *const *c_ll_all, int64_t row_begin, int64_t rows,
                                int64_t K, void *stream);
+/* Sibling matrices that share the activation row (q/k/v, gate/up) as ONE sharded launch (one
+ * sequence number for all of them): matrix j has its own LL output vector; c_ll_all is the
+ * [count][world] array of their per-rank buffers (c_ll_all[j * world + g]); row_begin[j] / rows[j]
+ * describe this rank's shard of matrix j.  2 <= count <= 4 (1 forwards to the call above).      */
+int lammcu_mul_mat_sharded_batch_dev(lammcu_comm_t comm, int w_type, int count,
+                                     const void *const *w_shards, int64_t w_stride_bytes,
+                                     const void *x, int x_back, void *const *c_ll_all,
+                                     const int64_t *row_begin, const int64_t *rows, int64_t K,
+                                     void *stream);
 /* LL vector (local, produced `back` sharded launches ago, >= 1) -> plain f32 out[M],
  * waiting for every element.  An ordinary kernel: it starts after all earlier work on
  * the stream has completed.                                                           */

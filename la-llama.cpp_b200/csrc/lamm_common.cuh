@@ -130,6 +130,9 @@ struct ShardInfo {
   int x_back;                                      // ... produced this many sharded launches ago
   unsigned int *arrive_ctr, *status;
   int n_peer, my_rank, row_begin;
+  // with a BatchInfo: the LL output vector of sibling j on every rank and this rank's first row of it
+  unsigned long long *ll_batch[4][LAMMCU_MAX_RANKS];
+  int64_t row_begin_b[4];
 };
 // sibling batch: `count` (2..4) matrices of one type / K / row stride that share the activation row
 struct BatchInfo {

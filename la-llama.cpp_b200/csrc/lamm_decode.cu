@@ -60,6 +60,9 @@ struct DecodeParams {
   unsigned int *status;                    // local: [0] set to 1 if a poll timed out
   int x_back;                              // XM == 2: x was produced x_back sharded launches ago (>= 1)
   int n_peer, my_rank, row_begin;
+  // sharded sibling batch: matrix j of the batch has its own LL vector on every rank;
+  // llb[j][g] is a VIRTUAL base (pointer + first row of this rank's shard - rows before matrix j)
+  unsigned long long *llb[4][LAMMCU_MAX_RANKS];
 };
 
 // ---- integer dots -------------------------------------------------------------------
@@ -729,6 +732,15 @@ __device__ __forceinline__ void store_c(const DecodeParams &p, int row, float v,
     c[row] = v;
   } else {
     const unsigned long long pair = ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
+    if (p.nbatch > 1) {
+      int j = 0;
+      if (row >= p.mc[0]) j = 1;
+      if (row >= p.mc[1]) j = 2;
+      if (row >= p.mc[2]) j = 3;
+      for (int g = 0; g < p.n_peer; g++)
+        asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p.llb[j][g] + row), "l"(pair) : "memory");
+      return;
+    }
     for (int g = 0; g < p.n_peer; g++)
       asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p.ll_peer[g] + p.row_begin + row), "l"(pair) : "memory");
   }
@@ -1039,8 +1051,10 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
     for (int j = 0; j < 4; j++) {
       const int jj = j < bt->count ? j : bt->count - 1;      // unused slots repeat the last matrix
       p.wb[j] = (const uint8_t *)bt->w[jj] - first[jj] * w_stride;
-      p.cb[j] = bt->c[jj] - first[jj];
+      p.cb[j] = sh ? nullptr : bt->c[jj] - first[jj];
       if (j > 0) p.mc[j - 1] = j < bt->count ? (int)first[j] : 0x7fffffff;
+      if (sh)
+        for (int g = 0; g < sh->n_peer; g++) p.llb[j][g] = sh->ll_batch[jj][g] + sh->row_begin_b[jj] - first[jj];
     }
   }
   int xm = x ? 1 : 0;

@@ -418,6 +418,55 @@ int lammcu_mul_mat_sharded_dev(lammcu_comm_t comm, int w_type, const void *w_sha
                        pick_stream(stream), &sh);
 }
 
+// sibling matrices (q/k/v, gate/up) that share the activation row: ONE sharded launch, one sequence number
+int lammcu_mul_mat_sharded_batch_dev(lammcu_comm_t comm, int w_type, int count, const void *const *w_shards,
+                                     int64_t w_stride, const void *x, int x_back, void *const *c_ll_all,
+                                     const int64_t *row_begin, const int64_t *rows, int64_t K, void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!comm || !w_shards || !x || !c_ll_all || !row_begin || !rows || count < 1 || count > 4 || x_back < 0) {
+    set_error("mul_mat_sharded_batch: bad argument");
+    return LAMMCU_ERR_ARG;
+  }
+  if (count == 1)
+    return lammcu_mul_mat_sharded_dev(comm, w_type, w_shards[0], w_stride, x, x_back, c_ll_all, row_begin[0], rows[0], K, stream);
+  ShardInfo sh = {};
+  BatchInfo bt = {};
+  bt.count = count;
+  int64_t total = 0;
+  for (int j = 0; j < count; j++) {
+    if (!w_shards[j] || rows[j] <= 0 || row_begin[j] < 0) { set_error("mul_mat_sharded_batch: bad operand %d", j); return LAMMCU_ERR_ARG; }
+    if (!decode_supported(w_type, w_shards[j], w_stride, x, rows[j], K) ||
+        (((uintptr_t)total * (uintptr_t)w_stride) & 15) != 0 || (((uintptr_t)w_shards[j] ^ (uintptr_t)w_shards[0]) & 15) != 0) {
+      set_error("mul_mat_sharded_batch: needs a quantized type, K %% 256 == 0, 16-byte aligned operands and row counts "
+                "that keep every matrix at the same 16-byte phase");
+      return LAMMCU_ERR_SHAPE;
+    }
+    for (int g = 0; g < comm->world; g++) {
+      void *v = c_ll_all[j * comm->world + g];
+      if (!v || ((uintptr_t)v & 15)) { set_error("mul_mat_sharded_batch: output %d/%d NULL or misaligned", j, g); return LAMMCU_ERR_ALIGN; }
+      sh.ll_batch[j][g] = (unsigned long long *)v;
+    }
+    sh.row_begin_b[j] = row_begin[j];
+    bt.w[j] = w_shards[j];
+    bt.M[j] = rows[j];
+    total += rows[j];
+  }
+  if (total > 0x3fffffff) { set_error("mul_mat_sharded_batch: too many rows"); return LAMMCU_ERR_SHAPE; }
+  for (int g = 0; g < comm->world; g++) sh.ll_peer[g] = sh.ll_batch[0][g];
+  if (x_back > 0) {
+    sh.x_ll = (const unsigned long long *)x;
+    sh.x_back = x_back;
+  }
+  sh.arrive_ctr = comm->ctrs;
+  sh.status = comm->ctrs + 2;
+  sh.n_peer = comm->world;
+  sh.my_rank = comm->rank;
+  sh.row_begin = (int)row_begin[0];
+  return launch_decode(w_type, w_shards[0], w_stride, (const float *)x, nullptr, nullptr, nullptr, total, K,
+                       pick_stream(stream), &sh, &bt);
+}
+
 // LL vector -> plain f32 (waits for every element's tag): the last consumer of a sharded chain
 __global__ void ll_unpack_kernel(const unsigned int *arrive_ctr, int grid_fixed, int back, const unsigned long long *ll,
                                  float *out, int64_t M, unsigned int *status) {
@@ -534,6 +583,9 @@ int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K,
   e = cudaMemcpy2D(h->dev, rs, (const char *)w_host + row_begin * w_stride, (size_t)w_stride, rs,
                    (size_t)rows, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemset((char *)h->dev + h->bytes, 0, 256);
+  // A pageable-memory cudaMemcpy returns once the LAST chunk is staged, not when its DMA has landed, and
+  // the memset is asynchronous on the legacy stream; the compute stream is non-blocking, so order by hand.
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e != cudaSuccess) {
     set_error("weight_register: upload: %s", cudaGetErrorString(e));
     cudaFree(h->dev);

@@ -132,6 +132,32 @@ class Comm:
         out.seq = self.seq
         self.seq += 1
 
+    def mul_mat_batch(self, w_type, w_shards, x, outs, ms, k):
+        """Sibling matrices sharing the activation row x (q/k/v, gate/up) as ONE sharded launch:
+        w_shards[j] = this rank's rows of matrix j (ms[j] rows in total), outs[j] its LLVector."""
+        n = len(w_shards)
+        assert n == len(outs) == len(ms) and 1 <= n <= 4
+        if isinstance(x, LLVector):
+            assert x.seq is not None, "LL activation vector was never produced"
+            xp, back = x.local, self.seq - x.seq
+            assert back >= 1
+        else:
+            xp, back = (x if isinstance(x, int) else x.data_ptr()), 0
+        los = [row_shard(m, self.rank, self.world) for m in ms]
+        for w, (lo, hi), o, m in zip(w_shards, los, outs, ms):
+            assert w.shape[0] == hi - lo and o.m >= m
+        stride = w_shards[0].stride(0) * w_shards[0].element_size()
+        wp = (C.c_void_p * n)(*[w.data_ptr() for w in w_shards])
+        cp = (C.c_void_p * (n * self.world))(*[p for o in outs for p in o.ptrs])
+        rb = (C.c_int64 * n)(*[lo for lo, _ in los])
+        rows = (C.c_int64 * n)(*[hi - lo for lo, hi in los])
+        self.lamm.check(self.lamm.lib().lammcu_mul_mat_sharded_batch_dev(
+            self.handle, w_type, n, wp, stride, xp, back, cp, rb, rows, k, self.lamm._stream_ptr()),
+            "mul_mat_sharded_batch")
+        for o in outs:
+            o.seq = self.seq
+        self.seq += 1
+
     def unpack(self, torch, vec, m=None):
         """LLVector -> plain f32 cuda tensor [m] (waits for every element on the device)."""
         m = m or vec.m

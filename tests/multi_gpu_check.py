@@ -56,6 +56,37 @@ def main():
         print(f"rank {rank} type {t} {m}x{k}: err {err:.3g} (tol {tol:.3g}), chained err {err2:.3g} (tol {tol2:.3g}) "
               f"{'ok' if good else 'FAIL'}", flush=True)
         dist.barrier()
+    # sibling batch: three matrices sharing x in ONE sharded launch, then a launch that consumes the middle one
+    for t, ms, k in [(Q4_1, (4096, 4096, 4096), 4096), (Q5_0, (1024, 512, 2048), 2048), (Q2_K, (512, 1024), 1024)]:
+        rng = np.random.default_rng(11)
+        ws = [o.quantize_weights(t, rng.standard_normal((m, k)).astype(np.float32), seed=5 + j) for j, m in enumerate(ms)]
+        x = rng.standard_normal((1, k)).astype(np.float32)
+        xd = torch.from_numpy(x).cuda()
+        shards, outs = [], []
+        for w, m in zip(ws, ms):
+            lo, hi = sharding.row_shard(m, rank, world)
+            shards.append(torch.from_numpy(w[lo:hi].copy()).cuda())
+            outs.append(sharding.LLVector(L, dist, m))
+        for it in range(2):
+            comm.mul_mat_batch(t, shards, xd, outs, list(ms), k)
+        k2 = ms[1]
+        w2 = o.quantize_weights(Q4_1, np.random.default_rng(13).standard_normal((512, k2)).astype(np.float32))
+        lo2, hi2 = sharding.row_shard(512, rank, world)
+        c2 = sharding.LLVector(L, dist, 512)
+        comm.mul_mat(Q4_1, torch.from_numpy(w2[lo2:hi2].copy()).cuda(), outs[1], c2, 512, k2)
+        gots = [comm.unpack(torch, v) for v in outs]
+        got2_t = comm.unpack(torch, c2)
+        torch.cuda.synchronize()
+        dist.barrier()
+        good = True
+        for w, g in zip(ws, gots):
+            want = o.mul_mat(t, w, x)
+            good &= bool(np.abs(g.cpu().numpy()[None, :] - want).max() <= 1e-5 * np.sqrt(k) * np.abs(want).max())
+        want2 = o.mul_mat(Q4_1, w2, gots[1].cpu().numpy()[None, :])
+        good &= bool(np.abs(got2_t.cpu().numpy()[None, :] - want2).max() <= 1e-5 * np.sqrt(k2) * np.abs(want2).max())
+        ok &= good
+        print(f"rank {rank} type {t} sibling batch {ms}x{k}: {'ok' if good else 'FAIL'}", flush=True)
+        dist.barrier()
     ok &= not comm.timed_out()
     flag = torch.tensor([0 if ok else 1], device="cuda")
     dist.all_reduce(flag)
