@@ -224,15 +224,23 @@ int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N,
  * [0] x memcpy to pinned, [1] H2D enqueue, [2] kernel enqueue, [3] wait for completion,
  * [4] C memcpy from pinned, [5] number of calls.                                        */
 void lammcu_host_profile(double *out8, int reset);
-/* How lammcu_mul_mat_host runs a decode-sized (N == 1) call:
- *   0  (default) copy-engine H2D of X, kernel (zero-copy f32 result in pinned memory), cudaStreamSynchronize;
- *   1  a staging kernel pulls X from the pinned buffer and the decode kernel follows it
- *      as a programmatic dependent launch; cudaStreamSynchronize;
- *   2  as 1, and the kernel stores {f32 value, u32 tag} pairs into pinned host memory which the
- *      calling thread polls while copying the values out (no synchronize).
- * Results are identical in every mode.  Environment override at load time: LAMM_HOST_MODE.      */
+/* How lammcu_mul_mat_host (and lamm_mul_mat above it) runs a decode-sized (N == 1) call:
+ *   0  copy-engine H2D of X, one kernel launch, zero-copy f32 result in pinned memory,
+ *      cudaStreamSynchronize (~30 us per call, most of it launch + completion latency);
+ *   1  (default) the call is a JOB for a resident decode server: one long-lived launch (a CTA per
+ *      SM) that polls a mailbox in pinned host memory, pulls X over PCIe, runs the same decode
+ *      body and copies C back; the calling thread only writes X + 16 tagged words and polls one
+ *      word.  The server exits by itself after LAMM_SERVER_IDLE_US (default 200) without a job and
+ *      is relaunched on demand; every other entry point that needs the library's stream stops it
+ *      first.  lammcu_host_quiesce() stops it explicitly (e.g. before timing unrelated GPU work).
+ * Results are bit-identical in both modes.  Environment override at load time: LAMM_HOST_MODE.  */
 int lammcu_set_host_mode(int mode);
 int lammcu_get_host_mode(void);
+int lammcu_host_quiesce(void);
+/* Diagnostics (LAMM_SERVER_TRACE=1 at load time): device time stamps (ns) of the last 64 server
+ * jobs, out[64][8] = {job seen, X slice forwarded, X quantized, CTA 0 done, last CTA arrived,
+ * result published, 0, 0}.  Stops the server.                                                  */
+int lammcu_server_trace(unsigned long long *out512);
 /* same, activations already quantized on the host (src1->type == vec_dot_type) */
 int lammcu_mul_mat_q_host(lammcu_weight_t w, const void *xq_host,
                           int64_t xq_stride_bytes, int64_t N, float *c_host,

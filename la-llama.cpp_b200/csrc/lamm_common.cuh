@@ -134,6 +134,25 @@ struct ShardInfo {
   unsigned long long *ll_batch[4][LAMMCU_MAX_RANKS];
   int64_t row_begin_b[4];
 };
+// resident decode server (lamm_decode.cu): jobs arrive through a mailbox in pinned host memory
+constexpr int kSrvWords = 16;      // 32-bit words of a job, each posted as a {word, tag} pair
+constexpr int kSrvStagers = 8;     // CTAs that pull the activation row over PCIe
+struct ServerParams {
+  const unsigned long long *mbox_host;   // pinned: kSrvWords pairs written by the CPU
+  unsigned long long *mbox_dev;          // device: the same pairs, forwarded by CTA 0
+  const float *x_host;                   // pinned: activation row of the current job
+  unsigned long long *x_ll;              // device: the row as {value, tag} pairs
+  float *c_dev;                          // device: result
+  float *c_host;                         // pinned: result, copied out by the last CTA to finish
+  volatile unsigned int *done_host;      // pinned: [0] tag of the last finished job, [1] tag the server gave up waiting for
+  unsigned int *done_ctr;                // device: arrival tickets
+  unsigned int *status;                  // device: set on a poll time-out
+  unsigned int seq0;                     // first job tag this launch serves
+  unsigned int idle_ns;                  // exit after this long without a job
+  unsigned long long *trace;             // optional: [64 jobs][8] globaltimer stamps (diagnostics)
+};
+int decode_server_job(int w_type, const void *w, int64_t w_stride, int64_t M, int64_t K, unsigned int *words);
+int launch_decode_server(int w_type, const ServerParams &sp, cudaStream_t st);
 // sibling batch: `count` (2..4) matrices of one type / K / row stride that share the activation row
 struct BatchInfo {
   int count;

@@ -746,9 +746,20 @@ __device__ __forceinline__ void store_c(const DecodeParams &p, int row, float v,
   }
 }
 
-template <int WT, int XM>
-__global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const DecodeParams p) {
-  extern __shared__ __align__(128) uint8_t smem[];
+__device__ __forceinline__ void srv_stamp(const ServerParams *sp, unsigned int job, int e) {
+  if (sp->trace && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    sp->trace[(size_t)(job & 63u) * 8 + e] = t;
+  }
+}
+
+// SERVER: the body runs as one job of the resident kernel (decode_server_kernel below): bid / nblk
+// are the job's virtual grid, the activations arrive as {value, tag} pairs staged from pinned host
+// memory by the first kSrvStagers CTAs, and the ring barriers are invalidated for the next job.
+template <int WT, int XM, bool SERVER>
+__device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *smem, const int bid, const int nblk,
+                                              const ServerParams *sp, const unsigned int job_tag) {
   constexpr bool kQ2K = (WT == LAMMCU_TYPE_Q2_K);
   constexpr int VT = type_info(WT).vec_dot;
   constexpr int NW = kQ2K ? 11 : DecFmt<WT>::NW;
@@ -766,8 +777,8 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
   constexpr int unit_bytes = kQ2K ? 42 : 4 * type_info(WT).size;
   const uint32_t seg_off = kQ2K ? (uint32_t)(u0 >> 1) * 84u : (uint32_t)u0 * unit_bytes;
   const uint32_t seg_bytes = kQ2K ? (uint32_t)((seg_n + 1) >> 1) * 84u : (uint32_t)seg_n * unit_bytes;
-  const int row0 = blockIdx.x + gridDim.x * rg, row_step = gridDim.x * p.RG;
-  const int n_rows = (row0 < p.M) ? (p.M - 1 - row0) / row_step + 1 : 0;
+  const int row0 = bid + nblk * rg, row_step = nblk * p.RG;
+  const int n_rows = (row0 < p.M && (!SERVER || bid < nblk)) ? (p.M - 1 - row0) / row_step + 1 : 0;
   const uint8_t *wseg = p.w + seg_off;
   const uint32_t ring_addr = smem_u32(ring);
 
@@ -802,7 +813,26 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
       if (s < n_rows) issue(s, s, pol);
   }
   unsigned int tag = 0u, x_tag = 0u;
-  if (p.n_peer > 0) {
+  if constexpr (SERVER) {
+    // stage the job's activation row: pinned host f32 (one PCIe round trip, split over the first
+    // CTAs) -> device {value, tag} pairs that every CTA's stage_x_row validates element by element
+    x_tag = job_tag;
+    if (bid < kSrvStagers) {
+      const int K4 = p.kb * (type_info(WT).blck / 4);
+      const int per = (K4 + kSrvStagers - 1) / kSrvStagers;
+      const int hi = min(K4, (bid + 1) * per);
+      const unsigned long long th = (unsigned long long)job_tag << 32;
+      for (int i = bid * per + (int)threadIdx.x; i < hi; i += (int)blockDim.x) {
+        unsigned int a, b, c, d;
+        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "l"(sp->x_host + 4 * (size_t)i) : "memory");
+        unsigned long long *dst = sp->x_ll + 4 * (size_t)i;
+        asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(th | a), "l"(th | b) : "memory");
+        asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst + 2), "l"(th | c), "l"(th | d) : "memory");
+      }
+    }
+    if (bid == 0) srv_stamp(sp, job_tag, 1);       // CTA 0's slice of X forwarded
+  } else if (p.n_peer > 0) {
     // This launch's tag = its sequence number on the communicator, from an arrival ticket: every CTA of
     // every sharded launch (all have gridDim.x == p.grid_fixed) adds 1 to a rank-local counter BEFORE it
     // lets the next launch start, so when a CTA of this launch draws its ticket all CTAs of all earlier
@@ -810,13 +840,13 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
     // previous grid's COMPLETION, so a launch whose activations are an LL vector never executes
     // griddepcontrol.wait: its inputs are validated element by element through their tags.
     volatile unsigned int *tag_s = reinterpret_cast<volatile unsigned int *>(smem + kDecCtrl - 16);
-    if (threadIdx.x == 0) *tag_s = atomicAdd(p.arrive_ctr, 1u) / gridDim.x + 1u;
+    if (threadIdx.x == 0) *tag_s = atomicAdd(p.arrive_ctr, 1u) / (unsigned int)nblk + 1u;
     __syncthreads();
     tag = *tag_s;
     x_tag = tag - (unsigned int)p.x_back;
     pdl_launch_dependents();
     if constexpr (XM != 2) pdl_wait();
-    if ((int)blockIdx.x >= p.M) return;              // padding CTA (the grid is fixed): owns no row
+    if (bid >= p.M) return;              // padding CTA (the grid is fixed): owns no row
     if constexpr (XM == 2) {
       // Sleep until the activations are (nearly) there: lane g of warp 0 watches the LAST element of
       // rank g's slice of x with a back-off while every other warp is parked at the barrier (no issue
@@ -850,6 +880,7 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
   stage_x_row<VT, XM>(p, xs, x_tag);
   __syncthreads();
   trace_stamp(p.trace, 3);
+  if constexpr (SERVER) { if (bid == 0) srv_stamp(sp, job_tag, 2); }   // activations quantized
   if (active) {
 
   const int U = p.units, ug = u0 + lane;
@@ -907,8 +938,106 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
       }
     }
   }
+  if constexpr (SERVER) {                    // every copy has been consumed: free the barriers for the next job
+    __syncwarp();
+    if (lane == 0)
+      for (int s = 0; s < S; s++) asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(&full[s])) : "memory");
+  }
   }   // active
   trace_stamp(p.trace, 4);
+}
+
+template <int WT, int XM>
+__global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const DecodeParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  decode16_body<WT, XM, false>(p, smem, (int)blockIdx.x, (int)gridDim.x, nullptr, 0u);
+}
+
+// ---- the resident decode server --------------------------------------------------------------
+// A synchronous host call (ggml's lamm_mul_mat on host tensors) pays ~10 us of launch + completion
+// latency per kernel on top of ~5 us of work.  The server is ONE long-lived launch, a CTA per SM,
+// that takes jobs from a mailbox in pinned host memory instead:
+//   host:  memcpy X into the pinned row, write 16 {word, tag} pairs (the job: weight pointer +
+//          launch plan) with tag = job number; poll done_host[0] == tag; memcpy C out.
+//   CTA 0: warp 0 polls the host mailbox over PCIe, forwards the pairs to a device mailbox that the
+//          other CTAs poll in L2 (self-validating pairs: no flag, no fence);
+//   all:   run the decode body on the job (weights prefetched while X crosses PCIe);
+//   last CTA to finish (arrival ticket): copies C to pinned memory with coalesced 16-byte stores
+//          (scattered 4-byte PCIe writes cost ~4 ns EACH), system fence, done_host[0] = tag.
+// It gives up after idle_ns without a job (done_host[1] = the tag it was waiting for) so that other
+// work can have the SMs; the host relaunches it on demand.  Every poll is bounded.
+template <int WT>
+__global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const ServerParams sp) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ DecodeParams jp;
+  __shared__ unsigned int jw[kSrvWords];
+  __shared__ int s_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (unsigned int s = sp.seq0;; ++s) {
+    if (warp == 0) {
+      const bool host_poll = blockIdx.x == 0;
+      const unsigned long long *src = host_poll ? sp.mbox_host : sp.mbox_dev;
+      unsigned long long v = 0, t0, now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+      bool give_up = false;
+      while (true) {
+        if (lane < kSrvWords) asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(src + lane) : "memory");
+        const bool ok = lane >= kSrvWords || (unsigned int)(v >> 32) == s;
+        if (__all_sync(0xffffffffu, ok)) break;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (host_poll) {
+          if (now - t0 > (unsigned long long)sp.idle_ns) { give_up = true; break; }
+        } else {
+          __nanosleep(50);
+          if (now - t0 > 4000000000ull) { give_up = true; *sp.status = 2u; break; }   // CTA 0 always publishes something
+        }
+      }
+      if (give_up) v = ((unsigned long long)s << 32) | (lane == 0 ? 2u : 0u);
+      if (lane < kSrvWords) {
+        jw[lane] = (unsigned int)v;
+        if (host_poll) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + lane), "l"(v) : "memory");
+      }
+      if (host_poll && give_up && lane == 0) {
+        sp.done_host[1] = s;
+        __threadfence_system();
+      }
+    }
+    __syncthreads();
+    if (blockIdx.x == 0) srv_stamp(&sp, s, 0);     // job seen
+    if (jw[0] != 1u) return;                       // 2: stop request or idle time-out
+    if (tid == 0) {
+      DecodeParams q = {};
+      q.w = reinterpret_cast<const uint8_t *>(((unsigned long long)jw[2] << 32) | jw[1]);
+      q.w_stride = (int64_t)jw[3];
+      q.M = (int)jw[4];  q.kb = (int)jw[5];  q.units = (int)jw[6];  q.KS = (int)jw[7];  q.seg_units = (int)jw[8];
+      q.RG = (int)jw[9];  q.slots = kD16Slots;  q.slot_bytes = (int)jw[10];  q.x_bytes = (int)jw[11];
+      q.x_ll = sp.x_ll;  q.c = sp.c_dev;  q.status = sp.status;
+      jp = q;
+    }
+    __syncthreads();
+    decode16_body<WT, 2, true>(jp, smem, (int)blockIdx.x, (int)jw[12], &sp, s);
+    __syncthreads();
+    if (blockIdx.x == 0) srv_stamp(&sp, s, 3);     // CTA 0's rows done
+    if (tid == 0) {
+      __threadfence();
+      s_last = (atomicAdd(sp.done_ctr, 1u) % gridDim.x) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last) {                                  // every CTA's rows are in c_dev (L2)
+      srv_stamp(&sp, s, 4);                        // last arrival
+      __threadfence();
+      const int M = jp.M, n4 = M >> 2;
+      const float4 *src4 = reinterpret_cast<const float4 *>(sp.c_dev);
+      float4 *dst4 = reinterpret_cast<float4 *>(sp.c_host);
+      for (int i = tid; i < n4; i += (int)blockDim.x) dst4[i] = __ldcg(src4 + i);
+      for (int i = 4 * n4 + tid; i < M; i += (int)blockDim.x) sp.c_host[i] = __ldcg(sp.c_dev + i);
+      __threadfence_system();
+      __syncthreads();
+      if (tid == 0) sp.done_host[0] = s;
+      srv_stamp(&sp, s, 5);                        // result published
+    }
+    __syncthreads();
+  }
 }
 
 // ---- host side --------------------------------------------------------------------------
@@ -1020,14 +1149,7 @@ bool decode_supported(int w_type, const void *w, int64_t w_stride, const void *x
   return (((uintptr_t)w | (uintptr_t)w_stride) & 15) == 0 && ((uintptr_t)x_or_xq & 15) == 0;
 }
 
-int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
-                  float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh, const BatchInfo *bt) {
-  const TypeInfo ti = type_info(w_type);
-  const bool q2k = (w_type == LAMMCU_TYPE_Q2_K);
-  DecodeParams p = {};
-  p.w = (const uint8_t *)w;  p.w_stride = w_stride;
-  p.x = x;  p.xq = (const uint8_t *)xq;  p.xq_out = (uint8_t *)xq_out;
-  p.c = c;  p.M = (int)M;
+static int plan_k_split(DecodeParams &p, const TypeInfo &ti, bool q2k, int64_t K) {
   p.kb = (int)(K / ti.blck);
   p.units = q2k ? 2 * p.kb : p.kb / 4;
   p.KS = (p.units + 31) / 32;
@@ -1039,6 +1161,89 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   p.seg_units = (((p.units + p.KS - 1) / p.KS) + gran - 1) / gran * gran;
   if (p.seg_units > 32) p.seg_units = 32;
   p.KS = (p.units + p.seg_units - 1) / p.seg_units;
+  return LAMMCU_OK;
+}
+
+// shared-memory shape of the 16-warp kernel for a planned K split; returns the dynamic bytes
+static int plan_d16_smem(DecodeParams &p, const TypeInfo &ti, bool q2k, int *warps_out) {
+  const int warps = (kD16Warps / p.KS) * p.KS;
+  p.RG = warps / p.KS;
+  const int seg_bytes = q2k ? (p.seg_units / 2) * 84 : p.seg_units * 4 * ti.size;
+  p.slot_bytes = ((seg_bytes + 15) & ~15) + 16;
+  p.x_bytes = q2k ? (p.units * (128 + 16) + p.kb * 4) : (p.units * 128 + p.kb * 8);
+  p.x_bytes = (p.x_bytes + 127) & ~127;
+  p.slots = kD16Slots;
+  *warps_out = warps;
+  return kDecCtrl + p.x_bytes + warps * p.slots * p.slot_bytes;
+}
+
+constexpr int kSrvSmem = 227 * 1024 - 2048;        // dynamic bytes of the server (static: the job's DecodeParams)
+
+// the job the host posts to the resident server for one N == 1 mul_mat (kSrvWords 32-bit words)
+int decode_server_job(int w_type, const void *w, int64_t w_stride, int64_t M, int64_t K, unsigned int *words) {
+  if (!decode_supported(w_type, w, w_stride, nullptr, M, K) || w_stride > 0xffffffffll) {
+    set_error("decode server: operands not supported");
+    return LAMMCU_ERR_SHAPE;
+  }
+  const TypeInfo ti = type_info(w_type);
+  const bool q2k = (w_type == LAMMCU_TYPE_Q2_K);
+  DecodeParams p = {};
+  int rc = plan_k_split(p, ti, q2k, K);
+  if (rc) return rc;
+  if (p.KS > kD16Warps) { set_error("decode server: K too large"); return LAMMCU_ERR_SHAPE; }
+  int warps = 0;
+  if (plan_d16_smem(p, ti, q2k, &warps) > kSrvSmem) { set_error("decode server: K too large for shared memory"); return LAMMCU_ERR_SHAPE; }
+  int grid = sm_count_cached();
+  const int64_t need = (M + p.RG - 1) / p.RG;
+  if (grid > need) grid = (int)need;
+  for (int i = 0; i < kSrvWords; i++) words[i] = 0u;
+  words[0] = 1u;
+  words[1] = (unsigned int)((uintptr_t)w & 0xffffffffu);
+  words[2] = (unsigned int)((uintptr_t)w >> 32);
+  words[3] = (unsigned int)w_stride;
+  words[4] = (unsigned int)M;   words[5] = (unsigned int)p.kb;        words[6] = (unsigned int)p.units;
+  words[7] = (unsigned int)p.KS; words[8] = (unsigned int)p.seg_units; words[9] = (unsigned int)p.RG;
+  words[10] = (unsigned int)p.slot_bytes;  words[11] = (unsigned int)p.x_bytes;  words[12] = (unsigned int)grid;
+  return LAMMCU_OK;
+}
+
+template <int WT>
+static int launch_server_t(const ServerParams &sp, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(decode_server_kernel<WT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSrvSmem);
+    if (e != cudaSuccess) { set_error("decode server: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return LAMMCU_ERR_CUDA; }
+    attr_set = true;
+  }
+  decode_server_kernel<WT><<<sm_count_cached(), kD16Warps * 32, kSrvSmem, st>>>(sp);
+  g_launch_count++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("decode server launch: %s", cudaGetErrorString(e)); return LAMMCU_ERR_CUDA; }
+  return LAMMCU_OK;
+}
+
+int launch_decode_server(int w_type, const ServerParams &sp, cudaStream_t st) {
+  switch (w_type) {
+  case LAMMCU_TYPE_Q4_0: return launch_server_t<LAMMCU_TYPE_Q4_0>(sp, st);
+  case LAMMCU_TYPE_Q4_1: return launch_server_t<LAMMCU_TYPE_Q4_1>(sp, st);
+  case LAMMCU_TYPE_Q5_0: return launch_server_t<LAMMCU_TYPE_Q5_0>(sp, st);
+  case LAMMCU_TYPE_Q5_1: return launch_server_t<LAMMCU_TYPE_Q5_1>(sp, st);
+  case LAMMCU_TYPE_Q8_0: return launch_server_t<LAMMCU_TYPE_Q8_0>(sp, st);
+  case LAMMCU_TYPE_Q2_K: return launch_server_t<LAMMCU_TYPE_Q2_K>(sp, st);
+  default: set_error("decode server: type %d", w_type); return LAMMCU_ERR_TYPE;
+  }
+}
+
+int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
+                  float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh, const BatchInfo *bt) {
+  const TypeInfo ti = type_info(w_type);
+  const bool q2k = (w_type == LAMMCU_TYPE_Q2_K);
+  DecodeParams p = {};
+  p.w = (const uint8_t *)w;  p.w_stride = w_stride;
+  p.x = x;  p.xq = (const uint8_t *)xq;  p.xq_out = (uint8_t *)xq_out;
+  p.c = c;  p.M = (int)M;
+  int rc = plan_k_split(p, ti, q2k, K);
+  if (rc) return rc;
   static const int variant_env = [] {
     const char *e = getenv("LAMM_DECODE_VARIANT");          // tuning knob: 8 or 16 (default) warps
     return (e && atoi(e) == 8) ? 8 : 16;

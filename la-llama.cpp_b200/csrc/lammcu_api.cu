@@ -48,9 +48,6 @@ struct DeviceState {
   void *hx = nullptr;  size_t hx_bytes = 0;      // pinned staging
   void *hc = nullptr;  size_t hc_bytes = 0;
   void *gws = nullptr; size_t gws_bytes = 0;     // prefill GEMM operand scratch
-  void *hll = nullptr; size_t hll_bytes = 0;     // host path: {value, tag} result pairs, pinned (polled by the CPU)
-  unsigned int *hctr = nullptr;                  // host path: arrival-ticket counter + status word
-  unsigned int hseq = 0;                         // host path: polled launches so far (= the last tag)
 };
 static DeviceState g_dev;
 static std::mutex g_mu;
@@ -107,6 +104,27 @@ void *gemm_workspace(size_t bytes) {
 }  // namespace lamm
 
 using namespace lamm;
+
+// resident decode server of the host path (see "the resident-server host path" below)
+constexpr size_t kSrvMaxK = 1 << 16;         // floats in the pinned activation row
+constexpr size_t kSrvMaxM = 1 << 18;         // floats in the result buffers
+
+struct ServerState {
+  bool ready = false;        // buffers allocated
+  bool running = false;      // a server launch is (believed to be) resident
+  int type = -1;             // weight format of the resident instance
+  unsigned int seq = 0;      // tag of the last job posted
+  volatile unsigned long long *mbox = nullptr;   // pinned
+  float *x_host = nullptr, *c_host = nullptr;     // pinned
+  volatile unsigned int *done = nullptr;          // pinned [0] done tag, [1] gave-up tag
+  unsigned long long *mbox_dev = nullptr, *x_ll = nullptr;
+  float *c_dev = nullptr;
+  unsigned int *ctrs = nullptr;                   // [0] arrival tickets, [2] status
+  unsigned long long *trace = nullptr;            // LAMM_SERVER_TRACE=1: [64][8] device time stamps
+};
+static ServerState g_srv;
+
+extern "C" { static void server_stop(); }
 
 struct lammcu_weight {
   const void *host;     // registry key
@@ -176,7 +194,14 @@ int lammcu_shutdown(void) {
   std::lock_guard<std::mutex> lk(g_mu);
   if (!g_dev.inited) return LAMMCU_OK;
   cudaSetDevice(g_dev.device);
+  server_stop();
   cudaDeviceSynchronize();
+  if (g_srv.ready) {
+    cudaFreeHost((void *)g_srv.mbox);  cudaFreeHost(g_srv.x_host);  cudaFreeHost(g_srv.c_host);  cudaFreeHost((void *)g_srv.done);
+    if (g_srv.trace) cudaFree(g_srv.trace);
+    cudaFree(g_srv.mbox_dev);  cudaFree(g_srv.x_ll);  cudaFree(g_srv.c_dev);  cudaFree(g_srv.ctrs);
+    g_srv = ServerState();
+  }
   for (auto &kv : g_weights) {
     cudaFree(kv.second->dev);
     delete kv.second;
@@ -188,8 +213,6 @@ int lammcu_shutdown(void) {
   if (g_dev.hx) cudaFreeHost(g_dev.hx);
   if (g_dev.hc) cudaFreeHost(g_dev.hc);
   if (g_dev.gws) cudaFree(g_dev.gws);
-  if (g_dev.hll) cudaFreeHost(g_dev.hll);
-  if (g_dev.hctr) cudaFree(g_dev.hctr);
   if (g_dev.sched) cudaFree(g_dev.sched);
   if (g_dev.stream) cudaStreamDestroy(g_dev.stream);
   g_dev = DeviceState();
@@ -611,6 +634,7 @@ int lammcu_weight_release(lammcu_weight_t w) {
   auto it = g_weights.find(w->host);
   if (it == g_weights.end() || it->second != w) { set_error("weight_release: bad handle"); return LAMMCU_ERR_ARG; }
   if (--w->refs > 0) return LAMMCU_OK;
+  server_stop();
   cudaStreamSynchronize(g_dev.stream);
   cudaFree(w->dev);
   g_weights.erase(it);
@@ -656,131 +680,165 @@ static int copy_c_back(lammcu_weight_t w, int64_t N, float *c_host, int64_t ldc)
   return LAMMCU_OK;
 }
 
-// ---- the low-latency host path (decode-sized calls) ---------------------------------------------
-// A blocking H2D copy + launch + stream synchronize costs ~30 us per call, 6x the kernel: the copy
-// engine -> compute hand-over alone is ~8 us.  For N = 1:
-//   mode 0  copy engine H2D, kernel (zero-copy f32 result in pinned memory), cudaStreamSynchronize;
-//   mode 1  a small staging KERNEL pulls X from the pinned buffer over PCIe into HBM and the decode
-//           kernel follows it as a programmatic dependent launch (its weight prefetch overlaps the
-//           PCIe read); completion by cudaStreamSynchronize;
-//   mode 2  as 1, but the decode kernel stores {f32 value, u32 tag} pairs (the multi-GPU "LL" format
-//           with the HOST as the only peer) into pinned memory and the calling thread polls the tags
-//           while it copies the values out: completion is carried by the data.
+// ---- the resident-server host path (decode-sized calls) ---------------------------------------
+// A synchronous call that launches a kernel pays ~10 us of launch + completion latency on top of
+// ~5 us of work (scratch/hostlat.cu measures the floor on this box).  In mode 1 an N == 1 call is a
+// JOB for the resident decode server (lamm_decode.cu: decode_server_kernel): the calling thread
+// copies X into a pinned row, posts 16 {word, tag} pairs, polls one pinned word and copies C out.
+// No CUDA API call on the steady-state path.  The server gives up after an idle period and is
+// relaunched on demand; anything else that needs the stream stops it first (server_stop).
+//   mode 0: copy-engine H2D, one kernel launch per call, cudaStreamSynchronize
+//   mode 1: resident server (default)
 static int g_host_mode = [] {
   const char *e = getenv("LAMM_HOST_MODE");
-  const int m = e ? atoi(e) : 0;
-  return (m < 0 || m > 2) ? 0 : m;
+  const int m = e ? atoi(e) : 1;
+  return (m < 0 || m > 1) ? 1 : m;
+}();
+static unsigned int g_srv_idle_us = [] {
+  const char *e = getenv("LAMM_SERVER_IDLE_US");
+  const int v = e ? atoi(e) : 200;
+  return (unsigned int)(v < 1 ? 1 : v > 1000000 ? 1000000 : v);
 }();
 
-__global__ void __launch_bounds__(256) stage_x_kernel(const float4 *__restrict__ src, float4 *__restrict__ dst, int n4) {
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-  const int i = blockIdx.x * 256 + threadIdx.x;
-  if (i < n4) {
-    float4 v;
-    asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(src + i) : "memory");
-    dst[i] = v;
+static int server_setup() {
+  if (g_srv.ready) return LAMMCU_OK;
+  void *p = nullptr;
+  CU_TRY(cudaMallocHost(&p, 256));                   g_srv.mbox = (volatile unsigned long long *)p;
+  CU_TRY(cudaMallocHost(&p, kSrvMaxK * 4));          g_srv.x_host = (float *)p;
+  CU_TRY(cudaMallocHost(&p, kSrvMaxM * 4));          g_srv.c_host = (float *)p;
+  CU_TRY(cudaMallocHost(&p, 256));                   g_srv.done = (volatile unsigned int *)p;
+  CU_TRY(cudaMalloc(&p, 256));                       g_srv.mbox_dev = (unsigned long long *)p;
+  CU_TRY(cudaMalloc(&p, kSrvMaxK * 8));              g_srv.x_ll = (unsigned long long *)p;
+  CU_TRY(cudaMalloc(&p, kSrvMaxM * 4));              g_srv.c_dev = (float *)p;
+  CU_TRY(cudaMalloc(&p, 256));                       g_srv.ctrs = (unsigned int *)p;
+  if (getenv("LAMM_SERVER_TRACE")) {
+    CU_TRY(cudaMalloc(&p, 64 * 8 * 8));
+    g_srv.trace = (unsigned long long *)p;
+    CU_TRY(cudaMemset(p, 0, 64 * 8 * 8));
   }
-}
-
-static int host_poll_setup(int64_t rows) {
-  if (!g_dev.hctr) {
-    CU_TRY(cudaMalloc(&g_dev.hctr, 256));
-    CU_TRY(cudaMemset(g_dev.hctr, 0, 256));
-    CU_TRY(cudaDeviceSynchronize());
-    g_dev.hseq = 0;
-  }
-  const size_t need = (size_t)rows * 8;
-  if (g_dev.hll_bytes < need) {
-    CU_TRY(cudaStreamSynchronize(g_dev.stream));
-    int rc = grow(&g_dev.hll, &g_dev.hll_bytes, need, true);
-    if (rc) return rc;
-    memset(g_dev.hll, 0, g_dev.hll_bytes);         // tag 0 is never issued
-  }
+  memset((void *)g_srv.mbox, 0, 256);
+  memset((void *)g_srv.done, 0, 256);
+  CU_TRY(cudaMemset(g_srv.mbox_dev, 0, 256));
+  CU_TRY(cudaMemset(g_srv.x_ll, 0, kSrvMaxK * 8));   // tag 0 is never issued
+  CU_TRY(cudaMemset(g_srv.ctrs, 0, 256));
+  CU_TRY(cudaDeviceSynchronize());
+  g_srv.seq = 0;
+  g_srv.ready = true;
   return LAMMCU_OK;
 }
 
-// after a failed or timed-out polled launch: re-derive the sequence number from the device counter
-static void host_poll_resync() {
-  cudaStreamSynchronize(g_dev.stream);
-  unsigned int ctr = 0;
-  if (cudaMemcpy(&ctr, g_dev.hctr, sizeof(ctr), cudaMemcpyDeviceToHost) == cudaSuccess)
-    g_dev.hseq = ctr / (unsigned int)sm_count_cached();
-  cudaGetLastError();
+static void server_post(const unsigned int *words) {
+  const unsigned int s = ++g_srv.seq;
+  __atomic_thread_fence(__ATOMIC_RELEASE);           // X (and everything before) is visible before the job
+  for (int i = 0; i < kSrvWords; i++) g_srv.mbox[i] = ((unsigned long long)s << 32) | words[i];
+  __atomic_thread_fence(__ATOMIC_RELEASE);
 }
 
-// N == 1, operands the decode kernel takes; g_dev.hx / xin are large enough (caller)
-static int mul_mat_host_fast(lammcu_weight_t w, const float *x_host, float *c_host) {
-  const int64_t K = w->K, rows = w->row_end - w->row_begin;
-  const bool polled = g_host_mode == 2;
-  int rc;
-  float *c_dev = nullptr;
-  if (polled) rc = host_poll_setup(rows);
-  else rc = out_buffer(w, 1, &c_dev);
+static int server_launch(int type) {
+  ServerParams sp = {};
+  sp.mbox_host = (const unsigned long long *)g_srv.mbox;
+  sp.mbox_dev = g_srv.mbox_dev;
+  sp.x_host = g_srv.x_host;
+  sp.x_ll = g_srv.x_ll;
+  sp.c_dev = g_srv.c_dev;
+  sp.c_host = g_srv.c_host;
+  sp.done_host = g_srv.done;
+  sp.done_ctr = g_srv.ctrs;
+  sp.status = g_srv.ctrs + 2;
+  sp.seq0 = g_srv.seq;                               // the job just posted
+  sp.idle_ns = g_srv_idle_us * 1000u;
+  sp.trace = g_srv.trace;
+  int rc = launch_decode_server(type, sp, g_dev.stream);
   if (rc) return rc;
+  g_srv.running = true;
+  g_srv.type = type;
+  return LAMMCU_OK;
+}
+
+// Make the resident instance exit and wait for it (a no-op when none is running).
+static void server_stop() {
+  if (!g_srv.ready || !g_srv.running) return;
+  unsigned int words[kSrvWords] = {2u};
+  server_post(words);
+  cudaStreamSynchronize(g_dev.stream);
+  g_srv.running = false;
+}
+
+// N == 1, operands the decode kernel takes
+static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_host) {
+  const int64_t K = w->K, rows = w->row_end - w->row_begin;
+  int rc = server_setup();
+  if (rc) return rc;
+  unsigned int words[kSrvWords];
+  if ((rc = decode_server_job(w->type, w->dev, w->stride, rows, K, words))) return rc;
+  if (g_srv.running && g_srv.type != w->type) server_stop();
   const double t0 = now_us();
-  memcpy(g_dev.hx, x_host, (size_t)K * 4);
+  memcpy(g_srv.x_host, x_host, (size_t)K * 4);
   const double t1 = now_us();
-  const int n4 = (int)(K / 4);
-  stage_x_kernel<<<(n4 + 255) / 256, 256, 0, g_dev.stream>>>((const float4 *)g_dev.hx, (float4 *)g_dev.xin, n4);
-  g_launch_count++;
+  server_post(words);
+  unsigned int s = g_srv.seq;
+  // An instance that gave up waiting for tag s has left an EXIT word with that tag in the device
+  // mailbox: the job is re-posted under a fresh tag before a new instance is launched.
+  if (g_srv.running && g_srv.done[1] == s) {
+    g_srv.running = false;
+    server_post(words);
+    s = g_srv.seq;
+  }
+  if (!g_srv.running && (rc = server_launch(w->type))) return rc;
   const double t2 = now_us();
-  if (polled) {
-    ShardInfo sh = {};
-    sh.ll_peer[0] = (unsigned long long *)g_dev.hll;
-    sh.arrive_ctr = g_dev.hctr;
-    sh.status = g_dev.hctr + 2;
-    sh.n_peer = 1;
-    rc = launch_decode(w->type, w->dev, w->stride, (const float *)g_dev.xin, nullptr, nullptr, nullptr, rows, K,
-                       g_dev.stream, &sh);
-  } else {
-    rc = launch_decode(w->type, w->dev, w->stride, (const float *)g_dev.xin, nullptr, nullptr, c_dev, rows, K,
-                       g_dev.stream);
-  }
-  const double t3 = now_us();
-  g_hp[0] += t1 - t0;  g_hp[1] += t2 - t1;  g_hp[2] += t3 - t2;
-  if (!polled) {
-    if (rc) return rc;
-    return copy_c_back(w, 1, c_host, rows);
-  }
-  if (rc) { host_poll_resync(); return rc; }
-  const unsigned int tag = ++g_dev.hseq;
-  const volatile unsigned long long *ll = (const volatile unsigned long long *)g_dev.hll;
-  float *out = c_host + w->row_begin;
-  uint32_t spins = 0;
+  unsigned int spins = 0;
   double t_first = 0;
-  for (int64_t i = 0; i < rows; i++) {
-    unsigned long long v;
-    while ((unsigned int)((v = ll[i]) >> 32) != tag) {
-      __builtin_ia32_pause();
-      if ((++spins & 0xfffu) == 0) {
-        const double now = now_us();
-        if (t_first == 0) t_first = now;
-        else if (now - t_first > 2e6 || cudaStreamQuery(g_dev.stream) != cudaErrorNotReady) {
-          // finished (or failed) without delivering row i, or 2 s without progress
-          cudaError_t e = cudaStreamSynchronize(g_dev.stream);
-          if ((unsigned int)(ll[i] >> 32) == tag) continue;          // it did arrive
-          set_error("mul_mat_host: result row %lld never arrived (%s)", (long long)i, cudaGetErrorString(e));
-          host_poll_resync();
-          return LAMMCU_ERR_CUDA;
-        }
+  while (g_srv.done[0] != s) {
+    __builtin_ia32_pause();
+    if (g_srv.done[1] == s) {                                           // the idle exit raced with the post
+      server_post(words);
+      s = g_srv.seq;
+      if ((rc = server_launch(w->type))) return rc;
+      continue;
+    }
+    if ((++spins & 0x3fffu) == 0) {
+      const double now = now_us();
+      if (t_first == 0) t_first = now;
+      else if (now - t_first > 5e6) {
+        cudaError_t e = cudaStreamSynchronize(g_dev.stream);
+        g_srv.running = false;
+        if (g_srv.done[0] == s) break;
+        set_error("mul_mat_host: the decode server did not answer job %u (%s)", s, cudaGetErrorString(e));
+        return LAMMCU_ERR_CUDA;
       }
     }
-    const uint32_t bits = (uint32_t)v;
-    memcpy(out + i, &bits, 4);
   }
-  g_hp[3] += now_us() - t3;  g_hp[5] += 1;
+  const double t3 = now_us();
+  __atomic_thread_fence(__ATOMIC_ACQUIRE);
+  memcpy(c_host + w->row_begin, g_srv.c_host, (size_t)rows * 4);
+  const double t4 = now_us();
+  g_hp[0] += t1 - t0;  g_hp[2] += t2 - t1;  g_hp[3] += t3 - t2;  g_hp[4] += t4 - t3;  g_hp[5] += 1;
   return LAMMCU_OK;
 }
 
 int lammcu_set_host_mode(int mode) {
-  if (mode < 0 || mode > 2) { set_error("set_host_mode: 0, 1 or 2"); return LAMMCU_ERR_ARG; }
+  if (mode < 0 || mode > 1) { set_error("set_host_mode: 0 or 1"); return LAMMCU_ERR_ARG; }
   std::lock_guard<std::mutex> lk(g_mu);
+  server_stop();
   if (g_dev.inited) cudaStreamSynchronize(g_dev.stream);
   g_host_mode = mode;
   return LAMMCU_OK;
 }
 int lammcu_get_host_mode(void) { return g_host_mode; }
+/* diagnostics (LAMM_SERVER_TRACE=1): device time stamps of the last 64 server jobs, [64][8] ns:
+ * job seen, X slice forwarded, X quantized, CTA 0 done, last arrival, result published */
+int lammcu_server_trace(unsigned long long *out512) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_srv.trace || !out512) { set_error("server_trace: tracing is off"); return LAMMCU_ERR_ARG; }
+  server_stop();
+  CU_TRY(cudaMemcpy(out512, g_srv.trace, 64 * 8 * 8, cudaMemcpyDeviceToHost));
+  return LAMMCU_OK;
+}
+int lammcu_host_quiesce(void) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  server_stop();
+  return LAMMCU_OK;
+}
 
 int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N, int64_t ldx,
                         float *c_host, int64_t ldc, void *xq_out_host) {
@@ -792,9 +850,10 @@ int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N, int64
   const size_t xbytes = (size_t)N * K * 4;
   if ((rc = grow(&g_dev.hx, &g_dev.hx_bytes, xbytes, true))) return rc;
   if ((rc = grow(&g_dev.xin, &g_dev.xin_bytes, xbytes, false))) return rc;
-  if (N == 1 && g_host_mode > 0 && !xq_out_host && g_decode_kernel &&
-      decode_supported(w->type, w->dev, w->stride, g_dev.xin, rows, K))
-    return mul_mat_host_fast(w, x_host, c_host);
+  if (N == 1 && g_host_mode == 1 && !xq_out_host && g_decode_kernel && (size_t)K <= kSrvMaxK &&
+      (size_t)rows <= kSrvMaxM && decode_supported(w->type, w->dev, w->stride, nullptr, rows, K))
+    return mul_mat_host_server(w, x_host, c_host);
+  server_stop();                                   // the launches below queue behind a resident instance
   float *c_dev = nullptr;
   if ((rc = out_buffer(w, N, &c_dev))) return rc;
   const double t0 = now_us();
@@ -831,6 +890,7 @@ int lammcu_mul_mat_q_host(lammcu_weight_t w, const void *xq_host, int64_t xq_str
   if (rc) return rc;
   if (!w || !xq_host || !c_host || N <= 0) { set_error("mul_mat_q_host: bad argument"); return LAMMCU_ERR_ARG; }
   std::lock_guard<std::mutex> lk(g_mu);
+  server_stop();
   const int64_t K = w->K, rows = w->row_end - w->row_begin;
   const int vt = type_info(w->type).vec_dot;
   const size_t rs = (vt == LAMMCU_TYPE_F32) ? (size_t)K * 4 : lammcu_row_size(vt, K);
