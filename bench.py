@@ -585,8 +585,9 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
     t0 = time.perf_counter()
     for _ in range(steps):
         token()
-    torch.cuda.synchronize()
     sec = time.perf_counter() - t0
+    lib.lammcu_host_quiesce()                 # outside the timed region: every call above was synchronous
+    torch.cuda.synchronize()
     lib.lammcu_host_profile(prof, 1)
     calls = max(prof[5], 1.0)
     phases = {k: round(prof[i] / calls, 2) for i, k in enumerate(
@@ -602,7 +603,11 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
             "steps": steps, "ms_per_step": sec / steps * 1e3, "per_call_phases": phases,
             "host_mode": int(lib.lammcu_get_host_mode()),
             "api": "lamm_can_mul_mat + lamm_mul_mat(ggml_compute_params*, ggml_tensor*) on host tensors, "
-                   "one synchronous call per matmul (225 per token); host wall clock",
+                   "one synchronous call per matmul (225 per token); host wall clock; host mode %d (%s)"
+                   % (int(lib.lammcu_get_host_mode()),
+                      "jobs posted to the resident decode server: X pulled from pinned host memory by the kernel, "
+                      "C written back as tagged pairs the caller polls" if lib.lammcu_get_host_mode() == 1 else
+                      "copy-engine H2D + one launch + stream synchronize per call"),
             "note": "weights uploaded once at first use (registry keyed by src0->data); with N>1 the "
                     "per-rank C slices are not gathered in this leg"}
 

@@ -238,8 +238,8 @@ int lammcu_set_host_mode(int mode);
 int lammcu_get_host_mode(void);
 int lammcu_host_quiesce(void);
 /* Diagnostics (LAMM_SERVER_TRACE=1 at load time): device time stamps (ns) of the last 64 server
- * jobs, out[64][8] = {job seen, X slice forwarded, X quantized, CTA 0 done, last CTA arrived,
- * result published, 0, 0}.  Stops the server.                                                  */
+ * jobs, out[64][8] = {job seen by CTA 0, X republished in HBM, X quantized, CTA 0's rows done,
+ * CTA 0's chunk written to host memory, 0, 0, 0}.  Stops the server.                            */
 int lammcu_server_trace(unsigned long long *out512);
 /* same, activations already quantized on the host (src1->type == vec_dot_type) */
 int lammcu_mul_mat_q_host(lammcu_weight_t w, const void *xq_host,

@@ -136,16 +136,13 @@ struct ShardInfo {
 };
 // resident decode server (lamm_decode.cu): jobs arrive through a mailbox in pinned host memory
 constexpr int kSrvWords = 16;      // 32-bit words of a job, each posted as a {word, tag} pair
-constexpr int kSrvStagers = 8;     // CTAs that pull the activation row over PCIe
 struct ServerParams {
   const unsigned long long *mbox_host;   // pinned: kSrvWords pairs written by the CPU
-  unsigned long long *mbox_dev;          // device: the same pairs, forwarded by CTA 0
+  unsigned long long *mbox_dev;          // device: the same pairs, republished by CTA 0
   const float *x_host;                   // pinned: activation row of the current job
   unsigned long long *x_ll;              // device: the row as {value, tag} pairs
-  float *c_dev;                          // device: result
-  float *c_host;                         // pinned: result, copied out by the last CTA to finish
-  volatile unsigned int *done_host;      // pinned: [0] tag of the last finished job, [1] tag the server gave up waiting for
-  unsigned int *done_ctr;                // device: arrival tickets
+  unsigned long long *c_ll_host;         // pinned: the result as {value, tag} pairs
+  volatile unsigned int *done_host;      // pinned: [1] tag the server gave up waiting for
   unsigned int *status;                  // device: set on a poll time-out
   unsigned int seq0;                     // first job tag this launch serves
   unsigned int idle_ns;                  // exit after this long without a job

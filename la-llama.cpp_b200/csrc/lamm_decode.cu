@@ -232,7 +232,7 @@ __device__ __forceinline__ void load_x8(const DecodeParams &p, size_t e, unsigne
 #pragma unroll
       for (int i = 0; i < 8; i++) ok &= ((unsigned int)(v[i] >> 32) == tag);
       if (ok) break;
-      __nanosleep(100);          // a spinning warp would steal issue slots from the producer on this SM
+      __nanosleep(p.n_peer > 0 ? 100 : 20);   // a spinning warp would steal issue slots from a producer sharing this SM
       if ((++spins & 1023u) == 0) {
         unsigned long long now;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
@@ -756,10 +756,10 @@ __device__ __forceinline__ void srv_stamp(const ServerParams *sp, unsigned int j
 
 // SERVER: the body runs as one job of the resident kernel (decode_server_kernel below): bid / nblk
 // are the job's virtual grid, the activations arrive as {value, tag} pairs staged from pinned host
-// memory by the first kSrvStagers CTAs, and the ring barriers are invalidated for the next job.
+// memory by CTA 0, the results go to the `cs` staging row, and the ring barriers are invalidated for the next job.
 template <int WT, int XM, bool SERVER>
 __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *smem, const int bid, const int nblk,
-                                              const ServerParams *sp, const unsigned int job_tag) {
+                                              const ServerParams *sp, const unsigned int job_tag, float *cs) {
   constexpr bool kQ2K = (WT == LAMMCU_TYPE_Q2_K);
   constexpr int VT = type_info(WT).vec_dot;
   constexpr int NW = kQ2K ? 11 : DecFmt<WT>::NW;
@@ -777,8 +777,13 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
   constexpr int unit_bytes = kQ2K ? 42 : 4 * type_info(WT).size;
   const uint32_t seg_off = kQ2K ? (uint32_t)(u0 >> 1) * 84u : (uint32_t)u0 * unit_bytes;
   const uint32_t seg_bytes = kQ2K ? (uint32_t)((seg_n + 1) >> 1) * 84u : (uint32_t)seg_n * unit_bytes;
-  const int row0 = bid + nblk * rg, row_step = nblk * p.RG;
-  const int n_rows = (row0 < p.M && (!SERVER || bid < nblk)) ? (p.M - 1 - row0) / row_step + 1 : 0;
+  // rows of this warp: interleaved over the grid (a launch), or -- SERVER, where nblk is the number of
+  // rows per CTA -- a contiguous chunk per CTA so that its results leave as one coalesced PCIe write
+  const int chunk_lo = SERVER ? bid * nblk : 0;
+  const int chunk_hi = SERVER ? min(p.M, chunk_lo + nblk) : p.M;
+  const int row0 = SERVER ? chunk_lo + rg : bid + nblk * rg;
+  const int row_step = SERVER ? p.RG : nblk * p.RG;
+  const int n_rows = (row0 < chunk_hi) ? (chunk_hi - 1 - row0) / row_step + 1 : 0;
   const uint8_t *wseg = p.w + seg_off;
   const uint32_t ring_addr = smem_u32(ring);
 
@@ -814,24 +819,7 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
   }
   unsigned int tag = 0u, x_tag = 0u;
   if constexpr (SERVER) {
-    // stage the job's activation row: pinned host f32 (one PCIe round trip, split over the first
-    // CTAs) -> device {value, tag} pairs that every CTA's stage_x_row validates element by element
-    x_tag = job_tag;
-    if (bid < kSrvStagers) {
-      const int K4 = p.kb * (type_info(WT).blck / 4);
-      const int per = (K4 + kSrvStagers - 1) / kSrvStagers;
-      const int hi = min(K4, (bid + 1) * per);
-      const unsigned long long th = (unsigned long long)job_tag << 32;
-      for (int i = bid * per + (int)threadIdx.x; i < hi; i += (int)blockDim.x) {
-        unsigned int a, b, c, d;
-        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
-                     : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "l"(sp->x_host + 4 * (size_t)i) : "memory");
-        unsigned long long *dst = sp->x_ll + 4 * (size_t)i;
-        asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(th | a), "l"(th | b) : "memory");
-        asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst + 2), "l"(th | c), "l"(th | d) : "memory");
-      }
-    }
-    if (bid == 0) srv_stamp(sp, job_tag, 1);       // CTA 0's slice of X forwarded
+    x_tag = job_tag;                               // the server kernel has staged X as {value, tag} pairs
   } else if (p.n_peer > 0) {
     // This launch's tag = its sequence number on the communicator, from an arrival ticket: every CTA of
     // every sharded launch (all have gridDim.x == p.grid_fixed) adds 1 to a rank-local counter BEFORE it
@@ -917,7 +905,10 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
         uint32_t w[NW];
         mbar_wait(full + s, (uint32_t)ph);
         if (i0 == 0 && s == 0) trace_stamp(p.trace, 5);
-        load_unit<WT, NW>(w, ring_addr + (uint32_t)s * p.slot_bytes + a15, lane_c);
+        // SERVER rows step by RG: Q2_K rows (84 B per super-block) then differ in their 16-byte phase
+        const uint32_t a15r = !SERVER ? a15
+            : (uint32_t)((uintptr_t)(wseg + (int64_t)(row0 + (i0 + s) * row_step) * p.w_stride) & 15);
+        load_unit<WT, NW>(w, ring_addr + (uint32_t)s * p.slot_bytes + a15r, lane_c);
         acc[s] = dot_unit_sx<WT, NW>(w, xaddr, jstride, xd, xsc, xbs);
         __syncwarp();
         if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
@@ -926,7 +917,10 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
     }
     const float tot = warp_sum2(acc[0], acc[1], lane);
     if (p.KS == 1) {
-      if (lane < nb) store_c(p, row0 + (i0 + lane) * row_step, tot, tag);
+      if (lane < nb) {
+        if constexpr (SERVER) cs[row0 + (i0 + lane) * row_step - chunk_lo] = tot;
+        else store_c(p, row0 + (i0 + lane) * row_step, tot, tag);
+      }
     } else {
       float *pb = part + (size_t)((rg * 2 + ph) * p.KS) * 2;
       if (lane < 2) pb[seg * 2 + lane] = tot;
@@ -934,7 +928,8 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
       if (seg == 0 && lane < nb) {
         float t = 0.f;
         for (int k = 0; k < p.KS; k++) t += pb[k * 2 + lane];
-        store_c(p, row0 + (i0 + lane) * row_step, t, tag);
+        if constexpr (SERVER) cs[row0 + (i0 + lane) * row_step - chunk_lo] = t;
+        else store_c(p, row0 + (i0 + lane) * row_step, t, tag);
       }
     }
   }
@@ -950,7 +945,7 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
 template <int WT, int XM>
 __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const DecodeParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
-  decode16_body<WT, XM, false>(p, smem, (int)blockIdx.x, (int)gridDim.x, nullptr, 0u);
+  decode16_body<WT, XM, false>(p, smem, (int)blockIdx.x, (int)gridDim.x, nullptr, 0u, nullptr);
 }
 
 // ---- the resident decode server --------------------------------------------------------------
@@ -958,84 +953,115 @@ __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const Decod
 // latency per kernel on top of ~5 us of work.  The server is ONE long-lived launch, a CTA per SM,
 // that takes jobs from a mailbox in pinned host memory instead:
 //   host:  memcpy X into the pinned row, write 16 {word, tag} pairs (the job: weight pointer +
-//          launch plan) with tag = job number; poll done_host[0] == tag; memcpy C out.
-//   CTA 0: warp 0 polls the host mailbox over PCIe, forwards the pairs to a device mailbox that the
-//          other CTAs poll in L2 (self-validating pairs: no flag, no fence);
-//   all:   run the decode body on the job (weights prefetched while X crosses PCIe);
-//   last CTA to finish (arrival ticket): copies C to pinned memory with coalesced 16-byte stores
-//          (scattered 4-byte PCIe writes cost ~4 ns EACH), system fence, done_host[0] = tag.
+//          launch plan) with tag = job number; then poll the result pairs while copying them out.
+//   CTA 0: warp 0 polls the host mailbox over PCIe and republishes the pairs in a device mailbox
+//          that the other CTAs poll in L2 (self-validating pairs: no flag, no fence).  It alone
+//          ACCEPTS jobs, so an idle exit is one decision for the whole grid.  It then pulls X over
+//          PCIe (one round trip, all 512 threads) and republishes it as {value, tag} pairs that
+//          every CTA's stage_x_row validates element by element.
+//   all:   run the decode body on a contiguous chunk of rows (weights prefetched while X crosses
+//          PCIe) and write the chunk to pinned memory as {value, tag} pairs with coalesced 16-byte
+//          stores (scattered 4-byte PCIe writes cost ~4 ns EACH).  Completion is carried by the
+//          data: no arrival counter, no system fence (measured at 2.5 - 5 us per job).
 // It gives up after idle_ns without a job (done_host[1] = the tag it was waiting for) so that other
 // work can have the SMs; the host relaunches it on demand.  Every poll is bounded.
+
 template <int WT>
 __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const ServerParams sp) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ DecodeParams jp;
   __shared__ unsigned int jw[kSrvWords];
-  __shared__ int s_last;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int bid = blockIdx.x;
   for (unsigned int s = sp.seq0;; ++s) {
+    // ---- 1. the job
     if (warp == 0) {
-      const bool host_poll = blockIdx.x == 0;
-      const unsigned long long *src = host_poll ? sp.mbox_host : sp.mbox_dev;
+      const unsigned long long *src = bid == 0 ? sp.mbox_host : sp.mbox_dev;
       unsigned long long v = 0, t0, now;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
       bool give_up = false;
       while (true) {
         if (lane < kSrvWords) asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(src + lane) : "memory");
-        const bool ok = lane >= kSrvWords || (unsigned int)(v >> 32) == s;
-        if (__all_sync(0xffffffffu, ok)) break;
+        if (__all_sync(0xffffffffu, lane >= kSrvWords || (unsigned int)(v >> 32) == s)) break;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-        if (host_poll) {
+        if (bid == 0) {
           if (now - t0 > (unsigned long long)sp.idle_ns) { give_up = true; break; }
         } else {
-          __nanosleep(50);
+          __nanosleep(40);
           if (now - t0 > 4000000000ull) { give_up = true; *sp.status = 2u; break; }   // CTA 0 always publishes something
         }
       }
       if (give_up) v = ((unsigned long long)s << 32) | (lane == 0 ? 2u : 0u);
       if (lane < kSrvWords) {
         jw[lane] = (unsigned int)v;
-        if (host_poll) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + lane), "l"(v) : "memory");
+        if (bid == 0) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + lane), "l"(v) : "memory");
       }
-      if (host_poll && give_up && lane == 0) {
+      if (bid == 0 && give_up && lane == 0) {
         sp.done_host[1] = s;
         __threadfence_system();
       }
     }
     __syncthreads();
-    if (blockIdx.x == 0) srv_stamp(&sp, s, 0);     // job seen
+    if (bid == 0) srv_stamp(&sp, s, 0);            // job seen
     if (jw[0] != 1u) return;                       // 2: stop request or idle time-out
+    // ---- 2. CTA 0: X, pinned host memory -> {value, tag} pairs in HBM (one PCIe round trip)
+    if (bid == 0) {
+      const int K4 = (int)jw[5] * (type_info(WT).blck / 4);
+      const unsigned long long th = (unsigned long long)s << 32;
+      for (int base = 0; base < K4; base += 4 * (int)blockDim.x) {
+        uint4 xr[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+          const int i = base + r * (int)blockDim.x + tid;
+          if (i < K4)
+            asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(xr[r].x), "=r"(xr[r].y), "=r"(xr[r].z), "=r"(xr[r].w)
+                         : "l"(sp.x_host + 4 * (size_t)i) : "memory");
+        }
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+          const int i = base + r * (int)blockDim.x + tid;
+          if (i < K4) {
+            unsigned long long *dst = sp.x_ll + 4 * (size_t)i;
+            asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(th | xr[r].x), "l"(th | xr[r].y) : "memory");
+            asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst + 2), "l"(th | xr[r].z), "l"(th | xr[r].w) : "memory");
+          }
+        }
+      }
+      srv_stamp(&sp, s, 1);                        // X forwarded
+    }
     if (tid == 0) {
       DecodeParams q = {};
       q.w = reinterpret_cast<const uint8_t *>(((unsigned long long)jw[2] << 32) | jw[1]);
       q.w_stride = (int64_t)jw[3];
       q.M = (int)jw[4];  q.kb = (int)jw[5];  q.units = (int)jw[6];  q.KS = (int)jw[7];  q.seg_units = (int)jw[8];
       q.RG = (int)jw[9];  q.slots = kD16Slots;  q.slot_bytes = (int)jw[10];  q.x_bytes = (int)jw[11];
-      q.x_ll = sp.x_ll;  q.c = sp.c_dev;  q.status = sp.status;
+      q.x_ll = sp.x_ll;  q.status = sp.status;
       jp = q;
     }
     __syncthreads();
-    decode16_body<WT, 2, true>(jp, smem, (int)blockIdx.x, (int)jw[12], &sp, s);
+    // ---- 3. the rows of this CTA's chunk
+    const int R = (int)jw[12];                     // rows per CTA (multiple of 4)
+    float *cs = reinterpret_cast<float *>(smem + jw[13]);
+    decode16_body<WT, 2, true>(jp, smem, bid, R, &sp, s, cs);
     __syncthreads();
-    if (blockIdx.x == 0) srv_stamp(&sp, s, 3);     // CTA 0's rows done
-    if (tid == 0) {
-      __threadfence();
-      s_last = (atomicAdd(sp.done_ctr, 1u) % gridDim.x) == gridDim.x - 1;
+    if (bid == 0) srv_stamp(&sp, s, 3);            // CTA 0's rows done
+    // ---- 4. results: the chunk as {value, tag} pairs, coalesced, straight to pinned memory
+    {
+      const int lo = bid * R, n = max(0, min(jp.M, lo + R) - lo);
+      const unsigned long long th = (unsigned long long)s << 32;
+      unsigned long long *dst = sp.c_ll_host + lo;
+      for (int i = 2 * tid; i < n; i += 2 * (int)blockDim.x) {
+        const unsigned long long a = th | __float_as_uint(cs[i]);
+        if (i + 1 < n) {
+          const unsigned long long b = th | __float_as_uint(cs[i + 1]);
+          asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst + i), "l"(a), "l"(b) : "memory");
+        } else {
+          asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(dst + i), "l"(a) : "memory");
+        }
+      }
     }
-    __syncthreads();
-    if (s_last) {                                  // every CTA's rows are in c_dev (L2)
-      srv_stamp(&sp, s, 4);                        // last arrival
-      __threadfence();
-      const int M = jp.M, n4 = M >> 2;
-      const float4 *src4 = reinterpret_cast<const float4 *>(sp.c_dev);
-      float4 *dst4 = reinterpret_cast<float4 *>(sp.c_host);
-      for (int i = tid; i < n4; i += (int)blockDim.x) dst4[i] = __ldcg(src4 + i);
-      for (int i = 4 * n4 + tid; i < M; i += (int)blockDim.x) sp.c_host[i] = __ldcg(sp.c_dev + i);
-      __threadfence_system();
-      __syncthreads();
-      if (tid == 0) sp.done_host[0] = s;
-      srv_stamp(&sp, s, 5);                        // result published
-    }
+    if (bid == 0) srv_stamp(&sp, s, 4);            // CTA 0's chunk written
     __syncthreads();
   }
 }
@@ -1192,10 +1218,9 @@ int decode_server_job(int w_type, const void *w, int64_t w_stride, int64_t M, in
   if (rc) return rc;
   if (p.KS > kD16Warps) { set_error("decode server: K too large"); return LAMMCU_ERR_SHAPE; }
   int warps = 0;
-  if (plan_d16_smem(p, ti, q2k, &warps) > kSrvSmem) { set_error("decode server: K too large for shared memory"); return LAMMCU_ERR_SHAPE; }
-  int grid = sm_count_cached();
-  const int64_t need = (M + p.RG - 1) / p.RG;
-  if (grid > need) grid = (int)need;
+  const int body_smem = (plan_d16_smem(p, ti, q2k, &warps) + 127) & ~127;
+  const int64_t R = ((M + sm_count_cached() - 1) / sm_count_cached() + 3) & ~(int64_t)3;   // rows per CTA
+  if (K > 65536 || body_smem + R * 4 > kSrvSmem) { set_error("decode server: shape too large for shared memory"); return LAMMCU_ERR_SHAPE; }
   for (int i = 0; i < kSrvWords; i++) words[i] = 0u;
   words[0] = 1u;
   words[1] = (unsigned int)((uintptr_t)w & 0xffffffffu);
@@ -1203,7 +1228,8 @@ int decode_server_job(int w_type, const void *w, int64_t w_stride, int64_t M, in
   words[3] = (unsigned int)w_stride;
   words[4] = (unsigned int)M;   words[5] = (unsigned int)p.kb;        words[6] = (unsigned int)p.units;
   words[7] = (unsigned int)p.KS; words[8] = (unsigned int)p.seg_units; words[9] = (unsigned int)p.RG;
-  words[10] = (unsigned int)p.slot_bytes;  words[11] = (unsigned int)p.x_bytes;  words[12] = (unsigned int)grid;
+  words[10] = (unsigned int)p.slot_bytes;  words[11] = (unsigned int)p.x_bytes;  words[12] = (unsigned int)R;
+  words[13] = (unsigned int)body_smem;
   return LAMMCU_OK;
 }
 

@@ -114,13 +114,13 @@ struct ServerState {
   bool running = false;      // a server launch is (believed to be) resident
   int type = -1;             // weight format of the resident instance
   unsigned int seq = 0;      // tag of the last job posted
-  volatile unsigned long long *mbox = nullptr;   // pinned
-  float *x_host = nullptr, *c_host = nullptr;     // pinned
-  volatile unsigned int *done = nullptr;          // pinned [0] done tag, [1] gave-up tag
+  volatile unsigned long long *mbox = nullptr;    // pinned: the job
+  float *x_host = nullptr;                         // pinned: activation row
+  volatile unsigned long long *c_ll = nullptr;     // pinned: result pairs
+  volatile unsigned int *done = nullptr;           // pinned: [1] gave-up tag
   unsigned long long *mbox_dev = nullptr, *x_ll = nullptr;
-  float *c_dev = nullptr;
-  unsigned int *ctrs = nullptr;                   // [0] arrival tickets, [2] status
-  unsigned long long *trace = nullptr;            // LAMM_SERVER_TRACE=1: [64][8] device time stamps
+  unsigned int *ctrs = nullptr;                    // [2] status
+  unsigned long long *trace = nullptr;             // LAMM_SERVER_TRACE=1: [64][8] device time stamps
 };
 static ServerState g_srv;
 
@@ -197,9 +197,9 @@ int lammcu_shutdown(void) {
   server_stop();
   cudaDeviceSynchronize();
   if (g_srv.ready) {
-    cudaFreeHost((void *)g_srv.mbox);  cudaFreeHost(g_srv.x_host);  cudaFreeHost(g_srv.c_host);  cudaFreeHost((void *)g_srv.done);
+    cudaFreeHost((void *)g_srv.mbox);  cudaFreeHost(g_srv.x_host);  cudaFreeHost((void *)g_srv.c_ll);  cudaFreeHost((void *)g_srv.done);
     if (g_srv.trace) cudaFree(g_srv.trace);
-    cudaFree(g_srv.mbox_dev);  cudaFree(g_srv.x_ll);  cudaFree(g_srv.c_dev);  cudaFree(g_srv.ctrs);
+    cudaFree(g_srv.mbox_dev);  cudaFree(g_srv.x_ll);  cudaFree(g_srv.ctrs);
     g_srv = ServerState();
   }
   for (auto &kv : g_weights) {
@@ -705,21 +705,21 @@ static int server_setup() {
   void *p = nullptr;
   CU_TRY(cudaMallocHost(&p, 256));                   g_srv.mbox = (volatile unsigned long long *)p;
   CU_TRY(cudaMallocHost(&p, kSrvMaxK * 4));          g_srv.x_host = (float *)p;
-  CU_TRY(cudaMallocHost(&p, kSrvMaxM * 4));          g_srv.c_host = (float *)p;
+  CU_TRY(cudaMallocHost(&p, kSrvMaxM * 8));          g_srv.c_ll = (volatile unsigned long long *)p;
   CU_TRY(cudaMallocHost(&p, 256));                   g_srv.done = (volatile unsigned int *)p;
   CU_TRY(cudaMalloc(&p, 256));                       g_srv.mbox_dev = (unsigned long long *)p;
   CU_TRY(cudaMalloc(&p, kSrvMaxK * 8));              g_srv.x_ll = (unsigned long long *)p;
-  CU_TRY(cudaMalloc(&p, kSrvMaxM * 4));              g_srv.c_dev = (float *)p;
   CU_TRY(cudaMalloc(&p, 256));                       g_srv.ctrs = (unsigned int *)p;
   if (getenv("LAMM_SERVER_TRACE")) {
     CU_TRY(cudaMalloc(&p, 64 * 8 * 8));
     g_srv.trace = (unsigned long long *)p;
     CU_TRY(cudaMemset(p, 0, 64 * 8 * 8));
   }
-  memset((void *)g_srv.mbox, 0, 256);
+  memset((void *)g_srv.mbox, 0, 256);                // tag 0 is never issued
   memset((void *)g_srv.done, 0, 256);
+  memset((void *)g_srv.c_ll, 0, kSrvMaxM * 8);
   CU_TRY(cudaMemset(g_srv.mbox_dev, 0, 256));
-  CU_TRY(cudaMemset(g_srv.x_ll, 0, kSrvMaxK * 8));   // tag 0 is never issued
+  CU_TRY(cudaMemset(g_srv.x_ll, 0, kSrvMaxK * 8));
   CU_TRY(cudaMemset(g_srv.ctrs, 0, 256));
   CU_TRY(cudaDeviceSynchronize());
   g_srv.seq = 0;
@@ -740,10 +740,8 @@ static int server_launch(int type) {
   sp.mbox_dev = g_srv.mbox_dev;
   sp.x_host = g_srv.x_host;
   sp.x_ll = g_srv.x_ll;
-  sp.c_dev = g_srv.c_dev;
-  sp.c_host = g_srv.c_host;
+  sp.c_ll_host = (unsigned long long *)g_srv.c_ll;
   sp.done_host = g_srv.done;
-  sp.done_ctr = g_srv.ctrs;
   sp.status = g_srv.ctrs + 2;
   sp.seq0 = g_srv.seq;                               // the job just posted
   sp.idle_ns = g_srv_idle_us * 1000u;
@@ -753,6 +751,42 @@ static int server_launch(int type) {
   g_srv.running = true;
   g_srv.type = type;
   return LAMMCU_OK;
+}
+
+// values of `n` result pairs whose tags all equal `tag` -> out; returns how many leading pairs were ready
+static size_t ll_take_scalar(const volatile unsigned long long *ll, size_t n, unsigned int tag, float *out) {
+  size_t i = 0;
+  for (; i < n; i++) {
+    const unsigned long long v = ll[i];
+    if ((unsigned int)(v >> 32) != tag) break;
+    const uint32_t bits = (uint32_t)v;
+    memcpy(out + i, &bits, 4);
+  }
+  return i;
+}
+#if defined(__x86_64__)
+#include <immintrin.h>
+__attribute__((target("avx2"))) static size_t ll_take_avx2(const volatile unsigned long long *ll, size_t n, unsigned int tag,
+                                                          float *out) {
+  const __m256i want = _mm256_set1_epi32((int)tag);
+  const __m256i pick = _mm256_setr_epi32(0, 2, 4, 6, 1, 3, 5, 7);     // values to the low half, tags to the high half
+  size_t i = 0;
+  for (; i + 8 <= n; i += 8) {
+    const __m256i a = _mm256_permutevar8x32_epi32(_mm256_loadu_si256((const __m256i *)(const void *)(ll + i)), pick);
+    const __m256i b = _mm256_permutevar8x32_epi32(_mm256_loadu_si256((const __m256i *)(const void *)(ll + i + 4)), pick);
+    const __m256i tags = _mm256_permute2x128_si256(a, b, 0x31);
+    if (_mm256_movemask_epi8(_mm256_cmpeq_epi32(tags, want)) != -1) break;
+    _mm256_storeu_si256((__m256i *)(out + i), _mm256_permute2x128_si256(a, b, 0x20));
+  }
+  return i + ll_take_scalar(ll + i, n - i < 8 ? n - i : 8, tag, out + i);
+}
+#endif
+static size_t ll_take(const volatile unsigned long long *ll, size_t n, unsigned int tag, float *out) {
+#if defined(__x86_64__)
+  static const bool avx2 = __builtin_cpu_supports("avx2");
+  if (avx2) return ll_take_avx2(ll, n, tag, out);
+#endif
+  return ll_take_scalar(ll, n, tag, out);
 }
 
 // Make the resident instance exit and wait for it (a no-op when none is running).
@@ -786,13 +820,20 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
   }
   if (!g_srv.running && (rc = server_launch(w->type))) return rc;
   const double t2 = now_us();
+  // the result arrives as {value, tag} pairs, chunk by chunk: take what is there, spin on the rest
+  float *out = c_host + w->row_begin;
+  size_t got = 0;
   unsigned int spins = 0;
   double t_first = 0;
-  while (g_srv.done[0] != s) {
+  while (true) {
+    got += ll_take(g_srv.c_ll + got, (size_t)rows - got, s, out + got);
+    if (got == (size_t)rows) break;
     __builtin_ia32_pause();
+    asm volatile("" ::: "memory");                                      // re-read the pairs
     if (g_srv.done[1] == s) {                                           // the idle exit raced with the post
       server_post(words);
       s = g_srv.seq;
+      got = 0;
       if ((rc = server_launch(w->type))) return rc;
       continue;
     }
@@ -802,17 +843,14 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
       else if (now - t_first > 5e6) {
         cudaError_t e = cudaStreamSynchronize(g_dev.stream);
         g_srv.running = false;
-        if (g_srv.done[0] == s) break;
-        set_error("mul_mat_host: the decode server did not answer job %u (%s)", s, cudaGetErrorString(e));
+        set_error("mul_mat_host: the decode server did not answer job %u (row %zu of %lld, %s)", s, got,
+                  (long long)rows, cudaGetErrorString(e));
         return LAMMCU_ERR_CUDA;
       }
     }
   }
   const double t3 = now_us();
-  __atomic_thread_fence(__ATOMIC_ACQUIRE);
-  memcpy(c_host + w->row_begin, g_srv.c_host, (size_t)rows * 4);
-  const double t4 = now_us();
-  g_hp[0] += t1 - t0;  g_hp[2] += t2 - t1;  g_hp[3] += t3 - t2;  g_hp[4] += t4 - t3;  g_hp[5] += 1;
+  g_hp[0] += t1 - t0;  g_hp[2] += t2 - t1;  g_hp[3] += t3 - t2;  g_hp[5] += 1;
   return LAMMCU_OK;
 }
 
@@ -826,7 +864,7 @@ int lammcu_set_host_mode(int mode) {
 }
 int lammcu_get_host_mode(void) { return g_host_mode; }
 /* diagnostics (LAMM_SERVER_TRACE=1): device time stamps of the last 64 server jobs, [64][8] ns:
- * job seen, X slice forwarded, X quantized, CTA 0 done, last arrival, result published */
+ * job seen, X republished, X quantized, CTA 0's rows done, CTA 0's chunk written */
 int lammcu_server_trace(unsigned long long *out512) {
   std::lock_guard<std::mutex> lk(g_mu);
   if (!g_srv.trace || !out512) { set_error("server_trace: tracing is off"); return LAMMCU_ERR_ARG; }
