@@ -193,6 +193,19 @@ int lammcu_mul_mat_sharded_batch_dev(lammcu_comm_t comm, int w_type, int count,
                                      const void *x, int x_back, void *const *c_ll_all,
                                      const int64_t *row_begin, const int64_t *rows, int64_t K,
                                      void *stream);
+/* Row-sharded PREFILL (N > 1): this rank multiplies its rows [row_begin, row_begin + rows) of W
+ * with the replicated f32 activations x [N][ldx]; the GEMM epilogue stores the result straight into
+ * the full f32 result C [N][ldc] (ggml layout, ldc >= M) of EVERY rank: c_all[g] is rank g's C,
+ * lammcu_ipc_alloc'ed and opened on every rank.  flags_all[g] is rank g's flag array (>= 64 bytes,
+ * zero-initialised, from lammcu_ipc_alloc): when the call's work has run on the stream, every rank's
+ * rows are complete in the LOCAL C (a publish + wait launch follow the GEMM; all ranks must issue
+ * the same sequence of these calls).  Shapes the tensor-core path does not take still work (the
+ * slab is then copied to the peers).                                                           */
+int lammcu_mul_mat_sharded_gemm_dev(lammcu_comm_t comm, int w_type, const void *w_shard,
+                                    int64_t w_stride_bytes, const float *x, int64_t ldx,
+                                    void *const *c_all, int64_t ldc, void *const *flags_all,
+                                    int64_t row_begin, int64_t rows, int64_t N, int64_t K,
+                                    void *stream);
 /* LL vector (local, produced `back` sharded launches ago, >= 1) -> plain f32 out[M],
  * waiting for every element.  An ordinary kernel: it starts after all earlier work on
  * the stream has completed.                                                           */
@@ -237,6 +250,11 @@ void lammcu_host_profile(double *out8, int reset);
 int lammcu_set_host_mode(int mode);
 int lammcu_get_host_mode(void);
 int lammcu_host_quiesce(void);
+/* The server leaves the GPU after idle_us without a job (default 200, LAMM_SERVER_IDLE_US) and at
+ * the first job boundary life_us after its launch (default 5000, LAMM_SERVER_LIFE_US), so that a
+ * caller that never pauses cannot starve kernels queued on other streams.  It is relaunched by the
+ * next call; both paths are transparent to the caller.                                          */
+int lammcu_set_server_timeouts(unsigned int idle_us, unsigned int life_us);
 /* Diagnostics (LAMM_SERVER_TRACE=1 at load time): device time stamps (ns) of the last 64 server
  * jobs, out[64][8] = {job seen by CTA 0, X republished in HBM, X quantized, CTA 0's rows done,
  * CTA 0's chunk written to host memory, 0, 0, 0}.  Stops the server.                            */

@@ -146,6 +146,7 @@ struct ServerParams {
   unsigned int *status;                  // device: set on a poll time-out
   unsigned int seq0;                     // first job tag this launch serves
   unsigned int idle_ns;                  // exit after this long without a job
+  unsigned int life_ns;                  // ... or this long after the launch (other streams' work gets the SMs)
   unsigned long long *trace;             // optional: [64 jobs][8] globaltimer stamps (diagnostics)
 };
 int decode_server_job(int w_type, const void *w, int64_t w_stride, int64_t M, int64_t K, unsigned int *words);
@@ -164,6 +165,13 @@ int launch_gemm_prep(int vt, int perm, const void *xq, int64_t xq_stride, void *
                      int64_t N, int64_t Npad, int64_t K, cudaStream_t st);
 int launch_gemm_prep_so(int vt, int perm, const void *xq, int64_t xq_stride, void *xh, void *xl, void *sh, float *colscale,
                         int64_t N, int64_t Npad, int64_t K, cudaStream_t st);
+// row-sharded prefill: where the GEMM epilogue stores C (c[g] = rank g's full result + this rank's first column)
+struct GemmPeers {
+  float *c[LAMMCU_MAX_RANKS];
+  int n;
+};
+void gemm_set_peers(const GemmPeers *peers);     // thread-local; consumed by the next scaled-operand / direct GEMM launch
+bool gemm_peers_used();
 constexpr int kSoShift = 6;      // scaled-operand GEMM: A carries 2^kSoShift, B carries 2^-kSoShift
 size_t gemm_so_ws_bytes(int64_t N, int64_t K);
 int launch_gemm_so(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,

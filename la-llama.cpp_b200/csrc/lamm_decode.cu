@@ -973,14 +973,17 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
   __shared__ unsigned int jw[kSrvWords];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int bid = blockIdx.x;
+  unsigned long long t_launch;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_launch));
   for (unsigned int s = sp.seq0;; ++s) {
     // ---- 1. the job
     if (warp == 0) {
       const unsigned long long *src = bid == 0 ? sp.mbox_host : sp.mbox_dev;
       unsigned long long v = 0, t0, now;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-      bool give_up = false;
-      while (true) {
+      // bounded lifetime: a caller that never pauses must not starve kernels queued on other streams
+      bool give_up = bid == 0 && s != sp.seq0 && t0 - t_launch > (unsigned long long)sp.life_ns;
+      while (!give_up) {
         if (lane < kSrvWords) asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(src + lane) : "memory");
         if (__all_sync(0xffffffffu, lane >= kSrvWords || (unsigned int)(v >> 32) == s)) break;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));

@@ -44,7 +44,34 @@ struct SoParams {
   float *c;
   int64_t ldc;
   int M, N, Npad, K;
+  // row-sharded multi-GPU prefill: the epilogue stores every C element into the full [N][ldc] result
+  // of EVERY rank (peer-mapped, already offset to this rank's first column) instead of `c`
+  float *cp[LAMMCU_MAX_RANKS];
+  int n_peer;
 };
+
+static thread_local const GemmPeers *t_peers = nullptr;
+static thread_local bool t_peers_used = false;
+void gemm_set_peers(const GemmPeers *peers) { t_peers = peers;  t_peers_used = false; }
+bool gemm_peers_used() { return t_peers_used; }
+static void fill_peers(SoParams &p) {
+  p.n_peer = 0;
+  for (int g = 0; g < LAMMCU_MAX_RANKS; g++) p.cp[g] = nullptr;
+  if (t_peers) {
+    p.n_peer = t_peers->n;
+    for (int g = 0; g < t_peers->n; g++) p.cp[g] = t_peers->c[g];
+    t_peers_used = true;
+  }
+}
+
+// one accumulator element to its destination(s)
+__device__ __forceinline__ void store_out(const SoParams &p, int64_t idx, float v) {
+  if (p.n_peer == 0) {
+    p.c[idx] = v;
+  } else {
+    for (int g = 0; g < p.n_peer; g++) p.cp[g][idx] = v;
+  }
+}
 
 template <int WT> struct SoSmem {
   static constexpr int BS = type_info(WT).size;
@@ -322,7 +349,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
 #pragma unroll
         for (int i = 0; i < 16; i++) {
           const int n = n0 + c16 * 16 + i;
-          if (n < p.N) p.c[(int64_t)n * p.ldc + m] = __uint_as_float(v[i]) * __ldg(p.colscale + n);
+          if (n < p.N) store_out(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * __ldg(p.colscale + n));
         }
       }
     }
@@ -423,7 +450,7 @@ gemm_direct_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_const
 #pragma unroll
         for (int i = 0; i < 16; i++) {
           const int n = n0 + c16 * 16 + i;
-          if (n < p.N) p.c[(int64_t)n * p.ldc + m] = __uint_as_float(v[i]) * __ldg(p.colscale + n);
+          if (n < p.N) store_out(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * __ldg(p.colscale + n));
         }
       }
     }
@@ -462,6 +489,7 @@ int launch_gemm_direct(int w_type, const void *w, int64_t w_stride, const void *
   SoParams p;
   p.colscale = colscale;  p.c = c;  p.ldc = ldc;
   p.M = (int)M;  p.N = (int)N;  p.Npad = (int)npad;  p.K = (int)K;
+  fill_peers(p);
   constexpr int smem = kDirStages * 4 * kTileBytes + 256 + 1024;
   static bool attr_set = false;
   if (!attr_set) {
@@ -548,6 +576,7 @@ int launch_gemm_so(int w_type, const void *w, int64_t w_stride, const void *xq, 
   SoParams p;
   p.colscale = colscale;  p.c = c;  p.ldc = ldc;
   p.M = (int)M;  p.N = (int)N;  p.Npad = (int)npad;  p.K = (int)K;
+  fill_peers(p);
   switch (w_type) {
   case LAMMCU_TYPE_Q4_0: return launch_so<LAMMCU_TYPE_Q4_0>(tm_w, tm_xh, tm_xl, tm_sh, p, st);
   case LAMMCU_TYPE_Q4_1: return launch_so<LAMMCU_TYPE_Q4_1>(tm_w, tm_xh, tm_xl, tm_sh, p, st);

@@ -106,6 +106,12 @@ void *gemm_workspace(size_t bytes) {
 using namespace lamm;
 
 // resident decode server of the host path (see "the resident-server host path" below)
+static unsigned int g_srv_life_us = [] {
+  const char *e = getenv("LAMM_SERVER_LIFE_US");
+  const int v = e ? atoi(e) : 5000;
+  return (unsigned int)(v < 10 ? 10 : v > 4000000 ? 4000000 : v);
+}();
+
 constexpr size_t kSrvMaxK = 1 << 16;         // floats in the pinned activation row
 constexpr size_t kSrvMaxM = 1 << 18;         // floats in the result buffers
 
@@ -490,6 +496,80 @@ int lammcu_mul_mat_sharded_batch_dev(lammcu_comm_t comm, int w_type, int count, 
                        pick_stream(stream), &sh, &bt);
 }
 
+// ---- row-sharded multi-GPU prefill ----------------------------------------------------------------
+// Every rank runs the GEMM on its row shard; the epilogue stores the C tile straight into the full
+// [N][ldc] result of every rank through peer-mapped pointers (SURVEY 8e "preferred").  Completion:
+// a publish launch after the GEMM raises flag[my_rank] = sequence number on every rank (the kernel
+// boundary has made the GEMM's peer stores visible; one system fence in front of the flag), and a
+// wait launch polls this rank's flags until all ranks have published.  ~10 us on a >= 100 us GEMM.
+struct FlagPtrs { unsigned int *p[LAMMCU_MAX_RANKS]; };
+__global__ void gemm_publish_kernel(unsigned int *seq_ctr, FlagPtrs flags, int rank, int world) {
+  __shared__ unsigned int seq;
+  if (threadIdx.x == 0) seq = atomicAdd(seq_ctr, 1u) + 1u;
+  __syncthreads();
+  __threadfence_system();
+  if ((int)threadIdx.x < world)
+    asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(flags.p[threadIdx.x] + rank), "r"(seq) : "memory");
+}
+__global__ void gemm_wait_kernel(const unsigned int *seq_ctr, const unsigned int *flags, int world, unsigned int *status) {
+  const unsigned int seq = *reinterpret_cast<const volatile unsigned int *>(seq_ctr);   // stream order: after the publish
+  if ((int)threadIdx.x < world) {
+    unsigned int v, spins = 0;
+    unsigned long long t0 = 0;
+    while (true) {
+      asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + threadIdx.x) : "memory");
+      if ((int)(v - seq) >= 0) break;
+      __nanosleep(200);
+      if ((++spins & 1023u) == 0) {
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > 5000000000ull) { *status = 1u; break; }
+      }
+    }
+  }
+  __threadfence_system();
+}
+
+int lammcu_mul_mat_sharded_gemm_dev(lammcu_comm_t comm, int w_type, const void *w_shard, int64_t w_stride,
+                                    const float *x, int64_t ldx, void *const *c_all, int64_t ldc,
+                                    void *const *flags_all, int64_t row_begin, int64_t rows, int64_t N, int64_t K,
+                                    void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!comm || !w_shard || !x || !c_all || !flags_all || rows <= 0 || row_begin < 0 || N <= 0 || row_begin + rows > ldc) {
+    set_error("mul_mat_sharded_gemm: bad argument");
+    return LAMMCU_ERR_ARG;
+  }
+  GemmPeers peers = {};
+  FlagPtrs fl = {};
+  peers.n = comm->world;
+  for (int g = 0; g < comm->world; g++) {
+    if (!c_all[g] || !flags_all[g]) { set_error("mul_mat_sharded_gemm: buffer %d is NULL", g); return LAMMCU_ERR_ARG; }
+    peers.c[g] = (float *)c_all[g] + row_begin;
+    fl.p[g] = (unsigned int *)flags_all[g];
+  }
+  cudaStream_t st = pick_stream(stream);
+  float *c_local = peers.c[comm->rank];
+  gemm_set_peers(&peers);
+  rc = lammcu_mul_mat_dev(w_type, w_shard, w_stride, x, ldx, c_local, ldc, rows, N, K, nullptr, stream);
+  const bool fused = gemm_peers_used();
+  gemm_set_peers(nullptr);
+  if (rc) return rc;
+  if (!fused) {
+    // the dispatch took a kernel without the peer-store epilogue (GEMV sizes, exact mode): copy the slab out
+    for (int g = 0; g < comm->world; g++)
+      if (g != comm->rank)
+        CU_TRY(cudaMemcpy2DAsync(peers.c[g], (size_t)ldc * 4, c_local, (size_t)ldc * 4, (size_t)rows * 4, (size_t)N,
+                                 cudaMemcpyDeviceToDevice, st));
+  }
+  gemm_publish_kernel<<<1, 32, 0, st>>>(comm->ctrs + 4, fl, comm->rank, comm->world);
+  gemm_wait_kernel<<<1, 32, 0, st>>>(comm->ctrs + 4, fl.p[comm->rank], comm->world, comm->ctrs + 2);
+  g_launch_count += 2;
+  CU_TRY(cudaGetLastError());
+  return LAMMCU_OK;
+}
+
 // LL vector -> plain f32 (waits for every element's tag): the last consumer of a sharded chain
 __global__ void ll_unpack_kernel(const unsigned int *arrive_ctr, int grid_fixed, int back, const unsigned long long *ll,
                                  float *out, int64_t M, unsigned int *status) {
@@ -745,6 +825,7 @@ static int server_launch(int type) {
   sp.status = g_srv.ctrs + 2;
   sp.seq0 = g_srv.seq;                               // the job just posted
   sp.idle_ns = g_srv_idle_us * 1000u;
+  sp.life_ns = g_srv_life_us * 1000u;
   sp.trace = g_srv.trace;
   int rc = launch_decode_server(type, sp, g_dev.stream);
   if (rc) return rc;
@@ -863,6 +944,17 @@ int lammcu_set_host_mode(int mode) {
   return LAMMCU_OK;
 }
 int lammcu_get_host_mode(void) { return g_host_mode; }
+int lammcu_set_server_timeouts(unsigned int idle_us, unsigned int life_us) {
+  if (idle_us < 1 || idle_us > 1000000 || life_us < 10 || life_us > 4000000) {
+    set_error("set_server_timeouts: idle 1..1e6 us, life 10..4e6 us");
+    return LAMMCU_ERR_ARG;
+  }
+  std::lock_guard<std::mutex> lk(g_mu);
+  server_stop();
+  g_srv_idle_us = idle_us;
+  g_srv_life_us = life_us;
+  return LAMMCU_OK;
+}
 /* diagnostics (LAMM_SERVER_TRACE=1): device time stamps of the last 64 server jobs, [64][8] ns:
  * job seen, X republished, X quantized, CTA 0's rows done, CTA 0's chunk written */
 int lammcu_server_trace(unsigned long long *out512) {

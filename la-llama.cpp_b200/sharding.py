@@ -110,6 +110,7 @@ class Comm:
         lamm.check(lamm.lib().lammcu_comm_create(self.rank, self.world, C.byref(h)), "comm_create")
         self.handle = h
         self.seq = 0               # sharded launches issued (or captured) so far
+        self._flags = None         # prefill completion flags (one u32 per rank), allocated on first use
 
     def vector(self, m):
         return LLVector(self.lamm, self.dist, m)
@@ -157,6 +158,23 @@ class Comm:
         for o in outs:
             o.seq = self.seq
         self.seq += 1
+
+    def result_buffer(self, n, m):
+        """Full f32 prefill result [n][m] (ggml layout), one buffer per rank mapped into every process."""
+        return SharedBuffer(self.lamm, self.dist, n * m * 4)
+
+    def mul_mat_gemm(self, w_type, w_shard, x, c_buf, m, n, k):
+        """Row-sharded prefill: x = cuda f32 [n, k] (replicated), w_shard = this rank's rows of an M-row
+        weight, c_buf = result_buffer(n, m); afterwards (stream order) the LOCAL buffer holds all of C."""
+        lo, hi = row_shard(m, self.rank, self.world)
+        assert w_shard.shape[0] == hi - lo and x.shape == (n, k)
+        if self._flags is None:
+            self._flags = SharedBuffer(self.lamm, self.dist, 256)
+        fp32 = C.POINTER(C.c_float)
+        self.lamm.check(self.lamm.lib().lammcu_mul_mat_sharded_gemm_dev(
+            self.handle, w_type, w_shard.data_ptr(), w_shard.stride(0) * w_shard.element_size(),
+            C.cast(x.data_ptr(), fp32), x.stride(0), c_buf.ptr_array(), m, self._flags.ptr_array(), lo, hi - lo, n, k,
+            self.lamm._stream_ptr()), "mul_mat_sharded_gemm")
 
     def unpack(self, torch, vec, m=None):
         """LLVector -> plain f32 cuda tensor [m] (waits for every element on the device)."""

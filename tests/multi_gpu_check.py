@@ -87,6 +87,29 @@ def main():
         ok &= good
         print(f"rank {rank} type {t} sibling batch {ms}x{k}: {'ok' if good else 'FAIL'}", flush=True)
         dist.barrier()
+    # row-sharded PREFILL: every rank ends up with the full [N][M] result through the GEMM's peer-store epilogue
+    from oracle_lib import Q5_1, F32
+    for t, m, k, n in [(Q4_1, 1024, 1024, 96), (Q5_1, 1000, 512, 200), (Q8_0, 2048, 2048, 130), (Q2_K, 768, 1024, 64),
+                       (Q4_1, 512, 256, 5)]:
+        rng = np.random.default_rng(21)
+        w = o.quantize_weights(t, rng.standard_normal((m, k)).astype(np.float32), seed=4)
+        x = rng.standard_normal((n, k)).astype(np.float32)
+        want = o.mul_mat(t, w, x)
+        lo, hi = sharding.row_shard(m, rank, world)
+        wd = torch.from_numpy(w[lo:hi].copy()).cuda()
+        xd = torch.from_numpy(x).cuda()
+        cbuf = comm.result_buffer(n, m)
+        for it in range(2):
+            comm.mul_mat_gemm(t, wd, xd, cbuf, m, n, k)
+        got = cbuf.to_tensor(torch, torch.float32, n * m).view(n, m)
+        torch.cuda.synchronize()
+        dist.barrier()
+        err = np.abs(got.cpu().numpy() - want).max()
+        tol = 1e-5 * np.sqrt(k) * np.abs(want).max()
+        good = bool(err <= tol)
+        ok &= good
+        print(f"rank {rank} type {t} sharded prefill {m}x{k} N={n}: err {err:.3g} (tol {tol:.3g}) {'ok' if good else 'FAIL'}", flush=True)
+        dist.barrier()
     ok &= not comm.timed_out()
     flag = torch.tensor([0 if ok else 1], device="cuda")
     dist.all_reduce(flag)

@@ -222,7 +222,17 @@ def test_operator_decode_host_modes(gpu, oracle, t):
                 import time
                 time.sleep(0.002)                    # longer than the idle period: the server exits and is relaunched
         assert lib.lammcu_host_quiesce() == 0
+        # hostile timeouts: the server gives up after 1 us idle / at the first job boundary 10 us after its
+        # launch, so nearly every call meets a server that has just left or is leaving (re-post + relaunch)
+        assert lib.lammcu_set_server_timeouts(1, 10) == 0
+        for rep in range(30):
+            (m, k), w = shapes[rep % len(shapes)], ws[rep % len(shapes)]
+            x = rng.standard_normal((1, k)).astype(np.float32)
+            can, got1 = gpu.lamm_mul_mat_host(t, w, x, nth=1)
+            want = oracle.mul_mat(t, w, x)
+            assert can and np.abs(got1 - want).max() <= tol_c(want, k), f"{TYPE_NAMES[t]} {m}x{k} job {rep} (short-lived server)"
     finally:
+        lib.lammcu_set_server_timeouts(200, 5000)
         lib.lammcu_set_host_mode(default_mode)
     assert lib.lammcu_set_host_mode(2) != 0
 
