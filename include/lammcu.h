@@ -58,7 +58,11 @@ typedef enum {
 enum {
   LAMMCU_TYPE_F32 = 0, LAMMCU_TYPE_Q4_0 = 2, LAMMCU_TYPE_Q4_1 = 3,
   LAMMCU_TYPE_Q5_0 = 6, LAMMCU_TYPE_Q5_1 = 7, LAMMCU_TYPE_Q8_0 = 8,
-  LAMMCU_TYPE_Q8_1 = 9, LAMMCU_TYPE_Q2_K = 10, LAMMCU_TYPE_Q8_K = 15
+  LAMMCU_TYPE_Q8_1 = 9, LAMMCU_TYPE_Q2_K = 10, LAMMCU_TYPE_Q8_K = 15,
+  /* the K-quants the reference lists as TODO (dev.md:86-95; the reference's gate
+   * refuses them, so ggml's own ggml_vec_dot_q{3,4,5,6}_K_q8_K is the behaviour matched here).
+   * Same Q8_K activation kernel as Q2_K.                                                      */
+  LAMMCU_TYPE_Q3_K = 11, LAMMCU_TYPE_Q4_K = 12, LAMMCU_TYPE_Q5_K = 13, LAMMCU_TYPE_Q6_K = 14
 };
 
 /* ---- library / device ------------------------------------------------- */

@@ -20,10 +20,13 @@ LIB_PATH = os.path.join(HERE, "liblammcu.so")
 
 # ggml type ids (llama.cpp-b2430/ggml.h:341-369)
 F32, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0, Q8_1, Q2_K, Q8_K = 0, 2, 3, 6, 7, 8, 9, 10, 15
+Q3_K, Q4_K, Q5_K, Q6_K = 11, 12, 13, 14                   # beyond the reference's table
 TYPE_NAMES = {F32: "f32", Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1",
-              Q8_0: "q8_0", Q8_1: "q8_1", Q2_K: "q2_k", Q8_K: "q8_k"}
+              Q8_0: "q8_0", Q8_1: "q8_1", Q2_K: "q2_k", Q8_K: "q8_k",
+              Q3_K: "q3_k", Q4_K: "q4_k", Q5_K: "q5_k", Q6_K: "q6_k"}
 NAME_TO_TYPE = {v: k for k, v in TYPE_NAMES.items()}
 W_TYPES = (F32, Q2_K, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0)      # src/loongarch_matmul.cpp:37-42
+KQ_TYPES = (Q3_K, Q4_K, Q5_K, Q6_K)
 TASK_INIT, TASK_COMPUTE, TASK_FINALIZE = 0, 1, 2
 
 # every symbol include/lammcu.h and include/lamm_b200.h declare

@@ -31,8 +31,19 @@ __host__ __device__ constexpr TypeInfo type_info(int t) {
   case LAMMCU_TYPE_Q8_1: return {32, 36, LAMMCU_TYPE_Q8_1};
   case LAMMCU_TYPE_Q2_K: return {256, 84, LAMMCU_TYPE_Q8_K};
   case LAMMCU_TYPE_Q8_K: return {256, 292, LAMMCU_TYPE_Q8_K};
+  // K-quants beyond the reference's table (ggml-common.h:228-313)
+  case LAMMCU_TYPE_Q3_K: return {256, 110, LAMMCU_TYPE_Q8_K};
+  case LAMMCU_TYPE_Q4_K: return {256, 144, LAMMCU_TYPE_Q8_K};
+  case LAMMCU_TYPE_Q5_K: return {256, 176, LAMMCU_TYPE_Q8_K};
+  case LAMMCU_TYPE_Q6_K: return {256, 210, LAMMCU_TYPE_Q8_K};
   default:               return {0, 0, -1};
   }
+}
+
+// K-quants served by the generic GEMV (N <= 8) and the dequantize-once GEMM only: they are not in the
+// reference's table (src/loongarch_matmul.cpp:37-42), the single-launch decode kernel has no unit for them
+__host__ __device__ constexpr bool is_kquant_ext(int t) {
+  return t == LAMMCU_TYPE_Q3_K || t == LAMMCU_TYPE_Q4_K || t == LAMMCU_TYPE_Q5_K || t == LAMMCU_TYPE_Q6_K;
 }
 
 // byte offsets inside the activation blocks

@@ -409,10 +409,12 @@ int get_gemm_exact() { return g_gemm_exact; }
 // Q2_K / F32 weights: dequantize-once + TMA-fed GEMM (lamm_gemm_so.cu, direct variant)
 static bool gemm_direct_supported(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride,
                                   int64_t M, int64_t N, int64_t K) {
-  if (w_type != LAMMCU_TYPE_Q2_K && w_type != LAMMCU_TYPE_F32) return false;
+  if (w_type != LAMMCU_TYPE_Q2_K && w_type != LAMMCU_TYPE_F32 && !is_kquant_ext(w_type)) return false;
   if (K <= 0 || K % 256 || M <= 0 || N <= 0 || M > 0x3fffffff || N > 0x3fffffff) return false;
   const uintptr_t al = (w_type == LAMMCU_TYPE_F32) ? 15 : 3;
-  return (((uintptr_t)w | (uintptr_t)w_stride | (uintptr_t)xq | (uintptr_t)xq_stride) & al) == 0;
+  // Q3_K / Q6_K blocks (110 / 210 bytes) are only 2-byte aligned: their dequantizer reads 16-bit words
+  const uintptr_t alw = (w_type == LAMMCU_TYPE_Q3_K || w_type == LAMMCU_TYPE_Q6_K) ? 1 : al;
+  return (((uintptr_t)w | (uintptr_t)w_stride) & alw) == 0 && (((uintptr_t)xq | (uintptr_t)xq_stride) & al) == 0;
 }
 
 int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,

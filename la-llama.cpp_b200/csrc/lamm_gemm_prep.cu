@@ -380,6 +380,83 @@ __device__ __forceinline__ void split_store32(const float (&v)[32], __half *hi, 
   }
 }
 
+// ---- K-quants beyond the reference's table: one 32-element group g of a super-block ----
+// Layouts ggml-common.h:228-313; element order and scale packing as dequantize_row_q{3,4,5,6}_K
+// (ggml-quants.c:2550-2598, 2851-2874, 3134-3160, 3383-3412).  Blocks are only 2-byte aligned for
+// Q3_K / Q6_K, so everything is read as bytes or 16-bit words.
+__device__ __forceinline__ uint32_t ldg16(const uint8_t *p) { return *reinterpret_cast<const uint16_t *>(p); }
+// get_scale_min_k4 (ggml-quants.c:2027-2034): 6-bit scale and min of group j from the 12 packed bytes
+__device__ __forceinline__ void scale_min_k4(int j, const uint8_t *q, int &sc, int &mn) {
+  if (j < 4) {
+    sc = q[j] & 63;
+    mn = q[j + 4] & 63;
+  } else {
+    sc = (q[j + 4] & 0xF) | ((q[j - 4] >> 6) << 4);
+    mn = (q[j + 4] >> 4) | ((q[j] >> 6) << 4);
+  }
+}
+// 6-bit Q3_K scale j (0..15), before the -32 (ggml-quants.c:2570-2575)
+__device__ __forceinline__ int scale_q3k(int j, const uint8_t *s) {
+  const int lo = (j < 8) ? (s[j] & 0xF) : (s[j - 8] >> 4);
+  const int hi = (s[8 + (j & 3)] >> (2 * (j >> 2))) & 3;
+  return lo | (hi << 4);
+}
+template <int WT>
+__device__ __forceinline__ void kquant_group32(const uint8_t *blk, int g, float S, float (&v)[32]) {
+  if constexpr (WT == LAMMCU_TYPE_Q4_K || WT == LAMMCU_TYPE_Q5_K) {
+    // {f16 d, dmin; u8 scales[12]; (Q5_K: u8 qh[32];) u8 qs[128]}
+    const float d = half_bits_to_float(ldg16(blk)) * S, dmin = half_bits_to_float(ldg16(blk + 2)) * S;
+    int sc, mn;
+    scale_min_k4(g, blk + 4, sc, mn);
+    const float dl = d * (float)sc, ml = dmin * (float)mn;
+    const uint8_t *qs = blk + (WT == LAMMCU_TYPE_Q4_K ? 16 : 48) + 32 * (g >> 1);
+    const int sh = 4 * (g & 1);
+#pragma unroll
+    for (int l = 0; l < 32; l += 2) {
+      const uint32_t q2 = ldg16(qs + l) >> sh;
+      uint32_t q0 = q2 & 15u, q1 = (q2 >> 8) & 15u;
+      if constexpr (WT == LAMMCU_TYPE_Q5_K) {
+        const uint32_t h2 = ldg16(blk + 16 + l) >> g;
+        q0 |= (h2 & 1u) << 4;
+        q1 |= ((h2 >> 8) & 1u) << 4;
+      }
+      v[l] = fmaf(dl, (float)q0, -ml);
+      v[l + 1] = fmaf(dl, (float)q1, -ml);
+    }
+  } else if constexpr (WT == LAMMCU_TYPE_Q6_K) {
+    // {u8 ql[128]; u8 qh[64]; i8 scales[16]; f16 d}
+    const int n = g >> 2, j = g & 3;
+    const float d = half_bits_to_float(ldg16(blk + 208)) * S;
+    const signed char *scp = reinterpret_cast<const signed char *>(blk + 192 + 8 * n + 2 * j);
+    const float d0 = d * (float)scp[0], d1 = d * (float)scp[1];
+    const uint8_t *ql = blk + 64 * n + 32 * (j & 1), *qh = blk + 128 + 32 * n;
+    const int shl = 4 * (j >> 1), shh = 2 * j;
+#pragma unroll
+    for (int l = 0; l < 32; l += 2) {
+      const uint32_t a = ldg16(ql + l) >> shl, h = ldg16(qh + l) >> shh;
+      const int q0 = (int)((a & 15u) | ((h & 3u) << 4)) - 32;
+      const int q1 = (int)(((a >> 8) & 15u) | (((h >> 8) & 3u) << 4)) - 32;
+      v[l] = (l < 16 ? d0 : d1) * (float)q0;
+      v[l + 1] = (l < 16 ? d0 : d1) * (float)q1;
+    }
+  } else {   // Q3_K {u8 hmask[32]; u8 qs[64]; u8 scales[12]; f16 d}
+    const int n = g >> 2, j = g & 3;
+    const float d = half_bits_to_float(ldg16(blk + 108)) * S;
+    const float d0 = d * (float)(scale_q3k(8 * n + 2 * j, blk + 96) - 32);
+    const float d1 = d * (float)(scale_q3k(8 * n + 2 * j + 1, blk + 96) - 32);
+    const uint8_t *qs = blk + 32 + 32 * n;
+    const int hb = 4 * n + j;
+#pragma unroll
+    for (int l = 0; l < 32; l += 2) {
+      const uint32_t a = ldg16(qs + l) >> (2 * j), h = ldg16(blk + l) >> hb;
+      const int q0 = (int)(a & 3u) - ((h & 1u) ? 0 : 4);
+      const int q1 = (int)((a >> 8) & 3u) - (((h >> 8) & 1u) ? 0 : 4);
+      v[l] = (l < 16 ? d0 : d1) * (float)q0;
+      v[l + 1] = (l < 16 ? d0 : d1) * (float)q1;
+    }
+  }
+}
+
 // W (Q2_K super-blocks or f32 rows) -> AH, AL fp16 [Mpad][K], value * 2^kSoShift, natural K order.
 // Q2_K element (ggml-common.h:214-225, src/lamm_kernel_q2_k.hpp:49-71): for half n of the super-block and
 // shift s in {0,2,4,6}, elements 128n + 16s .. + 31 are (qs[32n + l] >> s) & 3 with scale bytes
@@ -415,6 +492,8 @@ __global__ void __launch_bounds__(256) dequant_hilo_kernel(const uint8_t *__rest
             v[4 * j + e] = (j < 4) ? fmaf(d0, qv, -m0) : fmaf(d1, qv, -m1);
           }
         }
+      } else if constexpr (is_kquant_ext(WT)) {
+        kquant_group32<WT>(w + (int64_t)m * w_stride + (int64_t)(b >> 3) * type_info(WT).size, b & 7, S, v);
       } else {
         const float4 *src = reinterpret_cast<const float4 *>(w + (int64_t)m * w_stride + (int64_t)b * 128);
 #pragma unroll
@@ -440,6 +519,15 @@ int launch_dequant_hilo(int w_type, const void *w, int64_t w_stride, void *ah, v
   else if (w_type == LAMMCU_TYPE_F32)
     dequant_hilo_kernel<LAMMCU_TYPE_F32><<<blocks, 256, 0, st>>>((const uint8_t *)w, w_stride, (__half *)ah, (__half *)al,
                                                               (int)M, (int)Mpad, (int)K);
+#define LAMM_DQ_CASE(T)                                                                                             \
+  else if (w_type == T)                                                                                             \
+    dequant_hilo_kernel<T><<<blocks, 256, 0, st>>>((const uint8_t *)w, w_stride, (__half *)ah, (__half *)al, (int)M, \
+                                                   (int)Mpad, (int)K);
+  LAMM_DQ_CASE(LAMMCU_TYPE_Q3_K)
+  LAMM_DQ_CASE(LAMMCU_TYPE_Q4_K)
+  LAMM_DQ_CASE(LAMMCU_TYPE_Q5_K)
+  LAMM_DQ_CASE(LAMMCU_TYPE_Q6_K)
+#undef LAMM_DQ_CASE
   else {
     set_error("dequant_hilo: weight type %d not supported", w_type);
     return LAMMCU_ERR_TYPE;

@@ -311,6 +311,124 @@ __device__ __forceinline__ void dot_unit_q2k(const uint8_t *rowp, int u, const G
   }
 }
 
+// ---- Q3_K / Q4_K / Q5_K / Q6_K x Q8_K ---------------------------------------
+// Not in the reference's table: the behaviour matched is ggml's own ggml_vec_dot_q{3,4,5,6}_K_q8_K
+// (ggml-quants.c:6127, 7000, 7609, 8305; scalar forms :6583-6646, 7301-7358, 7968-8029, 8695-8737).
+// Same work unit and the same shared activation layout as Q2_K above: unit u = sb*8 + half*4 + c
+// covers elements 128*half + 32*j + 8c + t (plane j < 4, t < 8) of super-block sb, and owns the
+// bsums terms of the 16-element sub-blocks 2*(u&7), 2*(u&7)+1 (= 32-element group u&7).
+__device__ __forceinline__ int lds_s8(const uint8_t *p) {
+  int v;
+  asm volatile("ld.shared.s8 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)));
+  return v;
+}
+__device__ __forceinline__ int byte_of(uint32_t w, int i) { return (int)((w >> (8 * i)) & 0xFFu); }
+
+template <int WT, int NC>
+__device__ __forceinline__ void dot_unit_kq(const uint8_t *rowp, int u, const GemvParams &p,
+                                            const uint8_t *xs, float (&acc)[NC]) {
+  const int U = p.units;
+  const uint2 *xq = reinterpret_cast<const uint2 *>(xs);
+  const uint32_t *xbs = reinterpret_cast<const uint32_t *>(xq + (size_t)NC * 4 * U);
+  const float *xd = reinterpret_cast<const float *>(xbs + (size_t)NC * U);
+  const int sb = u >> 3, half = (u >> 2) & 1, c = u & 3;
+  const uint8_t *blk = rowp + sb * type_info(WT).size;
+  uint32_t pl[4][2];          // the 4 planes of the unit as unsigned bytes
+  int sc[4];                  // integer scale of each plane's sub-block
+  int ms0, ms1;               // multipliers of bsums[2*(u&7)], bsums[2*(u&7)+1]
+  float wd, wdmin = 0.f;
+  if constexpr (WT == LAMMCU_TYPE_Q4_K || WT == LAMMCU_TYPE_Q5_K) {
+    constexpr int QS = (WT == LAMMCU_TYPE_Q4_K) ? 16 : 48;
+    uint32_t hdr[4], a[2], b[2];
+    lds_words_a4<4>(blk, hdr);                                  // d | dmin, scales[0..11]
+    lds_words_a4<2>(blk + QS + 64 * half + 8 * c, a);           // pair 2*half:   planes 0 (lo), 1 (hi)
+    lds_words_a4<2>(blk + QS + 64 * half + 32 + 8 * c, b);      // pair 2*half+1: planes 2 (lo), 3 (hi)
+    wd = half_bits_to_float(hdr[0] & 0xffffu);
+    wdmin = half_bits_to_float(hdr[0] >> 16);
+    // get_scale_min_k4 for groups 4*half .. 4*half+3, four at a time
+    const uint32_t scw = half ? ((hdr[3] & 0x0F0F0F0Fu) | (((hdr[1] >> 6) & 0x03030303u) << 4)) : (hdr[1] & 0x3F3F3F3Fu);
+    const uint32_t mnw = half ? (((hdr[3] >> 4) & 0x0F0F0F0Fu) | (((hdr[2] >> 6) & 0x03030303u) << 4))
+                              : (hdr[2] & 0x3F3F3F3Fu);
+#pragma unroll
+    for (int j = 0; j < 4; j++) sc[j] = byte_of(scw, j);
+    ms0 = ms1 = byte_of(mnw, c);
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      pl[0][k] = a[k] & 0x0F0F0F0Fu;  pl[1][k] = (a[k] >> 4) & 0x0F0F0F0Fu;
+      pl[2][k] = b[k] & 0x0F0F0F0Fu;  pl[3][k] = (b[k] >> 4) & 0x0F0F0F0Fu;
+    }
+    if constexpr (WT == LAMMCU_TYPE_Q5_K) {
+      uint32_t h[2];
+      lds_words_a4<2>(blk + 16 + 8 * c, h);                     // bit g of qh[l]: 5th bit of element 32g + l
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+#pragma unroll
+        for (int k = 0; k < 2; k++) pl[j][k] |= ((h[k] >> (4 * half + j)) & 0x01010101u) << 4;
+    }
+  } else if constexpr (WT == LAMMCU_TYPE_Q6_K) {
+    uint32_t a[2], b[2], h[2];
+    lds_words_a2<2>(blk + 64 * half + 8 * c, a);                // ql: planes 0 (lo), 2 (hi)
+    lds_words_a2<2>(blk + 64 * half + 32 + 8 * c, b);           // ql: planes 1 (lo), 3 (hi)
+    lds_words_a2<2>(blk + 128 + 32 * half + 8 * c, h);          // qh: 2 bits per plane
+    wd = half_bits_to_float(lds_u16(blk + 208));
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      pl[0][k] = (a[k] & 0x0F0F0F0Fu) | ((h[k] & 0x03030303u) << 4);
+      pl[1][k] = (b[k] & 0x0F0F0F0Fu) | (((h[k] >> 2) & 0x03030303u) << 4);
+      pl[2][k] = ((a[k] >> 4) & 0x0F0F0F0Fu) | (((h[k] >> 4) & 0x03030303u) << 4);
+      pl[3][k] = ((b[k] >> 4) & 0x0F0F0F0Fu) | (((h[k] >> 6) & 0x03030303u) << 4);
+    }
+    const uint8_t *scp = blk + 192 + 8 * half;                  // int8 scales of this half's 8 sub-blocks
+#pragma unroll
+    for (int j = 0; j < 4; j++) sc[j] = lds_s8(scp + 2 * j + (c >> 1));
+    ms0 = 32 * lds_s8(scp + 2 * c);                             // sum (q - 32) x = sum q x - 32 bsum
+    ms1 = 32 * lds_s8(scp + 2 * c + 1);
+  } else {   // Q3_K
+    uint32_t q[2], h[2], s3[3];
+    lds_words_a2<2>(blk + 32 + 32 * half + 8 * c, q);           // low 2 bits, 4 planes per byte
+    lds_words_a2<2>(blk + 8 * c, h);                            // hmask: bit 4*half + j belongs to plane j
+    lds_words_a2<3>(blk + 96, s3);
+    wd = half_bits_to_float(lds_u16(blk + 108));
+    // the 16 6-bit scales as bytes of aux[0..3] (ggml-quants.c:2570-2575)
+    uint32_t aux[4];
+    aux[0] = (s3[0] & 0x0F0F0F0Fu) | ((s3[2] & 0x03030303u) << 4);
+    aux[1] = (s3[1] & 0x0F0F0F0Fu) | (((s3[2] >> 2) & 0x03030303u) << 4);
+    aux[2] = ((s3[0] >> 4) & 0x0F0F0F0Fu) | (((s3[2] >> 4) & 0x03030303u) << 4);
+    aux[3] = ((s3[1] >> 4) & 0x0F0F0F0Fu) | (((s3[2] >> 6) & 0x03030303u) << 4);
+    const uint32_t lo = half ? aux[2] : aux[0], hi = half ? aux[3] : aux[1];     // sub-blocks 8*half .. +7
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      sc[j] = byte_of(j < 2 ? lo : hi, 2 * (j & 1) + (c >> 1)) - 32;
+#pragma unroll
+      for (int k = 0; k < 2; k++)
+        pl[j][k] = ((q[k] >> (2 * j)) & 0x03030303u) | (((h[k] >> (4 * half + j)) & 0x01010101u) << 2);
+    }
+    const uint32_t own = (c >> 1) ? hi : lo;                    // sub-blocks 8*half + 2c, + 2c + 1
+    ms0 = 4 * (byte_of(own, 2 * (c & 1)) - 32);                 // value = (q | hbit << 2) - 4
+    ms1 = 4 * (byte_of(own, 2 * (c & 1) + 1) - 32);
+  }
+#pragma unroll
+  for (int n = 0; n < NC; n++) {
+    int isum = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const uint2 x = xq[(size_t)(n * 4 + j) * U + u];
+      int t = dp4a_us(pl[j][0], x.x, 0);
+      t = dp4a_us(pl[j][1], x.y, t);
+      isum += sc[j] * t;
+    }
+    const uint32_t bs = xbs[n * U + u];
+    const int summs = (int)(short)(bs & 0xffffu) * ms0 + (int)(short)(bs >> 16) * ms1;
+    const float d8 = xd[n * p.kb + sb];
+    if constexpr (WT == LAMMCU_TYPE_Q4_K || WT == LAMMCU_TYPE_Q5_K) {
+      acc[n] = fmaf(d8 * wd, (float)isum, acc[n]);
+      acc[n] = fmaf(-(d8 * wdmin), (float)summs, acc[n]);
+    } else {
+      acc[n] = fmaf(d8 * wd, (float)(isum - summs), acc[n]);
+    }
+  }
+}
+
 // ---- F32 x F32 ------------------------------------------------------------------------
 // unit = one float4 of the row; X rows are copied to shared memory as they are.
 template <int NC>
@@ -344,7 +462,7 @@ __device__ __forceinline__ void dot_unit_f32(const uint8_t *rowp, int u, const G
 template <int WT, int NC>
 __device__ __forceinline__ void stage_x(const GemvParams &p, uint8_t *xs, int tid) {
   if constexpr (WT == LAMMCU_TYPE_F32) stage_xf32<NC>(p, xs, tid);
-  else if constexpr (WT == LAMMCU_TYPE_Q2_K) stage_xq2k<NC>(p, xs, tid);
+  else if constexpr (WT == LAMMCU_TYPE_Q2_K || is_kquant_ext(WT)) stage_xq2k<NC>(p, xs, tid);
   else stage_x32<type_info(WT).vec_dot, NC>(p, xs, tid);
 }
 template <int WT, int NC>
@@ -352,6 +470,7 @@ __device__ __forceinline__ void dot_unit(const uint8_t *rowp, int u, const GemvP
                                          const uint8_t *xs, float (&acc)[NC]) {
   if constexpr (WT == LAMMCU_TYPE_F32) dot_unit_f32<NC>(rowp, u, p, xs, acc);
   else if constexpr (WT == LAMMCU_TYPE_Q2_K) dot_unit_q2k<NC>(rowp, u, p, xs, acc);
+  else if constexpr (is_kquant_ext(WT)) dot_unit_kq<WT, NC>(rowp, u, p, xs, acc);
   else dot_unit32<WT, NC>(rowp, u, p, xs, acc);
 }
 
@@ -511,7 +630,7 @@ static int launch_nc(int nc, const GemvParams &p, int grid, int smem, cudaStream
 static int x_bytes_for(int w_type, int nc, int kb, int64_t K) {
   int b;
   if (w_type == LAMMCU_TYPE_F32) b = nc * (int)K * 4;
-  else if (w_type == LAMMCU_TYPE_Q2_K) b = nc * kb * 292;
+  else if (type_info(w_type).blck == 256) b = nc * kb * 292;
   else b = nc * kb * 40;
   return (b + 127) & ~127;
 }
@@ -528,7 +647,8 @@ int launch_gemv(int w_type, const void *w, int64_t w_stride, const void *xq, int
     set_error("gemv: bad shape M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K);
     return LAMMCU_ERR_SHAPE;
   }
-  const int walign = (w_type == LAMMCU_TYPE_F32 || w_type == LAMMCU_TYPE_Q2_K) ? 4 : 2;
+  const int walign = (w_type == LAMMCU_TYPE_F32 || w_type == LAMMCU_TYPE_Q2_K || w_type == LAMMCU_TYPE_Q4_K ||
+                      w_type == LAMMCU_TYPE_Q5_K) ? 4 : 2;
   const int xalign = (ti.vec_dot == LAMMCU_TYPE_Q8_0) ? 2 : 4;
   if (((uintptr_t)w | (uintptr_t)w_stride) % walign || ((uintptr_t)xq | (uintptr_t)xq_stride) % xalign ||
       ((uintptr_t)c & 3)) {
@@ -549,7 +669,7 @@ int launch_gemv(int w_type, const void *w, int64_t w_stride, const void *xq, int
   p.M = (int)M;              p.kb = kb;
   p.row_bytes = (int)row_bytes64;
   p.slot_pitch = slot_pitch;
-  p.units = (w_type == LAMMCU_TYPE_F32) ? (int)(K / 4) : (w_type == LAMMCU_TYPE_Q2_K ? kb * 8 : kb);
+  p.units = (w_type == LAMMCU_TYPE_F32) ? (int)(K / 4) : (ti.blck == 256 ? kb * 8 : kb);
 
   // rows per tile: the largest of 8/4/2/1 whose stage stays <= 24 KB
   int R = 8;
@@ -596,6 +716,10 @@ int launch_gemv(int w_type, const void *w, int64_t w_stride, const void *xq, int
     case LAMMCU_TYPE_Q5_0: rc = launch_nc<LAMMCU_TYPE_Q5_0>(nc, p, grid, smem, st); break;
     case LAMMCU_TYPE_Q5_1: rc = launch_nc<LAMMCU_TYPE_Q5_1>(nc, p, grid, smem, st); break;
     case LAMMCU_TYPE_Q8_0: rc = launch_nc<LAMMCU_TYPE_Q8_0>(nc, p, grid, smem, st); break;
+    case LAMMCU_TYPE_Q3_K: rc = launch_nc<LAMMCU_TYPE_Q3_K>(nc, p, grid, smem, st); break;
+    case LAMMCU_TYPE_Q4_K: rc = launch_nc<LAMMCU_TYPE_Q4_K>(nc, p, grid, smem, st); break;
+    case LAMMCU_TYPE_Q5_K: rc = launch_nc<LAMMCU_TYPE_Q5_K>(nc, p, grid, smem, st); break;
+    case LAMMCU_TYPE_Q6_K: rc = launch_nc<LAMMCU_TYPE_Q6_K>(nc, p, grid, smem, st); break;
     default:               rc = launch_nc<LAMMCU_TYPE_Q2_K>(nc, p, grid, smem, st); break;
     }
     if (rc != LAMMCU_OK) return rc;

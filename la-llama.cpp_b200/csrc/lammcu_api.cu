@@ -233,7 +233,7 @@ void lammcu_launch_count_reset(void) { g_launch_count = 0; }
 int lammcu_type_supported(int t) {
   return t == LAMMCU_TYPE_F32 || t == LAMMCU_TYPE_Q2_K || t == LAMMCU_TYPE_Q4_0 ||
          t == LAMMCU_TYPE_Q4_1 || t == LAMMCU_TYPE_Q5_0 || t == LAMMCU_TYPE_Q5_1 ||
-         t == LAMMCU_TYPE_Q8_0;
+         t == LAMMCU_TYPE_Q8_0 || is_kquant_ext(t);
 }
 int lammcu_blck_size(int t) { return type_info(t).blck; }
 size_t lammcu_type_size(int t) { return (size_t)type_info(t).size; }

@@ -18,7 +18,7 @@ import sys
 import numpy as np
 
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests"))
-from oracle_lib import (F32, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES, Ref, build_ref)
+from oracle_lib import (F32, KQ_TYPES, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES, Ref, build_ref)
 
 OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
 
@@ -73,6 +73,23 @@ def main():
                         q8_0=r.quantize_act(Q8_0, x, prefill=0xAB),
                         q8_1=r.quantize_act(Q8_1, x, prefill=0xAB),
                         q8_k=r.quantize_act(Q8_K, x, prefill=0xAB))
+    # SURVEY 8f-1 K-quants (own generator so the fixtures above stay byte-identical): lamm's gate refuses
+    # these types, so the reference behaviour is ggml's own path (c_graph) / ggml_vec_dot_q*_K_q8_K
+    rng = np.random.default_rng(20240315)
+    m, n, k = 33, 18, 1024
+    w = rng.standard_normal((m, k)).astype(np.float32)
+    x = make_x(rng, n, k)
+    for t in KQ_TYPES:
+        name = TYPE_NAMES[t]
+        wq = r.quantize_weights(t, w)
+        xq = r.quantize_act(Q8_K, x, prefill=0xAB)
+        xq0 = r.quantize_act(Q8_K, x, prefill=0)
+        c_vecdot = r.vec_dot(t, wq, xq0, k)
+        c_graph = r.graph_mul_mat(t, wq, x)
+        np.savez_compressed(os.path.join(OUT, f"mulmat_{name}_m{m}_n{n}_k{k}.npz"),
+                            w_type=t, wq=wq, x=x, xq=xq, c_vecdot=c_vecdot, c_graph=c_graph,
+                            w_deq=r.dequantize(t, wq, k))
+        print(name, m, n, k, "graph-vecdot", float(np.abs(c_graph - c_vecdot).max()))
 
 
 if __name__ == "__main__":

@@ -23,6 +23,7 @@ int orc_blck_size(int type) {
   case ORC_TYPE_Q4_0: case ORC_TYPE_Q4_1: case ORC_TYPE_Q5_0:
   case ORC_TYPE_Q5_1: case ORC_TYPE_Q8_0: case ORC_TYPE_Q8_1: return 32;
   case ORC_TYPE_Q2_K: case ORC_TYPE_Q8_K: return 256;
+  case ORC_TYPE_Q3_K: case ORC_TYPE_Q4_K: case ORC_TYPE_Q5_K: case ORC_TYPE_Q6_K: return 256;
   default: return 0;
   }
 }
@@ -38,6 +39,10 @@ size_t orc_type_size(int type) {
   case ORC_TYPE_Q8_1: return sizeof(orc_q8_1);
   case ORC_TYPE_Q2_K: return sizeof(orc_q2_K);
   case ORC_TYPE_Q8_K: return sizeof(orc_q8_K);
+  case ORC_TYPE_Q3_K: return sizeof(orc_q3_K);
+  case ORC_TYPE_Q4_K: return sizeof(orc_q4_K);
+  case ORC_TYPE_Q5_K: return sizeof(orc_q5_K);
+  case ORC_TYPE_Q6_K: return sizeof(orc_q6_K);
   default: return 0;
   }
 }
@@ -49,6 +54,7 @@ int orc_vec_dot_type(int type) {
   case ORC_TYPE_Q4_0: case ORC_TYPE_Q5_0: case ORC_TYPE_Q8_0: return ORC_TYPE_Q8_0;
   case ORC_TYPE_Q4_1: case ORC_TYPE_Q5_1: case ORC_TYPE_Q8_1: return ORC_TYPE_Q8_1;
   case ORC_TYPE_Q2_K: return ORC_TYPE_Q8_K;
+  case ORC_TYPE_Q3_K: case ORC_TYPE_Q4_K: case ORC_TYPE_Q5_K: case ORC_TYPE_Q6_K: return ORC_TYPE_Q8_K;
   default: return -1;
   }
 }
@@ -326,6 +332,35 @@ void orc_random_q2_K(void *vy, int64_t n_blocks, uint64_t seed) {
   }
 }
 
+int orc_random_kquant(int type, void *vy, int64_t n_blocks, uint64_t seed) {
+  if (type == ORC_TYPE_Q2_K) { orc_random_q2_K(vy, n_blocks, seed); return 0; }
+  const size_t bs = orc_type_size(type);
+  size_t off_d, off_dmin = 0;                 /* byte offsets of the fp16 super-block scales */
+  switch (type) {
+  case ORC_TYPE_Q3_K: off_d = offsetof(orc_q3_K, d); break;
+  case ORC_TYPE_Q4_K: off_d = 0; off_dmin = 2; break;
+  case ORC_TYPE_Q5_K: off_d = 0; off_dmin = 2; break;
+  case ORC_TYPE_Q6_K: off_d = offsetof(orc_q6_K, d); break;
+  default: return -1;
+  }
+  uint8_t *y = (uint8_t *)vy;
+  uint64_t s = seed;
+  for (int64_t i = 0; i < n_blocks; i++, y += bs) {
+    for (size_t j = 0; j < bs; j += 8) {
+      uint64_t r = sm64(&s);
+      memcpy(y + j, &r, bs - j < 8 ? bs - j : 8);
+    }
+    uint64_t r = sm64(&s);
+    uint16_t h = orc_fp32_to_fp16(0.001f + 0.099f * ((float)(r & 0xFFFFFF) / 16777216.0f));
+    memcpy(y + off_d, &h, 2);
+    if (off_dmin) {
+      h = orc_fp32_to_fp16(0.001f + 0.099f * ((float)((r >> 24) & 0xFFFFFF) / 16777216.0f));
+      memcpy(y + off_dmin, &h, 2);
+    }
+  }
+  return 0;
+}
+
 /* ------------------------------------------------------------------ */
 /* unpack helpers: one block -> 32 (or 256) integer weights            */
 /* ------------------------------------------------------------------ */
@@ -346,7 +381,98 @@ static inline void unpack_q2K(const orc_q2_K *b, int q[256]) {
       for (int l = 0; l < 32; l++) q[e++] = (b->qs[n * 32 + l] >> sh) & 3;
 }
 
+/* ---- K-quants of SURVEY 8f-1 -----------------------------------------
+ * One super-block -> 256 signed integer weights q[e] in element order, the
+ * integer scale sc[g] of every 16-element sub-block g = e/16 and, for the
+ * formats with a minimum, the integer min mn[g]:
+ *     w[e] = f(d) * sc[e/16] * q[e] - f(dmin) * mn[e/16]
+ * get_scale_min_k4: ggml-quants.c:2027-2034.                              */
+static inline void scale_min_k4(int j, const uint8_t *q, int *d, int *m) {
+  if (j < 4) { *d = q[j] & 63; *m = q[j + 4] & 63; }
+  else { *d = (q[j + 4] & 0xF) | ((q[j - 4] >> 6) << 4); *m = (q[j + 4] >> 4) | ((q[j] >> 6) << 4); }
+}
+typedef struct { int q[256]; int sc[16]; int mn[16]; float d, dmin; } orc_kq;
+
+static void unpack_kq(int type, const void *vb, orc_kq *o) {
+  memset(o->mn, 0, sizeof o->mn);
+  o->dmin = 0.0f;
+  switch (type) {
+  case ORC_TYPE_Q4_K: {          /* ggml-quants.c:2851-2874 / 7301-7358 */
+    const orc_q4_K *b = (const orc_q4_K *)vb;
+    o->d = orc_fp16_to_fp32(b->d); o->dmin = orc_fp16_to_fp32(b->dmin);
+    for (int g = 0; g < 8; g++) {              /* 32-element groups */
+      int sc, m; scale_min_k4(g, b->scales, &sc, &m);
+      o->sc[2 * g] = o->sc[2 * g + 1] = sc;
+      o->mn[2 * g] = o->mn[2 * g + 1] = m;
+      for (int l = 0; l < 32; l++) {
+        const uint8_t by = b->qs[32 * (g >> 1) + l];
+        o->q[32 * g + l] = (g & 1) ? (by >> 4) : (by & 0xF);
+      }
+    }
+  } break;
+  case ORC_TYPE_Q5_K: {          /* ggml-quants.c:3134-3160 / 7968-8029 */
+    const orc_q5_K *b = (const orc_q5_K *)vb;
+    o->d = orc_fp16_to_fp32(b->d); o->dmin = orc_fp16_to_fp32(b->dmin);
+    for (int g = 0; g < 8; g++) {
+      int sc, m; scale_min_k4(g, b->scales, &sc, &m);
+      o->sc[2 * g] = o->sc[2 * g + 1] = sc;
+      o->mn[2 * g] = o->mn[2 * g + 1] = m;
+      for (int l = 0; l < 32; l++) {
+        const uint8_t by = b->qs[32 * (g >> 1) + l];
+        o->q[32 * g + l] = ((g & 1) ? (by >> 4) : (by & 0xF)) + (((b->qh[l] >> g) & 1) ? 16 : 0);
+      }
+    }
+  } break;
+  case ORC_TYPE_Q6_K: {          /* ggml-quants.c:3383-3412 / 8695-8737 */
+    const orc_q6_K *b = (const orc_q6_K *)vb;
+    o->d = orc_fp16_to_fp32(b->d);
+    for (int n = 0; n < 2; n++)
+      for (int l = 0; l < 32; l++) {
+        const uint8_t la = b->ql[64 * n + l], lb = b->ql[64 * n + 32 + l], h = b->qh[32 * n + l];
+        int *q = o->q + 128 * n;
+        q[l]      = (int)((la & 0xF) | (((h >> 0) & 3) << 4)) - 32;
+        q[l + 32] = (int)((lb & 0xF) | (((h >> 2) & 3) << 4)) - 32;
+        q[l + 64] = (int)((la >> 4)  | (((h >> 4) & 3) << 4)) - 32;
+        q[l + 96] = (int)((lb >> 4)  | (((h >> 6) & 3) << 4)) - 32;
+      }
+    for (int g = 0; g < 16; g++) o->sc[g] = b->scales[g];
+  } break;
+  default: {                     /* Q3_K: ggml-quants.c:2550-2598 / 6583-6646 */
+    const orc_q3_K *b = (const orc_q3_K *)vb;
+    o->d = orc_fp16_to_fp32(b->d);
+    for (int g = 0; g < 16; g++) {
+      const int lo = (g < 8) ? (b->scales[g] & 0xF) : (b->scales[g - 8] >> 4);
+      const int hi = (b->scales[8 + (g & 3)] >> (2 * (g >> 2))) & 3;
+      o->sc[g] = (lo | (hi << 4)) - 32;
+    }
+    int e = 0;
+    for (int n = 0; n < 2; n++)
+      for (int j = 0; j < 4; j++)
+        for (int l = 0; l < 32; l++)
+          o->q[e++] = (int)((b->qs[32 * n + l] >> (2 * j)) & 3) - (((b->hmask[l] >> (4 * n + j)) & 1) ? 0 : 4);
+  } break;
+  }
+}
+static int is_kq_ext(int t) {
+  return t == ORC_TYPE_Q3_K || t == ORC_TYPE_Q4_K || t == ORC_TYPE_Q5_K || t == ORC_TYPE_Q6_K;
+}
+
 int orc_dequantize_row(int type, const void *vx, float *y, int64_t k) {
+  if (is_kq_ext(type)) {
+    orc_kq u;
+    const size_t bs = orc_type_size(type);
+    for (int64_t i = 0; i < k / 256; i++) {
+      unpack_kq(type, (const char *)vx + (size_t)i * bs, &u);
+      for (int e = 0; e < 256; e++) {
+        /* dequantize_row_q{4,5}_K: d1 = d*sc, m1 = min*m, y = d1*q - m1; q{3,6}_K: (d*sc)*q */
+        const float dl = u.d * (float)u.sc[e / 16];
+        y[i * 256 + e] = (type == ORC_TYPE_Q4_K || type == ORC_TYPE_Q5_K)
+                             ? dl * (float)u.q[e] - u.dmin * (float)u.mn[e / 16]
+                             : dl * (float)u.q[e];
+      }
+    }
+    return 0;
+  }
   int q[256];
   switch (type) {
   case ORC_TYPE_F32: memcpy(y, vx, (size_t)k * 4); return 0;
@@ -483,7 +609,24 @@ static inline orc_term term_q2_K(const orc_q2_K *w, const orc_q8_K *x) {
   return t;
 }
 
+/* ggml_vec_dot_q{3,4,5,6}_K_q8_K, scalar forms: integer sub-block dots times the
+ * integer scales, the min term from bsums; term = x.d*f(w.d)*isum - x.d*f(w.dmin)*summs */
+static inline orc_term term_kq(int type, const void *w, const orc_q8_K *x) {
+  orc_kq u; unpack_kq(type, w, &u);
+  int isum = 0, summs = 0;
+  for (int g = 0; g < 16; g++) {
+    int sub = 0;
+    for (int l = 0; l < 16; l++) sub += u.q[g * 16 + l] * (int)x->qs[g * 16 + l];
+    isum += u.sc[g] * sub;
+    summs += (int)x->bsums[g] * u.mn[g];
+  }
+  orc_term t = { x->d * u.d, isum, x->d * u.dmin, 0, summs };
+  return t;
+}
+
 static inline orc_term block_term(int w_type, const char *w, const char *x, int64_t kb) {
+  if (is_kq_ext(w_type))
+    return term_kq(w_type, w + (size_t)kb * orc_type_size(w_type), (const orc_q8_K *)x + kb);
   switch (w_type) {
   case ORC_TYPE_Q4_0: return term_q4_0((const orc_q4_0 *)w + kb, (const orc_q8_0 *)x + kb);
   case ORC_TYPE_Q4_1: return term_q4_1((const orc_q4_1 *)w + kb, (const orc_q8_1 *)x + kb);
@@ -497,7 +640,7 @@ static inline orc_term block_term(int w_type, const char *w, const char *x, int6
 static int supported_w(int t) {
   return t == ORC_TYPE_F32 || t == ORC_TYPE_Q4_0 || t == ORC_TYPE_Q4_1 ||
          t == ORC_TYPE_Q5_0 || t == ORC_TYPE_Q5_1 || t == ORC_TYPE_Q8_0 ||
-         t == ORC_TYPE_Q2_K;
+         t == ORC_TYPE_Q2_K || is_kq_ext(t);
 }
 
 /* one output element, double accumulation */
@@ -511,7 +654,7 @@ static double dot_f64(int w_type, const char *wrow, const char *xrow, int64_t K)
   const int64_t nb = K / orc_blck_size(w_type);
   for (int64_t kb = 0; kb < nb; kb++) {
     orc_term t = block_term(w_type, wrow, xrow, kb);
-    if (w_type == ORC_TYPE_Q2_K)
+    if (w_type == ORC_TYPE_Q2_K || is_kq_ext(w_type))
       acc += (double)t.scale * (double)t.isum - (double)t.extra_a * (double)t.extra_i;
     else
       acc += (double)t.scale * (double)t.isum + (double)t.extra_a * (double)t.extra_b;
@@ -530,7 +673,7 @@ static float dot_f32(int w_type, const char *wrow, const char *xrow, int64_t K) 
   const int64_t nb = K / orc_blck_size(w_type);
   for (int64_t kb = 0; kb < nb; kb++) {
     orc_term t = block_term(w_type, wrow, xrow, kb);
-    if (w_type == ORC_TYPE_Q2_K) {
+    if (w_type == ORC_TYPE_Q2_K || is_kq_ext(w_type)) {
       const float a = t.scale * (float)t.isum;
       const float b = t.extra_a * (float)t.extra_i;
       acc += a - b;

@@ -42,7 +42,14 @@ enum {
   ORC_TYPE_Q8_0 = 8,
   ORC_TYPE_Q8_1 = 9,
   ORC_TYPE_Q2_K = 10,
-  ORC_TYPE_Q8_K = 15
+  ORC_TYPE_Q8_K = 15,
+  /* SURVEY 8f-1 K-quants: outside the reference's lamm table, so the behaviour
+   * restated is ggml's own ggml_vec_dot_q{3,4,5,6}_K_q8_K (scalar forms,
+   * ggml-quants.c:6583-6646, 7301-7358, 7968-8029, 8695-8737)              */
+  ORC_TYPE_Q3_K = 11,
+  ORC_TYPE_Q4_K = 12,
+  ORC_TYPE_Q5_K = 13,
+  ORC_TYPE_Q6_K = 14
 };
 
 #pragma pack(push, 1)
@@ -54,6 +61,11 @@ typedef struct { uint16_t d; int8_t qs[32]; } orc_q8_0;                   /* 34 
 typedef struct { uint16_t d, s; int8_t qs[32]; } orc_q8_1;                /* 36 B */
 typedef struct { uint8_t scales[16]; uint8_t qs[64]; uint16_t d, dmin; } orc_q2_K; /* 84 B / 256 */
 typedef struct { float d; int8_t qs[256]; int16_t bsums[16]; } orc_q8_K;  /* 292 B / 256 */
+/* ggml-common.h:228-313 */
+typedef struct { uint8_t hmask[32]; uint8_t qs[64]; uint8_t scales[12]; uint16_t d; } orc_q3_K;          /* 110 B */
+typedef struct { uint16_t d, dmin; uint8_t scales[12]; uint8_t qs[128]; } orc_q4_K;                      /* 144 B */
+typedef struct { uint16_t d, dmin; uint8_t scales[12]; uint8_t qh[32]; uint8_t qs[128]; } orc_q5_K;      /* 176 B */
+typedef struct { uint8_t ql[128]; uint8_t qh[64]; int8_t scales[16]; uint16_t d; } orc_q6_K;             /* 210 B */
 #pragma pack(pop)
 
 /* ---- type table ------------------------------------------------------- */
@@ -81,6 +93,9 @@ int  orc_quantize_act(int vec_dot_type, const float *x, int64_t ldx, void *y,
 int  orc_quantize_weights(int type, const float *x, void *y, int64_t n_rows,
                           int64_t k);
 void orc_random_q2_K(void *y, int64_t n_blocks, uint64_t seed);
+/* same for any super-block weight type (Q2_K .. Q6_K): uniform random bit
+ * patterns in every quant / scale field, d and dmin ~ fp16(U(0.001, 0.1))   */
+int  orc_random_kquant(int type, void *y, int64_t n_blocks, uint64_t seed);
 /* dequantize one row of k elements to f32 (ground truth helper) */
 int  orc_dequantize_row(int type, const void *x, float *y, int64_t k);
 

@@ -15,13 +15,19 @@ ORACLE_DIR = os.path.join(ROOT, "oracle")
 
 # ggml type ids (llama.cpp-b2430/ggml.h:341-369)
 F32, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0, Q8_1, Q2_K, Q8_K = 0, 2, 3, 6, 7, 8, 9, 10, 15
+Q3_K, Q4_K, Q5_K, Q6_K = 11, 12, 13, 14                   # SURVEY 8f-1 (dev.md:86-95)
 TYPE_NAMES = {F32: "f32", Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1",
-              Q8_0: "q8_0", Q8_1: "q8_1", Q2_K: "q2_k", Q8_K: "q8_k"}
+              Q8_0: "q8_0", Q8_1: "q8_1", Q2_K: "q2_k", Q8_K: "q8_k",
+              Q3_K: "q3_k", Q4_K: "q4_k", Q5_K: "q5_k", Q6_K: "q6_k"}
 NAME_TO_TYPE = {v: k for k, v in TYPE_NAMES.items()}
 W_TYPES = [F32, Q2_K, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0]     # src/loongarch_matmul.cpp:37-42
-BLCK = {F32: 1, Q4_0: 32, Q4_1: 32, Q5_0: 32, Q5_1: 32, Q8_0: 32, Q8_1: 32, Q2_K: 256, Q8_K: 256}
-TSIZE = {F32: 4, Q4_0: 18, Q4_1: 20, Q5_0: 22, Q5_1: 24, Q8_0: 34, Q8_1: 36, Q2_K: 84, Q8_K: 292}
-VEC_DOT = {F32: F32, Q4_0: Q8_0, Q4_1: Q8_1, Q5_0: Q8_0, Q5_1: Q8_1, Q8_0: Q8_0, Q2_K: Q8_K}
+KQ_TYPES = [Q3_K, Q4_K, Q5_K, Q6_K]                     # beyond the reference's table: ggml's own vec_dot is the oracle
+BLCK = {F32: 1, Q4_0: 32, Q4_1: 32, Q5_0: 32, Q5_1: 32, Q8_0: 32, Q8_1: 32, Q2_K: 256, Q8_K: 256,
+        Q3_K: 256, Q4_K: 256, Q5_K: 256, Q6_K: 256}
+TSIZE = {F32: 4, Q4_0: 18, Q4_1: 20, Q5_0: 22, Q5_1: 24, Q8_0: 34, Q8_1: 36, Q2_K: 84, Q8_K: 292,
+         Q3_K: 110, Q4_K: 144, Q5_K: 176, Q6_K: 210}
+VEC_DOT = {F32: F32, Q4_0: Q8_0, Q4_1: Q8_1, Q5_0: Q8_0, Q5_1: Q8_1, Q8_0: Q8_0, Q2_K: Q8_K,
+           Q3_K: Q8_K, Q4_K: Q8_K, Q5_K: Q8_K, Q6_K: Q8_K}
 
 i64, vp, fp = C.c_int64, C.c_void_p, C.POINTER(C.c_float)
 
@@ -64,6 +70,7 @@ class Oracle:
         L.orc_quantize_act.argtypes = [C.c_int, fp, i64, vp, i64, i64]
         L.orc_quantize_weights.argtypes = [C.c_int, fp, vp, i64, i64]
         L.orc_random_q2_K.argtypes = [vp, i64, C.c_uint64]
+        L.orc_random_kquant.argtypes = [C.c_int, vp, i64, C.c_uint64]
         L.orc_dequantize_row.argtypes = [C.c_int, vp, fp, i64]
         L.orc_mul_mat_q.argtypes = [C.c_int, vp, i64, vp, i64, fp, i64, i64, i64, i64]
         L.orc_mul_mat_q_f32.argtypes = L.orc_mul_mat_q.argtypes
@@ -80,12 +87,14 @@ class Oracle:
         return out
 
     def quantize_weights(self, t, w, seed=0):
-        """w: [M, K] f32 -> uint8 [M, row_size].  Q2_K: random super-blocks."""
+        """w: [M, K] f32 -> uint8 [M, row_size].  Q2_K .. Q6_K: random super-blocks."""
         w = np.ascontiguousarray(w, np.float32)
         m, k = w.shape
         out = np.zeros((m, row_size(t, k)), np.uint8)
         if t == Q2_K:
             self.L.orc_random_q2_K(_ptr(out), m * (k // 256), seed)
+        elif t in KQ_TYPES:
+            assert self.L.orc_random_kquant(t, _ptr(out), m * (k // 256), seed) == 0
         else:
             assert self.L.orc_quantize_weights(t, _fptr(w), _ptr(out), m, k) == 0
         return out

@@ -3,7 +3,7 @@ Runs only where that library exists (this container; it also travels to the GPU 
 import numpy as np
 import pytest
 from conftest import make_x, tol_c
-from oracle_lib import F32, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES
+from oracle_lib import F32, KQ_TYPES, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES
 
 
 @pytest.mark.parametrize("vt", [Q8_0, Q8_1, Q8_K])
@@ -50,6 +50,26 @@ def test_q2k_random_blocks(oracle, ref):
     assert np.isfinite(c).all()
     assert np.abs(ref.lamm_mul_mat(Q2_K, wq, x, xq) - c).max() <= tol_c(c, k)
     assert np.array_equal(oracle.dequantize(Q2_K, wq, k), ref.dequantize(Q2_K, wq, k))
+
+
+@pytest.mark.parametrize("t", KQ_TYPES)
+def test_kquants_vs_ggml_vec_dot(oracle, ref, t):
+    """Q3_K..Q6_K are outside lamm's table (its gate refuses them), so the pin is ggml's own
+    ggml_vec_dot_q*_K_q8_K and dequantize_row_q*_K -- on weights from ggml's quantizer AND on random
+    bit patterns (every scale / high-bit combination)."""
+    rng = np.random.default_rng(77 + t)
+    m, n, k = 19, 5, 2048
+    x = make_x(rng, n, k)
+    xq = ref.quantize_act(Q8_K, x)
+    for wq in (ref.quantize_weights(t, rng.standard_normal((m, k)).astype(np.float32)),
+               oracle.quantize_weights(t, np.zeros((m, k), np.float32), seed=1000 + t)):
+        c = oracle.mul_mat_q(t, wq, xq, k)
+        assert np.isfinite(c).all()
+        assert np.abs(ref.vec_dot(t, wq, xq, k) - c).max() <= tol_c(c, k)
+        assert np.abs(ref.graph_mul_mat(t, wq, x) - c).max() <= tol_c(c, k)     # lamm refuses -> ggml's own path
+        assert np.array_equal(oracle.dequantize(t, wq, k), ref.dequantize(t, wq, k))
+    with pytest.raises(AssertionError):
+        ref.lamm_mul_mat(t, wq, x, xq)                   # the reference operator itself refuses these types
 
 
 def test_fp16_tables_all_65536_halves(oracle, ref):
