@@ -55,10 +55,11 @@ def set_model(name):
 
 
 set_model("7b")
-TYPE_IDS = {"f32": 0, "q4_0": 2, "q4_1": 3, "q5_0": 6, "q5_1": 7, "q8_0": 8, "q2_k": 10}
-BLCK = {0: 1, 2: 32, 3: 32, 6: 32, 7: 32, 8: 32, 10: 256}
-TSIZE = {0: 4, 2: 18, 3: 20, 6: 22, 7: 24, 8: 34, 10: 84}
-VEC_DOT = {0: 0, 2: 8, 3: 9, 6: 8, 7: 9, 8: 8, 10: 15}
+TYPE_IDS = {"f32": 0, "q4_0": 2, "q4_1": 3, "q5_0": 6, "q5_1": 7, "q8_0": 8, "q2_k": 10,
+            "q3_k": 11, "q4_k": 12, "q5_k": 13, "q6_k": 14}          # 11-14: SURVEY 8f-1 (sweeps only)
+BLCK = {0: 1, 2: 32, 3: 32, 6: 32, 7: 32, 8: 32, 10: 256, 11: 256, 12: 256, 13: 256, 14: 256}
+TSIZE = {0: 4, 2: 18, 3: 20, 6: 22, 7: 24, 8: 34, 10: 84, 11: 110, 12: 144, 13: 176, 14: 210}
+VEC_DOT = {0: 0, 2: 8, 3: 9, 6: 8, 7: 9, 8: 8, 10: 15, 11: 15, 12: 15, 13: 15, 14: 15}
 ACT_SIZE = {0: (1, 4), 8: (32, 34), 9: (32, 36), 15: (256, 292)}
 
 
@@ -163,6 +164,14 @@ def synth_weight(torch, t, m, k, gen, device):
     kb, bs = k // BLCK[t], TSIZE[t]
     raw = torch.randint(0, 256, (m, kb, bs), generator=gen, device=device, dtype=torch.uint8)
     halves = raw.view(torch.int16)                       # [m, kb, bs/2]
+    if t in (11, 12, 13, 14):                            # Q3_K..Q6_K (sweeps only): random fields, finite fp16 d / dmin
+        d16 = (torch.rand((m, kb), generator=gen, device=device) * 0.009 + 0.001).to(torch.float16).view(torch.int16)
+        if t in (12, 13):
+            halves[:, :, 0] = d16
+            halves[:, :, 1] = d16
+        else:
+            halves[:, :, bs // 2 - 1] = d16
+        return raw.view(m, kb * bs)
     base = (k * _QVAR[t] * 1.0208) ** -0.5
     d = (torch.rand((m, kb), generator=gen, device=device) * 0.5 + 0.75) * base
     d16 = d.to(torch.float16)
@@ -569,12 +578,31 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
         keep.append((src0, src1, dst, p))
         calls.append((C.byref(p), C.byref(dst)))
     can, mm = lib.lamm_can_mul_mat, lib.lamm_mul_mat
+    # the same calls from a C loop (tools/bench_driver.c), as ggml makes them; Python loop if it was not built
+    drv = None
+    drv_path = os.path.join(ROOT, "tools", "libbench_driver.so")
+    if os.path.exists(drv_path) and not os.environ.get("LAMM_BENCH_PYLOOP"):
+        drv = C.CDLL(drv_path).bench_drive_calls
+        drv.restype = C.c_double
+        drv.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int, C.c_int]
+        n_calls = len(keep)
+        p_arr = (C.c_void_p * n_calls)(*[C.addressof(k_[3]) for k_ in keep])
+        d_arr = (C.c_void_p * n_calls)(*[C.addressof(k_[2]) for k_ in keep])
+        can_p, mm_p = C.cast(can, C.c_void_p), C.cast(mm, C.c_void_p)
 
-    def token():
-        for p, d in calls:
-            if not can(p, d):
+    def token(n_tok=1):
+        if drv is not None:
+            sec_ = drv(can_p, mm_p, p_arr, d_arr, n_calls, n_tok)
+            if sec_ < 0:
                 raise RuntimeError("lamm_can_mul_mat refused the bench shape")
-            mm(p, d)
+            return sec_
+        t_ = time.perf_counter()
+        for _ in range(n_tok):
+            for p, d in calls:
+                if not can(p, d):
+                    raise RuntimeError("lamm_can_mul_mat refused the bench shape")
+                mm(p, d)
+        return time.perf_counter() - t_
     token()          # uploads the weights
     token()
     torch.cuda.synchronize()
@@ -582,10 +610,7 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
         dist.barrier()
     prof = (C.c_double * 8)()
     lib.lammcu_host_profile(prof, 1)
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        token()
-    sec = time.perf_counter() - t0
+    sec = token(steps)
     lib.lammcu_host_quiesce()                 # outside the timed region: every call above was synchronous
     torch.cuda.synchronize()
     lib.lammcu_host_profile(prof, 1)
@@ -601,12 +626,16 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
     d2h = sum((shard(m)[1] - shard(m)[0]) * 4 for _, m, k in ops)
     return {"value": steps / sec, "unit": "tok/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "steps": steps, "ms_per_step": sec / steps * 1e3, "per_call_phases": phases,
-            "host_mode": int(lib.lammcu_get_host_mode()),
+            "host_mode": int(lib.lammcu_get_host_mode()), "caller": "C loop (tools/bench_driver.c)" if drv else "python ctypes loop",
+            "server_sentinel": int(os.environ.get("LAMM_SERVER_SENTINEL", "0")),
             "api": "lamm_can_mul_mat + lamm_mul_mat(ggml_compute_params*, ggml_tensor*) on host tensors, "
                    "one synchronous call per matmul (225 per token); host wall clock; host mode %d (%s)"
                    % (int(lib.lammcu_get_host_mode()),
                       "jobs posted to the resident decode server: X pulled from pinned host memory by the kernel, "
                       "C written back as tagged pairs the caller polls" if lib.lammcu_get_host_mode() == 1 else
+                      "jobs posted to the resident decode server: X written as tagged pairs next to the job and polled "
+                      "by the kernel in the same PCIe round trip, C written back as tagged pairs the caller polls"
+                      if lib.lammcu_get_host_mode() == 2 else
                       "copy-engine H2D + one launch + stream synchronize per call"),
             "note": "weights uploaded once at first use (registry keyed by src0->data); with N>1 the "
                     "per-rank C slices are not gathered in this leg"}
@@ -747,7 +776,7 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
-    ap.add_argument("--fmt", default="q4_1", choices=sorted(TYPE_IDS))
+    ap.add_argument("--fmt", default="q4_1", choices=sorted(f for f, t in TYPE_IDS.items() if t == 0 or t in _QVAR))
     ap.add_argument("--model", default="7b", choices=sorted(MODELS), help="chain shapes (the metric is quoted on 7b)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--host-mode", type=int, default=None, choices=[0, 1, 2],

@@ -820,6 +820,28 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
   unsigned int tag = 0u, x_tag = 0u;
   if constexpr (SERVER) {
     x_tag = job_tag;                               // the server kernel has staged X as {value, tag} pairs
+    // CTA 0 is still pulling X over PCIe: instead of 75 000 threads spinning on L2 (against CTA 0's own
+    // stores), one lane sleeps on the LAST pair and the rest are parked at the barrier.  A wake-up hint only:
+    // stage_x_row validates every element's tag.
+    if (sp->sentinel && bid != 0) {
+      if (threadIdx.x == 0) {
+        const unsigned long long *last = p.x_ll + ((size_t)p.kb * type_info(WT).blck - 1);
+        unsigned long long v, t0 = 0;
+        unsigned int spins = 0;
+        while (true) {
+          asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(last) : "memory");
+          if ((unsigned int)(v >> 32) == x_tag) break;
+          __nanosleep(60);
+          if ((++spins & 1023u) == 0) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 2000000000ull) break;        // stage_x_row reports the timeout
+          }
+        }
+      }
+      __syncthreads();
+    }
   } else if (p.n_peer > 0) {
     // This launch's tag = its sequence number on the communicator, from an arrival ticket: every CTA of
     // every sharded launch (all have gridDim.x == p.grid_fixed) adds 1 to a rank-local counter BEFORE it
@@ -975,7 +997,90 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
   const int bid = blockIdx.x;
   unsigned long long t_launch;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_launch));
+  __shared__ unsigned int ctl;                     // inline-X poll of CTA 0: 0 waiting, 1 job seen, 2 give up
+  const bool inl = sp.x_pairs_host != nullptr && bid == 0;
   for (unsigned int s = sp.seq0;; ++s) {
+    if (inl) {
+      // ---- 1 + 2 fused (host mode 2): the caller wrote X as {value, tag} pairs BEFORE the job, so CTA 0
+      // polls the job words and the first 8 * blockDim pairs of the row in the SAME PCIe round trip;
+      // every thread keeps its 8 pairs in registers and republishes them once all tags match.
+      const unsigned long long *xsrc = sp.x_pairs_host + 8 * (size_t)tid;
+      unsigned long long xv[8], t0 = 0;
+      if (tid == 0) {
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        ctl = (s != sp.seq0 && t0 - t_launch > (unsigned long long)sp.life_ns) ? 2u : 0u;
+      }
+      __syncthreads();
+      unsigned int st = ctl, x_iters = 0;
+      while (st != 2u) {
+        unsigned long long v = 0;
+        if (warp == 0 && lane < kSrvWords)
+          asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(sp.mbox_host + lane) : "memory");
+#pragma unroll
+        for (int i = 0; i < 4; i++) ld_ll2(xsrc + 2 * i, xv[2 * i], xv[2 * i + 1]);
+        if (warp == 0) {
+          const bool ok = __all_sync(0xffffffffu, lane >= kSrvWords || (unsigned int)(v >> 32) == s);
+          if (ok && lane < kSrvWords) jw[lane] = (unsigned int)v;
+          if (lane == 0) {
+            if (ok) ctl = 1u;
+            else if (ctl == 0u) {
+              unsigned long long now;
+              asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+              if (now - t0 > (unsigned long long)sp.idle_ns) ctl = 2u;
+            }
+          }
+        }
+        __syncthreads();
+        st = ctl;
+        bool mine = false;
+        if (st == 1u) {
+          if (jw[0] != 1u) mine = true;                            // stop request: no row to wait for
+          else {
+            const int K = (int)jw[5] * type_info(WT).blck;
+            bool ok = true;
+#pragma unroll
+            for (int i = 0; i < 8; i++) ok &= ((unsigned int)(xv[i] >> 32) == s);
+            mine = (8 * tid >= K) || ok;
+          }
+          if (++x_iters > 400000u) { if (tid == 0) *sp.status = 3u; mine = true; }   // the row never completed
+        }
+        if (__syncthreads_and(mine ? 1 : 0) || st == 2u) break;
+      }
+      if (warp == 0 && lane < kSrvWords) {
+        unsigned long long v = ((unsigned long long)s << 32) | (st == 2u ? (lane == 0 ? 2u : 0u) : jw[lane]);
+        jw[lane] = (unsigned int)v;
+        asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + lane), "l"(v) : "memory");
+        if (st == 2u && lane == 0) {
+          sp.done_host[1] = s;
+          __threadfence_system();
+        }
+      }
+      __syncthreads();
+      srv_stamp(&sp, s, 0);                        // job (and row) seen
+      if (jw[0] != 1u) return;
+      const int K = (int)jw[5] * type_info(WT).blck;
+      const unsigned long long th = (unsigned long long)s << 32;
+      for (int idx = 8 * tid; idx < K; idx += 8 * (int)blockDim.x) {
+        if (idx >= 8 * (int)blockDim.x) {          // K > 4096: the rest of the row, already in host memory
+          const unsigned long long *src = sp.x_pairs_host + idx;
+          for (unsigned int tries = 0;; tries++) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) ld_ll2(src + 2 * i, xv[2 * i], xv[2 * i + 1]);
+            bool ok = true;
+#pragma unroll
+            for (int i = 0; i < 8; i++) ok &= ((unsigned int)(xv[i] >> 32) == s);
+            if (ok) break;
+            if (tries > 400000u) { *sp.status = 3u; break; }
+          }
+        }
+        unsigned long long *dst = sp.x_ll + idx;
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+          asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst + 2 * i),
+                       "l"(th | (xv[2 * i] & 0xffffffffull)), "l"(th | (xv[2 * i + 1] & 0xffffffffull)) : "memory");
+      }
+      srv_stamp(&sp, s, 1);                        // X forwarded
+    } else {
     // ---- 1. the job
     if (warp == 0) {
       const unsigned long long *src = bid == 0 ? sp.mbox_host : sp.mbox_dev;
@@ -1007,8 +1112,9 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
     __syncthreads();
     if (bid == 0) srv_stamp(&sp, s, 0);            // job seen
     if (jw[0] != 1u) return;                       // 2: stop request or idle time-out
+    }
     // ---- 2. CTA 0: X, pinned host memory -> {value, tag} pairs in HBM (one PCIe round trip)
-    if (bid == 0) {
+    if (bid == 0 && !inl) {
       const int K4 = (int)jw[5] * (type_info(WT).blck / 4);
       const unsigned long long th = (unsigned long long)s << 32;
       for (int base = 0; base < K4; base += 4 * (int)blockDim.x) {

@@ -187,8 +187,9 @@ def test_lamm_mul_mat_operator(gpu, oracle, t):
     assert can and np.array_equal(again, got)
 
 
+@pytest.mark.parametrize("srv_mode,sentinel", [(1, 0), (2, 0), (2, 1), (1, 1)])
 @pytest.mark.parametrize("t", QTYPES)
-def test_operator_decode_host_modes(gpu, oracle, t):
+def test_operator_decode_host_modes(gpu, oracle, t, srv_mode, sentinel):
     """N == 1 through the operator in both modes of the host path (one launch + stream synchronize
     per call; jobs posted to the resident decode server): identical bits, fresh X each call (a
     stale staging row or tag would show), shapes of different row counts interleaved, and GPU work
@@ -199,20 +200,23 @@ def test_operator_decode_host_modes(gpu, oracle, t):
     ws = [weights(oracle, t, m, k, seed=7 * m + k) for m, k in shapes]
     rng = np.random.default_rng(t)
     default_mode = lib.lammcu_get_host_mode()
+    old_sentinel = os.environ.get("LAMM_SERVER_SENTINEL")
+    os.environ["LAMM_SERVER_SENTINEL"] = str(sentinel)       # read at every server launch
     try:
-        for rep in range(3):
+        for rep in range(3 if srv_mode == 1 and sentinel == 0 else 1):
             for (m, k), w in zip(shapes, ws):
                 x = rng.standard_normal((1, k)).astype(np.float32)
                 want = oracle.mul_mat(t, w, x)
                 got = {}
-                for mode in (0, 1):
+                for mode in (0, 1, 2):
                     assert lib.lammcu_set_host_mode(mode) == 0
                     can, got[mode] = gpu.lamm_mul_mat_host(t, w, x, nth=1)
                     assert can
                 assert np.abs(got[0] - want).max() <= tol_c(want, k), f"{TYPE_NAMES[t]} {m}x{k}"
                 assert np.array_equal(got[1], got[0]), f"{TYPE_NAMES[t]} {m}x{k}"
+                assert np.array_equal(got[2], got[0]), f"{TYPE_NAMES[t]} {m}x{k} (inline X)"
         # a run of server jobs back to back (no mode switch in between), torch work interleaved
-        assert lib.lammcu_set_host_mode(1) == 0
+        assert lib.lammcu_set_host_mode(srv_mode) == 0
         z = torch.ones(1024, device="cuda")
         for rep in range(40):
             (m, k), w = shapes[rep % len(shapes)], ws[rep % len(shapes)]
@@ -238,7 +242,11 @@ def test_operator_decode_host_modes(gpu, oracle, t):
     finally:
         lib.lammcu_set_server_timeouts(200, 5000)
         lib.lammcu_set_host_mode(default_mode)
-    assert lib.lammcu_set_host_mode(2) != 0
+        if old_sentinel is None:
+            os.environ.pop("LAMM_SERVER_SENTINEL", None)
+        else:
+            os.environ["LAMM_SERVER_SENTINEL"] = old_sentinel
+    assert lib.lammcu_set_host_mode(3) != 0
 
 
 # ---------------------------------------------------------------- single-launch decode kernel (N == 1)
