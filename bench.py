@@ -627,15 +627,12 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
     return {"value": steps / sec, "unit": "tok/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "steps": steps, "ms_per_step": sec / steps * 1e3, "per_call_phases": phases,
             "host_mode": int(lib.lammcu_get_host_mode()), "caller": "C loop (tools/bench_driver.c)" if drv else "python ctypes loop",
-            "server_sentinel": int(os.environ.get("LAMM_SERVER_SENTINEL", "0")),
             "api": "lamm_can_mul_mat + lamm_mul_mat(ggml_compute_params*, ggml_tensor*) on host tensors, "
                    "one synchronous call per matmul (225 per token); host wall clock; host mode %d (%s)"
                    % (int(lib.lammcu_get_host_mode()),
                       "jobs posted to the resident decode server: X pulled from pinned host memory by the kernel, "
                       "C written back as tagged pairs the caller polls" if lib.lammcu_get_host_mode() == 1 else
-                      "jobs posted to the resident decode server: X written as tagged pairs next to the job and polled "
-                      "by the kernel in the same PCIe round trip, C written back as tagged pairs the caller polls"
-                      if lib.lammcu_get_host_mode() == 2 else
+
                       "copy-engine H2D + one launch + stream synchronize per call"),
             "note": "weights uploaded once at first use (registry keyed by src0->data); with N>1 the "
                     "per-rank C slices are not gathered in this leg"}
@@ -779,7 +776,7 @@ def main():
     ap.add_argument("--fmt", default="q4_1", choices=sorted(f for f, t in TYPE_IDS.items() if t == 0 or t in _QVAR))
     ap.add_argument("--model", default="7b", choices=sorted(MODELS), help="chain shapes (the metric is quoted on 7b)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--host-mode", type=int, default=None, choices=[0, 1, 2],
+    ap.add_argument("--host-mode", type=int, default=None, choices=[0, 1],
                     help="e2e leg: completion mode of the host path (lammcu_set_host_mode; default: the library's)")
     ap.add_argument("--no-batch", dest="batch", action="store_false",
                     help="N=1: one launch per matmul (225/token) instead of one per sibling group (129/token)")

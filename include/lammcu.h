@@ -250,11 +250,7 @@ void lammcu_host_profile(double *out8, int reset);
  *      word.  The server exits by itself after LAMM_SERVER_IDLE_US (default 200) without a job and
  *      is relaunched on demand; every other entry point that needs the library's stream stops it
  *      first.  lammcu_host_quiesce() stops it explicitly (e.g. before timing unrelated GPU work).
- *   2  as 1, but the caller writes X as {value, tag} pairs BEFORE the job words and CTA 0 polls the
- *      job and the row in the same PCIe round trip ("inline X": one round trip less per call).
- * Results are bit-identical in all modes.  Environment override at load time: LAMM_HOST_MODE.
- * LAMM_SERVER_SENTINEL=1 (read at every server launch): the CTAs that wait for CTA 0 to republish X
- * park at a barrier behind one polling lane instead of all spinning on L2.                       */
+ * Results are bit-identical in both modes.  Environment override at load time: LAMM_HOST_MODE.  */
 int lammcu_set_host_mode(int mode);
 int lammcu_get_host_mode(void);
 int lammcu_host_quiesce(void);

@@ -159,10 +159,6 @@ struct ServerParams {
   unsigned int idle_ns;                  // exit after this long without a job
   unsigned int life_ns;                  // ... or this long after the launch (other streams' work gets the SMs)
   unsigned long long *trace;             // optional: [64 jobs][8] globaltimer stamps (diagnostics)
-  // host mode 2 ("inline X"): the caller writes the activation row as {value, tag} pairs next to the job and
-  // CTA 0 polls job AND row in the same PCIe round trip (NULL: mode 1, X pulled after the job was seen)
-  const unsigned long long *x_pairs_host;
-  int sentinel;                          // CTAs > 0 sleep on the last republished X pair instead of all spinning
 };
 int decode_server_job(int w_type, const void *w, int64_t w_stride, int64_t M, int64_t K, unsigned int *words);
 int launch_decode_server(int w_type, const ServerParams &sp, cudaStream_t st);

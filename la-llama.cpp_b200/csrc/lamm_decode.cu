@@ -720,6 +720,152 @@ __device__ __forceinline__ float dot_unit_sx(const uint32_t (&w)[NW], uint32_t x
   return acc;
 }
 
+// ---- K-quants beyond the reference's table: Q3_K / Q4_K / Q5_K / Q6_K x Q8_K ----------
+// Behaviour matched: ggml_vec_dot_q{3,4,5,6}_K_q8_K (ggml-quants.c:6127, 7000, 7609, 8305).  Same lane unit
+// as Q2_K -- half a super-block, 128 consecutive elements = activation slots 0..7 (16 int8 each) -- but
+// the weight words are pulled from the ring as they are needed (a unit is up to 112 bytes; holding it all
+// would not fit the 64-register budget).  Q3_K / Q6_K super-blocks (110 / 210 bytes) are only 2-byte
+// aligned in the ring: their words are assembled from aligned pairs with a funnel shift.
+template <int N, bool A2>
+__device__ __forceinline__ void lds_words(uint32_t (&out)[N], uint32_t addr) {
+  if constexpr (!A2) {
+    if constexpr (N % 4 == 0) {
+#pragma unroll
+      for (int i = 0; i < N / 4; i++)
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(out[4 * i]), "=r"(out[4 * i + 1]), "=r"(out[4 * i + 2]), "=r"(out[4 * i + 3])
+                     : "r"(addr + 16u * i));
+    } else {
+#pragma unroll
+      for (int i = 0; i < N; i++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(out[i]) : "r"(addr + 4u * i));
+    }
+  } else {
+    const uint32_t base = addr & ~3u, sh = (addr & 2u) * 8u;
+    uint32_t w[N + 1];
+#pragma unroll
+    for (int i = 0; i <= N; i++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[i]) : "r"(base + 4u * i));
+#pragma unroll
+    for (int i = 0; i < N; i++) out[i] = __funnelshift_r(w[i], w[i + 1], sh);
+  }
+}
+__device__ __forceinline__ int dot16(const uint32_t *q, const uint32_t (&x)[4], int acc) {
+  acc = dp4a_u8s8(q[0], x[0], acc);
+  acc = dp4a_u8s8(q[1], x[1], acc);
+  acc = dp4a_u8s8(q[2], x[2], acc);
+  return dp4a_u8s8(q[3], x[3], acc);
+}
+__device__ __forceinline__ int s16_lo(uint32_t v) { return (int)(short)(v & 0xffffu); }
+__device__ __forceinline__ int s16_hi(uint32_t v) { return (int)v >> 16; }
+
+// blk: shared address of the lane's super-block in the ring slot; h: which half; xaddr / jstride: the lane's
+// activation slots; xd: x.d of the super-block; xbs: the 8 int16 bsums of the half
+template <int WT>
+__device__ __forceinline__ float dot_unit_kx(uint32_t blk, int h, uint32_t xaddr, uint32_t jstride, float xd,
+                                             const uint32_t (&xbs)[4]) {
+  uint32_t x[4];
+  if constexpr (WT == LAMMCU_TYPE_Q4_K || WT == LAMMCU_TYPE_Q5_K) {
+    // {f16 d, dmin; u8 scales[12]; (Q5_K: u8 qh[32];) u8 qs[128]}: 16-byte aligned
+    constexpr uint32_t QS = (WT == LAMMCU_TYPE_Q4_K) ? 16u : 48u;
+    uint32_t hdr[4];
+    lds_words<4, false>(hdr, blk);
+    // get_scale_min_k4 (ggml-quants.c:2027-2034) for groups 4h .. 4h+3, four at a time
+    const uint32_t scw = h ? ((hdr[3] & 0x0F0F0F0Fu) | (((hdr[1] >> 6) & 0x03030303u) << 4)) : (hdr[1] & 0x3F3F3F3Fu);
+    const uint32_t mnw = h ? (((hdr[3] >> 4) & 0x0F0F0F0Fu) | (((hdr[2] >> 6) & 0x03030303u) << 4))
+                           : (hdr[2] & 0x3F3F3F3Fu);
+    int isum = 0;
+#pragma unroll
+    for (int pr = 0; pr < 2; pr++) {               // 32 bytes: low nibbles = group 4h+2pr, high = 4h+2pr+1
+      uint32_t q[8], lo[8], hi[8];
+      lds_words<8, false>(q, blk + QS + 64u * h + 32u * pr);
+#pragma unroll
+      for (int i = 0; i < 8; i++) { lo[i] = q[i] & 0x0F0F0F0Fu; hi[i] = (q[i] >> 4) & 0x0F0F0F0Fu; }
+      if constexpr (WT == LAMMCU_TYPE_Q5_K) {
+        uint32_t qh[8];
+        lds_words<8, false>(qh, blk + 16u);        // bit g of qh[l]: 5th bit of element 32g + l
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          const uint32_t b = qh[i] >> (4 * h + 2 * pr);
+          lo[i] |= (b & 0x01010101u) << 4;
+          hi[i] |= ((b >> 1) & 0x01010101u) << 4;
+        }
+      }
+      int tl = 0, th = 0;
+      lds128(x, xaddr + (uint32_t)(4 * pr) * jstride);      tl = dot16(lo, x, tl);
+      lds128(x, xaddr + (uint32_t)(4 * pr + 1) * jstride);  tl = dot16(lo + 4, x, tl);
+      lds128(x, xaddr + (uint32_t)(4 * pr + 2) * jstride);  th = dot16(hi, x, th);
+      lds128(x, xaddr + (uint32_t)(4 * pr + 3) * jstride);  th = dot16(hi + 4, x, th);
+      isum += (int)((scw >> (16 * pr)) & 0xFFu) * tl + (int)((scw >> (16 * pr + 8)) & 0xFFu) * th;
+    }
+    // min term: m[g] * (bsums[2g] + bsums[2g+1]) for the half's 4 groups
+    const uint32_t m01 = __byte_perm(mnw, 0u, 0x1100), m23 = __byte_perm(mnw, 0u, 0x3322);
+    int summs = dp2a_lo_s16u8(xbs[0], m01, 0);
+    summs = dp2a_hi_s16u8(xbs[1], m01, summs);
+    summs = dp2a_lo_s16u8(xbs[2], m23, summs);
+    summs = dp2a_hi_s16u8(xbs[3], m23, summs);
+    const float wd = half_bits_to_float(hdr[0] & 0xffffu), wdmin = half_bits_to_float(hdr[0] >> 16);
+    float acc = (xd * wd) * (float)isum;
+    return fmaf(-(xd * wdmin), (float)summs, acc);
+  } else if constexpr (WT == LAMMCU_TYPE_Q6_K) {
+    // {u8 ql[128]; u8 qh[64]; i8 scales[16]; f16 d}: 2-byte aligned.  Plane j (elements 32j.. of the half):
+    // j = 0: ql[l] & 15, 1: ql[32 + l] & 15, 2: ql[l] >> 4, 3: ql[32 + l] >> 4, each | ((qh[l] >> 2j) & 3) << 4
+    uint32_t hq[8], sc2[2], dw[1];
+    lds_words<8, true>(hq, blk + 128u + 32u * h);
+    lds_words<2, true>(sc2, blk + 192u + 8u * h);
+    lds_words<1, true>(dw, blk + 208u);
+    int isum = 0;
+#pragma unroll
+    for (int ab = 0; ab < 2; ab++) {               // ql[0..31] (planes 0, 2) then ql[32..63] (planes 1, 3)
+      uint32_t q[8], lo[8], hi[8];
+      lds_words<8, true>(q, blk + 64u * h + 32u * ab);
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        lo[i] = (q[i] & 0x0F0F0F0Fu) | (((hq[i] >> (2 * ab)) & 0x03030303u) << 4);
+        hi[i] = ((q[i] >> 4) & 0x0F0F0F0Fu) | (((hq[i] >> (2 * ab + 4)) & 0x03030303u) << 4);
+      }
+      // sub-blocks 2j, 2j+1 of the half; sum (q - 32) x = sum q x - 32 bsum
+      const int jl = ab, jh = ab + 2;
+      int t;
+      lds128(x, xaddr + (uint32_t)(2 * jl) * jstride);      t = dot16(lo, x, 0);
+      isum += (int)(signed char)((sc2[jl >> 1] >> (16 * (jl & 1))) & 0xFFu) * (t - 32 * s16_lo(xbs[jl]));
+      lds128(x, xaddr + (uint32_t)(2 * jl + 1) * jstride);  t = dot16(lo + 4, x, 0);
+      isum += (int)(signed char)((sc2[jl >> 1] >> (16 * (jl & 1) + 8)) & 0xFFu) * (t - 32 * s16_hi(xbs[jl]));
+      lds128(x, xaddr + (uint32_t)(2 * jh) * jstride);      t = dot16(hi, x, 0);
+      isum += (int)(signed char)((sc2[jh >> 1] >> (16 * (jh & 1))) & 0xFFu) * (t - 32 * s16_lo(xbs[jh]));
+      lds128(x, xaddr + (uint32_t)(2 * jh + 1) * jstride);  t = dot16(hi + 4, x, 0);
+      isum += (int)(signed char)((sc2[jh >> 1] >> (16 * (jh & 1) + 8)) & 0xFFu) * (t - 32 * s16_hi(xbs[jh]));
+    }
+    return (xd * half_bits_to_float(dw[0] & 0xffffu)) * (float)isum;
+  } else {
+    // Q3_K {u8 hmask[32]; u8 qs[64]; u8 scales[12]; f16 d}: 2-byte aligned.  Plane j of half h:
+    // (qs[32h + l] >> 2j) & 3, minus 4 unless bit 4h + j of hmask[l] is set
+    uint32_t hm[8], q[8], s3[3], dw[1];
+    lds_words<8, true>(hm, blk);
+    lds_words<8, true>(q, blk + 32u + 32u * h);
+    lds_words<3, true>(s3, blk + 96u);
+    lds_words<1, true>(dw, blk + 108u);
+    // the half's eight 6-bit scales as bytes of (slo, shi) (ggml-quants.c:2570-2575)
+    const uint32_t slo = h ? (((s3[0] >> 4) & 0x0F0F0F0Fu) | (((s3[2] >> 4) & 0x03030303u) << 4))
+                           : ((s3[0] & 0x0F0F0F0Fu) | ((s3[2] & 0x03030303u) << 4));
+    const uint32_t shi = h ? (((s3[1] >> 4) & 0x0F0F0F0Fu) | (((s3[2] >> 6) & 0x03030303u) << 4))
+                           : ((s3[1] & 0x0F0F0F0Fu) | (((s3[2] >> 2) & 0x03030303u) << 4));
+    int isum = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      uint32_t v[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+        v[i] = ((q[i] >> (2 * j)) & 0x03030303u) | (((hm[i] >> (4 * h + j)) & 0x01010101u) << 2);
+      const uint32_t sw = (j < 2 ? slo : shi) >> (16 * (j & 1));
+      int t;
+      lds128(x, xaddr + (uint32_t)(2 * j) * jstride);      t = dot16(v, x, 0);
+      isum += ((int)(sw & 0xFFu) - 32) * (t - 4 * s16_lo(xbs[j]));
+      lds128(x, xaddr + (uint32_t)(2 * j + 1) * jstride);  t = dot16(v + 4, x, 0);
+      isum += ((int)((sw >> 8) & 0xFFu) - 32) * (t - 4 * s16_hi(xbs[j]));
+    }
+    return (xd * half_bits_to_float(dw[0] & 0xffffu)) * (float)isum;
+  }
+}
+
 __device__ __forceinline__ void store_c(const DecodeParams &p, int row, float v, unsigned int tag) {
   if (p.n_peer == 0) {
     float *c = p.c;
@@ -760,9 +906,11 @@ __device__ __forceinline__ void srv_stamp(const ServerParams *sp, unsigned int j
 template <int WT, int XM, bool SERVER>
 __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *smem, const int bid, const int nblk,
                                               const ServerParams *sp, const unsigned int job_tag, float *cs) {
-  constexpr bool kQ2K = (WT == LAMMCU_TYPE_Q2_K);
+  constexpr bool kKX = is_kquant_ext(WT);                        // Q3_K..Q6_K: Q2_K's geometry, own dot
+  constexpr bool kQ2K = (WT == LAMMCU_TYPE_Q2_K) || kKX;         // unit = half a super-block
+  constexpr uint32_t SBB = (uint32_t)type_info(WT).size;         // bytes per super-block (84 for Q2_K)
   constexpr int VT = type_info(WT).vec_dot;
-  constexpr int NW = kQ2K ? 11 : DecFmt<WT>::NW;
+  constexpr int NW = kKX ? 4 : (kQ2K ? 11 : DecFmt<WT>::NW);
   constexpr int S = kD16Slots;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint64_t *full = reinterpret_cast<uint64_t *>(smem) + warp * S;
@@ -775,8 +923,8 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
   const int u0 = seg * p.seg_units;
   const int seg_n = max(0, min(p.seg_units, p.units - u0));
   constexpr int unit_bytes = kQ2K ? 42 : 4 * type_info(WT).size;
-  const uint32_t seg_off = kQ2K ? (uint32_t)(u0 >> 1) * 84u : (uint32_t)u0 * unit_bytes;
-  const uint32_t seg_bytes = kQ2K ? (uint32_t)((seg_n + 1) >> 1) * 84u : (uint32_t)seg_n * unit_bytes;
+  const uint32_t seg_off = kQ2K ? (uint32_t)(u0 >> 1) * SBB : (uint32_t)u0 * unit_bytes;
+  const uint32_t seg_bytes = kQ2K ? (uint32_t)((seg_n + 1) >> 1) * SBB : (uint32_t)seg_n * unit_bytes;
   // rows of this warp: interleaved over the grid (a launch), or -- SERVER, where nblk is the number of
   // rows per CTA -- a contiguous chunk per CTA so that its results leave as one coalesced PCIe write
   const int chunk_lo = SERVER ? bid * nblk : 0;
@@ -787,8 +935,7 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
   const uint8_t *wseg = p.w + seg_off;
   const uint32_t ring_addr = smem_u32(ring);
 
-  auto issue = [&](int i, int s, uint64_t pol) {
-    const int r = row0 + i * row_step;
+  auto row_ptr = [&](int r) -> uintptr_t {       // this warp's K-segment of (virtual) row r
     const uint8_t *base = wseg;
     if (p.nbatch > 1) {
       base = p.wb[0];
@@ -797,7 +944,10 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
       if (r >= p.mc[2]) base = p.wb[3];
       base += seg_off;
     }
-    const uintptr_t a = (uintptr_t)(base + (int64_t)r * p.w_stride);
+    return (uintptr_t)(base + (int64_t)r * p.w_stride);
+  };
+  auto issue = [&](int i, int s, uint64_t pol) {
+    const uintptr_t a = row_ptr(row0 + i * row_step);
     const uintptr_t a0 = a & ~(uintptr_t)15;
     const uint32_t bytes = (uint32_t)(((a + seg_bytes + 15) & ~(uintptr_t)15) - a0);
     uint64_t *bar = full + s;
@@ -820,28 +970,6 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
   unsigned int tag = 0u, x_tag = 0u;
   if constexpr (SERVER) {
     x_tag = job_tag;                               // the server kernel has staged X as {value, tag} pairs
-    // CTA 0 is still pulling X over PCIe: instead of 75 000 threads spinning on L2 (against CTA 0's own
-    // stores), one lane sleeps on the LAST pair and the rest are parked at the barrier.  A wake-up hint only:
-    // stage_x_row validates every element's tag.
-    if (sp->sentinel && bid != 0) {
-      if (threadIdx.x == 0) {
-        const unsigned long long *last = p.x_ll + ((size_t)p.kb * type_info(WT).blck - 1);
-        unsigned long long v, t0 = 0;
-        unsigned int spins = 0;
-        while (true) {
-          asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(last) : "memory");
-          if ((unsigned int)(v >> 32) == x_tag) break;
-          __nanosleep(60);
-          if ((++spins & 1023u) == 0) {
-            unsigned long long now;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-            if (t0 == 0) t0 = now;
-            else if (now - t0 > 2000000000ull) break;        // stage_x_row reports the timeout
-          }
-        }
-      }
-      __syncthreads();
-    }
   } else if (p.n_peer > 0) {
     // This launch's tag = its sequence number on the communicator, from an arrival ticket: every CTA of
     // every sharded launch (all have gridDim.x == p.grid_fixed) adds 1 to a rank-local counter BEFORE it
@@ -927,11 +1055,17 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
         uint32_t w[NW];
         mbar_wait(full + s, (uint32_t)ph);
         if (i0 == 0 && s == 0) trace_stamp(p.trace, 5);
-        // SERVER rows step by RG: Q2_K rows (84 B per super-block) then differ in their 16-byte phase
-        const uint32_t a15r = !SERVER ? a15
-            : (uint32_t)((uintptr_t)(wseg + (int64_t)(row0 + (i0 + s) * row_step) * p.w_stride) & 15);
-        load_unit<WT, NW>(w, ring_addr + (uint32_t)s * p.slot_bytes + a15r, lane_c);
-        acc[s] = dot_unit_sx<WT, NW>(w, xaddr, jstride, xd, xsc, xbs);
+        // SERVER rows step by RG: Q2_K rows (84 B per super-block) then differ in their 16-byte phase; so do
+        // Q3_K / Q6_K rows (110 / 210 B per super-block) whenever RG * kb is odd
+        const uint32_t a15r = (!SERVER && !kKX) ? a15 : (uint32_t)(row_ptr(row0 + (i0 + s) * row_step) & 15);
+        if constexpr (kKX) {
+          (void)w;
+          acc[s] = dot_unit_kx<WT>(ring_addr + (uint32_t)s * p.slot_bytes + a15r + (uint32_t)(lane_c >> 1) * SBB,
+                                   lane_c & 1, xaddr, jstride, xd[0], xbs);
+        } else {
+          load_unit<WT, NW>(w, ring_addr + (uint32_t)s * p.slot_bytes + a15r, lane_c);
+          acc[s] = dot_unit_sx<WT, NW>(w, xaddr, jstride, xd, xsc, xbs);
+        }
         __syncwarp();
         if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
         if (i0 == 0) trace_stamp(p.trace, 6 + s);
@@ -997,90 +1131,7 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
   const int bid = blockIdx.x;
   unsigned long long t_launch;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_launch));
-  __shared__ unsigned int ctl;                     // inline-X poll of CTA 0: 0 waiting, 1 job seen, 2 give up
-  const bool inl = sp.x_pairs_host != nullptr && bid == 0;
   for (unsigned int s = sp.seq0;; ++s) {
-    if (inl) {
-      // ---- 1 + 2 fused (host mode 2): the caller wrote X as {value, tag} pairs BEFORE the job, so CTA 0
-      // polls the job words and the first 8 * blockDim pairs of the row in the SAME PCIe round trip;
-      // every thread keeps its 8 pairs in registers and republishes them once all tags match.
-      const unsigned long long *xsrc = sp.x_pairs_host + 8 * (size_t)tid;
-      unsigned long long xv[8], t0 = 0;
-      if (tid == 0) {
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-        ctl = (s != sp.seq0 && t0 - t_launch > (unsigned long long)sp.life_ns) ? 2u : 0u;
-      }
-      __syncthreads();
-      unsigned int st = ctl, x_iters = 0;
-      while (st != 2u) {
-        unsigned long long v = 0;
-        if (warp == 0 && lane < kSrvWords)
-          asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(sp.mbox_host + lane) : "memory");
-#pragma unroll
-        for (int i = 0; i < 4; i++) ld_ll2(xsrc + 2 * i, xv[2 * i], xv[2 * i + 1]);
-        if (warp == 0) {
-          const bool ok = __all_sync(0xffffffffu, lane >= kSrvWords || (unsigned int)(v >> 32) == s);
-          if (ok && lane < kSrvWords) jw[lane] = (unsigned int)v;
-          if (lane == 0) {
-            if (ok) ctl = 1u;
-            else if (ctl == 0u) {
-              unsigned long long now;
-              asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-              if (now - t0 > (unsigned long long)sp.idle_ns) ctl = 2u;
-            }
-          }
-        }
-        __syncthreads();
-        st = ctl;
-        bool mine = false;
-        if (st == 1u) {
-          if (jw[0] != 1u) mine = true;                            // stop request: no row to wait for
-          else {
-            const int K = (int)jw[5] * type_info(WT).blck;
-            bool ok = true;
-#pragma unroll
-            for (int i = 0; i < 8; i++) ok &= ((unsigned int)(xv[i] >> 32) == s);
-            mine = (8 * tid >= K) || ok;
-          }
-          if (++x_iters > 400000u) { if (tid == 0) *sp.status = 3u; mine = true; }   // the row never completed
-        }
-        if (__syncthreads_and(mine ? 1 : 0) || st == 2u) break;
-      }
-      if (warp == 0 && lane < kSrvWords) {
-        unsigned long long v = ((unsigned long long)s << 32) | (st == 2u ? (lane == 0 ? 2u : 0u) : jw[lane]);
-        jw[lane] = (unsigned int)v;
-        asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + lane), "l"(v) : "memory");
-        if (st == 2u && lane == 0) {
-          sp.done_host[1] = s;
-          __threadfence_system();
-        }
-      }
-      __syncthreads();
-      srv_stamp(&sp, s, 0);                        // job (and row) seen
-      if (jw[0] != 1u) return;
-      const int K = (int)jw[5] * type_info(WT).blck;
-      const unsigned long long th = (unsigned long long)s << 32;
-      for (int idx = 8 * tid; idx < K; idx += 8 * (int)blockDim.x) {
-        if (idx >= 8 * (int)blockDim.x) {          // K > 4096: the rest of the row, already in host memory
-          const unsigned long long *src = sp.x_pairs_host + idx;
-          for (unsigned int tries = 0;; tries++) {
-#pragma unroll
-            for (int i = 0; i < 4; i++) ld_ll2(src + 2 * i, xv[2 * i], xv[2 * i + 1]);
-            bool ok = true;
-#pragma unroll
-            for (int i = 0; i < 8; i++) ok &= ((unsigned int)(xv[i] >> 32) == s);
-            if (ok) break;
-            if (tries > 400000u) { *sp.status = 3u; break; }
-          }
-        }
-        unsigned long long *dst = sp.x_ll + idx;
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-          asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst + 2 * i),
-                       "l"(th | (xv[2 * i] & 0xffffffffull)), "l"(th | (xv[2 * i + 1] & 0xffffffffull)) : "memory");
-      }
-      srv_stamp(&sp, s, 1);                        // X forwarded
-    } else {
     // ---- 1. the job
     if (warp == 0) {
       const unsigned long long *src = bid == 0 ? sp.mbox_host : sp.mbox_dev;
@@ -1112,9 +1163,8 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
     __syncthreads();
     if (bid == 0) srv_stamp(&sp, s, 0);            // job seen
     if (jw[0] != 1u) return;                       // 2: stop request or idle time-out
-    }
     // ---- 2. CTA 0: X, pinned host memory -> {value, tag} pairs in HBM (one PCIe round trip)
-    if (bid == 0 && !inl) {
+    if (bid == 0) {
       const int K4 = (int)jw[5] * (type_info(WT).blck / 4);
       const unsigned long long th = (unsigned long long)s << 32;
       for (int base = 0; base < K4; base += 4 * (int)blockDim.x) {
@@ -1255,6 +1305,10 @@ static int launch_decode16_x(int w_type, const DecodeParams &p, int grid, int th
   case LAMMCU_TYPE_Q5_0: return launch_decode16_t<LAMMCU_TYPE_Q5_0, XF32>(p, grid, threads, smem, st);
   case LAMMCU_TYPE_Q5_1: return launch_decode16_t<LAMMCU_TYPE_Q5_1, XF32>(p, grid, threads, smem, st);
   case LAMMCU_TYPE_Q8_0: return launch_decode16_t<LAMMCU_TYPE_Q8_0, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q3_K: return launch_decode16_t<LAMMCU_TYPE_Q3_K, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q4_K: return launch_decode16_t<LAMMCU_TYPE_Q4_K, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q5_K: return launch_decode16_t<LAMMCU_TYPE_Q5_K, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q6_K: return launch_decode16_t<LAMMCU_TYPE_Q6_K, XF32>(p, grid, threads, smem, st);
   default:               return launch_decode16_t<LAMMCU_TYPE_Q2_K, XF32>(p, grid, threads, smem, st);
   }
 }
@@ -1274,8 +1328,12 @@ static int launch_decode_x(int w_type, const DecodeParams &p, int grid, int thre
 // Whether the single-launch decode kernel can take this operand set (else the caller uses
 // the generic GEMV of lamm_gemv.cu, which handles any 2/4-byte alignment and any K).
 bool decode_supported(int w_type, const void *w, int64_t w_stride, const void *x_or_xq, int64_t M, int64_t K) {
-  if (w_type == LAMMCU_TYPE_F32 || is_kquant_ext(w_type) || !lammcu_type_supported(w_type)) return false;
+  if (w_type == LAMMCU_TYPE_F32 || !lammcu_type_supported(w_type)) return false;
   if (M <= 0 || M > 0x3fffffff || K <= 0 || K > (1 << 22)) return false;
+  if (w_type == LAMMCU_TYPE_Q3_K || w_type == LAMMCU_TYPE_Q6_K) {      // 110 / 210-byte super-blocks: 16-bit words
+    if (K % 256) return false;
+    return (((uintptr_t)w | (uintptr_t)w_stride) & 1) == 0 && ((uintptr_t)x_or_xq & 15) == 0;
+  }
   if (w_type == LAMMCU_TYPE_Q2_K) {
     if (K % 256) return false;
     return (((uintptr_t)w | (uintptr_t)w_stride) & 3) == 0 && ((uintptr_t)x_or_xq & 15) == 0;
@@ -1303,7 +1361,7 @@ static int plan_k_split(DecodeParams &p, const TypeInfo &ti, bool q2k, int64_t K
 static int plan_d16_smem(DecodeParams &p, const TypeInfo &ti, bool q2k, int *warps_out) {
   const int warps = (kD16Warps / p.KS) * p.KS;
   p.RG = warps / p.KS;
-  const int seg_bytes = q2k ? (p.seg_units / 2) * 84 : p.seg_units * 4 * ti.size;
+  const int seg_bytes = q2k ? (p.seg_units / 2) * ti.size : p.seg_units * 4 * ti.size;
   p.slot_bytes = ((seg_bytes + 15) & ~15) + 16;
   p.x_bytes = q2k ? (p.units * (128 + 16) + p.kb * 4) : (p.units * 128 + p.kb * 8);
   p.x_bytes = (p.x_bytes + 127) & ~127;
@@ -1321,7 +1379,7 @@ int decode_server_job(int w_type, const void *w, int64_t w_stride, int64_t M, in
     return LAMMCU_ERR_SHAPE;
   }
   const TypeInfo ti = type_info(w_type);
-  const bool q2k = (w_type == LAMMCU_TYPE_Q2_K);
+  const bool q2k = (ti.blck == 256);               // super-block formats: unit = half a super-block
   DecodeParams p = {};
   int rc = plan_k_split(p, ti, q2k, K);
   if (rc) return rc;
@@ -1365,6 +1423,10 @@ int launch_decode_server(int w_type, const ServerParams &sp, cudaStream_t st) {
   case LAMMCU_TYPE_Q5_1: return launch_server_t<LAMMCU_TYPE_Q5_1>(sp, st);
   case LAMMCU_TYPE_Q8_0: return launch_server_t<LAMMCU_TYPE_Q8_0>(sp, st);
   case LAMMCU_TYPE_Q2_K: return launch_server_t<LAMMCU_TYPE_Q2_K>(sp, st);
+  case LAMMCU_TYPE_Q3_K: return launch_server_t<LAMMCU_TYPE_Q3_K>(sp, st);
+  case LAMMCU_TYPE_Q4_K: return launch_server_t<LAMMCU_TYPE_Q4_K>(sp, st);
+  case LAMMCU_TYPE_Q5_K: return launch_server_t<LAMMCU_TYPE_Q5_K>(sp, st);
+  case LAMMCU_TYPE_Q6_K: return launch_server_t<LAMMCU_TYPE_Q6_K>(sp, st);
   default: set_error("decode server: type %d", w_type); return LAMMCU_ERR_TYPE;
   }
 }
@@ -1372,7 +1434,7 @@ int launch_decode_server(int w_type, const ServerParams &sp, cudaStream_t st) {
 int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
                   float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh, const BatchInfo *bt) {
   const TypeInfo ti = type_info(w_type);
-  const bool q2k = (w_type == LAMMCU_TYPE_Q2_K);
+  const bool q2k = (ti.blck == 256);               // super-block formats: unit = half a super-block
   DecodeParams p = {};
   p.w = (const uint8_t *)w;  p.w_stride = w_stride;
   p.x = x;  p.xq = (const uint8_t *)xq;  p.xq_out = (uint8_t *)xq_out;
@@ -1383,7 +1445,8 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
     const char *e = getenv("LAMM_DECODE_VARIANT");          // tuning knob: 8 or 16 (default) warps
     return (e && atoi(e) == 8) ? 8 : 16;
   }();
-  const int variant = (sh || bt) ? 16 : variant_env;        // peer stores and sibling batches live in the 16-warp kernel
+  // peer stores, sibling batches and the K-quants beyond Q2_K live in the 16-warp kernel
+  const int variant = (sh || bt || is_kquant_ext(w_type)) ? 16 : variant_env;
   if (bt) {
     p.nbatch = bt->count;
     int64_t first[4] = {0, 0, 0, 0};
@@ -1412,7 +1475,7 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
     if (kDecWarps % p.KS) warps = (kDecMaxWarps / p.KS) * p.KS;
   }
   p.RG = warps / p.KS;
-  const int seg_bytes = q2k ? (p.seg_units / 2) * 84 : p.seg_units * 4 * ti.size;
+  const int seg_bytes = q2k ? (p.seg_units / 2) * ti.size : p.seg_units * 4 * ti.size;
   p.slot_bytes = ((seg_bytes + 15) & ~15) + 16;
   p.x_bytes = q2k ? (p.units * (128 + 16) + p.kb * 4) : (p.units * 128 + p.kb * 8);
   p.x_bytes = (p.x_bytes + 127) & ~127;

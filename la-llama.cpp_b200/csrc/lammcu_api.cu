@@ -122,7 +122,6 @@ struct ServerState {
   unsigned int seq = 0;      // tag of the last job posted
   volatile unsigned long long *mbox = nullptr;    // pinned: the job
   float *x_host = nullptr;                         // pinned: activation row
-  unsigned long long *x_pairs = nullptr;           // pinned: activation row as {value, tag} pairs (host mode 2)
   volatile unsigned long long *c_ll = nullptr;     // pinned: result pairs
   volatile unsigned int *done = nullptr;           // pinned: [1] gave-up tag
   unsigned long long *mbox_dev = nullptr, *x_ll = nullptr;
@@ -769,13 +768,11 @@ static int copy_c_back(lammcu_weight_t w, int64_t N, float *c_host, int64_t ldc)
 // No CUDA API call on the steady-state path.  The server gives up after an idle period and is
 // relaunched on demand; anything else that needs the stream stops it first (server_stop).
 //   mode 0: copy-engine H2D, one kernel launch per call, cudaStreamSynchronize
-//   mode 1: resident server (default); CTA 0 sees the job, then pulls X from the pinned row (two PCIe round trips)
-//   mode 2: resident server, "inline X": the caller writes X as {value, tag} pairs before the job and CTA 0
-//           polls job and row together (one round trip)
+//   mode 1: resident server (default)
 static int g_host_mode = [] {
   const char *e = getenv("LAMM_HOST_MODE");
   const int m = e ? atoi(e) : 1;
-  return (m < 0 || m > 2) ? 1 : m;
+  return (m < 0 || m > 1) ? 1 : m;
 }();
 static unsigned int g_srv_idle_us = [] {
   const char *e = getenv("LAMM_SERVER_IDLE_US");
@@ -788,8 +785,6 @@ static int server_setup() {
   void *p = nullptr;
   CU_TRY(cudaMallocHost(&p, 256));                   g_srv.mbox = (volatile unsigned long long *)p;
   CU_TRY(cudaMallocHost(&p, kSrvMaxK * 4));          g_srv.x_host = (float *)p;
-  CU_TRY(cudaMallocHost(&p, kSrvMaxK * 8));          g_srv.x_pairs = (unsigned long long *)p;
-  memset(g_srv.x_pairs, 0, kSrvMaxK * 8);
   CU_TRY(cudaMallocHost(&p, kSrvMaxM * 8));          g_srv.c_ll = (volatile unsigned long long *)p;
   CU_TRY(cudaMallocHost(&p, 256));                   g_srv.done = (volatile unsigned int *)p;
   CU_TRY(cudaMalloc(&p, 256));                       g_srv.mbox_dev = (unsigned long long *)p;
@@ -832,9 +827,6 @@ static int server_launch(int type) {
   sp.idle_ns = g_srv_idle_us * 1000u;
   sp.life_ns = g_srv_life_us * 1000u;
   sp.trace = g_srv.trace;
-  sp.x_pairs_host = (g_host_mode == 2) ? g_srv.x_pairs : nullptr;
-  const char *sen = getenv("LAMM_SERVER_SENTINEL");          // tuning knob, read at every (rare) launch
-  sp.sentinel = sen ? atoi(sen) : 0;
   int rc = launch_decode_server(type, sp, g_dev.stream);
   if (rc) return rc;
   g_srv.running = true;
@@ -878,43 +870,6 @@ static size_t ll_take(const volatile unsigned long long *ll, size_t n, unsigned 
   return ll_take_scalar(ll, n, tag, out);
 }
 
-// the activation row as {value, tag} pairs for the NEXT job tag (host mode 2)
-static void x_pairs_scalar(const float *x, size_t n, unsigned int tag, unsigned long long *out) {
-  for (size_t i = 0; i < n; i++) {
-    uint32_t bits;
-    memcpy(&bits, x + i, 4);
-    out[i] = ((unsigned long long)tag << 32) | bits;
-  }
-}
-#if defined(__x86_64__)
-__attribute__((target("avx2"))) static void x_pairs_avx2(const float *x, size_t n, unsigned int tag, unsigned long long *out) {
-  const __m256i t = _mm256_set1_epi32((int)tag);
-  size_t i = 0;
-  for (; i + 8 <= n; i += 8) {
-    const __m256i v = _mm256_loadu_si256((const __m256i *)(const void *)(x + i));
-    const __m256i lo = _mm256_unpacklo_epi32(v, t), hi = _mm256_unpackhi_epi32(v, t);   // per 128-bit lane
-    _mm256_storeu_si256((__m256i *)(void *)(out + i), _mm256_permute2x128_si256(lo, hi, 0x20));
-    _mm256_storeu_si256((__m256i *)(void *)(out + i + 4), _mm256_permute2x128_si256(lo, hi, 0x31));
-  }
-  x_pairs_scalar(x + i, n - i, tag, out + i);
-}
-#endif
-// post one job; in mode 2 the row goes first, tagged with the job's number
-static void server_post_job(const unsigned int *words, const float *x_host, size_t K) {
-  if (g_host_mode == 2) {
-    const unsigned int tag = g_srv.seq + 1;
-#if defined(__x86_64__)
-    static const bool avx2 = __builtin_cpu_supports("avx2");
-    if (avx2) x_pairs_avx2(x_host, K, tag, g_srv.x_pairs);
-    else
-#endif
-      x_pairs_scalar(x_host, K, tag, g_srv.x_pairs);
-  } else {
-    memcpy(g_srv.x_host, x_host, K * 4);
-  }
-  server_post(words);
-}
-
 // Make the resident instance exit and wait for it (a no-op when none is running).
 static void server_stop() {
   if (!g_srv.ready || !g_srv.running) return;
@@ -933,14 +888,15 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
   if ((rc = decode_server_job(w->type, w->dev, w->stride, rows, K, words))) return rc;
   if (g_srv.running && g_srv.type != w->type) server_stop();
   const double t0 = now_us();
-  server_post_job(words, x_host, (size_t)K);
+  memcpy(g_srv.x_host, x_host, (size_t)K * 4);
   const double t1 = now_us();
+  server_post(words);
   unsigned int s = g_srv.seq;
   // An instance that gave up waiting for tag s has left an EXIT word with that tag in the device
   // mailbox: the job is re-posted under a fresh tag before a new instance is launched.
   if (g_srv.running && g_srv.done[1] == s) {
     g_srv.running = false;
-    server_post_job(words, x_host, (size_t)K);
+    server_post(words);
     s = g_srv.seq;
   }
   if (!g_srv.running && (rc = server_launch(w->type))) return rc;
@@ -956,7 +912,7 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
     __builtin_ia32_pause();
     asm volatile("" ::: "memory");                                      // re-read the pairs
     if (g_srv.done[1] == s) {                                           // the idle exit raced with the post
-      server_post_job(words, x_host, (size_t)K);
+      server_post(words);
       s = g_srv.seq;
       got = 0;
       if ((rc = server_launch(w->type))) return rc;
@@ -980,7 +936,7 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
 }
 
 int lammcu_set_host_mode(int mode) {
-  if (mode < 0 || mode > 2) { set_error("set_host_mode: 0, 1 or 2"); return LAMMCU_ERR_ARG; }
+  if (mode < 0 || mode > 1) { set_error("set_host_mode: 0 or 1"); return LAMMCU_ERR_ARG; }
   std::lock_guard<std::mutex> lk(g_mu);
   server_stop();
   if (g_dev.inited) cudaStreamSynchronize(g_dev.stream);
@@ -1024,7 +980,7 @@ int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N, int64
   const size_t xbytes = (size_t)N * K * 4;
   if ((rc = grow(&g_dev.hx, &g_dev.hx_bytes, xbytes, true))) return rc;
   if ((rc = grow(&g_dev.xin, &g_dev.xin_bytes, xbytes, false))) return rc;
-  if (N == 1 && g_host_mode >= 1 && !xq_out_host && g_decode_kernel && (size_t)K <= kSrvMaxK &&
+  if (N == 1 && g_host_mode == 1 && !xq_out_host && g_decode_kernel && (size_t)K <= kSrvMaxK &&
       (size_t)rows <= kSrvMaxM && decode_supported(w->type, w->dev, w->stride, nullptr, rows, K))
     return mul_mat_host_server(w, x_host, c_host);
   server_stop();                                   // the launches below queue behind a resident instance

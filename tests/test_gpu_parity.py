@@ -6,10 +6,11 @@ import os
 import numpy as np
 import pytest
 from conftest import GOLDEN, golden, make_x, tol_c
-from oracle_lib import F32, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES, row_size
+from oracle_lib import F32, KQ_TYPES, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES, row_size
 
 pytestmark = pytest.mark.gpu
 QTYPES = [t for t in W_TYPES if t != F32]
+DTYPES = QTYPES + KQ_TYPES          # everything the single-launch decode kernel takes (SURVEY 8f-1 K-quants included)
 
 
 def dev(a):
@@ -187,9 +188,8 @@ def test_lamm_mul_mat_operator(gpu, oracle, t):
     assert can and np.array_equal(again, got)
 
 
-@pytest.mark.parametrize("srv_mode,sentinel", [(1, 0), (2, 0), (2, 1), (1, 1)])
-@pytest.mark.parametrize("t", QTYPES)
-def test_operator_decode_host_modes(gpu, oracle, t, srv_mode, sentinel):
+@pytest.mark.parametrize("t", DTYPES)
+def test_operator_decode_host_modes(gpu, oracle, t):
     """N == 1 through the operator in both modes of the host path (one launch + stream synchronize
     per call; jobs posted to the resident decode server): identical bits, fresh X each call (a
     stale staging row or tag would show), shapes of different row counts interleaved, and GPU work
@@ -200,23 +200,20 @@ def test_operator_decode_host_modes(gpu, oracle, t, srv_mode, sentinel):
     ws = [weights(oracle, t, m, k, seed=7 * m + k) for m, k in shapes]
     rng = np.random.default_rng(t)
     default_mode = lib.lammcu_get_host_mode()
-    old_sentinel = os.environ.get("LAMM_SERVER_SENTINEL")
-    os.environ["LAMM_SERVER_SENTINEL"] = str(sentinel)       # read at every server launch
     try:
-        for rep in range(3 if srv_mode == 1 and sentinel == 0 else 1):
+        for rep in range(3):
             for (m, k), w in zip(shapes, ws):
                 x = rng.standard_normal((1, k)).astype(np.float32)
                 want = oracle.mul_mat(t, w, x)
                 got = {}
-                for mode in (0, 1, 2):
+                for mode in (0, 1):
                     assert lib.lammcu_set_host_mode(mode) == 0
                     can, got[mode] = gpu.lamm_mul_mat_host(t, w, x, nth=1)
                     assert can
                 assert np.abs(got[0] - want).max() <= tol_c(want, k), f"{TYPE_NAMES[t]} {m}x{k}"
                 assert np.array_equal(got[1], got[0]), f"{TYPE_NAMES[t]} {m}x{k}"
-                assert np.array_equal(got[2], got[0]), f"{TYPE_NAMES[t]} {m}x{k} (inline X)"
         # a run of server jobs back to back (no mode switch in between), torch work interleaved
-        assert lib.lammcu_set_host_mode(srv_mode) == 0
+        assert lib.lammcu_set_host_mode(1) == 0
         z = torch.ones(1024, device="cuda")
         for rep in range(40):
             (m, k), w = shapes[rep % len(shapes)], ws[rep % len(shapes)]
@@ -242,11 +239,7 @@ def test_operator_decode_host_modes(gpu, oracle, t, srv_mode, sentinel):
     finally:
         lib.lammcu_set_server_timeouts(200, 5000)
         lib.lammcu_set_host_mode(default_mode)
-        if old_sentinel is None:
-            os.environ.pop("LAMM_SERVER_SENTINEL", None)
-        else:
-            os.environ["LAMM_SERVER_SENTINEL"] = old_sentinel
-    assert lib.lammcu_set_host_mode(3) != 0
+    assert lib.lammcu_set_host_mode(2) != 0
 
 
 # ---------------------------------------------------------------- single-launch decode kernel (N == 1)
@@ -254,7 +247,7 @@ DECODE_SHAPES = [(33, 4096), (1, 256), (7, 512), (300, 11008), (64, 5120), (50, 
                  (1185, 4096), (2500, 1024), (129, 13824)]
 
 
-@pytest.mark.parametrize("t", QTYPES)
+@pytest.mark.parametrize("t", DTYPES)
 @pytest.mark.parametrize("m,k", DECODE_SHAPES)
 def test_decode_kernel_fused_quantize(gpu, oracle, t, m, k):
     """N == 1 through lammcu_mul_mat_dev: ONE launch (fused bit-exact activation quantize), Xq written
@@ -306,7 +299,7 @@ def test_decode_kernel_chain_pdl(gpu, oracle):
         assert np.abs(b.cpu().numpy() - y2).max() <= 2 * tol_c(y2, k)
 
 
-@pytest.mark.parametrize("t", QTYPES)
+@pytest.mark.parametrize("t", DTYPES)
 @pytest.mark.parametrize("k,ms", [(4096, (4096, 1024, 516)), (11008, (256, 1000)), (512, (33, 7, 64, 129))])
 def test_decode_batch_siblings(gpu, oracle, t, k, ms):
     """lammcu_mul_mat_batch_dev: sibling matmuls (q/k/v, gate/up) that share one activation row in ONE

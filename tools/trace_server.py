@@ -1,6 +1,6 @@
 """Device time line of resident-server jobs (diagnostics, run on the GPU box):
 
-    LAMM_SERVER_TRACE=1 python tools/trace_server.py [--mode 1|2] [--sentinel 0|1] [--m 4096 --k 4096]
+    LAMM_SERVER_TRACE=1 python tools/trace_server.py [--m 4096 --k 4096]
 
 Posts 64 N == 1 jobs through lamm_mul_mat on host tensors and prints, from the %globaltimer stamps the
 server kernel leaves per job (lammcu_server_trace): job seen -> X republished -> X quantized -> CTA 0's
@@ -19,20 +19,17 @@ import numpy as np  # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--mode", type=int, default=1)
-    ap.add_argument("--sentinel", type=int, default=0)
     ap.add_argument("--m", type=int, default=4096)
     ap.add_argument("--k", type=int, default=4096)
     ap.add_argument("--fmt", default="q4_1")
     a = ap.parse_args()
-    os.environ["LAMM_SERVER_SENTINEL"] = str(a.sentinel)
     import torch
     import lamm_b200 as L
     import bench
     torch.cuda.set_device(0)
     L.init(0)
     lib = L.lib()
-    assert lib.lammcu_set_host_mode(a.mode) == 0
+    assert lib.lammcu_set_host_mode(1) == 0
     t = bench.TYPE_IDS[a.fmt]
     gen = torch.Generator(device="cuda")
     gen.manual_seed(1)
@@ -53,7 +50,7 @@ def main():
     tr = tr[np.argsort(tr[:, 0])]                      # rows are indexed by job & 63: make them chronological
     d = tr[-48:, 1:5] - tr[-48:, 0:1]
     names = ("X republished", "X quantized", "CTA0 rows done", "CTA0 chunk written")
-    print(f"mode {a.mode} sentinel {a.sentinel} {a.fmt} {a.m}x{a.k}: host wall/call median {np.median(wall[16:]):.2f} us "
+    print(f"{a.fmt} {a.m}x{a.k}: host wall/call median {np.median(wall[16:]):.2f} us "
           f"(python ctypes included)")
     for i, n in enumerate(names):
         print(f"  job seen -> {n:20s} median {np.median(d[:, i]) / 1e3:6.2f} us   p90 {np.percentile(d[:, i], 90) / 1e3:6.2f} us")
