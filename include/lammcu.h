@@ -227,6 +227,12 @@ int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K,
                            int64_t row_end, lammcu_weight_t *out);
 int lammcu_weight_lookup(const void *w_host, lammcu_weight_t *out); /* LAMMCU_ERR_ARG if absent */
 int lammcu_weight_release(lammcu_weight_t w);
+/* The registry is keyed by the HOST address of src0->data (weights are immutable model state).  When the
+ * application frees a model it must say so, or a later tensor allocated at the same address with the same
+ * type and shape would hit the stale device copy: forget one tensor, or everything (e.g. from
+ * llama_free_model).  Handles to forgotten entries become invalid.                                      */
+int lammcu_weight_forget(const void *w_host);
+int lammcu_weight_forget_all(void);
 const void *lammcu_weight_dev_ptr(lammcu_weight_t w);
 int64_t lammcu_weight_rows(lammcu_weight_t w);
 

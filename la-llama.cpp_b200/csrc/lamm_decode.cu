@@ -1053,8 +1053,9 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
     for (int s = 0; s < S; s++) {
       if (s < nb) {
         uint32_t w[NW];
+        if (i0 == 0 && s == 0) trace_stamp(p.trace, 5);          // lane setup done, about to wait for the weights
         mbar_wait(full + s, (uint32_t)ph);
-        if (i0 == 0 && s == 0) trace_stamp(p.trace, 5);
+        if (i0 == 0 && s == 0) trace_stamp(p.trace, 6);          // first weights landed
         // SERVER rows step by RG: Q2_K rows (84 B per super-block) then differ in their 16-byte phase; so do
         // Q3_K / Q6_K rows (110 / 210 B per super-block) whenever RG * kb is odd
         const uint32_t a15r = (!SERVER && !kKX) ? a15 : (uint32_t)(row_ptr(row0 + (i0 + s) * row_step) & 15);
@@ -1068,7 +1069,7 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
         }
         __syncwarp();
         if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
-        if (i0 == 0) trace_stamp(p.trace, 6 + s);
+        if (i0 == 0 && s == 0) trace_stamp(p.trace, 7);          // first row's dot done
       }
     }
     const float tot = warp_sum2(acc[0], acc[1], lane);

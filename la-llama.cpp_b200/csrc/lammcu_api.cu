@@ -722,6 +722,32 @@ int lammcu_weight_release(lammcu_weight_t w) {
   return LAMMCU_OK;
 }
 
+// Drop registry entries whatever their reference count: the host tensor is about to be freed (model
+// unload), so a later tensor at the same address must not hit the stale device copy.
+int lammcu_weight_forget(const void *w_host) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto it = g_weights.find(w_host);
+  if (it == g_weights.end()) return LAMMCU_OK;
+  server_stop();
+  if (g_dev.inited) cudaStreamSynchronize(g_dev.stream);
+  cudaFree(it->second->dev);
+  delete it->second;
+  g_weights.erase(it);
+  return LAMMCU_OK;
+}
+int lammcu_weight_forget_all(void) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (g_weights.empty()) return LAMMCU_OK;
+  server_stop();
+  if (g_dev.inited) cudaStreamSynchronize(g_dev.stream);
+  for (auto &kv : g_weights) {
+    cudaFree(kv.second->dev);
+    delete kv.second;
+  }
+  g_weights.clear();
+  return LAMMCU_OK;
+}
+
 const void *lammcu_weight_dev_ptr(lammcu_weight_t w) { return w ? w->dev : nullptr; }
 int64_t lammcu_weight_rows(lammcu_weight_t w) { return w ? w->row_end - w->row_begin : 0; }
 

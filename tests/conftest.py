@@ -51,6 +51,16 @@ def gpu(lamm):
     return lamm
 
 
+@pytest.fixture(autouse=True)
+def _forget_host_weights(request):
+    """The weight registry is keyed by host address; numpy re-uses the addresses of freed test arrays, so
+    every GPU test ends by dropping the registry (what an application does when it frees a model)."""
+    yield
+    if request.node.get_closest_marker("gpu") is not None:
+        import lamm_b200
+        lamm_b200.lib().lammcu_weight_forget_all()
+
+
 def golden(name):
     return np.load(os.path.join(GOLDEN, name))
 

@@ -5,8 +5,8 @@
 Launches `chain` data-dependent mul_mats (each one's output row is the next one's activation row, PDL between
 them, distinct weights) with lammcu_set_trace armed and prints, per launch, medians over the CTAs of the
 stamps decode16_kernel leaves (lamm_decode.cu: trace_stamp): [0] %globaltimer at CTA start; [1..7] clock64 at
-start / after griddepcontrol.wait / activations quantized / CTA done / first weights landed / first row / second
-row.  clock64 deltas are converted with the SM clock."""
+start / after griddepcontrol.wait / activations quantized / CTA done / lane setup done (about to wait for the
+weights) / first weights landed / first row's dot done.  clock64 deltas are converted with the SM clock."""
 import argparse
 import os
 import sys
@@ -60,7 +60,7 @@ def main():
     tr = trace.cpu().numpy().reshape(a.chain, sms, 8).astype(np.float64)
     cyc = 1e3 / a.mhz                                  # ns per cycle
     print(f"{a.fmt} {a.m}x{a.k}, {a.chain} chained launches, {sms} CTAs each; ns, medians over CTAs")
-    print("launch  start-prev_start  wait_returns  x_quantized  first_weights  row0  row1  cta_done")
+    print("launch  start-prev_start  wait_returns  x_quantized  lane_setup  first_weights  row0  cta_done")
     prev = None
     for i in range(a.chain):
         r = tr[i]
