@@ -418,6 +418,20 @@ __device__ __forceinline__ void stage_x_row(const DecodeParams &p, uint8_t *xs, 
   }
 }
 
+// mbar_wait on a precomputed 32-bit shared address (no generic -> shared conversion on the critical path)
+__device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "LAMM_WAITA_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra LAMM_DONEA_%=;\n\t"
+      "bra LAMM_WAITA_%=;\n\t"
+      "LAMM_DONEA_%=:\n\t"
+      "}" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
 __device__ __forceinline__ void pdl_launch_dependents() {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
@@ -967,6 +981,23 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
     for (int s = 0; s < S; s++)
       if (s < n_rows) issue(s, s, pol);
   }
+  // ---- everything a lane needs that does NOT depend on the activations is computed (and pinned in
+  // registers) before the dependency resolves: the serial phase after griddepcontrol.wait is the launch's
+  // critical path, 16 warps in lockstep, and ~80 instructions of index math there cost ~0.5 us
+  const int U = p.units, ug = u0 + lane;
+  const bool lane_live = lane < seg_n;
+  const int lane_c = lane_live ? lane : 0;
+  // dead lanes read unit u0's quants against zero scales (Q2_K: zero d and bsums)
+  uint32_t xaddr = smem_u32(xs) + (uint32_t)(lane_live ? ug : u0) * 16u;
+  uint32_t jstride = (uint32_t)U * 16u;
+  // scales of the lane's unit: float2 [kb] behind the quants (Q8_K: uint4 bsums [U], then float d [kb])
+  uint32_t xs_addr = smem_u32(xs) + 8u * jstride + (kQ2K ? (uint32_t)ug * 16u : (uint32_t)ug * 32u);
+  uint32_t xd_addr = smem_u32(xs) + 9u * jstride + (uint32_t)(ug >> 1) * 4u;          // Q8_K only
+  // every row of this warp has the same (address & 15) -- also across the matrices of a batch (host check)
+  uint32_t a15 = (uint32_t)((uintptr_t)((p.nbatch > 1 ? p.wb[0] + seg_off : wseg) + (int64_t)row0 * p.w_stride) & 15);
+  uint32_t full_u32 = smem_u32(full);
+  asm volatile("" : "+r"(xaddr), "+r"(jstride), "+r"(xs_addr), "+r"(xd_addr), "+r"(a15), "+r"(full_u32));
+
   unsigned int tag = 0u, x_tag = 0u;
   if constexpr (SERVER) {
     x_tag = job_tag;                               // the server kernel has staged X as {value, tag} pairs
@@ -1021,31 +1052,20 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
   if constexpr (SERVER) { if (bid == 0) srv_stamp(sp, job_tag, 2); }   // activations quantized
   if (active) {
 
-  const int U = p.units, ug = u0 + lane;
-  const bool lane_live = lane < seg_n;
-  const int lane_c = lane_live ? lane : 0;
-  const uint4 *xqs = reinterpret_cast<const uint4 *>(xs);
-  // dead lanes read unit u0's quants against zero scales (Q2_K: zero d and bsums)
-  const uint32_t xaddr = smem_u32(xqs + (lane_live ? ug : u0));
-  const uint32_t jstride = (uint32_t)U * 16u;
   float xd[4] = {0.f, 0.f, 0.f, 0.f}, xsc[4] = {0.f, 0.f, 0.f, 0.f};
   uint32_t xbs[4] = {0u, 0u, 0u, 0u};
   if (lane_live) {
     if constexpr (kQ2K) {
-      const uint4 *xb = xqs + (size_t)8 * U;
-      const float *xdp = reinterpret_cast<const float *>(xb + U);
-      const uint4 b = xb[ug];
-      xbs[0] = b.x; xbs[1] = b.y; xbs[2] = b.z; xbs[3] = b.w;
-      xd[0] = xdp[ug >> 1];
+      lds128(xbs, xs_addr);
+      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(xd[0]) : "r"(xd_addr));
     } else {
-      const float4 *xds = reinterpret_cast<const float4 *>(xqs + (size_t)8 * U);   // float2 [kb]
-      const float4 v0 = xds[2 * ug], v1 = xds[2 * ug + 1];
-      xd[0] = v0.x; xsc[0] = v0.y; xd[1] = v0.z; xsc[1] = v0.w;
-      xd[2] = v1.x; xsc[2] = v1.y; xd[3] = v1.z; xsc[3] = v1.w;
+      uint32_t v0[4], v1[4];
+      lds128(v0, xs_addr);
+      lds128(v1, xs_addr + 16u);
+      xd[0] = __uint_as_float(v0[0]); xsc[0] = __uint_as_float(v0[1]); xd[1] = __uint_as_float(v0[2]); xsc[1] = __uint_as_float(v0[3]);
+      xd[2] = __uint_as_float(v1[0]); xsc[2] = __uint_as_float(v1[1]); xd[3] = __uint_as_float(v1[2]); xsc[3] = __uint_as_float(v1[3]);
     }
   }
-  // every row of this warp has the same (address & 15) -- also across the matrices of a batch (host check)
-  const uint32_t a15 = (uint32_t)((uintptr_t)((p.nbatch > 1 ? p.wb[0] + seg_off : wseg) + (int64_t)row0 * p.w_stride) & 15);
   for (int i0 = 0, ph = 0; i0 < n_rows; i0 += S, ph ^= 1) {
     const int nb = min(S, n_rows - i0);
     float acc[S] = {0.f, 0.f};
@@ -1054,7 +1074,7 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
       if (s < nb) {
         uint32_t w[NW];
         if (i0 == 0 && s == 0) trace_stamp(p.trace, 5);          // lane setup done, about to wait for the weights
-        mbar_wait(full + s, (uint32_t)ph);
+        mbar_wait_u32(full_u32 + 8u * s, (uint32_t)ph);
         if (i0 == 0 && s == 0) trace_stamp(p.trace, 6);          // first weights landed
         // SERVER rows step by RG: Q2_K rows (84 B per super-block) then differ in their 16-byte phase; so do
         // Q3_K / Q6_K rows (110 / 210 B per super-block) whenever RG * kb is odd
@@ -1065,10 +1085,23 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
                                    lane_c & 1, xaddr, jstride, xd[0], xbs);
         } else {
           load_unit<WT, NW>(w, ring_addr + (uint32_t)s * p.slot_bytes + a15r, lane_c);
+          // The slot is free as soon as every lane holds its words in registers: refill it BEFORE the dot
+          // product, not after (a slot is then busy for one DRAM round trip instead of round trip + dot).
+          // The vote consumes the LAST word loaded (shared-memory loads of a warp return in order), so all
+          // lanes' reads have completed before lane 0 hands the slot back to the copy engine.
+          {
+            unsigned int seen;
+            asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %1, 0;\n\tvote.sync.any.pred q, p, 0xffffffff;\n\t"
+                         "selp.u32 %0, 1, 0, q;\n\t}" : "=r"(seen) : "r"(w[NW - 1]) : "memory");
+            (void)seen;
+          }
+          if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
           acc[s] = dot_unit_sx<WT, NW>(w, xaddr, jstride, xd, xsc, xbs);
         }
-        __syncwarp();
-        if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
+        if constexpr (kKX) {
+          __syncwarp();
+          if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
+        }
         if (i0 == 0 && s == 0) trace_stamp(p.trace, 7);          // first row's dot done
       }
     }
