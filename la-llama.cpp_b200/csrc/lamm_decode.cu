@@ -21,6 +21,7 @@
 //     after griddepcontrol.wait.
 #include "lamm_quant_dev.cuh"
 
+#include <algorithm>
 #include <cstdlib>
 
 namespace lamm {
@@ -44,6 +45,7 @@ struct DecodeParams {
   int slots, slot_bytes;
   int x_bytes;          // shared-memory bytes of the staged activations
   unsigned long long *trace;   // optional: 8 globaltimer stamps per CTA (lammcu_set_trace)
+  int l2_ahead;                // 16-warp kernel: rows per warp prefetched into L2 beyond the shared-memory ring
   // sibling batch (16-warp kernel): up to 4 weight matrices of one type, K and row stride that share
   // the activation row (q/k/v, gate/up) form one virtual matrix of M total rows.  Global rows
   // [mc[j-1], mc[j]) belong to matrix j; wb[j] / cb[j] are VIRTUAL bases (pointer minus the rows
@@ -418,6 +420,10 @@ __device__ __forceinline__ void stage_x_row(const DecodeParams &p, uint8_t *xs, 
   }
 }
 
+// L2 prefetch of a 16-byte aligned span (SASS: UBLKPF): no shared memory, no barrier -- lookahead beyond the ring
+__device__ __forceinline__ void bulk_prefetch_l2(const void *gmem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem_src), "r"(bytes) : "memory");
+}
 // mbar_wait on a precomputed 32-bit shared address (no generic -> shared conversion on the critical path)
 __device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
   asm volatile(
@@ -967,6 +973,14 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
     uint64_t *bar = full + s;
     mbar_arrive_expect_tx(bar, bytes);
     bulk_g2s_stream(ring + (size_t)s * p.slot_bytes, reinterpret_cast<const void *>(a0), bytes, bar, pol);
+    // Lookahead beyond the ring: the row this warp will want l2_ahead rows after the ones in shared memory goes
+    // to L2 now, so the ring refill that follows later is an L2 hit (half the latency, no DRAM queueing) and
+    // DRAM keeps streaming while a dependent launch sits in its serial prologue with a full ring.
+    if (!SERVER && p.l2_ahead > 0 && i + p.l2_ahead < n_rows) {
+      const uintptr_t b = row_ptr(row0 + (i + p.l2_ahead) * row_step);
+      const uintptr_t b0 = b & ~(uintptr_t)15;
+      bulk_prefetch_l2(reinterpret_cast<const void *>(b0), (uint32_t)(((b + seg_bytes + 15) & ~(uintptr_t)15) - b0));
+    }
   };
 
   trace_stamp(p.trace, 0);
@@ -1528,6 +1542,12 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   if (grid > need) grid = (int)need;
   if (sh) grid = sm_count_cached();                // fixed grid: the arrival-ticket tag divides by it
   p.trace = next_trace_slot(grid);
+  static const int l2_ahead = [] {
+    const char *e = getenv("LAMM_DECODE_L2_AHEAD");          // tuning knob: rows per warp prefetched into L2 (0 = off)
+    const int v = e ? atoi(e) : 0;
+    return v < 0 ? 0 : (v > 16 ? 16 : v);
+  }();
+  p.l2_ahead = l2_ahead;
   if (variant == 16) {
     if (xm == 2) return launch_decode16_x<2>(w_type, p, grid, warps * 32, smem, st);
     return xm ? launch_decode16_x<1>(w_type, p, grid, warps * 32, smem, st)
