@@ -497,7 +497,9 @@ def run_cuda(args):
     # with N>1 every rank runs it on its shard)
     if args.host_mode is not None:
         L.lib().lammcu_set_host_mode(args.host_mode)
-    e2e = e2e_run(torch, L, t, ops, weights, shard, max(3, args.steps // 10), dist, dev, rank, world)
+    e2e = None
+    if not args.no_e2e:
+        e2e = e2e_run(torch, L, t, ops, weights, shard, max(3, args.steps // 10), dist, dev, rank, world)
 
     if rank != 0:
         return finish(dist)
@@ -776,6 +778,8 @@ def main():
     ap.add_argument("--fmt", default="q4_1", choices=sorted(f for f, t in TYPE_IDS.items() if t == 0 or t in _QVAR))
     ap.add_argument("--model", default="7b", choices=sorted(MODELS), help="chain shapes (the metric is quoted on 7b)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true",
+                    help="skip the e2e leg (profiler runs only: ncu replays kernels, the resident server talks to the host)")
     ap.add_argument("--host-mode", type=int, default=None, choices=[0, 1],
                     help="e2e leg: completion mode of the host path (lammcu_set_host_mode; default: the library's)")
     ap.add_argument("--no-batch", dest="batch", action="store_false",

@@ -1250,12 +1250,15 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
     // ---- 3. the rows of this CTA's chunk
     const int R = (int)jw[12];                     // rows per CTA (multiple of 4)
     float *cs = reinterpret_cast<float *>(smem + jw[13]);
-    decode16_body<WT, 2, true>(jp, smem, bid, R, &sp, s, cs);
+    // jw[14] != 0: CTA 0 only accepts jobs and forwards X (it is the last to start on its rows, so its chunk
+    // is the call's critical path); the row chunks are dealt to CTAs 1 .. grid-1 (virtual id vb)
+    const int vb = jw[14] ? (bid == 0 ? (int)gridDim.x - 1 : bid - 1) : bid;
+    if (!(jw[14] && bid == 0)) decode16_body<WT, 2, true>(jp, smem, vb, R, &sp, s, cs);
     __syncthreads();
-    if (bid == 0) srv_stamp(&sp, s, 3);            // CTA 0's rows done
+    if (vb == 0) srv_stamp(&sp, s, 3);             // first chunk's rows done
     // ---- 4. results: the chunk as {value, tag} pairs, coalesced, straight to pinned memory
     {
-      const int lo = bid * R, n = max(0, min(jp.M, lo + R) - lo);
+      const int lo = vb * R, n = (jw[14] && bid == 0) ? 0 : max(0, min(jp.M, lo + R) - lo);
       const unsigned long long th = (unsigned long long)s << 32;
       unsigned long long *dst = sp.c_ll_host + lo;
       for (int i = 2 * tid; i < n; i += 2 * (int)blockDim.x) {
@@ -1268,7 +1271,7 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
         }
       }
     }
-    if (bid == 0) srv_stamp(&sp, s, 4);            // CTA 0's chunk written
+    if (vb == 0) srv_stamp(&sp, s, 4);             // first chunk written
     __syncthreads();
   }
 }
@@ -1434,7 +1437,10 @@ int decode_server_job(int w_type, const void *w, int64_t w_stride, int64_t M, in
   if (p.KS > kD16Warps) { set_error("decode server: K too large"); return LAMMCU_ERR_SHAPE; }
   int warps = 0;
   const int body_smem = (plan_d16_smem(p, ti, q2k, &warps) + 127) & ~127;
-  const int64_t R = ((M + sm_count_cached() - 1) / sm_count_cached() + 3) & ~(int64_t)3;   // rows per CTA
+  // CTA 0 accepts jobs and forwards X but computes no rows (default; LAMM_SERVER_IO_CTA=0 gives it a chunk too)
+  static const int io_cta = [] { const char *e = getenv("LAMM_SERVER_IO_CTA"); return e ? atoi(e) : 1; }();
+  const int workers = sm_count_cached() - (io_cta && sm_count_cached() > 1 ? 1 : 0);
+  const int64_t R = ((M + workers - 1) / workers + 3) & ~(int64_t)3;                         // rows per CTA
   if (K > 65536 || body_smem + R * 4 > kSrvSmem) { set_error("decode server: shape too large for shared memory"); return LAMMCU_ERR_SHAPE; }
   for (int i = 0; i < kSrvWords; i++) words[i] = 0u;
   words[0] = 1u;
@@ -1445,6 +1451,7 @@ int decode_server_job(int w_type, const void *w, int64_t w_stride, int64_t M, in
   words[7] = (unsigned int)p.KS; words[8] = (unsigned int)p.seg_units; words[9] = (unsigned int)p.RG;
   words[10] = (unsigned int)p.slot_bytes;  words[11] = (unsigned int)p.x_bytes;  words[12] = (unsigned int)R;
   words[13] = (unsigned int)body_smem;
+  words[14] = (io_cta && sm_count_cached() > 1) ? 1u : 0u;
   return LAMMCU_OK;
 }
 
