@@ -65,7 +65,9 @@ ACT_SIZE = {0: (1, 4), 8: (32, 34), 9: (32, 36), 15: (256, 292)}
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, averaged over the chain's
 # launches, from the committed `ncu --set full` capture (profiles/); None until measured for a format
-TRAFFIC_PER_LAUNCH = {}
+# q4_1: profiles/r1_launches_bench.csv -- 903 launches of decode16_kernel<q4_1>, 32.075 MB read + 0.002 MB written on
+# average against 32.09 MB algorithmic (ratio 0.9995: every weight byte crosses DRAM once, C and X stay in L2)
+TRAFFIC_PER_LAUNCH = {"q4_1": 32.077e6}
 
 
 def chain_ops():

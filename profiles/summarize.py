@@ -86,7 +86,8 @@ def main():
             k = rep_summary(os.path.join(src, f), os.path.join(here, "%s_ncu_%s.csv" % (tag, f[:-8])))
             print(f, k, "launches")
     for f in ("bench.json", "bench_nobatch.json", "bench_reference.json", "sweep_decode_fused.jsonl", "sweep_gemm_n512.jsonl",
-              "sweep_gemm_13b_n2048.jsonl", "sweep_gemm_30b_q5_0_n512.jsonl", "pytest_gpu.log"):
+              "sweep_gemm_13b_n2048.jsonl", "sweep_gemm_30b_q5_0_n512.jsonl", "pytest_gpu.log", "trace_decode.txt",
+              "trace_server.txt", "hostlat.txt"):
         p = os.path.join(src, f)
         if os.path.exists(p):
             with open(p) as a, open(os.path.join(here, "%s_%s" % (tag, f)), "w") as b:
