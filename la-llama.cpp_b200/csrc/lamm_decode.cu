@@ -927,6 +927,7 @@ template <int WT, int XM, bool SERVER>
 __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *smem, const int bid, const int nblk,
                                               const ServerParams *sp, const unsigned int job_tag, float *cs) {
   constexpr bool kKX = is_kquant_ext(WT);                        // Q3_K..Q6_K: Q2_K's geometry, own dot
+  constexpr bool kEarlyRefill = !(WT == LAMMCU_TYPE_Q5_0 || WT == LAMMCU_TYPE_Q5_1);
   constexpr bool kQ2K = (WT == LAMMCU_TYPE_Q2_K) || kKX;         // unit = half a super-block
   constexpr uint32_t SBB = (uint32_t)type_info(WT).size;         // bytes per super-block (84 for Q2_K)
   constexpr int VT = type_info(WT).vec_dot;
@@ -1103,16 +1104,18 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
           // product, not after (a slot is then busy for one DRAM round trip instead of round trip + dot).
           // The vote consumes the LAST word loaded (shared-memory loads of a warp return in order), so all
           // lanes' reads have completed before lane 0 hands the slot back to the copy engine.
-          {
+          // Not for Q5_0 / Q5_1: their 22/24 live weight words + the refill's address math spill at 64
+          // registers and the kernel gets 10 % slower (measured), so they refill after the dot.
+          if constexpr (kEarlyRefill) {
             unsigned int seen;
             asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %1, 0;\n\tvote.sync.any.pred q, p, 0xffffffff;\n\t"
                          "selp.u32 %0, 1, 0, q;\n\t}" : "=r"(seen) : "r"(w[NW - 1]) : "memory");
             (void)seen;
+            if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
           }
-          if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
           acc[s] = dot_unit_sx<WT, NW>(w, xaddr, jstride, xd, xsc, xbs);
         }
-        if constexpr (kKX) {
+        if constexpr (kKX || !kEarlyRefill) {
           __syncwarp();
           if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
         }

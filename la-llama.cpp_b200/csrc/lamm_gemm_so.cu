@@ -65,11 +65,16 @@ static void fill_peers(SoParams &p) {
 }
 
 // one accumulator element to its destination(s)
+// PEERS is a template parameter of the kernels: the single-GPU epilogue must stay the plain coalesced store
+// (a run-time branch + dynamically indexed pointer array in the 16-wide store loop cost 25 % of the GEMM)
+template <bool PEERS>
 __device__ __forceinline__ void store_out(const SoParams &p, int64_t idx, float v) {
-  if (p.n_peer == 0) {
+  if constexpr (!PEERS) {
     p.c[idx] = v;
   } else {
-    for (int g = 0; g < p.n_peer; g++) p.cp[g][idx] = v;
+#pragma unroll
+    for (int g = 0; g < LAMMCU_MAX_RANKS; g++)
+      if (g < p.n_peer) p.cp[g][idx] = v;
   }
 }
 
@@ -145,7 +150,7 @@ __device__ __forceinline__ uint4 chunk_mins(const uint32_t (&raw)[NWR]) {
                     *reinterpret_cast<const uint32_t *>(&c), *reinterpret_cast<const uint32_t *>(&d));
 }
 
-template <int WT>
+template <int WT, bool PEERS>
 __global__ void __launch_bounds__(kSoThreads, 1)
 gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_xh,
                const __grid_constant__ CUtensorMap tm_xl, const __grid_constant__ CUtensorMap tm_sh, const SoParams p) {
@@ -349,7 +354,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
 #pragma unroll
         for (int i = 0; i < 16; i++) {
           const int n = n0 + c16 * 16 + i;
-          if (n < p.N) store_out(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * __ldg(p.colscale + n));
+          if (n < p.N) store_out<PEERS>(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * __ldg(p.colscale + n));
         }
       }
     }
@@ -366,6 +371,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
 // GEMM: no unpack warps, no extra stages.  Same three MMAs per K step, same epilogue.
 constexpr int kDirStages = 3;
 
+template <bool PEERS>
 __global__ void __launch_bounds__(192, 1)
 gemm_direct_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant__ CUtensorMap tm_al,
                    const __grid_constant__ CUtensorMap tm_xh, const __grid_constant__ CUtensorMap tm_xl, const SoParams p) {
@@ -450,7 +456,7 @@ gemm_direct_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_const
 #pragma unroll
         for (int i = 0; i < 16; i++) {
           const int n = n0 + c16 * 16 + i;
-          if (n < p.N) store_out(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * __ldg(p.colscale + n));
+          if (n < p.N) store_out<PEERS>(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * __ldg(p.colscale + n));
         }
       }
     }
@@ -493,7 +499,9 @@ int launch_gemm_direct(int w_type, const void *w, int64_t w_stride, const void *
   constexpr int smem = kDirStages * 4 * kTileBytes + 256 + 1024;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = cudaFuncSetAttribute(gemm_direct_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_direct_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) {
       set_error("gemm_direct: cudaFuncSetAttribute(%d): %s", smem, cudaGetErrorString(e));
       return LAMMCU_ERR_CUDA;
@@ -501,7 +509,8 @@ int launch_gemm_direct(int w_type, const void *w, int64_t w_stride, const void *
     attr_set = true;
   }
   const int tiles = (int)((mpad / GM) * (npad / GN));
-  gemm_direct_kernel<<<tiles, 192, smem, st>>>(tm_ah, tm_al, tm_xh, tm_xl, p);
+  if (p.n_peer) gemm_direct_kernel<true><<<tiles, 192, smem, st>>>(tm_ah, tm_al, tm_xh, tm_xl, p);
+  else gemm_direct_kernel<false><<<tiles, 192, smem, st>>>(tm_ah, tm_al, tm_xh, tm_xl, p);
   g_launch_count++;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
@@ -520,7 +529,9 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
   static_assert(smem <= 227 * 1024, "shared memory budget");
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_so_kernel<WT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = cudaFuncSetAttribute(gemm_so_kernel<WT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_so_kernel<WT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) {
       set_error("gemm_so: cudaFuncSetAttribute(%d): %s", smem, cudaGetErrorString(e));
       return LAMMCU_ERR_CUDA;
@@ -528,7 +539,8 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
     attr_set = true;
   }
   const int tiles = ((p.M + GM - 1) / GM) * ((p.N + GN - 1) / GN);
-  gemm_so_kernel<WT><<<tiles, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);
+  if (p.n_peer) gemm_so_kernel<WT, true><<<tiles, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);
+  else gemm_so_kernel<WT, false><<<tiles, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);
   g_launch_count++;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
