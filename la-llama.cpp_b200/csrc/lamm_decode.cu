@@ -1061,7 +1061,14 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
     pdl_wait();
   }
   trace_stamp(p.trace, 2);
-  stage_x_row<VT, XM>(p, xs, x_tag);
+  if constexpr (SERVER) {
+    // p.x_back != 0 (job word 15): the host found this call's activation row identical to the previous job's
+    // (q/k/v and gate/up share src1), and this instance quantized that row into xs then: nothing crossed
+    // PCIe for it and nothing is staged again (the ring and the result row never overlap xs)
+    if (p.x_back == 0) stage_x_row<VT, XM>(p, xs, x_tag);
+  } else {
+    stage_x_row<VT, XM>(p, xs, x_tag);
+  }
   __syncthreads();
   trace_stamp(p.trace, 3);
   if constexpr (SERVER) { if (bid == 0) srv_stamp(sp, job_tag, 2); }   // activations quantized
@@ -1215,7 +1222,7 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
     if (bid == 0) srv_stamp(&sp, s, 0);            // job seen
     if (jw[0] != 1u) return;                       // 2: stop request or idle time-out
     // ---- 2. CTA 0: X, pinned host memory -> {value, tag} pairs in HBM (one PCIe round trip)
-    if (bid == 0) {
+    if (bid == 0 && jw[15] == 0u) {                 // jw[15] != 0: same row as the previous job, still staged
       const int K4 = (int)jw[5] * (type_info(WT).blck / 4);
       const unsigned long long th = (unsigned long long)s << 32;
       for (int base = 0; base < K4; base += 4 * (int)blockDim.x) {
@@ -1238,8 +1245,8 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
           }
         }
       }
-      srv_stamp(&sp, s, 1);                        // X forwarded
     }
+    if (bid == 0) srv_stamp(&sp, s, 1);            // X forwarded (or known unchanged)
     if (tid == 0) {
       DecodeParams q = {};
       q.w = reinterpret_cast<const uint8_t *>(((unsigned long long)jw[2] << 32) | jw[1]);
@@ -1247,6 +1254,7 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
       q.M = (int)jw[4];  q.kb = (int)jw[5];  q.units = (int)jw[6];  q.KS = (int)jw[7];  q.seg_units = (int)jw[8];
       q.RG = (int)jw[9];  q.slots = kD16Slots;  q.slot_bytes = (int)jw[10];  q.x_bytes = (int)jw[11];
       q.x_ll = sp.x_ll;  q.status = sp.status;
+      q.x_back = (int)jw[15];                      // server jobs: "activations unchanged" (see decode16_body)
       jp = q;
     }
     __syncthreads();

@@ -112,6 +112,9 @@ static unsigned int g_srv_life_us = [] {
   return (unsigned int)(v < 10 ? 10 : v > 4000000 ? 4000000 : v);
 }();
 
+// 1 (default): a call whose activation row equals the previous call's does not send it again
+static const int g_srv_x_reuse = [] { const char *e = getenv("LAMM_SERVER_X_REUSE"); return e ? atoi(e) : 1; }();
+
 constexpr size_t kSrvMaxK = 1 << 16;         // floats in the pinned activation row
 constexpr size_t kSrvMaxM = 1 << 18;         // floats in the result buffers
 
@@ -120,6 +123,7 @@ struct ServerState {
   bool running = false;      // a server launch is (believed to be) resident
   int type = -1;             // weight format of the resident instance
   unsigned int seq = 0;      // tag of the last job posted
+  int64_t x_k = 0;           // K of the row in x_host that the RUNNING instance answered last (0: none)
   volatile unsigned long long *mbox = nullptr;    // pinned: the job
   float *x_host = nullptr;                         // pinned: activation row
   volatile unsigned long long *c_ll = nullptr;     // pinned: result pairs
@@ -857,6 +861,7 @@ static int server_launch(int type) {
   if (rc) return rc;
   g_srv.running = true;
   g_srv.type = type;
+  g_srv.x_k = 0;                                     // a fresh instance has nothing staged
   return LAMMCU_OK;
 }
 
@@ -914,7 +919,14 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
   if ((rc = decode_server_job(w->type, w->dev, w->stride, rows, K, words))) return rc;
   if (g_srv.running && g_srv.type != w->type) server_stop();
   const double t0 = now_us();
-  memcpy(g_srv.x_host, x_host, (size_t)K * 4);
+  // ggml hands q/k/v (and gate/up) the same src1: when this row is bit-identical to the one the running
+  // instance answered last, its quantized copy is still in every CTA's shared memory and the job only
+  // says so (word 15) -- no copy to pinned memory, no PCIe pull, no quantize.  A job that ends up on a
+  // new instance (below) always carries the row.
+  const bool same = g_srv_x_reuse && g_srv.running && g_srv.x_k == K && memcmp(g_srv.x_host, x_host, (size_t)K * 4) == 0;
+  if (!same) memcpy(g_srv.x_host, x_host, (size_t)K * 4);
+  words[15] = same ? 1u : 0u;
+  g_srv.x_k = 0;
   const double t1 = now_us();
   server_post(words);
   unsigned int s = g_srv.seq;
@@ -922,6 +934,7 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
   // mailbox: the job is re-posted under a fresh tag before a new instance is launched.
   if (g_srv.running && g_srv.done[1] == s) {
     g_srv.running = false;
+    words[15] = 0u;
     server_post(words);
     s = g_srv.seq;
   }
@@ -938,6 +951,7 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
     __builtin_ia32_pause();
     asm volatile("" ::: "memory");                                      // re-read the pairs
     if (g_srv.done[1] == s) {                                           // the idle exit raced with the post
+      words[15] = 0u;
       server_post(words);
       s = g_srv.seq;
       got = 0;
@@ -957,7 +971,8 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
     }
   }
   const double t3 = now_us();
-  g_hp[0] += t1 - t0;  g_hp[2] += t2 - t1;  g_hp[3] += t3 - t2;  g_hp[5] += 1;
+  g_srv.x_k = K;                                     // the instance that answered holds this row
+  g_hp[0] += t1 - t0;  g_hp[2] += t2 - t1;  g_hp[3] += t3 - t2;  g_hp[5] += 1;  g_hp[6] += words[15];
   return LAMMCU_OK;
 }
 

@@ -1,5 +1,6 @@
 """Parity of the CUDA path against the oracle and the golden fixtures.  All calls go through
 the C-ABI (ctypes -> liblammcu.so); torch only owns the device buffers."""
+import ctypes as C
 import glob
 import os
 
@@ -240,6 +241,61 @@ def test_operator_decode_host_modes(gpu, oracle, t):
         lib.lammcu_set_server_timeouts(200, 5000)
         lib.lammcu_set_host_mode(default_mode)
     assert lib.lammcu_set_host_mode(2) != 0
+
+
+@pytest.mark.parametrize("t", DTYPES)
+def test_operator_decode_repeated_rows(gpu, oracle, t):
+    """Host mode 1 sends an activation row once when consecutive calls carry bit-identical rows (ggml
+    gives wq/wk/wv and gate/up the same src1): the later jobs reuse the quantized row the resident
+    instance holds.  Results must equal mode 0 bit for bit for: the same row against several weights,
+    a row changed IN PLACE (first element, last element), a row of another K in between, and all of it
+    again with a server that dies after every job (the re-posted job must carry the row)."""
+    lib = gpu.lib()
+    shapes = [(4096, 4096), (33, 4096), (1000, 4096), (515, 11008)]
+    ws = [weights(oracle, t, m, k, seed=11 * m + k) for m, k in shapes]
+    rng = np.random.default_rng(100 + t)
+    xa = rng.standard_normal((1, 4096)).astype(np.float32)
+    xb = rng.standard_normal((1, 11008)).astype(np.float32)
+    # (weight index, row, edit applied in place before the call); rows marked True may be reused
+    plan = [(0, xa, None, False), (1, xa, None, True), (2, xa, None, True), (0, xa, None, True),
+            (1, xa, 0, False), (2, xa, None, True), (0, xa, 4095, False), (3, xb, None, False),
+            (3, xb, None, True), (1, xa, None, False), (2, xa, None, True)]
+    default_mode = lib.lammcu_get_host_mode()
+    prof = (C.c_double * 8)()
+    try:
+        def run(mode):
+            xa0, xb0 = xa.copy(), xb.copy()
+            assert lib.lammcu_set_host_mode(mode) == 0
+            out = []
+            for wi, x, edit, _ in plan:
+                if edit is not None:
+                    x[0, edit] += 1.5
+                can, c = gpu.lamm_mul_mat_host(t, ws[wi], x, nth=1)
+                assert can
+                out.append(c)
+            xa[:], xb[:] = xa0, xb0
+            return out
+        ref = run(0)
+        want = oracle.mul_mat(t, ws[0], xa)
+        assert np.abs(ref[0] - want).max() <= tol_c(want, 4096)
+        assert not np.array_equal(ref[1], ref[4]) and not np.array_equal(ref[3], ref[6])  # the edits matter
+        assert lib.lammcu_set_server_timeouts(100000, 4000000) == 0       # one instance for the whole run
+        lib.lammcu_host_profile(prof, 1)
+        got = run(1)
+        lib.lammcu_host_profile(prof, 1)
+        for i, (g, r) in enumerate(zip(got, ref)):
+            assert np.array_equal(g, r), f"{TYPE_NAMES[t]} call {i}"
+        expected = sum(1 for p_ in plan if p_[3])
+        assert 1 <= prof[6] <= expected, (prof[6], expected)
+        assert lib.lammcu_host_quiesce() == 0
+        assert lib.lammcu_set_server_timeouts(1, 10) == 0                 # nearly every job meets a new instance
+        for rep in range(3):
+            got = run(1)
+            for i, (g, r) in enumerate(zip(got, ref)):
+                assert np.array_equal(g, r), f"{TYPE_NAMES[t]} call {i} (short-lived server, pass {rep})"
+    finally:
+        lib.lammcu_set_server_timeouts(200, 5000)
+        lib.lammcu_set_host_mode(default_mode)
 
 
 # ---------------------------------------------------------------- single-launch decode kernel (N == 1)
