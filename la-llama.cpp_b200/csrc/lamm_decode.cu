@@ -923,7 +923,10 @@ __device__ __forceinline__ void srv_stamp(const ServerParams *sp, unsigned int j
 // SERVER: the body runs as one job of the resident kernel (decode_server_kernel below): bid / nblk
 // are the job's virtual grid, the activations arrive as {value, tag} pairs staged from pinned host
 // memory by CTA 0, the results go to the `cs` staging row, and the ring barriers are invalidated for the next job.
-template <int WT, int XM, bool SERVER>
+// RD: depth of each warp's ring (rows in flight per warp).  2 is the default everywhere; 3 / 4 exist for the
+// single-GPU fused-quantize kernel only (LAMM_DECODE_RING, see launch_decode): with 0.33-0.43 B/weight a
+// K = 4096 row of Q2_K / Q3_K is 1.3-1.8 KB, so two rows per warp keep only ~45-55 KB per SM in flight.
+template <int WT, int XM, bool SERVER, int RD = 2>
 __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *smem, const int bid, const int nblk,
                                               const ServerParams *sp, const unsigned int job_tag, float *cs) {
   constexpr bool kKX = is_kquant_ext(WT);                        // Q3_K..Q6_K: Q2_K's geometry, own dot
@@ -932,12 +935,13 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
   constexpr uint32_t SBB = (uint32_t)type_info(WT).size;         // bytes per super-block (84 for Q2_K)
   constexpr int VT = type_info(WT).vec_dot;
   constexpr int NW = kKX ? 4 : (kQ2K ? 11 : DecFmt<WT>::NW);
-  constexpr int S = kD16Slots;
+  constexpr int S = kD16Slots;                                   // rows per loop iteration (one shuffle tree)
+  static_assert(RD >= 2 && RD <= 4 && kD16Warps * RD * 8 <= 512, "ring barriers live in the first 512 bytes");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint64_t *full = reinterpret_cast<uint64_t *>(smem) + warp * S;
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem) + warp * RD;
   float *part = reinterpret_cast<float *>(smem + 512);          // [RG][2][KS][2]
   uint8_t *xs = smem + kDecCtrl;
-  uint8_t *ring = xs + p.x_bytes + (size_t)warp * S * p.slot_bytes;
+  uint8_t *ring = xs + p.x_bytes + (size_t)warp * RD * p.slot_bytes;
 
   const bool active = warp < p.RG * p.KS;
   const int rg = warp / p.KS, seg = warp - rg * p.KS;
@@ -989,11 +993,11 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
   uint64_t pol = 0;
   if (active && lane == 0) {
 #pragma unroll
-    for (int s = 0; s < S; s++) mbar_init(&full[s], 1);
+    for (int s = 0; s < RD; s++) mbar_init(&full[s], 1);
     fence_barrier_init();
     pol = policy_evict_first();
 #pragma unroll
-    for (int s = 0; s < S; s++)
+    for (int s = 0; s < RD; s++)
       if (s < n_rows) issue(s, s, pol);
   }
   // ---- everything a lane needs that does NOT depend on the activations is computed (and pinned in
@@ -1088,6 +1092,10 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
       xd[2] = __uint_as_float(v1[0]); xsc[2] = __uint_as_float(v1[1]); xd[3] = __uint_as_float(v1[2]); xsc[3] = __uint_as_float(v1[3]);
     }
   }
+  // RD == 2: row i0 + s lives in slot s and every slot flips its phase once per iteration.  Deeper rings walk
+  // the slots round-robin (rsl = slot of the next row, bit k of rph = the phase slot k completes next).
+  uint32_t rsl = 0u, rph = 0u;
+  (void)rsl; (void)rph;
   for (int i0 = 0, ph = 0; i0 < n_rows; i0 += S, ph ^= 1) {
     const int nb = min(S, n_rows - i0);
     float acc[S] = {0.f, 0.f};
@@ -1095,18 +1103,26 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
     for (int s = 0; s < S; s++) {
       if (s < nb) {
         uint32_t w[NW];
+        uint32_t sl = (uint32_t)s;                               // this row's ring slot
         if (i0 == 0 && s == 0) trace_stamp(p.trace, 5);          // lane setup done, about to wait for the weights
-        mbar_wait_u32(full_u32 + 8u * s, (uint32_t)ph);
+        if constexpr (RD == 2) {
+          mbar_wait_u32(full_u32 + 8u * s, (uint32_t)ph);
+        } else {
+          sl = rsl;
+          mbar_wait_u32(full_u32 + 8u * sl, (rph >> sl) & 1u);
+          rph ^= 1u << sl;
+          rsl = (sl + 1u == (uint32_t)RD) ? 0u : sl + 1u;
+        }
         if (i0 == 0 && s == 0) trace_stamp(p.trace, 6);          // first weights landed
         // SERVER rows step by RG: Q2_K rows (84 B per super-block) then differ in their 16-byte phase; so do
         // Q3_K / Q6_K rows (110 / 210 B per super-block) whenever RG * kb is odd
         const uint32_t a15r = (!SERVER && !kKX) ? a15 : (uint32_t)(row_ptr(row0 + (i0 + s) * row_step) & 15);
         if constexpr (kKX) {
           (void)w;
-          acc[s] = dot_unit_kx<WT>(ring_addr + (uint32_t)s * p.slot_bytes + a15r + (uint32_t)(lane_c >> 1) * SBB,
+          acc[s] = dot_unit_kx<WT>(ring_addr + sl * p.slot_bytes + a15r + (uint32_t)(lane_c >> 1) * SBB,
                                    lane_c & 1, xaddr, jstride, xd[0], xbs);
         } else {
-          load_unit<WT, NW>(w, ring_addr + (uint32_t)s * p.slot_bytes + a15r, lane_c);
+          load_unit<WT, NW>(w, ring_addr + sl * p.slot_bytes + a15r, lane_c);
           // The slot is free as soon as every lane holds its words in registers: refill it BEFORE the dot
           // product, not after (a slot is then busy for one DRAM round trip instead of round trip + dot).
           // The vote consumes the LAST word loaded (shared-memory loads of a warp return in order), so all
@@ -1118,13 +1134,13 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
             asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %1, 0;\n\tvote.sync.any.pred q, p, 0xffffffff;\n\t"
                          "selp.u32 %0, 1, 0, q;\n\t}" : "=r"(seen) : "r"(w[NW - 1]) : "memory");
             (void)seen;
-            if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
+            if (lane == 0 && i0 + RD + s < n_rows) issue(i0 + RD + s, (int)sl, pol);
           }
           acc[s] = dot_unit_sx<WT, NW>(w, xaddr, jstride, xd, xsc, xbs);
         }
         if constexpr (kKX || !kEarlyRefill) {
           __syncwarp();
-          if (lane == 0 && i0 + S + s < n_rows) issue(i0 + S + s, s, pol);
+          if (lane == 0 && i0 + RD + s < n_rows) issue(i0 + RD + s, (int)sl, pol);
         }
         if (i0 == 0 && s == 0) trace_stamp(p.trace, 7);          // first row's dot done
       }
@@ -1150,16 +1166,16 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
   if constexpr (SERVER) {                    // every copy has been consumed: free the barriers for the next job
     __syncwarp();
     if (lane == 0)
-      for (int s = 0; s < S; s++) asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(&full[s])) : "memory");
+      for (int s = 0; s < RD; s++) asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(&full[s])) : "memory");
   }
   }   // active
   trace_stamp(p.trace, 4);
 }
 
-template <int WT, int XM>
+template <int WT, int XM, int RD = 2>
 __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const DecodeParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
-  decode16_body<WT, XM, false>(p, smem, (int)blockIdx.x, (int)gridDim.x, nullptr, 0u, nullptr);
+  decode16_body<WT, XM, false, RD>(p, smem, (int)blockIdx.x, (int)gridDim.x, nullptr, 0u, nullptr);
 }
 
 // ---- the resident decode server --------------------------------------------------------------
@@ -1328,11 +1344,11 @@ static int launch_decode_t(const DecodeParams &p, int grid, int threads, int sme
   return launch_decode_tt<WT, XF32, kDecMaxThreads>(p, grid, threads, smem, st);
 }
 
-template <int WT, int XF32>
+template <int WT, int XF32, int RD = 2>
 static int launch_decode16_t(const DecodeParams &p, int grid, int threads, int smem, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(decode16_kernel<WT, XF32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(decode16_kernel<WT, XF32, RD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          kDecSmemMax);
     if (e != cudaSuccess) {
       set_error("decode16: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -1350,7 +1366,7 @@ static int launch_decode16_t(const DecodeParams &p, int grid, int threads, int s
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, decode16_kernel<WT, XF32>, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, decode16_kernel<WT, XF32, RD>, p);
   g_launch_count++;
   if (e != cudaSuccess) {
     set_error("decode16 launch (type %d, smem %d): %s", WT, smem, cudaGetErrorString(e));
@@ -1359,19 +1375,19 @@ static int launch_decode16_t(const DecodeParams &p, int grid, int threads, int s
   return LAMMCU_OK;
 }
 
-template <int XF32>
+template <int XF32, int RD = 2>
 static int launch_decode16_x(int w_type, const DecodeParams &p, int grid, int threads, int smem, cudaStream_t st) {
   switch (w_type) {
-  case LAMMCU_TYPE_Q4_0: return launch_decode16_t<LAMMCU_TYPE_Q4_0, XF32>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q4_1: return launch_decode16_t<LAMMCU_TYPE_Q4_1, XF32>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q5_0: return launch_decode16_t<LAMMCU_TYPE_Q5_0, XF32>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q5_1: return launch_decode16_t<LAMMCU_TYPE_Q5_1, XF32>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q8_0: return launch_decode16_t<LAMMCU_TYPE_Q8_0, XF32>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q3_K: return launch_decode16_t<LAMMCU_TYPE_Q3_K, XF32>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q4_K: return launch_decode16_t<LAMMCU_TYPE_Q4_K, XF32>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q5_K: return launch_decode16_t<LAMMCU_TYPE_Q5_K, XF32>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q6_K: return launch_decode16_t<LAMMCU_TYPE_Q6_K, XF32>(p, grid, threads, smem, st);
-  default:               return launch_decode16_t<LAMMCU_TYPE_Q2_K, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q4_0: return launch_decode16_t<LAMMCU_TYPE_Q4_0, XF32, RD>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q4_1: return launch_decode16_t<LAMMCU_TYPE_Q4_1, XF32, RD>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q5_0: return launch_decode16_t<LAMMCU_TYPE_Q5_0, XF32, RD>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q5_1: return launch_decode16_t<LAMMCU_TYPE_Q5_1, XF32, RD>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q8_0: return launch_decode16_t<LAMMCU_TYPE_Q8_0, XF32, RD>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q3_K: return launch_decode16_t<LAMMCU_TYPE_Q3_K, XF32, RD>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q4_K: return launch_decode16_t<LAMMCU_TYPE_Q4_K, XF32, RD>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q5_K: return launch_decode16_t<LAMMCU_TYPE_Q5_K, XF32, RD>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q6_K: return launch_decode16_t<LAMMCU_TYPE_Q6_K, XF32, RD>(p, grid, threads, smem, st);
+  default:               return launch_decode16_t<LAMMCU_TYPE_Q2_K, XF32, RD>(p, grid, threads, smem, st);
   }
 }
 
@@ -1546,7 +1562,22 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   p.x_bytes = q2k ? (p.units * (128 + 16) + p.kb * 4) : (p.units * 128 + p.kb * 8);
   p.x_bytes = (p.x_bytes + 127) & ~127;
   p.slots = (variant == 16) ? kD16Slots : kDecMaxSlots;
-  const int smem = kDecCtrl + p.x_bytes + warps * p.slots * p.slot_bytes;
+  int smem = kDecCtrl + p.x_bytes + warps * p.slots * p.slot_bytes;
+  // Experimental (off by default, NOT yet measured on hardware): a deeper ring per warp for the plain
+  // single-GPU fused-quantize launch, where it still leaves room for two CTAs per SM (the next launch's
+  // prefetch).  LAMM_DECODE_RING=3|4.
+  static const int ring_env = [] {
+    const char *e = getenv("LAMM_DECODE_RING");
+    const int v = e ? atoi(e) : 2;
+    return (v == 3 || v == 4) ? v : 2;
+  }();
+  int ring = 2;
+  if (variant == 16 && ring_env > 2 && x && !sh) {
+    for (int r = ring_env; r > 2; r--) {
+      const int need = kDecCtrl + p.x_bytes + warps * r * p.slot_bytes;
+      if (2 * (need + 1024) <= 228 * 1024) { ring = r;  smem = need;  p.slots = r;  break; }
+    }
+  }
   if (smem > kDecSmemMax) {
     set_error("decode: K=%lld too large for shared memory", (long long)K);
     return LAMMCU_ERR_SHAPE;
@@ -1568,6 +1599,8 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   p.l2_ahead = l2_ahead;
   if (variant == 16) {
     if (xm == 2) return launch_decode16_x<2>(w_type, p, grid, warps * 32, smem, st);
+    if (ring == 3) return launch_decode16_x<1, 3>(w_type, p, grid, warps * 32, smem, st);
+    if (ring == 4) return launch_decode16_x<1, 4>(w_type, p, grid, warps * 32, smem, st);
     return xm ? launch_decode16_x<1>(w_type, p, grid, warps * 32, smem, st)
               : launch_decode16_x<0>(w_type, p, grid, warps * 32, smem, st);
   }

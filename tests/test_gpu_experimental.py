@@ -1,0 +1,72 @@
+"""Opt-in checks of tuning knobs that are compiled in but OFF by default and not yet measured on
+hardware.  They run only with LAMM_TEST_EXPERIMENTAL=1 so that the default `-m gpu` run exercises
+exactly what ships:
+
+    LAMM_TEST_EXPERIMENTAL=1 python -m pytest tests/test_gpu_experimental.py -m gpu -q
+
+LAMM_DECODE_RING=3|4 (lamm_decode.cu, launch_decode): a deeper per-warp TMA ring in the single-launch
+decode kernel.  The knob is read once per process, so each setting runs in a child process; the child
+must give bit-identical results to ring depth 2 (same per-row arithmetic, only the copy schedule
+differs) and stay within the tier tolerance of the oracle."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(not os.environ.get("LAMM_TEST_EXPERIMENTAL"), reason="opt-in: LAMM_TEST_EXPERIMENTAL=1")]
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+CHILD = r"""
+import sys, os
+sys.path.insert(0, os.path.join(%(root)r, "tests"))
+sys.path.insert(0, %(root)r)
+import numpy as np, torch
+import lamm_b200 as L
+from oracle_lib import Oracle, W_TYPES, KQ_TYPES
+from test_gpu_parity import weights
+L.init(0)
+orc = Oracle()
+out = {}
+for t in list(W_TYPES) + list(KQ_TYPES):
+    if t == 0:
+        continue
+    for (m, k) in [(33, 4096), (1185, 4096), (300, 11008), (2500, 1024), (7, 512), (4096, 4096)]:
+        w = weights(orc, t, m, k, seed=m + 3 * k + t)
+        x = np.random.default_rng(m * k).standard_normal((1, k)).astype(np.float32)
+        c = L.mul_mat(t, torch.from_numpy(w).cuda(), torch.from_numpy(x).cuda()).cpu().numpy()
+        out["%%d_%%d_%%d" %% (t, m, k)] = c
+np.savez(sys.argv[1], **out)
+"""
+
+
+def _run(ring, path):
+    env = dict(os.environ)
+    env.pop("LAMM_DECODE_RING", None)
+    if ring != 2:
+        env["LAMM_DECODE_RING"] = str(ring)
+    subprocess.run([sys.executable, "-c", CHILD % {"root": ROOT}, path], check=True, env=env, timeout=600)
+    return dict(np.load(path))
+
+
+@pytest.mark.parametrize("ring", [3, 4])
+def test_decode_ring_depth(tmp_path, oracle, ring):
+    from conftest import tol_c
+    from test_gpu_parity import weights
+    base = _run(2, str(tmp_path / "r2.npz"))
+    deep = _run(ring, str(tmp_path / f"r{ring}.npz"))
+    assert base.keys() == deep.keys()
+    for key in base:
+        assert np.array_equal(base[key], deep[key]), f"ring {ring}: {key} differs from ring 2"
+    # and ring 2 itself against the oracle on one case per format (the rest is tests/test_gpu_parity.py)
+    for key in base:
+        t, m, k = (int(v) for v in key.split("_"))
+        if (m, k) != (33, 4096):
+            continue
+        w = weights(oracle, t, m, k, seed=m + 3 * k + t)
+        x = np.random.default_rng(m * k).standard_normal((1, k)).astype(np.float32)
+        want = oracle.mul_mat(t, w, x)
+        assert np.abs(deep[key] - want).max() <= tol_c(want, k)
