@@ -1,6 +1,7 @@
 """the K-quants the reference lists as TODO (Q3_K, Q4_K, Q5_K, Q6_K x Q8_K) on the CUDA path,
 against the oracle (pinned to ggml's own ggml_vec_dot_q*_K_q8_K, tests/test_oracle_vs_ref.py) and the golden
-fixtures.  Decode (N <= 8) runs the streaming GEMV, prefill the dequantize-once tcgen05 GEMM.  C-ABI only."""
+fixtures.  N == 1 runs the single-launch decode kernel (dot_unit_kx), 2 <= N <= 8 the streaming GEMV, prefill
+the dequantize-once tcgen05 GEMM.  C-ABI only."""
 import numpy as np
 import pytest
 from conftest import make_x, tol_c
