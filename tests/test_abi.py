@@ -124,3 +124,19 @@ def test_no_cpu_fallback(lamm):
     assert rc == -1 and b"CUDA" in L.lammcu_last_error() or b"device" in L.lammcu_last_error()
     h = C.c_void_p()
     assert L.lammcu_weight_register(buf.ctypes.data, lamm.Q4_1, 1, 32, 20, 0, 1, C.byref(h)) == -1
+
+
+def test_every_environment_variable_is_documented():
+    """INTEGRATION.md section 6 lists every LAMM_* variable the library reads (and nothing it does not)."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    read = set()
+    csrc = os.path.join(root, "la-llama.cpp_b200", "csrc")
+    for f in os.listdir(csrc):
+        with open(os.path.join(csrc, f)) as fh:
+            read |= set(re.findall(r'getenv\("(LAMM_[A-Z0-9_]+)"\)', fh.read()))
+    with open(os.path.join(root, "INTEGRATION.md")) as fh:
+        doc = fh.read()
+    table = set(re.findall(r"^\| `(LAMM_[A-Z0-9_]+)` \|", doc, flags=re.M))
+    assert read, "no getenv found: the scan is broken"
+    assert read == table, f"undocumented: {sorted(read - table)}; stale: {sorted(table - read)}"
