@@ -18,7 +18,7 @@ import sys
 import numpy as np
 
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests"))
-from oracle_lib import (F32, KQ_TYPES, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES, Ref, build_ref)
+from oracle_lib import (F16, F32, KQ_TYPES, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES, Ref, build_ref)
 
 OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
 
@@ -90,6 +90,16 @@ def main():
                             w_type=t, wq=wq, x=x, xq=xq, c_vecdot=c_vecdot, c_graph=c_graph,
                             w_deq=r.dequantize(t, wq, k))
         print(name, m, n, k, "graph-vecdot", float(np.abs(c_graph - c_vecdot).max()))
+    # SURVEY 8f-2, oracle step: F16 weights through stock ggml (lamm's gate refuses F16).  Own generator and
+    # an own file-name prefix: the CUDA path has no F16 kernel yet, and the GPU tests sweep mulmat_*.npz
+    rng = np.random.default_rng(20240316)
+    m, n, k = 33, 18, 4096
+    w = rng.standard_normal((m, k)).astype(np.float32)
+    x = make_x(rng, n, k)
+    x[6] *= np.float32(1e-2)                      # keep every row inside the fp16 range (make_x scales it by 3e3)
+    wq = r.quantize_weights(F16, w)
+    np.savez_compressed(os.path.join(OUT, f"next_f16_m{m}_n{n}_k{k}.npz"), w_type=F16, wq=wq, x=x,
+                        c_graph=r.graph_mul_mat(F16, wq, x), w_deq=r.dequantize(F16, wq, k))
 
 
 if __name__ == "__main__":

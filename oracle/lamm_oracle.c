@@ -19,7 +19,7 @@
 /* ------------------------------------------------------------------ */
 int orc_blck_size(int type) {
   switch (type) {
-  case ORC_TYPE_F32: return 1;
+  case ORC_TYPE_F32: case ORC_TYPE_F16: return 1;
   case ORC_TYPE_Q4_0: case ORC_TYPE_Q4_1: case ORC_TYPE_Q5_0:
   case ORC_TYPE_Q5_1: case ORC_TYPE_Q8_0: case ORC_TYPE_Q8_1: return 32;
   case ORC_TYPE_Q2_K: case ORC_TYPE_Q8_K: return 256;
@@ -31,6 +31,7 @@ int orc_blck_size(int type) {
 size_t orc_type_size(int type) {
   switch (type) {
   case ORC_TYPE_F32: return 4;
+  case ORC_TYPE_F16: return 2;
   case ORC_TYPE_Q4_0: return sizeof(orc_q4_0);
   case ORC_TYPE_Q4_1: return sizeof(orc_q4_1);
   case ORC_TYPE_Q5_0: return sizeof(orc_q5_0);
@@ -51,6 +52,7 @@ size_t orc_type_size(int type) {
 int orc_vec_dot_type(int type) {
   switch (type) {
   case ORC_TYPE_F32: return ORC_TYPE_F32;
+  case ORC_TYPE_F16: return ORC_TYPE_F16;            /* ggml.c:486-496 */
   case ORC_TYPE_Q4_0: case ORC_TYPE_Q5_0: case ORC_TYPE_Q8_0: return ORC_TYPE_Q8_0;
   case ORC_TYPE_Q4_1: case ORC_TYPE_Q5_1: case ORC_TYPE_Q8_1: return ORC_TYPE_Q8_1;
   case ORC_TYPE_Q2_K: return ORC_TYPE_Q8_K;
@@ -212,6 +214,9 @@ int orc_quantize_act(int vec_dot_type, const float *x, int64_t ldx, void *y,
     case ORC_TYPE_Q8_1: orc_quantize_row_q8_1(xr, yr, k); break;
     case ORC_TYPE_Q8_K: orc_quantize_row_q8_K(xr, yr, k); break;
     case ORC_TYPE_F32: memcpy(yr, xr, (size_t)k * 4); break;
+    case ORC_TYPE_F16:                               /* ggml_fp32_to_fp16_row, ggml.c:354-372 */
+      for (int64_t i = 0; i < k; i++) ((uint16_t *)yr)[i] = orc_fp32_to_fp16(xr[i]);
+      break;
     default: return -1;
     }
   }
@@ -272,6 +277,10 @@ static void pack_high_bits(const uint8_t q[32], uint8_t qh[4]) {
 int orc_quantize_weights(int type, const float *x, void *vy, int64_t n_rows,
                          int64_t k) {
   if (type == ORC_TYPE_F32) { memcpy(vy, x, (size_t)(n_rows * k) * 4); return 0; }
+  if (type == ORC_TYPE_F16) {
+    for (int64_t i = 0; i < n_rows * k; i++) ((uint16_t *)vy)[i] = orc_fp32_to_fp16(x[i]);
+    return 0;
+  }
   if (orc_blck_size(type) != 32 || k % 32) return -1;
   const int64_t nb = n_rows * (k / 32);
   uint8_t q[32];
@@ -476,6 +485,9 @@ int orc_dequantize_row(int type, const void *vx, float *y, int64_t k) {
   int q[256];
   switch (type) {
   case ORC_TYPE_F32: memcpy(y, vx, (size_t)k * 4); return 0;
+  case ORC_TYPE_F16:
+    for (int64_t i = 0; i < k; i++) y[i] = orc_fp16_to_fp32(((const uint16_t *)vx)[i]);
+    return 0;
   case ORC_TYPE_Q4_0: {
     const orc_q4_0 *x = (const orc_q4_0 *)vx;
     for (int64_t i = 0; i < k / 32; i++) {
@@ -638,7 +650,7 @@ static inline orc_term block_term(int w_type, const char *w, const char *x, int6
 }
 
 static int supported_w(int t) {
-  return t == ORC_TYPE_F32 || t == ORC_TYPE_Q4_0 || t == ORC_TYPE_Q4_1 ||
+  return t == ORC_TYPE_F32 || t == ORC_TYPE_F16 || t == ORC_TYPE_Q4_0 || t == ORC_TYPE_Q4_1 ||
          t == ORC_TYPE_Q5_0 || t == ORC_TYPE_Q5_1 || t == ORC_TYPE_Q8_0 ||
          t == ORC_TYPE_Q2_K || is_kq_ext(t);
 }
@@ -649,6 +661,12 @@ static double dot_f64(int w_type, const char *wrow, const char *xrow, int64_t K)
   if (w_type == ORC_TYPE_F32) {
     const float *a = (const float *)wrow, *b = (const float *)xrow;
     for (int64_t k = 0; k < K; k++) acc += (double)a[k] * (double)b[k];
+    return acc;
+  }
+  if (w_type == ORC_TYPE_F16) {                      /* ggml_vec_dot_f16: products of the two halves */
+    const uint16_t *a = (const uint16_t *)wrow, *b = (const uint16_t *)xrow;
+    for (int64_t k = 0; k < K; k++)
+      acc += (double)orc_fp16_to_fp32(a[k]) * (double)orc_fp16_to_fp32(b[k]);
     return acc;
   }
   const int64_t nb = K / orc_blck_size(w_type);
@@ -668,6 +686,11 @@ static float dot_f32(int w_type, const char *wrow, const char *xrow, int64_t K) 
   if (w_type == ORC_TYPE_F32) {
     const float *a = (const float *)wrow, *b = (const float *)xrow;
     for (int64_t k = 0; k < K; k++) acc += a[k] * b[k];
+    return acc;
+  }
+  if (w_type == ORC_TYPE_F16) {
+    const uint16_t *a = (const uint16_t *)wrow, *b = (const uint16_t *)xrow;
+    for (int64_t k = 0; k < K; k++) acc += orc_fp16_to_fp32(a[k]) * orc_fp16_to_fp32(b[k]);
     return acc;
   }
   const int64_t nb = K / orc_blck_size(w_type);

@@ -49,7 +49,12 @@ enum {
   ORC_TYPE_Q3_K = 11,
   ORC_TYPE_Q4_K = 12,
   ORC_TYPE_Q5_K = 13,
-  ORC_TYPE_Q6_K = 14
+  ORC_TYPE_Q6_K = 14,
+  /* SURVEY 8f-2 (oracle only so far; no CUDA kernel yet): F16 weights.  Not in the reference's
+   * lamm table either: ggml converts src1 with ggml_fp32_to_fp16_row (ggml.c:354-372, RNE) and
+   * runs ggml_vec_dot_f16 (ggml.c:1589-1630: f32 products of the two halves, f32 SIMD partial
+   * sums)                                                                               */
+  ORC_TYPE_F16 = 1
 };
 
 #pragma pack(push, 1)

@@ -29,10 +29,24 @@ TSIZE = {F32: 4, Q4_0: 18, Q4_1: 20, Q5_0: 22, Q5_1: 24, Q8_0: 34, Q8_1: 36, Q2_
 VEC_DOT = {F32: F32, Q4_0: Q8_0, Q4_1: Q8_1, Q5_0: Q8_0, Q5_1: Q8_1, Q8_0: Q8_0, Q2_K: Q8_K,
            Q3_K: Q8_K, Q4_K: Q8_K, Q5_K: Q8_K, Q6_K: Q8_K}
 
+# SURVEY 8f-2, oracle only so far (no CUDA kernel; the product's type table refuses it, tests/test_abi.py):
+# kept out of BLCK / TSIZE / VEC_DOT, which tests/test_abi.py compares with the product's table
+F16 = 1
+TYPE_NAMES[F16] = "f16"
+NAME_TO_TYPE["f16"] = F16
+ORACLE_ONLY = {F16: (1, 2, F16)}                          # type -> (block, bytes, vec-dot type), ggml.c:486-496
+
+
+def vec_dot_of(t):
+    return VEC_DOT[t] if t in VEC_DOT else ORACLE_ONLY[t][2]
+
+
 i64, vp, fp = C.c_int64, C.c_void_p, C.POINTER(C.c_float)
 
 
 def row_size(t, k):
+    if t in ORACLE_ONLY:
+        return (k // ORACLE_ONLY[t][0]) * ORACLE_ONLY[t][1]
     return (k // BLCK[t]) * TSIZE[t]
 
 
@@ -122,7 +136,7 @@ class Oracle:
         x = np.ascontiguousarray(x, np.float32)
         m, (n, k) = wq.shape[0], x.shape
         c = np.zeros((n, m), np.float32)
-        xq = np.zeros((n, row_size(VEC_DOT[t], k)), np.uint8)
+        xq = np.zeros((n, row_size(vec_dot_of(t), k)), np.uint8)
         assert self.L.orc_mul_mat(t, _ptr(wq), wq.strides[0], _fptr(x), k, _fptr(c), m, m, n, k, _ptr(xq)) == 0
         return (c, xq) if want_xq else c
 

@@ -6,7 +6,7 @@ import os
 import numpy as np
 import pytest
 from conftest import GOLDEN, golden, tol_c
-from oracle_lib import F32, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT
+from oracle_lib import F16, F32, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT
 
 MULMAT = sorted(os.path.basename(p) for p in glob.glob(os.path.join(GOLDEN, "mulmat_*.npz")))
 
@@ -69,6 +69,19 @@ def test_f32_order_variant(oracle, name):
     a = oracle.mul_mat_q(t, g["wq"], xq, k)
     b = oracle.mul_mat_q(t, g["wq"], xq, k, f32_order=True)
     assert np.abs(a - b).max() <= 0.05 * tol_c(a, k)
+
+
+def test_f16_weights_golden(oracle):
+    """SURVEY 8f-2, oracle step: F16 weights against stock ggml's graph result (fixture from the compiled
+    reference; the CUDA path does not take F16 yet)."""
+    g = golden("next_f16_m33_n18_k4096.npz")
+    assert int(g["w_type"]) == F16
+    k = g["x"].shape[1]
+    c = oracle.mul_mat(F16, g["wq"], g["x"])
+    assert np.isfinite(c).all() and np.abs(c - g["c_graph"]).max() <= tol_c(g["c_graph"], k)
+    assert np.array_equal(oracle.dequantize(F16, g["wq"], k), g["w_deq"])
+    assert np.array_equal(oracle.quantize_act(F16, g["x"]).view(np.uint16).reshape(g["x"].shape),
+                          g["x"].astype(np.float16).view(np.uint16))
 
 
 def test_threaded_port_matches(oracle):

@@ -3,7 +3,7 @@ Runs only where that library exists (this container; it also travels to the GPU 
 import numpy as np
 import pytest
 from conftest import make_x, tol_c
-from oracle_lib import F32, KQ_TYPES, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES
+from oracle_lib import F16, F32, KQ_TYPES, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES
 
 
 @pytest.mark.parametrize("vt", [Q8_0, Q8_1, Q8_K])
@@ -70,6 +70,34 @@ def test_kquants_vs_ggml_vec_dot(oracle, ref, t):
         assert np.array_equal(oracle.dequantize(t, wq, k), ref.dequantize(t, wq, k))
     with pytest.raises(AssertionError):
         ref.lamm_mul_mat(t, wq, x, xq)                   # the reference operator itself refuses these types
+
+
+def test_f16_weights_vs_ggml_graph(oracle, ref):
+    """SURVEY 8f-2, oracle step: F16 weights.  lamm's gate refuses F16, so the behaviour to match is stock
+    ggml: src1 -> ggml_fp32_to_fp16_row (RNE), ggml_vec_dot_f16.  The conversions must be byte-exact (also
+    against numpy's IEEE float16), C within the tier tolerance; K need not be a multiple of anything."""
+    rng = np.random.default_rng(4242)
+    for (m, n, k) in [(33, 18, 4096), (7, 1, 100), (5, 3, 33), (19, 2, 11008)]:
+        w = rng.standard_normal((m, k)).astype(np.float32)
+        x = rng.standard_normal((n, k)).astype(np.float32)
+        x[0, ::3] *= np.float32(1e-6)                  # fp16 subnormals
+        x[-1, 1::5] *= np.float32(3e3)
+        x[-1, 0] = np.float32(1e6)                     # beyond the fp16 range: +inf in the row, as in ggml
+        wq = oracle.quantize_weights(F16, w)
+        assert np.array_equal(wq, ref.quantize_weights(F16, w))
+        assert np.array_equal(wq.view(np.float16).reshape(m, k), w.astype(np.float16))
+        xq = oracle.quantize_act(F16, x)
+        with np.errstate(over="ignore"):
+            assert np.array_equal(xq.view(np.uint16).reshape(n, k), x.astype(np.float16).view(np.uint16))
+        assert np.array_equal(oracle.dequantize(F16, wq, k), ref.dequantize(F16, wq, k))
+        c = oracle.mul_mat(F16, wq, x)
+        g = ref.graph_mul_mat(F16, wq, x)
+        fin = np.isfinite(c)
+        assert np.array_equal(fin, np.isfinite(g)) and fin[:-1].all() and not fin[-1].any()
+        cf, gf = np.where(fin, c, 0), np.where(fin, g, 0)
+        assert np.abs(cf - gf).max() <= tol_c(cf, k)
+        v = ref.vec_dot(F16, wq, xq, k)
+        assert np.abs(np.where(fin, v, 0) - cf).max() <= tol_c(cf, k)
 
 
 def test_fp16_tables_all_65536_halves(oracle, ref):
