@@ -79,7 +79,7 @@ def test_f16_weights_golden(oracle):
     k = g["x"].shape[1]
     c = oracle.mul_mat(F16, g["wq"], g["x"])
     assert np.isfinite(c).all() and np.abs(c - g["c_graph"]).max() <= tol_c(g["c_graph"], k)
-    assert np.array_equal(oracle.dequantize(F16, g["wq"], k), g["w_deq"])
+    assert np.array_equal(oracle.dequantize(F16, g["wq"], k), g["wq"].view(np.float16).astype(np.float32))
     assert np.array_equal(oracle.quantize_act(F16, g["x"]).view(np.uint16).reshape(g["x"].shape),
                           g["x"].astype(np.float16).view(np.uint16))
 
