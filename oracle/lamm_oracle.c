@@ -759,6 +759,21 @@ int orc_mul_mat(int w_type, const void *w, int64_t w_stride, const float *x,
   return rc;
 }
 
+/* ggml_mul_mat_id (ggml.c:10992-11170): row j of X against expert ids[j][id] */
+int orc_mul_mat_id(int w_type, const void *const *ws, int n_as, int64_t w_stride,
+                   const int32_t *ids, int64_t ids_stride, int id, const float *x,
+                   int64_t ldx, float *c, int64_t ldc, int64_t M, int64_t N, int64_t K) {
+  int rc = check_shape(w_type, K);
+  if (rc) return rc;
+  for (int64_t j = 0; j < N; j++) {
+    const int32_t e = ids[j * ids_stride + id];
+    if (e < 0 || e >= n_as) return -4;
+    rc = orc_mul_mat(w_type, ws[e], w_stride, x + j * ldx, ldx, c + j * ldc, ldc, M, 1, K, NULL);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
 /* ---- threaded f32 variant (timed CPU "port" baseline) -------------- */
 typedef struct {
   int w_type; const char *w; int64_t w_stride; const char *xq; int64_t xq_stride;

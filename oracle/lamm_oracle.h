@@ -121,6 +121,13 @@ int orc_mul_mat_q_f32(int w_type, const void *w, int64_t w_stride,
 int orc_mul_mat(int w_type, const void *w, int64_t w_stride, const float *x,
                 int64_t ldx, float *c, int64_t ldc, int64_t M, int64_t N,
                 int64_t K, void *xq_out);
+/* SURVEY 8f-2 (oracle only so far): ggml_mul_mat_id -- token j is multiplied by expert matrix
+ * ws[ids[j * ids_stride + id]] (ggml.c:4616-4656; forward ggml.c:10992-11170 groups the rows
+ * per expert and runs the same vec_dot).  ws: n_as matrices of one type and shape.
+ * Returns -4 when an id is outside [0, n_as).                                          */
+int orc_mul_mat_id(int w_type, const void *const *ws, int n_as, int64_t w_stride,
+                   const int32_t *ids, int64_t ids_stride, int id, const float *x,
+                   int64_t ldx, float *c, int64_t ldc, int64_t M, int64_t N, int64_t K);
 /* multi-threaded (pthreads over M) f32-order variant: the timed "port" CPU
  * baseline.  nth threads, rows split like src/lamm_impl.hpp:40-45 but with the
  * remainder rows given to the last thread (defect 9-3 not reproduced).      */

@@ -189,6 +189,40 @@ int ref_graph_mul_mat(int w_type, const void *w, const float *x, float *c,
   return 0;
 }
 
+// ggml_mul_mat_id (ggml.c:4616-4656, forward ggml.c:10992-11170): n_as expert matrices of one
+// type/shape packed back to back in `ws`, ids = I32 [n_ids, N] (row per token), the node takes
+// column `id`.  SURVEY 8f-2: the other caller of the same inner product (lamm's hook is not in it).
+int ref_graph_mul_mat_id(int w_type, const void *ws, int n_as, const int32_t *ids, int n_ids, int id,
+                         const float *x, float *c, int64_t M, int64_t N, int64_t K, int nth) {
+  ref_init();
+  if (n_as < 1 || n_as > GGML_MAX_SRC - 2 || id < 0 || id >= n_ids) return -2;
+  const size_t wbytes = ggml_row_size((enum ggml_type)w_type, K) * (size_t)M;
+  size_t ctx_size = wbytes * (size_t)n_as + (size_t)K * N * 4 + (size_t)M * N * 4 +
+                    (size_t)n_ids * N * 4 + (16u << 20);
+  struct ggml_init_params ip = {ctx_size, nullptr, false};
+  struct ggml_context *ctx = ggml_init(ip);
+  if (!ctx) return -1;
+  struct ggml_tensor *as[GGML_MAX_SRC];
+  for (int e = 0; e < n_as; e++) {
+    as[e] = ggml_new_tensor_2d(ctx, (enum ggml_type)w_type, K, M);
+    memcpy(as[e]->data, (const char *)ws + (size_t)e * wbytes, wbytes);
+  }
+  struct ggml_tensor *tid = ggml_new_tensor_2d(ctx, GGML_TYPE_I32, n_ids, N);
+  memcpy(tid->data, ids, (size_t)n_ids * N * 4);
+  struct ggml_tensor *tx = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, K, N);
+  memcpy(tx->data, x, (size_t)K * N * 4);
+  struct ggml_tensor *tc = ggml_mul_mat_id(ctx, as, n_as, tid, id, tx);
+  struct ggml_cgraph *g = ggml_new_graph(ctx);
+  ggml_build_forward_expand(g, tc);
+  struct ggml_cplan plan = ggml_graph_plan(g, nth);
+  std::vector<uint8_t> work(plan.work_size + 16);
+  plan.work_data = work.data();
+  ggml_graph_compute(g, &plan);
+  memcpy(c, tc->data, (size_t)M * N * 4);
+  ggml_free(ctx);
+  return 0;
+}
+
 // Timing loop after src/la-benchmark-matmult.cpp:322-390: each iteration times
 // one full ggml_graph_compute (plan + INIT quantize + COMPUTE) of graph 1,
 // then runs a second, untimed graph on other weights to disturb the caches.

@@ -90,6 +90,8 @@ class Oracle:
         L.orc_mul_mat_q_f32.argtypes = L.orc_mul_mat_q.argtypes
         L.orc_mul_mat.argtypes = [C.c_int, vp, i64, fp, i64, fp, i64, i64, i64, i64, vp]
         L.orc_mul_mat_mt.argtypes = [C.c_int, vp, i64, fp, i64, fp, i64, i64, i64, i64, C.c_int, vp]
+        L.orc_mul_mat_id.argtypes = [C.c_int, C.POINTER(vp), C.c_int, i64, vp, i64, C.c_int, fp, i64, fp, i64,
+                                     i64, i64, i64]
 
     def quantize_act(self, vt, x, prefill=0):
         """x: [N, K] f32 -> uint8 [N, row_size].  Output pre-filled (Q8_K bsums of
@@ -140,6 +142,19 @@ class Oracle:
         assert self.L.orc_mul_mat(t, _ptr(wq), wq.strides[0], _fptr(x), k, _fptr(c), m, m, n, k, _ptr(xq)) == 0
         return (c, xq) if want_xq else c
 
+    def mul_mat_id(self, t, wqs, ids, id_, x):
+        """wqs: list of uint8 [M, row_size] expert matrices, ids: int32 [N, n_ids], x: [N, K] -> C [N, M]"""
+        wqs = [np.ascontiguousarray(w) for w in wqs]
+        ids = np.ascontiguousarray(ids, np.int32)
+        x = np.ascontiguousarray(x, np.float32)
+        m, (n, k) = wqs[0].shape[0], x.shape
+        c = np.zeros((n, m), np.float32)
+        ptrs = (vp * len(wqs))(*[w.ctypes.data for w in wqs])
+        rc = self.L.orc_mul_mat_id(t, ptrs, len(wqs), wqs[0].strides[0], _ptr(ids), ids.shape[1], id_, _fptr(x), k,
+                                   _fptr(c), m, m, n, k)
+        assert rc == 0, rc
+        return c
+
     def mul_mat_mt(self, t, wq, x, nth):
         wq = np.ascontiguousarray(wq)
         x = np.ascontiguousarray(x, np.float32)
@@ -167,6 +182,8 @@ class Ref:
         L.ref_vec_dot.argtypes = [C.c_int, vp, vp, i64]
         L.ref_lamm_mul_mat.argtypes = [C.c_int, vp, i64, fp, vp, fp, i64, i64, i64, i64, C.c_int]
         L.ref_graph_mul_mat.argtypes = [C.c_int, vp, fp, fp, i64, i64, i64, C.c_int]
+        if hasattr(L, "ref_graph_mul_mat_id"):
+            L.ref_graph_mul_mat_id.argtypes = [C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, fp, fp, i64, i64, i64, C.c_int]
         L.ref_bench_mul_mat.argtypes = [C.c_int, vp, fp, i64, i64, i64, C.c_int, C.c_int, C.POINTER(C.c_double)]
         L.ref_row_size.restype = C.c_size_t
         L.ref_row_size.argtypes = [C.c_int, i64]
@@ -220,6 +237,18 @@ class Ref:
         m, (n, k) = wq.shape[0], x.shape
         c = np.zeros((n, m), np.float32)
         assert self.L.ref_graph_mul_mat(t, _ptr(wq), _fptr(x), _fptr(c), m, n, k, nth) == 0
+        return c
+
+    def graph_mul_mat_id(self, t, wqs, ids, id_, x, nth=1):
+        """ggml_mul_mat_id through ggml_graph_compute (stock ggml; lamm's hook is not on this op)."""
+        ws = np.ascontiguousarray(np.stack([np.ascontiguousarray(w) for w in wqs]))
+        ids = np.ascontiguousarray(ids, np.int32)
+        x = np.ascontiguousarray(x, np.float32)
+        m, (n, k) = wqs[0].shape[0], x.shape
+        c = np.zeros((n, m), np.float32)
+        rc = self.L.ref_graph_mul_mat_id(t, _ptr(ws), len(wqs), _ptr(ids), ids.shape[1], id_, _fptr(x), _fptr(c),
+                                         m, n, k, nth)
+        assert rc == 0, rc
         return c
 
     def bench(self, t, m, n, k, nth, iters, wq=None, x=None):

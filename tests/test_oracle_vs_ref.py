@@ -100,6 +100,44 @@ def test_f16_weights_vs_ggml_graph(oracle, ref):
         assert np.abs(np.where(fin, v, 0) - cf).max() <= tol_c(cf, k)
 
 
+@pytest.mark.parametrize("t", [3, 8, Q2_K, 12, F16, F32])
+def test_mul_mat_id_vs_ggml_graph(oracle, ref, t):
+    """SURVEY 8f-2, oracle step: ggml_mul_mat_id (expert selection per token) against stock ggml's graph,
+    for a lamm format, Q8_0, both K-quant families, F16 and F32; every column of ids, experts that get
+    no token, tokens that all pick one expert, 1 and 3 threads."""
+    rng = np.random.default_rng(900 + t)
+    m, n, k, n_as, n_ids = 37, 11, 1024, 4, 2
+    x = make_x(rng, n, k)
+    if t in (3, 8):
+        # ggml's INIT phase runs the AVX2 quantize_row_q8_{0,1}, which rounds exact .5 ties to even where the
+        # _reference quantizer rounds away (SURVEY 9-5): make_x's tie rows would differ by design, so these
+        # formats get plain Gaussian rows here and the tie behaviour stays with test_act_quantizers_bit_exact
+        x = rng.standard_normal((n, k)).astype(np.float32)
+    wqs = []
+    for e in range(n_as):
+        w = rng.standard_normal((m, k)).astype(np.float32)
+        if t == F32:
+            wqs.append(w.copy().view(np.uint8).reshape(m, k * 4))
+        elif t in (Q2_K, 12):
+            wqs.append(ref.quantize_weights(t, w))
+        else:
+            wqs.append(oracle.quantize_weights(t, w))
+    ids = rng.integers(0, n_as - 1, (n, n_ids)).astype(np.int32)      # expert n_as-1 never chosen in column 0
+    ids[:, 1] = 2                                                     # column 1: every token picks expert 2
+    ids[0, 0] = 0
+    for id_ in range(n_ids):
+        want = oracle.mul_mat_id(t, wqs, ids, id_, x)
+        per_token = np.stack([oracle.mul_mat(t, wqs[ids[j, id_]], x[j:j + 1])[0] for j in range(n)])
+        assert np.array_equal(want, per_token)
+        for nth in (1, 3):
+            got = ref.graph_mul_mat_id(t, wqs, ids, id_, x, nth=nth)
+            assert np.abs(got - want).max() <= tol_c(want, k), f"{TYPE_NAMES[t]} id {id_} nth {nth}"
+    bad = ids.copy()
+    bad[3, 0] = n_as
+    with pytest.raises(AssertionError):
+        oracle.mul_mat_id(t, wqs, bad, 0, x)
+
+
 def test_fp16_tables_all_65536_halves(oracle, ref):
     """fp16 -> f32 of every half bit pattern: reference table (through dequantize_row_q8_0 with
     qs = 1, ggml-impl.h:237-250) == oracle == IEEE (numpy).  NaNs compared by 'is NaN'."""
