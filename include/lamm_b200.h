@@ -112,6 +112,21 @@ void lamm_mul_mat(const struct ggml_compute_params *params,
  * run time with the environment variable LAMM_OPT_LEVEL.                      */
 int lamm_get_opt_level(void);
 
+/* SURVEY 8f-2, an extension with no counterpart in the reference (its hook sits in
+ * ggml_compute_forward_mul_mat only): the same pair for GGML_OP_MUL_MAT_ID, to be called at the top
+ * of ggml_compute_forward_mul_mat_id (ggml.c:10992) exactly like the mul_mat hook
+ * (ggml.c:10858-10863).  dst->src[0] = ids (I32 [n_ids, N]), src[1] = b (F32 [K, N]),
+ * src[2 .. 2+n_as) = the expert matrices (one type and shape), op_params[0] = id,
+ * op_params[1] = n_as (ggml.c:4616-4656).  Token j is multiplied by expert ids[j][id]; the tokens
+ * of one expert are gathered and run as one mul_mat through the same kernels as lamm_mul_mat
+ * (a single token, the decode case, goes straight to the decode path).  2-D operands only.
+ * NOT YET VERIFIED ON HARDWARE (written after this round's GPU budget was spent); the opt-in check
+ * is tests/test_gpu_experimental.py.                                                           */
+bool lamm_can_mul_mat_id(const struct ggml_compute_params *params,
+                         const struct ggml_tensor *dst);
+void lamm_mul_mat_id(const struct ggml_compute_params *params,
+                     struct ggml_tensor *dst);
+
 /* Test hook: after lamm_mul_mat, copy the GPU's quantized activations back
  * into params->wdata (what ggml's INIT phase would have written there).       */
 void lamm_set_writeback_wdata(int enable);

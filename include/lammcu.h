@@ -233,6 +233,15 @@ int lammcu_weight_release(lammcu_weight_t w);
  * llama_free_model).  Handles to forgotten entries become invalid.                                      */
 int lammcu_weight_forget(const void *w_host);
 int lammcu_weight_forget_all(void);
+
+/* Expert selection of ggml_mul_mat_id (ggml.c:11066-11078 builds the same lists as
+ * matrix_row_counts / matrix_rows in its INIT phase): token j goes to expert
+ * ids[j * ids_stride + id] (ids_stride in int32 elements).  counts[n_as] receives the number of
+ * tokens per expert, order[n_tokens] the token indices grouped by expert (expert 0's tokens first,
+ * ascending within an expert).  Pure host function: needs no device and takes no lock.
+ * LAMMCU_ERR_ARG for a bad argument or an id outside [0, n_as) (ggml asserts there).            */
+int lammcu_mul_mat_id_plan(const int32_t *ids, int64_t ids_stride, int id, int64_t n_tokens,
+                           int n_as, int64_t *counts, int64_t *order);
 const void *lammcu_weight_dev_ptr(lammcu_weight_t w);
 int64_t lammcu_weight_rows(lammcu_weight_t w);
 

@@ -39,6 +39,7 @@ EXPORTS = [
     "lammcu_mul_mat_batch_dev", "lammcu_set_gemm_exact", "lammcu_get_gemm_exact", "lammcu_host_profile", "lammcu_set_host_mode", "lammcu_get_host_mode", "lammcu_host_quiesce", "lammcu_set_server_timeouts", "lammcu_server_trace", "lammcu_comm_create", "lammcu_comm_destroy", "lammcu_comm_status", "lammcu_ll_bytes", "lammcu_mul_mat_sharded_dev", "lammcu_mul_mat_sharded_batch_dev", "lammcu_mul_mat_sharded_gemm_dev", "lammcu_ll_unpack_dev", "lammcu_weight_register", "lammcu_weight_lookup", "lammcu_weight_release", "lammcu_weight_forget", "lammcu_weight_forget_all",
     "lammcu_weight_dev_ptr", "lammcu_weight_rows", "lammcu_mul_mat_host", "lammcu_mul_mat_q_host",
     "lamm_can_mul_mat", "lamm_mul_mat", "lamm_get_opt_level", "lamm_set_writeback_wdata",
+    "lammcu_mul_mat_id_plan", "lamm_can_mul_mat_id", "lamm_mul_mat_id",
 ]
 
 
@@ -135,6 +136,12 @@ def lib():
     L.lamm_can_mul_mat.argtypes = [C.POINTER(GgmlComputeParams), C.POINTER(GgmlTensor)]
     L.lamm_mul_mat.restype = None
     L.lamm_mul_mat.argtypes = [C.POINTER(GgmlComputeParams), C.POINTER(GgmlTensor)]
+    L.lamm_can_mul_mat_id.restype = C.c_bool
+    L.lamm_can_mul_mat_id.argtypes = [C.POINTER(GgmlComputeParams), C.POINTER(GgmlTensor)]
+    L.lamm_mul_mat_id.restype = None
+    L.lamm_mul_mat_id.argtypes = [C.POINTER(GgmlComputeParams), C.POINTER(GgmlTensor)]
+    L.lammcu_mul_mat_id_plan.restype = C.c_int
+    L.lammcu_mul_mat_id_plan.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
     L.lamm_set_writeback_wdata.restype = None
     L.lamm_set_writeback_wdata.argtypes = [C.c_int]
     _lib = L
@@ -269,4 +276,53 @@ def lamm_mul_mat_host(w_type, w_np, x_np, nth=1, wdata=None, task=TASK_COMPUTE):
             can = False
             break
         L.lamm_mul_mat(C.byref(p), C.byref(dst))
+    return can, c
+
+
+I32 = 26                                                    # GGML_TYPE_I32, ggml.h:367
+
+
+def mul_mat_id_plan(ids_np, id_, n_as):
+    """lammcu_mul_mat_id_plan on an int32 [N, n_ids] array -> (counts[n_as], order[N]) or raises LammError.
+    Pure host logic: works without a device."""
+    import numpy as np
+    ids_np = np.ascontiguousarray(ids_np, np.int32)
+    n = ids_np.shape[0]
+    counts = np.zeros(n_as, np.int64)
+    order = np.zeros(max(n, 1), np.int64)
+    rc = lib().lammcu_mul_mat_id_plan(ids_np.ctypes.data, ids_np.shape[1], id_, n, n_as, counts.ctypes.data,
+                                      order.ctypes.data)
+    if rc != 0:
+        raise LammError(f"lammcu_mul_mat_id_plan: rc {rc}")
+    return counts, order[:n]
+
+
+def lamm_mul_mat_id_host(w_type, w_list, ids_np, id_, x_np, nth=1):
+    """Drive lamm_can_mul_mat_id + lamm_mul_mat_id on hand-built ggml tensors the way a hook at the top of
+    ggml_compute_forward_mul_mat_id (ggml.c:10992) would.  w_list: expert matrices (uint8 [M, row bytes], or
+    float32 [M, K]); ids_np: int32 [N, n_ids]; x_np: float32 [N, K].  Returns (can, C[N, M])."""
+    import numpy as np
+    L = lib()
+    m = w_list[0].shape[0]
+    n, k = x_np.shape
+    ids_np = np.ascontiguousarray(ids_np, np.int32)
+    c = np.zeros((n, m), np.float32)
+    tid = make_tensor_2d(I32, ids_np.shape[1], n, ids_np.ctypes.data, ids_np.strides[0])
+    tid.nb[0] = 4
+    src1 = make_tensor_2d(F32, k, n, x_np.ctypes.data, x_np.strides[0])
+    dst = make_tensor_2d(F32, m, n, c.ctypes.data)
+    dst.src[0] = C.pointer(tid)
+    dst.src[1] = C.pointer(src1)
+    experts = [make_tensor_2d(w_type, k, m, w.ctypes.data, w.strides[0]) for w in w_list]
+    for e, t in enumerate(experts):
+        dst.src[2 + e] = C.pointer(t)
+    dst.op_params[0] = id_
+    dst.op_params[1] = len(w_list)
+    can = True
+    for ith in range(nth):
+        p = GgmlComputeParams(TASK_COMPUTE, ith, nth, 0, None)
+        if not L.lamm_can_mul_mat_id(C.byref(p), C.byref(dst)):
+            can = False
+            break
+        L.lamm_mul_mat_id(C.byref(p), C.byref(dst))
     return can, c

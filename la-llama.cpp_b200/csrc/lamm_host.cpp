@@ -17,6 +17,8 @@
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
+#include <vector>
 
 #ifndef LAMM_OPT_LEVEL
 #define LAMM_OPT_LEVEL 3        // src/lamm_common.h:96-100
@@ -120,6 +122,88 @@ void lamm_mul_mat(const struct ggml_compute_params *params, struct ggml_tensor *
           die("mul_mat");
       }
     }
+  }
+}
+
+// ---- GGML_OP_MUL_MAT_ID (no counterpart in the reference) --------------------------
+
+int lammcu_mul_mat_id_plan(const int32_t *ids, int64_t ids_stride, int id, int64_t n_tokens, int n_as,
+                           int64_t *counts, int64_t *order) {
+  if (!ids || !counts || !order || n_tokens < 0 || n_as < 1 || id < 0 || ids_stride <= id) return LAMMCU_ERR_ARG;
+  for (int e = 0; e < n_as; e++) counts[e] = 0;
+  for (int64_t j = 0; j < n_tokens; j++) {                 // ggml.c:11070-11077
+    const int32_t e = ids[j * ids_stride + id];
+    if (e < 0 || e >= n_as) return LAMMCU_ERR_ARG;
+    counts[e]++;
+  }
+  std::vector<int64_t> at((size_t)n_as);
+  int64_t run = 0;
+  for (int e = 0; e < n_as; e++) { at[(size_t)e] = run;  run += counts[e]; }
+  for (int64_t j = 0; j < n_tokens; j++) order[at[(size_t)ids[j * ids_stride + id]]++] = j;
+  return LAMMCU_OK;
+}
+
+bool lamm_can_mul_mat_id(const struct ggml_compute_params *params, const struct ggml_tensor *dst) {
+  if (opt_level() == 0) return false;
+  if (params->type != GGML_TASK_TYPE_COMPUTE) return false;
+  const ggml_tensor *ids = dst->src[0], *src1 = dst->src[1];
+  const int id = dst->op_params[0], n_as = dst->op_params[1];
+  if (!ids || !src1 || n_as < 1 || n_as > GGML_MAX_SRC - 2) return false;
+  if ((int)ids->type != 26 /* GGML_TYPE_I32 */ || ids->nb[0] != 4 || ids->nb[1] % 4) return false;
+  if (id < 0 || id >= ids->ne[0] || ids->ne[1] != src1->ne[1]) return false;
+  if (src1->type != GGML_TYPE_F32 || src1->nb[0] != 4 || src1->nb[1] % 4) return false;   // quantized here
+  if (src1->ne[2] != 1 || src1->ne[3] != 1 || ids->ne[2] != 1 || ids->ne[3] != 1) return false;
+  if (dst->type != GGML_TYPE_F32 || dst->nb[0] != sizeof(float) || dst->nb[1] % 4) return false;
+  const ggml_tensor *a0 = dst->src[2];
+  if (!a0 || !lammcu_type_supported(a0->type)) return false;
+  const int64_t K = a0->ne[0];
+  const int kmul = (a0->type == GGML_TYPE_F32) ? 8 : lammcu_blck_size(a0->type);
+  if (K <= 0 || K % kmul || K != src1->ne[0]) return false;
+  for (int e = 0; e < n_as; e++) {
+    const ggml_tensor *a = dst->src[2 + e];
+    if (!a || a->type != a0->type || a->ne[0] != K || a->ne[1] != a0->ne[1] || a->ne[2] != 1 || a->ne[3] != 1)
+      return false;
+    if (a->nb[0] != lammcu_type_size(a->type) || a->nb[1] < lammcu_row_size(a->type, K)) return false;
+  }
+  if (dst->ne[0] != a0->ne[1] || dst->ne[1] != src1->ne[1]) return false;
+  return device_ok();
+}
+
+void lamm_mul_mat_id(const struct ggml_compute_params *params, struct ggml_tensor *dst) {
+  if (params->ith != 0) return;
+  const ggml_tensor *ids = dst->src[0], *src1 = dst->src[1], *a0 = dst->src[2];
+  const int id = dst->op_params[0], n_as = dst->op_params[1];
+  const int64_t N = src1->ne[1], K = a0->ne[0], M = a0->ne[1];
+  const int64_t ldx = (int64_t)(src1->nb[1] / sizeof(float)), ldc = (int64_t)(dst->nb[1] / sizeof(float));
+  std::vector<int64_t> counts((size_t)n_as), order((size_t)(N > 0 ? N : 1));
+  if (lammcu_mul_mat_id_plan((const int32_t *)ids->data, (int64_t)(ids->nb[1] / 4), id, N, n_as, counts.data(),
+                             order.data()) != LAMMCU_OK) {
+    std::fprintf(stderr, "lamm_mul_mat_id: expert id outside [0, %d)\n", n_as);      // ggml.c:11074 asserts
+    std::abort();
+  }
+  const float *x = (const float *)src1->data;
+  float *c = (float *)dst->data;
+  std::vector<float> xg, cg;
+  int64_t at = 0;
+  for (int e = 0; e < n_as; e++) {
+    const int64_t cnt = counts[(size_t)e];
+    if (!cnt) continue;
+    const ggml_tensor *a = dst->src[2 + e];
+    lammcu_weight_t w;
+    if (lammcu_weight_register(a->data, a->type, M, K, (int64_t)a->nb[1], 0, M, &w) != LAMMCU_OK) die("weight upload");
+    const int64_t *rows = order.data() + at;
+    at += cnt;
+    // the expert's tokens are consecutive rows of src1 / dst: no gather
+    if (rows[cnt - 1] - rows[0] == cnt - 1) {
+      if (lammcu_mul_mat_host(w, x + rows[0] * ldx, cnt, ldx, c + rows[0] * ldc, ldc, nullptr) != LAMMCU_OK)
+        die("mul_mat_id");
+      continue;
+    }
+    xg.resize((size_t)(cnt * K));
+    cg.resize((size_t)(cnt * M));
+    for (int64_t r = 0; r < cnt; r++) std::memcpy(xg.data() + r * K, x + rows[r] * ldx, (size_t)K * 4);
+    if (lammcu_mul_mat_host(w, xg.data(), cnt, K, cg.data(), M, nullptr) != LAMMCU_OK) die("mul_mat_id");
+    for (int64_t r = 0; r < cnt; r++) std::memcpy(c + rows[r] * ldc, cg.data() + r * M, (size_t)M * 4);
   }
 }
 

@@ -140,3 +140,34 @@ def test_every_environment_variable_is_documented():
     table = set(re.findall(r"^\| `(LAMM_[A-Z0-9_]+)` \|", doc, flags=re.M))
     assert read, "no getenv found: the scan is broken"
     assert read == table, f"undocumented: {sorted(read - table)}; stale: {sorted(table - read)}"
+
+
+def test_mul_mat_id_plan_groups_tokens_like_ggml(lamm):
+    """lammcu_mul_mat_id_plan (pure host logic) against the row lists ggml_compute_forward_mul_mat_id builds
+    in its INIT phase (ggml.c:11066-11078): per-expert counts, tokens in ascending order within an expert."""
+    rng = np.random.default_rng(5)
+    for n, n_as, n_ids in [(1, 4, 2), (11, 4, 2), (64, 8, 3), (7, 1, 1), (0, 3, 1)]:
+        ids = rng.integers(0, n_as, (n, n_ids)).astype(np.int32)
+        for id_ in range(n_ids):
+            counts, order = lamm.mul_mat_id_plan(ids, id_, n_as)
+            want_rows = [[j for j in range(n) if ids[j, id_] == e] for e in range(n_as)]
+            assert counts.tolist() == [len(r) for r in want_rows]
+            assert order.tolist() == [j for r in want_rows for j in r]
+    ids = np.array([[0, 1], [3, 1], [1, 4]], np.int32)
+    assert lamm.mul_mat_id_plan(ids, 0, 4)[0].tolist() == [1, 1, 0, 1]
+    for bad_id, n_as in [(1, 4), (2, 8), (-1, 8), (0, 3)]:          # id 4 >= n_as, column outside ids, expert 3 >= 3
+        with pytest.raises(lamm.LammError):
+            lamm.mul_mat_id_plan(ids, bad_id, n_as)
+    ids[1, 0] = -1
+    with pytest.raises(lamm.LammError):
+        lamm.mul_mat_id_plan(ids, 0, 4)
+
+
+def test_mul_mat_id_gate_without_device(lamm):
+    """lamm_can_mul_mat_id: false without a CUDA device (ggml then keeps its own path), for a well-formed node."""
+    if not _no_device(lamm):
+        pytest.skip("a CUDA device is present")
+    w = [np.zeros((4, 20 * 8), np.uint8) for _ in range(3)]          # Q4_1, K = 256
+    ids = np.array([[0], [2]], np.int32)
+    can, c = lamm.lamm_mul_mat_id_host(lamm.Q4_1, w, ids, 0, np.zeros((2, 256), np.float32))
+    assert can is False and not c.any()

@@ -70,3 +70,24 @@ def test_decode_ring_depth(tmp_path, oracle, ring):
         x = np.random.default_rng(m * k).standard_normal((1, k)).astype(np.float32)
         want = oracle.mul_mat(t, w, x)
         assert np.abs(deep[key] - want).max() <= tol_c(want, k)
+
+
+@pytest.mark.parametrize("t", [3, 8, 10, 12, 0])
+def test_operator_mul_mat_id(gpu, oracle, t):
+    """lamm_can_mul_mat_id + lamm_mul_mat_id (written after the round's GPU budget was spent) against
+    orc_mul_mat_id, which is pinned to stock ggml's ggml_mul_mat_id graph (tests/test_oracle_vs_ref.py): one
+    token (decode), scattered tokens (gather / scatter), consecutive tokens per expert, an expert nobody picks."""
+    from conftest import make_x, tol_c
+    from test_gpu_parity import weights
+    rng = np.random.default_rng(300 + t)
+    m, k, n_as = 130, 1024, 4
+    ws = [weights(oracle, t, m, k, seed=50 * t + e) for e in range(n_as)]
+    for n, ids in [(1, np.array([[2, 0]], np.int32)),
+                   (11, np.stack([rng.integers(0, n_as - 1, 11), np.full(11, 1)], axis=1).astype(np.int32)),
+                   (9, np.stack([np.repeat([0, 1, 3], 3), np.repeat([3, 3, 0], 3)], axis=1).astype(np.int32))]:
+        x = make_x(rng, max(n, 8), k)[:n]
+        for id_ in (0, 1):
+            can, got = gpu.lamm_mul_mat_id_host(t, ws, ids, id_, x)
+            assert can
+            want = oracle.mul_mat_id(t, ws, ids, id_, x)
+            assert np.abs(got - want).max() <= tol_c(want, k), f"type {t} n {n} id {id_}"
