@@ -234,6 +234,33 @@ int lammcu_weight_release(lammcu_weight_t w);
 int lammcu_weight_forget(const void *w_host);
 int lammcu_weight_forget_all(void);
 
+/* ---- GGUF weights straight into (sharded) device memory ---------------------------
+ * Replaces gguf_init_from_file + the tensor-data reads of llama.cpp's model loader
+ * (llama.cpp-b2430/ggml.c:20655-20850) for the weights of the path: the file is memory-mapped, the
+ * container parsed (versions 2 and 3, every read bounds-checked), and a 2-D tensor's rows
+ * [row_begin, row_end) are registered from the mapping as they are -- the on-disk block layout is
+ * the device layout.  Errors: LAMMCU_ERR_ARG with the reason in lammcu_last_error().
+ * Strings returned by lammcu_gguf_tensor stay valid until lammcu_gguf_close; weights registered from
+ * a file are keyed by their address in the mapping, so lammcu_weight_forget_all() (or _forget per
+ * tensor) belongs before lammcu_gguf_close.                                                      */
+typedef struct lammcu_gguf *lammcu_gguf_t;
+int      lammcu_gguf_open(const char *path, lammcu_gguf_t *out);
+int      lammcu_gguf_close(lammcu_gguf_t g);
+int64_t  lammcu_gguf_tensor_count(lammcu_gguf_t g);
+uint32_t lammcu_gguf_alignment(lammcu_gguf_t g);          /* general.alignment, default 32 (ggml.h:250) */
+uint64_t lammcu_gguf_data_offset(lammcu_gguf_t g);        /* gguf_get_data_offset */
+/* any out pointer may be NULL.  ne4: 4 entries, unused dims = 1.  nbytes = 0 for a ggml type this
+ * library has no size for (the data pointer is still valid).                                     */
+int      lammcu_gguf_tensor(lammcu_gguf_t g, int64_t i, const char **name, int *type, int *n_dims,
+                            int64_t *ne4, const void **data, uint64_t *nbytes);
+int64_t  lammcu_gguf_find(lammcu_gguf_t g, const char *name);          /* index, or -1 */
+int      lammcu_gguf_get_u32(lammcu_gguf_t g, const char *key, uint32_t *out);
+int      lammcu_gguf_get_f32(lammcu_gguf_t g, const char *key, float *out);
+int64_t  lammcu_gguf_get_str(lammcu_gguf_t g, const char *key, char *buf, int64_t cap); /* length, or -1 */
+/* lammcu_weight_register on rows [row_begin, row_end) of 2-D tensor i (a rank's shard, or all rows) */
+int      lammcu_gguf_upload_rows(lammcu_gguf_t g, int64_t i, int64_t row_begin, int64_t row_end,
+                                 lammcu_weight_t *out);
+
 /* Expert selection of ggml_mul_mat_id (ggml.c:11066-11078 builds the same lists as
  * matrix_row_counts / matrix_rows in its INIT phase): token j goes to expert
  * ids[j * ids_stride + id] (ids_stride in int32 elements).  counts[n_as] receives the number of

@@ -40,6 +40,9 @@ EXPORTS = [
     "lammcu_weight_dev_ptr", "lammcu_weight_rows", "lammcu_mul_mat_host", "lammcu_mul_mat_q_host",
     "lamm_can_mul_mat", "lamm_mul_mat", "lamm_get_opt_level", "lamm_set_writeback_wdata",
     "lammcu_mul_mat_id_plan", "lamm_can_mul_mat_id", "lamm_mul_mat_id",
+    "lammcu_gguf_open", "lammcu_gguf_close", "lammcu_gguf_tensor_count", "lammcu_gguf_alignment",
+    "lammcu_gguf_data_offset", "lammcu_gguf_tensor", "lammcu_gguf_find", "lammcu_gguf_get_u32", "lammcu_gguf_get_f32",
+    "lammcu_gguf_get_str", "lammcu_gguf_upload_rows",
 ]
 
 
@@ -140,6 +143,23 @@ def lib():
     L.lamm_can_mul_mat_id.argtypes = [C.POINTER(GgmlComputeParams), C.POINTER(GgmlTensor)]
     L.lamm_mul_mat_id.restype = None
     L.lamm_mul_mat_id.argtypes = [C.POINTER(GgmlComputeParams), C.POINTER(GgmlTensor)]
+    L.lammcu_gguf_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    L.lammcu_gguf_close.argtypes = [C.c_void_p]
+    L.lammcu_gguf_tensor_count.restype = C.c_int64
+    L.lammcu_gguf_tensor_count.argtypes = [C.c_void_p]
+    L.lammcu_gguf_alignment.restype = C.c_uint32
+    L.lammcu_gguf_alignment.argtypes = [C.c_void_p]
+    L.lammcu_gguf_data_offset.restype = C.c_uint64
+    L.lammcu_gguf_data_offset.argtypes = [C.c_void_p]
+    L.lammcu_gguf_tensor.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_char_p), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                     C.POINTER(C.c_int64), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    L.lammcu_gguf_find.restype = C.c_int64
+    L.lammcu_gguf_find.argtypes = [C.c_void_p, C.c_char_p]
+    L.lammcu_gguf_get_u32.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_uint32)]
+    L.lammcu_gguf_get_f32.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_float)]
+    L.lammcu_gguf_get_str.restype = C.c_int64
+    L.lammcu_gguf_get_str.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int64]
+    L.lammcu_gguf_upload_rows.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.POINTER(C.c_void_p)]
     L.lammcu_mul_mat_id_plan.restype = C.c_int
     L.lammcu_mul_mat_id_plan.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
     L.lamm_set_writeback_wdata.restype = None
@@ -326,3 +346,72 @@ def lamm_mul_mat_id_host(w_type, w_list, ids_np, id_, x_np, nth=1):
             break
         L.lamm_mul_mat_id(C.byref(p), C.byref(dst))
     return can, c
+
+
+class Gguf:
+    """A memory-mapped GGUF file (include/lammcu.h, lammcu_gguf_*).  Parsing needs no device."""
+
+    def __init__(self, path):
+        self.h = C.c_void_p()
+        if lib().lammcu_gguf_open(str(path).encode(), C.byref(self.h)) != 0:
+            raise LammError(f"lammcu_gguf_open({path}): {lib().lammcu_last_error().decode()}")
+
+    def close(self):
+        if self.h:
+            lib().lammcu_gguf_close(self.h)
+            self.h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __len__(self):
+        return int(lib().lammcu_gguf_tensor_count(self.h))
+
+    @property
+    def alignment(self):
+        return int(lib().lammcu_gguf_alignment(self.h))
+
+    @property
+    def data_offset(self):
+        return int(lib().lammcu_gguf_data_offset(self.h))
+
+    def tensor(self, i):
+        """-> (name, ggml type, n_dims, ne[4], bytes as a numpy uint8 COPY)"""
+        import numpy as np
+        name, t, nd = C.c_char_p(), C.c_int(), C.c_int()
+        ne = (C.c_int64 * 4)()
+        data, nb = C.c_void_p(), C.c_uint64()
+        if lib().lammcu_gguf_tensor(self.h, i, C.byref(name), C.byref(t), C.byref(nd), ne, C.byref(data), C.byref(nb)) != 0:
+            raise LammError("lammcu_gguf_tensor: bad index")
+        raw = np.ctypeslib.as_array(C.cast(data, C.POINTER(C.c_uint8)), shape=(nb.value,)).copy() if nb.value else \
+            np.zeros(0, np.uint8)
+        return name.value.decode(errors="replace"), t.value, nd.value, list(ne), raw
+
+    def find(self, name):
+        return int(lib().lammcu_gguf_find(self.h, name.encode()))
+
+    def get_u32(self, key):
+        v = C.c_uint32()
+        return int(v.value) if lib().lammcu_gguf_get_u32(self.h, key.encode(), C.byref(v)) == 0 else None
+
+    def get_f32(self, key):
+        v = C.c_float()
+        return float(v.value) if lib().lammcu_gguf_get_f32(self.h, key.encode(), C.byref(v)) == 0 else None
+
+    def get_str(self, key):
+        n = lib().lammcu_gguf_get_str(self.h, key.encode(), None, 0)
+        if n < 0:
+            return None
+        buf = C.create_string_buffer(n + 1)
+        lib().lammcu_gguf_get_str(self.h, key.encode(), buf, n + 1)
+        return buf.value.decode()
+
+    def upload_rows(self, i, row_begin, row_end):
+        """Register rows [row_begin, row_end) of 2-D tensor i on the device -> weight handle (c_void_p)."""
+        w = C.c_void_p()
+        if lib().lammcu_gguf_upload_rows(self.h, i, row_begin, row_end, C.byref(w)) != 0:
+            raise LammError(f"lammcu_gguf_upload_rows: {lib().lammcu_last_error().decode()}")
+        return w

@@ -100,6 +100,11 @@ def main():
     wq = r.quantize_weights(F16, w)
     np.savez_compressed(os.path.join(OUT, f"next_f16_m{m}_n{n}_k{k}.npz"), w_type=F16, wq=wq, x=x,
                         c_graph=r.graph_mul_mat(F16, wq, x))
+    # a GGUF file written by the reference's own writer (key/values of every kind + 9 tensors)
+    from oracle_lib import Oracle
+    from test_gguf import FIXTURE, fixture_tensors
+    r.gguf_write(FIXTURE, fixture_tensors(Oracle()), alignment=0)
+    print("gguf fixture", os.path.getsize(FIXTURE), "bytes")
 
 
 if __name__ == "__main__":

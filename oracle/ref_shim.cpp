@@ -223,6 +223,48 @@ int ref_graph_mul_mat_id(int w_type, const void *ws, int n_as, const int32_t *id
   return 0;
 }
 
+// A GGUF file written by the reference's own writer (gguf_add_tensor + gguf_write_to_file,
+// ggml.c:21160-21420), with key/values of every scalar kind, a string array and a numeric array
+// ahead of the tensors: the fixture our reader (csrc/lamm_gguf.cpp) is pinned against.
+// ne: [n][2] (ne1 == 0: a 1-D tensor); data[i]: the tensor's bytes; alignment 0 = default (32).
+int ref_gguf_write(const char *path, uint32_t alignment, int n, const char *const *names, const int *types,
+                   const int64_t *ne, const void *const *data) {
+  ref_init();
+  size_t total = 1u << 20;
+  for (int i = 0; i < n; i++)
+    total += ggml_row_size((enum ggml_type)types[i], ne[2 * i]) * (size_t)(ne[2 * i + 1] ? ne[2 * i + 1] : 1) + 1024;
+  struct ggml_init_params ip = {total, nullptr, false};
+  struct ggml_context *ctx = ggml_init(ip);
+  if (!ctx) return -1;
+  struct gguf_context *g = gguf_init_empty();
+  gguf_set_val_str(g, "general.architecture", "llama");
+  if (alignment) gguf_set_val_u32(g, "general.alignment", alignment);
+  gguf_set_val_u32(g, "llama.block_count", 32);
+  gguf_set_val_f32(g, "llama.rope.freq_base", 10000.5f);
+  gguf_set_val_bool(g, "test.flag", true);
+  gguf_set_val_u64(g, "test.u64", 0x123456789abcdefull);
+  gguf_set_val_f64(g, "test.f64", 2.5);
+  gguf_set_val_i8(g, "test.i8", -3);
+  gguf_set_val_u16(g, "test.u16", 65535);
+  const int32_t arr[5] = {1, -2, 3, -4, 5};
+  gguf_set_arr_data(g, "test.arr_i32", GGUF_TYPE_INT32, arr, 5);
+  const char *toks[4] = {"<s>", "</s>", "", "hello world"};
+  gguf_set_arr_str(g, "tokenizer.ggml.tokens", toks, 4);
+  gguf_set_val_str(g, "general.name", "lamm gguf fixture");
+  for (int i = 0; i < n; i++) {
+    struct ggml_tensor *t = ne[2 * i + 1]
+        ? ggml_new_tensor_2d(ctx, (enum ggml_type)types[i], ne[2 * i], ne[2 * i + 1])
+        : ggml_new_tensor_1d(ctx, (enum ggml_type)types[i], ne[2 * i]);
+    ggml_set_name(t, names[i]);
+    memcpy(t->data, data[i], ggml_nbytes(t));
+    gguf_add_tensor(g, t);
+  }
+  gguf_write_to_file(g, path, false);
+  gguf_free(g);
+  ggml_free(ctx);
+  return 0;
+}
+
 // Timing loop after src/la-benchmark-matmult.cpp:322-390: each iteration times
 // one full ggml_graph_compute (plan + INIT quantize + COMPUTE) of graph 1,
 // then runs a second, untimed graph on other weights to disturb the caches.

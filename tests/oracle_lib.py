@@ -251,6 +251,19 @@ class Ref:
         assert rc == 0, rc
         return c
 
+    def gguf_write(self, path, tensors, alignment=0):
+        """tensors: list of (name, ggml type, numpy array [ne1, row bytes] or 1-D bytes, ne0, ne1 (0 = 1-D)) written with
+        the reference's own gguf writer, preceded by a fixed set of key/values of every kind."""
+        n = len(tensors)
+        names = (C.c_char_p * n)(*[t[0].encode() for t in tensors])
+        types = (C.c_int * n)(*[t[1] for t in tensors])
+        arrs = [np.ascontiguousarray(t[2]) for t in tensors]
+        ne = (i64 * (2 * n))(*[v for t in tensors for v in (t[3], t[4])])
+        data = (vp * n)(*[a.ctypes.data for a in arrs])
+        self.L.ref_gguf_write.argtypes = [C.c_char_p, C.c_uint32, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int),
+                                          C.POINTER(i64), C.POINTER(vp)]
+        assert self.L.ref_gguf_write(path.encode(), alignment, n, names, types, ne, data) == 0
+
     def bench(self, t, m, n, k, nth, iters, wq=None, x=None):
         us = (C.c_double * iters)()
         wp = _ptr(np.ascontiguousarray(wq)) if wq is not None else None

@@ -91,3 +91,32 @@ def test_operator_mul_mat_id(gpu, oracle, t):
             assert can
             want = oracle.mul_mat_id(t, ws, ids, id_, x)
             assert np.abs(got - want).max() <= tol_c(want, k), f"type {t} n {n} id {id_}"
+
+
+def test_gguf_rows_to_device_and_mul_mat(gpu, oracle):
+    """SURVEY 8f-4 on the device (the parser itself is CPU-tested in tests/test_gguf.py): rows of the committed
+    GGUF fixture registered straight from the file mapping -- whole tensors and a two-way row shard -- then
+    multiplied through lammcu_mul_mat_host and compared with the oracle on the same bytes."""
+    import ctypes as C
+    from conftest import tol_c
+    from test_gguf import FIXTURE
+    lib = gpu.lib()
+    with gpu.Gguf(FIXTURE) as g:
+        try:
+            for name in ("blk.0.attn_q.weight", "blk.0.attn_k.weight", "blk.0.ffn_down.weight", "blk.0.ffn_up.weight",
+                         "blk.0.ffn_gate.weight"):
+                i = g.find(name)
+                _, t, _, ne, raw = g.tensor(i)
+                k, m = ne[0], ne[1]
+                wq = raw.reshape(m, -1)
+                x = np.random.default_rng(m + k).standard_normal((3, k)).astype(np.float32)
+                want = oracle.mul_mat(t, wq, x)
+                for lo, hi in [(0, m), (0, m // 2), (m // 2, m)]:
+                    w = g.upload_rows(i, lo, hi)
+                    c = np.zeros((3, m), np.float32)
+                    rc = lib.lammcu_mul_mat_host(w, x.ctypes.data_as(C.POINTER(C.c_float)), 3, k,
+                                                 c.ctypes.data_as(C.POINTER(C.c_float)), m, None)
+                    assert rc == 0, lib.lammcu_last_error()
+                    assert np.abs(c[:, lo:hi] - want[:, lo:hi]).max() <= tol_c(want, k), f"{name} rows {lo}:{hi}"
+        finally:
+            lib.lammcu_weight_forget_all()                    # before the mapping goes away
