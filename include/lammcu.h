@@ -257,6 +257,9 @@ int64_t  lammcu_gguf_find(lammcu_gguf_t g, const char *name);          /* index,
 int      lammcu_gguf_get_u32(lammcu_gguf_t g, const char *key, uint32_t *out);
 int      lammcu_gguf_get_f32(lammcu_gguf_t g, const char *key, float *out);
 int64_t  lammcu_gguf_get_str(lammcu_gguf_t g, const char *key, char *buf, int64_t cap); /* length, or -1 */
+/* the bytes of rows [row_begin, row_end) of 1-D / 2-D tensor i in the mapping: one contiguous range */
+int      lammcu_gguf_rows(lammcu_gguf_t g, int64_t i, int64_t row_begin, int64_t row_end,
+                          const void **data, uint64_t *nbytes);
 /* lammcu_weight_register on rows [row_begin, row_end) of 2-D tensor i (a rank's shard, or all rows) */
 int      lammcu_gguf_upload_rows(lammcu_gguf_t g, int64_t i, int64_t row_begin, int64_t row_end,
                                  lammcu_weight_t *out);

@@ -42,7 +42,7 @@ EXPORTS = [
     "lammcu_mul_mat_id_plan", "lamm_can_mul_mat_id", "lamm_mul_mat_id",
     "lammcu_gguf_open", "lammcu_gguf_close", "lammcu_gguf_tensor_count", "lammcu_gguf_alignment",
     "lammcu_gguf_data_offset", "lammcu_gguf_tensor", "lammcu_gguf_find", "lammcu_gguf_get_u32", "lammcu_gguf_get_f32",
-    "lammcu_gguf_get_str", "lammcu_gguf_upload_rows",
+    "lammcu_gguf_get_str", "lammcu_gguf_upload_rows", "lammcu_gguf_rows",
 ]
 
 
@@ -159,6 +159,7 @@ def lib():
     L.lammcu_gguf_get_f32.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_float)]
     L.lammcu_gguf_get_str.restype = C.c_int64
     L.lammcu_gguf_get_str.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int64]
+    L.lammcu_gguf_rows.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     L.lammcu_gguf_upload_rows.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.POINTER(C.c_void_p)]
     L.lammcu_mul_mat_id_plan.restype = C.c_int
     L.lammcu_mul_mat_id_plan.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
@@ -408,6 +409,14 @@ class Gguf:
         buf = C.create_string_buffer(n + 1)
         lib().lammcu_gguf_get_str(self.h, key.encode(), buf, n + 1)
         return buf.value.decode()
+
+    def rows(self, i, row_begin, row_end):
+        """Bytes of rows [row_begin, row_end) of tensor i (a rank's shard) as a numpy uint8 COPY."""
+        import numpy as np
+        data, nb = C.c_void_p(), C.c_uint64()
+        if lib().lammcu_gguf_rows(self.h, i, row_begin, row_end, C.byref(data), C.byref(nb)) != 0:
+            raise LammError("lammcu_gguf_rows: bad tensor or row range")
+        return np.ctypeslib.as_array(C.cast(data, C.POINTER(C.c_uint8)), shape=(nb.value,)).copy()
 
     def upload_rows(self, i, row_begin, row_end):
         """Register rows [row_begin, row_end) of 2-D tensor i on the device -> weight handle (c_void_p)."""

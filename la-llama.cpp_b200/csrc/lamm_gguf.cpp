@@ -283,11 +283,26 @@ int64_t lammcu_gguf_get_str(lammcu_gguf_t g, const char *key, char *buf, int64_t
   return (int64_t)k->len;
 }
 
+int lammcu_gguf_rows(lammcu_gguf_t g, int64_t i, int64_t row_begin, int64_t row_end, const void **data,
+                     uint64_t *nbytes) {
+  if (!g || i < 0 || i >= (int64_t)g->tensors.size()) return LAMMCU_ERR_ARG;
+  const Tensor &t = g->tensors[(size_t)i];
+  const uint64_t rb = row_bytes(t.type, t.ne[0]);
+  if (t.n_dims > 2 || t.ne[2] != 1 || t.ne[3] != 1 || !rb) return LAMMCU_ERR_ARG;
+  if (row_begin < 0 || row_end > t.ne[1] || row_begin >= row_end) return LAMMCU_ERR_ARG;
+  if (data) *data = g->map + g->data_start + t.offset + (uint64_t)row_begin * rb;
+  if (nbytes) *nbytes = (uint64_t)(row_end - row_begin) * rb;
+  return LAMMCU_OK;
+}
+
 int lammcu_gguf_upload_rows(lammcu_gguf_t g, int64_t i, int64_t row_begin, int64_t row_end, lammcu_weight_t *out) {
   if (!g || !out || i < 0 || i >= (int64_t)g->tensors.size()) return LAMMCU_ERR_ARG;
   const Tensor &t = g->tensors[(size_t)i];
-  if (t.n_dims > 2 || t.ne[2] != 1 || t.ne[3] != 1 || !lammcu_type_supported(t.type)) return LAMMCU_ERR_ARG;
-  if (row_begin < 0 || row_end > t.ne[1] || row_begin >= row_end) return LAMMCU_ERR_ARG;
+  if (!lammcu_type_supported(t.type) || lammcu_gguf_rows(g, i, row_begin, row_end, nullptr, nullptr) != LAMMCU_OK) {
+    lamm::set_error("gguf: tensor %lld is not a 2-D weight of a supported type, or rows [%lld, %lld) are outside it",
+                    (long long)i, (long long)row_begin, (long long)row_end);
+    return LAMMCU_ERR_ARG;
+  }
   // the file mapping is the host copy: its rows go to the device as they are (weights are keyed by this address)
   return lammcu_weight_register(g->map + g->data_start + t.offset, t.type, t.ne[1], t.ne[0],
                                 (int64_t)lammcu_row_size(t.type, t.ne[0]), row_begin, row_end, out);

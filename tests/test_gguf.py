@@ -130,6 +130,20 @@ def test_truncated_and_corrupt_files_fail_cleanly(lamm, tmp_path):
     assert n == 9
 
 
+def test_row_ranges_are_contiguous_byte_ranges(lamm):
+    with lamm.Gguf(FIXTURE) as g:
+        for i in range(len(g)):
+            _, t, nd, ne, raw = g.tensor(i)
+            m = ne[1]
+            rb = len(raw) // m
+            for lo, hi in [(0, m), (0, 1), (m - 1, m), (m // 3, m // 3 + max(1, m // 2))]:
+                hi = min(hi, m)
+                assert np.array_equal(g.rows(i, lo, hi), raw[lo * rb:hi * rb])
+            for lo, hi in [(-1, 1), (0, m + 1), (1, 1)]:
+                with pytest.raises(lamm.LammError):
+                    g.rows(i, lo, hi)
+
+
 def test_upload_needs_a_device_and_a_weight_type(lamm):
     """lammcu_gguf_upload_rows: refused for 1-D / unsupported-type tensors and bad row ranges; without a CUDA
     device the registration itself fails loudly (no CPU fallback)."""

@@ -72,6 +72,26 @@ def _worker(rank, world, port, q):
         slices = [b.numpy()[:, :row_shard(m, g, world)[1] - row_shard(m, g, world)[0]] for g, b in enumerate(bufs)]
         full = assemble_rows(slices, m, world)
         ok &= bool(np.array_equal(full, o.mul_mat(t, w, x)))  # rows are independent: bit-identical
+    # each rank takes its row shard straight from the GGUF file (one contiguous byte range of the
+    # mapping); the per-rank results assemble to the whole tensor's result
+    import lamm_b200
+    from test_gguf import FIXTURE
+    with lamm_b200.Gguf(FIXTURE) as g:
+        for name in ("blk.0.attn_q.weight", "blk.0.ffn_down.weight", "blk.0.ffn_up.weight"):
+            i = g.find(name)
+            _, t, _, ne, raw = g.tensor(i)
+            k, m = ne[0], ne[1]
+            x = np.random.default_rng(3).standard_normal((2, k)).astype(np.float32)
+            lo, hi = row_shard(m, rank, world)
+            shard = g.rows(i, lo, hi).reshape(hi - lo, -1)
+            ok &= bool(np.array_equal(shard, raw.reshape(m, -1)[lo:hi]))
+            per = (m + world - 1) // world
+            pad = np.zeros((2, per), np.float32)
+            pad[:, :hi - lo] = o.mul_mat(t, shard, x)
+            bufs = [torch.zeros((2, per)) for _ in range(world)]
+            dist.all_gather(bufs, torch.from_numpy(pad))
+            slices = [b.numpy()[:, :row_shard(m, r, world)[1] - row_shard(m, r, world)[0]] for r, b in enumerate(bufs)]
+            ok &= bool(np.array_equal(assemble_rows(slices, m, world), o.mul_mat(t, raw.reshape(m, -1), x)))
     dist.barrier()
     dist.destroy_process_group()
     q.put((rank, ok))
