@@ -120,8 +120,8 @@ int lamm_get_opt_level(void);
  * op_params[1] = n_as (ggml.c:4616-4656).  Token j is multiplied by expert ids[j][id]; the tokens
  * of one expert are gathered and run as one mul_mat through the same kernels as lamm_mul_mat
  * (a single token, the decode case, goes straight to the decode path).  2-D operands only.
- * NOT YET VERIFIED ON HARDWARE (written after this round's GPU budget was spent); the opt-in check
- * is tests/test_gpu_experimental.py.                                                           */
+ * Host logic verified on CPU (tests/test_host_logic.py); NOT YET RUN ON HARDWARE (written after
+ * this round's GPU budget was spent) -- the opt-in GPU check is tests/test_gpu_experimental.py.  */
 bool lamm_can_mul_mat_id(const struct ggml_compute_params *params,
                          const struct ggml_tensor *dst);
 void lamm_mul_mat_id(const struct ggml_compute_params *params,
