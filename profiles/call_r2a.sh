@@ -32,6 +32,10 @@ for r in (2, 3, 4):
 for key in sorted(rows):
     print(key, " ".join("ring%d=%s" % (r, rows[key].get(r)) for r in (2, 3, 4)))
 P
+LAMM_DECODE_PAIR=1 timeout 100 python bench.py --suite gemv --fused --fmts q4_0,q4_1 \
+  --shapes 4096x4096,11008x4096,4096x11008,32000x4096 > $O/sweep_pair.jsonl 2>&1; echo "pair sweep rc=$?"; cut -c1-120 $O/sweep_pair.jsonl
+LAMM_DECODE_PAIR=1 timeout 60 python bench.py --no-cpu --no-e2e > $O/bench_pair.json 2> $O/bench_pair.err
+python -c "import json;d=json.loads(open('$O/bench_pair.json').read().strip().splitlines()[-1]);print('pair', d['value'], d['roofline']['frac'])"
 for r in 2 3 4; do
   LAMM_DECODE_RING=$r timeout 60 python bench.py --no-cpu --no-e2e > $O/bench_ring$r.json 2> $O/bench_ring$r.err
   python -c "import json;d=json.loads(open('$O/bench_ring$r.json').read().strip().splitlines()[-1]);print('ring $r', d['value'], d['roofline']['frac'])"

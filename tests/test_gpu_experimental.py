@@ -43,11 +43,14 @@ np.savez(sys.argv[1], **out)
 """
 
 
-def _run(ring, path):
+def _run(ring, path, pair=False):
     env = dict(os.environ)
     env.pop("LAMM_DECODE_RING", None)
+    env.pop("LAMM_DECODE_PAIR", None)
     if ring != 2:
         env["LAMM_DECODE_RING"] = str(ring)
+    if pair:
+        env["LAMM_DECODE_PAIR"] = "1"
     subprocess.run([sys.executable, "-c", CHILD % {"root": ROOT}, path], check=True, env=env, timeout=600)
     return dict(np.load(path))
 
@@ -70,6 +73,15 @@ def test_decode_ring_depth(tmp_path, oracle, ring):
         x = np.random.default_rng(m * k).standard_normal((1, k)).astype(np.float32)
         want = oracle.mul_mat(t, w, x)
         assert np.abs(deep[key] - want).max() <= tol_c(want, k)
+
+
+def test_decode_pair_rows(tmp_path):
+    """LAMM_DECODE_PAIR=1 (Q4_0 / Q4_1: two rows share each read of the activation quants): same arithmetic per row,
+    so every result must equal the default path bit for bit."""
+    base = _run(2, str(tmp_path / "base.npz"))
+    pair = _run(2, str(tmp_path / "pair.npz"), pair=True)
+    for key in base:
+        assert np.array_equal(base[key], pair[key]), f"pair: {key} differs"
 
 
 @pytest.mark.parametrize("t", [3, 8, 10, 12, 0])
