@@ -98,7 +98,8 @@ bool lamm_can_mul_mat(const struct ggml_compute_params *params,
                       const struct ggml_tensor *dst);
 
 /* src/loongarch_matmul.cpp:64-143.  Thread ith==0 runs the whole operator on
- * the GPU (weights uploaded once per src0->data); other threads return at
+ * the GPU (leaf weights uploaded once per src0->data; a src0 that is a view, an
+ * op result, an INPUT or a PARAM is uploaded on every call); other threads return at
  * once -- ggml's barrier after COMPUTE (ggml.c:18443-18450) publishes dst.
  * Activations come from src1->data (f32, quantized on the GPU) or, when src1
  * already has the vec-dot type, are uploaded as they are.  A CUDA failure
@@ -120,8 +121,8 @@ int lamm_get_opt_level(void);
  * op_params[1] = n_as (ggml.c:4616-4656).  Token j is multiplied by expert ids[j][id]; the tokens
  * of one expert are gathered and run as one mul_mat through the same kernels as lamm_mul_mat
  * (a single token, the decode case, goes straight to the decode path).  2-D operands only.
- * Host logic verified on CPU (tests/test_host_logic.py); NOT YET RUN ON HARDWARE (written after
- * this round's GPU budget was spent) -- the opt-in GPU check is tests/test_gpu_experimental.py.  */
+ * Host logic verified on CPU (tests/test_host_logic.py), the device path by
+ * tests/test_gpu_parity.py::test_operator_mul_mat_id.                                             */
 bool lamm_can_mul_mat_id(const struct ggml_compute_params *params,
                          const struct ggml_tensor *dst);
 void lamm_mul_mat_id(const struct ggml_compute_params *params,

@@ -221,10 +221,21 @@ typedef struct lammcu_weight *lammcu_weight_t;
 
 /* Upload W once (weights are immutable); rows [row_begin,row_end) only, so a
  * rank can hold its shard.  Keyed by (host pointer, shard) in a registry so a
- * second registration of the same tensor returns the same handle.            */
+ * second registration of the same tensor returns the same handle (one more
+ * reference: pair every register with a lammcu_weight_release).  Registering a
+ * DIFFERENT tensor at the same address evicts the old entry; a holder's handle
+ * to it stays valid until that holder releases it.                           */
 int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K,
                            int64_t w_stride_bytes, int64_t row_begin,
                            int64_t row_end, lammcu_weight_t *out);
+/* The operator's own way in (lamm_mul_mat / lamm_mul_mat_id): the registry keeps the entry, the caller takes no
+ * reference and never releases.  refresh = 0: src0 is immutable model state (a leaf tensor: op == GGML_OP_NONE,
+ * no view_src, not a PARAM) -- a hit serves the resident device copy.  refresh != 0: src0 can change between
+ * calls while its address and shape stay the same (a K/V-cache view, an activation used as src0, a trainable
+ * weight; the reference reads src0->data on every call, src/loongarch_matmul.cpp:131-135) -- the bytes are
+ * uploaded again into the existing device buffer on every call.                                            */
+int lammcu_weight_for_op(const void *w_host, int w_type, int64_t M, int64_t K, int64_t w_stride_bytes,
+                         int refresh, lammcu_weight_t *out);
 int lammcu_weight_lookup(const void *w_host, lammcu_weight_t *out); /* LAMMCU_ERR_ARG if absent */
 int lammcu_weight_release(lammcu_weight_t w);
 /* The registry is keyed by the HOST address of src0->data (weights are immutable model state).  When the

@@ -36,7 +36,7 @@ EXPORTS = [
     "lammcu_blck_size", "lammcu_type_size", "lammcu_vec_dot_type", "lammcu_row_size",
     "lammcu_quantize_act_dev", "lammcu_mul_mat_q_dev", "lammcu_mul_mat_dev", "lammcu_set_gemv_max_n",
     "lammcu_get_gemv_max_n", "lammcu_set_decode_kernel", "lammcu_get_decode_kernel", "lammcu_set_trace", "lammcu_ipc_alloc", "lammcu_ipc_open", "lammcu_ipc_close", "lammcu_ipc_free", "lammcu_memcpy_async",
-    "lammcu_mul_mat_batch_dev", "lammcu_set_gemm_exact", "lammcu_get_gemm_exact", "lammcu_host_profile", "lammcu_set_host_mode", "lammcu_get_host_mode", "lammcu_host_quiesce", "lammcu_set_server_timeouts", "lammcu_server_trace", "lammcu_comm_create", "lammcu_comm_destroy", "lammcu_comm_status", "lammcu_ll_bytes", "lammcu_mul_mat_sharded_dev", "lammcu_mul_mat_sharded_batch_dev", "lammcu_mul_mat_sharded_gemm_dev", "lammcu_ll_unpack_dev", "lammcu_weight_register", "lammcu_weight_lookup", "lammcu_weight_release", "lammcu_weight_forget", "lammcu_weight_forget_all",
+    "lammcu_mul_mat_batch_dev", "lammcu_set_gemm_exact", "lammcu_get_gemm_exact", "lammcu_host_profile", "lammcu_set_host_mode", "lammcu_get_host_mode", "lammcu_host_quiesce", "lammcu_set_server_timeouts", "lammcu_server_trace", "lammcu_comm_create", "lammcu_comm_destroy", "lammcu_comm_status", "lammcu_ll_bytes", "lammcu_mul_mat_sharded_dev", "lammcu_mul_mat_sharded_batch_dev", "lammcu_mul_mat_sharded_gemm_dev", "lammcu_ll_unpack_dev", "lammcu_weight_register", "lammcu_weight_for_op", "lammcu_weight_lookup", "lammcu_weight_release", "lammcu_weight_forget", "lammcu_weight_forget_all",
     "lammcu_weight_dev_ptr", "lammcu_weight_rows", "lammcu_mul_mat_host", "lammcu_mul_mat_q_host",
     "lamm_can_mul_mat", "lamm_mul_mat", "lamm_get_opt_level", "lamm_set_writeback_wdata",
     "lammcu_mul_mat_id_plan", "lamm_can_mul_mat_id", "lamm_mul_mat_id",
@@ -126,6 +126,7 @@ def lib():
                                                   i64, i64, i64, i64, vp]
     L.lammcu_ll_unpack_dev.argtypes = [vp, vp, C.c_int, fp, i64, vp]
     L.lammcu_weight_register.argtypes = [vp, C.c_int, i64, i64, i64, i64, i64, C.POINTER(vp)]
+    L.lammcu_weight_for_op.argtypes = [vp, C.c_int, i64, i64, i64, C.c_int, C.POINTER(vp)]
     L.lammcu_weight_lookup.argtypes = [vp, C.POINTER(vp)]
     L.lammcu_weight_release.argtypes = [vp]
     L.lammcu_weight_forget.argtypes = [vp]
@@ -274,10 +275,12 @@ def make_tensor_2d(ttype, ne0, ne1, data_ptr, nb1=None):
     return t
 
 
-def lamm_mul_mat_host(w_type, w_np, x_np, nth=1, wdata=None, task=TASK_COMPUTE):
+def lamm_mul_mat_host(w_type, w_np, x_np, nth=1, wdata=None, task=TASK_COMPUTE, src0_kind="leaf"):
     """Build ggml_tensor / ggml_compute_params by hand and drive lamm_can_mul_mat +
     lamm_mul_mat exactly as ggml.c:10858-10863 does, once per thread.
     w_np: uint8 [M, row bytes] (or float32 [M, K] for F32); x_np: float32 [N, K].
+    src0_kind: "leaf" (a model weight: op NONE, no view_src), "view" (a view of another tensor, e.g. of
+    the K cache), "op" (the result of a graph node), "param" (a trainable leaf).
     Returns (can, C[N, M] float32)."""
     import numpy as np
     L = lib()
@@ -289,6 +292,16 @@ def lamm_mul_mat_host(w_type, w_np, x_np, nth=1, wdata=None, task=TASK_COMPUTE):
     dst = make_tensor_2d(F32, m, n, c.ctypes.data)
     dst.src[0] = C.pointer(src0)
     dst.src[1] = C.pointer(src1)
+    if src0_kind == "view":
+        parent = make_tensor_2d(w_type, k, m, w_np.ctypes.data, w_np.strides[0])
+        src0.view_src = C.pointer(parent)
+        src0.op = 32                                        # GGML_OP_VIEW (any op != NONE)
+    elif src0_kind == "op":
+        src0.op = 24                                        # a computed tensor (GGML_OP_MUL_MAT)
+    elif src0_kind == "param":
+        src0.flags = 4                                      # GGML_TENSOR_FLAG_PARAM
+    else:
+        assert src0_kind == "leaf"
     can = True
     for ith in range(nth):
         p = GgmlComputeParams(task, ith, nth, wdata.nbytes if wdata is not None else 0,

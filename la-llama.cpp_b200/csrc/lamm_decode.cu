@@ -45,7 +45,6 @@ struct DecodeParams {
   int slots, slot_bytes;
   int x_bytes;          // shared-memory bytes of the staged activations
   unsigned long long *trace;   // optional: 8 globaltimer stamps per CTA (lammcu_set_trace)
-  int l2_ahead;                // 16-warp kernel: rows per warp prefetched into L2 beyond the shared-memory ring
   // sibling batch (16-warp kernel): up to 4 weight matrices of one type, K and row stride that share
   // the activation row (q/k/v, gate/up) form one virtual matrix of M total rows.  Global rows
   // [mc[j-1], mc[j]) belong to matrix j; wb[j] / cb[j] are VIRTUAL bases (pointer minus the rows
@@ -420,10 +419,6 @@ __device__ __forceinline__ void stage_x_row(const DecodeParams &p, uint8_t *xs, 
   }
 }
 
-// L2 prefetch of a 16-byte aligned span (SASS: UBLKPF): no shared memory, no barrier -- lookahead beyond the ring
-__device__ __forceinline__ void bulk_prefetch_l2(const void *gmem_src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem_src), "r"(bytes) : "memory");
-}
 // mbar_wait on a precomputed 32-bit shared address (no generic -> shared conversion on the critical path)
 __device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
   asm volatile(
@@ -740,32 +735,6 @@ __device__ __forceinline__ float dot_unit_sx(const uint32_t (&w)[NW], uint32_t x
   return acc;
 }
 
-// Two rows against ONE read of the lane's activation quants (32-element formats): the 8 x LDS.128 of a unit are
-// 62 % of the dot phase's shared-memory traffic when they are repeated per row (DESIGN d1).  Same arithmetic per
-// row as dot_unit_sx, so the results are bit-identical to the one-row path.
-template <int WT, int NW>
-__device__ __forceinline__ void dot_unit_sx2(const uint32_t (&w0)[NW], const uint32_t (&w1)[NW], uint32_t xaddr,
-                                             uint32_t jstride, const float (&xd)[4], const float (&xs)[4],
-                                             float &r0, float &r1) {
-  float acc0 = 0.f, acc1 = 0.f;
-  uint32_t a[4], b[4];
-#define LAMM_D16_BLOCK2(J)                                                                  \
-  lds128(a, xaddr + (uint32_t)(2 * J) * jstride);                                           \
-  lds128(b, xaddr + (uint32_t)(2 * J + 1) * jstride);                                       \
-  {                                                                                         \
-    const uint32_t xq[8] = {a[0], a[1], a[2], a[3], b[0], b[1], b[2], b[3]};                \
-    acc0 = block_dot8<WT, J, NW>(w0, xq, xd[J], xs[J], acc0);                               \
-    acc1 = block_dot8<WT, J, NW>(w1, xq, xd[J], xs[J], acc1);                               \
-  }
-  LAMM_D16_BLOCK2(0)
-  LAMM_D16_BLOCK2(1)
-  LAMM_D16_BLOCK2(2)
-  LAMM_D16_BLOCK2(3)
-#undef LAMM_D16_BLOCK2
-  r0 = acc0;
-  r1 = acc1;
-}
-
 // ---- K-quants beyond the reference's table: Q3_K / Q4_K / Q5_K / Q6_K x Q8_K ----------
 // Behaviour matched: ggml_vec_dot_q{3,4,5,6}_K_q8_K (ggml-quants.c:6127, 7000, 7609, 8305).  Same lane unit
 // as Q2_K -- half a super-block, 128 consecutive elements = activation slots 0..7 (16 int8 each) -- but
@@ -949,10 +918,10 @@ __device__ __forceinline__ void srv_stamp(const ServerParams *sp, unsigned int j
 // SERVER: the body runs as one job of the resident kernel (decode_server_kernel below): bid / nblk
 // are the job's virtual grid, the activations arrive as {value, tag} pairs staged from pinned host
 // memory by CTA 0, the results go to the `cs` staging row, and the ring barriers are invalidated for the next job.
-// RD: depth of each warp's ring (rows in flight per warp).  2 is the default everywhere; 3 / 4 exist for the
-// single-GPU fused-quantize kernel only (LAMM_DECODE_RING, see launch_decode): with 0.33-0.43 B/weight a
-// K = 4096 row of Q2_K / Q3_K is 1.3-1.8 KB, so two rows per warp keep only ~45-55 KB per SM in flight.
-template <int WT, int XM, bool SERVER, int RD = 2, bool PAIR = false>
+// Each warp keeps RD = 2 rows in flight (its private ring).  Deeper rings (3 / 4 slots where two CTAs still fit on an
+// SM) and a two-rows-per-activation-read dot were measured in round 2 and removed: no format gained from the deeper
+// ring (Q2_K / Q3_K lost 1-8 %, profiles/r2a/sweep_ring*.jsonl) and the row pair spilled (1094 -> 922 tok/s).
+template <int WT, int XM, bool SERVER>
 __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *smem, const int bid, const int nblk,
                                               const ServerParams *sp, const unsigned int job_tag, float *cs) {
   constexpr bool kKX = is_kquant_ext(WT);                        // Q3_K..Q6_K: Q2_K's geometry, own dot
@@ -962,9 +931,7 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
   constexpr int VT = type_info(WT).vec_dot;
   constexpr int NW = kKX ? 4 : (kQ2K ? 11 : DecFmt<WT>::NW);
   constexpr int S = kD16Slots;                                   // rows per loop iteration (one shuffle tree)
-  static_assert(RD >= 2 && RD <= 4 && kD16Warps * RD * 8 <= 512, "ring barriers live in the first 512 bytes");
-  // PAIR (LAMM_DECODE_PAIR, experimental): the two rows of an iteration share each read of the activation quants
-  static_assert(!PAIR || (RD == 2 && !SERVER && !is_kquant_ext(WT) && WT != LAMMCU_TYPE_Q2_K), "PAIR: 32-element formats");
+  constexpr int RD = kD16Slots;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint64_t *full = reinterpret_cast<uint64_t *>(smem) + warp * RD;
   float *part = reinterpret_cast<float *>(smem + 512);          // [RG][2][KS][2]
@@ -1006,14 +973,6 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
     uint64_t *bar = full + s;
     mbar_arrive_expect_tx(bar, bytes);
     bulk_g2s_stream(ring + (size_t)s * p.slot_bytes, reinterpret_cast<const void *>(a0), bytes, bar, pol);
-    // Lookahead beyond the ring: the row this warp will want l2_ahead rows after the ones in shared memory goes
-    // to L2 now, so the ring refill that follows later is an L2 hit (half the latency, no DRAM queueing) and
-    // DRAM keeps streaming while a dependent launch sits in its serial prologue with a full ring.
-    if (!SERVER && p.l2_ahead > 0 && i + p.l2_ahead < n_rows) {
-      const uintptr_t b = row_ptr(row0 + (i + p.l2_ahead) * row_step);
-      const uintptr_t b0 = b & ~(uintptr_t)15;
-      bulk_prefetch_l2(reinterpret_cast<const void *>(b0), (uint32_t)(((b + seg_bytes + 15) & ~(uintptr_t)15) - b0));
-    }
   };
 
   trace_stamp(p.trace, 0);
@@ -1120,47 +1079,17 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
       xd[2] = __uint_as_float(v1[0]); xsc[2] = __uint_as_float(v1[1]); xd[3] = __uint_as_float(v1[2]); xsc[3] = __uint_as_float(v1[3]);
     }
   }
-  // RD == 2: row i0 + s lives in slot s and every slot flips its phase once per iteration.  Deeper rings walk
-  // the slots round-robin (rsl = slot of the next row, bit k of rph = the phase slot k completes next).
-  uint32_t rsl = 0u, rph = 0u;
-  (void)rsl; (void)rph;
+  // row i0 + s lives in slot s and every slot flips its phase once per iteration
   for (int i0 = 0, ph = 0; i0 < n_rows; i0 += S, ph ^= 1) {
     const int nb = min(S, n_rows - i0);
     float acc[S] = {0.f, 0.f};
-    bool paired = false;
-    if constexpr (PAIR) {
-      if (nb == 2) {                                             // warp-uniform
-        paired = true;
-        uint32_t w0[NW], w1[NW];
-        mbar_wait_u32(full_u32, (uint32_t)ph);
-        mbar_wait_u32(full_u32 + 8u, (uint32_t)ph);
-        load_unit<WT, NW>(w0, ring_addr + a15, lane_c);
-        load_unit<WT, NW>(w1, ring_addr + p.slot_bytes + a15, lane_c);
-        unsigned int seen;                                       // both slots read by every lane: hand them back
-        asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %1, 0;\n\tvote.sync.any.pred q, p, 0xffffffff;\n\t"
-                     "selp.u32 %0, 1, 0, q;\n\t}" : "=r"(seen) : "r"(w0[NW - 1] | w1[NW - 1]) : "memory");
-        (void)seen;
-        if (lane == 0) {
-          if (i0 + 2 < n_rows) issue(i0 + 2, 0, pol);
-          if (i0 + 3 < n_rows) issue(i0 + 3, 1, pol);
-        }
-        dot_unit_sx2<WT, NW>(w0, w1, xaddr, jstride, xd, xsc, acc[0], acc[1]);
-      }
-    }
 #pragma unroll
     for (int s = 0; s < S; s++) {
-      if (s < nb && !paired) {
+      if (s < nb) {
         uint32_t w[NW];
-        uint32_t sl = (uint32_t)s;                               // this row's ring slot
+        const uint32_t sl = (uint32_t)s;                         // this row's ring slot
         if (i0 == 0 && s == 0) trace_stamp(p.trace, 5);          // lane setup done, about to wait for the weights
-        if constexpr (RD == 2) {
-          mbar_wait_u32(full_u32 + 8u * s, (uint32_t)ph);
-        } else {
-          sl = rsl;
-          mbar_wait_u32(full_u32 + 8u * sl, (rph >> sl) & 1u);
-          rph ^= 1u << sl;
-          rsl = (sl + 1u == (uint32_t)RD) ? 0u : sl + 1u;
-        }
+        mbar_wait_u32(full_u32 + 8u * s, (uint32_t)ph);
         if (i0 == 0 && s == 0) trace_stamp(p.trace, 6);          // first weights landed
         // SERVER rows step by RG: Q2_K rows (84 B per super-block) then differ in their 16-byte phase; so do
         // Q3_K / Q6_K rows (110 / 210 B per super-block) whenever RG * kb is odd
@@ -1220,10 +1149,10 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
   trace_stamp(p.trace, 4);
 }
 
-template <int WT, int XM, int RD = 2, bool PAIR = false>
+template <int WT, int XM>
 __global__ void __launch_bounds__(kD16Warps * 32, 2) decode16_kernel(const DecodeParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
-  decode16_body<WT, XM, false, RD, PAIR>(p, smem, (int)blockIdx.x, (int)gridDim.x, nullptr, 0u, nullptr);
+  decode16_body<WT, XM, false>(p, smem, (int)blockIdx.x, (int)gridDim.x, nullptr, 0u, nullptr);
 }
 
 // ---- the resident decode server --------------------------------------------------------------
@@ -1392,11 +1321,11 @@ static int launch_decode_t(const DecodeParams &p, int grid, int threads, int sme
   return launch_decode_tt<WT, XF32, kDecMaxThreads>(p, grid, threads, smem, st);
 }
 
-template <int WT, int XF32, int RD = 2, bool PAIR = false>
+template <int WT, int XF32>
 static int launch_decode16_t(const DecodeParams &p, int grid, int threads, int smem, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(decode16_kernel<WT, XF32, RD, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(decode16_kernel<WT, XF32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          kDecSmemMax);
     if (e != cudaSuccess) {
       set_error("decode16: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -1414,7 +1343,7 @@ static int launch_decode16_t(const DecodeParams &p, int grid, int threads, int s
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, decode16_kernel<WT, XF32, RD, PAIR>, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, decode16_kernel<WT, XF32>, p);
   g_launch_count++;
   if (e != cudaSuccess) {
     set_error("decode16 launch (type %d, smem %d): %s", WT, smem, cudaGetErrorString(e));
@@ -1423,28 +1352,20 @@ static int launch_decode16_t(const DecodeParams &p, int grid, int threads, int s
   return LAMMCU_OK;
 }
 
-template <int XF32, int RD = 2>
+template <int XF32>
 static int launch_decode16_x(int w_type, const DecodeParams &p, int grid, int threads, int smem, cudaStream_t st) {
   switch (w_type) {
-  case LAMMCU_TYPE_Q4_0: return launch_decode16_t<LAMMCU_TYPE_Q4_0, XF32, RD>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q4_1: return launch_decode16_t<LAMMCU_TYPE_Q4_1, XF32, RD>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q5_0: return launch_decode16_t<LAMMCU_TYPE_Q5_0, XF32, RD>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q5_1: return launch_decode16_t<LAMMCU_TYPE_Q5_1, XF32, RD>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q8_0: return launch_decode16_t<LAMMCU_TYPE_Q8_0, XF32, RD>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q3_K: return launch_decode16_t<LAMMCU_TYPE_Q3_K, XF32, RD>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q4_K: return launch_decode16_t<LAMMCU_TYPE_Q4_K, XF32, RD>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q5_K: return launch_decode16_t<LAMMCU_TYPE_Q5_K, XF32, RD>(p, grid, threads, smem, st);
-  case LAMMCU_TYPE_Q6_K: return launch_decode16_t<LAMMCU_TYPE_Q6_K, XF32, RD>(p, grid, threads, smem, st);
-  default:               return launch_decode16_t<LAMMCU_TYPE_Q2_K, XF32, RD>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q4_0: return launch_decode16_t<LAMMCU_TYPE_Q4_0, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q4_1: return launch_decode16_t<LAMMCU_TYPE_Q4_1, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q5_0: return launch_decode16_t<LAMMCU_TYPE_Q5_0, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q5_1: return launch_decode16_t<LAMMCU_TYPE_Q5_1, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q8_0: return launch_decode16_t<LAMMCU_TYPE_Q8_0, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q3_K: return launch_decode16_t<LAMMCU_TYPE_Q3_K, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q4_K: return launch_decode16_t<LAMMCU_TYPE_Q4_K, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q5_K: return launch_decode16_t<LAMMCU_TYPE_Q5_K, XF32>(p, grid, threads, smem, st);
+  case LAMMCU_TYPE_Q6_K: return launch_decode16_t<LAMMCU_TYPE_Q6_K, XF32>(p, grid, threads, smem, st);
+  default:               return launch_decode16_t<LAMMCU_TYPE_Q2_K, XF32>(p, grid, threads, smem, st);
   }
-}
-
-// LAMM_DECODE_PAIR (experimental, not yet measured): Q4_0 / Q4_1, fused f32 activations, ring depth 2.  Two rows'
-// weight words live at once is 36 / 40 registers: ptxas spills 36 / 80 bytes at the 64 registers two-CTA residency
-// allows (Q5_0 96, Q5_1 164, Q8_0 176 bytes: those formats are not offered).
-static int launch_decode16_pair(int w_type, const DecodeParams &p, int grid, int threads, int smem, cudaStream_t st) {
-  if (w_type == LAMMCU_TYPE_Q4_0) return launch_decode16_t<LAMMCU_TYPE_Q4_0, 1, 2, true>(p, grid, threads, smem, st);
-  return launch_decode16_t<LAMMCU_TYPE_Q4_1, 1, 2, true>(p, grid, threads, smem, st);
 }
 
 template <bool XF32>
@@ -1619,21 +1540,6 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   p.x_bytes = (p.x_bytes + 127) & ~127;
   p.slots = (variant == 16) ? kD16Slots : kDecMaxSlots;
   int smem = kDecCtrl + p.x_bytes + warps * p.slots * p.slot_bytes;
-  // Experimental (off by default, NOT yet measured on hardware): a deeper ring per warp for the plain
-  // single-GPU fused-quantize launch, where it still leaves room for two CTAs per SM (the next launch's
-  // prefetch).  LAMM_DECODE_RING=3|4.
-  static const int ring_env = [] {
-    const char *e = getenv("LAMM_DECODE_RING");
-    const int v = e ? atoi(e) : 2;
-    return (v == 3 || v == 4) ? v : 2;
-  }();
-  int ring = 2;
-  if (variant == 16 && ring_env > 2 && x && !sh) {
-    for (int r = ring_env; r > 2; r--) {
-      const int need = kDecCtrl + p.x_bytes + warps * r * p.slot_bytes;
-      if (2 * (need + 1024) <= 228 * 1024) { ring = r;  smem = need;  p.slots = r;  break; }
-    }
-  }
   if (smem > kDecSmemMax) {
     set_error("decode: K=%lld too large for shared memory", (long long)K);
     return LAMMCU_ERR_SHAPE;
@@ -1647,19 +1553,8 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   if (grid > need) grid = (int)need;
   if (sh) grid = sm_count_cached();                // fixed grid: the arrival-ticket tag divides by it
   p.trace = next_trace_slot(grid);
-  static const int l2_ahead = [] {
-    const char *e = getenv("LAMM_DECODE_L2_AHEAD");          // tuning knob: rows per warp prefetched into L2 (0 = off)
-    const int v = e ? atoi(e) : 0;
-    return v < 0 ? 0 : (v > 16 ? 16 : v);
-  }();
-  p.l2_ahead = l2_ahead;
   if (variant == 16) {
     if (xm == 2) return launch_decode16_x<2>(w_type, p, grid, warps * 32, smem, st);
-    static const int pair_env = [] { const char *e = getenv("LAMM_DECODE_PAIR"); return e ? atoi(e) : 0; }();
-    if (pair_env && ring == 2 && x && !sh && (w_type == LAMMCU_TYPE_Q4_0 || w_type == LAMMCU_TYPE_Q4_1))
-      return launch_decode16_pair(w_type, p, grid, warps * 32, smem, st);
-    if (ring == 3) return launch_decode16_x<1, 3>(w_type, p, grid, warps * 32, smem, st);
-    if (ring == 4) return launch_decode16_x<1, 4>(w_type, p, grid, warps * 32, smem, st);
     return xm ? launch_decode16_x<1>(w_type, p, grid, warps * 32, smem, st)
               : launch_decode16_x<0>(w_type, p, grid, warps * 32, smem, st);
   }

@@ -50,6 +50,14 @@ bool is_contiguous(const ggml_tensor *t) {
          t->nb[2] == t->nb[1] * t->ne[1] && t->nb[3] == t->nb[2] * t->ne[2];
 }
 
+// Only immutable model state may be served from the resident device copy.  ggml also hands the hook a
+// mutable src0 -- a view of the K/V cache (-ctk q8_0 ...), an F32 activation or KV tensor as src0, a
+// trainable weight -- whose address and shape do not change between calls: those are uploaded every call.
+bool is_leaf_weight(const ggml_tensor *t) {
+  return t->op == 0 /* GGML_OP_NONE */ && t->view_src == nullptr && t->grad == nullptr &&
+         (t->flags & (1 | 4)) == 0 /* not GGML_TENSOR_FLAG_INPUT / _PARAM (ggml.h:532-534) */;
+}
+
 [[noreturn]] void die(const char *what) {
   std::fprintf(stderr, "lamm_mul_mat: %s: %s\n", what, lammcu_last_error());
   std::abort();
@@ -108,7 +116,7 @@ void lamm_mul_mat(const struct ggml_compute_params *params, struct ggml_tensor *
       const char *a = (const char *)src0->data + (i12 / r2) * nb02 + (i13 / r3) * nb03;
       float *c = (float *)((char *)dst->data + i12 * nb2 + i13 * nb3);
       lammcu_weight_t w;
-      if (lammcu_weight_register(a, src0->type, ne01, ne00, (int64_t)nb01, 0, ne01, &w) != LAMMCU_OK)
+      if (lammcu_weight_for_op(a, src0->type, ne01, ne00, (int64_t)nb01, is_leaf_weight(src0) ? 0 : 1, &w) != LAMMCU_OK)
         die("weight upload");
       const char *b = (const char *)src1->data + i12 * nb12 + i13 * nb13;
       if (src1_quantized) {
@@ -190,7 +198,8 @@ void lamm_mul_mat_id(const struct ggml_compute_params *params, struct ggml_tenso
     if (!cnt) continue;
     const ggml_tensor *a = dst->src[2 + e];
     lammcu_weight_t w;
-    if (lammcu_weight_register(a->data, a->type, M, K, (int64_t)a->nb[1], 0, M, &w) != LAMMCU_OK) die("weight upload");
+    if (lammcu_weight_for_op(a->data, a->type, M, K, (int64_t)a->nb[1], is_leaf_weight(a) ? 0 : 1, &w) != LAMMCU_OK)
+      die("weight upload");
     const int64_t *rows = order.data() + at;
     at += cnt;
     // the expert's tokens are consecutive rows of src1 / dst: no gather

@@ -75,9 +75,20 @@ unsigned int *next_sched_slot() {
   return g_dev.sched + 2 * i;
 }
 
+// The current CUDA device is per host thread: ggml calls the operator from its worker pool, an application may
+// call from any thread.  Every entry point binds the calling thread to the library's device once.
+static thread_local bool t_bound = false;
 static int ensure_init() {
-  if (g_dev.inited) return LAMMCU_OK;
-  return lammcu_init(-1);
+  if (!g_dev.inited) {
+    int rc = lammcu_init(-1);
+    if (rc) return rc;
+  }
+  if (!t_bound) {
+    cudaError_t e = cudaSetDevice(g_dev.device);
+    if (e != cudaSuccess) { set_error("cudaSetDevice(%d): %s", g_dev.device, cudaGetErrorString(e)); return LAMMCU_ERR_CUDA; }
+    t_bound = true;
+  }
+  return LAMMCU_OK;
 }
 
 static int grow(void **p, size_t *have, size_t need, bool pinned) {
@@ -143,9 +154,17 @@ struct lammcu_weight {
   int64_t stride;       // bytes between device rows (packed)
   void *dev;
   size_t bytes;
-  int refs;
+  int refs;             // explicit holders (lammcu_weight_register); entries made by the operator path have 0
+  bool detached;        // evicted from the registry while held: freed by the last lammcu_weight_release
 };
 static std::map<const void *, lammcu_weight *> g_weights;
+
+// drop an entry from the registry (g_mu held): freed now, or by its last holder's release
+static void evict_entry(lammcu_weight *h) {
+  if (h->refs > 0) { h->detached = true; return; }
+  cudaFree(h->dev);
+  delete h;
+}
 
 extern "C" {
 
@@ -645,9 +664,11 @@ int lammcu_mul_mat_batch_dev(int w_type, int count, const void *const *w_dev, in
 }
 
 // ---- host operands --------------------------------------------------------------
-int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K,
-                           int64_t w_stride, int64_t row_begin, int64_t row_end,
-                           lammcu_weight_t *out) {
+// hold: 1 = an explicit registration (the caller gets a reference and releases it), 0 = the operator path (the
+// registry owns the entry).  refresh: the host bytes may have changed since the last call (src0 is not a leaf
+// weight): re-upload them into the existing device copy instead of trusting it.
+static int weight_get(const void *w_host, int w_type, int64_t M, int64_t K, int64_t w_stride, int64_t row_begin,
+                      int64_t row_end, int hold, int refresh, lammcu_weight_t *out) {
   int rc = ensure_init();
   if (rc) return rc;
   if (!w_host || !out) { set_error("weight_register: NULL argument"); return LAMMCU_ERR_ARG; }
@@ -660,25 +681,35 @@ int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K,
   }
   const size_t rs = lammcu_row_size(w_type, K);
   if ((size_t)w_stride < rs) { set_error("weight_register: row stride smaller than a row"); return LAMMCU_ERR_SHAPE; }
+  const int64_t rows = row_end - row_begin;
   std::lock_guard<std::mutex> lk(g_mu);
   auto it = g_weights.find(w_host);
   if (it != g_weights.end()) {
     lammcu_weight *h = it->second;
     if (h->type == w_type && h->M == M && h->K == K && h->row_begin == row_begin && h->row_end == row_end) {
-      h->refs++;
+      if (refresh) {
+        server_stop();                                 // a resident instance may still be reading the old bytes
+        cudaError_t e = cudaStreamSynchronize(g_dev.stream);
+        if (e == cudaSuccess)
+          e = cudaMemcpy2D(h->dev, rs, (const char *)w_host + row_begin * w_stride, (size_t)w_stride, rs, (size_t)rows,
+                           cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { set_error("weight refresh: %s", cudaGetErrorString(e)); return LAMMCU_ERR_CUDA; }
+      }
+      if (hold) h->refs++;
       *out = h;
       return LAMMCU_OK;
     }
-    // same address, different tensor: the old one is stale
-    cudaFree(h->dev);
-    delete h;
+    // same address, different tensor: the old one is stale (a holder of its handle keeps it alive until release)
+    server_stop();
+    cudaStreamSynchronize(g_dev.stream);
     g_weights.erase(it);
+    evict_entry(h);
   }
   lammcu_weight *h = new lammcu_weight();
   h->host = w_host; h->type = w_type; h->M = M; h->K = K;
   h->row_begin = row_begin; h->row_end = row_end;
-  h->stride = (int64_t)rs; h->refs = 1;
-  const int64_t rows = row_end - row_begin;
+  h->stride = (int64_t)rs; h->refs = hold ? 1 : 0; h->detached = false;
   h->bytes = rs * (size_t)rows;
   // +256: the GEMV's bulk copies round every row span out to 16-byte boundaries
   cudaError_t e = cudaMalloc(&h->dev, h->bytes + 256);
@@ -704,6 +735,17 @@ int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K,
   return LAMMCU_OK;
 }
 
+int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K,
+                           int64_t w_stride, int64_t row_begin, int64_t row_end,
+                           lammcu_weight_t *out) {
+  return weight_get(w_host, w_type, M, K, w_stride, row_begin, row_end, 1, 0, out);
+}
+
+int lammcu_weight_for_op(const void *w_host, int w_type, int64_t M, int64_t K, int64_t w_stride, int refresh,
+                         lammcu_weight_t *out) {
+  return weight_get(w_host, w_type, M, K, w_stride, 0, M, 0, refresh, out);
+}
+
 int lammcu_weight_lookup(const void *w_host, lammcu_weight_t *out) {
   std::lock_guard<std::mutex> lk(g_mu);
   auto it = g_weights.find(w_host);
@@ -715,8 +757,15 @@ int lammcu_weight_lookup(const void *w_host, lammcu_weight_t *out) {
 int lammcu_weight_release(lammcu_weight_t w) {
   if (!w) return LAMMCU_ERR_ARG;
   std::lock_guard<std::mutex> lk(g_mu);
+  if (w->detached) {                                   // evicted while held (same address, new tensor; forget)
+    if (w->refs <= 0) { set_error("weight_release: bad handle"); return LAMMCU_ERR_ARG; }
+    if (--w->refs > 0) return LAMMCU_OK;
+    cudaFree(w->dev);
+    delete w;
+    return LAMMCU_OK;
+  }
   auto it = g_weights.find(w->host);
-  if (it == g_weights.end() || it->second != w) { set_error("weight_release: bad handle"); return LAMMCU_ERR_ARG; }
+  if (it == g_weights.end() || it->second != w || w->refs <= 0) { set_error("weight_release: bad handle"); return LAMMCU_ERR_ARG; }
   if (--w->refs > 0) return LAMMCU_OK;
   server_stop();
   cudaStreamSynchronize(g_dev.stream);

@@ -167,6 +167,16 @@ static ref_graph *graph_new(int w_type, const void *w, const float *x, int64_t M
   return rg;
 }
 
+// When this shim is linked against liblammcu.so instead of the reference's loongarch_matmul.o (make ref_b200:
+// the real ggml.c -DLA_LLAMA driving the B200 operator through its own hook), every graph copies its weights
+// into a fresh ggml context, so a freed context's addresses come back with other bytes: tell the operator's
+// weight registry when a "model" goes away, as an application does in llama_free_model.  Absent (weak, NULL)
+// in the plain reference build.
+extern int lammcu_weight_forget_all(void) __attribute__((weak));
+extern void lamm_set_writeback_wdata(int) __attribute__((weak));
+static void model_freed(void) { if (lammcu_weight_forget_all) lammcu_weight_forget_all(); }
+int ref_is_b200(void) { return lammcu_weight_forget_all ? 1 : 0; }
+
 static void graph_compute(ref_graph *rg, int nth) {
   struct ggml_cplan plan = ggml_graph_plan(rg->g, nth);
   if (plan.work_size > 0) {
@@ -184,6 +194,25 @@ int ref_graph_mul_mat(int w_type, const void *w, const float *x, float *c,
   if (!rg) return -1;
   graph_compute(rg, nth);
   memcpy(c, rg->c->data, (size_t)M * N * 4);
+  model_freed();
+  ggml_free(rg->ctx);
+  delete rg;
+  return 0;
+}
+
+// The same graph, also returning what is in the plan's work buffer afterwards (params->wdata: the quantized
+// activations of ggml.c:10865-10887, packed at row_size stride).  With the B200 operator and its write-back
+// hook enabled these are the GPU's Xq bytes; `reps` > 1 recomputes the same graph (resident weights).
+int ref_graph_mul_mat_wdata(int w_type, const void *w, const float *x, float *c, void *wdata_out, size_t wdata_cap,
+                            int64_t M, int64_t N, int64_t K, int nth, int reps, int writeback) {
+  ref_graph *rg = graph_new(w_type, w, x, M, N, K);
+  if (!rg) return -1;
+  if (lamm_set_writeback_wdata) lamm_set_writeback_wdata(writeback);
+  for (int r = 0; r < (reps < 1 ? 1 : reps); r++) graph_compute(rg, nth);
+  if (lamm_set_writeback_wdata) lamm_set_writeback_wdata(0);
+  memcpy(c, rg->c->data, (size_t)M * N * 4);
+  if (wdata_out) memcpy(wdata_out, rg->work.data(), rg->work.size() < wdata_cap ? rg->work.size() : wdata_cap);
+  model_freed();
   ggml_free(rg->ctx);
   delete rg;
   return 0;
@@ -219,6 +248,7 @@ int ref_graph_mul_mat_id(int w_type, const void *ws, int n_as, const int32_t *id
   plan.work_data = work.data();
   ggml_graph_compute(g, &plan);
   memcpy(c, tc->data, (size_t)M * N * 4);
+  model_freed();
   ggml_free(ctx);
   return 0;
 }
@@ -290,6 +320,7 @@ int ref_bench_mul_mat(int w_type, const void *w, const float *x, int64_t M,
     usec_out[i] = (double)(ggml_time_us() - t0);
     graph_compute(g2, nth);
   }
+  model_freed();
   ggml_free(g1->ctx); ggml_free(g2->ctx);
   delete g1; delete g2;
   return 0;

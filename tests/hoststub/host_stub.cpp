@@ -36,6 +36,13 @@ int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K,
   *out = w;
   return LAMMCU_OK;
 }
+long g_refresh = 0;
+int lammcu_weight_for_op(const void *w_host, int w_type, int64_t M, int64_t K, int64_t stride, int refresh,
+                         lammcu_weight_t *out) {
+  g_refresh += refresh ? 1 : 0;
+  return lammcu_weight_register(w_host, w_type, M, K, stride, 0, M, out);
+}
+long stub_refreshes(void) { return g_refresh; }
 int lammcu_mul_mat_host(lammcu_weight_t w, const float *x, int64_t N, int64_t ldx, float *c, int64_t ldc, void *xq_out) {
   g_calls++;
   g_rows += N;
@@ -54,7 +61,7 @@ int lammcu_mul_mat_q_host(lammcu_weight_t w, const void *xq, int64_t xq_stride, 
 long stub_calls(void) { return g_calls; }
 long stub_rows(void) { return g_rows; }
 void stub_reset(void) {
-  g_calls = g_rows = 0;
+  g_calls = g_rows = g_refresh = 0;
   for (lammcu_weight *w : g_weights) delete w;
   g_weights.clear();
 }

@@ -166,14 +166,17 @@ class Oracle:
 
 class Ref:
     """The real reference (oracle/_ref/libref.so)."""
+    LIBNAME = "libref.so"
 
-    @staticmethod
-    def available():
-        return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libref.so"))
+    @classmethod
+    def available(cls):
+        return os.path.exists(os.path.join(ORACLE_DIR, "_ref", cls.LIBNAME))
 
     def __init__(self):
-        L = self.L = C.CDLL(os.path.join(ORACLE_DIR, "_ref", "libref.so"))
+        L = self.L = C.CDLL(os.path.join(ORACLE_DIR, "_ref", self.LIBNAME))
         L.ref_init()
+        if hasattr(L, "ref_graph_mul_mat_wdata"):
+            L.ref_graph_mul_mat_wdata.argtypes = [C.c_int, vp, fp, fp, vp, C.c_size_t, i64, i64, i64, C.c_int, C.c_int, C.c_int]
         L.ref_quantize_act.argtypes = [C.c_int, fp, i64, vp, i64, i64]
         L.ref_quantize_act_native.argtypes = L.ref_quantize_act.argtypes
         L.ref_quantize_weights.argtypes = [C.c_int, fp, vp, i64, i64]
@@ -239,6 +242,18 @@ class Ref:
         assert self.L.ref_graph_mul_mat(t, _ptr(wq), _fptr(x), _fptr(c), m, n, k, nth) == 0
         return c
 
+    def graph_mul_mat_wdata(self, t, wq, x, nth=1, reps=1, writeback=0):
+        """As graph_mul_mat; also returns the first N * row_size(vec_dot, K) bytes of the plan's work buffer
+        (params->wdata: the quantized activations) as they are after the last compute."""
+        wq = np.ascontiguousarray(wq)
+        x = np.ascontiguousarray(x, np.float32)
+        m, (n, k) = wq.shape[0], x.shape
+        c = np.zeros((n, m), np.float32)
+        wd = np.zeros((n, row_size(vec_dot_of(t), k) if t != F32 else 4), np.uint8)
+        assert self.L.ref_graph_mul_mat_wdata(t, _ptr(wq), _fptr(x), _fptr(c), _ptr(wd), wd.nbytes, m, n, k, nth, reps,
+                                              writeback) == 0
+        return c, wd
+
     def graph_mul_mat_id(self, t, wqs, ids, id_, x, nth=1):
         """ggml_mul_mat_id through ggml_graph_compute (stock ggml; lamm's hook is not on this op)."""
         ws = np.ascontiguousarray(np.stack([np.ascontiguousarray(w) for w in wqs]))
@@ -270,3 +285,14 @@ class Ref:
         xp = _fptr(np.ascontiguousarray(x, np.float32)) if x is not None else None
         assert self.L.ref_bench_mul_mat(t, wp, xp, m, n, k, nth, iters, us) == 0
         return list(us)
+
+
+class RefB200(Ref):
+    """oracle/_ref/libref_b200.so: the reference's own ggml.c (-DLA_LLAMA) + ref_shim.cpp linked against
+    la-llama.cpp_b200/liblammcu.so instead of the reference's loongarch_matmul.o (oracle/Makefile, ref_b200).
+    ggml_graph_compute's real thread pool calls the B200 operator through the hook at ggml.c:10858-10863."""
+    LIBNAME = "libref_b200.so"
+
+    def __init__(self):
+        super().__init__()
+        assert self.L.ref_is_b200() == 1, "libref_b200.so is not linked against liblammcu.so"

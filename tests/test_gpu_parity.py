@@ -384,3 +384,53 @@ def test_decode_batch_siblings(gpu, oracle, t, k, ms):
         want = oracle.mul_mat(t, w, x)
         assert np.array_equal(got, sep), f"batch differs from separate launch (M={m})"
         assert np.abs(got - want).max() <= tol_c(want, k)
+
+
+@pytest.mark.parametrize("t", [3, 8, 10, 12, 0])
+def test_operator_mul_mat_id(gpu, oracle, t):
+    """lamm_can_mul_mat_id + lamm_mul_mat_id against
+    orc_mul_mat_id, which is pinned to stock ggml's ggml_mul_mat_id graph (tests/test_oracle_vs_ref.py): one
+    token (decode), scattered tokens (gather / scatter), consecutive tokens per expert, an expert nobody picks."""
+    from conftest import make_x, tol_c
+    from test_gpu_parity import weights
+    rng = np.random.default_rng(300 + t)
+    m, k, n_as = 130, 1024, 4
+    ws = [weights(oracle, t, m, k, seed=50 * t + e) for e in range(n_as)]
+    for n, ids in [(1, np.array([[2, 0]], np.int32)),
+                   (11, np.stack([rng.integers(0, n_as - 1, 11), np.full(11, 1)], axis=1).astype(np.int32)),
+                   (9, np.stack([np.repeat([0, 1, 3], 3), np.repeat([3, 3, 0], 3)], axis=1).astype(np.int32))]:
+        x = make_x(rng, max(n, 8), k)[:n]
+        for id_ in (0, 1):
+            can, got = gpu.lamm_mul_mat_id_host(t, ws, ids, id_, x)
+            assert can
+            want = oracle.mul_mat_id(t, ws, ids, id_, x)
+            assert np.abs(got - want).max() <= tol_c(want, k), f"type {t} n {n} id {id_}"
+
+
+def test_gguf_rows_to_device_and_mul_mat(gpu, oracle):
+    """SURVEY 8f-4 on the device (the parser itself is CPU-tested in tests/test_gguf.py): rows of the committed
+    GGUF fixture registered straight from the file mapping -- whole tensors and a two-way row shard -- then
+    multiplied through lammcu_mul_mat_host and compared with the oracle on the same bytes."""
+    import ctypes as C
+    from conftest import tol_c
+    from test_gguf import FIXTURE
+    lib = gpu.lib()
+    with gpu.Gguf(FIXTURE) as g:
+        try:
+            for name in ("blk.0.attn_q.weight", "blk.0.attn_k.weight", "blk.0.ffn_down.weight", "blk.0.ffn_up.weight",
+                         "blk.0.ffn_gate.weight"):
+                i = g.find(name)
+                _, t, _, ne, raw = g.tensor(i)
+                k, m = ne[0], ne[1]
+                wq = raw.reshape(m, -1)
+                x = np.random.default_rng(m + k).standard_normal((3, k)).astype(np.float32)
+                want = oracle.mul_mat(t, wq, x)
+                for lo, hi in [(0, m), (0, m // 2), (m // 2, m)]:
+                    w = g.upload_rows(i, lo, hi)
+                    c = np.zeros((3, m), np.float32)
+                    rc = lib.lammcu_mul_mat_host(w, x.ctypes.data_as(C.POINTER(C.c_float)), 3, k,
+                                                 c.ctypes.data_as(C.POINTER(C.c_float)), m, None)
+                    assert rc == 0, lib.lammcu_last_error()
+                    assert np.abs(c[:, lo:hi] - want[:, lo:hi]).max() <= tol_c(want, k), f"{name} rows {lo}:{hi}"
+        finally:
+            lib.lammcu_weight_forget_all()                    # before the mapping goes away

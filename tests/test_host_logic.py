@@ -35,6 +35,7 @@ def host(lamm):
         getattr(L, name).argtypes = [P, T]
     L.stub_calls.restype = C.c_long
     L.stub_rows.restype = C.c_long
+    L.stub_refreshes.restype = C.c_long
     L.stub_reset()
     return L
 
@@ -119,6 +120,38 @@ def test_gates(lamm, host, oracle):
     assert not run(lamm, host, node(kk=k - 32 + 16))                    # K % QK
     assert not run(lamm, host, node(dst_type=F16))                      # :34
     assert not run(lamm, host, node(x_type=Q8_0))                       # Q4_1 pairs with Q8_1, not Q8_0
+
+
+def test_only_leaf_weights_are_served_from_the_resident_copy(lamm, host, oracle):
+    """ggml also hands the hook a MUTABLE src0 whose address and shape stay the same between calls: a view of the
+    K/V cache, an activation or op result used as src0, a trainable (PARAM) or INPUT leaf.  The reference reads
+    src0->data on every call (src/loongarch_matmul.cpp:131-135); here only a true leaf weight (op NONE, no
+    view_src, no grad, neither INPUT nor PARAM) may hit the resident device copy -- everything else asks the
+    registry for a refresh on every call."""
+    rng = np.random.default_rng(5)
+    m, n, k = 4, 2, 256
+    w = oracle.quantize_weights(Q8_0, rng.standard_normal((m, k)).astype(np.float32))
+    x = rng.standard_normal((n, k)).astype(np.float32)
+    c = np.zeros((n, m), np.float32)
+    parent = tensor(lamm, Q8_0, [k, m], [lamm.type_size(Q8_0), row_size(Q8_0, k)], w)
+
+    def refreshes(**kw):
+        s0 = tensor(lamm, Q8_0, [k, m], [lamm.type_size(Q8_0), row_size(Q8_0, k)], w)
+        for key, v in kw.items():
+            setattr(s0, key, v)
+        s1 = tensor(lamm, F32, [k, n], [4, k * 4], x)
+        d = tensor(lamm, F32, [m, n], [4, m * 4], c)
+        d.src[0], d.src[1] = C.pointer(s0), C.pointer(s1)
+        host.stub_reset()
+        assert run(lamm, host, d)
+        return host.stub_refreshes()
+    assert refreshes() == 0                                             # a model weight
+    assert refreshes(flags=2) == 0                                      # GGML_TENSOR_FLAG_OUTPUT alone changes nothing
+    assert refreshes(view_src=C.pointer(parent)) == 1                   # K-cache view
+    assert refreshes(op=24) == 1                                        # an op result as src0
+    assert refreshes(flags=4) == 1                                      # GGML_TENSOR_FLAG_PARAM (finetune)
+    assert refreshes(flags=1) == 1                                      # GGML_TENSOR_FLAG_INPUT
+    assert refreshes(grad=C.pointer(parent)) == 1
 
 
 @pytest.mark.parametrize("t", [3, Q8_0, Q2_K])
