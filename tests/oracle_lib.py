@@ -104,8 +104,9 @@ class Oracle:
 
     def quantize_weights(self, t, w, seed=0):
         """w: [M, K] f32 -> uint8 [M, row_size].  Q2_K .. Q6_K: random super-blocks."""
-        w = np.ascontiguousarray(w, np.float32)
-        m, k = w.shape
+        m, k = w.shape                       # Q2_K .. Q6_K: random super-blocks, only w.shape is used
+        if t != Q2_K and t not in KQ_TYPES:
+            w = np.ascontiguousarray(w, np.float32)
         out = np.zeros((m, row_size(t, k)), np.uint8)
         if t == Q2_K:
             self.L.orc_random_q2_K(_ptr(out), m * (k // 256), seed)
