@@ -183,8 +183,10 @@ struct GemmPeers {
 };
 void gemm_set_peers(const GemmPeers *peers);     // thread-local; consumed by the next scaled-operand / direct GEMM launch
 bool gemm_peers_used();
-constexpr int kSoShift = 6;      // scaled-operand GEMM: A carries 2^kSoShift, B carries 2^-kSoShift
-size_t gemm_so_ws_bytes(int64_t N, int64_t K);
+const GemmPeers *gemm_peers_take();                // the pending peer set (marks it used), or NULL
+size_t gemm_so_ws_bytes(int64_t M, int64_t N, int64_t K);
+int launch_wrow_scale(int w_type, const void *w, int64_t w_stride, float *rowscale, int64_t M, int64_t Mpad, int64_t K,
+                      cudaStream_t st);
 int launch_gemm_so(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
                    int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st, const float *x = nullptr,
                    int64_t ldx = 0);
@@ -194,8 +196,8 @@ bool gemm_tc_supported(int w_type, const void *w, int64_t w_stride, int64_t M, i
 size_t gemm_direct_ws_bytes(int64_t M, int64_t N, int64_t K);
 int launch_gemm_direct(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
                        int64_t ldc, int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st);
-int launch_dequant_hilo(int w_type, const void *w, int64_t w_stride, void *ah, void *al, int64_t M, int64_t Mpad,
-                        int64_t K, cudaStream_t st);
+int launch_dequant_hilo(int w_type, const void *w, int64_t w_stride, void *ah, void *al, float *rowscale, int64_t M,
+                        int64_t Mpad, int64_t K, cudaStream_t st);
 int launch_prep_direct(int vt, const void *xq, int64_t xq_stride, void *xh, void *xl, float *colscale, int64_t N,
                        int64_t Npad, int64_t K, cudaStream_t st);
 void set_gemm_exact(int on);

@@ -421,7 +421,7 @@ int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int
                 int64_t ldc, int64_t M, int64_t N, int64_t K, cudaStream_t st) {
   if (gemm_tc_supported(w_type, w, w_stride, M, N, K)) {
     if (!g_gemm_exact) {
-      void *ws = gemm_workspace(gemm_so_ws_bytes(N, K));
+      void *ws = gemm_workspace(gemm_so_ws_bytes(M, N, K));
       if (!ws) return LAMMCU_ERR_NOMEM;
       return launch_gemm_so(w_type, w, w_stride, xq, xq_stride, c, ldc, M, N, K, ws, st);
     }

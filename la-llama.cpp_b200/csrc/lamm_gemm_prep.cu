@@ -111,7 +111,7 @@ int launch_gemm_prep(int vt, int perm, const void *xq, int64_t xq_stride, void *
 // bits).  Each activation row n is normalised by an exact power of two 2^-E_n (E_n from the row's
 // largest block scale, so that |v| 2^-E_n < 2^11: any activation range fits fp16) and split into two
 // fp16 terms, v 2^-E_n ~= hi + lo, |residue| <= 2^-22 |v| (or 2^-25 absolute for elements far below
-// the row maximum).  The epilogue multiplies column n by colscale[n] = 2^(E_n - kSoShift).
+// the row maximum).  The epilogue multiplies column n by colscale[n] = 2^E_n.
 //   XH, XL   : fp16 [Npad][K]      same element order as X16 above (perm 1 / perm 0)
 //   SH       : fp16 [Npad][Kbpad]  s_x 2^-E_n (q8_1 only; s_x is an fp16 field, so one term is exact)
 //                                  for the m_w * s_x extra stages; Kbpad = Kb rounded up to 64, zero filled
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(256) gemm_prep_so_kernel(const uint8_t *__rest
     int E = 0;
     if (dmax > 0.f && dmax < 3.0e38f) E = ilogbf(dmax) - 3;         // |d q| < 2^(ilogb + 8)  ->  < 2^11 after 2^-E
     const float down = ldexpf(1.0f, -E);                            // exact power of two
-    if (lane == 0) colscale[n] = ldexpf(1.0f, E - kSoShift);
+    if (lane == 0) colscale[n] = ldexpf(1.0f, E);
     for (int b = lane; b < kbpad; b += 32) {
       if (b >= kb) {                                                // zero tail of the s_x tile row
         if (VT == LAMMCU_TYPE_Q8_1) sh[(int64_t)n * kbpad + b] = __float2half_rn(0.f);
@@ -262,7 +262,7 @@ __global__ void __launch_bounds__(256) quant_prep_so_kernel(const float *__restr
     int E = 0;
     if (dmax > 0.f && dmax < 3.0e38f) E = ilogbf(dmax) - 3;
     const float down = ldexpf(1.0f, -E);
-    if (tid == 0) colscale[n] = ldexpf(1.0f, E - kSoShift);
+    if (tid == 0) colscale[n] = ldexpf(1.0f, E);
     for (int b = tid; b < kbpad; b += 256) {
       if (b >= kb) {
         if (VT == LAMMCU_TYPE_Q8_1) sh[(int64_t)n * kbpad + b] = __float2half_rn(0.f);
@@ -457,72 +457,152 @@ __device__ __forceinline__ void kquant_group32(const uint8_t *blk, int g, float 
   }
 }
 
-// W (Q2_K super-blocks or f32 rows) -> AH, AL fp16 [Mpad][K], value * 2^kSoShift, natural K order.
+// W (Q2_K .. Q6_K super-blocks or f32 rows) -> AH, AL fp16 [Mpad][K], value * 2^F_m, natural K order, and
+// rowscale[m] = 2^F_m: an exact power of two per weight row that lifts the row's largest |w| to [2^14, 2^15) so that
+// neither large weights (|w| >= 1024 used to overflow a fixed 2^6 pre-scale) nor tiny ones (lo term lost to fp16
+// subnormals) leave the 22-bit hi + lo representation; the GEMM epilogue multiplies row m by 2^-F_m.
 // Q2_K element (ggml-common.h:214-225, src/lamm_kernel_q2_k.hpp:49-71): for half n of the super-block and
 // shift s in {0,2,4,6}, elements 128n + 16s .. + 31 are (qs[32n + l] >> s) & 3 with scale bytes
 // scales[8n + s] (l < 16) and scales[8n + s + 1]; w = d * (sc & 15) * q - dmin * (sc >> 4).
 template <int WT>
-__global__ void __launch_bounds__(256) dequant_hilo_kernel(const uint8_t *__restrict__ w, int64_t w_stride,
-                                                          __half *__restrict__ ah, __half *__restrict__ al, int M,
-                                                          int Mpad, int K) {
-  const int kb32 = K / 32;
-  const int64_t total = (int64_t)Mpad * kb32;
-  constexpr float S = (float)(1 << kSoShift);
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int m = (int)(i / kb32), b = (int)(i - (int64_t)m * kb32);
-    float v[32];
+__device__ __forceinline__ void dequant_group32(const uint8_t *row, int b, float S, float (&v)[32]) {
+  if constexpr (WT == LAMMCU_TYPE_Q2_K) {
+    const uint8_t *blk = row + (int64_t)(b >> 3) * 84;
+    const int ib = b & 7, n = ib >> 2, shift = 2 * (ib & 3);
+    const uint32_t dd = *reinterpret_cast<const uint32_t *>(blk + 80);
+    const float d = half_bits_to_float(dd & 0xffffu) * S, dmin = half_bits_to_float(dd >> 16) * S;
+    const uint32_t sc2 = *reinterpret_cast<const uint16_t *>(blk + 2 * ib);
+    const float d0 = d * (float)(sc2 & 15u), m0 = dmin * (float)((sc2 >> 4) & 15u);
+    const float d1 = d * (float)((sc2 >> 8) & 15u), m1 = dmin * (float)(sc2 >> 12);
+    const uint32_t *qs = reinterpret_cast<const uint32_t *>(blk + 16 + 32 * n);
 #pragma unroll
-    for (int l = 0; l < 32; l++) v[l] = 0.f;
-    if (m < M) {
-      if constexpr (WT == LAMMCU_TYPE_Q2_K) {
-        const uint8_t *blk = w + (int64_t)m * w_stride + (int64_t)(b >> 3) * 84;
-        const int ib = b & 7, n = ib >> 2, shift = 2 * (ib & 3);
-        const uint32_t dd = *reinterpret_cast<const uint32_t *>(blk + 80);
-        const float d = half_bits_to_float(dd & 0xffffu) * S, dmin = half_bits_to_float(dd >> 16) * S;
-        const uint32_t sc2 = *reinterpret_cast<const uint16_t *>(blk + 2 * ib);
-        const float d0 = d * (float)(sc2 & 15u), m0 = dmin * (float)((sc2 >> 4) & 15u);
-        const float d1 = d * (float)((sc2 >> 8) & 15u), m1 = dmin * (float)(sc2 >> 12);
-        const uint32_t *qs = reinterpret_cast<const uint32_t *>(blk + 16 + 32 * n);
+    for (int j = 0; j < 8; j++) {
+      const uint32_t qw = qs[j] >> shift;
 #pragma unroll
-        for (int j = 0; j < 8; j++) {
-          const uint32_t qw = qs[j] >> shift;
-#pragma unroll
-          for (int e = 0; e < 4; e++) {
-            const float qv = (float)((qw >> (8 * e)) & 3u);
-            v[4 * j + e] = (j < 4) ? fmaf(d0, qv, -m0) : fmaf(d1, qv, -m1);
-          }
-        }
-      } else if constexpr (is_kquant_ext(WT)) {
-        kquant_group32<WT>(w + (int64_t)m * w_stride + (int64_t)(b >> 3) * type_info(WT).size, b & 7, S, v);
-      } else {
-        const float4 *src = reinterpret_cast<const float4 *>(w + (int64_t)m * w_stride + (int64_t)b * 128);
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-          const float4 f = src[j];
-          v[4 * j] = f.x * S;  v[4 * j + 1] = f.y * S;  v[4 * j + 2] = f.z * S;  v[4 * j + 3] = f.w * S;
-        }
+      for (int e = 0; e < 4; e++) {
+        const float qv = (float)((qw >> (8 * e)) & 3u);
+        v[4 * j + e] = (j < 4) ? fmaf(d0, qv, -m0) : fmaf(d1, qv, -m1);
       }
     }
-    split_store32(v, ah + ((int64_t)m * kb32 + b) * 32, al + ((int64_t)m * kb32 + b) * 32);
+  } else if constexpr (is_kquant_ext(WT)) {
+    kquant_group32<WT>(row + (int64_t)(b >> 3) * type_info(WT).size, b & 7, S, v);
+  } else {
+    const float4 *src = reinterpret_cast<const float4 *>(row + (int64_t)b * 128);
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const float4 f = src[j];
+      v[4 * j] = f.x * S;  v[4 * j + 1] = f.y * S;  v[4 * j + 2] = f.z * S;  v[4 * j + 3] = f.w * S;
+    }
   }
 }
 
-int launch_dequant_hilo(int w_type, const void *w, int64_t w_stride, void *ah, void *al, int64_t M, int64_t Mpad,
-                        int64_t K, cudaStream_t st) {
-  const int64_t total = Mpad * (K / 32);
-  int blocks = (int)((total + 255) / 256);
+// 2^F with 2^14 <= vmax 2^F < 2^15 (1 for an all-zero or non-finite row); 2^F and 2^-F both stay normal f32
+__device__ __forceinline__ float lift_scale(float vmax) {
+  if (!(vmax > 0.f) || !(vmax < 3.0e38f)) return 1.0f;
+  const int F = 14 - ilogbf(vmax);
+  return ldexpf(1.0f, F > 120 ? 120 : F);
+}
+
+template <int WT>
+__global__ void __launch_bounds__(256) dequant_hilo_kernel(const uint8_t *__restrict__ w, int64_t w_stride,
+                                                          __half *__restrict__ ah, __half *__restrict__ al,
+                                                          float *__restrict__ rowscale, int M, int Mpad, int K) {
+  const int kb32 = K / 32;
+  __shared__ float red[8];
+  const int tid = threadIdx.x, lane = tid & 31;
+  for (int m = blockIdx.x; m < Mpad; m += gridDim.x) {              // one CTA per weight row
+    const uint8_t *row = w + (int64_t)m * w_stride;
+    float vmax = 0.f;
+    if (m < M) {
+      for (int b = tid; b < kb32; b += 256) {
+        float v[32];
+        dequant_group32<WT>(row, b, 1.0f, v);
+#pragma unroll
+        for (int l = 0; l < 32; l++) vmax = fmaxf(vmax, fabsf(v[l]));
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    __syncthreads();                                                // red[] of the previous row is consumed
+    if (lane == 0) red[tid >> 5] = vmax;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 8; i++) vmax = fmaxf(vmax, red[i]);
+    const float S = lift_scale(vmax);
+    if (tid == 0) rowscale[m] = S;
+    for (int b = tid; b < kb32; b += 256) {
+      float v[32];
+#pragma unroll
+      for (int l = 0; l < 32; l++) v[l] = 0.f;
+      if (m < M) dequant_group32<WT>(row, b, S, v);
+      split_store32(v, ah + ((int64_t)m * kb32 + b) * 32, al + ((int64_t)m * kb32 + b) * 32);
+    }
+  }
+}
+
+// The scaled-operand kernel unpacks W on the fly, so its per-row lift comes from a pass over the block headers:
+// rowscale[m] = 2^F_m from max_kb max(|d_w| * QMAX, |m_w|).  One warp per row.
+template <int WT>
+__global__ void __launch_bounds__(256) wrow_scale_kernel(const uint8_t *__restrict__ w, int64_t w_stride,
+                                                        float *__restrict__ rowscale, int M, int Mpad, int kb) {
+  constexpr int BS = type_info(WT).size;
+  constexpr float QMAX = (WT == LAMMCU_TYPE_Q4_0) ? 8.f : (WT == LAMMCU_TYPE_Q4_1) ? 15.f : (WT == LAMMCU_TYPE_Q5_0) ? 16.f
+                         : (WT == LAMMCU_TYPE_Q5_1) ? 31.f : 128.f;
+  constexpr bool kMin = (WT == LAMMCU_TYPE_Q4_1 || WT == LAMMCU_TYPE_Q5_1);
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int m = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; m < Mpad; m += warps) {
+    float vmax = 0.f;
+    if (m < M) {
+      const uint8_t *row = w + (int64_t)m * w_stride;
+      for (int b = lane; b < kb; b += 32) {
+        const uint8_t *blk = row + (int64_t)b * BS;
+        vmax = fmaxf(vmax, fabsf(half_bits_to_float(ldg16(blk))) * QMAX);
+        if (kMin) vmax = fmaxf(vmax, fabsf(half_bits_to_float(ldg16(blk + 2))));
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    if (lane == 0) rowscale[m] = lift_scale(vmax);
+  }
+}
+
+int launch_wrow_scale(int w_type, const void *w, int64_t w_stride, float *rowscale, int64_t M, int64_t Mpad, int64_t K,
+                      cudaStream_t st) {
+  const int kb = (int)(K / 32);
+  int blocks = (int)((Mpad + 7) / 8);
+  const int cap = sm_count_cached() * 8;
+  if (blocks > cap) blocks = cap;
+  const uint8_t *p = (const uint8_t *)w;
+  switch (w_type) {
+#define LAMM_WR(T) case T: wrow_scale_kernel<T><<<blocks, 256, 0, st>>>(p, w_stride, rowscale, (int)M, (int)Mpad, kb); break;
+  LAMM_WR(LAMMCU_TYPE_Q4_0) LAMM_WR(LAMMCU_TYPE_Q4_1) LAMM_WR(LAMMCU_TYPE_Q5_0) LAMM_WR(LAMMCU_TYPE_Q5_1) LAMM_WR(LAMMCU_TYPE_Q8_0)
+#undef LAMM_WR
+  default: set_error("wrow_scale: weight type %d not supported", w_type); return LAMMCU_ERR_TYPE;
+  }
+  g_launch_count++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("wrow_scale launch: %s", cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+int launch_dequant_hilo(int w_type, const void *w, int64_t w_stride, void *ah, void *al, float *rowscale, int64_t M,
+                        int64_t Mpad, int64_t K, cudaStream_t st) {
+  int blocks = (int)Mpad;
   const int cap = sm_count_cached() * 16;
   if (blocks > cap) blocks = cap;
   if (w_type == LAMMCU_TYPE_Q2_K)
     dequant_hilo_kernel<LAMMCU_TYPE_Q2_K><<<blocks, 256, 0, st>>>((const uint8_t *)w, w_stride, (__half *)ah, (__half *)al,
-                                                               (int)M, (int)Mpad, (int)K);
+                                                               rowscale, (int)M, (int)Mpad, (int)K);
   else if (w_type == LAMMCU_TYPE_F32)
     dequant_hilo_kernel<LAMMCU_TYPE_F32><<<blocks, 256, 0, st>>>((const uint8_t *)w, w_stride, (__half *)ah, (__half *)al,
-                                                              (int)M, (int)Mpad, (int)K);
+                                                              rowscale, (int)M, (int)Mpad, (int)K);
 #define LAMM_DQ_CASE(T)                                                                                             \
   else if (w_type == T)                                                                                             \
-    dequant_hilo_kernel<T><<<blocks, 256, 0, st>>>((const uint8_t *)w, w_stride, (__half *)ah, (__half *)al, (int)M, \
-                                                   (int)Mpad, (int)K);
+    dequant_hilo_kernel<T><<<blocks, 256, 0, st>>>((const uint8_t *)w, w_stride, (__half *)ah, (__half *)al, rowscale, \
+                                                   (int)M, (int)Mpad, (int)K);
   LAMM_DQ_CASE(LAMMCU_TYPE_Q3_K)
   LAMM_DQ_CASE(LAMMCU_TYPE_Q4_K)
   LAMM_DQ_CASE(LAMMCU_TYPE_Q5_K)
@@ -542,7 +622,7 @@ int launch_dequant_hilo(int w_type, const void *w, int64_t w_stride, void *ah, v
 }
 
 // Activations for the direct variant: Q8_K blocks (x.d is f32, ggml-common.h:316-321) or plain f32 rows
-// -> XH, XL fp16 [Npad][K] (natural order), row-normalised by 2^-E_n, and colscale[n] = 2^(E_n - kSoShift).
+// -> XH, XL fp16 [Npad][K] (natural order), row-normalised by 2^-E_n, and colscale[n] = 2^E_n.
 template <int VT>
 __global__ void __launch_bounds__(256) prep_direct_kernel(const uint8_t *__restrict__ xq, int64_t xq_stride,
                                                          __half *__restrict__ xh, __half *__restrict__ xl,
@@ -567,7 +647,7 @@ __global__ void __launch_bounds__(256) prep_direct_kernel(const uint8_t *__restr
     int E = 0;
     if (vmax > 0.f && vmax < 3.0e38f) E = ilogbf(vmax) - 10;       // |v| 2^-E < 2^11
     const float down = ldexpf(1.0f, -E);
-    if (lane == 0) colscale[n] = ldexpf(1.0f, E - kSoShift);
+    if (lane == 0) colscale[n] = ldexpf(1.0f, E);
     for (int b = lane; b < kb32; b += 32) {
       float v[32];
 #pragma unroll

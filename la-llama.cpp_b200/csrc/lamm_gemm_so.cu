@@ -7,7 +7,7 @@
 //
 //   C[n, m] = sum_k (d_w[m,b(k)] * q_w[m,k]) * (d_x[n,b(k)] * q_x[n,k])   (+ sum_b m_w[m,b] * s_x[n,b])
 //
-//   A' = d_w * q_w * 2^6     : split EXACTLY into two fp16 terms hi + lo (hi = rn(d q), lo = fma(d, q, -hi))
+//   A' = d_w * q_w * 2^F_m   : (F_m: per-row lift to [2^14, 2^15), lamm_gemm_prep.cu) split EXACTLY into two fp16 terms hi + lo (hi = rn(d q), lo = fma(d, q, -hi))
 //   B' = d_x * q_x * 2^-E_n  : exact in f32 (11 + 8 bits), row-normalised by a power of two and split
 //                              into two fp16 terms by lamm_gemm_prep.cu (residue <= 2^-22)
 //   A'B' ~= Ah*Bh + Ah*Bl + Al*Bh   -- three kind::f16 MMAs per K step, f32 accumulate in TMEM; the
@@ -40,7 +40,11 @@ constexpr int kSoThreads = 512;
 constexpr int kTileBytes = GM * GK * 2;        // 16 KB: one 128 x 64 fp16 operand tile
 
 struct SoParams {
-  const float *colscale;      // [Npad]: 2^(E_n - kSoShift), undoes the operands' power-of-two scales
+  const float *colscale;      // [Npad]: 2^E_n, undoes the activation rows' power-of-two normalisation
+  // [Mpad]: 2^F_m, an exact power of two per WEIGHT row that lifts the row's largest |d_w q_w| (and |m_w|) to
+  // 2^14 <= . < 2^15 before the fp16 hi/lo split, so that no fp16 scale -- 6e-8 .. 65504 -- overflows the split or
+  // loses its lo term to subnormals; the epilogue multiplies row m by 2^-F_m (wrow_scale_kernel, lamm_gemm_prep.cu)
+  const float *rowscale;
   float *c;
   int64_t ldc;
   int M, N, Npad, K;
@@ -54,6 +58,10 @@ static thread_local const GemmPeers *t_peers = nullptr;
 static thread_local bool t_peers_used = false;
 void gemm_set_peers(const GemmPeers *peers) { t_peers = peers;  t_peers_used = false; }
 bool gemm_peers_used() { return t_peers_used; }
+const GemmPeers *gemm_peers_take() {
+  if (t_peers) t_peers_used = true;
+  return t_peers;
+}
 static void fill_peers(SoParams &p) {
   p.n_peer = 0;
   for (int g = 0; g < LAMMCU_MAX_RANKS; g++) p.cp[g] = nullptr;
@@ -96,8 +104,8 @@ template <int WT> struct SoSmem {
 // 8 fp16 small integers (one 16-byte chunk of unpack_block) * d -> 8 fp16 hi + 8 fp16 lo, EXACT:
 // hi = rn(q * d) in fp16, lo = fma(q, d, -hi) is the rounding residual (<= 8 significant bits, exactly
 // representable as long as it stays above the fp16 subnormal step 2^-24).  d2 = (d, d) carries the
-// fixed pre-scale 2^kSoShift, which lifts realistic weight scales (1e-5 .. 8) well clear of the
-// subnormal range; the epilogue takes it out again (colscale).
+// per-row lift 2^F_m (SoParams::rowscale), which puts the row's largest |d q| in [2^14, 2^15): no fp16 scale
+// overflows the split and only blocks > 2^24 below the row's largest lose bits; the epilogue takes it out.
 __device__ __forceinline__ void scale_split8(const uint4 &q, __half2 d2, uint4 &hi, uint4 &lo) {
   const uint32_t in[4] = {q.x, q.y, q.z, q.w};
   uint32_t h[4], l[4];
@@ -115,13 +123,15 @@ __device__ __forceinline__ void scale_split8(const uint4 &q, __half2 d2, uint4 &
 
 // Block JB of the raw chunk (j = JB & 1: first / second 32-block of its 64-K stage) of the thread's row r.
 template <int WT, int JB, int NWR>
-__device__ __forceinline__ void unpack_block_so(const uint32_t (&raw)[NWR], uint32_t ah_stage, uint32_t al_stage, int r) {
+__device__ __forceinline__ void unpack_block_so(const uint32_t (&raw)[NWR], uint32_t ah_stage, uint32_t al_stage, int r,
+                                                float rs) {
   constexpr int j = JB & 1;
   const uint32_t row_off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u;
   uint4 out[4];
   float d, m;
   unpack_block<WT, JB, NWR>(raw, out, d, m);
-  const __half2 d2 = __float2half2_rn(d * (float)(1 << kSoShift));      // exact: d is an fp16 value
+  const __half2 d2 = __float2half2_rn(d * rs);      // d is an fp16 value, rs a power of two: exact unless the block's
+                                                    // scale is > 2^24 below the row's largest (then it is noise)
 #pragma unroll
   for (int w = 0; w < 4; w++) {
     uint4 hi, lo;
@@ -136,12 +146,11 @@ __device__ __forceinline__ void unpack_block_so(const uint32_t (&raw)[NWR], uint
   }
 }
 
-// the 8 m_w of the raw chunk (Q4_1 / Q5_1: fp16 at byte 2 of every block) times 2^kSoShift: one 16-byte
+// the 8 m_w of the raw chunk (Q4_1 / Q5_1: fp16 at byte 2 of every block) times the row's lift S: one 16-byte
 // chunk of the extra A tile (m_w is an fp16 field, the power-of-two scale keeps it exact)
 template <int WT, int NWR>
-__device__ __forceinline__ uint4 chunk_mins(const uint32_t (&raw)[NWR]) {
+__device__ __forceinline__ uint4 chunk_mins(const uint32_t (&raw)[NWR], float S) {
   constexpr int BS = type_info(WT).size;
-  constexpr float S = (float)(1 << kSoShift);
   const __half2 a = __floats2half2_rn(raw_half<0 * BS + 2, NWR>(raw) * S, raw_half<1 * BS + 2, NWR>(raw) * S);
   const __half2 b = __floats2half2_rn(raw_half<2 * BS + 2, NWR>(raw) * S, raw_half<3 * BS + 2, NWR>(raw) * S);
   const __half2 c = __floats2half2_rn(raw_half<4 * BS + 2, NWR>(raw) * S, raw_half<5 * BS + 2, NWR>(raw) * S);
@@ -286,6 +295,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
   } else if (warp >= 4 && warp < 12) {
     // ===================== weight unpack (thread = row x block j of the stage) =====================
     const int r = (threadIdx.x - 128) & 127, j = (warp - 4) >> 2;
+    const float rs = __ldg(p.rowscale + m0 + r);                      // [Mpad]: rows beyond M carry 1
     for (int ms = 0; ms < n_chunks; ms++) {
       mbar_wait(raw_full, (uint32_t)ms & 1u);
       uint32_t raw[NWR];
@@ -300,7 +310,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
       if constexpr (kMin) {
         if (j == 0) {
           if ((ms & 7) == 0 && ms > 0) mbar_wait(ext_empty, (uint32_t)((ms >> 3) - 1) & 1u);
-          const uint4 mh = chunk_mins<WT, NWR>(raw);
+          const uint4 mh = chunk_mins<WT, NWR>(raw, rs);
           const uint32_t off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u + (((uint32_t)(ms & 7) ^ (uint32_t)(r & 7)) * 16u);
           asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(smem + L::kEhOff) + off), "r"(mh.x),
                        "r"(mh.y), "r"(mh.z), "r"(mh.w)
@@ -318,15 +328,15 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
         mbar_wait(&empty_a[s], ((uint32_t)(st / kSoAStages) & 1u) ^ 1u);
         const uint32_t ah = smem_u32(smem + L::kAhOff + s * kTileBytes), al = smem_u32(smem + L::kAlOff + s * kTileBytes);
         if (j == 0) {
-          if (q == 0) unpack_block_so<WT, 0, NWR>(raw, ah, al, r);
-          else if (q == 1) unpack_block_so<WT, 2, NWR>(raw, ah, al, r);
-          else if (q == 2) unpack_block_so<WT, 4, NWR>(raw, ah, al, r);
-          else unpack_block_so<WT, 6, NWR>(raw, ah, al, r);
+          if (q == 0) unpack_block_so<WT, 0, NWR>(raw, ah, al, r, rs);
+          else if (q == 1) unpack_block_so<WT, 2, NWR>(raw, ah, al, r, rs);
+          else if (q == 2) unpack_block_so<WT, 4, NWR>(raw, ah, al, r, rs);
+          else unpack_block_so<WT, 6, NWR>(raw, ah, al, r, rs);
         } else {
-          if (q == 0) unpack_block_so<WT, 1, NWR>(raw, ah, al, r);
-          else if (q == 1) unpack_block_so<WT, 3, NWR>(raw, ah, al, r);
-          else if (q == 2) unpack_block_so<WT, 5, NWR>(raw, ah, al, r);
-          else unpack_block_so<WT, 7, NWR>(raw, ah, al, r);
+          if (q == 0) unpack_block_so<WT, 1, NWR>(raw, ah, al, r, rs);
+          else if (q == 1) unpack_block_so<WT, 3, NWR>(raw, ah, al, r, rs);
+          else if (q == 2) unpack_block_so<WT, 5, NWR>(raw, ah, al, r, rs);
+          else unpack_block_so<WT, 7, NWR>(raw, ah, al, r, rs);
         }
         fence_proxy_async();             // generic-proxy stores -> visible to the tensor core
         __syncwarp();
@@ -336,6 +346,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
   } else if (warp >= 12) {
     // ===================== epilogue (thread = TMEM lane = weight row) =====================
     const int q4 = warp & 3, row = q4 * 32 + lane, m = m0 + row;
+    const float rinv = 1.0f / __ldg(p.rowscale + m);                  // exact: a power of two ([Mpad] entries)
     mbar_wait(acc_full, 0u);
     tc_fence_after();
     const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16);
@@ -354,7 +365,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
 #pragma unroll
         for (int i = 0; i < 16; i++) {
           const int n = n0 + c16 * 16 + i;
-          if (n < p.N) store_out<PEERS>(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * __ldg(p.colscale + n));
+          if (n < p.N) store_out<PEERS>(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * (__ldg(p.colscale + n) * rinv));
         }
       }
     }
@@ -366,7 +377,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
 
 // ---- direct variant: both operands pre-split in global memory --------------------------------
 // Q2_K and F32 weights: lamm_gemm_prep.cu dequantizes W once per call into fp16 hi / lo [M][K]
-// (w * 2^kSoShift; Q2_K: w = d * sc * q - dmin * mn evaluated in f32, which is the reference's
+// (w * 2^F_m, the per-row lift; Q2_K: w = d * sc * q - dmin * mn evaluated in f32, which is the reference's
 // d*isum - dmin*summs regrouped, src/lamm_kernel_q2_k.hpp:28-75), so the mainloop is a plain TMA-fed
 // GEMM: no unpack warps, no extra stages.  Same three MMAs per K step, same epilogue.
 constexpr int kDirStages = 3;
@@ -438,6 +449,7 @@ gemm_direct_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_const
   } else {
     // epilogue warps 2..5: TMEM lane quarter = warp & 3
     const int q4 = warp & 3, row = q4 * 32 + lane, m = m0 + row;
+    const float rinv = 1.0f / __ldg(p.rowscale + m);                  // exact: a power of two ([Mpad] entries)
     mbar_wait(acc_full, 0u);
     tc_fence_after();
     const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16);
@@ -456,7 +468,7 @@ gemm_direct_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_const
 #pragma unroll
         for (int i = 0; i < 16; i++) {
           const int n = n0 + c16 * 16 + i;
-          if (n < p.N) store_out<PEERS>(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * __ldg(p.colscale + n));
+          if (n < p.N) store_out<PEERS>(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * (__ldg(p.colscale + n) * rinv));
         }
       }
     }
@@ -468,7 +480,7 @@ gemm_direct_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_const
 
 size_t gemm_direct_ws_bytes(int64_t M, int64_t N, int64_t K) {
   const int64_t npad = (N + GN - 1) / GN * GN, mpad = (M + GM - 1) / GM * GM;
-  return (size_t)(2 * mpad * K * 2 + 2 * npad * K * 2 + npad * 4 + 2048);
+  return (size_t)(2 * mpad * K * 2 + 2 * npad * K * 2 + npad * 4 + mpad * 4 + 2048);
 }
 
 // W: Q2_K blocks or f32; X: Q8_K blocks (Q2_K) or f32 (F32 weights)
@@ -479,7 +491,8 @@ int launch_gemm_direct(int w_type, const void *w, int64_t w_stride, const void *
   void *ah = base, *al = base + mpad * K * 2;
   void *xh = base + 2 * mpad * K * 2, *xl = (uint8_t *)xh + npad * K * 2;
   float *colscale = (float *)((uint8_t *)xl + npad * K * 2);
-  int rc = launch_dequant_hilo(w_type, w, w_stride, ah, al, M, mpad, K, st);
+  float *rowscale = colscale + npad;
+  int rc = launch_dequant_hilo(w_type, w, w_stride, ah, al, rowscale, M, mpad, K, st);
   if (rc) return rc;
   rc = launch_prep_direct(type_info(w_type).vec_dot, xq, xq_stride, xh, xl, colscale, N, npad, K, st);
   if (rc) return rc;
@@ -493,7 +506,7 @@ int launch_gemm_direct(int w_type, const void *w, int64_t w_stride, const void *
   if ((rc = make_map_2d(&tm_xl, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, xl, (uint64_t)K, (uint64_t)npad, (uint64_t)K * 2, GK, GN,
                         CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   SoParams p;
-  p.colscale = colscale;  p.c = c;  p.ldc = ldc;
+  p.colscale = colscale;  p.rowscale = rowscale;  p.c = c;  p.ldc = ldc;
   p.M = (int)M;  p.N = (int)N;  p.Npad = (int)npad;  p.K = (int)K;
   fill_peers(p);
   constexpr int smem = kDirStages * 4 * kTileBytes + 256 + 1024;
@@ -550,9 +563,9 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
   return LAMMCU_OK;
 }
 
-size_t gemm_so_ws_bytes(int64_t N, int64_t K) {
-  const int64_t npad = (N + GN - 1) / GN * GN, kbpad = (K / 32 + 63) / 64 * 64;
-  return (size_t)(2 * npad * K * 2 + npad * kbpad * 2 + npad * 4 + 1024);
+size_t gemm_so_ws_bytes(int64_t M, int64_t N, int64_t K) {
+  const int64_t npad = (N + GN - 1) / GN * GN, kbpad = (K / 32 + 63) / 64 * 64, mpad = (M + GM - 1) / GM * GM;
+  return (size_t)(2 * npad * K * 2 + npad * kbpad * 2 + npad * 4 + mpad * 4 + 1024);
 }
 
 // xq: quantized activations (ggml blocks, row stride xq_stride); ws: gemm_so_ws_bytes() of scratch
@@ -565,8 +578,11 @@ int launch_gemm_so(int w_type, const void *w, int64_t w_stride, const void *xq, 
   void *xh = base, *xl = base + npad * K * 2;
   void *sh = base + 2 * npad * K * 2;
   float *colscale = (float *)((uint8_t *)sh + npad * kbpad * 2);
+  float *rowscale = colscale + npad;
   const int perm = (w_type == LAMMCU_TYPE_Q8_0) ? 0 : 1;
-  int rc = x ? launch_quant_prep_so(ti.vec_dot, perm, x, ldx, const_cast<void *>(xq), xq_stride, xh, xl, sh, colscale, N,
+  int rc = launch_wrow_scale(w_type, w, w_stride, rowscale, M, (M + GM - 1) / GM * GM, K, st);
+  if (rc) return rc;
+  rc = x ? launch_quant_prep_so(ti.vec_dot, perm, x, ldx, const_cast<void *>(xq), xq_stride, xh, xl, sh, colscale, N,
                                     npad, K, st)
              : launch_gemm_prep_so(ti.vec_dot, perm, xq, xq_stride, xh, xl, sh, colscale, N, npad, K, st);
   if (rc) return rc;
@@ -586,7 +602,7 @@ int launch_gemm_so(int w_type, const void *w, int64_t w_stride, const void *xq, 
                    GK, GN, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
   SoParams p;
-  p.colscale = colscale;  p.c = c;  p.ldc = ldc;
+  p.colscale = colscale;  p.rowscale = rowscale;  p.c = c;  p.ldc = ldc;
   p.M = (int)M;  p.N = (int)N;  p.Npad = (int)npad;  p.K = (int)K;
   fill_peers(p);
   switch (w_type) {

@@ -332,7 +332,7 @@ int lammcu_mul_mat_dev(int w_type, const void *w, int64_t w_stride, const float 
   // unless the caller passed a workspace for it
   if (N > g_gemv_max_n && !get_gemm_exact() && gemm_tc_supported(w_type, w, w_stride, M, N, K) &&
       (((uintptr_t)x | (uintptr_t)(ldx * 4)) & 15) == 0 && (!xq_ws || ((uintptr_t)xq_ws & 3) == 0)) {
-    void *ws = gemm_workspace(gemm_so_ws_bytes(N, K));
+    void *ws = gemm_workspace(gemm_so_ws_bytes(M, N, K));
     if (!ws) return LAMMCU_ERR_NOMEM;
     return launch_gemm_so(w_type, w, w_stride, xq_ws, (int64_t)rs, c, ldc, M, N, K, ws, pick_stream(stream), x, ldx);
   }

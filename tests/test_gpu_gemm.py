@@ -38,8 +38,8 @@ def test_gemm_vs_oracle(gpu, oracle, t, m, n, k, gemm_mode):
     got = gpu.mul_mat(t, wd if t != F32 else wd.view(__import__("torch").float32), dev(x)).cpu().numpy()
     launches = gpu.lib().lammcu_launch_count()
     if t in TC_TYPES:
-        # scaled: fused quantize+prep, GEMM; exact: quantize, prep, GEMM
-        assert launches == (2 if gemm_mode == "scaled" else 3)
+        # scaled: weight-row lift, fused quantize+prep, GEMM; exact: quantize, prep, GEMM
+        assert launches == 3
     elif gemm_mode == "scaled" and k % 256 == 0:
         # Q2_K / F32 weights: (quantize +) weight dequantize + operand prep + TMA-fed tcgen05 GEMM
         assert launches == (4 if t == Q2_K else 3)
@@ -81,6 +81,64 @@ def test_gemm_llama_shapes_sampled(gpu, oracle, t):
         got2 = gpu.mul_mat(t, dev(w), dev(4 * x)).cpu().numpy()
         if t == Q8_0:
             assert np.array_equal(got2, 4 * got)
+
+
+def rescale_blocks(t, w, k, scale, rng=None):
+    """Multiply the fp16 scale fields (d, and m / dmin where the format has one) of every block by `scale`, in
+    fp16 arithmetic, leaving the quants alone; optionally plant one block per row with d = fp16 max and one with
+    a subnormal d.  Returns new block bytes (the oracle and the GPU then see identical weights)."""
+    from oracle_lib import TSIZE, BLCK
+    bs, nblk = TSIZE[t], k // BLCK[t]
+    blk = w.reshape(w.shape[0], nblk, bs).copy()
+    offs = {Q4_0: [0], Q5_0: [0], Q8_0: [0], Q4_1: [0, 2], Q5_1: [0, 2], Q2_K: [80, 82]}[t]
+    for o in offs:
+        h = blk[:, :, o:o + 2].copy().view(np.float16)
+        h = (h.astype(np.float32) * np.float32(scale)).astype(np.float16)
+        blk[:, :, o:o + 2] = h.view(np.uint8)
+    if rng is not None:
+        rows = np.arange(w.shape[0])
+        big = rng.integers(0, nblk, w.shape[0])
+        tiny = (big + 1 + rng.integers(0, nblk - 1, w.shape[0])) % nblk
+        blk[rows[::3], big[::3], offs[0]:offs[0] + 2] = np.array([65504.0], np.float16).view(np.uint8)
+        blk[rows[1::3], tiny[1::3], offs[0]:offs[0] + 2] = np.array([3e-7], np.float16).view(np.uint8)   # subnormal
+    return blk.reshape(w.shape[0], -1)
+
+
+@pytest.mark.parametrize("t", TC_TYPES + [Q2_K])
+@pytest.mark.parametrize("scale", [3e-5, 700.0, "planted"])
+def test_gemm_weight_scale_sweep(gpu, oracle, t, scale, gemm_mode):
+    """The reference's f32 path is range-safe for ANY fp16 block scale; so must the tensor-core paths be: weight
+    scales down to the fp16 subnormals and up to fp16 max (a fixed pre-scale used to overflow the hi/lo split
+    at |d q| 64 > 65504 and to lose the lo term for small d), rows that mix a huge and a tiny block."""
+    m, n, k = 200, 40, 1024
+    rng = np.random.default_rng(int(t) * 7 + 1)
+    w = weights(oracle, t, m, k, seed=t + 11)
+    w = rescale_blocks(t, w, k, 1.0, rng) if scale == "planted" else rescale_blocks(t, w, k, scale)
+    x = make_x(rng, n, k)
+    want = oracle.mul_mat(t, w, x)
+    assert np.isfinite(want).all()
+    got = gpu.mul_mat(t, dev(w), dev(x)).cpu().numpy()
+    assert np.isfinite(got).all(), f"{TYPE_NAMES[t]} scale {scale}: non-finite C"
+    # per weight row: a row's error is judged against that row's own magnitude (rows differ by 1e9 here)
+    for i in range(m):
+        tol = 1e-5 * np.sqrt(k) * max(float(np.abs(want[:, i]).max()), 1e-30)
+        assert np.abs(got[:, i] - want[:, i]).max() <= tol, f"{TYPE_NAMES[t]} scale {scale} row {i}"
+
+
+@pytest.mark.parametrize("scale", [1e-7, 1e4, 3e30, 1e-30])
+def test_gemm_f32_weight_range(gpu, oracle, scale, gemm_mode):
+    """F32 weights far outside fp16's range (|w| >= 1024 used to become inf in the hi/lo split)."""
+    m, n, k = 150, 20, 512
+    rng = np.random.default_rng(3)
+    w = (rng.standard_normal((m, k)) * scale).astype(np.float32)
+    w[::5] *= np.float32(1e-3)                                            # rows of very different magnitude
+    x = make_x(rng, n, k)
+    want = oracle.mul_mat(F32, w.view(np.uint8).reshape(m, -1), x)
+    got = gpu.mul_mat(F32, dev(w), dev(x)).cpu().numpy()
+    assert np.isfinite(got).all()
+    for i in range(m):
+        tol = 1e-5 * np.sqrt(k) * float(np.abs(want[:, i]).max())
+        assert np.abs(got[:, i] - want[:, i]).max() <= tol, f"f32 scale {scale} row {i}"
 
 
 def test_gemm_strided_output_and_weights(gpu, oracle):
