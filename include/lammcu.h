@@ -120,10 +120,13 @@ int lammcu_mul_mat_batch_dev(int w_type, int count, const void *const *w_dev,
  * memory-bound GEMV kernels, larger N the tensor-core GEMM.  Default 8.      */
 int lammcu_set_gemv_max_n(int n);
 int lammcu_get_gemv_max_n(void);
-/* Prefill (N > gemv_max_n) tensor-core kernel: 0 (default) = scaled-operand mainloop (scales folded
- * into bf16 hi/lo operand pairs, one accumulator over the whole K loop; error <= 2^-16 per product,
- * inside the path's 1e-5*sqrt(K) tolerance); 1 = exact per-32-block integer sums (bit-identical to the
- * reference's sumi), scaled on the CUDA cores, about half the throughput.                            */
+/* Prefill (N > gemv_max_n) tensor-core kernels.  Q2_K always runs on tcgen05 kind::i8 (scale-folded u8 x s8, one
+ * drain per 256-super-block, the min term as one extra int8 MMA: exact integer sums).  The 32-element formats:
+ *   0 (default)  scaled-operand mainloop (scales folded into fp16 hi/lo operand pairs, per-row power-of-two lifts on
+ *                both operands, one accumulator over the whole K loop; error <= 2^-22 per product, inside the
+ *                path's 1e-5*sqrt(K) tolerance);
+ *   1            exact per-32-block integer sums (bit-identical to the reference's sumi), scaled on the CUDA cores.
+ * Environment override at load time: LAMM_GEMM_EXACT.                                                          */
 int lammcu_set_gemm_exact(int on);
 int lammcu_get_gemm_exact(void);
 /* N == 1: 1 (default) = the single-launch decode kernel (fused activation

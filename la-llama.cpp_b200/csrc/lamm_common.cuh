@@ -200,6 +200,11 @@ int launch_dequant_hilo(int w_type, const void *w, int64_t w_stride, void *ah, v
                         int64_t Mpad, int64_t K, cudaStream_t st);
 int launch_prep_direct(int vt, const void *xq, int64_t xq_stride, void *xh, void *xl, float *colscale, int64_t N,
                        int64_t Npad, int64_t K, cudaStream_t st);
+// Q2_K prefill on tcgen05 kind::i8 (lamm_gemm_x.cu): exact integer sums, one drain per 256-super-block
+bool gemm_x_supported(int w_type, const void *w, int64_t w_stride, int64_t M, int64_t N, int64_t K);
+size_t gemm_x_ws_bytes(int64_t N, int64_t K);
+int launch_gemm_x(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c, int64_t ldc,
+                  int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st);
 void set_gemm_exact(int on);
 int get_gemm_exact();
 void *gemm_workspace(size_t bytes);      // library-owned scratch for the prefill GEMM (grown on demand)

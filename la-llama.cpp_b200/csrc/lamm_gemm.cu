@@ -419,6 +419,14 @@ static bool gemm_direct_supported(int w_type, const void *w, int64_t w_stride, c
 
 int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c,
                 int64_t ldc, int64_t M, int64_t N, int64_t K, cudaStream_t st) {
+  // Q2_K: the int8 fold is exact AND the fastest kernel, whatever the mode (LAMM_GEMM_Q2K_I8=0: the round-1
+  // dequantize-once path, for comparison)
+  static const int q2k_i8 = [] { const char *e = getenv("LAMM_GEMM_Q2K_I8"); return e ? atoi(e) : 1; }();
+  if (q2k_i8 && gemm_x_supported(w_type, w, w_stride, M, N, K) && (((uintptr_t)xq | (uintptr_t)xq_stride) & 3) == 0) {
+    void *ws = gemm_workspace(gemm_x_ws_bytes(N, K));
+    if (!ws) return LAMMCU_ERR_NOMEM;
+    return launch_gemm_x(w_type, w, w_stride, xq, xq_stride, c, ldc, M, N, K, ws, st);
+  }
   if (gemm_tc_supported(w_type, w, w_stride, M, N, K)) {
     if (!g_gemm_exact) {
       void *ws = gemm_workspace(gemm_so_ws_bytes(M, N, K));
