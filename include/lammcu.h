@@ -106,6 +106,22 @@ int lammcu_mul_mat_dev(int w_type, const void *w_dev, int64_t w_stride_bytes,
                        int64_t ldc, int64_t M, int64_t N, int64_t K,
                        void *xq_ws_dev, void *stream);
 
+/* No counterpart in the reference: added for callers that cannot allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The same result as
+ * lammcu_mul_mat_dev for 1 <= N <= 8 quantized-weight matmuls (activation quantize + GEMV), but the quantized-
+ * activation scratch lives in a static device array of LAMMCU_NOALLOC_MAX_SCRATCH bytes that every GPU loading the
+ * library holds until exit: the call performs no cudaMalloc / cudaFree and uses no library workspace.
+ *   - needs N * lammcu_row_size(lammcu_vec_dot_type(w_type), K) <= LAMMCU_NOALLOC_MAX_SCRATCH (e.g. N = 8 up to
+ *     K = 57344); larger requests fail with LAMMCU_ERR_SHAPE and a message; F32 weights (no scratch) are refused;
+ *   - lammcu_init must have been called before (it owns the library's only allocations); the first call per
+ *     process looks the array's device address up (cudaGetSymbolAddress, no allocation): make it outside capture;
+ *   - every call shares the one array and leaves its quantized rows there: calls that overlap on the GPU (two
+ *     streams, two host threads) race -- serialise them on one stream.  Nothing has to be cleared between calls.
+ * Asynchronous on `stream` (NULL = the library's stream).                                                        */
+#define LAMMCU_NOALLOC_MAX_SCRATCH (512 * 1024)
+int lammcu_mul_mat_noalloc_dev(int w_type, const void *w_dev, int64_t w_stride_bytes, const float *x_dev, int64_t ldx,
+                               float *c_dev, int64_t ldc, int64_t M, int64_t N, int64_t K, void *stream);
+
 /* N == 1, sibling matmuls: `count` weight matrices of the same type, K and row stride
  * that multiply the SAME activation row (wq/wk/wv, gate/up in llama.cpp's build_llama,
  * llama.cpp:5726-5800) -- C_j = W_j . x for every j.  Up to 4 of them run as ONE launch of

@@ -346,6 +346,61 @@ int lammcu_mul_mat_dev(int w_type, const void *w, int64_t w_stride, const float 
   return lammcu_mul_mat_q_dev(w_type, w, w_stride, xq_ws, (int64_t)rs, c, ldc, M, N, K, stream);
 }
 
+// ---- the no-allocation entry point (no counterpart in the reference) --
+// Same computation as lammcu_mul_mat_dev for 1 <= N <= 8 on the two-launch path (activation-quantize kernel ->
+// Xq scratch -> gemv_stream_kernel), but the Xq scratch is a file-scope device array instead of a cudaMalloc'ed
+// workspace: callers under CUDA graph capture, tight serving loops or harnesses that forbid allocation can use it.
+// Every GPU that loads the library holds the array until exit.  In host code `g_noalloc_xq` is only a host-side
+// stand-in for the symbol, not a device address: the device address is looked up once per device with
+// cudaGetSymbolAddress (that device current) and only that pointer is handed to kernels.
+constexpr size_t kNoAllocScratchBytes = LAMMCU_NOALLOC_MAX_SCRATCH;
+static __device__ __align__(256) unsigned char g_noalloc_xq[kNoAllocScratchBytes];
+static void *g_noalloc_ptr = nullptr;      // device address of g_noalloc_xq on device g_noalloc_dev
+static int g_noalloc_dev = -1;
+
+extern "C" int lammcu_mul_mat_noalloc_dev(int w_type, const void *w, int64_t w_stride, const float *x, int64_t ldx,
+                                          float *c, int64_t ldc, int64_t M, int64_t N, int64_t K, void *stream) {
+  // lammcu_init allocates (stream, scheduler counters): it must have happened before, not in here
+  if (!g_dev.inited) { set_error("mul_mat_noalloc: call lammcu_init first (this entry point allocates nothing)"); return LAMMCU_ERR_ARG; }
+  if (!w || !x || !c) { set_error("mul_mat_noalloc: NULL operand"); return LAMMCU_ERR_ARG; }
+  if (w_type == LAMMCU_TYPE_F32 || !lammcu_type_supported(w_type)) {
+    set_error("mul_mat_noalloc: type %d not supported (F32 weights need no scratch: use lammcu_mul_mat_dev)", w_type);
+    return LAMMCU_ERR_TYPE;
+  }
+  const TypeInfo ti = type_info(w_type);
+  if (M <= 0 || K <= 0 || K % ti.blck || N < 1 || N > 8) {
+    set_error("mul_mat_noalloc: bad shape M=%lld N=%lld K=%lld (1 <= N <= 8, K %% %d == 0)", (long long)M, (long long)N,
+              (long long)K, ti.blck);
+    return LAMMCU_ERR_SHAPE;
+  }
+  const size_t rs = lammcu_row_size(ti.vec_dot, K);
+  if (rs * (size_t)N > kNoAllocScratchBytes) {
+    set_error("mul_mat_noalloc: %lld rows of %zu quantized bytes need %zu bytes of scratch, the static array holds %zu",
+              (long long)N, rs, rs * (size_t)N, kNoAllocScratchBytes);
+    return LAMMCU_ERR_SHAPE;
+  }
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (g_noalloc_dev != g_dev.device) {
+      cudaError_t e = cudaSetDevice(g_dev.device);
+      void *ptr = nullptr;
+      if (e == cudaSuccess) e = cudaGetSymbolAddress(&ptr, g_noalloc_xq);
+      if (e != cudaSuccess || !ptr) {
+        set_error("mul_mat_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        return LAMMCU_ERR_CUDA;
+      }
+      g_noalloc_ptr = ptr;
+      g_noalloc_dev = g_dev.device;
+    }
+  }
+  cudaStream_t st = pick_stream(stream);
+  // nothing in the array has to start at zero: the quantize kernel writes every byte of the N rows it produces
+  // (Q8_K: bsums of all-zero super-blocks included), and the GEMV reads exactly those rows
+  int rc = launch_quantize_act(ti.vec_dot, x, ldx, g_noalloc_ptr, N, K, st);
+  if (rc) return rc;
+  return launch_gemv(w_type, w, w_stride, g_noalloc_ptr, (int64_t)rs, c, ldc, M, N, K, st);
+}
+
 // ---- row-sharded multi-GPU decode ---------------------------------------------------
 struct lammcu_comm {
   int rank, world;
