@@ -18,7 +18,7 @@
 //   warp 1       MMA issuer (one thread); tcgen05.commit hands accumulators to the drain and stages back
 //   warp 2       TMEM allocation (512 columns: a ring of 2 x {isum, summs})
 //   warps 4-11   weight unpack, thread = (row, half of the super-block): packed 2-bit quants * 4-bit scales -> u8
-//                bytes in the UMMA K-major SWIZZLE_128B layout; rows are read straight from global memory
+//                bytes in the UMMA K-major SWIZZLE_128B layout; the packed rows are staged by coalesced cp.async
 //   warps 12-27  drain, thread = TMEM lane (weight row) x 32 columns: tcgen05.ld, s32 -> f32, scale, accumulate
 //
 // Measured and removed (round 2): the same skeleton for the 32-element formats on kind::f16 with exact small
@@ -110,7 +110,9 @@ constexpr int kXB2Off = kXA2Off + 2 * kXTile;
 constexpr int kXDxOff = kXB2Off + 2 * kXTile;              // x.d      [ring][128 activation rows]
 constexpr int kXDwOff = kXDxOff + kXSRing * GN * 4;        // f(d)     [ring][128 weight rows]
 constexpr int kXMwOff = kXDwOff + kXSRing * GM * 4;        // f(dmin)  [ring][128 weight rows]
-constexpr int kXBarOff = kXMwOff + kXSRing * GM * 4;
+constexpr int kXRawOff = kXMwOff + kXSRing * GM * 4;        // raw packed super-blocks [2][128 rows][84 bytes]
+constexpr int kXRawUnit = GM * 84;
+constexpr int kXBarOff = kXRawOff + 2 * kXRawUnit;
 constexpr int kXTotal = kXBarOff + 512;
 
 // ---- Q2_K: one half (128 elements) of a super-block of the thread's row -> int8 operand bytes -----------
@@ -239,50 +241,58 @@ gemm_q2k_i8_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
   } else if (warp < 12) {
     // ===================== weight unpack: thread = (row, half of the super-block) =====================
     // Warps 4-7 turn the first half (elements 0..127) of every super-block of their 128 rows into stage 2u, warps
-    // 8-11 the second half into stage 2u + 1 and the min-term bytes.  Q2_K rows come straight from global memory
-    // (84-byte super-blocks: 4-byte aligned at best, row strides that are not multiples of 16 -- no TMA box), two
-    // super-blocks ahead in registers.
+    // 8-11 the second half into stage 2u + 1 and the min-term bytes.  (84-byte super-blocks are 4-byte aligned at
+    // best and row strides are not multiples of 16 for K % 1024 != 0 -- no TMA box: the warps stage them themselves.)
     const int h = (warp - 4) >> 2;
     const int r = (threadIdx.x - 128) & 127;
     const uint32_t r7 = (uint32_t)(r & 7);
     const uint32_t row_off = (uint32_t)(r >> 3) * 1024u + r7 * 128u;
-    const int m = m0 + r;
-    const bool live = m < p.M;
-    const uint32_t *wrow = reinterpret_cast<const uint32_t *>(p.w + (int64_t)(live ? m : 0) * p.w_stride);
-    // words of a super-block: [0, 4) scales, [4, 20) qs, 20 = {d, dmin}.  This thread needs the half's 8 qs words,
-    // all 4 scale words (h == 1 builds the min-term bytes from them) and, for h == 0, the {d, dmin} word.
-    auto fetch = [&](int u, uint32_t (&qs)[8], uint32_t (&sc)[4], uint32_t &dd) {
-      const uint32_t *b = wrow + (size_t)u * 21;
-      if (live && u < n_units) {
+    // Raw weights: a warp copies 16 rows per super-block, lanes 0..20 one 32-bit word each (cp.async, 84 contiguous
+    // bytes = 1-2 cache lines per instruction), into a staging slot whose 21-word row pitch is conflict-free for
+    // the per-row reads that follow.  (A first version had every thread __ldg its own row: 32 cache lines per
+    // warp-load, 13 loads per unit -- the L1 data pipe was 60 % busy with them and the kernel ran at 365-627 TOPS.)
+    // Rows beyond M re-read row M - 1 (their TMEM lanes are never stored).  Two slots: unit u + 2 is requested as
+    // soon as every thread has its words of unit u in registers.
+    const int uw = warp - 4;                                      // 0..7: rows 16 uw .. 16 uw + 15
+    const uint32_t raw_a = smem_u32(smem + kXRawOff);
+    // rows of this warp that exist; the copy pointer steps by the row stride only while the next row exists
+    const int rows_valid = max(1, min(16, p.M - (m0 + 16 * uw)));
+    const uint8_t *ubase = p.w + (int64_t)min(m0 + 16 * uw, p.M - 1) * p.w_stride + lane * 4;    // unit 0, row 0 of the warp
+    const uint32_t dst0 = raw_a + (uint32_t)(16 * uw * 84 + lane * 4);
+    const int64_t wstride = p.w_stride;
+    auto request = [&](int u) {
+      if (u < n_units && lane < 21) {
+        const uint8_t *src = ubase + (int64_t)u * 84;
+        const uint32_t dst = dst0 + (uint32_t)((u & 1) * kXRawUnit);
 #pragma unroll
-        for (int i = 0; i < 4; i++) sc[i] = __ldg(b + i);
-#pragma unroll
-        for (int i = 0; i < 8; i++) qs[i] = __ldg(b + 4 + 8 * h + i);
-        dd = __ldg(b + 20);
-      } else {
-#pragma unroll
-        for (int i = 0; i < 4; i++) sc[i] = 0u;
-#pragma unroll
-        for (int i = 0; i < 8; i++) qs[i] = 0u;
-        dd = 0u;
+        for (int i = 0; i < 16; i++) {
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + (uint32_t)(i * 84)), "l"(src) : "memory");
+          src += (i + 1 < rows_valid) ? wstride : 0;
+        }
       }
+      asm volatile("cp.async.commit_group;" ::: "memory");        // every thread commits (possibly empty) groups
     };
-    uint32_t qa[8], sa[4], da, qb[8], sb[4], db;
-    fetch(0, qa, sa, da);
-    fetch(1, qb, sb, db);
+    request(0);
+    request(1);
     for (int u = 0; u < n_units; u++) {
+      asm volatile("cp.async.wait_group 1;" ::: "memory");        // this thread's copies of unit u have landed
+      asm volatile("bar.sync 1, 256;" ::: "memory");              // ... and everybody else's
+      // words of a super-block: [0, 4) scales, [4, 20) qs, 20 = {d, dmin}.  This thread needs the half's 8 qs words,
+      // all 4 scale words (h == 1 builds the min-term bytes from them) and, for h == 0, the {d, dmin} word.
       uint32_t qs[8], sc[4], dd;
+      const uint32_t rb = raw_a + (uint32_t)((u & 1) * kXRawUnit + r * 84);
 #pragma unroll
-      for (int i = 0; i < 8; i++) { qs[i] = qa[i]; qa[i] = qb[i]; }
+      for (int i = 0; i < 4; i++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(sc[i]) : "r"(rb + 4u * i));
 #pragma unroll
-      for (int i = 0; i < 4; i++) { sc[i] = sa[i]; sa[i] = sb[i]; }
-      dd = da; da = db;
-      fetch(u + 2, qb, sb, db);
+      for (int i = 0; i < 8; i++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(qs[i]) : "r"(rb + 16u + 32u * h + 4u * i));
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(dd) : "r"(rb + 80u));
+      asm volatile("bar.sync 2, 256;" ::: "memory");              // the slot has been read by all: refill it
+      request(u + 2);
       const int st = 2 * u + h, s = st % S;
       const int g = u >> 2, mt = g & 1, q = u & 3;
       if (h == 1 && q == 0) mbar_wait(&m_empty[mt], ((uint32_t)(g >> 1) & 1u) ^ 1u);
       mbar_wait(&empty[s], ((uint32_t)(st / S) & 1u) ^ 1u);
-      const uint32_t sch[2] = {sc[2 * h], sc[2 * h + 1]};
+      const uint32_t sch[2] = {h ? sc[2] : sc[0], h ? sc[3] : sc[1]};     // (a run-time index would put sc[] in local memory)
       q2k_half_to_i8(qs, sch, smem_u32(smem + kXAOff + s * kXTile) + row_off, r7);
       if (h == 0) {
         const uint32_t slot = (uint32_t)((u % R) * GM + r) * 4u;
@@ -337,7 +347,8 @@ gemm_q2k_i8_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 #pragma unroll
         for (int c = 0; c < 4; c++) {
           const float4 xd = lds_f4(dx_a + 16u * (4 * hh + c));
-          // C += x.d * (d * isum - dmin * summs): src/lamm_kernel_q2_k.hpp:68-74 regrouped; the integers are exact
+          // C += x.d * (d * isum - dmin * summs): src/lamm_kernel_q2_k.hpp:68-74 regrouped; the integers are exact.
+          // (s32 -> f32 by I2FP: a magic-number conversion that keeps the XU pipe free measured 6 % SLOWER.)
           float2 t0 = fmul2s(wd, make_float2((float)(int)i1[4 * c], (float)(int)i1[4 * c + 1]));
           float2 t1 = fmul2s(wd, make_float2((float)(int)i1[4 * c + 2], (float)(int)i1[4 * c + 3]));
           t0 = ffma2s(wm, make_float2((float)(int)i2[4 * c], (float)(int)i2[4 * c + 1]), t0);
