@@ -348,7 +348,8 @@ gemm_q2k_i8_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         for (int c = 0; c < 4; c++) {
           const float4 xd = lds_f4(dx_a + 16u * (4 * hh + c));
           // C += x.d * (d * isum - dmin * summs): src/lamm_kernel_q2_k.hpp:68-74 regrouped; the integers are exact.
-          // (s32 -> f32 by I2FP: a magic-number conversion that keeps the XU pipe free measured 6 % SLOWER.)
+          // (s32 -> f32 by I2FP on the XU pipe.  A magic-number conversion -- as_float(v + 0x4B400000) - 1.5 * 2^23 on the
+          // ALU / FMA pipes -- for both sums or for summs only measured within +-2 %: profiles/r2l/.)
           float2 t0 = fmul2s(wd, make_float2((float)(int)i1[4 * c], (float)(int)i1[4 * c + 1]));
           float2 t1 = fmul2s(wd, make_float2((float)(int)i1[4 * c + 2], (float)(int)i1[4 * c + 3]));
           t0 = ffma2s(wm, make_float2((float)(int)i2[4 * c], (float)(int)i2[4 * c + 1]), t0);
