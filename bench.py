@@ -473,10 +473,15 @@ def run_cuda(args):
     g_full, launches_per_token = capture(one_token)
     sampler = ClockSampler(local)
     if rank == 0:
-        sampler.start()
+        sampler.start()               # runs across warm-up, the timed region, the sustained run, the gemm and e2e legs
     ms = timed(g_full, args.steps, max(args.warmup, 3))
-    clocks = sampler.stop() if rank == 0 else None
     tok_s = args.steps / (ms * 1e-3)
+    # the same graph for >= 2 s back to back: what the part sustains once clocks and power have settled
+    sustained = None
+    if args.sustain_s > 0:
+        n_sus = max(args.steps, int(args.sustain_s * tok_s))
+        ms_sus = timed(g_full, n_sus, 0)
+        sustained = {"value": n_sus / (ms_sus * 1e-3), "unit": "tok/s", "steps": n_sus, "seconds": ms_sus * 1e-3}
     # the chain's final output must be finite (unit-gain weights) and, with N>1, no poll may have timed out
     logits = comm.unpack(torch, buf["logits"]) if fused else buf["logits"].view(-1)
     torch.cuda.synchronize()
@@ -485,6 +490,22 @@ def run_cuda(args):
     if fused and comm.timed_out():
         raise SystemExit("bench: a peer poll timed out")
     logit_rms = float(logits.float().pow(2).mean().sqrt().item())
+    # ... and RIGHT: the chain once more without CUDA graph, sibling batching, PDL overlap or LL vectors -- one plain
+    # lammcu_mul_mat_dev per matmul on fresh buffers -- must give the same logits (a stale tag, a WAR on the reused
+    # activation vectors under graph replay or a mis-addressed sibling batch would still be finite)
+    chain_check = None
+    if world == 1:
+        ref_buf = {k_: torch.zeros((1, {"g": F, "u": F, "logits": V}.get(k_, H)), device=dev) for k_ in buf}
+        for wi, m, k, src, dst in plan:
+            wv = weights[wi] if t != 0 else weights[wi].view(torch.float32)
+            L.mul_mat(t, wv, x0 if src is None else ref_buf[src], out=ref_buf[dst])
+            torch.cuda.synchronize()
+        want = ref_buf["logits"].view(-1)
+        err = float((logits.float() - want).abs().max().item())
+        tol = 1e-5 * float(np.sqrt(H)) * float(want.abs().max().item()) * 8     # 225 chained matmuls: a few ulps of drift
+        chain_check = {"max_abs_err": err, "tol": tol, "vs": "un-batched, un-graphed lammcu_mul_mat_dev per matmul"}
+        if not err <= tol:
+            raise SystemExit("bench: the timed chain's logits differ from the plain chain: %g > %g" % (err, tol))
 
     # roofline of the dominant kernel (decode16_kernel, the ONLY kernel of the step at N=1): the
     # algorithmic bytes of this rank's launches (W blocks + f32 X + f32 C) over the average
@@ -500,9 +521,19 @@ def run_cuda(args):
     if args.host_mode is not None:
         L.lib().lammcu_set_host_mode(args.host_mode)
     e2e = None
-    if not args.no_e2e:
-        e2e = e2e_run(torch, L, t, ops, weights, shard, max(3, args.steps // 10), dist, dev, rank, world)
+    if not args.no_e2e and world == 1:
+        e2e = e2e_run(torch, L, t, ops, weights, shard, max(50, args.steps // 4), dist, dev, rank, world)
+    elif not args.no_e2e:
+        # ggml needs the whole C on the caller's host after every matmul; the row-sharded operator path returns each
+        # rank's slice only, so there is no honest end-to-end number at N > 1: it is left out rather than reported
+        # on 1/N of the result
+        e2e = {"value": None, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+               "unavailable": "the host operator is single-GPU; the sharded path is device-resident (value)"}
 
+    gemm = None
+    if world == 1 and rank == 0 and not args.no_gemm:
+        gemm = gemm_block(torch, L, dev, args)
+    clocks = sampler.stop() if rank == 0 else None
     if rank != 0:
         return finish(dist)
 
@@ -533,6 +564,8 @@ def run_cuda(args):
                             "avg %.2f us and %.2f MB per launch"
                             % (launches_q, ms * 1e3 / args.steps / max(launches_q, 1),
                                kern_bytes / max(launches_q, 1) / 1e6)},
+        "sustained": sustained, "chain_check": chain_check,
+        "gemm": gemm,
         "cpu_baseline": cpu,
         "e2e": e2e,
         "gpu_launches": launches_per_token * args.steps, "logits_rms": logit_rms,
@@ -540,6 +573,86 @@ def run_cuda(args):
     }
     print(json.dumps(line))
     return finish(dist)
+
+
+# measured on this pool's B200s with tools/i8peak.cu (tcgen05.mma kind::i8 / kind::f16, M128 x N256, operands resident
+# in shared memory, all 148 SMs; profiles/r2g/i8peak.txt, re-measured in profiles/r2k/): the GEMM fractions' denominators
+INT8_TOPS_MEASURED = 4563.3
+F16_TOPS_MEASURED = 2220.9
+
+
+def gemm_block(torch, L, dev, args):
+    """The prefill third of BASELINE.json's metric ("GEMM TOPS vs roofline") in the driver's record: the two prefill
+    configurations BASELINE names that fit one GPU -- LLaMA-13B Q4_1 N = 2048 (13824 x 5120, config 4) and LLaMA-7B
+    Q2_K N = 512 (11008 x 4096, config 3) -- through lammcu_mul_mat_dev (activation quantize + operand prep + tcgen05
+    GEMM, all inside the timed region), a ring of distinct weight matrices > L2 replayed from one CUDA graph, CUDA
+    events.  TOPS = 2 M N K / time, as the reference counts flops (src/la-benchmark-matmult.cpp:331-332).  Beside
+    them the reference's own CPU path at config 1's GEMM points: its benchmark's fixed shape K = 11008 M = 4096
+    N = 128 (src/la-benchmark-matmult.cpp:180-182) and 4096 x 4096 x 512."""
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(99)
+    out = {"unit": "TOPS", "int8_peak_tops_measured": INT8_TOPS_MEASURED, "f16_peak_tflops_measured": F16_TOPS_MEASURED,
+           "peak_source": "tools/i8peak.cu on this pool (profiles/r2g/i8peak.txt)", "cases": []}
+    for fmt, m, k, n, kind in (("q4_1", 13824, 5120, 2048, "tcgen05 kind::f16, 3 MMAs per product (scaled fp16 hi/lo operands)"),
+                               ("q2_k", 11008, 4096, 512, "tcgen05 kind::i8 (scale-folded u8 x s8, exact integer sums)")):
+        t = TYPE_IDS[fmt]
+        wb = m * w_row_bytes(t, k)
+        ring = max(2, min(16, (256 * (1 << 20) + wb - 1) // wb))
+        ws = [synth_weight(torch, t, m, k, gen, dev) for _ in range(ring)]
+        x = torch.randn((n, k), generator=gen, device=dev)
+        c = torch.zeros((n, m), device=dev)
+
+        def body():
+            for w in ws:
+                L.mul_mat(t, w, x, out=c)
+        s_ = torch.cuda.Stream()
+        s_.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s_):
+            body()
+        torch.cuda.current_stream().wait_stream(s_)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        L.lib().lammcu_launch_count_reset()
+        with torch.cuda.graph(g):
+            body()
+        launches = int(L.lib().lammcu_launch_count()) // ring
+        for _ in range(3):
+            g.replay()
+        torch.cuda.synchronize()
+        reps = max(3, 200 // ring)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / (reps * ring)
+        tops = 2.0 * m * n * k / us / 1e6
+        if not bool(torch.isfinite(c).all().item()):
+            raise SystemExit("bench gemm: non-finite C (%s)" % fmt)
+        out["cases"].append({"fmt": fmt, "M": m, "K": k, "N": n, "us": round(us, 2), "TOPS": round(tops, 1),
+                             "frac_int8_peak_measured": round(tops / INT8_TOPS_MEASURED, 4),
+                             "frac_f16_peak_measured": round(tops / F16_TOPS_MEASURED, 4),
+                             "tensor_path": kind, "launches_per_matmul": launches, "distinct_weights": ring,
+                             "includes": "activation quantize + operand prep + GEMM"})
+        del ws, g
+        torch.cuda.empty_cache()
+    if not args.no_cpu:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            from oracle_lib import Ref
+            if Ref.available():
+                r = Ref()
+                nth = host_threads()
+                cpu = []
+                for (m, k, n, why) in ((4096, 11008, 128, "la-benchmark-matmult's fixed shape"), (4096, 4096, 512, "config 1")):
+                    us_ = float(np.mean(r.bench(TYPE_IDS["q4_1"], m, n, k, nth, 4)[1:]))
+                    cpu.append({"fmt": "q4_1", "M": m, "K": k, "N": n, "us": round(us_, 1),
+                                "gflops": round(2.0 * m * n * k / us_ / 1e3, 1), "cores": nth, "kind": "reference", "why": why})
+                out["cpu_baseline"] = cpu
+        except Exception as e:
+            out["cpu_baseline"] = [{"kind": "unavailable", "why": str(e)}]
+    return out
 
 
 def finish(dist):
@@ -559,13 +672,11 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
     timed region, exactly once -- they are immutable model state; X goes H2D and C comes D2H inside
     every call."""
     lib = L.lib()
-    # host copies of a bounded set of distinct weights: one layer + head, cycled (host RAM, not HBM,
-    # is what limits holding 4 GB twice); the device-side registry still holds them as distinct buffers
-    host_w = {}
-    n_layer = len(LAYER_SHAPES)
-    idx_for = list(range(n_layer)) * LAYERS + [len(ops) - 1]
-    for i in set(idx_for):
-        host_w[i] = weights[i].cpu().numpy()
+    # host copies of ALL the chain's weight matrices (225 distinct host buffers, 4.13 GB for 7B Q4_1): the operator's
+    # registry is keyed by the host pointer, so the device then really holds 225 distinct buffers and every call
+    # streams its weights from HBM, as config.l2_defeat says
+    idx_for = list(range(len(ops)))
+    host_w = {i: weights[i].cpu().numpy() for i in idx_for}
     # activation rows as a ggml graph has them: one src1 tensor per producer -- wq/wk/wv share the
     # attention-norm output, gate/up share the ffn-norm output, wo / down / head have their own
     rng_x = np.random.default_rng(3)
@@ -617,6 +728,23 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
     token()          # uploads the weights
     token()
     torch.cuda.synchronize()
+    # the leg's results are checked, not just timed: a sample of the calls against the device-resident entry point
+    # on the same weights and the same activation row (same kernels underneath: must agree to f32 noise)
+    checked = 0
+    for ci in sorted(set([0, 3, 6, len(keep) // 2, len(keep) - 2, len(keep) - 1])):
+        name, m, k = ops[ci]
+        if not can(*calls[ci]):
+            raise RuntimeError("lamm_can_mul_mat refused the bench shape")
+        mm(*calls[ci])
+        got = ch[m][0, :weights[ci].shape[0]].copy()
+        want = L.mul_mat(t, weights[ci] if t != 0 else weights[ci].view(torch.float32),
+                         torch.from_numpy(xh[x_of[name]]).to(dev)).cpu().numpy()[0]
+        tol = 1e-5 * np.sqrt(k) * float(np.abs(want).max())
+        if not np.abs(got - want).max() <= tol:
+            raise SystemExit("bench e2e: operator result of call %d (%s) differs from the device path: %g > %g"
+                             % (ci, name, float(np.abs(got - want).max()), tol))
+        checked += 1
+    torch.cuda.synchronize()
     if dist:
         dist.barrier()
     prof = (C.c_double * 8)()
@@ -653,8 +781,8 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
                       if lib.lammcu_get_host_mode() == 1 else
 
                       "copy-engine H2D + one launch + stream synchronize per call"),
-            "note": "weights uploaded once at first use (registry keyed by src0->data); with N>1 the "
-                    "per-rank C slices are not gathered in this leg"}
+            "distinct_host_weight_buffers": len(host_w), "results_checked_against_device_path": checked,
+            "note": "weights uploaded once at first use (registry keyed by src0->data, leaf tensors only)"}
 
 
 # ---- per-format / per-shape sweep (not the driver's line; writes a table for profiles/) ----
@@ -795,6 +923,8 @@ def main():
     ap.add_argument("--fmt", default="q4_1", choices=sorted(f for f, t in TYPE_IDS.items() if t == 0 or t in _QVAR))
     ap.add_argument("--model", default="7b", choices=sorted(MODELS), help="chain shapes (the metric is quoted on 7b)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-gemm", action="store_true", help="skip the prefill GEMM block of the line")
+    ap.add_argument("--sustain-s", type=float, default=2.0, help="seconds of back-to-back replay for the sustained value (0: skip)")
     ap.add_argument("--no-e2e", action="store_true",
                     help="skip the e2e leg (profiler runs only: ncu replays kernels, the resident server talks to the host)")
     ap.add_argument("--host-mode", type=int, default=None, choices=[0, 1],
