@@ -68,6 +68,8 @@ ACT_SIZE = {0: (1, 4), 8: (32, 34), 9: (32, 36), 15: (256, 292)}
 # q4_1: profiles/r1_launches_bench.csv -- 903 launches of decode16_kernel<q4_1>, 32.075 MB read + 0.002 MB written on
 # average against 32.09 MB algorithmic (ratio 0.9995: every weight byte crosses DRAM once, C and X stay in L2)
 TRAFFIC_PER_LAUNCH = {"q4_1": 32.077e6}
+# the persistent chain kernel: one launch per token (filled in from profiles/ once captured)
+TRAFFIC_PER_CHAIN_LAUNCH = {}
 
 
 def chain_ops():
@@ -402,7 +404,16 @@ def run_cuda(args):
         else:
             groups.append([item])
 
+    chain = None
+    if args.chain == "persistent" and world == 1 and t != 0:
+        # ONE persistent launch per token (lammcu_chain_*): the same groups, separated by an in-kernel grid barrier
+        chain = L.Chain(t, [([weights[g[0]] for g in grp], x0 if grp[0][3] is None else buf[grp[0][3]],
+                             [buf[g[4]] for g in grp]) for grp in groups])
+
     def one_token():
+        if chain is not None:
+            chain.run()
+            return
         if args.batch and fused:
             for grp in groups:
                 xin = x0 if grp[0][3] is None else buf[grp[0][3]]
@@ -556,8 +567,8 @@ def run_cuda(args):
                                              sibling_batching=bool(args.batch and (fused or world == 1) and t != 0)),
         "path_gbs": path_bytes * args.steps / (ms * 1e-3) / 1e9,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": TRAFFIC_PER_LAUNCH.get(args.fmt) if world == 1 else None,
-                     "kernel": "lamm::decode16_kernel<%s>" % args.fmt,
+                     "traffic": (TRAFFIC_PER_CHAIN_LAUNCH.get(args.fmt) if chain is not None else TRAFFIC_PER_LAUNCH.get(args.fmt)) if world == 1 else None,
+                     "kernel": "lamm::decode_chain_kernel<%s>" % args.fmt if chain is not None else "lamm::decode16_kernel<%s>" % args.fmt,
                      "peak_source": peak_src,
                      "how": "the timed chain itself (every launch of the step is this kernel, activation quantize "
                             "fused), CUDA events; bytes = W blocks + f32 X + f32 C per launch; %d launches/step, "
@@ -931,9 +942,10 @@ def main():
                     help="e2e leg: completion mode of the host path (lammcu_set_host_mode; default: the library's)")
     ap.add_argument("--no-batch", dest="batch", action="store_false",
                     help="N=1: one launch per matmul (225/token) instead of one per sibling group (129/token)")
-    ap.add_argument("--chain", default="plain", choices=["plain", "ll"],
-                    help="N=1: activation vectors between matmuls as plain f32 (ggml layout, kernel boundary = "
-                         "dependency) or as LL {value, tag} vectors (dependency carried by the data)")
+    ap.add_argument("--chain", default="plain", choices=["plain", "persistent", "ll"],
+                    help="N=1: plain (default) = one PDL-chained launch per sibling group, plain f32 vectors; persistent = "
+                         "the token's matmuls as ONE launch (lammcu_chain_*; measured 13 %% slower: DESIGN d1); "
+                         "ll = LL {value, tag} vectors")
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
                     help="N>1: how C slices reach every rank (peer-store epilogue, or ncclAllGather per matmul)")
     ap.add_argument("--suite", default=None, choices=[None, "gemv", "gemm"], help="per-format sweep instead of the bench line")

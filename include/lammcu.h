@@ -132,6 +132,33 @@ int lammcu_mul_mat_batch_dev(int w_type, int count, const void *const *w_dev,
                              int64_t w_stride_bytes, const int64_t *M, const float *x_dev,
                              float *const *c_dev, int64_t K, void *xq_ws_dev, void *stream);
 
+/* N == 1, a CHAIN of dependent matmuls as ONE persistent launch (the same extension class as the sibling batch above;
+ * in llama.cpp's build_llama, llama.cpp:5726-5800, a decoded token is such a chain: q,k,v = W x; o = Wo v; g,u = W o;
+ * x' = Wd u; ...).  Op i multiplies 1..4 sibling matrices (one type, K and row stride) with the activation row x_dev
+ * and writes c_dev[j]; ops run in order and an op may read what earlier ops wrote -- a grid-wide barrier separates
+ * them inside the kernel.  Every warp's weight stream runs ahead across op boundaries (weights are immutable), so
+ * HBM does not idle while an op waits for its activations.  Results are identical to one lammcu_mul_mat_dev /
+ * lammcu_mul_mat_batch_dev call per op (same per-row arithmetic).
+ *   lammcu_chain_create   validates and uploads the op table (allocates: do it once, outside graph capture);
+ *   lammcu_chain_run_dev  one memset node + one cooperative launch on `stream` (grid = SM count: the GPU must be able
+ *                         to hold one CTA per SM at once; a resident decode server on the library's stream is stopped);
+ *   lammcu_chain_status   *timed_out = 1 if a barrier poll gave up after ~2 s (synchronous D2H read).
+ * The pointers in the table must stay valid until lammcu_chain_destroy.                                            */
+typedef struct {
+  int count;                  /* 1..4 matrices sharing the activation row */
+  const void *w_dev[4];
+  int64_t M[4];
+  float *c_dev[4];
+  const float *x_dev;         /* K f32 */
+  int64_t K;
+  int64_t w_stride_bytes;
+} lammcu_chain_op;
+typedef struct lammcu_chain *lammcu_chain_t;
+int lammcu_chain_create(int w_type, int n_ops, const lammcu_chain_op *ops, lammcu_chain_t *out);
+int lammcu_chain_run_dev(lammcu_chain_t chain, void *stream);
+int lammcu_chain_status(lammcu_chain_t chain, int *timed_out);
+int lammcu_chain_destroy(lammcu_chain_t chain);
+
 /* Path selection (diagnostics / benchmarking): N <= threshold runs the
  * memory-bound GEMV kernels, larger N the tensor-core GEMM.  Default 8.      */
 int lammcu_set_gemv_max_n(int n);

@@ -36,7 +36,7 @@ EXPORTS = [
     "lammcu_blck_size", "lammcu_type_size", "lammcu_vec_dot_type", "lammcu_row_size",
     "lammcu_quantize_act_dev", "lammcu_mul_mat_q_dev", "lammcu_mul_mat_dev", "lammcu_set_gemv_max_n",
     "lammcu_get_gemv_max_n", "lammcu_set_decode_kernel", "lammcu_get_decode_kernel", "lammcu_set_trace", "lammcu_ipc_alloc", "lammcu_ipc_open", "lammcu_ipc_close", "lammcu_ipc_free", "lammcu_memcpy_async",
-    "lammcu_mul_mat_batch_dev", "lammcu_mul_mat_noalloc_dev", "lammcu_set_gemm_exact", "lammcu_get_gemm_exact", "lammcu_host_profile", "lammcu_set_host_mode", "lammcu_get_host_mode", "lammcu_host_quiesce", "lammcu_set_server_timeouts", "lammcu_server_trace", "lammcu_comm_create", "lammcu_comm_destroy", "lammcu_comm_status", "lammcu_ll_bytes", "lammcu_mul_mat_sharded_dev", "lammcu_mul_mat_sharded_batch_dev", "lammcu_mul_mat_sharded_gemm_dev", "lammcu_ll_unpack_dev", "lammcu_weight_register", "lammcu_weight_for_op", "lammcu_weight_lookup", "lammcu_weight_release", "lammcu_weight_forget", "lammcu_weight_forget_all",
+    "lammcu_mul_mat_batch_dev", "lammcu_mul_mat_noalloc_dev", "lammcu_chain_create", "lammcu_chain_run_dev", "lammcu_chain_status", "lammcu_chain_destroy", "lammcu_set_gemm_exact", "lammcu_get_gemm_exact", "lammcu_host_profile", "lammcu_set_host_mode", "lammcu_get_host_mode", "lammcu_host_quiesce", "lammcu_set_server_timeouts", "lammcu_server_trace", "lammcu_comm_create", "lammcu_comm_destroy", "lammcu_comm_status", "lammcu_ll_bytes", "lammcu_mul_mat_sharded_dev", "lammcu_mul_mat_sharded_batch_dev", "lammcu_mul_mat_sharded_gemm_dev", "lammcu_ll_unpack_dev", "lammcu_weight_register", "lammcu_weight_for_op", "lammcu_weight_lookup", "lammcu_weight_release", "lammcu_weight_forget", "lammcu_weight_forget_all",
     "lammcu_weight_dev_ptr", "lammcu_weight_rows", "lammcu_mul_mat_host", "lammcu_mul_mat_q_host",
     "lamm_can_mul_mat", "lamm_mul_mat", "lamm_get_opt_level", "lamm_set_writeback_wdata",
     "lammcu_mul_mat_id_plan", "lamm_can_mul_mat_id", "lamm_mul_mat_id",
@@ -69,6 +69,12 @@ GgmlTensor._fields_ = [
     ("view_src", C.POINTER(GgmlTensor)), ("view_offs", C.c_size_t),
     ("data", C.c_void_p), ("name", C.c_char * 64), ("extra", C.c_void_p), ("padding", C.c_char * 8),
 ]
+
+class ChainOp(C.Structure):
+    """lammcu_chain_op (include/lammcu.h)"""
+    _fields_ = [("count", C.c_int), ("w_dev", C.c_void_p * 4), ("M", C.c_int64 * 4), ("c_dev", C.c_void_p * 4),
+                ("x_dev", C.c_void_p), ("K", C.c_int64), ("w_stride_bytes", C.c_int64)]
+
 
 _lib = None
 
@@ -104,6 +110,10 @@ def lib():
     L.lammcu_mul_mat_q_dev.argtypes = [C.c_int, vp, i64, vp, i64, fp, i64, i64, i64, i64, vp]
     L.lammcu_mul_mat_dev.argtypes = [C.c_int, vp, i64, fp, i64, fp, i64, i64, i64, i64, vp, vp]
     L.lammcu_mul_mat_noalloc_dev.argtypes = [C.c_int, vp, i64, fp, i64, fp, i64, i64, i64, i64, vp]
+    L.lammcu_chain_create.argtypes = [C.c_int, C.c_int, C.POINTER(ChainOp), C.POINTER(vp)]
+    L.lammcu_chain_run_dev.argtypes = [vp, vp]
+    L.lammcu_chain_status.argtypes = [vp, C.POINTER(C.c_int)]
+    L.lammcu_chain_destroy.argtypes = [vp]
     L.lammcu_set_gemv_max_n.argtypes = [C.c_int]
     L.lammcu_set_decode_kernel.argtypes = [C.c_int]
     L.lammcu_set_trace.argtypes = [vp, i64]
@@ -263,6 +273,43 @@ def mul_mat_batch(w_type, ws, x, outs):
 
 
 # ---- the drop-in operator on host (numpy) tensors, as ggml would call it -------------
+class Chain:
+    """lammcu_chain_*: a list of dependent N == 1 mul_mats as one persistent launch.  ops: list of
+    (weights, x, outs): weights = list of 1..4 uint8 [M_j, row bytes] device tensors of one type / K, x = f32 [1, K]
+    device tensor, outs = list of f32 [1, M_j] device tensors.  The tensors must outlive the chain."""
+
+    def __init__(self, w_type, ops):
+        L = lib()
+        self._keep = ops
+        arr = (ChainOp * len(ops))()
+        for i, (ws, x, outs) in enumerate(ops):
+            assert 1 <= len(ws) <= 4 and len(ws) == len(outs)
+            arr[i].count = len(ws)
+            for j, (w, o) in enumerate(zip(ws, outs)):
+                assert w.is_cuda and o.is_cuda and o.is_contiguous() and w.stride(-1) == 1
+                arr[i].w_dev[j] = w.data_ptr()
+                arr[i].M[j] = w.shape[0]
+                arr[i].c_dev[j] = o.data_ptr()
+            arr[i].x_dev = x.data_ptr()
+            arr[i].K = x.shape[-1]
+            arr[i].w_stride_bytes = ws[0].stride(0) * ws[0].element_size()
+        self.h = C.c_void_p()
+        check(L.lammcu_chain_create(w_type, len(ops), arr, C.byref(self.h)), "lammcu_chain_create")
+
+    def run(self):
+        check(lib().lammcu_chain_run_dev(self.h, _stream_ptr()), "lammcu_chain_run_dev")
+
+    def timed_out(self):
+        v = C.c_int(0)
+        check(lib().lammcu_chain_status(self.h, C.byref(v)), "lammcu_chain_status")
+        return bool(v.value)
+
+    def close(self):
+        if self.h:
+            lib().lammcu_chain_destroy(self.h)
+            self.h = None
+
+
 def make_tensor_2d(ttype, ne0, ne1, data_ptr, nb1=None):
     t = GgmlTensor()
     t.type = ttype

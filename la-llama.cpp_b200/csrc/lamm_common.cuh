@@ -172,6 +172,20 @@ struct BatchInfo {
 int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
                   float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh = nullptr,
                   const BatchInfo *bt = nullptr);
+// persistent decode chain (lamm_decode.cu): a list of N == 1 mul_mats, each possibly a sibling batch, run by ONE launch
+struct ChainOp {
+  int count;                 // 1..4 matrices that share the activation row
+  const void *w[4];
+  int64_t M[4];
+  float *c[4];
+  const float *x;
+  int64_t K, w_stride;
+};
+struct ChainPlan;            // opaque: device-side stage table + launch geometry
+int chain_create(int w_type, int n_ops, const ChainOp *ops, ChainPlan **out);
+int chain_run(ChainPlan *plan, cudaStream_t st);
+void chain_destroy(ChainPlan *plan);
+int chain_status(ChainPlan *plan, int *timed_out);
 int launch_gemm_prep(int vt, int perm, const void *xq, int64_t xq_stride, void *x16, float *dxT, float *sxT,
                      int64_t N, int64_t Npad, int64_t K, cudaStream_t st);
 int launch_gemm_prep_so(int vt, int perm, const void *xq, int64_t xq_stride, void *xh, void *xl, void *sh, float *colscale,

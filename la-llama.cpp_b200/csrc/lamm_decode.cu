@@ -22,6 +22,7 @@
 #include "lamm_quant_dev.cuh"
 
 #include <algorithm>
+#include <vector>
 #include <cstdlib>
 
 namespace lamm {
@@ -245,6 +246,12 @@ __device__ __forceinline__ void load_x8(const DecodeParams &p, size_t e, unsigne
                     __uint_as_float((unsigned int)v[2]), __uint_as_float((unsigned int)v[3]));
     b = make_float4(__uint_as_float((unsigned int)v[4]), __uint_as_float((unsigned int)v[5]),
                     __uint_as_float((unsigned int)v[6]), __uint_as_float((unsigned int)v[7]));
+  } else if constexpr (XM == 3) {
+    // persistent chain kernel: x was written by OTHER CTAs of the same launch a moment ago and this SM's L1 may still
+    // hold the buffer's previous contents (the activation vectors are reused across stages): read through L2
+    const float *xp = p.x + e;
+    asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "l"(xp) : "memory");
+    asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(xp + 4) : "memory");
   } else {
     const float4 *xp = reinterpret_cast<const float4 *>(p.x + e);
     a = xp[0];
@@ -1280,6 +1287,257 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
   }
 }
 
+// ---- the persistent decode chain --------------------------------------------------------------
+// A token's matmuls are a CHAIN (q,k,v = W x; o = Wo v; g,u = W o; x' = Wd u; ...): each launch of decode16_kernel
+// starts with a serial part -- wait for the previous grid, read + quantize the activation row, set the lanes up --
+// during which its weight ring is full and HBM idles: ~2 us x 129 launches of a 0.9 ms token (DESIGN d1).  Here ONE
+// launch runs the whole list.  A warp's TMA ring does not know about matmul boundaries: lane 0 walks the warp's rows
+// of stage s, then of stage s + 1, ... and keeps `slots` copies in flight (weights are immutable, so a later stage's
+// rows may arrive long before its activations exist); with one CTA per SM the ring is ~200 KB per SM, ~30 MB per
+// GPU = 4.6 us of streaming, several times the serial part.  Stages are separated by a grid barrier on a counter
+// (zeroed by a memset node in front of the launch): after its last row a CTA does bar.sync, fence, atomicAdd; before
+// reading the next activation row it polls the counter (bounded: 2 s, then status = 1).  All CTAs are co-resident
+// (grid = SM count, cooperative launch), so the barrier cannot deadlock.  Arithmetic per row is decode16_body's.
+//
+// MEASURED (round 2, LLaMA-7B Q4_1 chain, profiles/r2n .. r2q, tools/trace_chain.py): bit-identical to one launch per
+// op, but 920 tok/s against 1057 for 129 PDL-chained decode16 launches.  The stamps: per stage ~0.8 us from "rows done"
+// to the next stage's start (fence + atomic), ~1.0 us barrier wait, ~1.0 us activation quantize -- a 2.8 us serial
+// part against 2.15 us for griddepcontrol.wait + quantize -- and the rows phase consumes ~0.9 us per row per warp =
+// 16 rows/us/SM, which is just the DRAM rate: with 16 warps per SM the dot phase is latency-bound, the ring stays
+// full and nothing is prefetched during the serial part (two resident CTAs give the launch-per-op path 32 warps).
+// It stays as an entry point for callers that want one launch per token; the bench's default is the PDL chain.
+struct ChainStage {
+  const uint8_t *wb[4];   float *cb[4];   int mc[3];   int nbatch;   // as DecodeParams (virtual bases)
+  const float *x;
+  int64_t w_stride;
+  int M, kb, units, KS, seg_units, RG, x_bytes, inv_KS;     // inv_KS: (warp * inv_KS) >> 16 == warp / KS for warp < 32
+};
+struct ChainParams {
+  const ChainStage *stages;
+  int n_stages;
+  unsigned int *done_ctr, *status;
+  int slots, slot_bytes, x_bytes_max;
+  unsigned long long *trace;   // diagnostics (lammcu_set_trace): CTA 0 stamps [stage][4] = barrier wait begins, barrier
+                               // passed, activations quantized, rows done (globaltimer ns)
+};
+constexpr int kChainCtrl = 2048;          // [warps][slots] mbarriers (1 KB), partial sums at +1024, slot phases at +1536
+constexpr int kChainWarps = 16;           // measured: 16 warps (105-128 registers, no spills) 920 tok/s on the 7B Q4_1 chain;
+                                          // 32 warps at 64 registers (20-200 bytes of spills) 681 (profiles/r2q/)
+constexpr int kChainMaxSlots = 8;
+
+template <int WT>
+__global__ void __launch_bounds__(kChainWarps * 32, 1) decode_chain_kernel(const ChainParams cp) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ DecodeParams spb[2];                // the current stage's parameters; the next stage's are built ahead
+  constexpr bool kKX = is_kquant_ext(WT);
+  constexpr bool kEarlyRefill = !(WT == LAMMCU_TYPE_Q5_0 || WT == LAMMCU_TYPE_Q5_1);
+  constexpr bool kQ2K = (WT == LAMMCU_TYPE_Q2_K) || kKX;
+  constexpr uint32_t SBB = (uint32_t)type_info(WT).size;
+  constexpr int VT = type_info(WT).vec_dot;
+  constexpr int NW = kKX ? 4 : (kQ2K ? 11 : DecFmt<WT>::NW);
+  constexpr int unit_bytes = kQ2K ? 42 : 4 * type_info(WT).size;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int bid = (int)blockIdx.x, nblk = (int)gridDim.x;
+  const int D = cp.slots;
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem) + warp * kChainMaxSlots;
+  float *part = reinterpret_cast<float *>(smem + 1024);
+  // 16-byte phase of the row in each ring slot, written by lane 0 when it issues the copy (ordered by the mbarrier)
+  const uint32_t a15_u32 = smem_u32(smem + 1536) + (uint32_t)warp * (kChainMaxSlots * 4);
+  uint8_t *xs = smem + kChainCtrl;
+  uint8_t *ring = xs + cp.x_bytes_max + (size_t)warp * D * cp.slot_bytes;
+  const uint32_t ring_addr = smem_u32(ring), full_u32 = smem_u32(full);
+
+  // ---- the warp's rows of one stage: which K segment, which rows
+  struct Geo { int n_rows, row0, row_step; uint32_t seg_off, seg_bytes; int u0, seg_n, rg, seg; };
+  auto geometry = [&](const ChainStage &S) -> Geo {
+    Geo g;
+    const bool active = warp < S.RG * S.KS;
+    g.rg = (warp * S.inv_KS) >> 16;  g.seg = warp - g.rg * S.KS;
+    g.u0 = g.seg * S.seg_units;
+    g.seg_n = max(0, min(S.seg_units, S.units - g.u0));
+    g.seg_off = kQ2K ? (uint32_t)(g.u0 >> 1) * SBB : (uint32_t)g.u0 * unit_bytes;
+    g.seg_bytes = kQ2K ? (uint32_t)((g.seg_n + 1) >> 1) * SBB : (uint32_t)g.seg_n * unit_bytes;
+    g.row0 = bid + nblk * g.rg;
+    g.row_step = nblk * S.RG;
+    g.n_rows = (active && g.row0 < S.M) ? (S.M - 1 - g.row0) / g.row_step + 1 : 0;
+    return g;
+  };
+  // the matrix of a sibling batch that (virtual) row r belongs to: its base + the first row of the NEXT matrix
+  auto select_base = [&](const ChainStage &S, uint32_t seg_off, int r, const uint8_t *&base, int &lim) {
+    base = S.wb[0];
+    lim = 0x7fffffff;
+    if (S.nbatch > 1) {
+      lim = S.mc[0];
+      if (r >= S.mc[0]) { base = S.wb[1]; lim = S.mc[1]; }
+      if (r >= S.mc[1]) { base = S.wb[2]; lim = S.mc[2]; }
+      if (r >= S.mc[2]) { base = S.wb[3]; lim = 0x7fffffff; }
+    }
+    base += seg_off;
+  };
+
+  // ---- the copy cursor (lane 0): runs up to D rows ahead of the consumer, across stage boundaries.  Everything a
+  // copy needs sits in registers (the stage table is read when the cursor ENTERS a stage or a new matrix of a batch):
+  // the refill is on the consuming warp's critical path, once per row.
+  int is = -1, ii = 0, in_rows = 0, i_row = 0, i_step = 0, i_lim = 0;
+  uint32_t i_off = 0, i_bytes = 0, islot = 0;
+  const uint8_t *i_base = nullptr;
+  int64_t i_stride = 0;
+  uint64_t pol = 0;
+  auto next_stage = [&]() {                       // first stage after `is` in which this warp owns rows
+    for (++is; is < cp.n_stages; ++is) {
+      const ChainStage &S = cp.stages[is];
+      const Geo g = geometry(S);
+      if (g.n_rows > 0) {
+        ii = 0; in_rows = g.n_rows; i_row = g.row0; i_step = g.row_step; i_off = g.seg_off; i_bytes = g.seg_bytes;
+        i_stride = S.w_stride;
+        select_base(S, i_off, i_row, i_base, i_lim);
+        return;
+      }
+    }
+  };
+  auto issue_one = [&]() {                        // lane 0, is < n_stages
+    if (i_row >= i_lim) select_base(cp.stages[is], i_off, i_row, i_base, i_lim);
+    const uintptr_t a = (uintptr_t)(i_base + (int64_t)i_row * i_stride);
+    const uintptr_t a0 = a & ~(uintptr_t)15;
+    const uint32_t bytes = (uint32_t)(((a + i_bytes + 15) & ~(uintptr_t)15) - a0);
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(a15_u32 + 4u * islot), "r"((uint32_t)(a & 15)) : "memory");
+    uint64_t *bar = full + islot;
+    mbar_arrive_expect_tx(bar, bytes);
+    bulk_g2s_stream(ring + (size_t)islot * cp.slot_bytes, reinterpret_cast<const void *>(a0), bytes, bar, pol);
+    islot = (islot + 1u == (uint32_t)D) ? 0u : islot + 1u;
+    i_row += i_step;
+    if (++ii >= in_rows) next_stage();
+  };
+  if (lane == 0) {
+    for (int s_ = 0; s_ < D; s_++) mbar_init(&full[s_], 1);
+    fence_barrier_init();
+    pol = policy_evict_first();
+    next_stage();
+    for (int s_ = 0; s_ < D && is < cp.n_stages; s_++) issue_one();
+  }
+  uint32_t cslot = 0, cph = 0;                    // consumer: slot of the next row, parity of the current lap
+
+  auto build_params = [&](int st_) {               // one thread: stage st_'s parameters as the decode helpers want them
+    const ChainStage &S = cp.stages[st_];
+    DecodeParams q = {};
+    q.x = S.x;  q.c = S.cb[0];  q.M = S.M;  q.kb = S.kb;  q.units = S.units;  q.KS = S.KS;  q.seg_units = S.seg_units;
+    q.RG = S.RG;  q.x_bytes = S.x_bytes;  q.w_stride = S.w_stride;  q.nbatch = S.nbatch;
+    for (int j = 0; j < 4; j++) { q.wb[j] = S.wb[j];  q.cb[j] = S.cb[j]; }
+    for (int j = 0; j < 3; j++) q.mc[j] = S.mc[j];
+    spb[st_ & 1] = q;
+  };
+  if (tid == 0) build_params(0);
+
+  for (int st = 0; st < cp.n_stages; st++) {
+    const ChainStage &S = cp.stages[st];
+    const DecodeParams &sp = spb[st & 1];
+    if (tid == 0) {
+      if (cp.trace && bid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cp.trace[st * 4 + 0]));
+      if (st > 0) {                               // grid barrier: every CTA has stored its rows of stage st - 1
+        const unsigned int target = (unsigned int)nblk * (unsigned int)st;
+        unsigned int v, spins = 0;
+        unsigned long long t0 = 0;
+        while (true) {
+          asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(cp.done_ctr) : "memory");
+          if (v >= target) break;
+          if ((++spins & 255u) == 0) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 2000000000ull) { *cp.status = 1u; break; }
+          }
+        }
+        __threadfence();
+      }
+    }
+    __syncthreads();
+    if (cp.trace && bid == 0 && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cp.trace[st * 4 + 1]));
+    stage_x_row<VT, 3>(sp, xs);
+    __syncthreads();
+    if (cp.trace && bid == 0 && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cp.trace[st * 4 + 2]));
+    // the next stage's parameters (its buffer was last read in stage st - 1: two barriers ago); the last warp has the fewest rows
+    if (tid == kChainWarps * 32 - 1 && st + 1 < cp.n_stages) build_params(st + 1);
+    const Geo g = geometry(S);
+    if (g.n_rows > 0) {
+      const int U = S.units, ug = g.u0 + lane;
+      const bool lane_live = lane < g.seg_n;
+      const int lane_c = lane_live ? lane : 0;
+      const uint32_t xaddr = smem_u32(xs) + (uint32_t)(lane_live ? ug : g.u0) * 16u;
+      const uint32_t jstride = (uint32_t)U * 16u;
+      const uint32_t xs_addr = smem_u32(xs) + 8u * jstride + (kQ2K ? (uint32_t)ug * 16u : (uint32_t)ug * 32u);
+      const uint32_t xd_addr = smem_u32(xs) + 9u * jstride + (uint32_t)(ug >> 1) * 4u;          // Q8_K only
+      float xd[4] = {0.f, 0.f, 0.f, 0.f}, xsc[4] = {0.f, 0.f, 0.f, 0.f};
+      uint32_t xbs[4] = {0u, 0u, 0u, 0u};
+      if (lane_live) {
+        if constexpr (kQ2K) {
+          lds128(xbs, xs_addr);
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(xd[0]) : "r"(xd_addr));
+        } else {
+          uint32_t v0[4], v1[4];
+          lds128(v0, xs_addr);
+          lds128(v1, xs_addr + 16u);
+          xd[0] = __uint_as_float(v0[0]); xsc[0] = __uint_as_float(v0[1]); xd[1] = __uint_as_float(v0[2]); xsc[1] = __uint_as_float(v0[3]);
+          xd[2] = __uint_as_float(v1[0]); xsc[2] = __uint_as_float(v1[1]); xd[3] = __uint_as_float(v1[2]); xsc[3] = __uint_as_float(v1[3]);
+        }
+      }
+      for (int i0 = 0, ph = 0; i0 < g.n_rows; i0 += 2, ph ^= 1) {
+        const int nb = min(2, g.n_rows - i0);
+        float acc[2] = {0.f, 0.f};
+#pragma unroll
+        for (int s_ = 0; s_ < 2; s_++) {
+          if (s_ < nb) {
+            uint32_t w[NW];
+            const uint32_t sl = cslot;
+            mbar_wait_u32(full_u32 + 8u * sl, cph);
+            cslot = (sl + 1u == (uint32_t)D) ? 0u : sl + 1u;
+            if (cslot == 0u) cph ^= 1u;
+            uint32_t a15r;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(a15r) : "r"(a15_u32 + 4u * sl) : "memory");
+            if constexpr (kKX) {
+              (void)w;
+              acc[s_] = dot_unit_kx<WT>(ring_addr + sl * cp.slot_bytes + a15r + (uint32_t)(lane_c >> 1) * SBB, lane_c & 1, xaddr,
+                                        jstride, xd[0], xbs);
+            } else {
+              load_unit<WT, NW>(w, ring_addr + sl * cp.slot_bytes + a15r, lane_c);
+              if constexpr (kEarlyRefill) {       // the slot is free once every lane holds its words (see decode16_body)
+                unsigned int seen;
+                asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %1, 0;\n\tvote.sync.any.pred q, p, 0xffffffff;\n\t"
+                             "selp.u32 %0, 1, 0, q;\n\t}" : "=r"(seen) : "r"(w[NW - 1]) : "memory");
+                (void)seen;
+                if (lane == 0 && is < cp.n_stages) issue_one();
+              }
+              acc[s_] = dot_unit_sx<WT, NW>(w, xaddr, jstride, xd, xsc, xbs);
+            }
+            if constexpr (kKX || !kEarlyRefill) {
+              __syncwarp();
+              if (lane == 0 && is < cp.n_stages) issue_one();
+            }
+          }
+        }
+        const float tot = warp_sum2(acc[0], acc[1], lane);
+        if (S.KS == 1) {
+          if (lane < nb) store_c(sp, g.row0 + (i0 + lane) * g.row_step, tot, 0u);
+        } else {
+          float *pb = part + (size_t)((g.rg * 2 + ph) * S.KS) * 2;
+          if (lane < 2) pb[g.seg * 2 + lane] = tot;
+          asm volatile("bar.sync %0, %1;" ::"r"(1 + g.rg), "r"(S.KS * 32) : "memory");
+          if (g.seg == 0 && lane < nb) {
+            float t = 0.f;
+            for (int k = 0; k < S.KS; k++) t += pb[k * 2 + lane];
+            store_c(sp, g.row0 + (i0 + lane) * g.row_step, t, 0u);
+          }
+        }
+      }
+    }
+    __syncthreads();                                // all rows of the stage stored; xs and sp may be overwritten
+    if (cp.trace && bid == 0 && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cp.trace[st * 4 + 3]));
+    if (tid == 0 && st + 1 < cp.n_stages) {
+      __threadfence();
+      atomicAdd(cp.done_ctr, 1u);
+    }
+  }
+}
+
 // ---- host side --------------------------------------------------------------------------
 constexpr int kDecSmemMax = 227 * 1024;
 
@@ -1560,6 +1818,150 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   }
   return x ? launch_decode_x<true>(w_type, p, grid, warps * 32, smem, st)
            : launch_decode_x<false>(w_type, p, grid, warps * 32, smem, st);
+}
+
+// ---- persistent decode chain: host side ------------------------------------------------------------
+struct ChainPlan {
+  int w_type, n_stages, grid, smem;
+  ChainStage *stages_dev;
+  unsigned int *ctrs;           // [0] stage-done counter (zeroed before every launch), [2] status
+  ChainParams params;
+};
+
+template <int WT>
+static int chain_launch_t(const ChainPlan *pl, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(decode_chain_kernel<WT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDecSmemMax - 2048);
+    if (e != cudaSuccess) { set_error("decode chain: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return LAMMCU_ERR_CUDA; }
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(pl->grid);
+  cfg.blockDim = dim3(kChainWarps * 32);
+  cfg.dynamicSmemBytes = pl->smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;      // all CTAs co-resident: the grid barrier cannot deadlock
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, decode_chain_kernel<WT>, pl->params);
+  g_launch_count++;
+  if (e != cudaSuccess) {
+    set_error("decode chain launch (type %d, smem %d): %s", WT, pl->smem, cudaGetErrorString(e));
+    return LAMMCU_ERR_CUDA;
+  }
+  return LAMMCU_OK;
+}
+
+int chain_run(ChainPlan *pl, cudaStream_t st) {
+  pl->params.trace = (pl->n_stages * 4 <= pl->grid * 8) ? next_trace_slot(pl->grid) : nullptr;   // NULL unless armed
+  cudaError_t e = cudaMemsetAsync(pl->ctrs, 0, 4, st);
+  if (e != cudaSuccess) { set_error("decode chain: cudaMemsetAsync: %s", cudaGetErrorString(e)); return LAMMCU_ERR_CUDA; }
+  switch (pl->w_type) {
+  case LAMMCU_TYPE_Q4_0: return chain_launch_t<LAMMCU_TYPE_Q4_0>(pl, st);
+  case LAMMCU_TYPE_Q4_1: return chain_launch_t<LAMMCU_TYPE_Q4_1>(pl, st);
+  case LAMMCU_TYPE_Q5_0: return chain_launch_t<LAMMCU_TYPE_Q5_0>(pl, st);
+  case LAMMCU_TYPE_Q5_1: return chain_launch_t<LAMMCU_TYPE_Q5_1>(pl, st);
+  case LAMMCU_TYPE_Q8_0: return chain_launch_t<LAMMCU_TYPE_Q8_0>(pl, st);
+  case LAMMCU_TYPE_Q2_K: return chain_launch_t<LAMMCU_TYPE_Q2_K>(pl, st);
+  case LAMMCU_TYPE_Q3_K: return chain_launch_t<LAMMCU_TYPE_Q3_K>(pl, st);
+  case LAMMCU_TYPE_Q4_K: return chain_launch_t<LAMMCU_TYPE_Q4_K>(pl, st);
+  case LAMMCU_TYPE_Q5_K: return chain_launch_t<LAMMCU_TYPE_Q5_K>(pl, st);
+  case LAMMCU_TYPE_Q6_K: return chain_launch_t<LAMMCU_TYPE_Q6_K>(pl, st);
+  default: set_error("decode chain: type %d", pl->w_type); return LAMMCU_ERR_TYPE;
+  }
+}
+
+void chain_destroy(ChainPlan *pl) {
+  if (!pl) return;
+  cudaFree(pl->stages_dev);
+  cudaFree(pl->ctrs);
+  delete pl;
+}
+
+int chain_create(int w_type, int n_ops, const ChainOp *ops, ChainPlan **out) {
+  if (!ops || !out || n_ops < 1 || n_ops > 65536) { set_error("decode chain: bad argument"); return LAMMCU_ERR_ARG; }
+  const TypeInfo ti = type_info(w_type);
+  const bool q2k = (ti.blck == 256);
+  std::vector<ChainStage> stages((size_t)n_ops);
+  int slot_bytes = 0, x_bytes_max = 0;
+  for (int i = 0; i < n_ops; i++) {
+    const ChainOp &op = ops[i];
+    ChainStage &S = stages[(size_t)i];
+    S = ChainStage();
+    static_assert(kChainWarps * kChainMaxSlots * 8 <= 1024 && kChainWarps * kChainMaxSlots * 4 <= 512, "control area");
+    if (op.count < 1 || op.count > 4 || !op.x) { set_error("decode chain: op %d: 1..4 matrices and an activation row", i); return LAMMCU_ERR_ARG; }
+    int64_t first[4] = {0, 0, 0, 0}, total = 0;
+    for (int j = 0; j < op.count; j++) {
+      if (!op.w[j] || !op.c[j] || op.M[j] <= 0) { set_error("decode chain: op %d: bad operand %d", i, j); return LAMMCU_ERR_ARG; }
+      // same conditions as the sibling batch: every matrix the kernel can take, all rows at one 16-byte phase
+      if (!decode_supported(w_type, op.w[j], op.w_stride, op.x, op.M[j], op.K) ||
+          (((uintptr_t)total * (uintptr_t)op.w_stride) & 15) != 0 || (((uintptr_t)op.w[j] ^ (uintptr_t)op.w[0]) & 15) != 0) {
+        set_error("decode chain: op %d matrix %d: needs a quantized type, K %% 256 == 0, 16-byte aligned operands and row "
+                  "counts that keep every matrix of a batch at the same 16-byte phase", i, j);
+        return LAMMCU_ERR_SHAPE;
+      }
+      first[j] = total;
+      total += op.M[j];
+    }
+    if (total > 0x3fffffff) { set_error("decode chain: op %d: too many rows", i); return LAMMCU_ERR_SHAPE; }
+    DecodeParams p = {};
+    int rc = plan_k_split(p, ti, q2k, op.K);
+    if (rc) return rc;
+    if (p.KS > kD16Warps) { set_error("decode chain: op %d: K too large", i); return LAMMCU_ERR_SHAPE; }
+    int warps = 0;
+    plan_d16_smem(p, ti, q2k, &warps);
+    // 32 warps: twice the row groups of the 16-warp plan; K-split row groups reduce through named barriers 1..15
+    p.RG = kChainWarps / p.KS;
+    if (p.KS > 1 && p.RG > 15) p.RG = 15;
+    S.nbatch = op.count;
+    for (int j = 0; j < 4; j++) {
+      const int jj = j < op.count ? j : op.count - 1;
+      S.wb[j] = (const uint8_t *)op.w[jj] - first[jj] * op.w_stride;
+      S.cb[j] = op.c[jj] - first[jj];
+      if (j > 0) S.mc[j - 1] = j < op.count ? (int)first[j] : 0x7fffffff;
+    }
+    S.x = op.x;  S.w_stride = op.w_stride;  S.M = (int)total;
+    S.kb = p.kb;  S.units = p.units;  S.KS = p.KS;  S.seg_units = p.seg_units;  S.RG = p.RG;  S.x_bytes = p.x_bytes;
+    S.inv_KS = (65536 + p.KS - 1) / p.KS;
+    for (int wv = 0; wv < kChainWarps; wv++)
+      if (((wv * S.inv_KS) >> 16) != wv / p.KS) { set_error("decode chain: reciprocal of KS=%d is not exact", p.KS); return LAMMCU_ERR_SHAPE; }
+    slot_bytes = std::max(slot_bytes, p.slot_bytes);
+    x_bytes_max = std::max(x_bytes_max, p.x_bytes);
+  }
+  const int budget = kDecSmemMax - 2048 /* static: the stage's DecodeParams */ - kChainCtrl - x_bytes_max;
+  int slots = budget / (kChainWarps * slot_bytes);
+  if (slots > kChainMaxSlots) slots = kChainMaxSlots;
+  if (slots < 2) { set_error("decode chain: K too large for the shared-memory ring"); return LAMMCU_ERR_SHAPE; }
+  ChainPlan *pl = new ChainPlan();
+  pl->w_type = w_type;  pl->n_stages = n_ops;  pl->grid = sm_count_cached();
+  pl->smem = kChainCtrl + x_bytes_max + kChainWarps * slots * slot_bytes;
+  pl->stages_dev = nullptr;  pl->ctrs = nullptr;
+  cudaError_t e = cudaMalloc(&pl->stages_dev, sizeof(ChainStage) * (size_t)n_ops);
+  if (e == cudaSuccess) e = cudaMalloc(&pl->ctrs, 256);
+  if (e == cudaSuccess) e = cudaMemcpy(pl->stages_dev, stages.data(), sizeof(ChainStage) * (size_t)n_ops, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemset(pl->ctrs, 0, 256);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    set_error("decode chain: %s", cudaGetErrorString(e));
+    chain_destroy(pl);
+    return LAMMCU_ERR_CUDA;
+  }
+  pl->params.stages = pl->stages_dev;  pl->params.n_stages = n_ops;
+  pl->params.done_ctr = pl->ctrs;  pl->params.status = pl->ctrs + 2;
+  pl->params.slots = slots;  pl->params.slot_bytes = slot_bytes;  pl->params.x_bytes_max = x_bytes_max;
+  *out = pl;
+  return LAMMCU_OK;
+}
+
+int chain_status(ChainPlan *pl, int *timed_out) {
+  unsigned int v = 0;
+  cudaError_t e = cudaMemcpy(&v, pl->ctrs + 2, 4, cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) { set_error("decode chain status: %s", cudaGetErrorString(e)); return LAMMCU_ERR_CUDA; }
+  *timed_out = (int)v;
+  return LAMMCU_OK;
 }
 
 }  // namespace lamm

@@ -718,6 +718,52 @@ int lammcu_mul_mat_batch_dev(int w_type, int count, const void *const *w_dev, in
   return LAMMCU_OK;
 }
 
+// ---- persistent decode chain (lamm_decode.cu) ---------------------------------------------------
+struct lammcu_chain { ChainPlan *plan; };
+
+int lammcu_chain_create(int w_type, int n_ops, const lammcu_chain_op *ops, lammcu_chain_t *out) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!ops || !out || n_ops < 1) { set_error("chain_create: bad argument"); return LAMMCU_ERR_ARG; }
+  if (w_type == LAMMCU_TYPE_F32 || !lammcu_type_supported(w_type)) { set_error("chain_create: type %d not supported", w_type); return LAMMCU_ERR_TYPE; }
+  std::vector<ChainOp> v((size_t)n_ops);
+  for (int i = 0; i < n_ops; i++) {
+    ChainOp &o = v[(size_t)i];
+    o.count = ops[i].count;
+    for (int j = 0; j < 4; j++) { o.w[j] = ops[i].w_dev[j];  o.M[j] = ops[i].M[j];  o.c[j] = ops[i].c_dev[j]; }
+    o.x = ops[i].x_dev;  o.K = ops[i].K;  o.w_stride = ops[i].w_stride_bytes;
+  }
+  ChainPlan *pl = nullptr;
+  if ((rc = chain_create(w_type, n_ops, v.data(), &pl))) return rc;
+  lammcu_chain *h = new lammcu_chain();
+  h->plan = pl;
+  *out = h;
+  return LAMMCU_OK;
+}
+
+int lammcu_chain_run_dev(lammcu_chain_t ch, void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  if (!ch || !ch->plan) { set_error("chain_run: bad handle"); return LAMMCU_ERR_ARG; }
+  if (!stream || (cudaStream_t)stream == g_dev.stream) {      // the persistent kernel needs every SM: no resident server
+    std::lock_guard<std::mutex> lk(g_mu);
+    server_stop();
+  }
+  return chain_run(ch->plan, pick_stream(stream));
+}
+
+int lammcu_chain_status(lammcu_chain_t ch, int *timed_out) {
+  if (!ch || !ch->plan || !timed_out) { set_error("chain_status: bad argument"); return LAMMCU_ERR_ARG; }
+  return chain_status(ch->plan, timed_out);
+}
+
+int lammcu_chain_destroy(lammcu_chain_t ch) {
+  if (!ch) return LAMMCU_ERR_ARG;
+  chain_destroy(ch->plan);
+  delete ch;
+  return LAMMCU_OK;
+}
+
 // ---- host operands --------------------------------------------------------------
 // hold: 1 = an explicit registration (the caller gets a reference and releases it), 0 = the operator path (the
 // registry owns the entry).  refresh: the host bytes may have changed since the last call (src0 is not a leaf
