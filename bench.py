@@ -55,12 +55,12 @@ def set_model(name):
 
 
 set_model("7b")
-TYPE_IDS = {"f32": 0, "q4_0": 2, "q4_1": 3, "q5_0": 6, "q5_1": 7, "q8_0": 8, "q2_k": 10,
+TYPE_IDS = {"f32": 0, "f16": 1, "q4_0": 2, "q4_1": 3, "q5_0": 6, "q5_1": 7, "q8_0": 8, "q2_k": 10,
             "q3_k": 11, "q4_k": 12, "q5_k": 13, "q6_k": 14}          # 11-14: SURVEY 8f-1 (sweeps only)
-BLCK = {0: 1, 2: 32, 3: 32, 6: 32, 7: 32, 8: 32, 10: 256, 11: 256, 12: 256, 13: 256, 14: 256}
-TSIZE = {0: 4, 2: 18, 3: 20, 6: 22, 7: 24, 8: 34, 10: 84, 11: 110, 12: 144, 13: 176, 14: 210}
-VEC_DOT = {0: 0, 2: 8, 3: 9, 6: 8, 7: 9, 8: 8, 10: 15, 11: 15, 12: 15, 13: 15, 14: 15}
-ACT_SIZE = {0: (1, 4), 8: (32, 34), 9: (32, 36), 15: (256, 292)}
+BLCK = {0: 1, 1: 1, 2: 32, 3: 32, 6: 32, 7: 32, 8: 32, 10: 256, 11: 256, 12: 256, 13: 256, 14: 256}
+TSIZE = {0: 4, 1: 2, 2: 18, 3: 20, 6: 22, 7: 24, 8: 34, 10: 84, 11: 110, 12: 144, 13: 176, 14: 210}
+VEC_DOT = {0: 0, 1: 1, 2: 8, 3: 9, 6: 8, 7: 9, 8: 8, 10: 15, 11: 15, 12: 15, 13: 15, 14: 15}
+ACT_SIZE = {0: (1, 4), 1: (1, 2), 8: (32, 34), 9: (32, 36), 15: (256, 292)}
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, averaged over the chain's
@@ -165,6 +165,8 @@ def synth_weight(torch, t, m, k, gen, device):
     Returns uint8 [m, row_bytes]."""
     if t == 0:
         return (torch.randn((m, k), generator=gen, device=device, dtype=torch.float32) * (k ** -0.5)).view(torch.uint8)
+    if t == 1:                                           # F16 (SURVEY 8f-2, sweeps only)
+        return (torch.randn((m, k), generator=gen, device=device, dtype=torch.float32) * (k ** -0.5)).to(torch.float16).view(torch.uint8)
     kb, bs = k // BLCK[t], TSIZE[t]
     raw = torch.randint(0, 256, (m, kb, bs), generator=gen, device=device, dtype=torch.uint8)
     halves = raw.view(torch.int16)                       # [m, kb, bs/2]

@@ -56,7 +56,8 @@ typedef enum {
 
 /* ggml type ids accepted (llama.cpp-b2430/ggml.h:341-369) */
 enum {
-  LAMMCU_TYPE_F32 = 0, LAMMCU_TYPE_Q4_0 = 2, LAMMCU_TYPE_Q4_1 = 3,
+  LAMMCU_TYPE_F32 = 0, LAMMCU_TYPE_F16 = 1 /* fp16 weights, activations rounded to fp16 (ggml.c:486-496) */,
+  LAMMCU_TYPE_Q4_0 = 2, LAMMCU_TYPE_Q4_1 = 3,
   LAMMCU_TYPE_Q5_0 = 6, LAMMCU_TYPE_Q5_1 = 7, LAMMCU_TYPE_Q8_0 = 8,
   LAMMCU_TYPE_Q8_1 = 9, LAMMCU_TYPE_Q2_K = 10, LAMMCU_TYPE_Q8_K = 15,
   /* the K-quants the reference lists as TODO (dev.md:86-95; the reference's gate

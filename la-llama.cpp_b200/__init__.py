@@ -27,6 +27,9 @@ TYPE_NAMES = {F32: "f32", Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1"
 NAME_TO_TYPE = {v: k for k, v in TYPE_NAMES.items()}
 W_TYPES = (F32, Q2_K, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0)      # src/loongarch_matmul.cpp:37-42
 KQ_TYPES = (Q3_K, Q4_K, Q5_K, Q6_K)
+F16 = 1                                                   # F16 weights, activations rounded to fp16 (ggml.c:486-496)
+TYPE_NAMES[F16] = "f16"
+NAME_TO_TYPE["f16"] = F16
 TASK_INIT, TASK_COMPUTE, TASK_FINALIZE = 0, 1, 2
 
 # every symbol include/lammcu.h and include/lamm_b200.h declare

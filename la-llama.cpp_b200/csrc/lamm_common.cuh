@@ -23,6 +23,7 @@ struct TypeInfo {
 __host__ __device__ constexpr TypeInfo type_info(int t) {
   switch (t) {
   case LAMMCU_TYPE_F32:  return {1, 4, LAMMCU_TYPE_F32};
+  case LAMMCU_TYPE_F16:  return {1, 2, LAMMCU_TYPE_F16};   // vec_dot_type F16 (ggml.c:486-496)
   case LAMMCU_TYPE_Q4_0: return {32, 18, LAMMCU_TYPE_Q8_0};
   case LAMMCU_TYPE_Q4_1: return {32, 20, LAMMCU_TYPE_Q8_1};
   case LAMMCU_TYPE_Q5_0: return {32, 22, LAMMCU_TYPE_Q8_0};
@@ -219,6 +220,9 @@ bool gemm_x_supported(int w_type, const void *w, int64_t w_stride, int64_t M, in
 size_t gemm_x_ws_bytes(int64_t N, int64_t K);
 int launch_gemm_x(int w_type, const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c, int64_t ldc,
                   int64_t M, int64_t N, int64_t K, void *ws, cudaStream_t st);
+bool gemm_f16_supported(const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, int64_t M, int64_t N, int64_t K);
+int launch_gemm_f16(const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c, int64_t ldc, int64_t M,
+                    int64_t N, int64_t K, cudaStream_t st);
 void set_gemm_exact(int on);
 int get_gemm_exact();
 void *gemm_workspace(size_t bytes);      // library-owned scratch for the prefill GEMM (grown on demand)

@@ -1641,7 +1641,7 @@ static int launch_decode_x(int w_type, const DecodeParams &p, int grid, int thre
 // Whether the single-launch decode kernel can take this operand set (else the caller uses
 // the generic GEMV of lamm_gemv.cu, which handles any 2/4-byte alignment and any K).
 bool decode_supported(int w_type, const void *w, int64_t w_stride, const void *x_or_xq, int64_t M, int64_t K) {
-  if (w_type == LAMMCU_TYPE_F32 || !lammcu_type_supported(w_type)) return false;
+  if (w_type == LAMMCU_TYPE_F32 || w_type == LAMMCU_TYPE_F16 || !lammcu_type_supported(w_type)) return false;
   if (M <= 0 || M > 0x3fffffff || K <= 0 || K > (1 << 22)) return false;
   if (w_type == LAMMCU_TYPE_Q3_K || w_type == LAMMCU_TYPE_Q6_K) {      // 110 / 210-byte super-blocks: 16-bit words
     if (K % 256) return false;

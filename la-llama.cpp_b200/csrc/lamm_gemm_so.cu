@@ -382,13 +382,15 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
 // GEMM: no unpack warps, no extra stages.  Same three MMAs per K step, same epilogue.
 constexpr int kDirStages = 3;
 
-template <bool PEERS>
+// F16W (SURVEY 8f-2, F16 weights x activations rounded to fp16 = ggml_vec_dot_f16's operands): both operands ARE fp16,
+// so there is no lo tile, one MMA per K step and no rescaling in the epilogue; the A map sits on the caller's W.
+template <bool PEERS, bool F16W = false>
 __global__ void __launch_bounds__(192, 1)
 gemm_direct_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant__ CUtensorMap tm_al,
                    const __grid_constant__ CUtensorMap tm_xh, const __grid_constant__ CUtensorMap tm_xl, const SoParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  constexpr int kStageBytes = 4 * kTileBytes;                     // Ah, Al, Bh, Bl
+  constexpr int kStageBytes = (F16W ? 2 : 4) * kTileBytes;        // Ah, Al, Bh, Bl (F16W: A, B)
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kDirStages * kStageBytes);
   uint64_t *full = bars, *empty = bars + kDirStages, *acc_full = bars + 2 * kDirStages;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 8);
@@ -421,9 +423,13 @@ gemm_direct_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_const
         mbar_wait(&empty[s], ((uint32_t)(st / kDirStages) & 1u) ^ 1u);
         mbar_arrive_expect_tx(&full[s], (uint32_t)kStageBytes);
         tma_load_2d(stage, &tm_ah, st * GK, m0, &full[s]);
-        tma_load_2d(stage + kTileBytes, &tm_al, st * GK, m0, &full[s]);
-        tma_load_2d(stage + 2 * kTileBytes, &tm_xh, st * GK, n0, &full[s]);
-        tma_load_2d(stage + 3 * kTileBytes, &tm_xl, st * GK, n0, &full[s]);
+        if constexpr (F16W) {
+          tma_load_2d(stage + kTileBytes, &tm_xh, st * GK, n0, &full[s]);
+        } else {
+          tma_load_2d(stage + kTileBytes, &tm_al, st * GK, m0, &full[s]);
+          tma_load_2d(stage + 2 * kTileBytes, &tm_xh, st * GK, n0, &full[s]);
+          tma_load_2d(stage + 3 * kTileBytes, &tm_xl, st * GK, n0, &full[s]);
+        }
       }
     }
   } else if (warp == 1) {
@@ -434,13 +440,15 @@ gemm_direct_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_const
         tc_fence_after();
         const uint32_t base = smem_u32(smem + s * kStageBytes);
         const uint64_t ah = make_sw128_desc(base), al = make_sw128_desc(base + kTileBytes);
-        const uint64_t bh = make_sw128_desc(base + 2 * kTileBytes), bl = make_sw128_desc(base + 3 * kTileBytes);
+        const uint64_t bh = make_sw128_desc(base + (F16W ? 1 : 2) * kTileBytes), bl = make_sw128_desc(base + 3 * kTileBytes);
 #pragma unroll
         for (int kk = 0; kk < 4; kk++) {
           const uint64_t o = (uint64_t)(kk * 2);
           umma_f16(tmem_base, ah + o, bh + o, kIdescF16, (st | kk) ? 1u : 0u);
-          umma_f16(tmem_base, ah + o, bl + o, kIdescF16, 1u);
-          umma_f16(tmem_base, al + o, bh + o, kIdescF16, 1u);
+          if constexpr (!F16W) {
+            umma_f16(tmem_base, ah + o, bl + o, kIdescF16, 1u);
+            umma_f16(tmem_base, al + o, bh + o, kIdescF16, 1u);
+          }
         }
         umma_commit(&empty[s]);
       }
@@ -449,7 +457,7 @@ gemm_direct_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_const
   } else {
     // epilogue warps 2..5: TMEM lane quarter = warp & 3
     const int q4 = warp & 3, row = q4 * 32 + lane, m = m0 + row;
-    const float rinv = 1.0f / __ldg(p.rowscale + m);                  // exact: a power of two ([Mpad] entries)
+    const float rinv = F16W ? 1.0f : 1.0f / __ldg(p.rowscale + m);                  // exact: a power of two ([Mpad] entries)
     mbar_wait(acc_full, 0u);
     tc_fence_after();
     const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16);
@@ -468,7 +476,7 @@ gemm_direct_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_const
 #pragma unroll
         for (int i = 0; i < 16; i++) {
           const int n = n0 + c16 * 16 + i;
-          if (n < p.N) store_out<PEERS>(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * (__ldg(p.colscale + n) * rinv));
+          if (n < p.N) store_out<PEERS>(p, (int64_t)n * p.ldc + m, F16W ? __uint_as_float(v[i]) : __uint_as_float(v[i]) * (__ldg(p.colscale + n) * rinv));
         }
       }
     }
@@ -530,6 +538,41 @@ int launch_gemm_direct(int w_type, const void *w, int64_t w_stride, const void *
     set_error("gemm_direct launch: %s", cudaGetErrorString(e));
     return LAMMCU_ERR_CUDA;
   }
+  return LAMMCU_OK;
+}
+
+// F16 weights x fp16 activations (both as the caller has them): W [M][K] fp16 rows (16-byte aligned, stride % 16 == 0),
+// xq [N][K] fp16 rows.  Rows beyond M / N in the last tiles are zero-filled by the TMA unit.
+bool gemm_f16_supported(const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, int64_t M, int64_t N, int64_t K) {
+  if (K <= 0 || K % GK || M <= 0 || N <= 0 || M > 0x3fffffff || N > 0x3fffffff) return false;
+  return (((uintptr_t)w | (uintptr_t)w_stride | (uintptr_t)xq | (uintptr_t)xq_stride) & 15) == 0;
+}
+int launch_gemm_f16(const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c, int64_t ldc, int64_t M,
+                    int64_t N, int64_t K, cudaStream_t st) {
+  CUtensorMap tm_a, tm_x;
+  int rc;
+  if ((rc = make_map_2d(&tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, w, (uint64_t)K, (uint64_t)M, (uint64_t)w_stride, GK, GM,
+                        CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = make_map_2d(&tm_x, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, xq, (uint64_t)K, (uint64_t)N, (uint64_t)xq_stride, GK, GN,
+                        CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  SoParams p;
+  p.colscale = nullptr;  p.rowscale = nullptr;  p.c = c;  p.ldc = ldc;
+  p.M = (int)M;  p.N = (int)N;  p.Npad = (int)((N + GN - 1) / GN * GN);  p.K = (int)K;
+  fill_peers(p);
+  constexpr int smem = kDirStages * 2 * kTileBytes + 256 + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_direct_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_direct_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) { set_error("gemm_f16: cudaFuncSetAttribute(%d): %s", smem, cudaGetErrorString(e)); return LAMMCU_ERR_CUDA; }
+    attr_set = true;
+  }
+  const int tiles = (int)(((M + GM - 1) / GM) * ((N + GN - 1) / GN));
+  if (p.n_peer) gemm_direct_kernel<true, true><<<tiles, 192, smem, st>>>(tm_a, tm_a, tm_x, tm_x, p);
+  else gemm_direct_kernel<false, true><<<tiles, 192, smem, st>>>(tm_a, tm_a, tm_x, tm_x, p);
+  g_launch_count++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("gemm_f16 launch: %s", cudaGetErrorString(e)); return LAMMCU_ERR_CUDA; }
   return LAMMCU_OK;
 }
 

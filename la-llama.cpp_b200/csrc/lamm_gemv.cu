@@ -458,10 +458,49 @@ __device__ __forceinline__ void dot_unit_f32(const uint8_t *rowp, int u, const G
   }
 }
 
+// ---- F16 weights: ggml_vec_dot_f16 (ggml.c:1414-1457) on src1 rounded to fp16 -------------
+// unit = 16 bytes = 8 fp16 weights.  Xq holds the fp16 activations (ggml_fp32_to_fp16_row); they are widened back
+// to f32 once per CTA (exact), so every product w * x is exact in f32 (11 + 11 significant bits) and only the f32
+// accumulation order differs from ggml's SIMD lanes.
+template <int NC>
+__device__ __forceinline__ void stage_xf16(const GemvParams &p, uint8_t *xs, int tid) {
+  float *x = reinterpret_cast<float *>(xs);
+  const int K = p.units * 8;
+  for (int idx = tid; idx < NC * K; idx += kConsumerWarps * 32) {
+    const int n = idx / K, k = idx - n * K;
+    x[idx] = (n < p.n_valid)
+                 ? __half2float(*reinterpret_cast<const __half *>(p.xq + (int64_t)n * p.xq_stride + 2 * (int64_t)k))
+                 : 0.f;
+  }
+}
+template <int NC>
+__device__ __forceinline__ void dot_unit_f16(const uint8_t *rowp, int u, const GemvParams &p,
+                                             const uint8_t *xs, float (&acc)[NC]) {
+  uint32_t w[4];
+  lds_words_a4<4>(rowp + 16 * u, w);
+  float wf[8];
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&w[i]));
+    wf[2 * i] = f.x;
+    wf[2 * i + 1] = f.y;
+  }
+  const float4 *x = reinterpret_cast<const float4 *>(xs);
+#pragma unroll
+  for (int n = 0; n < NC; n++) {
+    const float4 a = x[(n * p.units + u) * 2], b = x[(n * p.units + u) * 2 + 1];
+    acc[n] = fmaf(wf[0], a.x, acc[n]);  acc[n] = fmaf(wf[1], a.y, acc[n]);
+    acc[n] = fmaf(wf[2], a.z, acc[n]);  acc[n] = fmaf(wf[3], a.w, acc[n]);
+    acc[n] = fmaf(wf[4], b.x, acc[n]);  acc[n] = fmaf(wf[5], b.y, acc[n]);
+    acc[n] = fmaf(wf[6], b.z, acc[n]);  acc[n] = fmaf(wf[7], b.w, acc[n]);
+  }
+}
+
 // ---- the kernel ---------------------------------------------------------------------
 template <int WT, int NC>
 __device__ __forceinline__ void stage_x(const GemvParams &p, uint8_t *xs, int tid) {
   if constexpr (WT == LAMMCU_TYPE_F32) stage_xf32<NC>(p, xs, tid);
+  else if constexpr (WT == LAMMCU_TYPE_F16) stage_xf16<NC>(p, xs, tid);
   else if constexpr (WT == LAMMCU_TYPE_Q2_K || is_kquant_ext(WT)) stage_xq2k<NC>(p, xs, tid);
   else stage_x32<type_info(WT).vec_dot, NC>(p, xs, tid);
 }
@@ -469,6 +508,7 @@ template <int WT, int NC>
 __device__ __forceinline__ void dot_unit(const uint8_t *rowp, int u, const GemvParams &p,
                                          const uint8_t *xs, float (&acc)[NC]) {
   if constexpr (WT == LAMMCU_TYPE_F32) dot_unit_f32<NC>(rowp, u, p, xs, acc);
+  else if constexpr (WT == LAMMCU_TYPE_F16) dot_unit_f16<NC>(rowp, u, p, xs, acc);
   else if constexpr (WT == LAMMCU_TYPE_Q2_K) dot_unit_q2k<NC>(rowp, u, p, xs, acc);
   else if constexpr (is_kquant_ext(WT)) dot_unit_kq<WT, NC>(rowp, u, p, xs, acc);
   else dot_unit32<WT, NC>(rowp, u, p, xs, acc);
@@ -629,7 +669,7 @@ static int launch_nc(int nc, const GemvParams &p, int grid, int smem, cudaStream
 
 static int x_bytes_for(int w_type, int nc, int kb, int64_t K) {
   int b;
-  if (w_type == LAMMCU_TYPE_F32) b = nc * (int)K * 4;
+  if (w_type == LAMMCU_TYPE_F32 || w_type == LAMMCU_TYPE_F16) b = nc * (int)K * 4;
   else if (type_info(w_type).blck == 256) b = nc * kb * 292;
   else b = nc * kb * 40;
   return (b + 127) & ~127;
@@ -642,21 +682,21 @@ int launch_gemv(int w_type, const void *w, int64_t w_stride, const void *xq, int
     set_error("gemv: weight type %d not supported", w_type);
     return LAMMCU_ERR_TYPE;
   }
-  const int kmul = (w_type == LAMMCU_TYPE_F32) ? 8 : ti.blck;    // src/lamm_impl.hpp:123-126
+  const int kmul = (w_type == LAMMCU_TYPE_F32 || w_type == LAMMCU_TYPE_F16) ? 8 : ti.blck;    // src/lamm_impl.hpp:123-126
   if (M <= 0 || N <= 0 || K <= 0 || K % kmul || M > 0x3fffffff || K > 0x3fffffff) {
     set_error("gemv: bad shape M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K);
     return LAMMCU_ERR_SHAPE;
   }
-  const int walign = (w_type == LAMMCU_TYPE_F32 || w_type == LAMMCU_TYPE_Q2_K || w_type == LAMMCU_TYPE_Q4_K ||
+  const int walign = (w_type == LAMMCU_TYPE_F32 || w_type == LAMMCU_TYPE_F16 || w_type == LAMMCU_TYPE_Q2_K || w_type == LAMMCU_TYPE_Q4_K ||
                       w_type == LAMMCU_TYPE_Q5_K) ? 4 : 2;
-  const int xalign = (ti.vec_dot == LAMMCU_TYPE_Q8_0) ? 2 : 4;
+  const int xalign = (ti.vec_dot == LAMMCU_TYPE_Q8_0 || ti.vec_dot == LAMMCU_TYPE_F16) ? 2 : 4;
   if (((uintptr_t)w | (uintptr_t)w_stride) % walign || ((uintptr_t)xq | (uintptr_t)xq_stride) % xalign ||
       ((uintptr_t)c & 3)) {
     set_error("gemv: operand alignment (W %d-byte, Xq %d-byte, C 4-byte) not met", walign, xalign);
     return LAMMCU_ERR_ALIGN;
   }
   const int kb = (int)(K / ti.blck);
-  const int64_t row_bytes64 = (w_type == LAMMCU_TYPE_F32) ? K * 4 : (int64_t)kb * ti.size;
+  const int64_t row_bytes64 = (w_type == LAMMCU_TYPE_F32) ? K * 4 : (w_type == LAMMCU_TYPE_F16) ? K * 2 : (int64_t)kb * ti.size;
   const int slot_pitch = (int)(((row_bytes64 + 15 + 15) & ~(int64_t)15) + 16);
   if (kCtrlBytes + x_bytes_for(w_type, 1, kb, K) + 2 * slot_pitch > kSmemMax) {
     set_error("gemv: K=%lld too large for the shared-memory pipeline", (long long)K);
@@ -669,7 +709,7 @@ int launch_gemv(int w_type, const void *w, int64_t w_stride, const void *xq, int
   p.M = (int)M;              p.kb = kb;
   p.row_bytes = (int)row_bytes64;
   p.slot_pitch = slot_pitch;
-  p.units = (w_type == LAMMCU_TYPE_F32) ? (int)(K / 4) : (ti.blck == 256 ? kb * 8 : kb);
+  p.units = (w_type == LAMMCU_TYPE_F32) ? (int)(K / 4) : (w_type == LAMMCU_TYPE_F16) ? (int)(K / 8) : (ti.blck == 256 ? kb * 8 : kb);
 
   // rows per tile: the largest of 8/4/2/1 whose stage stays <= 24 KB
   int R = 8;
@@ -711,6 +751,7 @@ int launch_gemv(int w_type, const void *w, int64_t w_stride, const void *xq, int
     int rc;
     switch (w_type) {
     case LAMMCU_TYPE_F32:  rc = launch_nc<LAMMCU_TYPE_F32>(nc, p, grid, smem, st); break;
+    case LAMMCU_TYPE_F16:  rc = launch_nc<LAMMCU_TYPE_F16>(nc, p, grid, smem, st); break;
     case LAMMCU_TYPE_Q4_0: rc = launch_nc<LAMMCU_TYPE_Q4_0>(nc, p, grid, smem, st); break;
     case LAMMCU_TYPE_Q4_1: rc = launch_nc<LAMMCU_TYPE_Q4_1>(nc, p, grid, smem, st); break;
     case LAMMCU_TYPE_Q5_0: rc = launch_nc<LAMMCU_TYPE_Q5_0>(nc, p, grid, smem, st); break;

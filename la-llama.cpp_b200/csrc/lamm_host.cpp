@@ -85,7 +85,7 @@ bool lamm_can_mul_mat(const struct ggml_compute_params *params, const struct ggm
   if (src1->type != GGML_TYPE_F32 && (int)src1->type != vec_dot) return false;
   // --- what the CUDA path additionally needs ---
   const int64_t K = src0->ne[0];
-  const int kmul = (src0->type == GGML_TYPE_F32) ? 8 : lammcu_blck_size(src0->type);
+  const int kmul = (src0->type == GGML_TYPE_F32 || src0->type == GGML_TYPE_F16) ? 8 : lammcu_blck_size(src0->type);
   if (K <= 0 || K % kmul) return false;                                 // lamm_impl.hpp:123-126 aborts instead
   if (src0->nb[0] != lammcu_type_size(src0->type)) return false;        // rows are block-contiguous
   if (src0->nb[1] < lammcu_row_size(src0->type, K)) return false;
@@ -165,7 +165,7 @@ bool lamm_can_mul_mat_id(const struct ggml_compute_params *params, const struct 
   const ggml_tensor *a0 = dst->src[2];
   if (!a0 || !lammcu_type_supported(a0->type)) return false;
   const int64_t K = a0->ne[0];
-  const int kmul = (a0->type == GGML_TYPE_F32) ? 8 : lammcu_blck_size(a0->type);
+  const int kmul = (a0->type == GGML_TYPE_F32 || a0->type == GGML_TYPE_F16) ? 8 : lammcu_blck_size(a0->type);
   if (K <= 0 || K % kmul || K != src1->ne[0]) return false;
   for (int e = 0; e < n_as; e++) {
     const ggml_tensor *a = dst->src[2 + e];

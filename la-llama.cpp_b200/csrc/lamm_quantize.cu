@@ -86,8 +86,39 @@ __global__ void __launch_bounds__(256) quantize_q8_K_kernel(const float *__restr
   }
 }
 
+// ---- F16 ---------------------------------------------------------
+// ggml converts src1 to the F16 vec-dot type with ggml_fp32_to_fp16_row (ggml.c:10865-10887 -> :378-: IEEE round to
+// nearest even, F16C on x86): __float2half_rn is bit-identical.  4 elements per thread.
+__global__ void __launch_bounds__(256) convert_f16_kernel(const float *__restrict__ x, int64_t ldx, __half *__restrict__ y,
+                                                         int64_t n_rows, int64_t k) {
+  const int64_t k4 = k >> 2, total = n_rows * k4;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = i / k4, c = (i - row * k4) * 4;
+    const float *p = x + row * ldx + c;
+    const __half2 a = __floats2half2_rn(p[0], p[1]), b = __floats2half2_rn(p[2], p[3]);
+    uint2 o;
+    o.x = *reinterpret_cast<const uint32_t *>(&a);
+    o.y = *reinterpret_cast<const uint32_t *>(&b);
+    *reinterpret_cast<uint2 *>(y + row * k + c) = o;
+  }
+}
+
 int launch_quantize_act(int vt, const float *x, int64_t ldx, void *xq, int64_t n_rows, int64_t k,
                         cudaStream_t st) {
+  if (vt == LAMMCU_TYPE_F16) {
+    if (n_rows <= 0 || k <= 0 || k % 8 || ((uintptr_t)x & 3) || ((uintptr_t)xq & 7)) {
+      set_error("quantize_act: F16 needs K %% 8 == 0 and an 8-byte aligned output");
+      return LAMMCU_ERR_SHAPE;
+    }
+    int64_t blocks = (n_rows * (k / 4) + 255) / 256;
+    const int64_t cap = (int64_t)sm_count_cached() * 16;
+    if (blocks > cap) blocks = cap;
+    convert_f16_kernel<<<(int)blocks, 256, 0, st>>>(x, ldx, (__half *)xq, n_rows, k);
+    g_launch_count++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("convert_f16 launch: %s", cudaGetErrorString(e)); return LAMMCU_ERR_CUDA; }
+    return LAMMCU_OK;
+  }
   const TypeInfo ti = type_info(vt);
   if (vt != LAMMCU_TYPE_Q8_0 && vt != LAMMCU_TYPE_Q8_1 && vt != LAMMCU_TYPE_Q8_K) {
     set_error("quantize_act: type %d is not an activation type", vt);

@@ -254,7 +254,7 @@ void lammcu_launch_count_reset(void) { g_launch_count = 0; }
 
 // ---- type table -------------------------------------------------------------
 int lammcu_type_supported(int t) {
-  return t == LAMMCU_TYPE_F32 || t == LAMMCU_TYPE_Q2_K || t == LAMMCU_TYPE_Q4_0 ||
+  return t == LAMMCU_TYPE_F32 || t == LAMMCU_TYPE_F16 || t == LAMMCU_TYPE_Q2_K || t == LAMMCU_TYPE_Q4_0 ||
          t == LAMMCU_TYPE_Q4_1 || t == LAMMCU_TYPE_Q5_0 || t == LAMMCU_TYPE_Q5_1 ||
          t == LAMMCU_TYPE_Q8_0 || is_kquant_ext(t);
 }
@@ -319,7 +319,7 @@ int lammcu_mul_mat_dev(int w_type, const void *w, int64_t w_stride, const float 
   if (w_type == LAMMCU_TYPE_F32)   // F32 x F32: X is used as it is (src/loongarch_matmul.cpp:89-94)
     return lammcu_mul_mat_q_dev(w_type, w, w_stride, x, ldx * 4, c, ldc, M, N, K, stream);
   const int vt = type_info(w_type).vec_dot;
-  if (K <= 0 || K % type_info(w_type).blck || N <= 0) {
+  if (K <= 0 || K % type_info(w_type).blck || N <= 0 || (w_type == LAMMCU_TYPE_F16 && K % 8)) {
     set_error("mul_mat: bad shape N=%lld K=%lld", (long long)N, (long long)K);
     return LAMMCU_ERR_SHAPE;
   }

@@ -27,7 +27,7 @@ size_t lammcu_type_size(int t) { return orc_type_size(t); }
 size_t lammcu_row_size(int t, int64_t k) { return orc_row_size(t, k); }
 int lammcu_vec_dot_type(int t) { return orc_vec_dot_type(t); }
 int lammcu_type_supported(int t) {                         // the product's table (tests/test_abi.py::test_type_table)
-  return t == 0 || t == 2 || t == 3 || t == 6 || t == 7 || t == 8 || (t >= 10 && t <= 14);
+  return t == 0 || t == 1 || t == 2 || t == 3 || t == 6 || t == 7 || t == 8 || (t >= 10 && t <= 14);
 }
 int lammcu_weight_register(const void *w_host, int w_type, int64_t M, int64_t K, int64_t stride, int64_t row_begin,
                            int64_t row_end, lammcu_weight_t *out) {

@@ -22,15 +22,14 @@ TYPE_NAMES = {F32: "f32", Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1"
 NAME_TO_TYPE = {v: k for k, v in TYPE_NAMES.items()}
 W_TYPES = [F32, Q2_K, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0]     # src/loongarch_matmul.cpp:37-42
 KQ_TYPES = [Q3_K, Q4_K, Q5_K, Q6_K]                     # beyond the reference's table: ggml's own vec_dot is the oracle
-BLCK = {F32: 1, Q4_0: 32, Q4_1: 32, Q5_0: 32, Q5_1: 32, Q8_0: 32, Q8_1: 32, Q2_K: 256, Q8_K: 256,
+BLCK = {F32: 1, 1: 1, Q4_0: 32, Q4_1: 32, Q5_0: 32, Q5_1: 32, Q8_0: 32, Q8_1: 32, Q2_K: 256, Q8_K: 256,
         Q3_K: 256, Q4_K: 256, Q5_K: 256, Q6_K: 256}
-TSIZE = {F32: 4, Q4_0: 18, Q4_1: 20, Q5_0: 22, Q5_1: 24, Q8_0: 34, Q8_1: 36, Q2_K: 84, Q8_K: 292,
+TSIZE = {F32: 4, 1: 2, Q4_0: 18, Q4_1: 20, Q5_0: 22, Q5_1: 24, Q8_0: 34, Q8_1: 36, Q2_K: 84, Q8_K: 292,
          Q3_K: 110, Q4_K: 144, Q5_K: 176, Q6_K: 210}
-VEC_DOT = {F32: F32, Q4_0: Q8_0, Q4_1: Q8_1, Q5_0: Q8_0, Q5_1: Q8_1, Q8_0: Q8_0, Q2_K: Q8_K,
+VEC_DOT = {F32: F32, 1: 1, Q4_0: Q8_0, Q4_1: Q8_1, Q5_0: Q8_0, Q5_1: Q8_1, Q8_0: Q8_0, Q2_K: Q8_K,
            Q3_K: Q8_K, Q4_K: Q8_K, Q5_K: Q8_K, Q6_K: Q8_K}
 
-# SURVEY 8f-2, oracle only so far (no CUDA kernel; the product's type table refuses it, tests/test_abi.py):
-# kept out of BLCK / TSIZE / VEC_DOT, which tests/test_abi.py compares with the product's table
+# F16 weights x activations rounded to fp16 (ggml.c:486-496); in the product's table since round 2
 F16 = 1
 TYPE_NAMES[F16] = "f16"
 NAME_TO_TYPE["f16"] = F16

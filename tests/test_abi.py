@@ -36,7 +36,7 @@ def test_type_table(lamm):
         assert lamm.row_size(t, 4096) == 4096 // bs * TSIZE[t]
     for t, vt in VEC_DOT.items():
         assert lamm.vec_dot_type(t) == vt and lamm.lib().lammcu_type_supported(t) == 1
-    for t in (1, 9, 15, 16):                      # F16, Q8_1, Q8_K, IQ2_XXS: not on the path
+    for t in (9, 15, 16):                         # Q8_1, Q8_K, IQ2_XXS: not weight types of the path
         assert lamm.lib().lammcu_type_supported(t) == 0
 
 
