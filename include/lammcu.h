@@ -332,6 +332,7 @@ int lammcu_mul_mat_id_plan(const int32_t *ids, int64_t ids_stride, int id, int64
                            int n_as, int64_t *counts, int64_t *order);
 const void *lammcu_weight_dev_ptr(lammcu_weight_t w);
 int64_t lammcu_weight_rows(lammcu_weight_t w);
+int64_t lammcu_weight_bytes(lammcu_weight_t w);   /* device bytes held for it: rows x row_size, a rank's shard only */
 
 /* X (host f32, N rows, ldx elements) -> H2D -> quantize -> mul_mat -> D2H into
  * C (host f32, ldc elements; only the handle's rows [row_begin,row_end) of

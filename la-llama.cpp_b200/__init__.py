@@ -40,7 +40,7 @@ EXPORTS = [
     "lammcu_quantize_act_dev", "lammcu_mul_mat_q_dev", "lammcu_mul_mat_dev", "lammcu_set_gemv_max_n",
     "lammcu_get_gemv_max_n", "lammcu_set_decode_kernel", "lammcu_get_decode_kernel", "lammcu_set_trace", "lammcu_ipc_alloc", "lammcu_ipc_open", "lammcu_ipc_close", "lammcu_ipc_free", "lammcu_memcpy_async",
     "lammcu_mul_mat_batch_dev", "lammcu_mul_mat_noalloc_dev", "lammcu_chain_create", "lammcu_chain_run_dev", "lammcu_chain_status", "lammcu_chain_destroy", "lammcu_set_gemm_exact", "lammcu_get_gemm_exact", "lammcu_host_profile", "lammcu_set_host_mode", "lammcu_get_host_mode", "lammcu_host_quiesce", "lammcu_set_server_timeouts", "lammcu_server_trace", "lammcu_comm_create", "lammcu_comm_destroy", "lammcu_comm_status", "lammcu_ll_bytes", "lammcu_mul_mat_sharded_dev", "lammcu_mul_mat_sharded_batch_dev", "lammcu_mul_mat_sharded_gemm_dev", "lammcu_ll_unpack_dev", "lammcu_weight_register", "lammcu_weight_for_op", "lammcu_weight_lookup", "lammcu_weight_release", "lammcu_weight_forget", "lammcu_weight_forget_all",
-    "lammcu_weight_dev_ptr", "lammcu_weight_rows", "lammcu_mul_mat_host", "lammcu_mul_mat_q_host",
+    "lammcu_weight_dev_ptr", "lammcu_weight_rows", "lammcu_weight_bytes", "lammcu_mul_mat_host", "lammcu_mul_mat_q_host",
     "lamm_can_mul_mat", "lamm_mul_mat", "lamm_get_opt_level", "lamm_set_writeback_wdata",
     "lammcu_mul_mat_id_plan", "lamm_can_mul_mat_id", "lamm_mul_mat_id",
     "lammcu_gguf_open", "lammcu_gguf_close", "lammcu_gguf_tensor_count", "lammcu_gguf_alignment",
@@ -148,6 +148,8 @@ def lib():
     L.lammcu_weight_dev_ptr.argtypes = [vp]
     L.lammcu_weight_rows.restype = i64
     L.lammcu_weight_rows.argtypes = [vp]
+    L.lammcu_weight_bytes.restype = i64
+    L.lammcu_weight_bytes.argtypes = [vp]
     L.lammcu_mul_mat_host.argtypes = [vp, fp, i64, i64, fp, i64, vp]
     L.lammcu_mul_mat_q_host.argtypes = [vp, vp, i64, i64, fp, i64]
     L.lamm_can_mul_mat.restype = C.c_bool

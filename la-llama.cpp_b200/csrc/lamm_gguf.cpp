@@ -211,10 +211,17 @@ int lammcu_gguf_open(const char *path, lammcu_gguf_t *out) {
   for (Tensor &t : g->tensors) {
     const int bs = lammcu_blck_size(t.type);
     if (bs > 1 && t.ne[0] % bs) return fail(g, "tensor row is not a whole number of blocks");
+    // every factor is bounded by the file size BEFORE it is multiplied in: no product can wrap (hostile dims are up to
+    // 2^63 each, and lammcu_row_size itself wraps in size_t for ne0 near 2^62)
+    if ((uint64_t)t.ne[0] > g->size * 256) return fail(g, "tensor larger than the file");   // >= 1 byte per 256 elements
     const uint64_t rb = row_bytes(t.type, t.ne[0]);
-    unsigned __int128 nb = (unsigned __int128)rb * (uint64_t)t.ne[1] * (uint64_t)t.ne[2] * (uint64_t)t.ne[3];
+    uint64_t nb = rb;
+    for (int j = 1; j < 4 && nb; j++) {
+      if (nb > g->size || (t.ne[j] && (uint64_t)t.ne[j] > g->size / nb)) return fail(g, "tensor larger than the file");
+      nb *= (uint64_t)t.ne[j];
+    }
     if (nb > g->size) return fail(g, "tensor larger than the file");
-    t.nbytes = (uint64_t)nb;                              // 0: a ggml type this library has no size for
+    t.nbytes = nb;                                        // 0: a ggml type this library has no size for
     if (t.offset % g->alignment) return fail(g, "tensor offset is not aligned");
     if (t.offset > g->size - g->data_start || t.nbytes > g->size - g->data_start - t.offset)
       return fail(g, "tensor data outside the file");

@@ -904,6 +904,7 @@ int lammcu_weight_forget_all(void) {
 
 const void *lammcu_weight_dev_ptr(lammcu_weight_t w) { return w ? w->dev : nullptr; }
 int64_t lammcu_weight_rows(lammcu_weight_t w) { return w ? w->row_end - w->row_begin : 0; }
+int64_t lammcu_weight_bytes(lammcu_weight_t w) { return w ? (int64_t)w->bytes : 0; }
 
 // D2H of the shard's column range of every output row
 // Small results (decode / GEMV sizes) are written by the kernel straight into pinned host memory

@@ -10,6 +10,11 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
+def row_empty_somewhere(m, world):
+    per = (m + world - 1) // world
+    return per * (world - 1) >= m
+
+
 def main():
     import torch
     import torch.distributed as dist
@@ -110,6 +115,91 @@ def main():
         ok &= good
         print(f"rank {rank} type {t} sharded prefill {m}x{k} N={n}: err {err:.3g} (tol {tol:.3g}) {'ok' if good else 'FAIL'}", flush=True)
         dist.barrier()
+    # SURVEY 8f-4, sharded load: every rank opens the committed GGUF fixture, registers ONLY its row range of each 2-D
+    # tensor from the file mapping (gguf_init_from_file + the loader's reads, ggml.c:20655), and the sharded decode on
+    # those device rows reproduces the oracle on the whole tensor
+    from test_gguf import FIXTURE
+
+    class DevRows:                                           # what Comm.mul_mat needs of a cuda uint8 [rows, row_bytes]
+        def __init__(self, h, row_bytes):
+            self.h, self.rb = h, row_bytes
+            self.shape = (int(L.lib().lammcu_weight_rows(h)), row_bytes)
+
+        def data_ptr(self):
+            return int(L.lib().lammcu_weight_dev_ptr(self.h))
+
+        def stride(self, d):
+            return self.rb
+
+        def element_size(self):
+            return 1
+    # the committed fixture (written by the reference's gguf writer) has at most 33 rows per tensor; a second file with
+    # model-sized row counts is assembled here by rank 0 (version 3, default alignment 32, no key-value pairs)
+    import struct
+    import tempfile
+    big = os.path.join(tempfile.gettempdir(), f"lamm_shard_{os.environ.get('MASTER_PORT', '0')}.gguf")
+    big_tensors = [("w.q4_1", Q4_1, 1000, 4096), ("w.q5_0", Q5_0, 515, 2048), ("w.q2_k", Q2_K, 300, 1024), ("w.f16", 1, 64, 512)]
+    if rank == 0:
+        meta = b"GGUF" + struct.pack("<IQQ", 3, len(big_tensors), 0)
+        blobs, off = [], 0
+        for name, t, m, k in big_tensors:
+            rng = np.random.default_rng(m)
+            if t == 1:
+                wq = rng.standard_normal((m, k)).astype(np.float16).view(np.uint8).reshape(m, -1)
+            else:
+                wq = o.quantize_weights(t, rng.standard_normal((m, k)).astype(np.float32), seed=m)
+            meta += struct.pack("<Q", len(name)) + name.encode() + struct.pack("<IQQIQ", 2, k, m, t, off)
+            b = wq.tobytes() + b"\0" * ((-wq.nbytes) % 32)
+            blobs.append(b)
+            off += len(b)
+        with open(big, "wb") as f:
+            f.write(meta + b"\0" * ((-len(meta)) % 32) + b"".join(blobs))
+    dist.barrier()
+    for path, names in [(FIXTURE, ("blk.0.attn_q.weight", "blk.0.attn_k.weight", "blk.0.ffn_down.weight",
+                                   "blk.0.ffn_up.weight", "output.weight")),
+                        (big, tuple(n for n, _, _, _ in big_tensors))]:
+      with L.Gguf(path) as g:
+        try:
+            for name in names:
+                i = g.find(name)
+                if row_empty_somewhere(g.tensor(i)[3][1], world):
+                    continue                                     # fewer rows than ranks: not a sharding case
+                _, t, _, ne, raw = g.tensor(i)
+                k, m = ne[0], ne[1]
+                wq = raw.reshape(m, -1)
+                x = np.random.default_rng(m + k).standard_normal((1, k)).astype(np.float32)
+                want = o.mul_mat(t, wq, x)
+                lo, hi = sharding.row_shard(m, rank, world)
+                good = True
+                h = g.upload_rows(i, lo, hi)
+                good &= int(L.lib().lammcu_weight_bytes(h)) == (hi - lo) * wq.shape[1]         # its byte range, no more
+                shard = DevRows(h, wq.shape[1])
+                if t == 1:                                       # F16 rows: the row-sharded prefill GEMM (N = 40)
+                    x = np.random.default_rng(m + k).standard_normal((40, k)).astype(np.float32)
+                    want = o.mul_mat(t, wq, x)
+                    cb = comm.result_buffer(40, m)
+                    comm.mul_mat_gemm(t, shard, torch.from_numpy(x).cuda(), cb, m, 40, k)
+                    got_t = cb.to_tensor(torch, torch.float32, 40 * m).view(40, m)
+                    torch.cuda.synchronize()
+                    dist.barrier()
+                    err = np.abs(got_t.cpu().numpy() - want).max()
+                else:
+                    cbuf = sharding.LLVector(L, dist, m)
+                    comm.mul_mat(t, shard, torch.from_numpy(x).cuda(), cbuf, m, k)
+                    got_t = comm.unpack(torch, cbuf)
+                    torch.cuda.synchronize()
+                    dist.barrier()
+                    err = np.abs(got_t.cpu().numpy()[None, :] - want).max()
+                good &= bool(err <= 1e-5 * np.sqrt(k) * np.abs(want).max())
+                ok &= good
+                print(f"rank {rank} gguf {name} rows {lo}:{hi} of {m}: err {err:.3g} {'ok' if good else 'FAIL'}", flush=True)
+                dist.barrier()
+        finally:
+            torch.cuda.synchronize()
+            L.lib().lammcu_weight_forget_all()
+    dist.barrier()
+    if rank == 0:
+        os.unlink(big)
     ok &= not comm.timed_out()
     flag = torch.tensor([0 if ok else 1], device="cuda")
     dist.all_reduce(flag)

@@ -130,6 +130,27 @@ def test_truncated_and_corrupt_files_fail_cleanly(lamm, tmp_path):
     assert n == 9
 
 
+def test_hostile_dimensions_cannot_wrap_the_size_check(lamm, tmp_path):
+    """Dimensions whose byte count wraps 64 (or 128) bits must not pass as 'inside the file': F32 ne0 = 2^62 + 8 has a
+    row size of 32 bytes modulo 2^64; 2^32 x 2^32 x 2^32 x 2^32 rows of 4 bytes is 0 modulo 2^128."""
+    import struct
+
+    def s(b):
+        return struct.pack("<Q", len(b)) + b
+    path = str(tmp_path / "hostile.gguf")
+    for dims, typ in [((2 ** 62 + 8, 1), 0), ((2 ** 32, 2 ** 32, 2 ** 32, 2 ** 32), 0), ((32, 2 ** 63 - 1), 3),
+                      ((2 ** 62, 4), 1), ((2 ** 63 - 256, 1), 10), ((8, 2 ** 61, 8), 0)]:
+        meta = b"GGUF" + struct.pack("<IQQ", 3, 1, 0) + s(b"t") + struct.pack("<I", len(dims))
+        meta += b"".join(struct.pack("<Q", d) for d in dims) + struct.pack("<IQ", typ, 0)
+        open(path, "wb").write(meta + b"\0" * ((-len(meta)) % 32) + b"\0" * 64)
+        with pytest.raises(lamm.LammError):
+            lamm.Gguf(path)
+    meta = b"GGUF" + struct.pack("<IQQ", 3, 1, 0) + s(b"t") + struct.pack("<IQQIQ", 2, 8, 2, 0, 0)     # 8 x 2 F32: fits
+    open(path, "wb").write(meta + b"\0" * ((-len(meta)) % 32) + b"\0" * 64)
+    with lamm.Gguf(path) as g:
+        assert g.tensor(0)[3] == [8, 2, 1, 1] and g.tensor(0)[4].nbytes == 64
+
+
 def test_row_ranges_are_contiguous_byte_ranges(lamm):
     with lamm.Gguf(FIXTURE) as g:
         for i in range(len(g)):

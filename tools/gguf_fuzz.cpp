@@ -5,6 +5,8 @@
 //       tools/gguf_fuzz.cpp la-llama.cpp_b200/csrc/lamm_gguf.cpp -o /tmp/gguf_fuzz
 //   /tmp/gguf_fuzz tests/golden/gguf_fixture_v3.gguf 100000 <seed>
 // Round 1: 320 000 mutated files over 4 seeds, no ASan / UBSan report (about 12 % still parse).  Not part of the product.
+// Round 2: a fourth mutation writes dimension-sized 64-bit values (2^62 + 8, 2^63 - 1, 2^32 ...) over the metadata; see
+// profiles/r2s/gguf_fuzz.txt.
 #include "../include/lammcu.h"
 #include <cstdio>
 #include <cstdlib>
@@ -28,7 +30,13 @@ int main(int argc, char **argv) {
     int nmut = 1 + rand_r(&seed) % 4;
     for (int m = 0; m < nmut; m++) {
       size_t pos = rand_r(&seed) % 960;            // metadata region
-      int kind = rand_r(&seed) % 3;
+      int kind = rand_r(&seed) % 4;
+      if (kind == 3) {                             // round 2: dimension-sized values whose products wrap 64 / 128 bits
+        static const unsigned long long hostile[] = {(1ull << 62) + 8, (1ull << 63) - 1, 1ull << 32, 1ull << 61,
+                                                     (1ull << 63) - 256, (1ull << 62) + 32, 1ull << 48, 0xFFFFFFFFFFFFFFFFull};
+        const unsigned long long v = hostile[rand_r(&seed) % 8];
+        if (pos + 8 <= b.size()) memcpy(&b[pos], &v, 8);
+      } else
       if (kind == 0) b[pos] = (unsigned char)rand_r(&seed);
       else if (kind == 1) b[pos] ^= 1u << (rand_r(&seed) % 8);
       else { for (int j = 0; j < 8 && pos + j < b.size(); j++) b[pos + j] = 0xFF; }
@@ -41,6 +49,10 @@ int main(int argc, char **argv) {
     for (int64_t i = 0; i < lammcu_gguf_tensor_count(g); i++) {
       const char *name; int t, nd; int64_t ne[4]; const void *d; uint64_t nb;
       lammcu_gguf_tensor(g, i, &name, &t, &nd, ne, &d, &nb);
+      if (nb) {                                    // the recorded size is the exact product, never a wrapped one
+        unsigned __int128 want = (unsigned __int128)(nb / ((uint64_t)ne[1] * ne[2] * ne[3] ? (uint64_t)ne[1] * ne[2] * ne[3] : 1));
+        if ((unsigned __int128)want * (uint64_t)ne[1] * (uint64_t)ne[2] * (uint64_t)ne[3] != nb || nb > (1ull << 20)) { printf("size check wrapped\n"); abort(); }
+      }
       for (uint64_t j = 0; j < nb; j += 97) sum += ((const unsigned char *)d)[j];
       if (nb) sum += ((const unsigned char *)d)[nb - 1];
       sum += strlen(name);
