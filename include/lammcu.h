@@ -51,7 +51,8 @@ typedef enum {
   LAMMCU_ERR_SHAPE = -4,       /* K not a multiple of the block size, M/N<=0.. */
   LAMMCU_ERR_ALIGN = -5,       /* pointer / stride alignment not supported     */
   LAMMCU_ERR_ARG = -6,         /* NULL pointer, bad handle                     */
-  LAMMCU_ERR_NOMEM = -7
+  LAMMCU_ERR_NOMEM = -7,
+  LAMMCU_ERR_TIMEOUT = -8      /* a peer never published what a sharded call polled for */
 } lammcu_status;
 
 /* ggml type ids accepted (llama.cpp-b2430/ggml.h:341-369) */
@@ -132,6 +133,40 @@ int lammcu_mul_mat_noalloc_dev(int w_type, const void *w_dev, int64_t w_stride_b
 int lammcu_mul_mat_batch_dev(int w_type, int count, const void *const *w_dev,
                              int64_t w_stride_bytes, const int64_t *M, const float *x_dev,
                              float *const *c_dev, int64_t K, void *xq_ws_dev, void *stream);
+
+/* ---- the ops either side of the path, fused into the activation quantizer ---------------------
+ * llama.cpp's graph (build_llama, llama.cpp:5726-5800) never hands a matmul a raw tensor: src1 is either
+ *   LAMMCU_XOP_RMS_NORM_MUL  llm_build_norm (llama.cpp:5171-5201): ggml_rms_norm(x, eps) (ggml.c:10355-10405) then
+ *                            ggml_mul by the norm weight -- in front of wq/wk/wv, gate/up and the output head;
+ *                            aux = norm weight [K] (NULL: no weight), eps > 0
+ *   LAMMCU_XOP_SILU_MUL      llm_build_ffn (llama.cpp:5203-5290): ggml_silu(gate) (ggml.c:1894-1902, the fp16 table)
+ *                            times up -- in front of the down projection; x = gate, aux = up [N][ld_aux]
+ * and ggml then quantizes that f32 tensor in the matmul's INIT phase (ggml.c:10865-10887).  These entry points replace
+ * the three nodes (op, mul, quantize) + the matmul: the f32 intermediate never exists in memory, and for N == 1 the
+ * op is applied inside the decode kernel while it stages the row (ONE launch for norm + quantize + matmul).  The
+ * arithmetic is ggml's operation for operation (same IEEE roundings; the SiLU table is built by the host libm exactly
+ * as ggml_init builds it), so the quantized activations are the ones ggml would have produced.
+ * Rows of x and aux must be 16-byte aligned.  xq_ws_dev (may be NULL) receives the quantized rows.               */
+enum { LAMMCU_XOP_RMS_NORM_MUL = 1, LAMMCU_XOP_SILU_MUL = 2 };
+typedef struct lammcu_xop {
+  int kind;
+  const float *aux;       /* device pointer */
+  int64_t ld_aux;         /* SILU_MUL: floats between rows of aux */
+  float eps;              /* RMS_NORM_MUL */
+} lammcu_xop;
+/* op + quantize only: xq_dev = quantize(vt, op(x)), N rows packed at lammcu_row_size(vt, K); vt may also be
+ * LAMMCU_TYPE_F16 / LAMMCU_TYPE_F32 (plain conversion / the f32 result itself, what F16 / F32 weights consume)  */
+int lammcu_quantize_act_xop_dev(const lammcu_xop *op, int vt, const float *x_dev, int64_t ldx, void *xq_dev,
+                                int64_t N, int64_t K, void *stream);
+/* C = W . op(x): lammcu_mul_mat_dev with the op in front */
+int lammcu_mul_mat_xop_dev(const lammcu_xop *op, int w_type, const void *w_dev, int64_t w_stride_bytes,
+                           const float *x_dev, int64_t ldx, float *c_dev, int64_t ldc, int64_t M, int64_t N, int64_t K,
+                           void *xq_ws_dev, void *stream);
+/* N == 1 siblings sharing op(x) (wq/wk/wv after attn_norm, gate/up after ffn_norm): lammcu_mul_mat_batch_dev with the
+ * op in front -- one launch for the norm, the quantize and up to 4 matrices                                      */
+int lammcu_mul_mat_batch_xop_dev(const lammcu_xop *op, int w_type, int count, const void *const *w_dev,
+                                 int64_t w_stride_bytes, const int64_t *M, const float *x_dev, float *const *c_dev,
+                                 int64_t K, void *xq_ws_dev, void *stream);
 
 /* N == 1, a CHAIN of dependent matmuls as ONE persistent launch (the same extension class as the sibling batch above;
  * in llama.cpp's build_llama, llama.cpp:5726-5800, a decoded token is such a chain: q,k,v = W x; o = Wo v; g,u = W o;
@@ -222,6 +257,9 @@ int lammcu_comm_create(int rank, int world, lammcu_comm_t *out);
 int lammcu_comm_destroy(lammcu_comm_t comm);
 /* *timed_out = 1 if any poll on this communicator gave up (synchronous D2H read)    */
 int lammcu_comm_status(lammcu_comm_t comm, int *timed_out);
+/* the synchronisation point of a sharded chain: waits for the stream, then LAMMCU_ERR_TIMEOUT (and a message) if any
+ * poll of any earlier sharded call on this communicator gave up -- the results since then are not to be used.       */
+int lammcu_comm_sync(lammcu_comm_t comm, void *stream);
 /* bytes of an LL vector of M elements (8 per element); allocate with lammcu_ipc_alloc
  * (zero-filled: tag 0 is never used)                                                  */
 size_t lammcu_ll_bytes(int64_t M);

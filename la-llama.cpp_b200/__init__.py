@@ -39,7 +39,7 @@ EXPORTS = [
     "lammcu_blck_size", "lammcu_type_size", "lammcu_vec_dot_type", "lammcu_row_size",
     "lammcu_quantize_act_dev", "lammcu_mul_mat_q_dev", "lammcu_mul_mat_dev", "lammcu_set_gemv_max_n",
     "lammcu_get_gemv_max_n", "lammcu_set_decode_kernel", "lammcu_get_decode_kernel", "lammcu_set_trace", "lammcu_ipc_alloc", "lammcu_ipc_open", "lammcu_ipc_close", "lammcu_ipc_free", "lammcu_memcpy_async",
-    "lammcu_mul_mat_batch_dev", "lammcu_mul_mat_noalloc_dev", "lammcu_chain_create", "lammcu_chain_run_dev", "lammcu_chain_status", "lammcu_chain_destroy", "lammcu_set_gemm_exact", "lammcu_get_gemm_exact", "lammcu_host_profile", "lammcu_set_host_mode", "lammcu_get_host_mode", "lammcu_host_quiesce", "lammcu_set_server_timeouts", "lammcu_server_trace", "lammcu_comm_create", "lammcu_comm_destroy", "lammcu_comm_status", "lammcu_ll_bytes", "lammcu_mul_mat_sharded_dev", "lammcu_mul_mat_sharded_batch_dev", "lammcu_mul_mat_sharded_gemm_dev", "lammcu_ll_unpack_dev", "lammcu_weight_register", "lammcu_weight_for_op", "lammcu_weight_lookup", "lammcu_weight_release", "lammcu_weight_forget", "lammcu_weight_forget_all",
+    "lammcu_mul_mat_batch_dev", "lammcu_quantize_act_xop_dev", "lammcu_mul_mat_xop_dev", "lammcu_mul_mat_batch_xop_dev", "lammcu_mul_mat_noalloc_dev", "lammcu_chain_create", "lammcu_chain_run_dev", "lammcu_chain_status", "lammcu_chain_destroy", "lammcu_set_gemm_exact", "lammcu_get_gemm_exact", "lammcu_host_profile", "lammcu_set_host_mode", "lammcu_get_host_mode", "lammcu_host_quiesce", "lammcu_set_server_timeouts", "lammcu_server_trace", "lammcu_comm_create", "lammcu_comm_destroy", "lammcu_comm_status", "lammcu_comm_sync", "lammcu_ll_bytes", "lammcu_mul_mat_sharded_dev", "lammcu_mul_mat_sharded_batch_dev", "lammcu_mul_mat_sharded_gemm_dev", "lammcu_ll_unpack_dev", "lammcu_weight_register", "lammcu_weight_for_op", "lammcu_weight_lookup", "lammcu_weight_release", "lammcu_weight_forget", "lammcu_weight_forget_all",
     "lammcu_weight_dev_ptr", "lammcu_weight_rows", "lammcu_weight_bytes", "lammcu_mul_mat_host", "lammcu_mul_mat_q_host",
     "lamm_can_mul_mat", "lamm_mul_mat", "lamm_get_opt_level", "lamm_set_writeback_wdata",
     "lammcu_mul_mat_id_plan", "lamm_can_mul_mat_id", "lamm_mul_mat_id",
@@ -126,11 +126,15 @@ def lib():
     L.lammcu_ipc_free.argtypes = [vp]
     L.lammcu_memcpy_async.argtypes = [vp, vp, sz, vp]
     L.lammcu_mul_mat_batch_dev.argtypes = [C.c_int, C.c_int, C.POINTER(vp), i64, C.POINTER(i64), fp, C.POINTER(vp), i64, vp, vp]
+    L.lammcu_quantize_act_xop_dev.argtypes = [vp, C.c_int, vp, i64, vp, i64, i64, vp]
+    L.lammcu_mul_mat_xop_dev.argtypes = [vp, C.c_int, vp, i64, vp, i64, vp, i64, i64, i64, i64, vp, vp]
+    L.lammcu_mul_mat_batch_xop_dev.argtypes = [vp, C.c_int, C.c_int, C.POINTER(vp), i64, C.POINTER(i64), vp, C.POINTER(vp), i64, vp, vp]
     L.lammcu_host_profile.restype = None
     L.lammcu_host_profile.argtypes = [C.POINTER(C.c_double), C.c_int]
     L.lammcu_comm_create.argtypes = [C.c_int, C.c_int, C.POINTER(vp)]
     L.lammcu_comm_destroy.argtypes = [vp]
     L.lammcu_comm_status.argtypes = [vp, C.POINTER(C.c_int)]
+    L.lammcu_comm_sync.argtypes = [vp, vp]
     L.lammcu_ll_bytes.restype = C.c_size_t
     L.lammcu_ll_bytes.argtypes = [i64]
     L.lammcu_mul_mat_sharded_dev.argtypes = [vp, C.c_int, vp, i64, vp, C.c_int, C.POINTER(vp), i64, i64, i64, vp]
@@ -274,6 +278,65 @@ def mul_mat_batch(w_type, ws, x, outs):
     ms = (C.c_int64 * n)(*[w.shape[0] for w in ws])
     check(lib().lammcu_mul_mat_batch_dev(w_type, n, wp, stride, ms, x.data_ptr(), cp, k, None, _stream_ptr()),
           "mul_mat_batch")
+    return outs
+
+
+# ---- the op in front of the matmul, fused into the activation quantizer ----
+XOP_RMS_NORM_MUL, XOP_SILU_MUL = 1, 2
+
+
+class XOp(C.Structure):
+    """include/lammcu.h: lammcu_xop"""
+    _fields_ = [("kind", C.c_int), ("aux", C.c_void_p), ("ld_aux", C.c_int64), ("eps", C.c_float)]
+
+
+def rms_norm_op(norm_w, eps):
+    """llm_build_norm: ggml_rms_norm(x, eps) * norm_w (cuda f32 [K], or None)"""
+    op = XOp(XOP_RMS_NORM_MUL, norm_w.data_ptr() if norm_w is not None else None, 0, eps)
+    op._keep = norm_w
+    return op
+
+
+def silu_mul_op(up):
+    """llm_build_ffn: silu(x) * up (cuda f32 [N, K], row stride up.stride(0))"""
+    op = XOp(XOP_SILU_MUL, up.data_ptr(), up.stride(0), 0.0)
+    op._keep = up
+    return op
+
+
+def quantize_act_xop(op, x, vt):
+    """quantize(vt, op(x)): x cuda f32 [N, K] -> cuda uint8 [N, row_size(vt, K)] (vt F32: the f32 bytes of op(x))"""
+    import torch
+    n, k = x.shape
+    rs = k * 4 if vt == F32 else row_size(vt, k)
+    out = torch.empty((n, rs), dtype=torch.uint8, device=x.device)
+    check(lib().lammcu_quantize_act_xop_dev(C.byref(op), vt, x.data_ptr(), x.stride(0), out.data_ptr(), n, k,
+                                            _stream_ptr()), "quantize_act_xop")
+    return out
+
+
+def mul_mat_xop(op, w_type, w, x, out=None, ws=None):
+    """C = W . op(x): mul_mat with the op fused in front (N == 1: one launch)."""
+    import torch
+    m, (n, k) = w.shape[0], x.shape
+    if out is None:
+        out = torch.empty((n, m), dtype=torch.float32, device=x.device)
+    check(lib().lammcu_mul_mat_xop_dev(C.byref(op), w_type, w.data_ptr(), w.stride(0) * w.element_size(), x.data_ptr(),
+                                       x.stride(0), out.data_ptr(), out.stride(0), m, n, k,
+                                       ws.data_ptr() if ws is not None else None, _stream_ptr()), "mul_mat_xop")
+    return out
+
+
+def mul_mat_batch_xop(op, w_type, ws, x, outs):
+    """Sibling matmuls sharing op(x) (N = 1): outs[j] = ws[j] . op(x), one launch when possible."""
+    n = len(ws)
+    k = x.shape[-1]
+    stride = ws[0].stride(0) * ws[0].element_size()
+    wp = (C.c_void_p * n)(*[w.data_ptr() for w in ws])
+    cp = (C.c_void_p * n)(*[o.data_ptr() for o in outs])
+    ms = (C.c_int64 * n)(*[w.shape[0] for w in ws])
+    check(lib().lammcu_mul_mat_batch_xop_dev(C.byref(op), w_type, n, wp, stride, ms, x.data_ptr(), cp, k, None,
+                                             _stream_ptr()), "mul_mat_batch_xop")
     return outs
 
 

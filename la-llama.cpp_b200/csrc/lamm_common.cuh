@@ -170,9 +170,10 @@ struct BatchInfo {
   float *c[4];
   int64_t M[4];
 };
+struct XOp;                                  // lamm_xop.cuh: the op fused in front of the matmul
 int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
                   float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh = nullptr,
-                  const BatchInfo *bt = nullptr);
+                  const BatchInfo *bt = nullptr, const XOp *xop = nullptr);
 // persistent decode chain (lamm_decode.cu): a list of N == 1 mul_mats, each possibly a sibling batch, run by ONE launch
 struct ChainOp {
   int count;                 // 1..4 matrices that share the activation row

@@ -20,6 +20,7 @@
 //     streaming its (immutable) weights while this one drains -- activations are only read
 //     after griddepcontrol.wait.
 #include "lamm_quant_dev.cuh"
+#include "lamm_xop.cuh"
 
 #include <algorithm>
 #include <vector>
@@ -65,6 +66,8 @@ struct DecodeParams {
   // sharded sibling batch: matrix j of the batch has its own LL vector on every rank;
   // llb[j][g] is a VIRTUAL base (pointer + first row of this rank's shard - rows before matrix j)
   unsigned long long *llb[4][LAMMCU_MAX_RANKS];
+  // SURVEY 8f-3 (XM == 1 only): the op in front of the matmul, applied while the row is staged (lamm_xop.cuh)
+  int xop_kind;  const float *x_aux;  float x_eps;  const uint16_t *silu_tab;
 };
 
 // ---- integer dots -------------------------------------------------------------------
@@ -256,6 +259,15 @@ __device__ __forceinline__ void load_x8(const DecodeParams &p, size_t e, unsigne
     const float4 *xp = reinterpret_cast<const float4 *>(p.x + e);
     a = xp[0];
     b = xp[1];
+    // for plain f32 rows `tag` is free and carries the bits of the row's RMS scale
+    if (p.xop_kind == 1) {
+      const float sc = __uint_as_float(tag);
+      a = xop_norm4(a, sc, p.x_aux ? p.x_aux + e : nullptr);
+      b = xop_norm4(b, sc, p.x_aux ? p.x_aux + e + 4 : nullptr);
+    } else if (p.xop_kind == 2) {
+      a = xop_silu4(a, p.x_aux + e, p.silu_tab);
+      b = xop_silu4(b, p.x_aux + e + 4, p.silu_tab);
+    }
   }
 }
 
@@ -1059,6 +1071,10 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
     pdl_wait();
   }
   trace_stamp(p.trace, 2);
+  if constexpr (XM == 1 && !SERVER) {
+    // llm_build_norm in front of this matmul: every CTA reduces the row itself (K floats, L2-resident)
+    if (p.xop_kind == 1) x_tag = __float_as_uint(cta_rms_scale(p.x, p.kb * (int)type_info(WT).blck, p.x_eps, smem + 256));   // [256, 516): free until the first partial sum
+  }
   if constexpr (SERVER) {
     // p.x_back != 0 (job word 15): the host found this call's activation row identical to the previous job's
     // (q/k/v and gate/up share src1), and this instance quantized that row into xs then: nothing crossed
@@ -1749,7 +1765,8 @@ int launch_decode_server(int w_type, const ServerParams &sp, cudaStream_t st) {
 }
 
 int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, const void *xq, void *xq_out,
-                  float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh, const BatchInfo *bt) {
+                  float *c, int64_t M, int64_t K, cudaStream_t st, const ShardInfo *sh, const BatchInfo *bt,
+                  const XOp *xop) {
   const TypeInfo ti = type_info(w_type);
   const bool q2k = (ti.blck == 256);               // super-block formats: unit = half a super-block
   DecodeParams p = {};
@@ -1763,7 +1780,14 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
     return (e && atoi(e) == 8) ? 8 : 16;
   }();
   // peer stores, sibling batches and the K-quants beyond Q2_K live in the 16-warp kernel
-  const int variant = (sh || bt || is_kquant_ext(w_type)) ? 16 : variant_env;
+  const int variant = (sh || bt || xop || is_kquant_ext(w_type)) ? 16 : variant_env;
+  if (xop && xop->kind) {
+    if (!x || (sh && sh->x_ll)) { set_error("decode: a fused op needs a plain f32 activation row"); return LAMMCU_ERR_ARG; }
+    if (xop->kind == 1 && !(xop->eps > 0.f)) { set_error("decode: rms_norm needs eps > 0"); return LAMMCU_ERR_ARG; }
+    if (((uintptr_t)xop->aux & 15) || (xop->kind == 2 && !xop->aux)) { set_error("decode: fused op operand NULL or not 16-byte aligned"); return LAMMCU_ERR_ALIGN; }
+    p.xop_kind = xop->kind;  p.x_aux = xop->aux;  p.x_eps = xop->eps;
+    if (xop->kind == 2 && !(p.silu_tab = silu_table_dev())) return LAMMCU_ERR_CUDA;
+  }
   if (bt) {
     p.nbatch = bt->count;
     int64_t first[4] = {0, 0, 0, 0};

@@ -4,6 +4,7 @@
 // exported signatures.  There is no CPU fallback: without a device every
 // compute entry point returns LAMMCU_ERR_NO_DEVICE.
 #include "lamm_common.cuh"
+#include "lamm_xop.cuh"
 #include <algorithm>
 #include <chrono>
 
@@ -492,6 +493,19 @@ int lammcu_comm_status(lammcu_comm_t c, int *timed_out) {
   return LAMMCU_OK;
 }
 
+int lammcu_comm_sync(lammcu_comm_t c, void *stream) {
+  if (!c) return LAMMCU_ERR_ARG;
+  CU_TRY(cudaStreamSynchronize(pick_stream(stream)));
+  int bad = 0;
+  int rc = lammcu_comm_status(c, &bad);
+  if (rc) return rc;
+  if (bad) {
+    set_error("comm_sync: rank %d of %d gave up polling a peer (a rank died or never launched its shard)", c->rank, c->world);
+    return LAMMCU_ERR_TIMEOUT;
+  }
+  return LAMMCU_OK;
+}
+
 size_t lammcu_ll_bytes(int64_t M) { return (size_t)M * 8; }
 
 int lammcu_mul_mat_sharded_dev(lammcu_comm_t comm, int w_type, const void *w_shard, int64_t w_stride,
@@ -713,6 +727,99 @@ int lammcu_mul_mat_batch_dev(int w_type, int count, const void *const *w_dev, in
   }
   for (int j = 0; j < count; j++) {
     rc = lammcu_mul_mat_dev(w_type, w_dev[j], w_stride, x_dev, K, c_dev[j], M[j], M[j], 1, K, xq_ws_dev, stream);
+    if (rc) return rc;
+  }
+  return LAMMCU_OK;
+}
+
+// ---- the op in front of the matmul, fused (lamm_xop.cuh) --------------------------------------
+static int xop_from(const lammcu_xop *op, XOp *out) {
+  if (!op || (op->kind != LAMMCU_XOP_RMS_NORM_MUL && op->kind != LAMMCU_XOP_SILU_MUL)) {
+    set_error("xop: NULL or unknown kind (1 = rms_norm x weight, 2 = silu(gate) x up)");
+    return LAMMCU_ERR_ARG;
+  }
+  out->kind = op->kind;  out->aux = op->aux;  out->ld_aux = op->ld_aux;  out->eps = op->eps;  out->silu = nullptr;
+  return LAMMCU_OK;
+}
+
+int lammcu_quantize_act_xop_dev(const lammcu_xop *op, int vt, const float *x, int64_t ldx, void *xq, int64_t N,
+                                int64_t K, void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  XOp xo;
+  if ((rc = xop_from(op, &xo))) return rc;
+  if (!x || !xq) { set_error("quantize_act_xop: NULL operand"); return LAMMCU_ERR_ARG; }
+  return launch_xop_quantize(xo, vt, x, ldx, xq, N, K, pick_stream(stream));
+}
+
+int lammcu_mul_mat_xop_dev(const lammcu_xop *op, int w_type, const void *w, int64_t w_stride, const float *x,
+                           int64_t ldx, float *c, int64_t ldc, int64_t M, int64_t N, int64_t K, void *xq_ws,
+                           void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  XOp xo;
+  if ((rc = xop_from(op, &xo))) return rc;
+  if (!w || !x || !c) { set_error("mul_mat_xop: NULL operand"); return LAMMCU_ERR_ARG; }
+  if (!lammcu_type_supported(w_type)) { set_error("mul_mat_xop: type %d not supported", w_type); return LAMMCU_ERR_TYPE; }
+  const int vt = type_info(w_type).vec_dot;
+  const int kmul = (w_type == LAMMCU_TYPE_F32 || w_type == LAMMCU_TYPE_F16) ? 8 : type_info(w_type).blck;
+  if (K <= 0 || K % kmul || N <= 0 || M <= 0) { set_error("mul_mat_xop: bad shape M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K); return LAMMCU_ERR_SHAPE; }
+  cudaStream_t st = pick_stream(stream);
+  // decode: ONE launch -- the op is applied while every CTA stages (and quantizes) the row
+  if (N == 1 && g_decode_kernel && decode_supported(w_type, w, w_stride, x, M, K) && (((uintptr_t)xo.aux) & 15) == 0 &&
+      (!xq_ws || ((uintptr_t)xq_ws & 3) == 0))
+    return launch_decode(w_type, w, w_stride, x, nullptr, xq_ws, c, M, K, st, nullptr, nullptr, &xo);
+  // otherwise: op + quantize in one launch, then the matmul on the quantized rows
+  const size_t rs = (w_type == LAMMCU_TYPE_F32) ? (size_t)K * 4 : lammcu_row_size(vt, K);
+  if (!xq_ws) {
+    rc = grow(&g_dev.ws, &g_dev.ws_bytes, rs * (size_t)N, false);
+    if (rc) return rc;
+    xq_ws = g_dev.ws;
+  }
+  rc = launch_xop_quantize(xo, vt, x, ldx, xq_ws, N, K, st);
+  if (rc) return rc;
+  return lammcu_mul_mat_q_dev(w_type, w, w_stride, xq_ws, (int64_t)rs, c, ldc, M, N, K, stream);
+}
+
+int lammcu_mul_mat_batch_xop_dev(const lammcu_xop *op, int w_type, int count, const void *const *w_dev, int64_t w_stride,
+                                 const int64_t *M, const float *x_dev, float *const *c_dev, int64_t K, void *xq_ws_dev,
+                                 void *stream) {
+  int rc = ensure_init();
+  if (rc) return rc;
+  XOp xo;
+  if ((rc = xop_from(op, &xo))) return rc;
+  if (count < 1 || !w_dev || !M || !x_dev || !c_dev) { set_error("mul_mat_batch_xop: bad argument"); return LAMMCU_ERR_ARG; }
+  for (int j = 0; j < count; j++)
+    if (!w_dev[j] || !c_dev[j] || M[j] <= 0) { set_error("mul_mat_batch_xop: bad operand %d", j); return LAMMCU_ERR_ARG; }
+  if (!lammcu_type_supported(w_type)) { set_error("mul_mat_batch_xop: type %d not supported", w_type); return LAMMCU_ERR_TYPE; }
+  bool fuse = count >= 2 && count <= 4 && g_decode_kernel && (((uintptr_t)xo.aux) & 15) == 0;
+  int64_t total = 0;
+  for (int j = 0; fuse && j < count; j++) {
+    fuse = decode_supported(w_type, w_dev[j], w_stride, x_dev, M[j], K) &&
+           (((uintptr_t)total * (uintptr_t)w_stride) & 15) == 0 && (((uintptr_t)w_dev[j] & 15) == ((uintptr_t)w_dev[0] & 15));
+    total += M[j];
+  }
+  if (fuse && total <= 0x3fffffff) {
+    BatchInfo bt = {};
+    bt.count = count;
+    for (int j = 0; j < count; j++) { bt.w[j] = w_dev[j]; bt.c[j] = c_dev[j]; bt.M[j] = M[j]; }
+    return launch_decode(w_type, w_dev[0], w_stride, x_dev, nullptr, nullptr, c_dev[0], total, K, pick_stream(stream),
+                         nullptr, &bt, &xo);
+  }
+  // not fusable: the op + quantize once, then one matmul per matrix on the shared quantized row
+  const int vt = type_info(w_type).vec_dot;
+  const int kmul = (w_type == LAMMCU_TYPE_F32 || w_type == LAMMCU_TYPE_F16) ? 8 : type_info(w_type).blck;
+  if (K <= 0 || K % kmul) { set_error("mul_mat_batch_xop: bad K=%lld", (long long)K); return LAMMCU_ERR_SHAPE; }
+  const size_t rs = (w_type == LAMMCU_TYPE_F32) ? (size_t)K * 4 : lammcu_row_size(vt, K);
+  if (!xq_ws_dev) {
+    rc = grow(&g_dev.ws, &g_dev.ws_bytes, rs, false);
+    if (rc) return rc;
+    xq_ws_dev = g_dev.ws;
+  }
+  rc = launch_xop_quantize(xo, vt, x_dev, K, xq_ws_dev, 1, K, pick_stream(stream));
+  if (rc) return rc;
+  for (int j = 0; j < count; j++) {
+    rc = lammcu_mul_mat_q_dev(w_type, w_dev[j], w_stride, xq_ws_dev, (int64_t)rs, c_dev[j], M[j], M[j], 1, K, stream);
     if (rc) return rc;
   }
   return LAMMCU_OK;

@@ -184,6 +184,10 @@ class Comm:
                                                              self.lamm._stream_ptr()), "ll_unpack")
         return out
 
+    def sync(self):
+        """Wait for the stream; raises LammError if any poll of an earlier sharded call gave up."""
+        self.lamm.check(self.lamm.lib().lammcu_comm_sync(self.handle, self.lamm._stream_ptr()), "comm_sync")
+
     def timed_out(self):
         v = C.c_int(0)
         self.lamm.check(self.lamm.lib().lammcu_comm_status(self.handle, C.byref(v)), "comm_status")

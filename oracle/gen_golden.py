@@ -100,6 +100,21 @@ def main():
     wq = r.quantize_weights(F16, w)
     np.savez_compressed(os.path.join(OUT, f"next_f16_m{m}_n{n}_k{k}.npz"), w_type=F16, wq=wq, x=x,
                         c_graph=r.graph_mul_mat(F16, wq, x))
+    # llm_build_norm and llm_build_ffn's silu(gate) * up in front of a Q4_1 matmul, through stock ggml's graph
+    # (one thread: SURVEY 9-3).  y = the f32 activation the matmul consumed; Gaussian rows only (no quantizer ties: the
+    # x86 INIT quantizer rounds halves to even)
+    rng = np.random.default_rng(20240317)
+    m, n, k = 33, 6, 2048
+    wq = r.quantize_weights(3, rng.standard_normal((m, k)).astype(np.float32))
+    x = (rng.standard_normal((n, k)) * 3).astype(np.float32)
+    x[1] = 0.0
+    norm_w = (1.0 + 0.1 * rng.standard_normal(k)).astype(np.float32)
+    c1, y1 = r.graph_xop_mul_mat(1, 3, wq, x, norm_w, 1e-5)
+    gate = (rng.standard_normal((n, k)) * 4).astype(np.float32)
+    up = rng.standard_normal((n, k)).astype(np.float32)
+    c2, y2 = r.graph_xop_mul_mat(2, 3, wq, gate, up)
+    np.savez_compressed(os.path.join(OUT, f"xop_q4_1_m{m}_n{n}_k{k}.npz"), w_type=3, wq=wq, x=x, norm_w=norm_w,
+                        eps=np.float32(1e-5), y_norm=y1, c_norm=c1, gate=gate, up=up, y_silu=y2, c_silu=c2)
     # a GGUF file written by the reference's own writer (key/values of every kind + 9 tensors)
     from oracle_lib import Oracle
     from test_gguf import FIXTURE, fixture_tensors

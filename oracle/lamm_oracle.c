@@ -789,6 +789,49 @@ static void *mt_worker(void *p) {
   return NULL;
 }
 
+/* ------------------------------------------------------------------ */
+/* the ops either side of the path                        */
+/* ------------------------------------------------------------------ */
+/* ggml_compute_forward_rms_norm_f32 (ggml.c:10355-10405): the sum of the f32 squares is kept in a double
+ * (ggml_float) in element order, mean = (float)(sum / K), scale = 1.0f / sqrtf(mean + eps), y = x * scale
+ * (ggml_vec_scale_f32); then llm_build_norm's ggml_mul by the norm weight (llama.cpp:5171-5201), one f32
+ * product per element.  norm_w may be NULL (no weight).                                                       */
+int orc_rms_norm_mul(const float *x, int64_t ldx, const float *norm_w, float eps, float *y, int64_t ldy,
+                     int64_t n_rows, int64_t k) {
+  if (!x || !y || n_rows < 0 || k <= 0 || !(eps > 0.0f)) return -1;
+  for (int64_t r = 0; r < n_rows; r++) {
+    const float *xr = x + r * ldx;
+    float *yr = y + r * ldy;
+    double sum = 0.0;
+    for (int64_t i = 0; i < k; i++) sum += (double)(xr[i] * xr[i]);
+    const float mean = (float)(sum / (double)k);
+    const float scale = 1.0f / sqrtf(mean + eps);
+    for (int64_t i = 0; i < k; i++) {
+      float v = xr[i] * scale;
+      if (norm_w) v = v * norm_w[i];
+      yr[i] = v;
+    }
+  }
+  return 0;
+}
+
+/* ggml_vec_silu_f32 with GGML_SILU_FP16 (ggml.c:157, 1894-1902): the argument is rounded to fp16 and looked up in a
+ * 65 536-entry table that ggml_init filled with fp16(silu(f32(h))), silu(f) = f / (1 + expf(-f)) (ggml.c:1883-1885,
+ * 2711-2719).  The value is therefore a function of the fp16 pattern only; expf is the host libm's, as in ggml.    */
+float orc_silu(float x) {
+  const float f = orc_fp16_to_fp32(orc_fp32_to_fp16(x));
+  return orc_fp16_to_fp32(orc_fp32_to_fp16(f / (1.0f + expf(-f))));
+}
+
+/* llm_build_ffn, LLM_FFN_SILU + LLM_FFN_PAR (llama.cpp:5203-5290): y = silu(gate) * up, one f32 product            */
+int orc_silu_mul(const float *gate, int64_t ldg, const float *up, int64_t ldu, float *y, int64_t ldy, int64_t n_rows,
+                 int64_t k) {
+  if (!gate || !up || !y || n_rows < 0 || k <= 0) return -1;
+  for (int64_t r = 0; r < n_rows; r++)
+    for (int64_t i = 0; i < k; i++) y[r * ldy + i] = orc_silu(gate[r * ldg + i]) * up[r * ldu + i];
+  return 0;
+}
+
 int orc_mul_mat_mt(int w_type, const void *w, int64_t w_stride, const float *x,
                    int64_t ldx, float *c, int64_t ldc, int64_t M, int64_t N,
                    int64_t K, int nth, void *xq_scratch) {

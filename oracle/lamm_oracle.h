@@ -131,6 +131,13 @@ int orc_mul_mat_id(int w_type, const void *const *ws, int n_as, int64_t w_stride
 /* multi-threaded (pthreads over M) f32-order variant: the timed "port" CPU
  * baseline.  nth threads, rows split like src/lamm_impl.hpp:40-45 but with the
  * remainder rows given to the last thread (defect 9-3 not reproduced).      */
+/* llm_build_norm (RMS norm, then the norm weight) and llm_build_ffn's silu(gate) * up, in f32 as ggml
+ * computes them; the matmul that follows quantizes the result like any other activation (orc_mul_mat).             */
+int orc_rms_norm_mul(const float *x, int64_t ldx, const float *norm_w, float eps, float *y, int64_t ldy,
+                     int64_t n_rows, int64_t k);
+float orc_silu(float x);
+int orc_silu_mul(const float *gate, int64_t ldg, const float *up, int64_t ldu, float *y, int64_t ldy, int64_t n_rows,
+                 int64_t k);
 int orc_mul_mat_mt(int w_type, const void *w, int64_t w_stride, const float *x,
                    int64_t ldx, float *c, int64_t ldc, int64_t M, int64_t N,
                    int64_t K, int nth, void *xq_scratch);

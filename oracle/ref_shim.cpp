@@ -253,6 +253,51 @@ int ref_graph_mul_mat_id(int w_type, const void *ws, int n_as, const int32_t *id
   return 0;
 }
 
+// the ops either side of the path as llama.cpp's graph builds them.
+//   kind 1: llm_build_norm (llama.cpp:5171-5201): ggml_rms_norm(x, eps) then ggml_mul(., norm_w)   [aux = norm_w, K floats]
+//   kind 2: llm_build_ffn's SiLU-gated branch (llama.cpp:5203-5290): ggml_silu(gate) then ggml_mul(., up)
+//           [x = gate, aux = up, both N x K]
+// followed by ggml_mul_mat(w, .).  y_out (may be NULL) receives the f32 activation the matmul consumed.
+int ref_graph_xop_mul_mat(int kind, int w_type, const void *w, const float *x, const float *aux, float eps, float *c,
+                          float *y_out, int64_t M, int64_t N, int64_t K, int nth) {
+  ref_init();
+  if (kind != 1 && kind != 2) return -2;
+  const size_t wbytes = ggml_row_size((enum ggml_type)w_type, K) * (size_t)M;
+  size_t ctx_size = wbytes + (size_t)K * N * 4 * 5 + (size_t)M * N * 4 + (16u << 20);
+  struct ggml_init_params ip = {ctx_size, nullptr, false};
+  struct ggml_context *ctx = ggml_init(ip);
+  if (!ctx) return -1;
+  struct ggml_tensor *tw = ggml_new_tensor_2d(ctx, (enum ggml_type)w_type, K, M);
+  memcpy(tw->data, w, wbytes);
+  struct ggml_tensor *tx = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, K, N);
+  memcpy(tx->data, x, (size_t)K * N * 4);
+  struct ggml_tensor *ty;
+  if (kind == 1) {
+    ty = ggml_rms_norm(ctx, tx, eps);
+    if (aux) {
+      struct ggml_tensor *tn = ggml_new_tensor_1d(ctx, GGML_TYPE_F32, K);
+      memcpy(tn->data, aux, (size_t)K * 4);
+      ty = ggml_mul(ctx, ty, tn);
+    }
+  } else {
+    struct ggml_tensor *tu = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, K, N);
+    memcpy(tu->data, aux, (size_t)K * N * 4);
+    ty = ggml_mul(ctx, ggml_silu(ctx, tx), tu);
+  }
+  struct ggml_tensor *tc = ggml_mul_mat(ctx, tw, ty);
+  struct ggml_cgraph *g = ggml_new_graph(ctx);
+  ggml_build_forward_expand(g, tc);
+  struct ggml_cplan plan = ggml_graph_plan(g, nth);
+  std::vector<uint8_t> work(plan.work_size + 16);
+  plan.work_data = work.data();
+  ggml_graph_compute(g, &plan);
+  memcpy(c, tc->data, (size_t)M * N * 4);
+  if (y_out) memcpy(y_out, ty->data, (size_t)K * N * 4);
+  model_freed();
+  ggml_free(ctx);
+  return 0;
+}
+
 // A GGUF file written by the reference's own writer (gguf_add_tensor + gguf_write_to_file,
 // ggml.c:21160-21420), with key/values of every scalar kind, a string array and a numeric array
 // ahead of the tensors: the fixture our reader (csrc/lamm_gguf.cpp) is pinned against.

@@ -200,6 +200,7 @@ def main():
     dist.barrier()
     if rank == 0:
         os.unlink(big)
+    comm.sync()                                              # raises if any LL poll gave up
     ok &= not comm.timed_out()
     flag = torch.tensor([0 if ok else 1], device="cuda")
     dist.all_reduce(flag)

@@ -155,6 +155,26 @@ class Oracle:
         assert rc == 0, rc
         return c
 
+    def rms_norm_mul(self, x, norm_w, eps):
+        """ggml_rms_norm then ggml_mul by the norm weight (None: no weight) -> f32 [N, K]"""
+        x = np.ascontiguousarray(x, np.float32)
+        n, k = x.shape
+        y = np.zeros((n, k), np.float32)
+        w = None if norm_w is None else np.ascontiguousarray(norm_w, np.float32)
+        self.L.orc_rms_norm_mul.argtypes = [fp, i64, fp, C.c_float, fp, i64, i64, i64]
+        assert self.L.orc_rms_norm_mul(_fptr(x), k, None if w is None else _fptr(w), eps, _fptr(y), k, n, k) == 0
+        return y
+
+    def silu_mul(self, gate, up):
+        """ggml_silu(gate) * up (fp16 table SiLU, ggml.c:1894-1902) -> f32 [N, K]"""
+        gate = np.ascontiguousarray(gate, np.float32)
+        up = np.ascontiguousarray(up, np.float32)
+        n, k = gate.shape
+        y = np.zeros((n, k), np.float32)
+        self.L.orc_silu_mul.argtypes = [fp, i64, fp, i64, fp, i64, i64, i64]
+        assert self.L.orc_silu_mul(_fptr(gate), k, _fptr(up), k, _fptr(y), k, n, k) == 0
+        return y
+
     def mul_mat_mt(self, t, wq, x, nth):
         wq = np.ascontiguousarray(wq)
         x = np.ascontiguousarray(x, np.float32)
@@ -265,6 +285,21 @@ class Ref:
                                          m, n, k, nth)
         assert rc == 0, rc
         return c
+
+    def graph_xop_mul_mat(self, kind, t, wq, x, aux, eps=0.0, nth=1):
+        """SURVEY 8f-3 through stock ggml's graph: kind 1 = rms_norm(x, eps) * aux[K] (aux None: no weight), kind 2 =
+        silu(x) * aux[N, K]; then ggml_mul_mat(w, .).  Returns (C [N, M], y [N, K] = what the matmul consumed)."""
+        wq = np.ascontiguousarray(wq)
+        x = np.ascontiguousarray(x, np.float32)
+        m, (n, k) = wq.shape[0], x.shape
+        c = np.zeros((n, m), np.float32)
+        y = np.zeros((n, k), np.float32)
+        a = None if aux is None else np.ascontiguousarray(aux, np.float32)
+        self.L.ref_graph_xop_mul_mat.argtypes = [C.c_int, C.c_int, vp, fp, fp, C.c_float, fp, fp, i64, i64, i64, C.c_int]
+        rc = self.L.ref_graph_xop_mul_mat(kind, t, _ptr(wq), _fptr(x), None if a is None else _fptr(a), eps, _fptr(c),
+                                          _fptr(y), m, n, k, nth)
+        assert rc == 0, rc
+        return c, y
 
     def gguf_write(self, path, tensors, alignment=0):
         """tensors: list of (name, ggml type, numpy array [ne1, row bytes] or 1-D bytes, ne0, ne1 (0 = 1-D)) written with

@@ -84,6 +84,19 @@ def test_f16_weights_golden(oracle):
                           g["x"].astype(np.float16).view(np.uint16))
 
 
+def test_xop_golden(oracle):
+    """SURVEY 8f-3, oracle step: RMS norm * weight and silu(gate) * up against the fixture stock ggml's graph wrote:
+    the f32 activations bit for bit, the Q4_1 matmul that consumes them within the tier tolerance."""
+    g = golden("xop_q4_1_m33_n6_k2048.npz")
+    k = g["x"].shape[1]
+    y = oracle.rms_norm_mul(g["x"], g["norm_w"], float(g["eps"]))
+    assert np.array_equal(y.view(np.uint32), g["y_norm"].view(np.uint32))
+    assert np.abs(oracle.mul_mat(3, g["wq"], y) - g["c_norm"]).max() <= tol_c(g["c_norm"], k)
+    y = oracle.silu_mul(g["gate"], g["up"])
+    assert np.array_equal(y.view(np.uint32), g["y_silu"].view(np.uint32))
+    assert np.abs(oracle.mul_mat(3, g["wq"], y) - g["c_silu"]).max() <= tol_c(g["c_silu"], k)
+
+
 def test_threaded_port_matches(oracle):
     g = golden("mulmat_q4_1_m33_n18_k512.npz")
     a = oracle.mul_mat(3, g["wq"], g["x"])

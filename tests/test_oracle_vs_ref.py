@@ -166,3 +166,43 @@ def test_fp32_to_fp16_rne(oracle):
         want = x.astype(np.float16).view(np.uint16)
     got = np.array([oracle.L.orc_fp32_to_fp16(float(v)) for v in x], np.uint16)
     assert np.array_equal(got, want)
+
+
+def test_xops_vs_ggml_graph(oracle, ref):
+    """SURVEY 8f-3, oracle step: llm_build_norm (ggml_rms_norm + ggml_mul) and llm_build_ffn's silu(gate) * up against
+    stock ggml's graph.  The f32 activations must be BIT-identical (same element order in the double sum, the same
+    libm expf behind the SiLU table), and the matmul that consumes them within the tier tolerance."""
+    rng = np.random.default_rng(83)
+    for (m, n, k, t) in [(33, 18, 4096, 3), (7, 1, 256, 6), (19, 5, 11008, Q2_K), (5, 3, 512, 2)]:     # not Q8_0: SURVEY 9-2
+        wq = oracle.quantize_weights(t, rng.standard_normal((m, k)).astype(np.float32), seed=k)
+        x = make_x(rng, n, k) * np.float32(3.0)
+        nw = (1.0 + 0.1 * rng.standard_normal(k)).astype(np.float32)
+        for eps in (1e-5, 1e-6):
+            for w_ in (nw, None):
+                c, y = ref.graph_xop_mul_mat(1, t, wq, x, w_, eps, nth=1)
+                yo = oracle.rms_norm_mul(x, w_, eps)
+                assert np.array_equal(y.view(np.uint32), yo.view(np.uint32))
+                co = oracle.mul_mat(t, wq, yo)
+                plain = [r for r in range(n) if r not in (3, 4)]     # make_x's tie rows: x86 ggml's INIT quantizer (AVX2)
+                assert np.abs(c - co)[plain].max() <= tol_c(co, k)   # rounds halves to even, the path's one away
+        gate = (rng.standard_normal((n, k)) * 4).astype(np.float32)
+        gate[0, :8] = [0.0, -0.0, 1e-8, -1e-8, 70000.0, -70000.0, 20.0, -20.0]      # fp16 zero / subnormal / inf inputs
+        up = rng.standard_normal((n, k)).astype(np.float32)
+        c, y = ref.graph_xop_mul_mat(2, t, wq, gate, up, nth=1)     # nth > 1 drops remainder rows in the reference (SURVEY 9-3)
+        yo = oracle.silu_mul(gate, up)
+        same = (y.view(np.uint32) == yo.view(np.uint32)) | (np.isnan(y) & np.isnan(yo))
+        assert same.all()
+        fin = np.isfinite(yo).all(axis=1)
+        if fin.any():
+            co = oracle.mul_mat(t, wq, yo[fin])
+            assert np.abs(c[fin] - co).max() <= tol_c(co, k)
+
+
+def test_silu_table_all_fp16_patterns(oracle, ref):
+    """Every fp16 input pattern of the SiLU table through the real ggml_silu (one 65 536-element row)."""
+    h = np.arange(65536, dtype=np.uint16).view(np.float16).astype(np.float32).reshape(1, -1)
+    ok = np.isfinite(h[0])
+    wq = oracle.quantize_weights(8, np.zeros((1, 65536), np.float32))
+    _, y = ref.graph_xop_mul_mat(2, 8, wq, np.where(ok, h, 0).astype(np.float32), np.ones_like(h))
+    yo = oracle.silu_mul(np.where(ok, h, 0).astype(np.float32), np.ones_like(h))
+    assert np.array_equal(y.view(np.uint32), yo.view(np.uint32))
