@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "liblammcu.so")
-SOURCES = ["lammcu_api.cu", "lamm_quantize.cu", "lamm_gemv.cu", "lamm_decode.cu", "lamm_gemm.cu", "lamm_gemm_prep.cu", "lamm_gemm_so.cu", "lamm_gemm_x.cu", "lamm_xop.cu", "lamm_host.cpp", "lamm_gguf.cpp"]
+SOURCES = ["lammcu_api.cu", "lamm_quantize.cu", "lamm_gemv.cu", "lamm_decode.cu", "lamm_gemm.cu", "lamm_gemm_prep.cu", "lamm_gemm_so.cu", "lamm_gemm_x.cu", "lamm_gemm_pair.cu", "lamm_xop.cu", "lamm_host.cpp", "lamm_gguf.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default",

@@ -200,6 +200,10 @@ struct GemmPeers {
 void gemm_set_peers(const GemmPeers *peers);     // thread-local; consumed by the next scaled-operand / direct GEMM launch
 bool gemm_peers_used();
 const GemmPeers *gemm_peers_take();                // the pending peer set (marks it used), or NULL
+// CTA-pair (cta_group::2) kernels, lamm_gemm_pair.cu
+bool gemm_f16_pair_supported(int64_t M, int64_t N, int64_t K);
+int launch_gemm_f16_pair(const void *w, int64_t w_stride, const void *xq, int64_t xq_stride, float *c, int64_t ldc,
+                         int64_t M, int64_t N, int64_t K, cudaStream_t st);
 size_t gemm_so_ws_bytes(int64_t M, int64_t N, int64_t K);
 int launch_wrow_scale(int w_type, const void *w, int64_t w_stride, float *rowscale, int64_t M, int64_t Mpad, int64_t K,
                       cudaStream_t st);

@@ -427,8 +427,10 @@ int launch_gemm(int w_type, const void *w, int64_t w_stride, const void *xq, int
     if (!ws) return LAMMCU_ERR_NOMEM;
     return launch_gemm_x(w_type, w, w_stride, xq, xq_stride, c, ldc, M, N, K, ws, st);
   }
-  if (w_type == LAMMCU_TYPE_F16 && gemm_f16_supported(w, w_stride, xq, xq_stride, M, N, K))
+  if (w_type == LAMMCU_TYPE_F16 && gemm_f16_supported(w, w_stride, xq, xq_stride, M, N, K)) {
+    if (gemm_f16_pair_supported(M, N, K)) return launch_gemm_f16_pair(w, w_stride, xq, xq_stride, c, ldc, M, N, K, st);
     return launch_gemm_f16(w, w_stride, xq, xq_stride, c, ldc, M, N, K, st);
+  }
   if (gemm_tc_supported(w_type, w, w_stride, M, N, K)) {
     if (!g_gemm_exact) {
       void *ws = gemm_workspace(gemm_so_ws_bytes(M, N, K));

@@ -34,8 +34,12 @@
 
 namespace lamm {
 
-constexpr int kSoAStages = 2;                  // unpacked weight tiles (hi + lo)
-constexpr int kSoBStages = 3;                  // activation tiles (hi + lo)
+// ring depths: unpacked weight tiles (hi + lo) / activation tiles (hi + lo).  Single CTA: 2 / 3.  CTA pair: 3 / 2 by
+// default -- a stage lasts twice as long there (12 M256 x N256 MMAs = 1536 tensor cycles), so two B stages cover the
+// TMA latency, while a third A stage takes the unpack warps of BOTH CTAs (16 arrivals per stage, the slowest decides)
+// off the MMA's critical path
+constexpr double kSoPairGain = 1.15;           // per-tile speed of the pair form over the single form (profiles/r2u)
+template <bool PAIR> struct SoRing { static constexpr int A = PAIR ? 3 : 2, B = PAIR ? 2 : 3; };
 constexpr int kSoThreads = 512;
 constexpr int kTileBytes = GM * GK * 2;        // 16 KB: one 128 x 64 fp16 operand tile
 
@@ -86,7 +90,7 @@ __device__ __forceinline__ void store_out(const SoParams &p, int64_t idx, float 
   }
 }
 
-template <int WT> struct SoSmem {
+template <int WT, int kSoAStages, int kSoBStages> struct SoSmem {
   static constexpr int BS = type_info(WT).size;
   static constexpr int kRawRowBytes = 8 * BS;                       // 8 blocks = 256 K elements = 4 stages
   static constexpr int kRawBytes = GM * kRawRowBytes;
@@ -159,24 +163,35 @@ __device__ __forceinline__ uint4 chunk_mins(const uint32_t (&raw)[NWR], float S)
                     *reinterpret_cast<const uint32_t *>(&c), *reinterpret_cast<const uint32_t *>(&d));
 }
 
-template <int WT, bool PEERS>
+// PAIR: the CTA-pair form (cta_group::2, launched as clusters of 2; see lamm_gemm_pair.cu for the protocol): each CTA
+// still unpacks its own 128 weight rows and loads 128 activation rows, but the pair's leader issues ONE M256 x N256
+// MMA stream over both, so per unit of work an SM reads half the shared memory and pulls half the activation bytes
+// from L2 (the 128 x 128 form is bound by exactly those two: 125 B/clk of MMA operand reads + 42 B/clk of B tiles).
+template <int WT, bool PEERS, bool PAIR>
 __global__ void __launch_bounds__(kSoThreads, 1)
 gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_xh,
                const __grid_constant__ CUtensorMap tm_xl, const __grid_constant__ CUtensorMap tm_sh, const SoParams p) {
-  using L = SoSmem<WT>;
+  constexpr int kSoAStages = SoRing<PAIR>::A, kSoBStages = SoRing<PAIR>::B;
+  using L = SoSmem<WT, kSoAStages, kSoBStages>;
   constexpr bool kMin = L::kMin;
   constexpr int NWR = 2 * L::BS;                                    // raw words per row chunk
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + L::kBarOff);
-  uint64_t *full_a = bars, *empty_a = bars + 2, *full_b = bars + 4, *empty_b = bars + 7, *raw_full = bars + 10,
-           *raw_empty = bars + 11, *acc_full = bars + 12, *ext_full = bars + 13, *ext_empty = bars + 14;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16);
+  uint64_t *full_a = bars, *empty_a = bars + 3, *full_b = bars + 6, *empty_b = bars + 9, *raw_full = bars + 12,
+           *raw_empty = bars + 13, *acc_full = bars + 14, *ext_full = bars + 15, *ext_empty = bars + 16;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 18);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_tiles = (p.N + GN - 1) / GN;
-  const int m0 = (blockIdx.x / n_tiles) * GM, n0 = (blockIdx.x % n_tiles) * GN;
+  constexpr int TN = PAIR ? 256 : GN;                                // accumulator columns per CTA
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+  const int tile = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int n_tiles = (p.N + TN - 1) / TN;
+  const int m0 = (tile / n_tiles) * (PAIR ? 256 : GM) + (int)rank * GM;   // this CTA's weight rows = accumulator rows
+  const int n0 = (tile % n_tiles) * TN;                                   // first accumulator column (activation row)
+  const int nb = n0 + (int)rank * GN;                                     // the activation rows THIS CTA loads
   const int n_stages = p.K / GK, n_chunks = n_stages / 4;
+  const bool leader = (rank == 0u);
 
   // Q4_1 / Q5_1: an extra stage (m_w tile x s_x tile) is folded in before main stage 4c for every raw
   // chunk c that completes a group of 64 blocks (c % 8 == 7) or is the last one.  The m_w tile is
@@ -189,7 +204,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kSoAStages; i++) {
-      mbar_init(&full_a[i], 8);                        // one arrival per unpack warp
+      mbar_init(&full_a[i], PAIR ? 16 : 8);            // one arrival per unpack warp (PAIR: of both CTAs, on the leader's)
       mbar_init(&empty_a[i], 1);                       // MMA commit
     }
     for (int i = 0; i < kSoBStages; i++) {
@@ -199,7 +214,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
     mbar_init(raw_full, 1);
     mbar_init(raw_empty, 8);
     mbar_init(acc_full, 1);
-    mbar_init(ext_full, 4);                            // the four unpack warps that own m_w (j == 0)
+    mbar_init(ext_full, PAIR ? 8 : 4);                 // the four unpack warps that own m_w (j == 0) (PAIR: of both CTAs)
     mbar_init(ext_empty, 1);
     fence_barrier_init();
     prefetch_tmap(&tm_w);
@@ -215,11 +230,38 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
       asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(e0 + 16u * i), "r"(0u) : "memory");
     fence_proxy_async();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, 128);
+  if constexpr (PAIR) {
+    __syncthreads();
+    cluster_sync_all();                                // both CTAs' barriers exist before anything remote arrives
+    if (warp == 2) tmem_alloc_pair(tmem_slot, 256);
+  } else {
+    if (warp == 2) tmem_alloc(tmem_slot, 128);
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // PAIR: "full" barriers live in the leader; arrivals / TMA completions of the peer go there through mapa
+  auto load_b = [&](void *dst, const CUtensorMap *map, int x, int y, uint64_t *bar) {
+    if constexpr (PAIR) tma_load_2d_pair(dst, map, x, y, mapa_rank(smem_u32(bar), 0u));
+    else tma_load_2d(dst, map, x, y, bar);
+  };
+  auto arrive_full = [&](uint64_t *bar) {
+    if constexpr (PAIR) {
+      if (leader) mbar_arrive(bar);
+      else mbar_arrive_cluster(mapa_rank(smem_u32(bar), 0u));
+    } else {
+      mbar_arrive(bar);
+    }
+  };
+  auto commit = [&](uint64_t *bar) {
+    if constexpr (PAIR) umma_commit_pair(bar);
+    else umma_commit(bar);
+  };
+  auto mma = [&](uint64_t a, uint64_t b, uint32_t acc) {
+    if constexpr (PAIR) umma_f16_pair(tmem_base, a, b, kIdescF16Pair, acc);
+    else umma_f16(tmem_base, a, b, kIdescF16, acc);
+  };
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -235,42 +277,44 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
         if (ext_before(st)) {
           const int s = bseq % kSoBStages, e = st >> 5;
           mbar_wait(&empty_b[s], ((uint32_t)(bseq / kSoBStages) & 1u) ^ 1u);
-          mbar_arrive_expect_tx(&full_b[s], (uint32_t)kTileBytes);
-          tma_load_2d(smem + L::kBhOff + s * kTileBytes, &tm_sh, e * 64, n0, &full_b[s]);
+          if (leader) mbar_arrive_expect_tx(&full_b[s], (uint32_t)((PAIR ? 2 : 1) * kTileBytes));
+          load_b(smem + L::kBhOff + s * kTileBytes, &tm_sh, e * 64, nb, &full_b[s]);
           bseq++;
         }
         const int s = bseq % kSoBStages;
         mbar_wait(&empty_b[s], ((uint32_t)(bseq / kSoBStages) & 1u) ^ 1u);
-        mbar_arrive_expect_tx(&full_b[s], (uint32_t)(2 * kTileBytes));
-        tma_load_2d(smem + L::kBhOff + s * kTileBytes, &tm_xh, st * GK, n0, &full_b[s]);
-        tma_load_2d(smem + L::kBlOff + s * kTileBytes, &tm_xl, st * GK, n0, &full_b[s]);
+        if (leader) mbar_arrive_expect_tx(&full_b[s], (uint32_t)((PAIR ? 4 : 2) * kTileBytes));
+        load_b(smem + L::kBhOff + s * kTileBytes, &tm_xh, st * GK, nb, &full_b[s]);
+        load_b(smem + L::kBlOff + s * kTileBytes, &tm_xl, st * GK, nb, &full_b[s]);
         bseq++;
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (PAIR: the leader's, for both CTAs) =====================
+    if (lane == 0 && leader) {
       int bseq = 0;
       uint32_t acc_on = 0u;                            // 0 only for the very first MMA of the tile
       for (int st = 0; st < n_stages; st++) {
         if (ext_before(st)) {
           const int sb = bseq % kSoBStages, e = st >> 5;
-          mbar_wait(ext_full, (uint32_t)e & 1u);
+          if constexpr (PAIR) mbar_wait_cluster(ext_full, (uint32_t)e & 1u);
+          else mbar_wait(ext_full, (uint32_t)e & 1u);
           mbar_wait(&full_b[sb], (uint32_t)(bseq / kSoBStages) & 1u);
           tc_fence_after();
           const uint64_t ah = make_sw128_desc(smem_u32(smem + L::kEhOff));
           const uint64_t bh = make_sw128_desc(smem_u32(smem + L::kBhOff + sb * kTileBytes));
 #pragma unroll
           for (int kk = 0; kk < 4; kk++) {
-            umma_f16(tmem_base, ah + (uint64_t)(kk * 2), bh + (uint64_t)(kk * 2), kIdescF16, acc_on);
+            mma(ah + (uint64_t)(kk * 2), bh + (uint64_t)(kk * 2), acc_on);
             acc_on = 1u;
           }
-          umma_commit(ext_empty);
-          umma_commit(&empty_b[sb]);
+          commit(ext_empty);
+          commit(&empty_b[sb]);
           bseq++;
         }
         const int sa = st % kSoAStages, sb = bseq % kSoBStages;
-        mbar_wait(&full_a[sa], (uint32_t)(st / kSoAStages) & 1u);
+        if constexpr (PAIR) mbar_wait_cluster(&full_a[sa], (uint32_t)(st / kSoAStages) & 1u);
+        else mbar_wait(&full_a[sa], (uint32_t)(st / kSoAStages) & 1u);
         mbar_wait(&full_b[sb], (uint32_t)(bseq / kSoBStages) & 1u);
         tc_fence_after();
         const uint64_t ah = make_sw128_desc(smem_u32(smem + L::kAhOff + sa * kTileBytes));
@@ -281,21 +325,22 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
         for (int kk = 0; kk < 4; kk++) {
           // the K offset inside the 128-byte swizzle atom advances the start address (16-byte units)
           const uint64_t o = (uint64_t)(kk * 2);
-          umma_f16(tmem_base, ah + o, bh + o, kIdescF16, acc_on);
+          mma(ah + o, bh + o, acc_on);
           acc_on = 1u;
-          umma_f16(tmem_base, ah + o, bl + o, kIdescF16, 1u);
-          umma_f16(tmem_base, al + o, bh + o, kIdescF16, 1u);
+          mma(ah + o, bl + o, 1u);
+          mma(al + o, bh + o, 1u);
         }
-        umma_commit(&empty_a[sa]);
-        umma_commit(&empty_b[sb]);
+        commit(&empty_a[sa]);
+        commit(&empty_b[sb]);
         bseq++;
       }
-      umma_commit(acc_full);
+      commit(acc_full);
     }
   } else if (warp >= 4 && warp < 12) {
     // ===================== weight unpack (thread = row x block j of the stage) =====================
     const int r = (threadIdx.x - 128) & 127, j = (warp - 4) >> 2;
-    const float rs = __ldg(p.rowscale + m0 + r);                      // [Mpad]: rows beyond M carry 1
+    const int mpad = (p.M + GM - 1) / GM * GM;                        // rowscale has [Mpad] entries: rows beyond M carry 1
+    const float rs = (m0 + r < mpad) ? __ldg(p.rowscale + m0 + r) : 1.f;   // (PAIR: the peer's tile may lie beyond Mpad)
     for (int ms = 0; ms < n_chunks; ms++) {
       mbar_wait(raw_full, (uint32_t)ms & 1u);
       uint32_t raw[NWR];
@@ -318,7 +363,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
           if ((ms & 7) == 7 || ms == n_chunks - 1) {
             fence_proxy_async();
             __syncwarp();
-            if (lane == 0) mbar_arrive(ext_full);
+            if (lane == 0) arrive_full(ext_full);
           }
         }
       }
@@ -340,18 +385,18 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
         }
         fence_proxy_async();             // generic-proxy stores -> visible to the tensor core
         __syncwarp();
-        if (lane == 0) mbar_arrive(&full_a[s]);
+        if (lane == 0) arrive_full(&full_a[s]);
       }
     }
   } else if (warp >= 12) {
     // ===================== epilogue (thread = TMEM lane = weight row) =====================
     const int q4 = warp & 3, row = q4 * 32 + lane, m = m0 + row;
-    const float rinv = 1.0f / __ldg(p.rowscale + m);                  // exact: a power of two ([Mpad] entries)
+    const float rinv = (m < p.M) ? 1.0f / __ldg(p.rowscale + m) : 1.f;    // exact: a power of two
     mbar_wait(acc_full, 0u);
     tc_fence_after();
     const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16);
 #pragma unroll 2
-    for (int c16 = 0; c16 < 8; c16++) {
+    for (int c16 = 0; c16 < TN / 16; c16++) {
       uint32_t v[16];
       asm volatile(
           "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
@@ -372,7 +417,12 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem_base, 128);
+  if constexpr (PAIR) {
+    cluster_sync_all();                                // the peer's shared memory and TMEM outlive the leader's MMAs
+    if (warp == 2) tmem_dealloc_pair(tmem_base, 256);
+  } else {
+    if (warp == 2) tmem_dealloc(tmem_base, 128);
+  }
 }
 
 // ---- direct variant: both operands pre-split in global memory --------------------------------
@@ -580,25 +630,57 @@ int launch_gemm_f16(const void *w, int64_t w_stride, const void *xq, int64_t xq_
 template <int WT>
 static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CUtensorMap &tm_xl,
                      const CUtensorMap &tm_sh, const SoParams &p, cudaStream_t st) {
-  using L = SoSmem<WT>;
-  constexpr int smem = L::kTotal + 1024;
-  static_assert(smem <= 227 * 1024, "shared memory budget");
+  constexpr int smem = SoSmem<WT, SoRing<false>::A, SoRing<false>::B>::kTotal + 1024;
+  constexpr int smem_pair = SoSmem<WT, SoRing<true>::A, SoRing<true>::B>::kTotal + 1024;
+  static_assert(smem <= 227 * 1024 && smem_pair <= 227 * 1024, "shared memory budget");
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_so_kernel<WT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = cudaFuncSetAttribute(gemm_so_kernel<WT, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(gemm_so_kernel<WT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      e = cudaFuncSetAttribute(gemm_so_kernel<WT, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_so_kernel<WT, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_pair);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_so_kernel<WT, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_pair);
     if (e != cudaSuccess) {
       set_error("gemm_so: cudaFuncSetAttribute(%d): %s", smem, cudaGetErrorString(e));
       return LAMMCU_ERR_CUDA;
     }
     attr_set = true;
   }
-  const int tiles = ((p.M + GM - 1) / GM) * ((p.N + GN - 1) / GN);
-  if (p.n_peer) gemm_so_kernel<WT, true><<<tiles, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);
-  else gemm_so_kernel<WT, false><<<tiles, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);
+  // CTA pairs (256 x 256 per cluster of 2) whenever both dimensions have more than one 128-tile; LAMM_GEMM_PAIR=0: never
+  static const int pair_on = [] { const char *e = getenv("LAMM_GEMM_PAIR"); return e ? atoi(e) : 1; }();
+  cudaError_t e;
+  // no persistent scheduler yet, so the form that needs less time for its waves wins: a pair tile is 4x the work of a
+  // single tile on 2 SMs = 2 single-tile times, divided by the measured per-tile gain of the pair form (LAMM_GEMM_PAIR=2:
+  // always pairs)
+  const int pairs = ((p.M + 255) / 256) * ((p.N + 255) / 256);
+  const int singles = ((p.M + GM - 1) / GM) * ((p.N + GN - 1) / GN);
+  const int sms = sm_count_cached(), slots = sms / 2;
+  const double t_pair = (double)((pairs + slots - 1) / slots) * 2.0 / kSoPairGain;
+  const double t_single = (double)((singles + sms - 1) / sms);
+  if (pair_on && p.M > GM && p.N > GN && (pair_on > 1 || t_pair < t_single)) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pairs);
+    cfg.blockDim = dim3(kSoThreads);
+    cfg.dynamicSmemBytes = smem_pair;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (p.n_peer) e = cudaLaunchKernelEx(&cfg, gemm_so_kernel<WT, true, true>, tm_w, tm_xh, tm_xl, tm_sh, p);
+    else e = cudaLaunchKernelEx(&cfg, gemm_so_kernel<WT, false, true>, tm_w, tm_xh, tm_xl, tm_sh, p);
+  } else {
+    const int tiles = ((p.M + GM - 1) / GM) * ((p.N + GN - 1) / GN);
+    if (p.n_peer) gemm_so_kernel<WT, true, false><<<tiles, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);
+    else gemm_so_kernel<WT, false, false><<<tiles, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);
+    e = cudaGetLastError();
+  }
   g_launch_count++;
-  cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("gemm_so launch (type %d): %s", WT, cudaGetErrorString(e));
     return LAMMCU_ERR_CUDA;
