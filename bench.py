@@ -546,6 +546,12 @@ def run_cuda(args):
     gemm = None
     if world == 1 and rank == 0 and not args.no_gemm:
         gemm = gemm_block(torch, L, dev, args)
+    extras = None
+    if not args.no_extras and t != 0:
+        if world > 1 and comm is None:
+            from lamm_b200 import sharding
+            comm = sharding.Comm(L, dist)
+        extras = scale_extras(torch, L, dist, dev, rank, world, comm if world > 1 else None, args)
     clocks = sampler.stop() if rank == 0 else None
     if rank != 0:
         return finish(dist)
@@ -579,6 +585,7 @@ def run_cuda(args):
                                kern_bytes / max(launches_q, 1) / 1e6)},
         "sustained": sustained, "chain_check": chain_check,
         "gemm": gemm,
+        "multi_gpu_workloads": extras,
         "cpu_baseline": cpu,
         "e2e": e2e,
         "gpu_launches": launches_per_token * args.steps, "logits_rms": logit_rms,
@@ -606,7 +613,7 @@ def gemm_block(torch, L, dev, args):
     gen.manual_seed(99)
     out = {"unit": "TOPS", "int8_peak_tops_measured": INT8_TOPS_MEASURED, "f16_peak_tflops_measured": F16_TOPS_MEASURED,
            "peak_source": "tools/i8peak.cu on this pool (profiles/r2g/i8peak.txt)", "cases": []}
-    for fmt, m, k, n, kind in (("q4_1", 13824, 5120, 2048, "tcgen05 kind::f16, 3 MMAs per product (scaled fp16 hi/lo operands)"),
+    for fmt, m, k, n, kind in (("q4_1", 13824, 5120, 2048, "tcgen05 kind::f16 cta_group::2 (CTA pairs, 256 x 256 tiles), 3 MMAs per product (scaled fp16 hi/lo operands)"),
                                ("q2_k", 11008, 4096, 512, "tcgen05 kind::i8 (scale-folded u8 x s8, exact integer sums)")):
         t = TYPE_IDS[fmt]
         wb = m * w_row_bytes(t, k)
@@ -665,6 +672,113 @@ def gemm_block(torch, L, dev, args):
                 out["cpu_baseline"] = cpu
         except Exception as e:
             out["cpu_baseline"] = [{"kind": "unavailable", "why": str(e)}]
+    return out
+
+
+def scale_extras(torch, L, dist, dev, rank, world, comm, args):
+    """The two multi-GPU workloads BASELINE.json names besides the 7B chain (configs 4 and 5), as extra keys of the line at
+    every N so the driver's 1/2/4/8 run carries them:
+      * LLaMA-30B Q5_0 decode chain (K = 6656, M = 17920 ...), weights row-sharded, fused LL epilogue: tok/s
+      * LLaMA-13B Q4_1 N = 2048 prefill on 13824 x 5120, rows sharded: aggregate TOPS compute-only (each rank's slab
+        into its own buffer) and compute + replicate (the peer-store epilogue leaves the full C on every rank)
+    Device time, CUDA events, barrier on both sides, max over ranks."""
+    out = {}
+
+    def timed(fn, reps):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if dist:
+            tt = torch.tensor([ms], device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dist.barrier()
+            ms = float(tt.item())
+        return ms / reps
+
+    def shard(m):
+        per = (m + world - 1) // world
+        lo = min(m, rank * per)
+        return lo, min(m, lo + per)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(4321)
+    # ---- 30B Q5_0 decode chain ----
+    Hh, Ff, Vv, Ll = MODELS["30b"]
+    t = TYPE_IDS["q5_0"]
+    if all(m % world == 0 for m in (Hh, Ff, Vv)):
+        def W(m, k):
+            lo, hi = shard(m)
+            return synth_weight(torch, t, hi - lo, k, gen, dev)
+        layers = [dict(qkv=[W(Hh, Hh) for _ in range(3)], wo=W(Hh, Hh), gu=[W(Ff, Hh) for _ in range(2)], down=W(Hh, Ff))
+                  for _ in range(Ll)]
+        head = W(Vv, Hh)
+        mk = comm.vector if comm is not None else (lambda m: torch.zeros((1, m), device=dev))
+        b = {k_: mk(m) for k_, m in (("x0", Hh), ("x1", Hh), ("q", Hh), ("k", Hh), ("v", Hh), ("o", Hh), ("g", Ff), ("u", Ff), ("logits", Vv))}
+        x_in = torch.randn((1, Hh), generator=gen, device=dev)
+
+        def mm(ws, xin, outs, ms, k):
+            if comm is not None:
+                if len(ws) == 1:
+                    comm.mul_mat(t, ws[0], xin, outs[0], ms[0], k)
+                else:
+                    comm.mul_mat_batch(t, ws, xin, outs, ms, k)
+            elif len(ws) == 1:
+                L.mul_mat(t, ws[0], xin, out=outs[0])
+            else:
+                L.mul_mat_batch(t, ws, xin, outs)
+
+        def token():
+            for li, ly in enumerate(layers):
+                xin = x_in if li == 0 else b["x%d" % (li % 2)]
+                mm(ly["qkv"], xin, [b["q"], b["k"], b["v"]], [Hh] * 3, Hh)
+                mm([ly["wo"]], b["v"], [b["o"]], [Hh], Hh)
+                mm(ly["gu"], b["o"], [b["g"], b["u"]], [Ff] * 2, Hh)
+                mm([ly["down"]], b["u"], [b["x%d" % ((li + 1) % 2)]], [Hh], Ff)
+            mm([head], b["x%d" % (Ll % 2)], [b["logits"]], [Vv], Hh)
+        s_ = torch.cuda.Stream()
+        s_.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s_):
+            token()
+            token()
+        torch.cuda.current_stream().wait_stream(s_)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            token()
+        ms = timed(g.replay, 20)
+        logits = comm.unpack(torch, b["logits"]) if comm is not None else b["logits"].view(-1)
+        torch.cuda.synchronize()
+        ok = bool(torch.isfinite(logits).all().item()) and not (comm is not None and comm.timed_out())
+        wbytes = sum(w_row_bytes(t, k) * m for m, k in [(Hh, Hh)] * 4 + [(Ff, Hh)] * 2 + [(Hh, Ff)]) * Ll + w_row_bytes(t, Hh) * Vv
+        out["llama30b_q5_0_decode_chain"] = {"value": 1e3 / ms if ok else None, "unit": "tok/s", "ms_per_token": ms,
+                                              "weight_gb_total": wbytes / 1e9, "aggregate_gbs": wbytes / ms / 1e6,
+                                              "sharding": "rows / %d, LL peer-store epilogue" % world if world > 1 else "one GPU"}
+        del layers, head, g
+        torch.cuda.empty_cache()
+    # ---- 13B Q4_1 N = 2048 prefill, rows sharded ----
+    t = TYPE_IDS["q4_1"]
+    m, k, n = 13824, 5120, 2048
+    if m % world == 0:
+        lo, hi = shard(m)
+        w = synth_weight(torch, t, hi - lo, k, gen, dev)
+        x = torch.randn((n, k), generator=gen, device=dev)
+        c_local = torch.zeros((n, hi - lo), device=dev)
+        ms_c = timed(lambda: L.mul_mat(t, w, x, out=c_local), 10)
+        rec = {"M": m, "K": k, "N": n, "rows_per_gpu": hi - lo, "compute_only_tops": 2.0 * m * n * k / ms_c / 1e9, "compute_only_us": ms_c * 1e3}
+        if comm is not None:
+            cbuf = comm.result_buffer(n, m)
+            ms_r = timed(lambda: comm.mul_mat_gemm(t, w, x, cbuf, m, n, k), 10)
+            rec.update(compute_and_replicate_tops=2.0 * m * n * k / ms_r / 1e9, compute_and_replicate_us=ms_r * 1e3,
+                       replicated_mb_per_gpu=n * m * 4 / 1e6)
+        out["llama13b_q4_1_n2048_prefill_row_sharded"] = rec
     return out
 
 
@@ -937,6 +1051,7 @@ def main():
     ap.add_argument("--model", default="7b", choices=sorted(MODELS), help="chain shapes (the metric is quoted on 7b)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-gemm", action="store_true", help="skip the prefill GEMM block of the line")
+    ap.add_argument("--no-extras", action="store_true", help="skip the 30B Q5_0 chain / 13B sharded prefill keys")
     ap.add_argument("--sustain-s", type=float, default=2.0, help="seconds of back-to-back replay for the sustained value (0: skip)")
     ap.add_argument("--no-e2e", action="store_true",
                     help="skip the e2e leg (profiler runs only: ncu replays kernels, the resident server talks to the host)")

@@ -16,7 +16,7 @@ import os
 from . import build as _build
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "liblammcu.so")
+LIB_PATH = os.environ.get("LAMM_LIB") or os.path.join(HERE, "liblammcu.so")     # LAMM_LIB: a variant build (kernel experiments)
 
 # ggml type ids (llama.cpp-b2430/ggml.h:341-369)
 F32, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0, Q8_1, Q2_K, Q8_K = 0, 2, 3, 6, 7, 8, 9, 10, 15

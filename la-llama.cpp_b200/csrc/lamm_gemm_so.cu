@@ -34,12 +34,18 @@
 
 namespace lamm {
 
-// ring depths: unpacked weight tiles (hi + lo) / activation tiles (hi + lo).  Single CTA: 2 / 3.  CTA pair: 3 / 2 by
-// default -- a stage lasts twice as long there (12 M256 x N256 MMAs = 1536 tensor cycles), so two B stages cover the
-// TMA latency, while a third A stage takes the unpack warps of BOTH CTAs (16 arrivals per stage, the slowest decides)
-// off the MMA's critical path
-constexpr double kSoPairGain = 1.15;           // per-tile speed of the pair form over the single form (profiles/r2u)
-template <bool PAIR> struct SoRing { static constexpr int A = PAIR ? 3 : 2, B = PAIR ? 2 : 3; };
+// ring depths: unpacked weight tiles (hi + lo) / activation tiles (hi + lo): 2 / 3 in both forms.  Measured on the pair
+// form at 13B Q4_1 N = 2048 (profiles/r2y): 2 / 3 490 TOPS, 3 / 2 465, 3 / 3 (fits Q4_0 only) 496 vs 498 -- the third B
+// stage (TMA latency) matters, a third A stage does not; two unpack groups of 8 warps on alternate stages (768
+// threads) were slower, 450 (profiles/r2x).  Barrier slots below assume <= 3 stages of either kind.
+constexpr double kSoPairGain = 1.25;           // per-tile speed of the pair form over the single form (profiles/r2y)
+#ifndef LAMM_SO_PAIR_NA
+#define LAMM_SO_PAIR_NA 2
+#endif
+#ifndef LAMM_SO_PAIR_NB
+#define LAMM_SO_PAIR_NB 3
+#endif
+template <bool PAIR> struct SoRing { static constexpr int A = PAIR ? LAMM_SO_PAIR_NA : 2, B = PAIR ? LAMM_SO_PAIR_NB : 3; };
 constexpr int kSoThreads = 512;
 constexpr int kTileBytes = GM * GK * 2;        // 16 KB: one 128 x 64 fp16 operand tile
 
@@ -632,15 +638,16 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
                      const CUtensorMap &tm_sh, const SoParams &p, cudaStream_t st) {
   constexpr int smem = SoSmem<WT, SoRing<false>::A, SoRing<false>::B>::kTotal + 1024;
   constexpr int smem_pair = SoSmem<WT, SoRing<true>::A, SoRing<true>::B>::kTotal + 1024;
-  static_assert(smem <= 227 * 1024 && smem_pair <= 227 * 1024, "shared memory budget");
+  static_assert(smem <= 227 * 1024, "shared memory budget");
+  constexpr bool pair_fits = smem_pair <= 227 * 1024;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(gemm_so_kernel<WT, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(gemm_so_kernel<WT, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e == cudaSuccess)
+    if (e == cudaSuccess && pair_fits)
       e = cudaFuncSetAttribute(gemm_so_kernel<WT, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_pair);
-    if (e == cudaSuccess)
+    if (e == cudaSuccess && pair_fits)
       e = cudaFuncSetAttribute(gemm_so_kernel<WT, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_pair);
     if (e != cudaSuccess) {
       set_error("gemm_so: cudaFuncSetAttribute(%d): %s", smem, cudaGetErrorString(e));
@@ -659,7 +666,7 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
   const int sms = sm_count_cached(), slots = sms / 2;
   const double t_pair = (double)((pairs + slots - 1) / slots) * 2.0 / kSoPairGain;
   const double t_single = (double)((singles + sms - 1) / sms);
-  if (pair_on && p.M > GM && p.N > GN && (pair_on > 1 || t_pair < t_single)) {
+  if (pair_fits && pair_on && p.M > GM && p.N > GN && (pair_on > 1 || t_pair < t_single)) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * pairs);
     cfg.blockDim = dim3(kSoThreads);
