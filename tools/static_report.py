@@ -1,9 +1,9 @@
 #!/usr/bin/env python
-"""Static evidence from the built library, no GPU needed:  python tools/static_report.py > profiles/r1_static_sass.md
+"""Static evidence from the built library, no GPU needed:  python tools/static_report.py > profiles/r2_static_sass.md
 
 Per kernel of la-llama.cpp_b200/liblammcu.so: registers / stack / shared memory (cuobjdump
 --dump-resource-usage) and how often the SASS mnemonics that prove the Blackwell paths occur
-(/opt/skills/guides/B200_PROFILING.md: tcgen05.mma -> UTC*MMA, tcgen05.ld/st -> LDTM/STTM,
+(/opt/skills/guides/B200_PROFILING.md: tcgen05.mma -> UTC*MMA (kind::f16 UTCHMMA, kind::i8 UTCIMMA; cta_group::2 -> .2CTA), tcgen05.ld/st -> LDTM/STTM,
 TMA -> UTMALDG / UTMASTG / UBLKCP; dp4a -> IDP.4A; mbarrier -> SYNCS; griddepcontrol -> ACQBULK /
 PREEXIT family).  Template instantiations are grouped by kernel name with min..max over the group."""
 import os
@@ -14,7 +14,7 @@ from collections import OrderedDict, defaultdict
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "la-llama.cpp_b200", "liblammcu.so")
-MNEMONICS = ["UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "UBLKPF", "IDP.4A", "IDP.2A",
+MNEMONICS = ["UTCHMMA", "UTCIMMA", ".2CTA", "UTCQMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "UBLKPF", "IDP.4A", "IDP.2A",
              "SYNCS", "ACQBULK", "PREEXIT", "HMMA", "IMMA", "STL", "LDL"]
 
 
@@ -54,7 +54,7 @@ def main():
             op = m.group(1)
             ninstr[cur] += 1
             for k in MNEMONICS:
-                if op == k or op.startswith(k + "."):
+                if op == k or op.startswith(k + ".") or (k.startswith(".") and k in op):
                     counts[cur][k] += 1
     names = demangle(sorted(usage))
     groups = OrderedDict()
@@ -77,7 +77,7 @@ def main():
         row += [rng([counts[f][k] for f in fns]) for k in used]
         print("| " + " | ".join(row) + " |")
     print("\nReading: `UBLKCP` = 1-D TMA bulk copies (decode / GEMV weight rings), `UTMALDG` = tensor-map TMA loads (GEMM")
-    print("operands), `UTCHMMA` = `tcgen05.mma.kind::f16`, `LDTM` = `tcgen05.ld` (TMEM → registers in the epilogues / drain),")
+    print("operands), `UTCHMMA` = `tcgen05.mma.kind::f16`, `UTCIMMA` = `tcgen05.mma.kind::i8` (the Q2_K GEMM), `.2CTA` = instructions of the `cta_group::2` pair form (MMA, TMA load, commit multicast, TMEM allocation), `LDTM` = `tcgen05.ld` (TMEM → registers in the epilogues / drain),")
     print("`IDP.4A` / `IDP.2A` = dp4a / dp2a of the decode and GEMV dot products, `SYNCS` = mbarrier operations,")
     print("`STL`/`LDL` = local-memory (spill) traffic.")
     return 0
