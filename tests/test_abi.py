@@ -135,6 +135,8 @@ def test_every_environment_variable_is_documented():
     for f in os.listdir(csrc):
         with open(os.path.join(csrc, f)) as fh:
             read |= set(re.findall(r'getenv\("(LAMM_[A-Z0-9_]+)"\)', fh.read()))
+    with open(os.path.join(root, "la-llama.cpp_b200", "__init__.py")) as fh:      # the ctypes binding reads LAMM_LIB
+        read |= set(re.findall(r'os\.environ\.get\("(LAMM_[A-Z0-9_]+)"\)', fh.read()))
     with open(os.path.join(root, "INTEGRATION.md")) as fh:
         doc = fh.read()
     table = set(re.findall(r"^\| `(LAMM_[A-Z0-9_]+)` \|", doc, flags=re.M))
