@@ -19,7 +19,10 @@
 //   m_w of 64 consecutive blocks in an extra A tile (fp16, exact), lamm_gemm_prep.cu lays the s_x out
 //   the same way (fp16, exact), and the MMA issuer folds the pair in as one extra stage per 64 blocks.
 //
-// One CTA = 128 weight rows x 128 activation rows, 16 warps:
+// PERSISTENT (round 2): a CTA (or CTA pair, below) walks tiles cl, cl + ncl, ... -- the rings and barrier phases run on
+// across tiles and the accumulator is double-buffered in TMEM, so tile i's epilogue and tile i + 1's prologue hide
+// behind the mainloops (13B Q4_1 N = 2048: 490 -> 519 TOPS, profiles/r2an).
+// One CTA = 128 weight rows x 128 activation rows per tile, 16 warps:
 //   warp 0      TMA producer: raw packed weight blocks (2-D box over bytes, 8 blocks per row), the two
 //               fp16 activation tiles (SWIZZLE_128B), the s_x tiles of the extra stages
 //   warp 1      MMA issuer (one thread): per 64-K stage 4 x 3 tcgen05.mma M128 N128 K16 into ONE
@@ -38,7 +41,7 @@ namespace lamm {
 // form at 13B Q4_1 N = 2048 (profiles/r2y): 2 / 3 490 TOPS, 3 / 2 465, 3 / 3 (fits Q4_0 only) 496 vs 498 -- the third B
 // stage (TMA latency) matters, a third A stage does not; two unpack groups of 8 warps on alternate stages (768
 // threads) were slower, 450 (profiles/r2x).  Barrier slots below assume <= 3 stages of either kind.
-constexpr double kSoPairGain = 1.25;           // per-tile speed of the pair form over the single form (profiles/r2y)
+constexpr double kSoPairGain = 1.4;            // per-tile speed of the pair form over the single form (519 vs 373 TOPS, profiles/r2an)
 #ifndef LAMM_SO_PAIR_NA
 #define LAMM_SO_PAIR_NA 2
 #endif
@@ -185,19 +188,24 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
   uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + L::kBarOff);
   uint64_t *full_a = bars, *empty_a = bars + 3, *full_b = bars + 6, *empty_b = bars + 9, *raw_full = bars + 12,
-           *raw_empty = bars + 13, *acc_full = bars + 14, *ext_full = bars + 15, *ext_empty = bars + 16;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 18);
+           *raw_empty = bars + 13, *acc_full = bars + 14, *acc_empty = bars + 16, *ext_full = bars + 18, *ext_empty = bars + 19;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 20);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int TN = PAIR ? 256 : GN;                                // accumulator columns per CTA
+  constexpr int TM = PAIR ? 256 : GM;                                // weight rows per tile (pair: 128 per CTA)
   const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
-  const int tile = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
-  const int n_tiles = (p.N + TN - 1) / TN;
-  const int m0 = (tile / n_tiles) * (PAIR ? 256 : GM) + (int)rank * GM;   // this CTA's weight rows = accumulator rows
-  const int n0 = (tile % n_tiles) * TN;                                   // first accumulator column (activation row)
-  const int nb = n0 + (int)rank * GN;                                     // the activation rows THIS CTA loads
-  const int n_stages = p.K / GK, n_chunks = n_stages / 4;
   const bool leader = (rank == 0u);
+  const int n_stages = p.K / GK, n_chunks = n_stages / 4;
+  // PERSISTENT: a CTA (pair) walks tiles cl, cl + ncl, ...; rings and barrier phases run on across tiles (global
+  // counters), and the accumulator is double-buffered in TMEM (2 x TN columns), so the epilogue of tile i and the
+  // prologue of tile i + 1 hide behind the mainloops instead of adding ~10 % per tile.
+  const int tiles_n = (p.N + TN - 1) / TN, n_tiles = ((p.M + TM - 1) / TM) * tiles_n;
+  const int cl = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, ncl = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int n_ext = kMin ? (n_chunks + 7) / 8 : 0;                   // extra (m_w x s_x) stages per tile
+  // tile t: m0 = this CTA's weight rows = accumulator rows; n0 = first accumulator column; nb = activation rows it loads
+  auto tile_m0 = [&](int tl) { return (tl / tiles_n) * TM + (int)rank * GM; };
+  auto tile_n0 = [&](int tl) { return (tl % tiles_n) * TN; };
 
   // Q4_1 / Q5_1: an extra stage (m_w tile x s_x tile) is folded in before main stage 4c for every raw
   // chunk c that completes a group of 64 blocks (c % 8 == 7) or is the last one.  The m_w tile is
@@ -219,7 +227,10 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
     }
     mbar_init(raw_full, 1);
     mbar_init(raw_empty, 8);
-    mbar_init(acc_full, 1);
+    for (int i = 0; i < 2; i++) {
+      mbar_init(&acc_full[i], 1);                      // MMA commit: accumulator i holds a finished tile
+      mbar_init(&acc_empty[i], PAIR ? 8 : 4);          // the epilogue warps (of both CTAs) have drained it
+    }
     mbar_init(ext_full, PAIR ? 8 : 4);                 // the four unpack warps that own m_w (j == 0) (PAIR: of both CTAs)
     mbar_init(ext_empty, 1);
     fence_barrier_init();
@@ -239,9 +250,9 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
   if constexpr (PAIR) {
     __syncthreads();
     cluster_sync_all();                                // both CTAs' barriers exist before anything remote arrives
-    if (warp == 2) tmem_alloc_pair(tmem_slot, 256);
+    if (warp == 2) tmem_alloc_pair(tmem_slot, 2 * TN);
   } else {
-    if (warp == 2) tmem_alloc(tmem_slot, 128);
+    if (warp == 2) tmem_alloc(tmem_slot, 2 * TN);
   }
   tc_fence_before();
   __syncthreads();
@@ -264,170 +275,199 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
     if constexpr (PAIR) umma_commit_pair(bar);
     else umma_commit(bar);
   };
-  auto mma = [&](uint64_t a, uint64_t b, uint32_t acc) {
-    if constexpr (PAIR) umma_f16_pair(tmem_base, a, b, kIdescF16Pair, acc);
-    else umma_f16(tmem_base, a, b, kIdescF16, acc);
-  };
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      int bseq = 0;                                    // B-ring sequence number (main + extra stages)
-      for (int st = 0; st < n_stages; st++) {
-        if ((st & 3) == 0) {
-          const int ms = st >> 2;
-          mbar_wait(raw_empty, ((uint32_t)ms & 1u) ^ 1u);
-          mbar_arrive_expect_tx(raw_full, (uint32_t)L::kRawBytes);
-          tma_load_2d(smem + L::kRawOff, &tm_w, ms * (L::kRawRowBytes / 2), m0, raw_full);
-        }
-        if (ext_before(st)) {
-          const int s = bseq % kSoBStages, e = st >> 5;
+      int bseq = 0;                                    // B-ring sequence number (main + extra stages), over all tiles
+      int gchunk = 0;                                  // raw chunks loaded so far
+      for (int tl = cl; tl < n_tiles; tl += ncl) {
+        const int m0 = tile_m0(tl), nb = tile_n0(tl) + (int)rank * GN;
+        for (int st = 0; st < n_stages; st++) {
+          if ((st & 3) == 0) {
+            const int ms = st >> 2;
+            mbar_wait(raw_empty, ((uint32_t)gchunk & 1u) ^ 1u);
+            mbar_arrive_expect_tx(raw_full, (uint32_t)L::kRawBytes);
+            tma_load_2d(smem + L::kRawOff, &tm_w, ms * (L::kRawRowBytes / 2), m0, raw_full);
+            gchunk++;
+          }
+          if (ext_before(st)) {
+            const int s = bseq % kSoBStages, e = st >> 5;
+            mbar_wait(&empty_b[s], ((uint32_t)(bseq / kSoBStages) & 1u) ^ 1u);
+            if (leader) mbar_arrive_expect_tx(&full_b[s], (uint32_t)((PAIR ? 2 : 1) * kTileBytes));
+            load_b(smem + L::kBhOff + s * kTileBytes, &tm_sh, e * 64, nb, &full_b[s]);
+            bseq++;
+          }
+          const int s = bseq % kSoBStages;
           mbar_wait(&empty_b[s], ((uint32_t)(bseq / kSoBStages) & 1u) ^ 1u);
-          if (leader) mbar_arrive_expect_tx(&full_b[s], (uint32_t)((PAIR ? 2 : 1) * kTileBytes));
-          load_b(smem + L::kBhOff + s * kTileBytes, &tm_sh, e * 64, nb, &full_b[s]);
+          if (leader) mbar_arrive_expect_tx(&full_b[s], (uint32_t)((PAIR ? 4 : 2) * kTileBytes));
+          load_b(smem + L::kBhOff + s * kTileBytes, &tm_xh, st * GK, nb, &full_b[s]);
+          load_b(smem + L::kBlOff + s * kTileBytes, &tm_xl, st * GK, nb, &full_b[s]);
           bseq++;
         }
-        const int s = bseq % kSoBStages;
-        mbar_wait(&empty_b[s], ((uint32_t)(bseq / kSoBStages) & 1u) ^ 1u);
-        if (leader) mbar_arrive_expect_tx(&full_b[s], (uint32_t)((PAIR ? 4 : 2) * kTileBytes));
-        load_b(smem + L::kBhOff + s * kTileBytes, &tm_xh, st * GK, nb, &full_b[s]);
-        load_b(smem + L::kBlOff + s * kTileBytes, &tm_xl, st * GK, nb, &full_b[s]);
-        bseq++;
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (PAIR: the leader's, for both CTAs) =====================
     if (lane == 0 && leader) {
-      int bseq = 0;
-      uint32_t acc_on = 0u;                            // 0 only for the very first MMA of the tile
-      for (int st = 0; st < n_stages; st++) {
-        if (ext_before(st)) {
-          const int sb = bseq % kSoBStages, e = st >> 5;
-          if constexpr (PAIR) mbar_wait_cluster(ext_full, (uint32_t)e & 1u);
-          else mbar_wait(ext_full, (uint32_t)e & 1u);
+      int bseq = 0, gst = 0, gext = 0, it = 0;         // B stages, A stages, extra stages, tiles so far
+      for (int tl = cl; tl < n_tiles; tl += ncl, it++) {
+        const int ab = it & 1;                         // accumulator buffer of this tile
+        if constexpr (PAIR) mbar_wait_cluster(&acc_empty[ab], ((uint32_t)(it >> 1) & 1u) ^ 1u);
+        else mbar_wait(&acc_empty[ab], ((uint32_t)(it >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + (uint32_t)(ab * TN);
+        auto mma = [&](uint64_t a, uint64_t b, uint32_t acc) {
+          if constexpr (PAIR) umma_f16_pair(tacc, a, b, kIdescF16Pair, acc);
+          else umma_f16(tacc, a, b, kIdescF16, acc);
+        };
+        uint32_t acc_on = 0u;                          // 0 only for the very first MMA of the tile
+        for (int st = 0; st < n_stages; st++) {
+          if (ext_before(st)) {
+            const int sb = bseq % kSoBStages;
+            if constexpr (PAIR) mbar_wait_cluster(ext_full, (uint32_t)gext & 1u);
+            else mbar_wait(ext_full, (uint32_t)gext & 1u);
+            mbar_wait(&full_b[sb], (uint32_t)(bseq / kSoBStages) & 1u);
+            tc_fence_after();
+            const uint64_t ah = make_sw128_desc(smem_u32(smem + L::kEhOff));
+            const uint64_t bh = make_sw128_desc(smem_u32(smem + L::kBhOff + sb * kTileBytes));
+#pragma unroll
+            for (int kk = 0; kk < 4; kk++) {
+              mma(ah + (uint64_t)(kk * 2), bh + (uint64_t)(kk * 2), acc_on);
+              acc_on = 1u;
+            }
+            commit(ext_empty);
+            commit(&empty_b[sb]);
+            bseq++;
+            gext++;
+          }
+          const int sa = gst % kSoAStages, sb = bseq % kSoBStages;
+          if constexpr (PAIR) mbar_wait_cluster(&full_a[sa], (uint32_t)(gst / kSoAStages) & 1u);
+          else mbar_wait(&full_a[sa], (uint32_t)(gst / kSoAStages) & 1u);
           mbar_wait(&full_b[sb], (uint32_t)(bseq / kSoBStages) & 1u);
           tc_fence_after();
-          const uint64_t ah = make_sw128_desc(smem_u32(smem + L::kEhOff));
+          const uint64_t ah = make_sw128_desc(smem_u32(smem + L::kAhOff + sa * kTileBytes));
+          const uint64_t al = make_sw128_desc(smem_u32(smem + L::kAlOff + sa * kTileBytes));
           const uint64_t bh = make_sw128_desc(smem_u32(smem + L::kBhOff + sb * kTileBytes));
+          const uint64_t bl = make_sw128_desc(smem_u32(smem + L::kBlOff + sb * kTileBytes));
 #pragma unroll
           for (int kk = 0; kk < 4; kk++) {
-            mma(ah + (uint64_t)(kk * 2), bh + (uint64_t)(kk * 2), acc_on);
+            // the K offset inside the 128-byte swizzle atom advances the start address (16-byte units)
+            const uint64_t o = (uint64_t)(kk * 2);
+            mma(ah + o, bh + o, acc_on);
             acc_on = 1u;
+            mma(ah + o, bl + o, 1u);
+            mma(al + o, bh + o, 1u);
           }
-          commit(ext_empty);
+          commit(&empty_a[sa]);
           commit(&empty_b[sb]);
           bseq++;
+          gst++;
         }
-        const int sa = st % kSoAStages, sb = bseq % kSoBStages;
-        if constexpr (PAIR) mbar_wait_cluster(&full_a[sa], (uint32_t)(st / kSoAStages) & 1u);
-        else mbar_wait(&full_a[sa], (uint32_t)(st / kSoAStages) & 1u);
-        mbar_wait(&full_b[sb], (uint32_t)(bseq / kSoBStages) & 1u);
-        tc_fence_after();
-        const uint64_t ah = make_sw128_desc(smem_u32(smem + L::kAhOff + sa * kTileBytes));
-        const uint64_t al = make_sw128_desc(smem_u32(smem + L::kAlOff + sa * kTileBytes));
-        const uint64_t bh = make_sw128_desc(smem_u32(smem + L::kBhOff + sb * kTileBytes));
-        const uint64_t bl = make_sw128_desc(smem_u32(smem + L::kBlOff + sb * kTileBytes));
-#pragma unroll
-        for (int kk = 0; kk < 4; kk++) {
-          // the K offset inside the 128-byte swizzle atom advances the start address (16-byte units)
-          const uint64_t o = (uint64_t)(kk * 2);
-          mma(ah + o, bh + o, acc_on);
-          acc_on = 1u;
-          mma(ah + o, bl + o, 1u);
-          mma(al + o, bh + o, 1u);
-        }
-        commit(&empty_a[sa]);
-        commit(&empty_b[sb]);
-        bseq++;
+        commit(&acc_full[ab]);
       }
-      commit(acc_full);
     }
   } else if (warp >= 4 && warp < 12) {
     // ===================== weight unpack (thread = row x block j of the stage) =====================
     const int r = (threadIdx.x - 128) & 127, j = (warp - 4) >> 2;
     const int mpad = (p.M + GM - 1) / GM * GM;                        // rowscale has [Mpad] entries: rows beyond M carry 1
-    const float rs = (m0 + r < mpad) ? __ldg(p.rowscale + m0 + r) : 1.f;   // (PAIR: the peer's tile may lie beyond Mpad)
-    for (int ms = 0; ms < n_chunks; ms++) {
-      mbar_wait(raw_full, (uint32_t)ms & 1u);
-      uint32_t raw[NWR];
-      const uint32_t src = smem_u32(smem + L::kRawOff) + (uint32_t)r * L::kRawRowBytes;
+    int gchunk = 0, gst0 = 0, it = 0;                                 // raw chunks, A stages before this tile, tiles so far
+    for (int tl = cl; tl < n_tiles; tl += ncl, it++, gst0 += n_stages) {
+      const int m0 = tile_m0(tl);
+      const float rs = (m0 + r < mpad) ? __ldg(p.rowscale + m0 + r) : 1.f;   // (PAIR: the peer's tile may lie beyond Mpad)
+      for (int ms = 0; ms < n_chunks; ms++, gchunk++) {
+        mbar_wait(raw_full, (uint32_t)gchunk & 1u);
+        uint32_t raw[NWR];
+        const uint32_t src = smem_u32(smem + L::kRawOff) + (uint32_t)r * L::kRawRowBytes;
 #pragma unroll
-      for (int i = 0; i < NWR / 4; i++)
-        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                     : "=r"(raw[4 * i]), "=r"(raw[4 * i + 1]), "=r"(raw[4 * i + 2]), "=r"(raw[4 * i + 3])
-                     : "r"(src + 16u * i));
-      __syncwarp();
-      if (lane == 0) mbar_arrive(raw_empty);
-      if constexpr (kMin) {
-        if (j == 0) {
-          if ((ms & 7) == 0 && ms > 0) mbar_wait(ext_empty, (uint32_t)((ms >> 3) - 1) & 1u);
-          const uint4 mh = chunk_mins<WT, NWR>(raw, rs);
-          const uint32_t off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u + (((uint32_t)(ms & 7) ^ (uint32_t)(r & 7)) * 16u);
-          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(smem + L::kEhOff) + off), "r"(mh.x),
-                       "r"(mh.y), "r"(mh.z), "r"(mh.w)
-                       : "memory");
-          if ((ms & 7) == 7 || ms == n_chunks - 1) {
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) arrive_full(ext_full);
+        for (int i = 0; i < NWR / 4; i++)
+          asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(raw[4 * i]), "=r"(raw[4 * i + 1]), "=r"(raw[4 * i + 2]), "=r"(raw[4 * i + 3])
+                       : "r"(src + 16u * i));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(raw_empty);
+        if constexpr (kMin) {
+          if (j == 0) {
+            if ((ms & 7) == 0) {                       // a new group of 64 blocks: the MMA must be done with the previous m_w tile
+              const int gg = it * n_ext + (ms >> 3);
+              if (gg > 0) mbar_wait(ext_empty, (uint32_t)(gg - 1) & 1u);
+            }
+            const uint4 mh = chunk_mins<WT, NWR>(raw, rs);
+            const uint32_t off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u + (((uint32_t)(ms & 7) ^ (uint32_t)(r & 7)) * 16u);
+            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(smem + L::kEhOff) + off), "r"(mh.x),
+                         "r"(mh.y), "r"(mh.z), "r"(mh.w)
+                         : "memory");
+            if ((ms & 7) == 7 || ms == n_chunks - 1) {
+              fence_proxy_async();
+              __syncwarp();
+              if (lane == 0) arrive_full(ext_full);
+            }
           }
         }
-      }
 #pragma unroll
-      for (int q = 0; q < 4; q++) {
-        const int st = ms * 4 + q, s = st % kSoAStages;
-        mbar_wait(&empty_a[s], ((uint32_t)(st / kSoAStages) & 1u) ^ 1u);
-        const uint32_t ah = smem_u32(smem + L::kAhOff + s * kTileBytes), al = smem_u32(smem + L::kAlOff + s * kTileBytes);
-        if (j == 0) {
-          if (q == 0) unpack_block_so<WT, 0, NWR>(raw, ah, al, r, rs);
-          else if (q == 1) unpack_block_so<WT, 2, NWR>(raw, ah, al, r, rs);
-          else if (q == 2) unpack_block_so<WT, 4, NWR>(raw, ah, al, r, rs);
-          else unpack_block_so<WT, 6, NWR>(raw, ah, al, r, rs);
-        } else {
-          if (q == 0) unpack_block_so<WT, 1, NWR>(raw, ah, al, r, rs);
-          else if (q == 1) unpack_block_so<WT, 3, NWR>(raw, ah, al, r, rs);
-          else if (q == 2) unpack_block_so<WT, 5, NWR>(raw, ah, al, r, rs);
-          else unpack_block_so<WT, 7, NWR>(raw, ah, al, r, rs);
+        for (int q = 0; q < 4; q++) {
+          const int st = gst0 + ms * 4 + q, s = st % kSoAStages;
+          mbar_wait(&empty_a[s], ((uint32_t)(st / kSoAStages) & 1u) ^ 1u);
+          const uint32_t ah = smem_u32(smem + L::kAhOff + s * kTileBytes), al = smem_u32(smem + L::kAlOff + s * kTileBytes);
+          if (j == 0) {
+            if (q == 0) unpack_block_so<WT, 0, NWR>(raw, ah, al, r, rs);
+            else if (q == 1) unpack_block_so<WT, 2, NWR>(raw, ah, al, r, rs);
+            else if (q == 2) unpack_block_so<WT, 4, NWR>(raw, ah, al, r, rs);
+            else unpack_block_so<WT, 6, NWR>(raw, ah, al, r, rs);
+          } else {
+            if (q == 0) unpack_block_so<WT, 1, NWR>(raw, ah, al, r, rs);
+            else if (q == 1) unpack_block_so<WT, 3, NWR>(raw, ah, al, r, rs);
+            else if (q == 2) unpack_block_so<WT, 5, NWR>(raw, ah, al, r, rs);
+            else unpack_block_so<WT, 7, NWR>(raw, ah, al, r, rs);
+          }
+          fence_proxy_async();             // generic-proxy stores -> visible to the tensor core
+          __syncwarp();
+          if (lane == 0) arrive_full(&full_a[s]);
         }
-        fence_proxy_async();             // generic-proxy stores -> visible to the tensor core
-        __syncwarp();
-        if (lane == 0) arrive_full(&full_a[s]);
       }
     }
   } else if (warp >= 12) {
     // ===================== epilogue (thread = TMEM lane = weight row) =====================
-    const int q4 = warp & 3, row = q4 * 32 + lane, m = m0 + row;
-    const float rinv = (m < p.M) ? 1.0f / __ldg(p.rowscale + m) : 1.f;    // exact: a power of two
-    mbar_wait(acc_full, 0u);
-    tc_fence_after();
-    const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16);
+    const int q4 = warp & 3, row = q4 * 32 + lane;
+    int it = 0;
+    for (int tl = cl; tl < n_tiles; tl += ncl, it++) {
+      const int ab = it & 1, m = tile_m0(tl) + row, n0 = tile_n0(tl);
+      const float rinv = (m < p.M) ? 1.0f / __ldg(p.rowscale + m) : 1.f;    // exact: a power of two
+      mbar_wait(&acc_full[ab], (uint32_t)(it >> 1) & 1u);
+      tc_fence_after();
+      const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(ab * TN);
 #pragma unroll 2
-    for (int c16 = 0; c16 < TN / 16; c16++) {
-      uint32_t v[16];
-      asm volatile(
-          "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-            "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-          : "r"(tbase + (uint32_t)(c16 * 16))
-          : "memory");
-      tmem_ld_wait();
-      if (m < p.M) {
+      for (int c16 = 0; c16 < TN / 16; c16++) {
+        uint32_t v[16];
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+              "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+            : "r"(tbase + (uint32_t)(c16 * 16))
+            : "memory");
+        tmem_ld_wait();
+        if (m < p.M) {
 #pragma unroll
-        for (int i = 0; i < 16; i++) {
-          const int n = n0 + c16 * 16 + i;
-          if (n < p.N) store_out<PEERS>(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * (__ldg(p.colscale + n) * rinv));
+          for (int i = 0; i < 16; i++) {
+            const int n = n0 + c16 * 16 + i;
+            if (n < p.N) store_out<PEERS>(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]) * (__ldg(p.colscale + n) * rinv));
+          }
         }
       }
+      // the accumulator buffer goes back to the MMA issuer: every lane's tcgen05.ld has completed (wait::ld above)
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) arrive_full(&acc_empty[ab]);
     }
   }
   tc_fence_before();
   __syncthreads();
   if constexpr (PAIR) {
     cluster_sync_all();                                // the peer's shared memory and TMEM outlive the leader's MMAs
-    if (warp == 2) tmem_dealloc_pair(tmem_base, 256);
+    if (warp == 2) tmem_dealloc_pair(tmem_base, 2 * TN);
   } else {
-    if (warp == 2) tmem_dealloc(tmem_base, 128);
+    if (warp == 2) tmem_dealloc(tmem_base, 2 * TN);
   }
 }
 
@@ -668,7 +708,7 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
   const double t_single = (double)((singles + sms - 1) / sms);
   if (pair_fits && pair_on && p.M > GM && p.N > GN && (pair_on > 1 || t_pair < t_single)) {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(2 * pairs);
+    cfg.gridDim = dim3(2 * (pairs < slots ? pairs : slots));         // persistent: one pair per TPC walks the tiles
     cfg.blockDim = dim3(kSoThreads);
     cfg.dynamicSmemBytes = smem_pair;
     cfg.stream = st;
@@ -682,9 +722,9 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
     if (p.n_peer) e = cudaLaunchKernelEx(&cfg, gemm_so_kernel<WT, true, true>, tm_w, tm_xh, tm_xl, tm_sh, p);
     else e = cudaLaunchKernelEx(&cfg, gemm_so_kernel<WT, false, true>, tm_w, tm_xh, tm_xl, tm_sh, p);
   } else {
-    const int tiles = ((p.M + GM - 1) / GM) * ((p.N + GN - 1) / GN);
-    if (p.n_peer) gemm_so_kernel<WT, true, false><<<tiles, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);
-    else gemm_so_kernel<WT, false, false><<<tiles, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);
+    const int grid = singles < sms ? singles : sms;                    // persistent: one CTA per SM walks the tiles
+    if (p.n_peer) gemm_so_kernel<WT, true, false><<<grid, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);
+    else gemm_so_kernel<WT, false, false><<<grid, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);
     e = cudaGetLastError();
   }
   g_launch_count++;
