@@ -47,6 +47,10 @@ struct DecodeParams {
   int slots, slot_bytes;
   int x_bytes;          // shared-memory bytes of the staged activations
   unsigned long long *trace;   // optional: 8 globaltimer stamps per CTA (lammcu_set_trace)
+  // 16-warp kernel: rows per warp prefetched into L2 beyond the shared-memory ring.  0 (off) everywhere: 1-4 rows ahead cost
+  // 4-10 % (round 1).  The never-taken branch stays in the refill path on purpose: without it ptxas lays the same kernel
+  // out 3.4 % slower (1057 vs 1092 tok/s on the 7B chain, measured three times on one box: profiles/r2ac, r2aq, r2ar).
+  int l2_ahead;
   // sibling batch (16-warp kernel): up to 4 weight matrices of one type, K and row stride that share
   // the activation row (q/k/v, gate/up) form one virtual matrix of M total rows.  Global rows
   // [mc[j-1], mc[j]) belong to matrix j; wb[j] / cb[j] are VIRTUAL bases (pointer minus the rows
@@ -259,7 +263,9 @@ __device__ __forceinline__ void load_x8(const DecodeParams &p, size_t e, unsigne
     const float4 *xp = reinterpret_cast<const float4 *>(p.x + e);
     a = xp[0];
     b = xp[1];
-    // for plain f32 rows `tag` is free and carries the bits of the row's RMS scale
+    // SURVEY 8f-3 (XM == 4 instantiations only: the plain kernel carries none of this): for f32 rows `tag` is free and
+    // carries the bits of the row's RMS scale
+    if constexpr (XM != 4) return;
     if (p.xop_kind == 1) {
       const float sc = __uint_as_float(tag);
       a = xop_norm4(a, sc, p.x_aux ? p.x_aux + e : nullptr);
@@ -992,6 +998,13 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
     uint64_t *bar = full + s;
     mbar_arrive_expect_tx(bar, bytes);
     bulk_g2s_stream(ring + (size_t)s * p.slot_bytes, reinterpret_cast<const void *>(a0), bytes, bar, pol);
+    // lookahead beyond the ring (LAMM_DECODE_L2_AHEAD, default 0 = never taken; see DecodeParams::l2_ahead)
+    if (!SERVER && p.l2_ahead > 0 && i + p.l2_ahead < n_rows) {
+      const uintptr_t b = row_ptr(row0 + (i + p.l2_ahead) * row_step);
+      const uintptr_t b0 = b & ~(uintptr_t)15;
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(reinterpret_cast<const void *>(b0)),
+                   "r"((uint32_t)(((b + seg_bytes + 15) & ~(uintptr_t)15) - b0)) : "memory");
+    }
   };
 
   trace_stamp(p.trace, 0);
@@ -1071,7 +1084,7 @@ __device__ __forceinline__ void decode16_body(const DecodeParams &p, uint8_t *sm
     pdl_wait();
   }
   trace_stamp(p.trace, 2);
-  if constexpr (XM == 1 && !SERVER) {
+  if constexpr (XM == 4 && !SERVER) {
     // llm_build_norm in front of this matmul: every CTA reduces the row itself (K floats, L2-resident)
     if (p.xop_kind == 1) x_tag = __float_as_uint(cta_rms_scale(p.x, p.kb * (int)type_info(WT).blck, p.x_eps, smem + 256));   // [256, 516): free until the first partial sum
   }
@@ -1780,6 +1793,12 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
     return (e && atoi(e) == 8) ? 8 : 16;
   }();
   // peer stores, sibling batches and the K-quants beyond Q2_K live in the 16-warp kernel
+  static const int l2_ahead = [] {
+    const char *e = getenv("LAMM_DECODE_L2_AHEAD");          // tuning knob: rows per warp prefetched into L2 (0 = off)
+    const int v = e ? atoi(e) : 0;
+    return v < 0 ? 0 : (v > 16 ? 16 : v);
+  }();
+  p.l2_ahead = l2_ahead;
   const int variant = (sh || bt || xop || is_kquant_ext(w_type)) ? 16 : variant_env;
   if (xop && xop->kind) {
     if (!x || (sh && sh->x_ll)) { set_error("decode: a fused op needs a plain f32 activation row"); return LAMMCU_ERR_ARG; }
@@ -1837,6 +1856,7 @@ int launch_decode(int w_type, const void *w, int64_t w_stride, const float *x, c
   p.trace = next_trace_slot(grid);
   if (variant == 16) {
     if (xm == 2) return launch_decode16_x<2>(w_type, p, grid, warps * 32, smem, st);
+    if (p.xop_kind) return launch_decode16_x<4>(w_type, p, grid, warps * 32, smem, st);    // the op-in-front instantiations
     return xm ? launch_decode16_x<1>(w_type, p, grid, warps * 32, smem, st)
               : launch_decode16_x<0>(w_type, p, grid, warps * 32, smem, st);
   }

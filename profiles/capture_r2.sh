@@ -14,7 +14,7 @@ timeout 200 python bench.py --suite gemm --n 2048 --fmts q4_0,q4_1,q5_0,q5_1,q8_
 timeout 120 python bench.py --suite gemm --n 512 --fmts q5_0 --shapes 6656x6656,17920x6656,6656x17920 > $O/sweep_gemm_30b_q5_0_n512.jsonl 2>&1
 timeout 90 python tools/trace_decode.py > $O/trace_decode.txt 2>&1
 # launch list of the bench command (2 timed steps): per-launch durations + DRAM bytes, cold-cache and serialised
-SHORT="--steps 2 --warmup 3 --no-cpu --no-e2e --no-extras --sustain-s 0"   # (the launch list of r2_launches_bench.csv was taken with the gemm block in; r2_launches_chain.csv adds --no-gemm)
+SHORT="--steps 2 --warmup 3 --no-cpu --no-e2e --no-extras --no-gemm --sustain-s 0"
 timeout 300 python bench.py $SHORT > $O/bench_short.json 2>&1 && \
 timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none \
     -k regex:'decode|gemv|quantize|gemm|prep|wrow|xop|convert' -c 2500 --csv \
