@@ -459,18 +459,29 @@ __device__ __forceinline__ void dot_unit_f32(const uint8_t *rowp, int u, const G
 }
 
 // ---- F16 weights: ggml_vec_dot_f16 (ggml.c:1414-1457) on src1 rounded to fp16 -------------
-// unit = 16 bytes = 8 fp16 weights.  Xq holds the fp16 activations (ggml_fp32_to_fp16_row); they are widened back
-// to f32 once per CTA (exact), so every product w * x is exact in f32 (11 + 11 significant bits) and only the f32
-// accumulation order differs from ggml's SIMD lanes.
+// unit = 16 bytes = 8 fp16 weights.  Xq holds the fp16 activations (ggml_fp32_to_fp16_row); they stay fp16 in shared
+// memory (one byte of activation read per byte of weight: as f32 the dot phase read 4 B of x per 2 B of w and the
+// kernel was shared-memory-bound at 30-48 % of the HBM peak) and both operands are widened in registers, so every
+// product w * x is exact in f32 (11 + 11 significant bits) and only the f32 accumulation order differs from ggml's
+// SIMD lanes.
 template <int NC>
 __device__ __forceinline__ void stage_xf16(const GemvParams &p, uint8_t *xs, int tid) {
-  float *x = reinterpret_cast<float *>(xs);
-  const int K = p.units * 8;
-  for (int idx = tid; idx < NC * K; idx += kConsumerWarps * 32) {
-    const int n = idx / K, k = idx - n * K;
-    x[idx] = (n < p.n_valid)
-                 ? __half2float(*reinterpret_cast<const __half *>(p.xq + (int64_t)n * p.xq_stride + 2 * (int64_t)k))
-                 : 0.f;
+  uint4 *x = reinterpret_cast<uint4 *>(xs);
+  const int U = p.units;                                         // 16-byte chunks per row
+  for (int idx = tid; idx < NC * U; idx += kConsumerWarps * 32) {
+    const int n = idx / U, u = idx - n * U;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (n < p.n_valid) {
+      const uint8_t *src = p.xq + (int64_t)n * p.xq_stride + 16 * (int64_t)u;
+      if ((((uintptr_t)p.xq | (uintptr_t)p.xq_stride) & 15) == 0) {
+        v = *reinterpret_cast<const uint4 *>(src);
+      } else {                                                   // 2-byte aligned rows
+        const uint16_t *h = reinterpret_cast<const uint16_t *>(src);
+        v = make_uint4(h[0] | ((uint32_t)h[1] << 16), h[2] | ((uint32_t)h[3] << 16), h[4] | ((uint32_t)h[5] << 16),
+                       h[6] | ((uint32_t)h[7] << 16));
+      }
+    }
+    x[idx] = v;
   }
 }
 template <int NC>
@@ -478,21 +489,20 @@ __device__ __forceinline__ void dot_unit_f16(const uint8_t *rowp, int u, const G
                                              const uint8_t *xs, float (&acc)[NC]) {
   uint32_t w[4];
   lds_words_a4<4>(rowp + 16 * u, w);
-  float wf[8];
+  float2 wf[4];
 #pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&w[i]));
-    wf[2 * i] = f.x;
-    wf[2 * i + 1] = f.y;
-  }
-  const float4 *x = reinterpret_cast<const float4 *>(xs);
+  for (int i = 0; i < 4; i++) wf[i] = __half22float2(*reinterpret_cast<const __half2 *>(&w[i]));
+  const uint4 *x = reinterpret_cast<const uint4 *>(xs);
 #pragma unroll
   for (int n = 0; n < NC; n++) {
-    const float4 a = x[(n * p.units + u) * 2], b = x[(n * p.units + u) * 2 + 1];
-    acc[n] = fmaf(wf[0], a.x, acc[n]);  acc[n] = fmaf(wf[1], a.y, acc[n]);
-    acc[n] = fmaf(wf[2], a.z, acc[n]);  acc[n] = fmaf(wf[3], a.w, acc[n]);
-    acc[n] = fmaf(wf[4], b.x, acc[n]);  acc[n] = fmaf(wf[5], b.y, acc[n]);
-    acc[n] = fmaf(wf[6], b.z, acc[n]);  acc[n] = fmaf(wf[7], b.w, acc[n]);
+    const uint4 xv = x[n * p.units + u];
+    const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const float2 xf = __half22float2(*reinterpret_cast<const __half2 *>(&xw[i]));
+      acc[n] = fmaf(wf[i].x, xf.x, acc[n]);
+      acc[n] = fmaf(wf[i].y, xf.y, acc[n]);
+    }
   }
 }
 
@@ -669,7 +679,8 @@ static int launch_nc(int nc, const GemvParams &p, int grid, int smem, cudaStream
 
 static int x_bytes_for(int w_type, int nc, int kb, int64_t K) {
   int b;
-  if (w_type == LAMMCU_TYPE_F32 || w_type == LAMMCU_TYPE_F16) b = nc * (int)K * 4;
+  if (w_type == LAMMCU_TYPE_F32) b = nc * (int)K * 4;
+  else if (w_type == LAMMCU_TYPE_F16) b = nc * (int)K * 2;
   else if (type_info(w_type).blck == 256) b = nc * kb * 292;
   else b = nc * kb * 40;
   return (b + 127) & ~127;
