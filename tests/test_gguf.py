@@ -4,6 +4,7 @@ committed fixture of the same kind for machines without the compiled reference. 
 device.  Robustness: every truncation of a valid file and single-byte corruptions of its header must be an
 error or a consistent parse, never a crash."""
 import os
+import sys
 
 import numpy as np
 import pytest
@@ -163,6 +164,24 @@ def test_row_ranges_are_contiguous_byte_ranges(lamm):
             for lo, hi in [(-1, 1), (0, m + 1), (1, 1)]:
                 with pytest.raises(lamm.LammError):
                     g.rows(i, lo, hi)
+
+
+def test_rank_shards_tile_every_tensor(lamm):
+    """SURVEY 8f-4, host half of the sharded load: the byte ranges the ranks of a 2-, 3- and 8-way row shard would upload
+    (lammcu_gguf_rows on sharding.row_shard) are disjoint, ordered and concatenate to the tensor's bytes."""
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from lamm_b200.sharding import row_shard
+    with lamm.Gguf(FIXTURE) as g:
+        for i in range(len(g)):
+            _, t, nd, ne, raw = g.tensor(i)
+            m = ne[1]
+            for world in (2, 3, 8):
+                parts = []
+                for rank in range(world):
+                    lo, hi = row_shard(m, rank, world)
+                    if hi > lo:
+                        parts.append(g.rows(i, lo, hi))
+                assert np.array_equal(np.concatenate(parts), raw), (i, world)
 
 
 def test_upload_needs_a_device_and_a_weight_type(lamm):
