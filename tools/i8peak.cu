@@ -164,6 +164,89 @@ __global__ void __launch_bounds__(128, 1) peak_kernel(int iters, unsigned long l
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
 }
 
+// ---- (2b) the CTA-pair form: tcgen05.mma.cta_group::2, M256 x N256 x K16 (kind::f16), operands resident ----------
+// Each CTA of the cluster of 2 holds 128 rows of A and 128 of the 256 rows of B; the leader issues; both time.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) peak_pair_kernel(int iters, unsigned long long *cycles) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t *sa = smem, *sb = smem + 16384;                 // A 128 rows, B 128 rows (this CTA's half), 128 bytes per row
+  uint64_t *bar = reinterpret_cast<uint64_t *>(smem + 32768);
+  uint32_t *slot = reinterpret_cast<uint32_t *>(smem + 32768 + 16);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  for (int i = tid; i < 32768 / 4; i += 128) reinterpret_cast<uint32_t *>(smem)[i] = 0x3c003c00u;
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *slot;
+  const unsigned long long t0 = clock64();
+  if (tid == 0 && rank == 0) {
+    const uint64_t ad = sw128_desc(smem_u32(sa)), bd = sw128_desc(smem_u32(sb));
+    const uint32_t idesc = make_idesc(1, 0, 0, 256, 256);
+    for (int it = 0; it < iters; it++) {
+      const uint32_t d = tmem + (uint32_t)((it & 1) * 256);
+#pragma unroll
+      for (int kk = 0; kk < 4; kk++)
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
+                     "l"(ad + (uint64_t)(2 * kk)), "l"(bd + (uint64_t)(2 * kk)), "r"(idesc), "r"((it > 1 || kk) ? 1u : 0u)
+                     : "memory");
+    }
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)),
+                 "h"((uint16_t)3)
+                 : "memory");
+  }
+  if (tid == 0) {
+    mbar_wait(bar, 0u);
+    cycles[blockIdx.x] = clock64() - t0;
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+}
+
+static void run_peak_pair(int sms, int iters) {
+  const int smem = 32768 + 64 + 1024;
+  const int ctas = sms & ~1;
+  CK(cudaFuncSetAttribute(peak_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  unsigned long long *cyc;
+  CK(cudaMalloc(&cyc, ctas * 8));
+  cudaEvent_t e0, e1;
+  CK(cudaEventCreate(&e0));
+  CK(cudaEventCreate(&e1));
+  double best_ms = 1e30;
+  for (int rep = 0; rep < 6; rep++) {
+    CK(cudaEventRecord(e0));
+    peak_pair_kernel<<<ctas, 128, smem>>>(iters, cyc);
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    float ms;
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    if (rep && ms < best_ms) best_ms = ms;
+  }
+  std::vector<unsigned long long> h(ctas);
+  CK(cudaMemcpy(h.data(), cyc, ctas * 8, cudaMemcpyDeviceToHost));
+  unsigned long long cmax = 0;
+  for (auto v : h) cmax = v > cmax ? v : cmax;
+  const double ops = 2.0 * 256 * 256 * 16 * 4.0 * iters * (ctas / 2);
+  printf("{\"kind\": \"f16\", \"tile\": \"M256xN256xK16\", \"cta_group\": 2, \"ctas\": %d, \"iters\": %d, \"ms\": %.4f, \"tops\": %.1f, "
+         "\"cycles_per_mma\": %.2f}\n",
+         ctas, iters, best_ms, ops / (best_ms * 1e-3) / 1e12, (double)cmax / (4.0 * iters));
+  CK(cudaFree(cyc));
+}
+
 template <int KIND>
 static void run_peak(const char *name, int sms, int iters, int N) {
   const int smem = 16384 + 32768 + 64 + 1024;
@@ -255,5 +338,6 @@ int main(int argc, char **argv) {
   run_peak<0>("f16", prop.multiProcessorCount, iters, 128);
   run_peak<1>("i8", prop.multiProcessorCount, iters, 128);
   run_peak<1>("i8", prop.multiProcessorCount, iters, 64);
+  run_peak_pair(prop.multiProcessorCount, iters);
   return bad ? 1 : 0;
 }
