@@ -614,9 +614,22 @@ def gemm_block(torch, L, dev, args):
     gen = torch.Generator(device=dev)
     gen.manual_seed(99)
     out = {"unit": "TOPS", "int8_peak_tops_measured": INT8_TOPS_MEASURED, "f16_peak_tflops_measured": F16_TOPS_MEASURED,
-           "peak_source": "tools/i8peak.cu on this pool (profiles/r2g/i8peak.txt)", "cases": []}
-    for fmt, m, k, n, kind in (("q4_1", 13824, 5120, 2048, "tcgen05 kind::f16 cta_group::2 (CTA pairs, 256 x 256 tiles), 3 MMAs per product (scaled fp16 hi/lo operands)"),
-                               ("q2_k", 11008, 4096, 512, "tcgen05 kind::i8 (scale-folded u8 x s8, exact integer sums)")):
+           "peak_source": "tools/i8peak.cu on this pool (profiles/r2g/i8peak.txt): an MMA stream on constant operands "
+                          "resident in shared memory, which never meets the board's power cap", "cases": []}
+    # the driver's dense figure: cuBLAS bf16 8192^3 on random data, burst / held for seconds under the 1 kW cap.  A
+    # tensor-bound kernel on real data is power-bound well below the constant-operand stream above (profiles/r2bd: the
+    # pair GEMM runs at 1485-1580 MHz of 1965 with sw_power_cap active), so the ISSUED fp16 tensor rate (3 MMAs per
+    # product for the 32-element formats) is also reported against this file's burst number
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            pk = json.load(f)
+        bf16_burst, bf16_sust = float(pk["bf16_tflops"]), float(pk.get("bf16_tflops_sustained", 0.0)) or None
+    except (OSError, KeyError, ValueError):
+        bf16_burst, bf16_sust = 1590.0, None                     # B200_PROFILING.md fallback
+    out["bf16_dense_tflops_file"] = {"burst": bf16_burst, "sustained": bf16_sust,
+                                     "source": "MEASURED_PEAKS.json (cuBLAS bf16)" if bf16_sust else "fallback (B200_PROFILING.md)"}
+    for fmt, m, k, n, mmas, kind in (("q4_1", 13824, 5120, 2048, 3, "tcgen05 kind::f16 cta_group::2 (CTA pairs, 256 x 256 tiles), 3 MMAs per product (scaled fp16 hi/lo operands)"),
+                                     ("q2_k", 11008, 4096, 512, 0, "tcgen05 kind::i8 (scale-folded u8 x s8, exact integer sums)")):
         t = TYPE_IDS[fmt]
         wb = m * w_row_bytes(t, k)
         ring = max(2, min(16, (256 * (1 << 20) + wb - 1) // wb))
@@ -657,6 +670,9 @@ def gemm_block(torch, L, dev, args):
                              "frac_f16_peak_measured": round(tops / F16_TOPS_MEASURED, 4),
                              "tensor_path": kind, "launches_per_matmul": launches, "distinct_weights": ring,
                              "includes": "activation quantize + operand prep + GEMM"})
+        if mmas:
+            out["cases"][-1]["issued_f16_tflops"] = round(tops * mmas, 1)
+            out["cases"][-1]["issued_frac_of_file_bf16_burst"] = round(tops * mmas / bf16_burst, 4)
         del ws, g
         torch.cuda.empty_cache()
     if not args.no_cpu:

@@ -194,7 +194,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
                      : "=r"(raw[4 * i]), "=r"(raw[4 * i + 1]), "=r"(raw[4 * i + 2]), "=r"(raw[4 * i + 3])
                      : "r"(src + 16u * i));
       __syncwarp();
-      if (lane == 0) mbar_arrive(&raw_empty[rs]);
+      if (lane == 0) mbar_arrive_after_loads(&raw_empty[rs], raw, (uint32_t)p.K & 1u);   // (lamm_common.cuh: not before the loads)
 #pragma unroll
       for (int q = 0; q < 4; q++) {
         const int st = ms * 4 + q, s = st % kGStages;

@@ -135,7 +135,8 @@ gemm_f16_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
 }
 
 bool gemm_f16_pair_supported(int64_t M, int64_t N, int64_t K) {
-  static const int on = [] { const char *e = getenv("LAMM_GEMM_PAIR"); return e ? atoi(e) : 1; }();
+  const char *e = getenv("LAMM_GEMM_PAIR");              // per call: tests compare both forms in one process
+  const int on = e ? atoi(e) : 1;
   return on && N > 128 && M > 128 && K % GK == 0;
 }
 

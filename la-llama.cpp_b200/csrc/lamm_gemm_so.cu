@@ -48,7 +48,16 @@ constexpr double kSoPairGain = 1.4;            // per-tile speed of the pair for
 #ifndef LAMM_SO_PAIR_NB
 #define LAMM_SO_PAIR_NB 3
 #endif
-template <bool PAIR> struct SoRing { static constexpr int A = PAIR ? LAMM_SO_PAIR_NA : 2, B = PAIR ? LAMM_SO_PAIR_NB : 3; };
+// ATM (pair form only): the unpacked weight tiles live in TENSOR MEMORY (3 stages x 64 columns behind ONE 256-column
+// accumulator) instead of shared memory, which leaves room for a deeper activation ring
+#ifndef LAMM_SO_ATM_NB
+#define LAMM_SO_ATM_NB 4
+#endif
+constexpr int kSoAtmStages = 3;
+template <bool PAIR, bool ATM = false> struct SoRing {
+  static constexpr int A = ATM ? kSoAtmStages : PAIR ? LAMM_SO_PAIR_NA : 2, B = ATM ? LAMM_SO_ATM_NB : PAIR ? LAMM_SO_PAIR_NB : 3;
+};
+constexpr int kSoMaxA = 3, kSoMaxB = 6;       // barrier slots
 constexpr int kSoThreads = 512;
 constexpr int kTileBytes = GM * GK * 2;        // 16 KB: one 128 x 64 fp16 operand tile
 
@@ -99,7 +108,8 @@ __device__ __forceinline__ void store_out(const SoParams &p, int64_t idx, float 
   }
 }
 
-template <int WT, int kSoAStages, int kSoBStages> struct SoSmem {
+template <int WT, int kSoAStagesAll, int kSoBStages, bool ATM = false> struct SoSmem {
+  static constexpr int kSoAStages = ATM ? 0 : kSoAStagesAll;         // A tiles in shared memory
   static constexpr int BS = type_info(WT).size;
   static constexpr int kRawRowBytes = 8 * BS;                       // 8 blocks = 256 K elements = 4 stages
   static constexpr int kRawBytes = GM * kRawRowBytes;
@@ -112,6 +122,7 @@ template <int WT, int kSoAStages, int kSoBStages> struct SoSmem {
   static constexpr int kRawOff = kEhOff + (kMin ? kTileBytes : 0);
   static constexpr int kBarOff = kRawOff + (kRawBytes + 127) / 128 * 128;
   static constexpr int kTotal = kBarOff + 256;
+  static_assert(kSoAStagesAll <= kSoMaxA && kSoBStages <= kSoMaxB, "barrier slots");
 };
 
 // 8 fp16 small integers (one 16-byte chunk of unpack_block) * d -> 8 fp16 hi + 8 fp16 lo, EXACT:
@@ -159,6 +170,26 @@ __device__ __forceinline__ void unpack_block_so(const uint32_t (&raw)[NWR], uint
   }
 }
 
+// ATM: the same block into the thread's TMEM lane: 16 words hi at column 16 j of the stage, 16 words lo 32 columns on
+template <int WT, int JB, int NWR>
+__device__ __forceinline__ void unpack_block_tm(const uint32_t (&raw)[NWR], uint32_t t_stage, float rs) {
+  constexpr int j = JB & 1;
+  uint4 out[4];
+  float d, m;
+  unpack_block<WT, JB, NWR>(raw, out, d, m);
+  const __half2 d2 = __float2half2_rn(d * rs);
+  uint32_t h[16], l[16];
+#pragma unroll
+  for (int w = 0; w < 4; w++) {
+    uint4 hi, lo;
+    scale_split8(out[w], d2, hi, lo);
+    h[4 * w] = hi.x;  h[4 * w + 1] = hi.y;  h[4 * w + 2] = hi.z;  h[4 * w + 3] = hi.w;
+    l[4 * w] = lo.x;  l[4 * w + 1] = lo.y;  l[4 * w + 2] = lo.z;  l[4 * w + 3] = lo.w;
+  }
+  tmem_st16(t_stage + (uint32_t)(16 * j), h);
+  tmem_st16(t_stage + (uint32_t)(32 + 16 * j), l);
+}
+
 // the 8 m_w of the raw chunk (Q4_1 / Q5_1: fp16 at byte 2 of every block) times the row's lift S: one 16-byte
 // chunk of the extra A tile (m_w is an fp16 field, the power-of-two scale keeps it exact)
 template <int WT, int NWR>
@@ -176,24 +207,31 @@ __device__ __forceinline__ uint4 chunk_mins(const uint32_t (&raw)[NWR], float S)
 // still unpacks its own 128 weight rows and loads 128 activation rows, but the pair's leader issues ONE M256 x N256
 // MMA stream over both, so per unit of work an SM reads half the shared memory and pulls half the activation bytes
 // from L2 (the 128 x 128 form is bound by exactly those two: 125 B/clk of MMA operand reads + 42 B/clk of B tiles).
-template <int WT, bool PEERS, bool PAIR>
+template <int WT, bool PEERS, bool PAIR, bool ATM = false>
 __global__ void __launch_bounds__(kSoThreads, 1)
 gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_xh,
                const __grid_constant__ CUtensorMap tm_xl, const __grid_constant__ CUtensorMap tm_sh, const SoParams p) {
-  constexpr int kSoAStages = SoRing<PAIR>::A, kSoBStages = SoRing<PAIR>::B;
-  using L = SoSmem<WT, kSoAStages, kSoBStages>;
+  static_assert(PAIR || !ATM, "A in tensor memory: pair form only");
+  constexpr int kSoAStages = SoRing<PAIR, ATM>::A, kSoBStages = SoRing<PAIR, ATM>::B;
+  using L = SoSmem<WT, kSoAStages, kSoBStages, ATM>;
   constexpr bool kMin = L::kMin;
   constexpr int NWR = 2 * L::BS;                                    // raw words per row chunk
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + L::kBarOff);
-  uint64_t *full_a = bars, *empty_a = bars + 3, *full_b = bars + 6, *empty_b = bars + 9, *raw_full = bars + 12,
-           *raw_empty = bars + 13, *acc_full = bars + 14, *acc_empty = bars + 16, *ext_full = bars + 18, *ext_empty = bars + 19;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 20);
+  uint64_t *full_a = bars, *empty_a = full_a + kSoMaxA, *full_b = empty_a + kSoMaxA, *empty_b = full_b + kSoMaxB,
+           *raw_full = empty_b + kSoMaxB, *raw_empty = raw_full + 1, *acc_full = raw_empty + 1, *acc_empty = acc_full + 2,
+           *ext_full = acc_empty + 2, *ext_empty = ext_full + 1;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(ext_empty + 1);
+  static_assert((2 * kSoMaxA + 2 * kSoMaxB + 8 + 1) * 8 <= 256, "barrier area");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int TN = PAIR ? 256 : GN;                                // accumulator columns per CTA
   constexpr int TM = PAIR ? 256 : GM;                                // weight rows per tile (pair: 128 per CTA)
+  // accumulators in TMEM: two (tile i drains while tile i + 1 accumulates), or ONE followed by the A stages (ATM)
+  constexpr int kAccBufs = ATM ? 1 : 2;
+  constexpr uint32_t kTmemCols = ATM ? 512u : (uint32_t)(2 * TN), kTmemA = (uint32_t)TN;
+  static_assert(!ATM || TN + kSoAStages * 64 <= 512, "tensor memory budget");
   const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
   const bool leader = (rank == 0u);
   const int n_stages = p.K / GK, n_chunks = n_stages / 4;
@@ -227,7 +265,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
     }
     mbar_init(raw_full, 1);
     mbar_init(raw_empty, 8);
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < kAccBufs; i++) {
       mbar_init(&acc_full[i], 1);                      // MMA commit: accumulator i holds a finished tile
       mbar_init(&acc_empty[i], PAIR ? 8 : 4);          // the epilogue warps (of both CTAs) have drained it
     }
@@ -250,9 +288,9 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
   if constexpr (PAIR) {
     __syncthreads();
     cluster_sync_all();                                // both CTAs' barriers exist before anything remote arrives
-    if (warp == 2) tmem_alloc_pair(tmem_slot, 2 * TN);
+    if (warp == 2) tmem_alloc_pair(tmem_slot, kTmemCols);
   } else {
-    if (warp == 2) tmem_alloc(tmem_slot, 2 * TN);
+    if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
   }
   tc_fence_before();
   __syncthreads();
@@ -312,9 +350,10 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
     if (lane == 0 && leader) {
       int bseq = 0, gst = 0, gext = 0, it = 0;         // B stages, A stages, extra stages, tiles so far
       for (int tl = cl; tl < n_tiles; tl += ncl, it++) {
-        const int ab = it & 1;                         // accumulator buffer of this tile
-        if constexpr (PAIR) mbar_wait_cluster(&acc_empty[ab], ((uint32_t)(it >> 1) & 1u) ^ 1u);
-        else mbar_wait(&acc_empty[ab], ((uint32_t)(it >> 1) & 1u) ^ 1u);
+        const int ab = ATM ? 0 : (it & 1);             // accumulator buffer of this tile
+        const uint32_t aph = (uint32_t)(ATM ? it : (it >> 1)) & 1u;
+        if constexpr (PAIR) mbar_wait_cluster(&acc_empty[ab], aph ^ 1u);
+        else mbar_wait(&acc_empty[ab], aph ^ 1u);
         tc_fence_after();
         const uint32_t tacc = tmem_base + (uint32_t)(ab * TN);
         auto mma = [&](uint64_t a, uint64_t b, uint32_t acc) {
@@ -346,18 +385,32 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
           else mbar_wait(&full_a[sa], (uint32_t)(gst / kSoAStages) & 1u);
           mbar_wait(&full_b[sb], (uint32_t)(bseq / kSoBStages) & 1u);
           tc_fence_after();
-          const uint64_t ah = make_sw128_desc(smem_u32(smem + L::kAhOff + sa * kTileBytes));
-          const uint64_t al = make_sw128_desc(smem_u32(smem + L::kAlOff + sa * kTileBytes));
           const uint64_t bh = make_sw128_desc(smem_u32(smem + L::kBhOff + sb * kTileBytes));
           const uint64_t bl = make_sw128_desc(smem_u32(smem + L::kBlOff + sb * kTileBytes));
+          if constexpr (ATM) {
+            // A from tensor memory: hi = 32 columns (64 fp16 per lane), lo the next 32; a K16 step is 8 columns
+            const uint32_t th = tmem_base + kTmemA + (uint32_t)(sa * 64), tl_ = th + 32u;
 #pragma unroll
-          for (int kk = 0; kk < 4; kk++) {
-            // the K offset inside the 128-byte swizzle atom advances the start address (16-byte units)
-            const uint64_t o = (uint64_t)(kk * 2);
-            mma(ah + o, bh + o, acc_on);
-            acc_on = 1u;
-            mma(ah + o, bl + o, 1u);
-            mma(al + o, bh + o, 1u);
+            for (int kk = 0; kk < 4; kk++) {
+              const uint64_t o = (uint64_t)(kk * 2);
+              const uint32_t oa = (uint32_t)(kk * 8);
+              umma_f16_pair_ts(tacc, th + oa, bh + o, kIdescF16Pair, acc_on);
+              acc_on = 1u;
+              umma_f16_pair_ts(tacc, th + oa, bl + o, kIdescF16Pair, 1u);
+              umma_f16_pair_ts(tacc, tl_ + oa, bh + o, kIdescF16Pair, 1u);
+            }
+          } else {
+            const uint64_t ah = make_sw128_desc(smem_u32(smem + L::kAhOff + sa * kTileBytes));
+            const uint64_t al = make_sw128_desc(smem_u32(smem + L::kAlOff + sa * kTileBytes));
+#pragma unroll
+            for (int kk = 0; kk < 4; kk++) {
+              // the K offset inside the 128-byte swizzle atom advances the start address (16-byte units)
+              const uint64_t o = (uint64_t)(kk * 2);
+              mma(ah + o, bh + o, acc_on);
+              acc_on = 1u;
+              mma(ah + o, bl + o, 1u);
+              mma(al + o, bh + o, 1u);
+            }
           }
           commit(&empty_a[sa]);
           commit(&empty_b[sb]);
@@ -384,8 +437,8 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
           asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
                        : "=r"(raw[4 * i]), "=r"(raw[4 * i + 1]), "=r"(raw[4 * i + 2]), "=r"(raw[4 * i + 3])
                        : "r"(src + 16u * i));
-        __syncwarp();
-        if (lane == 0) mbar_arrive(raw_empty);
+__syncwarp();
+        if (lane == 0) mbar_arrive_after_loads(raw_empty, raw, (uint32_t)p.K & 1u);   // K is a multiple of 64
         if constexpr (kMin) {
           if (j == 0) {
             if ((ms & 7) == 0) {                       // a new group of 64 blocks: the MMA must be done with the previous m_w tile
@@ -408,19 +461,38 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
         for (int q = 0; q < 4; q++) {
           const int st = gst0 + ms * 4 + q, s = st % kSoAStages;
           mbar_wait(&empty_a[s], ((uint32_t)(st / kSoAStages) & 1u) ^ 1u);
-          const uint32_t ah = smem_u32(smem + L::kAhOff + s * kTileBytes), al = smem_u32(smem + L::kAlOff + s * kTileBytes);
-          if (j == 0) {
-            if (q == 0) unpack_block_so<WT, 0, NWR>(raw, ah, al, r, rs);
-            else if (q == 1) unpack_block_so<WT, 2, NWR>(raw, ah, al, r, rs);
-            else if (q == 2) unpack_block_so<WT, 4, NWR>(raw, ah, al, r, rs);
-            else unpack_block_so<WT, 6, NWR>(raw, ah, al, r, rs);
+          if constexpr (ATM) {
+            // thread = row = TMEM lane (warp % 4 is the lane quarter); the MMA of the stage's previous use has completed
+            tc_fence_after();
+            const uint32_t ts = tmem_base + ((uint32_t)(r & ~31) << 16) + kTmemA + (uint32_t)(s * 64);
+            if (j == 0) {
+              if (q == 0) unpack_block_tm<WT, 0, NWR>(raw, ts, rs);
+              else if (q == 1) unpack_block_tm<WT, 2, NWR>(raw, ts, rs);
+              else if (q == 2) unpack_block_tm<WT, 4, NWR>(raw, ts, rs);
+              else unpack_block_tm<WT, 6, NWR>(raw, ts, rs);
+            } else {
+              if (q == 0) unpack_block_tm<WT, 1, NWR>(raw, ts, rs);
+              else if (q == 1) unpack_block_tm<WT, 3, NWR>(raw, ts, rs);
+              else if (q == 2) unpack_block_tm<WT, 5, NWR>(raw, ts, rs);
+              else unpack_block_tm<WT, 7, NWR>(raw, ts, rs);
+            }
+            tmem_st_wait();                  // the stores have landed in tensor memory
+            tc_fence_before();
           } else {
-            if (q == 0) unpack_block_so<WT, 1, NWR>(raw, ah, al, r, rs);
-            else if (q == 1) unpack_block_so<WT, 3, NWR>(raw, ah, al, r, rs);
-            else if (q == 2) unpack_block_so<WT, 5, NWR>(raw, ah, al, r, rs);
-            else unpack_block_so<WT, 7, NWR>(raw, ah, al, r, rs);
+            const uint32_t ah = smem_u32(smem + L::kAhOff + s * kTileBytes), al = smem_u32(smem + L::kAlOff + s * kTileBytes);
+            if (j == 0) {
+              if (q == 0) unpack_block_so<WT, 0, NWR>(raw, ah, al, r, rs);
+              else if (q == 1) unpack_block_so<WT, 2, NWR>(raw, ah, al, r, rs);
+              else if (q == 2) unpack_block_so<WT, 4, NWR>(raw, ah, al, r, rs);
+              else unpack_block_so<WT, 6, NWR>(raw, ah, al, r, rs);
+            } else {
+              if (q == 0) unpack_block_so<WT, 1, NWR>(raw, ah, al, r, rs);
+              else if (q == 1) unpack_block_so<WT, 3, NWR>(raw, ah, al, r, rs);
+              else if (q == 2) unpack_block_so<WT, 5, NWR>(raw, ah, al, r, rs);
+              else unpack_block_so<WT, 7, NWR>(raw, ah, al, r, rs);
+            }
+            fence_proxy_async();             // generic-proxy stores -> visible to the tensor core
           }
-          fence_proxy_async();             // generic-proxy stores -> visible to the tensor core
           __syncwarp();
           if (lane == 0) arrive_full(&full_a[s]);
         }
@@ -431,9 +503,9 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
     const int q4 = warp & 3, row = q4 * 32 + lane;
     int it = 0;
     for (int tl = cl; tl < n_tiles; tl += ncl, it++) {
-      const int ab = it & 1, m = tile_m0(tl) + row, n0 = tile_n0(tl);
+      const int ab = ATM ? 0 : (it & 1), m = tile_m0(tl) + row, n0 = tile_n0(tl);
       const float rinv = (m < p.M) ? 1.0f / __ldg(p.rowscale + m) : 1.f;    // exact: a power of two
-      mbar_wait(&acc_full[ab], (uint32_t)(it >> 1) & 1u);
+      mbar_wait(&acc_full[ab], (uint32_t)(ATM ? it : (it >> 1)) & 1u);
       tc_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(ab * TN);
 #pragma unroll 2
@@ -465,9 +537,9 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
   __syncthreads();
   if constexpr (PAIR) {
     cluster_sync_all();                                // the peer's shared memory and TMEM outlive the leader's MMAs
-    if (warp == 2) tmem_dealloc_pair(tmem_base, 2 * TN);
+    if (warp == 2) tmem_dealloc_pair(tmem_base, kTmemCols);
   } else {
-    if (warp == 2) tmem_dealloc(tmem_base, 2 * TN);
+    if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
   }
 }
 
@@ -679,7 +751,9 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
   constexpr int smem = SoSmem<WT, SoRing<false>::A, SoRing<false>::B>::kTotal + 1024;
   constexpr int smem_pair = SoSmem<WT, SoRing<true>::A, SoRing<true>::B>::kTotal + 1024;
   static_assert(smem <= 227 * 1024, "shared memory budget");
+  constexpr int smem_atm = SoSmem<WT, SoRing<true, true>::A, SoRing<true, true>::B, true>::kTotal + 1024;
   constexpr bool pair_fits = smem_pair <= 227 * 1024;
+  static_assert(smem_atm <= 227 * 1024, "shared memory budget (A in tensor memory)");
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(gemm_so_kernel<WT, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -689,6 +763,10 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
       e = cudaFuncSetAttribute(gemm_so_kernel<WT, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_pair);
     if (e == cudaSuccess && pair_fits)
       e = cudaFuncSetAttribute(gemm_so_kernel<WT, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_pair);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_so_kernel<WT, false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_atm);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_so_kernel<WT, true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_atm);
     if (e != cudaSuccess) {
       set_error("gemm_so: cudaFuncSetAttribute(%d): %s", smem, cudaGetErrorString(e));
       return LAMMCU_ERR_CUDA;
@@ -696,7 +774,16 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
     attr_set = true;
   }
   // CTA pairs (256 x 256 per cluster of 2) whenever both dimensions have more than one 128-tile; LAMM_GEMM_PAIR=0: never
-  static const int pair_on = [] { const char *e = getenv("LAMM_GEMM_PAIR"); return e ? atoi(e) : 1; }();
+  // (read per call, like LAMM_GEMM_ATM below: tests force each form on ragged shapes in one process)
+  const char *pair_env = getenv("LAMM_GEMM_PAIR");
+  const int pair_on = pair_env ? atoi(pair_env) : 1;
+  // Unpacked weight tiles of the pair form in TENSOR MEMORY (ATM) or in shared memory.  Measured at 13B N = 2048
+  // (profiles/r2bc, r2bd): ATM draws less power (1582 vs 1485 MHz under the cap) but needs more cycles per tile (one
+  // accumulator: the epilogue is exposed; tcgen05.st + wait::st sit in the unpack chain) -- Q4_1 492 vs 511 TOPS, Q4_0 501
+  // vs 522, Q8_0 483 vs 501, but Q5_1 483 vs 463 (its shared-memory form has the largest raw ring and the heaviest unpack).
+  // Default: ATM for Q5_1 only; LAMM_GEMM_ATM=0 / 1 forces the form (read per call, so one process can compare both).
+  const char *atm_env = getenv("LAMM_GEMM_ATM");
+  const int atm_on = atm_env ? (atoi(atm_env) != 0) : (WT == LAMMCU_TYPE_Q5_1 || !pair_fits);
   cudaError_t e;
   // no persistent scheduler yet, so the form that needs less time for its waves wins: a pair tile is 4x the work of a
   // single tile on 2 SMs = 2 single-tile times, divided by the measured per-tile gain of the pair form (LAMM_GEMM_PAIR=2:
@@ -706,11 +793,11 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
   const int sms = sm_count_cached(), slots = sms / 2;
   const double t_pair = (double)((pairs + slots - 1) / slots) * 2.0 / kSoPairGain;
   const double t_single = (double)((singles + sms - 1) / sms);
-  if (pair_fits && pair_on && p.M > GM && p.N > GN && (pair_on > 1 || t_pair < t_single)) {
+  if ((pair_fits || atm_on) && pair_on && p.M > GM && p.N > GN && (pair_on > 1 || t_pair < t_single)) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * (pairs < slots ? pairs : slots));         // persistent: one pair per TPC walks the tiles
     cfg.blockDim = dim3(kSoThreads);
-    cfg.dynamicSmemBytes = smem_pair;
+    cfg.dynamicSmemBytes = atm_on ? smem_atm : smem_pair;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -719,8 +806,14 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    if (p.n_peer) e = cudaLaunchKernelEx(&cfg, gemm_so_kernel<WT, true, true>, tm_w, tm_xh, tm_xl, tm_sh, p);
-    else e = cudaLaunchKernelEx(&cfg, gemm_so_kernel<WT, false, true>, tm_w, tm_xh, tm_xl, tm_sh, p);
+    if (atm_on) {
+      if (p.n_peer) e = cudaLaunchKernelEx(&cfg, gemm_so_kernel<WT, true, true, true>, tm_w, tm_xh, tm_xl, tm_sh, p);
+      else e = cudaLaunchKernelEx(&cfg, gemm_so_kernel<WT, false, true, true>, tm_w, tm_xh, tm_xl, tm_sh, p);
+    } else if (p.n_peer) {
+      e = cudaLaunchKernelEx(&cfg, gemm_so_kernel<WT, true, true>, tm_w, tm_xh, tm_xl, tm_sh, p);
+    } else {
+      e = cudaLaunchKernelEx(&cfg, gemm_so_kernel<WT, false, true>, tm_w, tm_xh, tm_xl, tm_sh, p);
+    }
   } else {
     const int grid = singles < sms ? singles : sms;                    // persistent: one CTA per SM walks the tiles
     if (p.n_peer) gemm_so_kernel<WT, true, false><<<grid, kSoThreads, smem, st>>>(tm_w, tm_xh, tm_xl, tm_sh, p);

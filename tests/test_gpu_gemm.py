@@ -83,6 +83,44 @@ def test_gemm_llama_shapes_sampled(gpu, oracle, t):
             assert np.array_equal(got2, 4 * got)
 
 
+PAIR_FORMS = [("0", None), ("2", "0"), ("2", "1")]      # (LAMM_GEMM_PAIR, LAMM_GEMM_ATM)
+
+
+@pytest.mark.parametrize("form", PAIR_FORMS, ids=["single", "pair-smem", "pair-tmem"])
+@pytest.mark.parametrize("t", TC_TYPES)
+def test_gemm_every_form_on_ragged_shapes(gpu, oracle, t, form, gemm_mode):
+    """The scaled-operand GEMM has three forms -- single CTA, CTA pair with the unpacked weights in shared memory, CTA
+    pair with them in tensor memory -- and the launcher picks by wave count, so small shapes only ever see the first.
+    Both knobs are read per call: force each form on shapes whose last tiles are ragged in M and N (a pair whose peer
+    CTA lies wholly beyond M; N tails of 1 and 255 columns; several tiles per pair so the rings and the accumulator
+    hand-off wrap) and compare with the oracle; the forms must also agree with each other to summation-order noise."""
+    import os
+    if gemm_mode == "exact":
+        pytest.skip("forms of the scaled-operand kernel")
+    pair, atm = form
+    old = {k_: os.environ.get(k_) for k_ in ("LAMM_GEMM_PAIR", "LAMM_GEMM_ATM")}
+    os.environ["LAMM_GEMM_PAIR"] = pair
+    if atm is not None:
+        os.environ["LAMM_GEMM_ATM"] = atm
+    try:
+        # the last shape is 10 x 9 = 90 pair tiles on 74 pair slots: some pairs walk two tiles (oracle on a row sample)
+        for (m, n, k) in [(300, 260, 512), (129, 129, 256), (257, 511, 1024), (640, 257, 768), (2500, 2100, 256)]:
+            w = weights(oracle, t, m, k, seed=m + n)
+            rng = np.random.default_rng(m * 7 + n)
+            x = make_x(rng, n, k)
+            rows = np.arange(m) if m < 1000 else np.unique(np.r_[0:3, 255:258, m - 3:m, rng.integers(0, m, 40)])
+            want = oracle.mul_mat(t, w[rows], x)
+            got = gpu.mul_mat(t, dev(w), dev(x)).cpu().numpy()[:, rows]
+            err = np.abs(got - want).max()
+            assert err <= tol_c(want, k), f"{TYPE_NAMES[t]} {m}x{n}x{k} form {form}: err {err} tol {tol_c(want, k)}"
+    finally:
+        for k_, v in old.items():
+            if v is None:
+                os.environ.pop(k_, None)
+            else:
+                os.environ[k_] = v
+
+
 def rescale_blocks(t, w, k, scale, rng=None):
     """Multiply the fp16 scale fields (d, and m / dmin where the format has one) of every block by `scale`, in
     fp16 arithmetic, leaving the quants alone; optionally plant one block per row with d = fp16 max and one with

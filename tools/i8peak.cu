@@ -10,6 +10,7 @@
 //  (2) peak: every SM issues `iters` x 4 MMAs (M128 x N256 x K32 for i8, x K16 for f16) on operands that stay
 //      resident in shared memory -- no loads, no drain -- timed with CUDA events over the whole grid:
 //      TOPS = 2 * 128 * 256 * K * 4 * iters * CTAs / time.  Printed as one JSON line per kind.
+//  (3) `i8peak <iters> <seconds>`: the same stream held for seconds -- the SUSTAINED peak under the board's power cap.
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -323,8 +324,55 @@ static int run_kat(const char *name, int a_signed) {
   return bad;
 }
 
+// ---- (3) sustained: the same resident-operand MMA stream for `seconds`, the clock the SMs actually ran at -------------
+// A 1 ms burst runs at the maximum clock; under the board's power cap a long tensor-bound kernel does not.  Launches of
+// ~20 ms back to back; the second half of the run is timed; MHz = clock64 cycles of the slowest CTA / launch time.
+template <int KIND>
+static void run_sustained(const char *name, int sms, double seconds) {
+  const int smem = 16384 + 32768 + 64 + 1024, iters = 80000;
+  CK(cudaFuncSetAttribute(peak_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  unsigned long long *cyc;
+  CK(cudaMalloc(&cyc, sms * 8));
+  cudaEvent_t e0, e1;
+  CK(cudaEventCreate(&e0));
+  CK(cudaEventCreate(&e1));
+  peak_kernel<KIND><<<sms, 128, smem>>>(iters, cyc, 256);
+  CK(cudaDeviceSynchronize());
+  CK(cudaEventRecord(e0));
+  peak_kernel<KIND><<<sms, 128, smem>>>(iters, cyc, 256);
+  CK(cudaEventRecord(e1));
+  CK(cudaEventSynchronize(e1));
+  float ms1;
+  CK(cudaEventElapsedTime(&ms1, e0, e1));
+  const int n = (int)(seconds * 1e3 / ms1 / 2) + 1;
+  for (int i = 0; i < n; i++) peak_kernel<KIND><<<sms, 128, smem>>>(iters, cyc, 256);
+  CK(cudaEventRecord(e0));
+  for (int i = 0; i < n; i++) peak_kernel<KIND><<<sms, 128, smem>>>(iters, cyc, 256);
+  CK(cudaEventRecord(e1));
+  CK(cudaEventSynchronize(e1));
+  float ms;
+  CK(cudaEventElapsedTime(&ms, e0, e1));
+  std::vector<unsigned long long> h(sms);
+  CK(cudaMemcpy(h.data(), cyc, sms * 8, cudaMemcpyDeviceToHost));
+  unsigned long long cmax = 0;
+  for (auto v : h) cmax = v > cmax ? v : cmax;
+  const int K = KIND == 1 ? 32 : 16;
+  const double ops = 2.0 * 128 * 256 * K * 4.0 * iters * sms * n;
+  printf("{\"kind\": \"%s\", \"sustained_s\": %.2f, \"launches\": %d, \"first_launch_ms\": %.3f, \"ms_per_launch\": %.3f, \"tops\": %.1f, "
+         "\"cycles_per_mma\": %.2f, \"sm_mhz_effective\": %.0f}\n",
+         name, ms * 1e-3, n, ms1, ms / n, ops / (ms * 1e-3) / 1e12, (double)cmax / (4.0 * iters), (double)cmax / (ms / n * 1e3));
+  CK(cudaFree(cyc));
+}
+
 int main(int argc, char **argv) {
   int iters = argc > 1 ? atoi(argv[1]) : 4000;
+  if (argc > 2) {                                  // i8peak <iters> <seconds>: sustained legs only
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, 0));
+    run_sustained<0>("f16", prop.multiProcessorCount, atof(argv[2]));
+    run_sustained<1>("i8", prop.multiProcessorCount, atof(argv[2]));
+    return 0;
+  }
   cudaDeviceProp prop;
   CK(cudaGetDeviceProperties(&prop, 0));
   printf("%s, %d SMs, max SM clock %d MHz\n", prop.name, prop.multiProcessorCount, prop.clockRate / 1000);
