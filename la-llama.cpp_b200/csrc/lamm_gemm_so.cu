@@ -111,7 +111,12 @@ __device__ __forceinline__ void store_out(const SoParams &p, int64_t idx, float 
 template <int WT, int kSoAStagesAll, int kSoBStages, bool ATM = false> struct SoSmem {
   static constexpr int kSoAStages = ATM ? 0 : kSoAStagesAll;         // A tiles in shared memory
   static constexpr int BS = type_info(WT).size;
-  static constexpr int kRawRowBytes = 8 * BS;                       // 8 blocks = 256 K elements = 4 stages
+  static constexpr int kRawChunkBytes = 8 * BS;                     // 8 blocks = 256 K elements = 4 stages
+  // Row pitch of the raw chunk in shared memory.  Thread = row reads its row with ld.shared.v4, so the pitch decides the
+  // bank conflicts: 144 / 176 / 272 bytes (Q4_0, Q5_0, Q8_0) are conflict-free, but 160 (Q4_1) is 2-way and 192 (Q5_1)
+  // 4-way (16 wavefronts per load; ncu counted 19 M conflicts per 13B launch).  Those two get a 16-byte pad: the TMA box is
+  // simply 16 bytes wider (it reads into the next chunk, or gets zeros past the row's end), 176 / 208-byte pitch.
+  static constexpr int kRawRowBytes = kRawChunkBytes + ((kRawChunkBytes / 16) % 2 == 0 ? 16 : 0);
   static constexpr int kRawBytes = GM * kRawRowBytes;
   static constexpr bool kMin = (WT == LAMMCU_TYPE_Q4_1 || WT == LAMMCU_TYPE_Q5_1);
   static constexpr int kAhOff = 0;
@@ -326,7 +331,7 @@ gemm_so_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
             const int ms = st >> 2;
             mbar_wait(raw_empty, ((uint32_t)gchunk & 1u) ^ 1u);
             mbar_arrive_expect_tx(raw_full, (uint32_t)L::kRawBytes);
-            tma_load_2d(smem + L::kRawOff, &tm_w, ms * (L::kRawRowBytes / 2), m0, raw_full);
+            tma_load_2d(smem + L::kRawOff, &tm_w, ms * (L::kRawChunkBytes / 2), m0, raw_full);
             gchunk++;
           }
           if (ext_before(st)) {
@@ -777,13 +782,13 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
   // (read per call, like LAMM_GEMM_ATM below: tests force each form on ragged shapes in one process)
   const char *pair_env = getenv("LAMM_GEMM_PAIR");
   const int pair_on = pair_env ? atoi(pair_env) : 1;
-  // Unpacked weight tiles of the pair form in TENSOR MEMORY (ATM) or in shared memory.  Measured at 13B N = 2048
-  // (profiles/r2bc, r2bd): ATM draws less power (1582 vs 1485 MHz under the cap) but needs more cycles per tile (one
-  // accumulator: the epilogue is exposed; tcgen05.st + wait::st sit in the unpack chain) -- Q4_1 492 vs 511 TOPS, Q4_0 501
-  // vs 522, Q8_0 483 vs 501, but Q5_1 483 vs 463 (its shared-memory form has the largest raw ring and the heaviest unpack).
-  // Default: ATM for Q5_1 only; LAMM_GEMM_ATM=0 / 1 forces the form (read per call, so one process can compare both).
+  // Unpacked weight tiles of the pair form in TENSOR MEMORY (ATM, opt-in) or in shared memory (default).  Measured at
+  // 13B N = 2048 (profiles/r2bc, r2bd, r2bh): ATM halves the shared-memory traffic and draws less power (1582 vs 1485 MHz
+  // under the cap) but needs more cycles per tile (ONE accumulator: the epilogue is exposed; tcgen05.st + wait::st sit in
+  // the unpack chain) -- Q4_1 499 vs 527 TOPS, Q4_0 501 vs 522, Q8_0 491 vs 514, Q5_1 491 vs 512 (it led Q5_1 only while
+  // that format's raw rows were 4-way bank-conflicted).  LAMM_GEMM_ATM=1 selects it (read per call: tests run both).
   const char *atm_env = getenv("LAMM_GEMM_ATM");
-  const int atm_on = atm_env ? (atoi(atm_env) != 0) : (WT == LAMMCU_TYPE_Q5_1 || !pair_fits);
+  const int atm_on = atm_env ? (atoi(atm_env) != 0) : !pair_fits;
   cudaError_t e;
   // no persistent scheduler yet, so the form that needs less time for its waves wins: a pair tile is 4x the work of a
   // single tile on 2 SMs = 2 single-tile times, divided by the measured per-tile gain of the pair form (LAMM_GEMM_PAIR=2:
@@ -828,6 +833,17 @@ static int launch_so(const CUtensorMap &tm_w, const CUtensorMap &tm_xh, const CU
   return LAMMCU_OK;
 }
 
+// box width of the raw-weight tensor map = the shared-memory row pitch of the kernel's raw chunk (SoSmem::kRawRowBytes)
+static int so_raw_row_bytes(int w_type) {
+  switch (w_type) {
+  case LAMMCU_TYPE_Q4_0: return SoSmem<LAMMCU_TYPE_Q4_0, 2, 3>::kRawRowBytes;
+  case LAMMCU_TYPE_Q4_1: return SoSmem<LAMMCU_TYPE_Q4_1, 2, 3>::kRawRowBytes;
+  case LAMMCU_TYPE_Q5_0: return SoSmem<LAMMCU_TYPE_Q5_0, 2, 3>::kRawRowBytes;
+  case LAMMCU_TYPE_Q5_1: return SoSmem<LAMMCU_TYPE_Q5_1, 2, 3>::kRawRowBytes;
+  default:               return SoSmem<LAMMCU_TYPE_Q8_0, 2, 3>::kRawRowBytes;
+  }
+}
+
 size_t gemm_so_ws_bytes(int64_t M, int64_t N, int64_t K) {
   const int64_t npad = (N + GN - 1) / GN * GN, kbpad = (K / 32 + 63) / 64 * 64, mpad = (M + GM - 1) / GM * GM;
   return (size_t)(2 * npad * K * 2 + npad * kbpad * 2 + npad * 4 + mpad * 4 + 1024);
@@ -854,7 +870,7 @@ int launch_gemm_so(int w_type, const void *w, int64_t w_stride, const void *xq, 
   CUtensorMap tm_w, tm_xh, tm_xl, tm_sh;
   // raw weights as uint16 [M][row_bytes / 2], box = 8 blocks x 128 rows
   rc = make_map_2d(&tm_w, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, w, (uint64_t)(kb * ti.size / 2), (uint64_t)M,
-                   (uint64_t)w_stride, (uint32_t)(4 * ti.size), GM, CU_TENSOR_MAP_SWIZZLE_NONE);
+                   (uint64_t)w_stride, (uint32_t)(so_raw_row_bytes(w_type) / 2), GM, CU_TENSOR_MAP_SWIZZLE_NONE);
   if (rc) return rc;
   rc = make_map_2d(&tm_xh, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, xh, (uint64_t)K, (uint64_t)npad, (uint64_t)K * 2, GK, GN,
                    CU_TENSOR_MAP_SWIZZLE_128B);
