@@ -913,6 +913,8 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
     assert all(ops[i][2] == H for i in same_as_prev)      # every repeated row of this chain has K = H
     h2d = int(h2d_all - reused * H * 4)                   # (the first job of a new server instance always sends its row)
     phases["x_rows_reused_per_step"] = round(reused, 2)
+    # calls answered by a job posted ahead of them (sibling speculation: the weight and the row were the predicted ones)
+    phases["calls_answered_by_speculative_job_per_step"] = round(prof[7] / max(steps, 1), 2)
     d2h = sum((shard(m)[1] - shard(m)[0]) * 4 for _, m, k in ops)
     return {"value": steps / sec, "unit": "tok/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "steps": steps, "ms_per_step": sec / steps * 1e3, "per_call_phases": phases,
@@ -922,7 +924,10 @@ def e2e_run(torch, L, t, ops, weights, shard, steps, dist, dev, rank, world):
                    % (int(lib.lammcu_get_host_mode()),
                       "jobs posted to the resident decode server: X pulled from pinned host memory by the kernel, "
                       "C written back as tagged pairs the caller polls; wq/wk/wv and gate/up get the same src1 "
-                      "tensor as in ggml's graph, and a row bit-identical to the previous call's is sent once"
+                      "tensor as in ggml's graph, and a row bit-identical to the previous call's is sent once; the jobs "
+                      "of the weights that followed a weight with the same row on the previous token are posted behind "
+                      "its job (LAMM_SERVER_SPEC), and a call is answered from such a job only if it is for that weight "
+                      "and its row memcmp-equals the job's"
                       if lib.lammcu_get_host_mode() == 1 else
 
                       "copy-engine H2D + one launch + stream synchronize per call"),

@@ -382,7 +382,8 @@ int lammcu_mul_mat_host(lammcu_weight_t w, const float *x_host, int64_t N,
 /* Diagnostics: accumulated host-path phase times in microseconds since the last reset:
  * [0] x memcpy to pinned, [1] H2D enqueue, [2] kernel enqueue, [3] wait for completion,
  * [4] C memcpy from pinned, [5] number of calls, [6] calls whose activation row was not sent
- * because it equalled the previous call's (host mode 1).                                 */
+ * because it equalled the previous call's (host mode 1), [7] calls answered by a job that was
+ * posted ahead of them (sibling speculation, LAMM_SERVER_SPEC).                           */
 void lammcu_host_profile(double *out8, int reset);
 /* How lammcu_mul_mat_host (and lamm_mul_mat above it) runs a decode-sized (N == 1) call:
  *   0  copy-engine H2D of X, one kernel launch, zero-copy f32 result in pinned memory,
@@ -395,7 +396,11 @@ void lammcu_host_profile(double *out8, int reset);
  *      first.  lammcu_host_quiesce() stops it explicitly (e.g. before timing unrelated GPU work).
  *      Consecutive calls with a bit-identical activation row (ggml gives q/k/v and gate/up the same
  *      src1) send it once: the later jobs reuse the quantized row the resident instance still holds
- *      (memcmp against the pinned copy; LAMM_SERVER_X_REUSE=0 turns this off).
+ *      (memcmp against the pinned copy; LAMM_SERVER_X_REUSE=0 turns this off).  The path also
+ *      learns which weight was called next with the same row and posts that weight's job behind
+ *      the current one (up to two followers; mailbox and result buffers are rings of 4): the
+ *      following call is answered from it only if it is for that weight and its row memcmp-equals
+ *      the job's; anything else is posted normally (LAMM_SERVER_SPEC=0 turns this off).
  * Results are bit-identical in both modes.  Environment override at load time: LAMM_HOST_MODE.  */
 int lammcu_set_host_mode(int mode);
 int lammcu_get_host_mode(void);

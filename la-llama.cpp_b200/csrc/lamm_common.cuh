@@ -162,12 +162,17 @@ struct ShardInfo {
 };
 // resident decode server (lamm_decode.cu): jobs arrive through a mailbox in pinned host memory
 constexpr int kSrvWords = 16;      // 32-bit words of a job, each posted as a {word, tag} pair
+// The mailbox and the result buffer are RINGS of kSrvSlots entries indexed by (job tag % kSrvSlots): the host may post
+// the jobs it expects next (the siblings of a q/k/v or gate/up group, which reuse the staged activation row) together
+// with the one it is waiting for; CTA 0 picks all of them up in ONE PCIe read and the grid runs them back to back.
+constexpr int kSrvSlots = 4;
 struct ServerParams {
-  const unsigned long long *mbox_host;   // pinned: kSrvWords pairs written by the CPU
+  const unsigned long long *mbox_host;   // pinned: kSrvSlots x kSrvWords pairs written by the CPU
   unsigned long long *mbox_dev;          // device: the same pairs, republished by CTA 0
   const float *x_host;                   // pinned: activation row of the current job
   unsigned long long *x_ll;              // device: the row as {value, tag} pairs
-  unsigned long long *c_ll_host;         // pinned: the result as {value, tag} pairs
+  unsigned long long *c_ll_host;         // pinned: kSrvSlots result buffers of {value, tag} pairs
+  unsigned int c_slot_pairs;             // pairs per result buffer
   volatile unsigned int *done_host;      // pinned: [1] tag the server gave up waiting for
   unsigned int *status;                  // device: set on a poll time-out
   unsigned int seq0;                     // first job tag this launch serves

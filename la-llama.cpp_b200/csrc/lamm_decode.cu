@@ -1218,33 +1218,76 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
   const int bid = blockIdx.x;
   unsigned long long t_launch;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_launch));
+  // CTA 0: pre_tag[slot] = tag of a job it has ALREADY republished into that device slot while accepting an earlier one
+  __shared__ unsigned int pre_tag[kSrvSlots];
+  if (tid < kSrvSlots) pre_tag[tid] = 0u;
+  __syncthreads();
   for (unsigned int s = sp.seq0;; ++s) {
     // ---- 1. the job
+    const int slot = (int)(s % (unsigned int)kSrvSlots);
     if (warp == 0) {
-      const unsigned long long *src = bid == 0 ? sp.mbox_host : sp.mbox_dev;
+      const bool pre = bid == 0 && pre_tag[slot] == s;     // accepted with an earlier job: in the device mailbox already
       unsigned long long v = 0, t0, now;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-      // bounded lifetime: a caller that never pauses must not starve kernels queued on other streams
-      bool give_up = bid == 0 && s != sp.seq0 && t0 - t_launch > (unsigned long long)sp.life_ns;
-      while (!give_up) {
-        if (lane < kSrvWords) asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(src + lane) : "memory");
-        if (__all_sync(0xffffffffu, lane >= kSrvWords || (unsigned int)(v >> 32) == s)) break;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-        if (bid == 0) {
-          if (now - t0 > (unsigned long long)sp.idle_ns) { give_up = true; break; }
+      if (bid == 0 && !pre) {
+        // The host mailbox, all kSrvSlots x 16 pairs per poll (one PCIe round trip either way): lane l holds pair l of
+        // slots 0/1 (v0) and of slots 2/3 (v1).  Bounded lifetime: a caller that never pauses must not starve kernels
+        // queued on other streams -- but a job that was republished is never given up (the other CTAs run it).
+        bool give_up = s != sp.seq0 && t0 - t_launch > (unsigned long long)sp.life_ns;
+        unsigned long long v0 = 0, v1 = 0;
+        auto slot_full = [&](unsigned int tag_, int sl) {
+          const unsigned int m0 = __ballot_sync(0xffffffffu, (unsigned int)(v0 >> 32) == tag_);
+          const unsigned int m1 = __ballot_sync(0xffffffffu, (unsigned int)(v1 >> 32) == tag_);
+          return (((sl < 2 ? m0 : m1) >> ((sl & 1) * 16)) & 0xffffu) == 0xffffu;
+        };
+        while (!give_up) {
+          asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v0) : "l"(sp.mbox_host + lane) : "memory");
+          asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v1) : "l"(sp.mbox_host + 32 + lane) : "memory");
+          if (slot_full(s, slot)) break;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+          give_up = __any_sync(0xffffffffu, now - t0 > (unsigned long long)sp.idle_ns);   // one decision for the warp
+        }
+        const int sl0 = lane >> 4, sl1 = 2 + (lane >> 4);      // slots of this lane's two pairs
+        if (give_up) {
+          v = ((unsigned long long)s << 32) | ((lane & 15) == 0 ? 2u : 0u);
+          if (sl0 == slot || sl1 == slot) {
+            jw[lane & 15] = (unsigned int)v;
+            asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + slot * kSrvWords + (lane & 15)), "l"(v) : "memory");
+          }
+          if (lane == 0) {
+            sp.done_host[1] = s;
+            __threadfence_system();
+          }
         } else {
+          // this job, and the next two if the same read found them complete (their slots were free: the host posts a
+          // tag only after the job kSrvSlots before it has been answered)
+          unsigned int pub = 1u << slot;
+#pragma unroll
+          for (int d = 1; d <= 2; d++) {
+            const int sl = (slot + d) % kSrvSlots;
+            if (slot_full(s + (unsigned int)d, sl)) {
+              pub |= 1u << sl;
+              if (lane == 0) pre_tag[sl] = s + (unsigned int)d;
+            }
+          }
+          if ((pub >> sl0) & 1u) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + lane), "l"(v0) : "memory");
+          if ((pub >> sl1) & 1u) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + 32 + lane), "l"(v1) : "memory");
+          if (sl0 == slot) jw[lane & 15] = (unsigned int)v0;
+          if (sl1 == slot) jw[lane & 15] = (unsigned int)v1;
+        }
+      } else {
+        // every other CTA (and CTA 0 for a job it republished earlier): the device slot, in L2
+        const unsigned long long *src = sp.mbox_dev + slot * kSrvWords;
+        bool give_up = false;
+        while (true) {
+          if (lane < kSrvWords) asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(src + lane) : "memory");
+          if (__all_sync(0xffffffffu, lane >= kSrvWords || (unsigned int)(v >> 32) == s)) break;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
           __nanosleep(40);
           if (now - t0 > 4000000000ull) { give_up = true; *sp.status = 2u; break; }   // CTA 0 always publishes something
         }
-      }
-      if (give_up) v = ((unsigned long long)s << 32) | (lane == 0 ? 2u : 0u);
-      if (lane < kSrvWords) {
-        jw[lane] = (unsigned int)v;
-        if (bid == 0) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + lane), "l"(v) : "memory");
-      }
-      if (bid == 0 && give_up && lane == 0) {
-        sp.done_host[1] = s;
-        __threadfence_system();
+        if (give_up) v = ((unsigned long long)s << 32) | (lane == 0 ? 2u : 0u);
+        if (lane < kSrvWords) jw[lane] = (unsigned int)v;
       }
     }
     __syncthreads();
@@ -1300,7 +1343,7 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
     {
       const int lo = vb * R, n = (jw[14] && bid == 0) ? 0 : max(0, min(jp.M, lo + R) - lo);
       const unsigned long long th = (unsigned long long)s << 32;
-      unsigned long long *dst = sp.c_ll_host + lo;
+      unsigned long long *dst = sp.c_ll_host + (size_t)slot * sp.c_slot_pairs + lo;
       for (int i = 2 * tid; i < n; i += 2 * (int)blockDim.x) {
         const unsigned long long a = th | __float_as_uint(cs[i]);
         if (i + 1 < n) {

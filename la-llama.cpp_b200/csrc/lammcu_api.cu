@@ -128,7 +128,9 @@ static unsigned int g_srv_life_us = [] {
 static const int g_srv_x_reuse = [] { const char *e = getenv("LAMM_SERVER_X_REUSE"); return e ? atoi(e) : 1; }();
 
 constexpr size_t kSrvMaxK = 1 << 16;         // floats in the pinned activation row
-constexpr size_t kSrvMaxM = 1 << 18;         // floats in the result buffers
+constexpr size_t kSrvMaxM = 1 << 18;         // floats in each of the kSrvSlots result buffers
+// 1 (default): after a job, also post the jobs of the weights that followed it with the same row last time
+static const int g_srv_spec = [] { const char *e = getenv("LAMM_SERVER_SPEC"); return e ? atoi(e) : 1; }();
 
 struct ServerState {
   bool ready = false;        // buffers allocated
@@ -143,8 +145,21 @@ struct ServerState {
   unsigned long long *mbox_dev = nullptr, *x_ll = nullptr;
   unsigned int *ctrs = nullptr;                    // [2] status
   unsigned long long *trace = nullptr;             // LAMM_SERVER_TRACE=1: [64][8] device time stamps
+  // speculative sibling jobs posted behind the last real job, in tag order (see mul_mat_host_server)
+  struct { unsigned int tag; lammcu_weight *w; } spec[2];
+  int n_spec = 0;
+  lammcu_weight *prev_w = nullptr;                 // weight of the previous call (sibling learning)
+  unsigned long long prev_gen = 0;
+  int64_t row_k = 0;                               // K of the row that x_host holds (whatever instance saw it)
+  unsigned int launch_seq0 = 0;                    // first tag of the instance believed to be resident
 };
+
 static ServerState g_srv;
+// The resident instance has exited (idle / lifetime) iff it left the tag it gave up waiting for: tags only grow and a
+// new instance always starts above the previous one's exit tag.
+static bool server_exited() { return g_srv.done[1] != 0u && (int)(g_srv.done[1] - g_srv.launch_seq0) >= 0; }
+// ... and it never served job s
+static bool server_missed(unsigned int s) { return server_exited() && (int)(s - g_srv.done[1]) >= 0; }
 
 extern "C" { static void server_stop(); }
 
@@ -157,11 +172,17 @@ struct lammcu_weight {
   size_t bytes;
   int refs;             // explicit holders (lammcu_weight_register); entries made by the operator path have 0
   bool detached;        // evicted from the registry while held: freed by the last lammcu_weight_release
+  // resident-server host path: the weight whose call FOLLOWED this one's with a bit-identical activation row last time
+  // (ggml hands wq/wk/wv one src1, gate/up another); valid while sib_gen == g_weight_gen
+  lammcu_weight *sib = nullptr;
+  unsigned long long sib_gen = 0;
 };
+static unsigned long long g_weight_gen = 1;   // bumped whenever a weight may have gone away: every sibling link dies
 static std::map<const void *, lammcu_weight *> g_weights;
 
 // drop an entry from the registry (g_mu held): freed now, or by its last holder's release
 static void evict_entry(lammcu_weight *h) {
+  g_weight_gen++;
   if (h->refs > 0) { h->detached = true; return; }
   cudaFree(h->dev);
   delete h;
@@ -1071,11 +1092,13 @@ static unsigned int g_srv_idle_us = [] {
 static int server_setup() {
   if (g_srv.ready) return LAMMCU_OK;
   void *p = nullptr;
-  CU_TRY(cudaMallocHost(&p, 256));                   g_srv.mbox = (volatile unsigned long long *)p;
+  constexpr size_t kMboxBytes = (size_t)kSrvSlots * kSrvWords * 8;
+  static_assert(kSrvSlots == 4 && kSrvWords == 16, "decode_server_kernel reads the mailbox as 2 x 32 pairs");
+  CU_TRY(cudaMallocHost(&p, kMboxBytes));            g_srv.mbox = (volatile unsigned long long *)p;
   CU_TRY(cudaMallocHost(&p, kSrvMaxK * 4));          g_srv.x_host = (float *)p;
-  CU_TRY(cudaMallocHost(&p, kSrvMaxM * 8));          g_srv.c_ll = (volatile unsigned long long *)p;
+  CU_TRY(cudaMallocHost(&p, kSrvSlots * kSrvMaxM * 8));  g_srv.c_ll = (volatile unsigned long long *)p;
   CU_TRY(cudaMallocHost(&p, 256));                   g_srv.done = (volatile unsigned int *)p;
-  CU_TRY(cudaMalloc(&p, 256));                       g_srv.mbox_dev = (unsigned long long *)p;
+  CU_TRY(cudaMalloc(&p, kMboxBytes));                g_srv.mbox_dev = (unsigned long long *)p;
   CU_TRY(cudaMalloc(&p, kSrvMaxK * 8));              g_srv.x_ll = (unsigned long long *)p;
   CU_TRY(cudaMalloc(&p, 256));                       g_srv.ctrs = (unsigned int *)p;
   if (getenv("LAMM_SERVER_TRACE")) {
@@ -1083,10 +1106,10 @@ static int server_setup() {
     g_srv.trace = (unsigned long long *)p;
     CU_TRY(cudaMemset(p, 0, 64 * 8 * 8));
   }
-  memset((void *)g_srv.mbox, 0, 256);                // tag 0 is never issued
+  memset((void *)g_srv.mbox, 0, kMboxBytes);         // tag 0 is never issued
   memset((void *)g_srv.done, 0, 256);
-  memset((void *)g_srv.c_ll, 0, kSrvMaxM * 8);
-  CU_TRY(cudaMemset(g_srv.mbox_dev, 0, 256));
+  memset((void *)g_srv.c_ll, 0, kSrvSlots * kSrvMaxM * 8);
+  CU_TRY(cudaMemset(g_srv.mbox_dev, 0, kMboxBytes));
   CU_TRY(cudaMemset(g_srv.x_ll, 0, kSrvMaxK * 8));
   CU_TRY(cudaMemset(g_srv.ctrs, 0, 256));
   CU_TRY(cudaDeviceSynchronize());
@@ -1095,31 +1118,47 @@ static int server_setup() {
   return LAMMCU_OK;
 }
 
-static void server_post(const unsigned int *words) {
-  const unsigned int s = ++g_srv.seq;
+// Post `n` jobs under the next n tags (slot = tag % kSrvSlots).  The LAST one is written first and the first one last:
+// the poll that finds the job the server is waiting for then finds its followers too and accepts them in the same
+// PCIe round trip.  Tags validate each slot, so a poll that lands between two writes only misses the look-ahead.
+static void server_post_n(const unsigned int (*words)[kSrvWords], int n) {
+  const unsigned int s0 = g_srv.seq + 1;
+  g_srv.seq += (unsigned int)n;
   __atomic_thread_fence(__ATOMIC_RELEASE);           // X (and everything before) is visible before the job
-  for (int i = 0; i < kSrvWords; i++) g_srv.mbox[i] = ((unsigned long long)s << 32) | words[i];
-  __atomic_thread_fence(__ATOMIC_RELEASE);
+  for (int j = n - 1; j >= 0; j--) {
+    const unsigned int s = s0 + (unsigned int)j;
+    volatile unsigned long long *slot = g_srv.mbox + (size_t)(s % kSrvSlots) * kSrvWords;
+    for (int i = 0; i < kSrvWords; i++) slot[i] = ((unsigned long long)s << 32) | words[j][i];
+    __atomic_thread_fence(__ATOMIC_RELEASE);
+  }
+}
+static void server_post(const unsigned int *words) {
+  unsigned int one[1][kSrvWords];
+  memcpy(one[0], words, sizeof(one[0]));
+  server_post_n(one, 1);
 }
 
-static int server_launch(int type) {
+static int server_launch(int type, unsigned int seq0) {
   ServerParams sp = {};
   sp.mbox_host = (const unsigned long long *)g_srv.mbox;
   sp.mbox_dev = g_srv.mbox_dev;
   sp.x_host = g_srv.x_host;
   sp.x_ll = g_srv.x_ll;
   sp.c_ll_host = (unsigned long long *)g_srv.c_ll;
+  sp.c_slot_pairs = (unsigned int)kSrvMaxM;
   sp.done_host = g_srv.done;
   sp.status = g_srv.ctrs + 2;
-  sp.seq0 = g_srv.seq;                               // the job just posted
+  sp.seq0 = seq0;                                    // the job the caller is waiting for
   sp.idle_ns = g_srv_idle_us * 1000u;
   sp.life_ns = g_srv_life_us * 1000u;
   sp.trace = g_srv.trace;
   int rc = launch_decode_server(type, sp, g_dev.stream);
   if (rc) return rc;
   g_srv.running = true;
+  g_srv.launch_seq0 = seq0;
   g_srv.type = type;
   g_srv.x_k = 0;                                     // a fresh instance has nothing staged
+  g_srv.n_spec = 0;                                  // ... and never looks at older tags
   return LAMMCU_OK;
 }
 
@@ -1166,37 +1205,101 @@ static void server_stop() {
   server_post(words);
   cudaStreamSynchronize(g_dev.stream);
   g_srv.running = false;
+  g_srv.n_spec = 0;
+  g_srv.prev_w = nullptr;
 }
 
 // N == 1, operands the decode kernel takes
+//
+// SIBLING SPECULATION (LAMM_SERVER_SPEC=1, default).  ggml calls wq, wk, wv with one src1 and gate, up with another, one
+// synchronous lamm_mul_mat after the other; each costs a job hand-over (PCIe poll, republish, result write-back) of
+// several microseconds around ~2 us of streaming.  The path learns, per weight, which weight was called NEXT with a
+// bit-identical row (w->sib); the next time that weight is called it posts the jobs of up to two predicted followers
+// behind its own, flagged "row unchanged" (they reuse the quantized row in the CTAs' shared memory), so the server runs
+// them back to back while the host is still copying the first result out.  A following call is a HIT when it is for
+// the predicted weight AND its row memcmp-equals the row those jobs used: it only collects the result.  Anything else
+// is a miss: the speculative results are ignored (their jobs still run, a few microseconds of device time) and the
+// call is posted normally.  Results are the same bits either way: same kernel, same weights, same quantized row.
 static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_host) {
   const int64_t K = w->K, rows = w->row_end - w->row_begin;
   int rc = server_setup();
   if (rc) return rc;
-  unsigned int words[kSrvWords];
+  if ((size_t)rows > kSrvMaxM || (size_t)K > kSrvMaxK) { set_error("mul_mat_host: shape too large for the server buffers"); return LAMMCU_ERR_SHAPE; }
+  unsigned int jobs[3][kSrvWords];
+  unsigned int *words = jobs[0];
   if ((rc = decode_server_job(w->type, w->dev, w->stride, rows, K, words))) return rc;
   if (g_srv.running && g_srv.type != w->type) server_stop();
+  if (g_srv.running && server_exited()) {            // it idled out (or reached its lifetime) since the last call
+    g_srv.running = false;
+    g_srv.n_spec = 0;
+    g_srv.x_k = 0;
+    // it left an EXIT word under the tag it was waiting for in the device mailbox: never issue that tag again, a new
+    // instance's CTAs would take the stale word for their first job
+    if ((int)(g_srv.done[1] - g_srv.seq) > 0) g_srv.seq = g_srv.done[1];
+  }
   const double t0 = now_us();
   // ggml hands q/k/v (and gate/up) the same src1: when this row is bit-identical to the one the running
   // instance answered last, its quantized copy is still in every CTA's shared memory and the job only
   // says so (word 15) -- no copy to pinned memory, no PCIe pull, no quantize.  A job that ends up on a
   // new instance (below) always carries the row.
-  const bool same = g_srv_x_reuse && g_srv.running && g_srv.x_k == K && memcmp(g_srv.x_host, x_host, (size_t)K * 4) == 0;
-  if (!same) memcpy(g_srv.x_host, x_host, (size_t)K * 4);
-  words[15] = same ? 1u : 0u;
-  g_srv.x_k = 0;
-  const double t1 = now_us();
-  server_post(words);
-  unsigned int s = g_srv.seq;
-  // An instance that gave up waiting for tag s has left an EXIT word with that tag in the device
-  // mailbox: the job is re-posted under a fresh tag before a new instance is launched.
-  if (g_srv.running && g_srv.done[1] == s) {
-    g_srv.running = false;
-    words[15] = 0u;
-    server_post(words);
-    s = g_srv.seq;
+  const bool row_eq = g_srv_x_reuse && g_srv.row_k == K && memcmp(g_srv.x_host, x_host, (size_t)K * 4) == 0;
+  const bool same = row_eq && g_srv.running && g_srv.x_k == K;
+  // learn: the previous call's weight was followed by this one with the same row (or not)
+  if (g_srv.prev_w && g_srv.prev_gen == g_weight_gen) {
+    g_srv.prev_w->sib = row_eq ? w : nullptr;
+    g_srv.prev_w->sib_gen = g_weight_gen;
   }
-  if (!g_srv.running && (rc = server_launch(w->type))) return rc;
+  g_srv.prev_w = w;
+  g_srv.prev_gen = g_weight_gen;
+  unsigned int s = 0;
+  bool hit = false;
+  if (g_srv.n_spec > 0) {
+    if (same && g_srv.spec[0].w == w) {
+      hit = true;                                    // the job is already posted (possibly already answered)
+      s = g_srv.spec[0].tag;
+      g_srv.spec[0] = g_srv.spec[1];
+      g_srv.n_spec--;
+    } else {
+      g_srv.n_spec = 0;                              // mispredicted: whatever those jobs produce is ignored
+    }
+  }
+  const double t1 = now_us();
+  if (!hit) {
+    if (!row_eq) {
+      memcpy(g_srv.x_host, x_host, (size_t)K * 4);
+      g_srv.row_k = K;
+    }
+    words[15] = same ? 1u : 0u;
+    g_srv.x_k = 0;
+    // the followers this weight had last time (same type / K: they reuse the staged row and the shared-memory plan)
+    int n = 1;
+    if (g_srv_spec && g_srv_x_reuse && g_srv.running) {
+      lammcu_weight *v = w;
+      while (n < 3) {
+        lammcu_weight *nx = (v->sib && v->sib_gen == g_weight_gen) ? v->sib : nullptr;
+        if (!nx || nx->type != w->type || nx->K != K || (size_t)(nx->row_end - nx->row_begin) > kSrvMaxM) break;
+        if (decode_server_job(nx->type, nx->dev, nx->stride, nx->row_end - nx->row_begin, K, jobs[n])) break;
+        jobs[n][15] = 1u;
+        g_srv.spec[n - 1].w = nx;
+        v = nx;
+        n++;
+      }
+    }
+    server_post_n(jobs, n);
+    s = g_srv.seq - (unsigned int)(n - 1);
+    for (int j = 1; j < n; j++) g_srv.spec[j - 1].tag = s + (unsigned int)j;
+    g_srv.n_spec = n - 1;
+    // An instance that gave up waiting for tag s has left an EXIT word with that tag in the device
+    // mailbox: the job is re-posted under a fresh tag before a new instance is launched.
+    if (g_srv.running && server_missed(s)) {
+      g_srv.running = false;
+      g_srv.n_spec = 0;
+      words[15] = 0u;
+      server_post(words);
+      s = g_srv.seq;
+    }
+    if (!g_srv.running && (rc = server_launch(w->type, s))) return rc;
+  }
   const double t2 = now_us();
   // the result arrives as {value, tag} pairs, chunk by chunk: take what is there, spin on the rest
   float *out = c_host + w->row_begin;
@@ -1204,16 +1307,18 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
   unsigned int spins = 0;
   double t_first = 0;
   while (true) {
-    got += ll_take(g_srv.c_ll + got, (size_t)rows - got, s, out + got);
+    const volatile unsigned long long *buf = g_srv.c_ll + (size_t)(s % kSrvSlots) * kSrvMaxM;
+    got += ll_take(buf + got, (size_t)rows - got, s, out + got);
     if (got == (size_t)rows) break;
     __builtin_ia32_pause();
     asm volatile("" ::: "memory");                                      // re-read the pairs
-    if (g_srv.done[1] == s) {                                           // the idle exit raced with the post
-      words[15] = 0u;
+    if (server_missed(s)) {                                             // the idle / lifetime exit raced with the post
+      g_srv.n_spec = 0;
+      words[15] = 0u;                                                   // (x_host holds this row: a hit implies row_eq)
       server_post(words);
       s = g_srv.seq;
       got = 0;
-      if ((rc = server_launch(w->type))) return rc;
+      if ((rc = server_launch(w->type, s))) return rc;
       continue;
     }
     if ((++spins & 0x3fffu) == 0) {
@@ -1222,6 +1327,7 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
       else if (now - t_first > 5e6) {
         cudaError_t e = cudaStreamSynchronize(g_dev.stream);
         g_srv.running = false;
+        g_srv.n_spec = 0;
         set_error("mul_mat_host: the decode server did not answer job %u (row %zu of %lld, %s)", s, got,
                   (long long)rows, cudaGetErrorString(e));
         return LAMMCU_ERR_CUDA;
@@ -1230,7 +1336,8 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
   }
   const double t3 = now_us();
   g_srv.x_k = K;                                     // the instance that answered holds this row
-  g_hp[0] += t1 - t0;  g_hp[2] += t2 - t1;  g_hp[3] += t3 - t2;  g_hp[5] += 1;  g_hp[6] += words[15];
+  g_hp[0] += t1 - t0;  g_hp[2] += t2 - t1;  g_hp[3] += t3 - t2;  g_hp[5] += 1;  g_hp[6] += (hit || words[15]) ? 1 : 0;
+  g_hp[7] += hit ? 1 : 0;
   return LAMMCU_OK;
 }
 

@@ -7,7 +7,7 @@ import os
 import numpy as np
 import pytest
 from conftest import GOLDEN, golden, make_x, tol_c
-from oracle_lib import F32, KQ_TYPES, Q2_K, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES, row_size
+from oracle_lib import F32, KQ_TYPES, Q2_K, Q4_1, Q8_0, Q8_1, Q8_K, TYPE_NAMES, VEC_DOT, W_TYPES, row_size
 
 pytestmark = pytest.mark.gpu
 QTYPES = [t for t in W_TYPES if t != F32]
@@ -296,6 +296,75 @@ def test_operator_decode_repeated_rows(gpu, oracle, t):
     finally:
         lib.lammcu_set_server_timeouts(200, 5000)
         lib.lammcu_set_host_mode(default_mode)
+
+
+@pytest.mark.parametrize("t", [Q4_1, Q8_0, Q2_K])
+def test_operator_sibling_speculation(gpu, oracle, t):
+    """Host mode 1 learns which weight followed which with a bit-identical row (ggml: wq -> wk -> wv, gate -> up) and
+    posts the followers' jobs behind the first one; a following call is answered from such a job only when it is for
+    the predicted weight AND its row memcmp-equals the row the job used.  A decoder-layer-like call sequence over
+    several tokens (fresh rows every token) must equal mode 0 bit for bit, with hits from the second token on; so must
+    every way of breaking the prediction: a sibling skipped, a sibling's row edited in place, another weight in
+    between, the same weight twice, weights forgotten and re-registered, and a server that dies after every job."""
+    lib = gpu.lib()
+    k, kf = 2048, 5632
+    shapes = {"q": (512, k), "k": (136, k), "v": (136, k), "o": (512, k), "gate": (700, k), "up": (700, k), "down": (512, kf)}
+    ws = {n: weights(oracle, t, m, kk, seed=17 * m + kk + i) for i, (n, (m, kk)) in enumerate(shapes.items())}
+    rng = np.random.default_rng(7 + t)
+    default_mode = lib.lammcu_get_host_mode()
+    prof = (C.c_double * 8)()
+
+    def token(rows, order, edit=None):
+        out = []
+        for j, name in enumerate(order):
+            x = rows["f"] if name == "down" else rows[{"q": "a", "k": "a", "v": "a", "o": "b", "gate": "c", "up": "c"}[name]]
+            if edit is not None and edit[0] == j:
+                x = x.copy()
+                x[0, edit[1]] += 0.75
+            can, c = gpu.lamm_mul_mat_host(t, ws[name], x, nth=1)
+            assert can
+            out.append(c)
+        return out
+    layer = ["q", "k", "v", "o", "gate", "up", "down"]
+    cases = [(layer, None)] * 4 + [
+        (["q", "v", "k", "o", "gate", "down", "up"], None),            # siblings out of order, another weight in between
+        (layer, None), (layer, (1, 0)), (layer, (2, k - 1)), (layer, (5, 7)),      # a sibling's row differs in one element
+        (["q", "q", "k", "k", "v", "o", "gate", "gate", "up", "down"], None),   # the same weight twice in a row
+        (layer, None), (layer, None)]
+    toks = [{n: rng.standard_normal((1, kk)).astype(np.float32) for n, kk in (("a", k), ("b", k), ("c", k), ("f", kf))}
+            for _ in cases]
+    try:
+        def run(mode):
+            assert lib.lammcu_set_host_mode(mode) == 0
+            return [token(rows, order, edit) for rows, (order, edit) in zip(toks, cases)]
+        ref = run(0)
+        want = oracle.mul_mat(t, ws["q"], toks[0]["a"])
+        assert np.abs(ref[0][0] - want).max() <= tol_c(want, k)
+        assert lib.lammcu_set_server_timeouts(100000, 4000000) == 0       # one instance for the whole run
+        lib.lammcu_host_profile(prof, 1)
+        got = run(1)
+        lib.lammcu_host_profile(prof, 1)
+        for i, (g, r) in enumerate(zip(got, ref)):
+            for j, (a, b) in enumerate(zip(g, r)):
+                assert np.array_equal(a, b), f"{TYPE_NAMES[t]} token {i} call {j}"
+        assert prof[7] >= 3 * 3, f"speculative hits: {prof[7]} (k, v, up of tokens 2..4 at least)"
+        # weights forgotten (their device copies freed) between tokens: every learned link must die with them
+        assert lib.lammcu_weight_forget_all() == 0
+        got = run(1)
+        for i, (g, r) in enumerate(zip(got, ref)):
+            for j, (a, b) in enumerate(zip(g, r)):
+                assert np.array_equal(a, b), f"{TYPE_NAMES[t]} token {i} call {j} (after forget_all)"
+        assert lib.lammcu_host_quiesce() == 0
+        assert lib.lammcu_set_server_timeouts(1, 10) == 0                 # nearly every job meets a new instance
+        for rep in range(2):
+            got = run(1)
+            for i, (g, r) in enumerate(zip(got, ref)):
+                for j, (a, b) in enumerate(zip(g, r)):
+                    assert np.array_equal(a, b), f"{TYPE_NAMES[t]} token {i} call {j} (short-lived server, pass {rep})"
+    finally:
+        lib.lammcu_set_server_timeouts(200, 5000)
+        lib.lammcu_set_host_mode(default_mode)
+        lib.lammcu_weight_forget_all()
 
 
 # ---------------------------------------------------------------- single-launch decode kernel (N == 1)
