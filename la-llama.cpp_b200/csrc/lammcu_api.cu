@@ -1200,6 +1200,11 @@ static size_t ll_take(const volatile unsigned long long *ll, size_t n, unsigned 
 
 // Make the resident instance exit and wait for it (a no-op when none is running).
 static void server_stop() {
+  // every path that frees, replaces or rewrites a weight stops the server first: the sibling links learned so far die
+  // here (they hold raw handles), whether or not an instance is resident; one token later they are learned again
+  g_weight_gen++;
+  g_srv.n_spec = 0;
+  g_srv.prev_w = nullptr;
   if (!g_srv.ready || !g_srv.running) return;
   unsigned int words[kSrvWords] = {2u};
   server_post(words);
