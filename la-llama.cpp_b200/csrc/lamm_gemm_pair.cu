@@ -42,96 +42,125 @@ __device__ __forceinline__ void pair_store(const PairParams &p, int64_t off, flo
 }
 
 // F16 weights x fp16 activations: one MMA per K step, no rescaling.
+// PERSISTENT (as gemm_so_kernel): a pair walks tiles cl, cl + ncl, ...; the TMA ring and its barrier phases run on across
+// tiles and the accumulator is double-buffered in TMEM (2 x 256 columns), so a tile's drain and the next tile's first
+// loads hide behind the mainloops.
 template <bool PEERS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1)
 gemm_f16_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_x, const PairParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kPairStages * kPairStageBytes);
-  uint64_t *full = bars, *empty = bars + kPairStages, *acc_full = bars + 2 * kPairStages;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * kPairStages + 2);
+  uint64_t *full = bars, *empty = bars + kPairStages, *acc_full = bars + 2 * kPairStages, *acc_empty = acc_full + 2;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 2);
+  static_assert((2 * kPairStages + 4) * 8 + 4 <= 256, "barrier area");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
-  const int pair = blockIdx.x >> 1;
-  const int n_tiles = (p.N + 255) / 256;
-  const int mt = (pair / n_tiles) * 256, nt = (pair % n_tiles) * 256;
-  const int m0 = mt + (int)rank * 128;                // this CTA's weight rows (A) and accumulator rows
-  const int nb = nt + (int)rank * 128;                // this CTA's half of the activation rows (B)
+  const int cl = (int)(blockIdx.x >> 1), ncl = (int)(gridDim.x >> 1);
+  const int tiles_n = (p.N + 255) / 256, n_tiles = ((p.M + 255) / 256) * tiles_n;
   const int n_stages = p.K / GK;
+  // tile tl: this CTA's weight rows (A) = its accumulator rows; first accumulator column; its half of the activation rows (B)
+  auto tile_m0 = [&](int tl) { return (tl / tiles_n) * 256 + (int)rank * 128; };
+  auto tile_n0 = [&](int tl) { return (tl % tiles_n) * 256; };
   if (threadIdx.x == 0) {
     for (int i = 0; i < kPairStages; i++) {
       mbar_init(&full[i], 1);                          // the leader's own arrive.expect_tx (bytes of both CTAs)
       mbar_init(&empty[i], 1);                         // multicast MMA commit
     }
-    mbar_init(acc_full, 1);
+    for (int i = 0; i < 2; i++) {
+      mbar_init(&acc_full[i], 1);                      // multicast MMA commit: accumulator i holds a finished tile
+      mbar_init(&acc_empty[i], 8);                     // the four epilogue warps of both CTAs have drained it (leader's copy counts)
+    }
     fence_barrier_init();
     prefetch_tmap(&tm_a);
     prefetch_tmap(&tm_x);
   }
   __syncthreads();
   cluster_sync_all();                                  // barriers of both CTAs exist before anything remote touches them
-  if (warp == 1) tmem_alloc_pair(tmem_slot, 256);
+  if (warp == 1) tmem_alloc_pair(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   if (warp == 0) {
     if (lane == 0) {
-      for (int st = 0; st < n_stages; st++) {
-        const int s = st % kPairStages;
-        uint8_t *stage = smem + s * kPairStageBytes;
-        mbar_wait(&empty[s], ((uint32_t)(st / kPairStages) & 1u) ^ 1u);
-        if (rank == 0) mbar_arrive_expect_tx(&full[s], (uint32_t)(2 * kPairStageBytes));
-        const uint32_t bar = mapa_rank(smem_u32(&full[s]), 0u);
-        tma_load_2d_pair(stage, &tm_a, st * GK, m0, bar);
-        tma_load_2d_pair(stage + GM * GK * 2, &tm_x, st * GK, nb, bar);
+      int gst = 0;                                     // ring stages so far, over all tiles
+      for (int tl = cl; tl < n_tiles; tl += ncl) {
+        const int m0 = tile_m0(tl), nb = tile_n0(tl) + (int)rank * 128;
+        for (int st = 0; st < n_stages; st++, gst++) {
+          const int s = gst % kPairStages;
+          uint8_t *stage = smem + s * kPairStageBytes;
+          mbar_wait(&empty[s], ((uint32_t)(gst / kPairStages) & 1u) ^ 1u);
+          if (rank == 0) mbar_arrive_expect_tx(&full[s], (uint32_t)(2 * kPairStageBytes));
+          const uint32_t bar = mapa_rank(smem_u32(&full[s]), 0u);
+          tma_load_2d_pair(stage, &tm_a, st * GK, m0, bar);
+          tma_load_2d_pair(stage + GM * GK * 2, &tm_x, st * GK, nb, bar);
+        }
       }
     }
   } else if (warp == 1) {
     if (lane == 0 && rank == 0) {
-      for (int st = 0; st < n_stages; st++) {
-        const int s = st % kPairStages;
-        mbar_wait(&full[s], (uint32_t)(st / kPairStages) & 1u);
+      int gst = 0, it = 0;
+      for (int tl = cl; tl < n_tiles; tl += ncl, it++) {
+        const int ab = it & 1;                         // accumulator buffer of this tile
+        mbar_wait_cluster(&acc_empty[ab], ((uint32_t)(it >> 1) & 1u) ^ 1u);
         tc_fence_after();
-        const uint32_t base = smem_u32(smem + s * kPairStageBytes);
-        const uint64_t a = make_sw128_desc(base), b = make_sw128_desc(base + GM * GK * 2);
+        const uint32_t tacc = tmem_base + (uint32_t)(ab * 256);
+        for (int st = 0; st < n_stages; st++, gst++) {
+          const int s = gst % kPairStages;
+          mbar_wait(&full[s], (uint32_t)(gst / kPairStages) & 1u);
+          tc_fence_after();
+          const uint32_t base = smem_u32(smem + s * kPairStageBytes);
+          const uint64_t a = make_sw128_desc(base), b = make_sw128_desc(base + GM * GK * 2);
 #pragma unroll
-        for (int kk = 0; kk < 4; kk++)
-          umma_f16_pair(tmem_base, a + (uint64_t)(kk * 2), b + (uint64_t)(kk * 2), kIdescF16Pair, (st | kk) ? 1u : 0u);
-        umma_commit_pair(&empty[s]);
+          for (int kk = 0; kk < 4; kk++)
+            umma_f16_pair(tacc, a + (uint64_t)(kk * 2), b + (uint64_t)(kk * 2), kIdescF16Pair, (st | kk) ? 1u : 0u);
+          umma_commit_pair(&empty[s]);
+        }
+        umma_commit_pair(&acc_full[ab]);
       }
-      umma_commit_pair(acc_full);
     }
   } else {
-    // epilogue warps 2..5: TMEM lane quarter = warp & 3; 256 accumulator columns = activation rows nt .. nt + 255
-    const int q4 = warp & 3, row = q4 * 32 + lane, m = m0 + row;
-    mbar_wait(acc_full, 0u);
-    tc_fence_after();
-    const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16);
+    // epilogue warps 2..5: TMEM lane quarter = warp & 3; 256 accumulator columns = activation rows n0 .. n0 + 255
+    const int q4 = warp & 3, row = q4 * 32 + lane;
+    int it = 0;
+    for (int tl = cl; tl < n_tiles; tl += ncl, it++) {
+      const int ab = it & 1, m = tile_m0(tl) + row, n0 = tile_n0(tl);
+      mbar_wait(&acc_full[ab], (uint32_t)(it >> 1) & 1u);
+      tc_fence_after();
+      const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(ab * 256);
 #pragma unroll 2
-    for (int c16 = 0; c16 < 16; c16++) {
-      uint32_t v[16];
-      asm volatile(
-          "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-            "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-          : "r"(tbase + (uint32_t)(c16 * 16))
-          : "memory");
-      tmem_ld_wait();
-      if (m < p.M) {
+      for (int c16 = 0; c16 < 16; c16++) {
+        uint32_t v[16];
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+              "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+            : "r"(tbase + (uint32_t)(c16 * 16))
+            : "memory");
+        tmem_ld_wait();
+        if (m < p.M) {
 #pragma unroll
-        for (int i = 0; i < 16; i++) {
-          const int n = nt + c16 * 16 + i;
-          if (n < p.N) pair_store<PEERS>(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]));
+          for (int i = 0; i < 16; i++) {
+            const int n = n0 + c16 * 16 + i;
+            if (n < p.N) pair_store<PEERS>(p, (int64_t)n * p.ldc + m, __uint_as_float(v[i]));
+          }
         }
+      }
+      // the buffer goes back to the MMA issuer: every lane's tcgen05.ld has completed (wait::ld above)
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (rank == 0) mbar_arrive(&acc_empty[ab]);
+        else mbar_arrive_cluster(mapa_rank(smem_u32(&acc_empty[ab]), 0u));
       }
     }
   }
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();                                  // the peer's shared memory and TMEM outlive the leader's MMAs
-  if (warp == 1) tmem_dealloc_pair(tmem_base, 256);
+  if (warp == 1) tmem_dealloc_pair(tmem_base, 512);
 }
 
 bool gemm_f16_pair_supported(int64_t M, int64_t N, int64_t K) {
@@ -161,9 +190,10 @@ int launch_gemm_f16_pair(const void *w, int64_t w_stride, const void *xq, int64_
     if (e != cudaSuccess) { set_error("gemm_f16_pair: cudaFuncSetAttribute(%d): %s", kPairSmem, cudaGetErrorString(e)); return LAMMCU_ERR_CUDA; }
     attr_set = true;
   }
-  const int pairs = (int)(((M + 255) / 256) * ((N + 255) / 256));
-  if (p.n_peer) gemm_f16_pair_kernel<true><<<2 * pairs, 192, kPairSmem, st>>>(tm_a, tm_x, p);
-  else gemm_f16_pair_kernel<false><<<2 * pairs, 192, kPairSmem, st>>>(tm_a, tm_x, p);
+  const int pairs = (int)(((M + 255) / 256) * ((N + 255) / 256)), slots = sm_count_cached() / 2;
+  const int grid = 2 * (pairs < slots ? pairs : slots);                // persistent: one pair per TPC walks the tiles
+  if (p.n_peer) gemm_f16_pair_kernel<true><<<grid, 192, kPairSmem, st>>>(tm_a, tm_x, p);
+  else gemm_f16_pair_kernel<false><<<grid, 192, kPairSmem, st>>>(tm_a, tm_x, p);
   g_launch_count++;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("gemm_f16_pair launch: %s", cudaGetErrorString(e)); return LAMMCU_ERR_CUDA; }

@@ -63,6 +63,32 @@ def test_mul_mat_vs_oracle(gpu, oracle, m, n, k):
     assert err <= tol_c(want, k), f"f16 {m}x{n}x{k}: err {err} tol {tol_c(want, k)}"
 
 
+def test_pair_kernel_walks_several_tiles(gpu, oracle):
+    """The CTA-pair F16 kernel is persistent: 2500 x 2100 is 10 x 9 = 90 pair tiles on 74 pair slots, so some pairs walk
+    two tiles (ring phases run on, the second tile lands in the other accumulator buffer, the drain of the first hands
+    its buffer back); ragged in M (the last pair's peer CTA lies beyond M) and in N.  Oracle on a row sample; the whole
+    result must also equal the single-CTA kernel's to summation-order noise."""
+    import os
+    m, n, k = 2500, 2100, 320
+    w = f16_weights(m, k, seed=9)
+    rng = np.random.default_rng(10)
+    x = make_x(rng, n, k)
+    rows = np.unique(np.r_[0:3, 127:130, 255:258, 2300:2310, m - 3:m, rng.integers(0, m, 40)])
+    want = oracle.mul_mat(F16, w[rows], x)
+    got = gpu.mul_mat(F16, dev(w), dev(x)).cpu().numpy()
+    assert np.abs(got[:, rows] - want).max() <= tol_c(want, k)
+    old = os.environ.get("LAMM_GEMM_PAIR")
+    os.environ["LAMM_GEMM_PAIR"] = "0"
+    try:
+        single = gpu.mul_mat(F16, dev(w), dev(x)).cpu().numpy()
+    finally:
+        if old is None:
+            os.environ.pop("LAMM_GEMM_PAIR", None)
+        else:
+            os.environ["LAMM_GEMM_PAIR"] = old
+    assert np.abs(got - single).max() <= 0.05 * tol_c(want, k)
+
+
 def test_prefill_kernel_is_the_tensor_core_one(gpu, oracle):
     """N >= the GEMM threshold with 16-byte aligned rows: convert + ONE tcgen05 kernel (2 launches); the products
     of two halves are exact in the f32 accumulator, so the result is far inside the tolerance."""
