@@ -1113,7 +1113,10 @@ static int server_setup() {
   CU_TRY(cudaMemset(g_srv.x_ll, 0, kSrvMaxK * 8));
   CU_TRY(cudaMemset(g_srv.ctrs, 0, 256));
   CU_TRY(cudaDeviceSynchronize());
-  g_srv.seq = 0;
+  // job tags are 32-bit and only ever compared for equality / signed distance; LAMM_SERVER_SEQ0 starts them elsewhere
+  // (test knob: tests/test_gpu_parity.py crosses the restart below in a few hundred calls)
+  const char *seq0 = getenv("LAMM_SERVER_SEQ0");
+  g_srv.seq = seq0 ? (unsigned int)strtoul(seq0, nullptr, 10) : 0u;
   g_srv.ready = true;
   return LAMMCU_OK;
 }
@@ -1234,6 +1237,21 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
   unsigned int *words = jobs[0];
   if ((rc = decode_server_job(w->type, w->dev, w->stride, rows, K, words))) return rc;
   if (g_srv.running && g_srv.type != w->type) server_stop();
+  // Tags restart from 1 long before they could wrap (4e9 jobs = half a day of uninterrupted decoding): tag 0 means
+  // "nothing" in the mailbox, in pre_tag and in done[1].  Everything stale then carries a huge tag, never a small one.
+  if (g_srv.seq > 0xffffff00u) {
+    server_stop();
+    // no pair anywhere may still carry a small tag from the first hours of the process (a result entry beyond the
+    // rows of every later job in its slot would): wipe every tagged buffer once
+    memset((void *)g_srv.mbox, 0, (size_t)kSrvSlots * kSrvWords * 8);
+    memset((void *)g_srv.c_ll, 0, kSrvSlots * kSrvMaxM * 8);
+    CU_TRY(cudaMemset(g_srv.mbox_dev, 0, (size_t)kSrvSlots * kSrvWords * 8));
+    CU_TRY(cudaMemset(g_srv.x_ll, 0, kSrvMaxK * 8));
+    CU_TRY(cudaDeviceSynchronize());
+    g_srv.seq = 0;
+    g_srv.done[1] = 0;
+    g_srv.launch_seq0 = 0;
+  }
   if (g_srv.running && server_exited()) {            // it idled out (or reached its lifetime) since the last call
     g_srv.running = false;
     g_srv.n_spec = 0;

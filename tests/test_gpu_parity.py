@@ -367,6 +367,47 @@ def test_operator_sibling_speculation(gpu, oracle, t):
         lib.lammcu_weight_forget_all()
 
 
+def test_operator_tag_restart(gpu, oracle):
+    """Job tags of the resident server are 32-bit; the host path restarts them from 1 (server stopped, every tagged
+    buffer wiped) before they could wrap.  A child process whose tags start just below that point makes a few hundred
+    host-tensor calls across it -- siblings, repeated rows and new rows -- and every result must equal the
+    launch-per-call mode's bits."""
+    import subprocess
+    import sys
+    child = r"""
+import os, sys
+sys.path.insert(0, %(root)r); sys.path.insert(0, os.path.join(%(root)r, "tests"))
+import numpy as np
+import lamm_b200 as L
+from oracle_lib import Oracle, Q4_1
+L.init(0)
+lib = L.lib()
+o = Oracle()
+rng = np.random.default_rng(3)
+ws = [o.quantize_weights(Q4_1, rng.standard_normal((m, 1024)).astype(np.float32), seed=m) for m in (300, 132, 132, 640)]
+seq = [0, 1, 2, 3]
+def run(mode, n):
+    assert lib.lammcu_set_host_mode(mode) == 0
+    r = np.random.default_rng(9)
+    out = []
+    for i in range(n):
+        xa, xb = r.standard_normal((1, 1024)).astype(np.float32), r.standard_normal((1, 1024)).astype(np.float32)
+        for wi in seq:
+            can, c = L.lamm_mul_mat_host(Q4_1, ws[wi], xa if wi < 3 else xb, nth=1)
+            assert can
+            out.append(c)
+    return out
+ref = run(0, 60)
+got = run(1, 60)
+bad = [i for i, (a, b) in enumerate(zip(got, ref)) if not np.array_equal(a, b)]
+print("calls", len(got), "bad", bad[:5])
+sys.exit(1 if bad else 0)
+""" % {"root": os.path.dirname(os.path.dirname(os.path.abspath(__file__)))}
+    env = dict(os.environ, LAMM_SERVER_SEQ0=str(0xffffff00 - 100))
+    r = subprocess.run([sys.executable, "-c", child], env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
 # ---------------------------------------------------------------- single-launch decode kernel (N == 1)
 DECODE_SHAPES = [(33, 4096), (1, 256), (7, 512), (300, 11008), (64, 5120), (50, 17920), (9, 6656),
                  (1185, 4096), (2500, 1024), (129, 13824)]
