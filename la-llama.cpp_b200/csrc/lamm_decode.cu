@@ -1220,6 +1220,11 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_launch));
   // CTA 0: pre_tag[slot] = tag of a job it has ALREADY republished into that device slot while accepting an earlier one
   __shared__ unsigned int pre_tag[kSrvSlots];
+  // Every CTA: the job AFTER the one it is accepting, when that was already in the device mailbox (read by the idle
+  // half of the warp in the same load): the next iteration starts from this stash without another L2 round trip.
+  __shared__ unsigned int jn[kSrvWords];
+  __shared__ unsigned int jn_tag;
+  if (tid == 0) jn_tag = 0u;
   if (tid < kSrvSlots) pre_tag[tid] = 0u;
   __syncthreads();
   for (unsigned int s = sp.seq0;; ++s) {
@@ -1227,9 +1232,14 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
     const int slot = (int)(s % (unsigned int)kSrvSlots);
     if (warp == 0) {
       const bool pre = bid == 0 && pre_tag[slot] == s;     // accepted with an earlier job: in the device mailbox already
+      const bool stashed = jn_tag == s;                   // (tags are never 0: lammcu_api.cu restarts them before the wrap)
       unsigned long long v = 0, t0, now;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-      if (bid == 0 && !pre) {
+      __syncwarp();
+      if (stashed) {
+        if (lane < kSrvWords) jw[lane] = jn[lane];
+        if (lane == 0) jn_tag = 0u;
+      } else if (bid == 0 && !pre) {
         // The host mailbox, all kSrvSlots x 16 pairs per poll (one PCIe round trip either way): lane l holds pair l of
         // slots 0/1 (v0) and of slots 2/3 (v1).  Bounded lifetime: a caller that never pauses must not starve kernels
         // queued on other streams -- but a job that was republished is never given up (the other CTAs run it).
@@ -1270,24 +1280,37 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
               if (lane == 0) pre_tag[sl] = s + (unsigned int)d;
             }
           }
+          // the half that holds the NEXT slot goes first, so that a CTA that sees this job usually sees its follower too
+          const bool v1_first = slot == 1;                  // slots 1 -> 2 live in v0 -> v1; 3 -> 0 in v1 -> v0 (v0 first)
+          if (v1_first && ((pub >> sl1) & 1u)) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + 32 + lane), "l"(v1) : "memory");
           if ((pub >> sl0) & 1u) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + lane), "l"(v0) : "memory");
-          if ((pub >> sl1) & 1u) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + 32 + lane), "l"(v1) : "memory");
+          if (!v1_first && ((pub >> sl1) & 1u)) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(sp.mbox_dev + 32 + lane), "l"(v1) : "memory");
           if (sl0 == slot) jw[lane & 15] = (unsigned int)v0;
           if (sl1 == slot) jw[lane & 15] = (unsigned int)v1;
+          const int sln = (slot + 1) % kSrvSlots;
+          if ((pub >> sln) & 1u) {
+            if (sl0 == sln) jn[lane & 15] = (unsigned int)v0;
+            if (sl1 == sln) jn[lane & 15] = (unsigned int)v1;
+            if (lane == 0) jn_tag = s + 1u;
+          }
         }
       } else {
         // every other CTA (and CTA 0 for a job it republished earlier): the device slot, in L2
-        const unsigned long long *src = sp.mbox_dev + slot * kSrvWords;
+        // lanes 0..15: this job's slot; lanes 16..31: the next slot, in the same load
+        const unsigned long long *src = sp.mbox_dev + (lane < kSrvWords ? slot : (slot + 1) % kSrvSlots) * kSrvWords + (lane & 15);
         bool give_up = false;
         while (true) {
-          if (lane < kSrvWords) asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(src + lane) : "memory");
+          asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(src) : "memory");
           if (__all_sync(0xffffffffu, lane >= kSrvWords || (unsigned int)(v >> 32) == s)) break;
           asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
           __nanosleep(40);
           if (now - t0 > 4000000000ull) { give_up = true; *sp.status = 2u; break; }   // CTA 0 always publishes something
         }
+        const bool nx = !give_up && __all_sync(0xffffffffu, lane < kSrvWords || (unsigned int)(v >> 32) == s + 1u);
         if (give_up) v = ((unsigned long long)s << 32) | (lane == 0 ? 2u : 0u);
         if (lane < kSrvWords) jw[lane] = (unsigned int)v;
+        else if (nx) jn[lane - kSrvWords] = (unsigned int)v;
+        if (nx && lane == 0) jn_tag = s + 1u;
       }
     }
     __syncthreads();
