@@ -4,6 +4,7 @@
 // exported signatures.  There is no CPU fallback: without a device every
 // compute entry point returns LAMMCU_ERR_NO_DEVICE.
 #include "lamm_common.cuh"
+#include "lamm_sibling.h"
 #include "lamm_xop.cuh"
 #include <algorithm>
 #include <chrono>
@@ -145,11 +146,8 @@ struct ServerState {
   unsigned long long *mbox_dev = nullptr, *x_ll = nullptr;
   unsigned int *ctrs = nullptr;                    // [2] status
   unsigned long long *trace = nullptr;             // LAMM_SERVER_TRACE=1: [64][8] device time stamps
-  // speculative sibling jobs posted behind the last real job, in tag order (see mul_mat_host_server)
-  struct { unsigned int tag; lammcu_weight *w; } spec[2];
-  int n_spec = 0;
-  lammcu_weight *prev_w = nullptr;                 // weight of the previous call (sibling learning)
-  unsigned long long prev_gen = 0;
+  // sibling speculation: what was learned / posted (lamm_sibling.h; see mul_mat_host_server)
+  lamm::SibTracker<lammcu_weight> sib;
   int64_t row_k = 0;                               // K of the row that x_host holds (whatever instance saw it)
   unsigned int launch_seq0 = 0;                    // first tag of the instance believed to be resident
 };
@@ -1161,7 +1159,7 @@ static int server_launch(int type, unsigned int seq0) {
   g_srv.launch_seq0 = seq0;
   g_srv.type = type;
   g_srv.x_k = 0;                                     // a fresh instance has nothing staged
-  g_srv.n_spec = 0;                                  // ... and never looks at older tags
+  g_srv.sib.drop_posted();                           // ... and never looks at older tags
   return LAMMCU_OK;
 }
 
@@ -1206,15 +1204,13 @@ static void server_stop() {
   // every path that frees, replaces or rewrites a weight stops the server first: the sibling links learned so far die
   // here (they hold raw handles), whether or not an instance is resident; one token later they are learned again
   g_weight_gen++;
-  g_srv.n_spec = 0;
-  g_srv.prev_w = nullptr;
+  g_srv.sib.reset();
   if (!g_srv.ready || !g_srv.running) return;
   unsigned int words[kSrvWords] = {2u};
   server_post(words);
   cudaStreamSynchronize(g_dev.stream);
   g_srv.running = false;
-  g_srv.n_spec = 0;
-  g_srv.prev_w = nullptr;
+  g_srv.sib.reset();
 }
 
 // N == 1, operands the decode kernel takes
@@ -1254,7 +1250,7 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
   }
   if (g_srv.running && server_exited()) {            // it idled out (or reached its lifetime) since the last call
     g_srv.running = false;
-    g_srv.n_spec = 0;
+    g_srv.sib.drop_posted();
     g_srv.x_k = 0;
     // it left an EXIT word under the tag it was waiting for in the device mailbox: never issue that tag again, a new
     // instance's CTAs would take the stale word for their first job
@@ -1268,24 +1264,11 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
   const bool row_eq = g_srv_x_reuse && g_srv.row_k == K && memcmp(g_srv.x_host, x_host, (size_t)K * 4) == 0;
   const bool same = row_eq && g_srv.running && g_srv.x_k == K;
   // learn: the previous call's weight was followed by this one with the same row (or not)
-  if (g_srv.prev_w && g_srv.prev_gen == g_weight_gen) {
-    g_srv.prev_w->sib = row_eq ? w : nullptr;
-    g_srv.prev_w->sib_gen = g_weight_gen;
-  }
-  g_srv.prev_w = w;
-  g_srv.prev_gen = g_weight_gen;
+  g_srv.sib.learn(w, row_eq, g_weight_gen);
   unsigned int s = 0;
-  bool hit = false;
-  if (g_srv.n_spec > 0) {
-    if (same && g_srv.spec[0].w == w) {
-      hit = true;                                    // the job is already posted (possibly already answered)
-      s = g_srv.spec[0].tag;
-      g_srv.spec[0] = g_srv.spec[1];
-      g_srv.n_spec--;
-    } else {
-      g_srv.n_spec = 0;                              // mispredicted: whatever those jobs produce is ignored
-    }
-  }
+  // hit: the job is already posted (possibly already answered); a misprediction empties the queue -- whatever those
+  // jobs produce is ignored
+  const bool hit = g_srv.sib.take_hit(w, same, &s);
   const double t1 = now_us();
   if (!hit) {
     if (!row_eq) {
@@ -1296,27 +1279,23 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
     g_srv.x_k = 0;
     // the followers this weight had last time (same type / K: they reuse the staged row and the shared-memory plan)
     int n = 1;
+    lammcu_weight *fol[lamm::SibTracker<lammcu_weight>::kMaxFollowers];
     if (g_srv_spec && g_srv_x_reuse && g_srv.running) {
-      lammcu_weight *v = w;
-      while (n < 3) {
-        lammcu_weight *nx = (v->sib && v->sib_gen == g_weight_gen) ? v->sib : nullptr;
-        if (!nx || nx->type != w->type || nx->K != K || (size_t)(nx->row_end - nx->row_begin) > kSrvMaxM) break;
-        if (decode_server_job(nx->type, nx->dev, nx->stride, nx->row_end - nx->row_begin, K, jobs[n])) break;
+      const int nf = g_srv.sib.followers(w, g_weight_gen, (int64_t)kSrvMaxM, fol);
+      for (int j = 0; j < nf; j++) {
+        if (decode_server_job(fol[j]->type, fol[j]->dev, fol[j]->stride, fol[j]->row_end - fol[j]->row_begin, K, jobs[n])) break;
         jobs[n][15] = 1u;
-        g_srv.spec[n - 1].w = nx;
-        v = nx;
         n++;
       }
     }
     server_post_n(jobs, n);
     s = g_srv.seq - (unsigned int)(n - 1);
-    for (int j = 1; j < n; j++) g_srv.spec[j - 1].tag = s + (unsigned int)j;
-    g_srv.n_spec = n - 1;
+    g_srv.sib.posted(s + 1u, fol, n - 1);
     // An instance that gave up waiting for tag s has left an EXIT word with that tag in the device
     // mailbox: the job is re-posted under a fresh tag before a new instance is launched.
     if (g_srv.running && server_missed(s)) {
       g_srv.running = false;
-      g_srv.n_spec = 0;
+      g_srv.sib.drop_posted();
       words[15] = 0u;
       server_post(words);
       s = g_srv.seq;
@@ -1336,7 +1315,7 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
     __builtin_ia32_pause();
     asm volatile("" ::: "memory");                                      // re-read the pairs
     if (server_missed(s)) {                                             // the idle / lifetime exit raced with the post
-      g_srv.n_spec = 0;
+      g_srv.sib.drop_posted();
       words[15] = 0u;                                                   // (x_host holds this row: a hit implies row_eq)
       server_post(words);
       s = g_srv.seq;
@@ -1350,7 +1329,7 @@ static int mul_mat_host_server(lammcu_weight_t w, const float *x_host, float *c_
       else if (now - t_first > 5e6) {
         cudaError_t e = cudaStreamSynchronize(g_dev.stream);
         g_srv.running = false;
-        g_srv.n_spec = 0;
+        g_srv.sib.drop_posted();
         set_error("mul_mat_host: the decode server did not answer job %u (row %zu of %lld, %s)", s, got,
                   (long long)rows, cudaGetErrorString(e));
         return LAMMCU_ERR_CUDA;
