@@ -1304,7 +1304,11 @@ __global__ void __launch_bounds__(kD16Warps * 32, 1) decode_server_kernel(const 
           if (__all_sync(0xffffffffu, lane >= kSrvWords || (unsigned int)(v >> 32) == s)) break;
           asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
           __nanosleep(40);
-          if (now - t0 > 4000000000ull) { give_up = true; *sp.status = 2u; break; }   // CTA 0 always publishes something
+          if (__any_sync(0xffffffffu, now - t0 > 4000000000ull)) {   // one decision for the warp; CTA 0 always publishes something
+            give_up = true;
+            *sp.status = 2u;
+            break;
+          }
         }
         const bool nx = !give_up && __all_sync(0xffffffffu, lane < kSrvWords || (unsigned int)(v >> 32) == s + 1u);
         if (give_up) v = ((unsigned long long)s << 32) | (lane == 0 ? 2u : 0u);
